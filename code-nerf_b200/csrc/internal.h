@@ -1,0 +1,32 @@
+// Internal C++ interfaces between the translation units of libcnrf.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+// ---- sgemm.cu : fp32 SIMT GEMM toolkit -------------------------------------------------------------------------
+// C(m,n) = epi( sum_k A(m,k) * B(k,n) ),  A(m,k) = A[m*a_rs + k*a_cs],  B(k,n) = B[k*b_rs + n*b_cs], C row-major (ldc).
+struct GemmArgs {
+  const float* A = nullptr; int64_t a_rs = 0, a_cs = 0;
+  const float* B = nullptr; int64_t b_rs = 0, b_cs = 0;
+  float* C = nullptr; int64_t ldc = 0;
+  int64_t M = 0; int N = 0; int64_t K = 0;
+  // epilogue: + bias[((m / bias_div) % bias_mod) * ld_bias + n], relu, * (mask(m,n) > 0)
+  const float* bias = nullptr; int64_t ld_bias = 0; int64_t bias_div = 1; int64_t bias_mod = INT64_MAX;
+  int relu = 0;
+  const float* mask = nullptr; int64_t ld_mask = 0;
+  int accumulate = 0;   // C += result (no bias/relu/mask)
+  int split_k = 1;      // > 1: partial sums are atomically added into C, which the caller zero-fills
+};
+int cnrf_sgemm(const GemmArgs& a, cudaStream_t st);
+// out[g*ld_out + n] = sum_{q<Q} X[(g*g_stride + q*q_stride)*ld_x + n],  g < G, n < N
+int cnrf_strided_rowsum(const float* X, int64_t ld_x, int64_t G, int64_t g_stride, int64_t Q, int64_t q_stride, int N,
+                        float* out, int64_t ld_out, cudaStream_t st);
+// out[n] = sum_m X[m*ld_x + n]  (out is zero-filled by the callee)
+int cnrf_colsum(const float* X, int64_t ld_x, int64_t M, int N, float* out, cudaStream_t st);
+int cnrf_fill_zero(void* p, size_t bytes, cudaStream_t st);
+
+// ---- posembed.cu -------------------------------------------------------------------------------------------------
+int cnrf_pos_embed_fwd_ld(const float* x, int64_t M, int D, const float* freqs, int L, int inc, int64_t ld_out,
+                          float* out, cudaStream_t st);
+int cnrf_pos_embed_bwd_ld(const float* x, const float* g_out, int64_t M, int D, const float* freqs, int L, int inc,
+                          int64_t ld_g, float* g_x, cudaStream_t st);

@@ -1,0 +1,256 @@
+// Stratified + hierarchical sampling: PointSampler.sample_uniform / .sample_pdf
+// (view_synthesis/nerf/point_sampler.py:49-120).  One warp per ray.
+//   sample_uniform : z = lower + (upper-lower)*t  and pts = ro + rd*z, float4 stores of the packed (S,3) row.
+//   sample_pdf     : warp-scan CDF in registers -> staged in shared memory, per-lane binary search for
+//                    searchsorted(right=True), lerp, in-warp bitonic sort of [z_coarse | samples], float4 stores.
+// Multiplies and adds are kept un-fused (__fmul_rn/__fadd_rn) wherever the reference's eager ops are, so that given
+// an identical CDF the samples, sorted depths and points are bit-identical to the reference.
+#include "common.cuh"
+#include <math_constants.h>
+
+constexpr int WARPS_PER_BLOCK = 4;
+
+// pts row writer: the ray's S*3 floats are contiguous; element e -> (s = e/3, c = e%3).
+__device__ __forceinline__ void write_points(float* __restrict__ dst, const float* zsm, int S, float ro0, float ro1,
+                                             float ro2, float rd0, float rd1, float rd2, int lane) {
+  const int total = S * 3;
+  auto val = [&](int e) {
+    int s = e / 3, c = e - 3 * s;
+    float o = c == 0 ? ro0 : (c == 1 ? ro1 : ro2);
+    float d = c == 0 ? rd0 : (c == 1 ? rd1 : rd2);
+    return __fadd_rn(o, __fmul_rn(d, zsm[s]));           // ro + rd * z  (point_sampler.py:70,118)
+  };
+  if ((total & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+    float4* d4 = reinterpret_cast<float4*>(dst);
+    for (int q = lane; q < total / 4; q += 32) {
+      int e = q * 4;
+      d4[q] = make_float4(val(e), val(e + 1), val(e + 2), val(e + 3));
+    }
+  } else {
+    for (int e = lane; e < total; e += 32) dst[e] = val(e);
+  }
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+sample_uniform_kernel(const float* __restrict__ ro, const float* __restrict__ rd, int64_t N, int S,
+                      const float* __restrict__ z_table, const float* __restrict__ lower,
+                      const float* __restrict__ upper, const float* __restrict__ t_rand, float* __restrict__ pts,
+                      float* __restrict__ z_out) {
+  extern __shared__ float smem[];
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* zsm = smem + (size_t)wid * S;
+  int64_t n = (int64_t)blockIdx.x * WARPS_PER_BLOCK + wid;
+  if (n >= N) return;
+  for (int s = lane; s < S; s += 32) {
+    float z;
+    if (t_rand) {
+      float lo = lower[s], up = upper[s];
+      z = __fadd_rn(lo, __fmul_rn(__fsub_rn(up, lo), t_rand[n * S + s]));   // point_sampler.py:65
+    } else {
+      z = z_table[s];                                                        // point_sampler.py:67
+    }
+    zsm[s] = z;
+    z_out[n * S + s] = z;
+  }
+  __syncwarp();
+  write_points(pts + n * (int64_t)S * 3, zsm, S, ro[n * 3], ro[n * 3 + 1], ro[n * 3 + 2], rd[n * 3], rd[n * 3 + 1],
+               rd[n * 3 + 2], lane);
+}
+
+// d ro = sum_s g_pts ; d rd = sum_s g_pts * z.  One warp per ray.
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+points_bwd_kernel(const float* __restrict__ g_pts, const float* __restrict__ z, int64_t N, int S,
+                  float* __restrict__ g_ro, float* __restrict__ g_rd) {
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  int64_t n = (int64_t)blockIdx.x * WARPS_PER_BLOCK + wid;
+  if (n >= N) return;
+  float a[3] = {0.f, 0.f, 0.f}, b[3] = {0.f, 0.f, 0.f};
+  const float* g = g_pts + n * (int64_t)S * 3;
+  for (int s = lane; s < S; s += 32) {
+    float zz = z[n * S + s];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float v = g[s * 3 + c];
+      a[c] += v;
+      b[c] += v * zz;
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    a[c] = warp_sum(a[c]);
+    b[c] = warp_sum(b[c]);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      g_ro[n * 3 + c] = a[c];
+      g_rd[n * 3 + c] = b[c];
+    }
+  }
+}
+
+// searchsorted(cdf, u, right=True): number of entries <= u in a non-decreasing row (point_sampler.py:101).
+__device__ __forceinline__ int upper_bound_smem(const float* cdf, int C, float u) {
+  int lo = 0, hi = C;
+  while (lo < hi) {
+    int mid = (lo + hi) >> 1;
+    if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// inverse-CDF sample for one u given the row's cdf and bins in shared memory (point_sampler.py:101-113)
+__device__ __forceinline__ float invert_one(const float* cdf, const float* bins, int C, float u, int* ind_out) {
+  int ind = upper_bound_smem(cdf, C, u);
+  int below = max(0, ind - 1), above = min(C - 1, ind);
+  float cb = cdf[below], ca = cdf[above], bb = bins[below], ba = bins[above];
+  float denom = __fsub_rn(ca, cb);
+  denom = denom < 1e-5f ? 1.0f : denom;
+  float t = __fdiv_rn(__fsub_rn(u, cb), denom);
+  *ind_out = ind;
+  return __fadd_rn(bb, __fmul_rn(t, __fsub_rn(ba, bb)));
+}
+
+// in-warp bitonic sort of P (power of two) floats in shared memory, ascending
+__device__ __forceinline__ void bitonic_sort_smem(float* a, int P, int lane) {
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = lane; i < P; i += 32) {
+        int l = i ^ j;
+        if (l > i) {
+          float x = a[i], y = a[l];
+          bool up = (i & k) == 0;
+          if ((x > y) == up) { a[i] = y; a[l] = x; }
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+sample_pdf_kernel(const float* __restrict__ ro, const float* __restrict__ rd, const float* __restrict__ weights,
+                  int64_t w_stride, const float* __restrict__ z_coarse, int64_t N, int Sc, int Nf, int P,
+                  const float* __restrict__ u_in, float* __restrict__ pts, float* __restrict__ z_out,
+                  float* __restrict__ cdf_out, int64_t* __restrict__ inds_out) {
+  extern __shared__ float smem[];
+  const int C = Sc - 1;                                     // entries in cdf and bins
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* cdf = smem + (size_t)wid * (2 * C + P);
+  float* bins = cdf + C;
+  float* zs = bins + C;                                     // P floats: [z_coarse | samples | +inf pad]
+  int64_t n = (int64_t)blockIdx.x * WARPS_PER_BLOCK + wid;
+  if (n >= N) return;
+  const float* w = weights + n * w_stride;
+  const float* zc = z_coarse + n * (int64_t)Sc;
+  const int S = Sc + Nf;
+
+  // pdf normaliser: sum(w + 1e-5)   (point_sampler.py:86-87)
+  float part = 0.f;
+  for (int j = lane; j < C - 1; j += 32) part += __fadd_rn(w[j], 1e-5f);
+  float total = warp_sum(part);
+  // cdf = [0, cumsum(pdf)]  (point_sampler.py:88-89): chunked warp scan with carry
+  if (lane == 0) cdf[0] = 0.f;
+  float carry = 0.f;
+  for (int base = 0; base < C - 1; base += 32) {
+    int j = base + lane;
+    float p = j < C - 1 ? __fdiv_rn(__fadd_rn(w[j], 1e-5f), total) : 0.f;
+    float inc = warp_scan_inclusive(p, lane) + carry;
+    if (j < C - 1) cdf[j + 1] = inc;
+    carry = __shfl_sync(FULL_MASK, inc, 31);
+  }
+  for (int j = lane; j < C; j += 32) bins[j] = __fmul_rn(0.5f, __fadd_rn(zc[j + 1], zc[j]));  // :85
+  for (int j = lane; j < Sc; j += 32) zs[j] = zc[j];
+  for (int j = S + lane; j < P; j += 32) zs[j] = CUDART_INF_F;
+  __syncwarp();
+  if (cdf_out) for (int j = lane; j < C; j += 32) cdf_out[n * C + j] = cdf[j];
+
+  for (int k = lane; k < Nf; k += 32) {
+    // u: the caller's rand draw (:93) or linspace(0,1,Nf) (:95): torch's linspace is start + step*k below the midpoint
+    // and end - step*(Nf-1-k) above it.
+    float u;
+    if (u_in) {
+      u = u_in[n * (int64_t)Nf + k];
+    } else {
+      float step = Nf > 1 ? __fdiv_rn(1.0f, (float)(Nf - 1)) : 0.f;
+      u = (k < Nf / 2) ? __fmul_rn(step, (float)k) : __fsub_rn(1.0f, __fmul_rn(step, (float)(Nf - 1 - k)));
+    }
+    int ind;
+    zs[Sc + k] = invert_one(cdf, bins, C, u, &ind);
+    if (inds_out) inds_out[n * (int64_t)Nf + k] = ind;
+  }
+  __syncwarp();
+  bitonic_sort_smem(zs, P, lane);                           // sort(cat(z_vals, z_samples))  (:116)
+  for (int j = lane; j < S; j += 32) z_out[n * (int64_t)S + j] = zs[j];
+  write_points(pts + n * (int64_t)S * 3, zs, S, ro[n * 3], ro[n * 3 + 1], ro[n * 3 + 2], rd[n * 3], rd[n * 3 + 1],
+               rd[n * 3 + 2], lane);
+}
+
+__global__ void __launch_bounds__(WARPS_PER_BLOCK * 32)
+invert_cdf_kernel(const float* __restrict__ cdf_g, const float* __restrict__ bins_g, const float* __restrict__ u,
+                  int64_t N, int C, int K, float* __restrict__ samples, int64_t* __restrict__ inds) {
+  extern __shared__ float smem[];
+  int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* cdf = smem + (size_t)wid * 2 * C;
+  float* bins = cdf + C;
+  int64_t n = (int64_t)blockIdx.x * WARPS_PER_BLOCK + wid;
+  if (n >= N) return;
+  for (int j = lane; j < C; j += 32) { cdf[j] = cdf_g[n * C + j]; bins[j] = bins_g[n * C + j]; }
+  __syncwarp();
+  for (int k = lane; k < K; k += 32) {
+    int ind;
+    float s = invert_one(cdf, bins, C, u[n * (int64_t)K + k], &ind);
+    samples[n * (int64_t)K + k] = s;
+    inds[n * (int64_t)K + k] = ind;
+  }
+}
+
+static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+extern "C" int cnrf_sample_uniform_fwd(const float* ro, const float* rd, int64_t N, int32_t S, const float* z_table,
+                                       const float* lower, const float* upper, const float* t_rand, float* pts,
+                                       float* z, cnrf_stream_t stream) {
+  CNRF_REQUIRE(ro && rd && pts && z, CNRF_E_NULL);
+  CNRF_REQUIRE(t_rand ? (lower && upper) : (z_table != nullptr), CNRF_E_NULL);
+  CNRF_REQUIRE(N > 0 && S > 0 && S <= 4096, CNRF_E_SHAPE);
+  size_t smem = (size_t)WARPS_PER_BLOCK * S * sizeof(float);
+  sample_uniform_kernel<<<grid_for(N, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, smem, as_stream(stream)>>>(
+      ro, rd, N, S, z_table, lower, upper, t_rand, pts, z);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
+extern "C" int cnrf_points_bwd(const float* g_pts, const float* z, int64_t N, int32_t S, float* g_ro, float* g_rd,
+                               cnrf_stream_t stream) {
+  CNRF_REQUIRE(g_pts && z && g_ro && g_rd, CNRF_E_NULL);
+  CNRF_REQUIRE(N > 0 && S > 0, CNRF_E_SHAPE);
+  points_bwd_kernel<<<grid_for(N, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, 0, as_stream(stream)>>>(g_pts, z, N, S, g_ro,
+                                                                                                 g_rd);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
+extern "C" int cnrf_sample_pdf_fwd(const float* ro, const float* rd, const float* weights, int64_t w_stride,
+                                   const float* z_coarse, int64_t N, int32_t Sc, int32_t Nf, const float* u, float* pts,
+                                   float* z, float* cdf_out, int64_t* inds_out, cnrf_stream_t stream) {
+  CNRF_REQUIRE(ro && rd && weights && z_coarse && pts && z, CNRF_E_NULL);
+  CNRF_REQUIRE(N > 0 && Sc >= 3 && Nf > 0 && Sc + Nf <= 2048, CNRF_E_SHAPE);
+  int P = next_pow2(Sc + Nf);
+  size_t smem = (size_t)WARPS_PER_BLOCK * (2 * (Sc - 1) + P) * sizeof(float);
+  CNRF_REQUIRE(smem <= 48 * 1024, CNRF_E_SHAPE);
+  sample_pdf_kernel<<<grid_for(N, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, smem, as_stream(stream)>>>(
+      ro, rd, weights, w_stride, z_coarse, N, Sc, Nf, P, u, pts, z, cdf_out, inds_out);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
+extern "C" int cnrf_invert_cdf(const float* cdf, const float* bins, const float* u, int64_t N, int32_t C, int32_t K,
+                               float* samples, int64_t* inds, cnrf_stream_t stream) {
+  CNRF_REQUIRE(cdf && bins && u && samples && inds, CNRF_E_NULL);
+  CNRF_REQUIRE(N > 0 && C > 0 && K > 0 && C <= 1024, CNRF_E_SHAPE);
+  size_t smem = (size_t)WARPS_PER_BLOCK * 2 * C * sizeof(float);
+  invert_cdf_kernel<<<grid_for(N, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, smem, as_stream(stream)>>>(cdf, bins, u, N, C,
+                                                                                                    K, samples, inds);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}

@@ -1,0 +1,195 @@
+/*
+ * cnrf.h -- C ABI of libcnrf.so, the sm_100a implementation of code-nerf's volumetric-rendering hot path.
+ *
+ * The reference (akashsharma02/code-nerf) is pure Python/PyTorch: it has no FFI.  Its "plugin boundary" for
+ * this path is the Python call surface of view_synthesis.nerf / view_synthesis.models.
+ * Each entry point below states the reference function (file:line, relative to the reference tree) whose
+ * arithmetic it replaces; the drop-in Python package code-nerf_b200/view_synthesis binds them with ctypes
+ * (INTEGRATION.md shows the stub).
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no torch / C++ types cross this boundary.
+ *   - every pointer is a DEVICE pointer unless named host_*; the caller owns every buffer.
+ *   - the library never allocates device memory, never synchronises, never throws; work is enqueued on
+ *     `stream` (a cudaStream_t passed as void*).  Scratch space is passed in as `workspace`; its size comes
+ *     from the matching *_workspace_bytes query.
+ *   - return value: 0 = ok, < 0 = argument error (CNRF_E_*), > 0 = a cudaError_t from launch/enqueue.
+ *   - all floating-point tensors are fp32, row-major, densely packed unless a stride argument says otherwise.
+ *   - indices are int64 ("long") exactly as torch / numpy hand them over.
+ */
+#ifndef CNRF_H_
+#define CNRF_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CNRF_ABI_VERSION 1
+
+#define CNRF_OK 0
+#define CNRF_E_NULL (-1)     /* a required pointer is NULL            */
+#define CNRF_E_SHAPE (-2)    /* a size is out of the supported range  */
+#define CNRF_E_WORKSPACE (-3)/* workspace / saved buffer too small    */
+#define CNRF_E_UNSUPPORTED (-4)
+#define CNRF_E_DEVICE (-5)   /* not an sm_100 device                  */
+
+typedef void* cnrf_stream_t; /* cudaStream_t */
+
+int cnrf_abi_version(void);
+const char* cnrf_error_string(int code);
+/* 0 when the current device can run the tcgen05 kernels (compute capability 10.x), else CNRF_E_DEVICE. */
+int cnrf_device_check(void);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Ray generation.  RaySampler.__init__ / get_bundle / sample, view_synthesis/nerf/ray_sampler.py:31-51,84-99,66-80.
+ * directions[h,w] = ((w-cx)/f, -(h-cy)/f, -1) is evaluated on the fly (same IEEE ops as :44-51);
+ * rd = R_b * directions, ro = t_b.  `select` == NULL renders all H*W pixels of every image (get_bundle),
+ * otherwise select[b*n + i] is the flat pixel index h*W+w of ray i of image b (the numpy permutation of :71-75
+ * stays on the host so the RNG stream is the reference's).  ro may be NULL (get_bundle returns a broadcast).
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_ray_bundle_fwd(const float* pose /*[B,4,4]*/, int64_t B, int32_t H, int32_t W, float focal, float cx,
+                        float cy, const int64_t* select /*[B,n] or NULL*/, int64_t n,
+                        float* ro /*[B*n,3] or NULL*/, float* rd /*[B*n,3]*/, cnrf_stream_t stream);
+/* d pose[b, :3, :3] and d pose[b, :3, 3]; g_pose [B,4,4] is fully written (row 3 = 0).  g_ro may be NULL. */
+int cnrf_ray_bundle_bwd(const float* g_ro, const float* g_rd, int64_t B, int32_t H, int32_t W, float focal,
+                        float cx, float cy, const int64_t* select, int64_t n, float* g_pose /*[B,4,4]*/,
+                        cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Stratified sampling.  PointSampler.sample_uniform, view_synthesis/nerf/point_sampler.py:60-71.
+ * z = lower + (upper-lower)*t_rand (t_rand != NULL, the rand_like draw of :64 supplied by the caller) or the
+ * z table (perturb off); pts = ro + rd*z.
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_sample_uniform_fwd(const float* ro, const float* rd, int64_t N, int32_t S, const float* z_table,
+                            const float* lower, const float* upper, const float* t_rand /*[N,S] or NULL*/,
+                            float* pts /*[N,S,3]*/, float* z /*[N,S]*/, cnrf_stream_t stream);
+/* Backward of pts = ro + rd*z w.r.t. ro, rd (z carries no gradient: SURVEY F9).  Used by both samplers. */
+int cnrf_points_bwd(const float* g_pts /*[N,S,3]*/, const float* z /*[N,S]*/, int64_t N, int32_t S,
+                    float* g_ro /*[N,3]*/, float* g_rd /*[N,3]*/, cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Hierarchical sampling.  PointSampler.sample_pdf, view_synthesis/nerf/point_sampler.py:84-120.
+ * weights: (N, Sc-2) with row stride w_stride (the caller passes the view weights[..., 1:-1], nerf/__init__.py:87).
+ * u: (N, Nf) uniform draws of :93, or NULL for linspace(0,1,Nf) (:95-96).
+ * Outputs: z [N,Sc+Nf] sorted merge of z_coarse and the new samples (:116), pts = ro + rd*z (:118);
+ * optional debug outputs cdf [N,Sc-1] (:86-89) and inds [N,Nf] = searchsorted(cdf,u,right=True) (:101).
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_sample_pdf_fwd(const float* ro, const float* rd, const float* weights, int64_t w_stride,
+                        const float* z_coarse /*[N,Sc]*/, int64_t N, int32_t Sc, int32_t Nf, const float* u,
+                        float* pts, float* z, float* cdf_out /*or NULL*/, int64_t* inds_out /*or NULL*/,
+                        cnrf_stream_t stream);
+/* The inverse-CDF step alone on a caller-supplied CDF tensor (point_sampler.py:98-113): lets tests check the
+ * bin indices bit-exactly "given an identical CDF tensor".  cdf, bins: [N,C]; u, samples, inds: [N,K]. */
+int cnrf_invert_cdf(const float* cdf, const float* bins, const float* u, int64_t N, int32_t C, int32_t K,
+                    float* samples, int64_t* inds, cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Positional encoding.  PositionalEmbedder.embed, view_synthesis/nerf/position_embed.py:44-53.
+ * out[m] = [x (if include_input) | sin(f0 x) | cos(f0 x) | sin(f1 x) | ...], every block D wide.
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_pos_embed_fwd(const float* x /*[M,D]*/, int64_t M, int32_t D, const float* freqs /*[L]*/, int32_t L,
+                       int32_t include_input, float* out /*[M, D*(include_input+2L)]*/, cnrf_stream_t stream);
+int cnrf_pos_embed_bwd(const float* x, const float* g_out, int64_t M, int32_t D, const float* freqs, int32_t L,
+                       int32_t include_input, float* g_x /*[M,D]*/, cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Alpha compositing.  volume_render, view_synthesis/nerf/volumetric_render.py:36-66.
+ * raw [N,S,4] = (r,g,b,sigma) pre-activation; any output pointer may be NULL.
+ * Backward: any upstream gradient may be NULL (treated as zero); g_z / g_rd may be NULL when not needed.
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_composite_fwd(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, float* rgb /*[N,3]*/,
+                       float* disp /*[N]*/, float* acc /*[N]*/, float* weights /*[N,S]*/, float* depth /*[N]*/,
+                       cnrf_stream_t stream);
+int cnrf_composite_bwd(const float* raw, const float* z, const float* rd, int64_t N, int32_t S,
+                       const float* g_rgb, const float* g_disp, const float* g_acc, const float* g_weights,
+                       const float* g_depth, float* g_raw /*[N,S,4]*/, float* g_z /*[N,S] or NULL*/,
+                       float* g_rd /*[N,3] or NULL*/, cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * CodeNeRF radiance field.  CodeNeRFModel.forward, view_synthesis/models/model.py:160-194, and forward_pass,
+ * view_synthesis/nerf/__init__.py:94-134.
+ *
+ * Layer order of the weight/bias pointer tables (state_dict names, models/model.py:145-156):
+ * ---------------------------------------------------------------------------------------------------- */
+#define CNRF_NUM_LAYERS 9
+#define CNRF_L_XYZ1 0     /* layer_xyz1          [H, dim_xyz]      */
+#define CNRF_L_XYZ2 1     /* layer_xyz2          [H, H+C]          */
+#define CNRF_L_FC_OUT 2   /* fc_out              [C+1, H+C]        */
+#define CNRF_L_SHAPE1 3   /* shape_code_layer1   [C, C]            */
+#define CNRF_L_SHAPE2 4   /* shape_code_layer2   [C, C]            */
+#define CNRF_L_TEXTURE1 5 /* texture_code_layer1 [C, C]            */
+#define CNRF_L_DIR1 6     /* layer_dir1          [H, C+dim_dir]    */
+#define CNRF_L_DIR2 7     /* layer_dir2          [H, H]            */
+#define CNRF_L_FC_RGB 8   /* fc_rgb              [3, H+C]          */
+
+#define CNRF_PRECISION_FP32 0 /* fp32 FMA on CUDA cores: the 1e-3 parity mode                                     */
+#define CNRF_PRECISION_BF16 1 /* tcgen05.mma kind::f16, bf16 operands / fp32 TMEM accumulators: the throughput mode */
+
+#define CNRF_PAIRING_REFERENCE 0 /* flat row k=n*S+s gets the view direction of ray k mod N (nerf/__init__.py:127) */
+#define CNRF_PAIRING_CORRECT 1   /* ... of its own ray k / S                                                               */
+
+typedef struct {
+  const float* weight[CNRF_NUM_LAYERS]; /* torch.nn.Linear layout: [out][in] row-major */
+  const float* bias[CNRF_NUM_LAYERS];
+} cnrf_codenerf_params;
+
+typedef struct {
+  float* weight[CNRF_NUM_LAYERS]; /* same shapes as the parameters; every buffer is fully overwritten */
+  float* bias[CNRF_NUM_LAYERS];
+} cnrf_codenerf_grads;
+
+typedef struct {
+  int32_t hidden;       /* H                                                                    */
+  int32_t code;         /* C = shape_code_size = texture_code_size (models/model.py:145-156)    */
+  int32_t dim_xyz;      /* 3*(include_input + 2*L_xyz), 63 in every live config                 */
+  int32_t dim_dir;      /* 27                                                                   */
+  int64_t num_rays;     /* N: rows of z_s / z_t / view directions                               */
+  int32_t num_samples;  /* S: samples per ray; the field has M = N*S rows                       */
+  int32_t pairing;      /* CNRF_PAIRING_*                                                       */
+  int32_t precision;    /* CNRF_PRECISION_*                                                     */
+  int32_t keep;         /* 1: fill `saved` for a later backward, 0: inference                   */
+} cnrf_field_shape;
+
+size_t cnrf_codenerf_saved_bytes(const cnrf_field_shape* s);
+size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32_t backward);
+
+/* The operator as the reference states it, on already-embedded inputs:
+ *   x_xyz [M, dim_xyz] (row stride ld_xyz), x_dir [N, dim_dir] (row stride ld_dir; row r serves the samples the
+ *   pairing assigns to ray r), z_s / z_t [N, C] with row strides (0 = one code broadcast to all rays, eval.py:149).
+ * CodeNeRFModel.forward(z_s, z_t, x) with per-sample codes is the case N = M, S = 1 with x_xyz = x[:, :dim_xyz],
+ * x_dir = x[:, dim_xyz:] (ld = dim_xyz+dim_dir).  raw [M,4] = [rgb_raw | sigma_raw] (models/model.py:194).
+ * The latent-code layers run once per ray and enter the per-sample layers as biases (DESIGN.md "code folding");
+ * results equal the as-written per-sample evaluation up to fp32 summation order. */
+int cnrf_codenerf_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* x_xyz, int64_t ld_xyz,
+                      const float* x_dir, int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t,
+                      int64_t ld_zt, float* raw /*[M,4]*/, void* saved, size_t saved_bytes, void* workspace,
+                      size_t workspace_bytes, cnrf_stream_t stream);
+/* g_z_s, g_z_t: dense [N, C].  g_x_xyz [M, dim_xyz] / g_x_dir [N, dim_dir] may be NULL when not needed. */
+int cnrf_codenerf_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* x_xyz, int64_t ld_xyz,
+                      const float* x_dir, int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t,
+                      int64_t ld_zt, const float* g_raw /*[M,4]*/, const void* saved, size_t saved_bytes,
+                      const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t, float* g_x_xyz, float* g_x_dir,
+                      void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+
+/* forward_pass (nerf/__init__.py:116-134): positional-encode pts [N,S,3] (freqs_xyz, L_xyz) and the L2-normalised
+ * view directions rd [N,3] (freqs_dir, L_dir), pair them (s->pairing), run the field.  include_input_* follow
+ * dim = 3*(include_input + 2L).  In CNRF_PRECISION_BF16 the encoding is fused into the first tensor-core layer. */
+size_t cnrf_field_workspace_bytes(const cnrf_field_shape* s, int32_t backward);
+int cnrf_field_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                   const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const float* z_s,
+                   int64_t ld_zs, const float* z_t, int64_t ld_zt, float* raw /*[N,S,4]*/, void* saved,
+                   size_t saved_bytes, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+/* g_pts [N,S,3] / g_rd [N,3] may be NULL (training: rays carry no gradient; test-time pose optimisation needs them). */
+int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                   const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const float* z_s,
+                   int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* g_raw, const void* saved,
+                   size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t, float* g_pts,
+                   float* g_rd, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CNRF_H_ */
