@@ -1,0 +1,89 @@
+"""ctypes binding of libcnrf.so (include/cnrf.h).  No CPU fallback: if the library is missing, or a call
+returns non-zero, this raises."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libcnrf.so")
+
+NUM_LAYERS = 9
+LAYER_NAMES = ("layer_xyz1", "layer_xyz2", "fc_out", "shape_code_layer1", "shape_code_layer2",
+               "texture_code_layer1", "layer_dir1", "layer_dir2", "fc_rgb")
+PRECISION_FP32, PRECISION_BF16 = 0, 1
+PAIRING_REFERENCE, PAIRING_CORRECT = 0, 1
+
+c_f32p = C.c_void_p   # device pointers travel as integers
+c_i64 = C.c_int64
+c_i32 = C.c_int32
+c_sz = C.c_size_t
+c_f = C.c_float
+
+
+class FieldShape(C.Structure):
+    _fields_ = [("hidden", c_i32), ("code", c_i32), ("dim_xyz", c_i32), ("dim_dir", c_i32), ("num_rays", c_i64),
+                ("num_samples", c_i32), ("pairing", c_i32), ("precision", c_i32), ("keep", c_i32)]
+
+
+class PtrTable(C.Structure):   # cnrf_codenerf_params and cnrf_codenerf_grads share this layout
+    _fields_ = [("weight", C.c_void_p * NUM_LAYERS), ("bias", C.c_void_p * NUM_LAYERS)]
+
+
+_SIGS = {
+    "cnrf_abi_version": (C.c_int, []),
+    "cnrf_error_string": (C.c_char_p, [C.c_int]),
+    "cnrf_device_check": (C.c_int, []),
+    "cnrf_ray_bundle_fwd": (C.c_int, [c_f32p, c_i64, c_i32, c_i32, c_f, c_f, c_f, c_f32p, c_i64, c_f32p, c_f32p, C.c_void_p]),
+    "cnrf_ray_bundle_bwd": (C.c_int, [c_f32p, c_f32p, c_i64, c_i32, c_i32, c_f, c_f, c_f, c_f32p, c_i64, c_f32p, C.c_void_p]),
+    "cnrf_sample_uniform_fwd": (C.c_int, [c_f32p, c_f32p, c_i64, c_i32, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, C.c_void_p]),
+    "cnrf_points_bwd": (C.c_int, [c_f32p, c_f32p, c_i64, c_i32, c_f32p, c_f32p, C.c_void_p]),
+    "cnrf_sample_pdf_fwd": (C.c_int, [c_f32p, c_f32p, c_f32p, c_i64, c_f32p, c_i64, c_i32, c_i32, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, C.c_void_p]),
+    "cnrf_invert_cdf": (C.c_int, [c_f32p, c_f32p, c_f32p, c_i64, c_i32, c_i32, c_f32p, c_f32p, C.c_void_p]),
+    "cnrf_pos_embed_fwd": (C.c_int, [c_f32p, c_i64, c_i32, c_f32p, c_i32, c_i32, c_f32p, C.c_void_p]),
+    "cnrf_pos_embed_bwd": (C.c_int, [c_f32p, c_f32p, c_i64, c_i32, c_f32p, c_i32, c_i32, c_f32p, C.c_void_p]),
+    "cnrf_composite_fwd": (C.c_int, [c_f32p, c_f32p, c_f32p, c_i64, c_i32, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, C.c_void_p]),
+    "cnrf_composite_bwd": (C.c_int, [c_f32p, c_f32p, c_f32p, c_i64, c_i32, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, C.c_void_p]),
+    "cnrf_codenerf_saved_bytes": (c_sz, [C.POINTER(FieldShape)]),
+    "cnrf_codenerf_workspace_bytes": (c_sz, [C.POINTER(FieldShape), c_i32]),
+    "cnrf_field_workspace_bytes": (c_sz, [C.POINTER(FieldShape), c_i32]),
+    "cnrf_codenerf_fwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_i64, c_f32p, c_i64, c_f32p, c_i64,
+                                    c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_codenerf_bwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_i64, c_f32p, c_i64, c_f32p, c_i64,
+                                    c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p,
+                                    c_f32p, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_field_fwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
+                                 c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_field_bwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
+                                 c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.POINTER(PtrTable), c_f32p,
+                                 c_f32p, c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
+}
+
+EXPORTS = tuple(sorted(_SIGS))
+_lib = None
+
+
+class CnrfError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen libcnrf.so and attach signatures.  Raises if the in-tree library has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CnrfError(f"{LIB_PATH} not found: build it with `python code-nerf_b200/build.py` "
+                        "(there is no CPU or PyTorch fallback for this path)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _SIGS.items():
+        fn = getattr(lib, name)
+        fn.restype, fn.argtypes = res, args
+    if lib.cnrf_abi_version() != 1:
+        raise CnrfError("libcnrf.so ABI version mismatch")
+    _lib = lib
+    return lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = load().cnrf_error_string(int(rc)).decode()
+        raise CnrfError(f"{what} failed with code {rc}: {msg}")

@@ -1,0 +1,387 @@
+"""torch.autograd.Function wrappers over the C ABI of libcnrf.so.
+
+torch is plumbing here: it owns device memory, the current stream and the autograd graph.  Every arithmetic
+operation of the hot path happens inside libcnrf.so; a non-CUDA tensor or a missing library raises.
+"""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import FieldShape, PtrTable, check
+
+_f32 = torch.float32
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _req_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise _lib.CnrfError("libcnrf operators need CUDA tensors (no CPU fallback on this path)")
+
+
+def _c(t):
+    """fp32 + contiguous view of a tensor (no copy when it already is)."""
+    if t.dtype != _f32:
+        t = t.to(_f32)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _rows(t):
+    """(tensor, row stride) for a 2-D operand whose rows may be broadcast (stride 0) -- eval.py:149 passes
+    `code.expand(N, -1)`; materialising that copy is exactly what the reference's forward_pass does and we avoid."""
+    if t.dtype != _f32:
+        t = t.to(_f32)
+    if t.dim() == 2 and t.stride(1) == 1 and (t.stride(0) == 0 or t.stride(0) >= t.shape[1]):
+        return t, t.stride(0)
+    t = t.contiguous()
+    return t, t.stride(0)
+
+
+# ----------------------------------------------------------------------------------------------------------
+class _RayBundle(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pose, H, W, focal, cx, cy, select, n, want_ro):
+        _req_cuda(pose, select)
+        lib = _lib.load()
+        pose = _c(pose)
+        B = pose.shape[0]
+        rd = torch.empty((B * n, 3), dtype=_f32, device=pose.device)
+        ro = torch.empty((B * n, 3), dtype=_f32, device=pose.device) if want_ro else None
+        check(lib.cnrf_ray_bundle_fwd(_p(pose), B, H, W, focal, cx, cy, _p(select), n, _p(ro), _p(rd), _stream()),
+              "cnrf_ray_bundle_fwd")
+        ctx.args = (B, H, W, focal, cx, cy, n)
+        ctx.select = select
+        if want_ro:
+            return ro, rd
+        dummy = rd.new_empty(0)
+        ctx.mark_non_differentiable(dummy)
+        return dummy, rd
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_ro, g_rd):
+        B, H, W, focal, cx, cy, n = ctx.args
+        lib = _lib.load()
+        if g_rd is None:
+            g_rd = torch.zeros((B * n, 3), dtype=_f32, device=g_ro.device)
+        g_rd = _c(g_rd)
+        g_ro = _c(g_ro) if (g_ro is not None and g_ro.numel() == B * n * 3) else None
+        g_pose = torch.empty((B, 4, 4), dtype=_f32, device=g_rd.device)
+        check(lib.cnrf_ray_bundle_bwd(_p(g_ro), _p(g_rd), B, H, W, focal, cx, cy, _p(ctx.select), n, _p(g_pose),
+                                      _stream()), "cnrf_ray_bundle_bwd")
+        return g_pose, None, None, None, None, None, None, None, None
+
+
+def ray_bundle(pose, H, W, focal, cx, cy, select=None, n=None, want_ro=True):
+    """rd (and ro) of shape (B*n, 3).  select: int64 CUDA tensor (B, n) of flat pixel indices, or None = all pixels."""
+    n = H * W if select is None else n
+    ro, rd = _RayBundle.apply(pose, H, W, float(focal), float(cx), float(cy), select, int(n), want_ro)
+    return (ro if want_ro else None), rd
+
+
+# ----------------------------------------------------------------------------------------------------------
+class _SampleUniform(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ro, rd, z_table, lower, upper, t_rand):
+        _req_cuda(ro, rd, z_table, t_rand)
+        lib = _lib.load()
+        ro, rd = _c(ro), _c(rd)
+        N, S = ro.shape[0], z_table.shape[0]
+        pts = torch.empty((N, S, 3), dtype=_f32, device=ro.device)
+        z = torch.empty((N, S), dtype=_f32, device=ro.device)
+        t_rand = _c(t_rand) if t_rand is not None else None
+        check(lib.cnrf_sample_uniform_fwd(_p(ro), _p(rd), N, S, _p(z_table), _p(lower), _p(upper), _p(t_rand), _p(pts),
+                                          _p(z), _stream()), "cnrf_sample_uniform_fwd")
+        ctx.save_for_backward(z)
+        ctx.mark_non_differentiable(z)
+        return pts, z
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_pts, _g_z):
+        (z,) = ctx.saved_tensors
+        g_ro, g_rd = points_bwd(g_pts, z)
+        return g_ro, g_rd, None, None, None, None
+
+
+def points_bwd(g_pts, z):
+    lib = _lib.load()
+    g_pts = _c(g_pts)
+    N, S = z.shape
+    g_ro = torch.empty((N, 3), dtype=_f32, device=z.device)
+    g_rd = torch.empty((N, 3), dtype=_f32, device=z.device)
+    check(lib.cnrf_points_bwd(_p(g_pts), _p(z), N, S, _p(g_ro), _p(g_rd), _stream()), "cnrf_points_bwd")
+    return g_ro, g_rd
+
+
+def sample_uniform(ro, rd, z_table, lower, upper, t_rand):
+    return _SampleUniform.apply(ro, rd, z_table, lower, upper, t_rand)
+
+
+class _SamplePdf(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ro, rd, weights, z_coarse, num_fine, u, debug):
+        _req_cuda(ro, rd, weights, z_coarse, u)
+        lib = _lib.load()
+        ro, rd, z_coarse = _c(ro), _c(rd), _c(z_coarse)
+        weights, w_stride = _rows(weights.detach())
+        N, Sc = z_coarse.shape
+        S = Sc + num_fine
+        pts = torch.empty((N, S, 3), dtype=_f32, device=ro.device)
+        z = torch.empty((N, S), dtype=_f32, device=ro.device)
+        cdf = torch.empty((N, Sc - 1), dtype=_f32, device=ro.device) if debug else None
+        inds = torch.empty((N, num_fine), dtype=torch.int64, device=ro.device) if debug else None
+        u = _c(u) if u is not None else None
+        check(lib.cnrf_sample_pdf_fwd(_p(ro), _p(rd), _p(weights), w_stride, _p(z_coarse), N, Sc, num_fine, _p(u),
+                                      _p(pts), _p(z), _p(cdf), _p(inds), _stream()), "cnrf_sample_pdf_fwd")
+        ctx.save_for_backward(z)
+        ctx.mark_non_differentiable(z)
+        if debug:
+            ctx.mark_non_differentiable(cdf, inds)
+            return pts, z, cdf, inds
+        return pts, z
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_pts, *_):
+        (z,) = ctx.saved_tensors
+        g_ro, g_rd = points_bwd(g_pts, z)
+        return g_ro, g_rd, None, None, None, None, None
+
+
+def sample_pdf(ro, rd, weights, z_coarse, num_fine, u, debug=False):
+    return _SamplePdf.apply(ro, rd, weights, z_coarse, int(num_fine), u, bool(debug))
+
+
+def invert_cdf(cdf, bins, u):
+    _req_cuda(cdf, bins, u)
+    lib = _lib.load()
+    cdf, bins, u = _c(cdf), _c(bins), _c(u)
+    N, Cn = cdf.shape
+    K = u.shape[1]
+    samples = torch.empty((N, K), dtype=_f32, device=cdf.device)
+    inds = torch.empty((N, K), dtype=torch.int64, device=cdf.device)
+    check(lib.cnrf_invert_cdf(_p(cdf), _p(bins), _p(u), N, Cn, K, _p(samples), _p(inds), _stream()), "cnrf_invert_cdf")
+    return samples, inds
+
+
+# ----------------------------------------------------------------------------------------------------------
+class _PosEmbed(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, freqs, include_input):
+        _req_cuda(x, freqs)
+        lib = _lib.load()
+        x = _c(x)
+        M, D = x.shape
+        L = freqs.shape[0]
+        out = torch.empty((M, D * (int(include_input) + 2 * L)), dtype=_f32, device=x.device)
+        check(lib.cnrf_pos_embed_fwd(_p(x), M, D, _p(freqs), L, int(include_input), _p(out), _stream()),
+              "cnrf_pos_embed_fwd")
+        ctx.save_for_backward(x, freqs)
+        ctx.inc = int(include_input)
+        return out
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_out):
+        x, freqs = ctx.saved_tensors
+        lib = _lib.load()
+        g_out = _c(g_out)
+        g_x = torch.empty_like(x)
+        check(lib.cnrf_pos_embed_bwd(_p(x), _p(g_out), x.shape[0], x.shape[1], _p(freqs), freqs.shape[0], ctx.inc,
+                                     _p(g_x), _stream()), "cnrf_pos_embed_bwd")
+        return g_x, None, None
+
+
+def pos_embed(x, freqs, include_input):
+    return _PosEmbed.apply(x, freqs, bool(include_input))
+
+
+# ----------------------------------------------------------------------------------------------------------
+class _Composite(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, raw, z, rd):
+        _req_cuda(raw, z, rd)
+        lib = _lib.load()
+        raw, z, rd = _c(raw), _c(z), _c(rd)
+        N, S = z.shape
+        dev = raw.device
+        rgb = torch.empty((N, 3), dtype=_f32, device=dev)
+        disp = torch.empty((N,), dtype=_f32, device=dev)
+        acc = torch.empty((N,), dtype=_f32, device=dev)
+        weights = torch.empty((N, S), dtype=_f32, device=dev)
+        depth = torch.empty((N,), dtype=_f32, device=dev)
+        check(lib.cnrf_composite_fwd(_p(raw), _p(z), _p(rd), N, S, _p(rgb), _p(disp), _p(acc), _p(weights), _p(depth),
+                                     _stream()), "cnrf_composite_fwd")
+        ctx.save_for_backward(raw, z, rd)
+        return rgb, disp, acc, weights, depth
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_rgb, g_disp, g_acc, g_weights, g_depth):
+        raw, z, rd = ctx.saved_tensors
+        lib = _lib.load()
+        N, S = z.shape
+        gs = [None if g is None else _c(g) for g in (g_rgb, g_disp, g_acc, g_weights, g_depth)]
+        g_raw = torch.empty_like(raw)
+        g_z = torch.empty_like(z) if ctx.needs_input_grad[1] else None
+        g_rd = torch.empty_like(rd) if ctx.needs_input_grad[2] else None
+        check(lib.cnrf_composite_bwd(_p(raw), _p(z), _p(rd), N, S, _p(gs[0]), _p(gs[1]), _p(gs[2]), _p(gs[3]), _p(gs[4]),
+                                     _p(g_raw), _p(g_z), _p(g_rd), _stream()), "cnrf_composite_bwd")
+        return g_raw, g_z, g_rd
+
+
+def composite(raw, z, rd):
+    """-> (rgb, disp, acc, weights, depth), the tuple order of volume_render (volumetric_render.py:66)."""
+    return _Composite.apply(raw, z, rd)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# CodeNeRF field
+# ----------------------------------------------------------------------------------------------------------
+def _ptr_table(tensors18):
+    t = PtrTable()
+    for l in range(_lib.NUM_LAYERS):
+        t.weight[l] = tensors18[2 * l].data_ptr()
+        t.bias[l] = tensors18[2 * l + 1].data_ptr()
+    return t
+
+
+def _bytes(n, device):
+    return torch.empty((max(int(n), 1),), dtype=torch.uint8, device=device)
+
+
+def _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, keep):
+    return FieldShape(int(hidden), int(code), int(dim_xyz), int(dim_dir), int(N), int(S), int(pairing), int(precision),
+                      int(keep))
+
+
+class _Field(torch.autograd.Function):
+    """forward_pass (nerf/__init__.py:94-134): pts (N,S,3), rd (N,3), z_s/z_t (N,C) -> raw (N,S,4)."""
+
+    @staticmethod
+    def forward(ctx, cfg, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, *params):
+        _req_cuda(pts, rd, z_s, z_t, *params)
+        lib = _lib.load()
+        hidden, code, dim_xyz, dim_dir, pairing, precision = cfg
+        pts, rd = _c(pts), _c(rd)
+        z_s, ld_zs = _rows(z_s)
+        z_t, ld_zt = _rows(z_t)
+        params = tuple(_c(p) for p in params)
+        N, S = pts.shape[0], pts.shape[1]
+        keep = int(any(ctx.needs_input_grad))
+        shp = _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, keep)
+        saved = _bytes(lib.cnrf_codenerf_saved_bytes(C.byref(shp)), pts.device)
+        ws_bytes = lib.cnrf_field_workspace_bytes(C.byref(shp), 0)
+        ws = _bytes(ws_bytes, pts.device)
+        raw = torch.empty((N, S, 4), dtype=_f32, device=pts.device)
+        tab = _ptr_table(params)
+        check(lib.cnrf_field_fwd(C.byref(shp), C.byref(tab), _p(pts), _p(rd), _p(freqs_xyz), freqs_xyz.shape[0],
+                                 _p(freqs_dir), freqs_dir.shape[0], _p(z_s), ld_zs, _p(z_t), ld_zt, _p(raw),
+                                 _p(saved) if keep else None, saved.numel() if keep else 0, _p(ws), ws.numel(),
+                                 _stream()), "cnrf_field_fwd")
+        if keep:
+            ctx.save_for_backward(pts, rd, z_s, z_t, freqs_xyz, freqs_dir, saved, *params)
+            ctx.cfg, ctx.lds = cfg, (ld_zs, ld_zt)
+        return raw
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_raw):
+        pts, rd, z_s, z_t, freqs_xyz, freqs_dir, saved, *params = ctx.saved_tensors
+        lib = _lib.load()
+        hidden, code, dim_xyz, dim_dir, pairing, precision = ctx.cfg
+        ld_zs, ld_zt = ctx.lds
+        N, S = pts.shape[0], pts.shape[1]
+        shp = _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, 1)
+        g_raw = _c(g_raw)
+        dev = pts.device
+        grads = tuple(torch.empty_like(p) for p in params)
+        g_zs = torch.empty((N, code), dtype=_f32, device=dev)
+        g_zt = torch.empty((N, code), dtype=_f32, device=dev)
+        g_pts = torch.empty_like(pts) if ctx.needs_input_grad[1] else None
+        g_rd = torch.empty_like(rd) if ctx.needs_input_grad[2] else None
+        ws = _bytes(lib.cnrf_field_workspace_bytes(C.byref(shp), 1), dev)
+        tab, gtab = _ptr_table(params), _ptr_table(grads)
+        check(lib.cnrf_field_bwd(C.byref(shp), C.byref(tab), _p(pts), _p(rd), _p(freqs_xyz), freqs_xyz.shape[0],
+                                 _p(freqs_dir), freqs_dir.shape[0], _p(z_s), ld_zs, _p(z_t), ld_zt, _p(g_raw), _p(saved),
+                                 saved.numel(), C.byref(gtab), _p(g_zs), _p(g_zt), _p(g_pts), _p(g_rd), _p(ws),
+                                 ws.numel(), _stream()), "cnrf_field_bwd")
+        return (None, g_pts, g_rd, g_zs, g_zt, None, None) + grads
+
+
+def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code, dim_xyz, dim_dir,
+                   pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_BF16):
+    """params: the 18 tensors (weight, bias per layer) in _lib.LAYER_NAMES order."""
+    cfg = (hidden, code, dim_xyz, dim_dir, pairing, precision)
+    return _Field.apply(cfg, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, *params)
+
+
+class _Model(torch.autograd.Function):
+    """CodeNeRFModel.forward(z_s, z_t, x) as written (models/model.py:160-194): per-sample codes, pre-embedded x."""
+
+    @staticmethod
+    def forward(ctx, cfg, z_s, z_t, x, *params):
+        _req_cuda(z_s, z_t, x, *params)
+        lib = _lib.load()
+        hidden, code, dim_xyz, dim_dir, precision = cfg
+        x = _c(x)
+        z_s, ld_zs = _rows(z_s)
+        z_t, ld_zt = _rows(z_t)
+        params = tuple(_c(p) for p in params)
+        M = x.shape[0]
+        keep = int(any(ctx.needs_input_grad))
+        shp = _shape(hidden, code, dim_xyz, dim_dir, M, 1, _lib.PAIRING_CORRECT, precision, keep)
+        saved = _bytes(lib.cnrf_codenerf_saved_bytes(C.byref(shp)), x.device)
+        ws = _bytes(lib.cnrf_codenerf_workspace_bytes(C.byref(shp), 0), x.device)
+        raw = torch.empty((M, 4), dtype=_f32, device=x.device)
+        ld = x.shape[1]
+        x_dir = C.c_void_p(x.data_ptr() + 4 * dim_xyz)
+        tab = _ptr_table(params)
+        check(lib.cnrf_codenerf_fwd(C.byref(shp), C.byref(tab), _p(x), ld, x_dir, ld, _p(z_s), ld_zs, _p(z_t), ld_zt,
+                                    _p(raw), _p(saved) if keep else None, saved.numel() if keep else 0, _p(ws),
+                                    ws.numel(), _stream()), "cnrf_codenerf_fwd")
+        if keep:
+            ctx.save_for_backward(z_s, z_t, x, saved, *params)
+            ctx.cfg, ctx.lds = cfg, (ld_zs, ld_zt)
+        return raw
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_raw):
+        z_s, z_t, x, saved, *params = ctx.saved_tensors
+        lib = _lib.load()
+        hidden, code, dim_xyz, dim_dir, precision = ctx.cfg
+        ld_zs, ld_zt = ctx.lds
+        M, ld = x.shape
+        shp = _shape(hidden, code, dim_xyz, dim_dir, M, 1, _lib.PAIRING_CORRECT, precision, 1)
+        g_raw = _c(g_raw)
+        dev = x.device
+        grads = tuple(torch.empty_like(p) for p in params)
+        g_zs = torch.empty((M, code), dtype=_f32, device=dev)
+        g_zt = torch.empty((M, code), dtype=_f32, device=dev)
+        need_x = ctx.needs_input_grad[3]
+        g_xyz = torch.empty((M, dim_xyz), dtype=_f32, device=dev) if need_x else None
+        g_dir = torch.empty((M, dim_dir), dtype=_f32, device=dev) if need_x else None
+        ws = _bytes(lib.cnrf_codenerf_workspace_bytes(C.byref(shp), 1), dev)
+        x_dir = C.c_void_p(x.data_ptr() + 4 * dim_xyz)
+        tab, gtab = _ptr_table(params), _ptr_table(grads)
+        check(lib.cnrf_codenerf_bwd(C.byref(shp), C.byref(tab), _p(x), ld, x_dir, ld, _p(z_s), ld_zs, _p(z_t), ld_zt,
+                                    _p(g_raw), _p(saved), saved.numel(), C.byref(gtab), _p(g_zs), _p(g_zt), _p(g_xyz),
+                                    _p(g_dir), _p(ws), ws.numel(), _stream()), "cnrf_codenerf_bwd")
+        g_x = torch.cat((g_xyz, g_dir), dim=-1) if need_x else None
+        return (None, g_zs, g_zt, g_x) + grads
+
+
+def codenerf_model(params, z_s, z_t, x, hidden, code, dim_xyz, dim_dir, precision=_lib.PRECISION_FP32):
+    cfg = (hidden, code, dim_xyz, dim_dir, precision)
+    return _Model.apply(cfg, z_s, z_t, x, *params)

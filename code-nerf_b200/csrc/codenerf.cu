@@ -1,0 +1,495 @@
+// CodeNeRF radiance field: CodeNeRFModel.forward (view_synthesis/models/model.py:160-194) and forward_pass
+// (view_synthesis/nerf/__init__.py:94-134), forward and backward, behind cnrf_codenerf_* / cnrf_field_*.
+//
+// Code folding: the three latent-code layers and the code halves of layer_xyz2 / fc_out / fc_rgb, and the
+// view-direction half of layer_dir1, depend on the RAY only.  They are evaluated once per ray (fp32, sgemm.cu) into
+// bias tables
+//     beta2 = W2c relu(Ws1 z_s + bs1) + b2     betao = Woc relu(Ws2 z_s + bs2) + bo
+//     betar = Wrt relu(Wt  z_t + bt ) + br     betad = Wdv gamma(d^) + bd1
+// and the per-SAMPLE chain is  h1 = relu(W1 gamma(x) + b1), h2 = relu(W2h h1 + beta2[ray]), o = Woh h2 + betao[ray],
+// v1 = relu(Wdf o[1:] + betad[pair]), v2 = relu(Wd2 v1 + bd2), rgb = Wrv v2 + betar[ray].   `pair` reproduces the
+// reference's view-direction tiling (row k -> ray k mod N, nerf/__init__.py:127) unless CNRF_PAIRING_CORRECT.
+// The chain runs either as fp32 SIMT GEMMs (this file; parity mode) or as the fused tcgen05 kernels of mlp_tc.cu.
+#include <algorithm>
+#include "common.cuh"
+#include "internal.h"
+
+namespace {
+
+struct Arena {
+  char* base; size_t cap; size_t off = 0; bool ok = true;
+  Arena(void* p, size_t c) : base(static_cast<char*>(p)), cap(c) {}
+  float* take(size_t nfloat) {
+    size_t bytes = (nfloat * sizeof(float) + 255) & ~size_t(255);
+    if (off + bytes > cap) { ok = false; return nullptr; }
+    float* r = reinterpret_cast<float*>(base + off);
+    off += bytes;
+    return r;
+  }
+};
+inline size_t al(size_t nfloat) { return (nfloat * sizeof(float) + 255) & ~size_t(255); }
+
+struct Dims {
+  int H, C, dx, dd, S, pairing;
+  int64_t N, M;
+};
+inline Dims dims_of(const cnrf_field_shape* s) {
+  Dims d;
+  d.H = s->hidden; d.C = s->code; d.dx = s->dim_xyz; d.dd = s->dim_dir; d.S = s->num_samples; d.pairing = s->pairing;
+  d.N = s->num_rays; d.M = s->num_rays * (int64_t)s->num_samples;
+  return d;
+}
+inline int check_shape(const cnrf_field_shape* s) {
+  if (!s) return CNRF_E_NULL;
+  if (s->hidden <= 0 || s->code <= 0 || s->dim_xyz <= 0 || s->dim_dir <= 0 || s->num_rays <= 0 || s->num_samples <= 0)
+    return CNRF_E_SHAPE;
+  if (s->pairing != CNRF_PAIRING_REFERENCE && s->pairing != CNRF_PAIRING_CORRECT) return CNRF_E_SHAPE;
+  if (s->precision != CNRF_PRECISION_FP32 && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
+  return CNRF_OK;
+}
+
+// saved-for-backward layout (fp32 precision)
+struct SavedF32 { float *h1, *h2, *o, *v1, *v2, *as1, *as2, *at; };
+inline size_t saved_f32_bytes(const Dims& d) {
+  return 4 * al(d.M * d.H) + al(d.M * (d.C + 1)) + 3 * al(d.N * d.C);
+}
+inline bool carve_saved(const Dims& d, void* p, size_t bytes, SavedF32& s) {
+  Arena a(p, bytes);
+  s.h1 = a.take(d.M * d.H); s.h2 = a.take(d.M * d.H); s.o = a.take(d.M * (d.C + 1));
+  s.v1 = a.take(d.M * d.H); s.v2 = a.take(d.M * d.H);
+  s.as1 = a.take(d.N * d.C); s.as2 = a.take(d.N * d.C); s.at = a.take(d.N * d.C);
+  return a.ok;
+}
+// per-ray bias tables (forward workspace) and their gradients (backward workspace)
+struct Tables { float *b2, *bo, *br, *bd; };
+inline size_t tables_bytes(const Dims& d) { return 2 * al(d.N * d.H) + al(d.N * (d.C + 1)) + al(d.N * 3); }
+inline void carve_tables(const Dims& d, Arena& a, Tables& t) {
+  t.b2 = a.take(d.N * d.H); t.bo = a.take(d.N * (d.C + 1)); t.br = a.take(d.N * 3); t.bd = a.take(d.N * d.H);
+}
+
+#define RUN(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
+
+// Y[rows,Nout] = act(X[rows,K] W[Nout,K]^T + bias[(m/div)%mod])
+int lin(const float* X, int64_t ldx, int64_t rows, int K, const float* W, int64_t ldw, int Nout, float* Y, int64_t ldy,
+        const float* bias, int64_t ld_bias, int64_t div, int64_t mod, int relu, cudaStream_t st) {
+  GemmArgs g;
+  g.A = X; g.a_rs = ldx; g.a_cs = 1; g.B = W; g.b_rs = 1; g.b_cs = ldw; g.C = Y; g.ldc = ldy;
+  g.M = rows; g.N = Nout; g.K = K; g.bias = bias; g.ld_bias = ld_bias; g.bias_div = div; g.bias_mod = mod; g.relu = relu;
+  return cnrf_sgemm(g, st);
+}
+// dX[rows,K] (+)= (dY[rows,Nout] W[Nout,K]) * (mask > 0)
+int dgrad(const float* dY, int64_t ldy, int64_t rows, int Nout, const float* W, int64_t ldw, int K, float* dX,
+          int64_t ldx, const float* mask, int64_t ldm, int accumulate, cudaStream_t st) {
+  GemmArgs g;
+  g.A = dY; g.a_rs = ldy; g.a_cs = 1; g.B = W; g.b_rs = ldw; g.b_cs = 1; g.C = dX; g.ldc = ldx;
+  g.M = rows; g.N = K; g.K = Nout; g.mask = mask; g.ld_mask = ldm; g.accumulate = accumulate;
+  return cnrf_sgemm(g, st);
+}
+// dW[Nout,K] = dY[rows,Nout]^T X[rows,K]   (dW must be zero-filled: split-K partials are added atomically)
+int wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int64_t rows, int Nout, int K, float* dW,
+          int64_t ldw, cudaStream_t st) {
+  GemmArgs g;
+  g.A = dY; g.a_rs = 1; g.a_cs = ldy; g.B = X; g.b_rs = ldx; g.b_cs = 1; g.C = dW; g.ldc = ldw;
+  g.M = Nout; g.N = K; g.K = rows;
+  int64_t tiles = ((Nout + 63) / 64) * (int64_t)((K + 63) / 64);
+  int64_t want = (1184 + tiles - 1) / tiles, cap = (rows + 511) / 512;
+  g.split_k = (int)std::max<int64_t>(1, std::min<int64_t>(want, cap));
+  if (g.split_k == 1) g.accumulate = 1;   // still += into the zero-filled buffer
+  return cnrf_sgemm(g, st);
+}
+
+__global__ void copy_col_kernel(const float* __restrict__ src, int64_t ld_src, float* __restrict__ dst, int64_t ld_dst,
+                                int64_t M) {
+  int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (m < M) dst[m * ld_dst] = src[m * ld_src];
+}
+int copy_col(const float* src, int64_t ld_src, float* dst, int64_t ld_dst, int64_t M, cudaStream_t st) {
+  copy_col_kernel<<<grid_for(M, 256), 256, 0, st>>>(src, ld_src, dst, ld_dst, M);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
+inline void pair_index(const Dims& d, int64_t& div, int64_t& mod) {
+  if (d.pairing == CNRF_PAIRING_REFERENCE) { div = 1; mod = d.N; } else { div = d.S; mod = INT64_MAX; }
+}
+
+// ---- per-ray layers ------------------------------------------------------------------------------------------
+int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir, int64_t ld_dir, const float* z_s,
+                int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
+                cudaStream_t st) {
+  const int H = d.H, C = d.C;
+  const int64_t INF = INT64_MAX;
+  RUN(lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 0, 1, INF, 1, st));   // model.py:174
+  RUN(lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 0, 1, INF, 1, st));   // :175
+  RUN(lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 0, 1, INF, 1, st));// :177
+  RUN(lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0, 1, INF, 0, st));
+  RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+  RUN(lin(at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0, 1, INF, 0, st));
+  RUN(lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0, 1, INF, 0, st));
+  return CNRF_OK;
+}
+
+// gradients of the bias tables -> code-layer weights, code halves of the split layers, z_s / z_t / x_dir
+int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codenerf_grads* g, const float* x_dir,
+                int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* as1,
+                const float* as2, const float* at, const Tables& dt, float* tmp /*[N,C]*/, float* g_z_s, float* g_z_t,
+                float* g_x_dir, cudaStream_t st) {
+  const int H = d.H, C = d.C;
+  // texture branch: betar = Wrt at + br
+  RUN(cnrf_colsum(dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB], st));
+  RUN(wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C, st));
+  RUN(dgrad(dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp, C, at, C, 0, st));
+  RUN(wgrad(tmp, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C, st));
+  RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_TEXTURE1], st));
+  RUN(dgrad(tmp, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, 0, st));
+  // shape branch 2: betao = Woc as2 + bo
+  RUN(cnrf_colsum(dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT], st));
+  RUN(wgrad(dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C, st));
+  RUN(dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp, C, as2, C, 0, st));
+  RUN(wgrad(tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C, st));
+  RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_SHAPE2], st));
+  RUN(dgrad(tmp, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, 0, st));
+  // shape branch 1: beta2 = W2c as1 + b2
+  RUN(cnrf_colsum(dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2], st));
+  RUN(wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C, st));
+  RUN(dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp, C, as1, C, 0, st));
+  RUN(wgrad(tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C, st));
+  RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_SHAPE1], st));
+  RUN(dgrad(tmp, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1, st));
+  // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
+  RUN(cnrf_colsum(dt.bd, H, d.N, H, g->bias[CNRF_L_DIR1], st));
+  RUN(wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd, st));
+  if (g_x_dir) RUN(dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0, st));
+  return CNRF_OK;
+}
+
+// ---- per-sample chain, fp32 SIMT ------------------------------------------------------------------------------
+int chain_fwd_f32(const Dims& d, const cnrf_codenerf_params* p, const float* x_xyz, int64_t ld_xyz, const Tables& t,
+                  const SavedF32& s, float* raw, cudaStream_t st) {
+  const int H = d.H, C = d.C;
+  const int64_t INF = INT64_MAX;
+  int64_t pdiv, pmod;
+  pair_index(d, pdiv, pmod);
+  RUN(lin(x_xyz, ld_xyz, d.M, d.dx, p->weight[CNRF_L_XYZ1], d.dx, H, s.h1, H, p->bias[CNRF_L_XYZ1], 0, 1, INF, 1, st)); // model.py:179
+  RUN(lin(s.h1, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, s.h2, H, t.b2, H, d.S, INF, 1, st));                        // :180-181
+  RUN(lin(s.h2, H, d.M, H, p->weight[CNRF_L_FC_OUT], H + C, C + 1, s.o, C + 1, t.bo, C + 1, d.S, INF, 0, st));           // :182-184
+  RUN(lin(s.o + 1, C + 1, d.M, C, p->weight[CNRF_L_DIR1], C + d.dd, H, s.v1, H, t.bd, H, pdiv, pmod, 1, st));            // :186-189
+  RUN(lin(s.v1, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, s.v2, H, p->bias[CNRF_L_DIR2], 0, 1, INF, 1, st));              // :190
+  RUN(lin(s.v2, H, d.M, H, p->weight[CNRF_L_FC_RGB], H + C, 3, raw, 4, t.br, 3, d.S, INF, 0, st));                       // :191-192
+  RUN(copy_col(s.o, C + 1, raw + 3, 4, d.M, st));                                                                       // :194  [rgb | sigma]
+  return CNRF_OK;
+}
+
+// ga, gb: [M, max(H, C+1)] scratch.  Fills the hidden halves of the weight grads, b1 / bd2 grads, the bias-table
+// gradients dt, and (optionally) g_x_xyz.
+int chain_bwd_f32(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codenerf_grads* g, const float* x_xyz,
+                  int64_t ld_xyz, const float* g_raw, const SavedF32& s, float* ga, float* gb, const Tables& dt,
+                  float* g_x_xyz, cudaStream_t st) {
+  const int H = d.H, C = d.C;
+  // fc_rgb
+  RUN(wgrad(g_raw, 4, s.v2, H, d.M, 3, H, g->weight[CNRF_L_FC_RGB], H + C, st));
+  RUN(cnrf_strided_rowsum(g_raw, 4, d.N, d.S, d.S, 1, 3, dt.br, 3, st));
+  RUN(dgrad(g_raw, 4, d.M, 3, p->weight[CNRF_L_FC_RGB], H + C, H, ga, H, s.v2, H, 0, st));
+  // layer_dir2
+  RUN(wgrad(ga, H, s.v1, H, d.M, H, H, g->weight[CNRF_L_DIR2], H, st));
+  RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_DIR2], st));
+  RUN(dgrad(ga, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, gb, H, s.v1, H, 0, st));
+  // layer_dir1 (feature half)
+  RUN(wgrad(gb, H, s.o + 1, C + 1, d.M, H, C, g->weight[CNRF_L_DIR1], C + d.dd, st));
+  if (d.pairing == CNRF_PAIRING_REFERENCE) RUN(cnrf_strided_rowsum(gb, H, d.N, 1, d.S, d.N, H, dt.bd, H, st));
+  else RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.bd, H, st));
+  RUN(dgrad(gb, H, d.M, H, p->weight[CNRF_L_DIR1], C + d.dd, C, ga + 1, C + 1, nullptr, 0, 0, st));
+  RUN(copy_col(g_raw + 3, 4, ga, C + 1, d.M, st));                       // d sigma_raw -> column 0 of d o
+  // fc_out
+  RUN(wgrad(ga, C + 1, s.h2, H, d.M, C + 1, H, g->weight[CNRF_L_FC_OUT], H + C, st));
+  RUN(cnrf_strided_rowsum(ga, C + 1, d.N, d.S, d.S, 1, C + 1, dt.bo, C + 1, st));
+  RUN(dgrad(ga, C + 1, d.M, C + 1, p->weight[CNRF_L_FC_OUT], H + C, H, gb, H, s.h2, H, 0, st));
+  // layer_xyz2
+  RUN(wgrad(gb, H, s.h1, H, d.M, H, H, g->weight[CNRF_L_XYZ2], H + C, st));
+  RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.b2, H, st));
+  RUN(dgrad(gb, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, ga, H, s.h1, H, 0, st));
+  // layer_xyz1
+  RUN(wgrad(ga, H, x_xyz, ld_xyz, d.M, H, d.dx, g->weight[CNRF_L_XYZ1], d.dx, st));
+  RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_XYZ1], st));
+  if (g_x_xyz) RUN(dgrad(ga, H, d.M, H, p->weight[CNRF_L_XYZ1], d.dx, d.dx, g_x_xyz, d.dx, nullptr, 0, 0, st));
+  return CNRF_OK;
+}
+
+int zero_weight_grads(const Dims& d, const cnrf_codenerf_grads* g, cudaStream_t st) {
+  const int H = d.H, C = d.C;
+  const size_t n[CNRF_NUM_LAYERS] = {(size_t)H * d.dx, (size_t)H * (H + C), (size_t)(C + 1) * (H + C), (size_t)C * C,
+                                     (size_t)C * C, (size_t)C * C, (size_t)H * (C + d.dd), (size_t)H * H,
+                                     (size_t)3 * (H + C)};
+  for (int l = 0; l < CNRF_NUM_LAYERS; ++l) {
+    if (!g->weight[l] || !g->bias[l]) return CNRF_E_NULL;
+    RUN(cnrf_fill_zero(g->weight[l], n[l] * sizeof(float), st));
+  }
+  return CNRF_OK;
+}
+
+inline size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
+
+}  // namespace
+
+// tensor-core chain (mlp_tc.cu)
+size_t cnrf_tc_saved_bytes(int64_t M);
+size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward);
+
+extern "C" size_t cnrf_codenerf_saved_bytes(const cnrf_field_shape* s) {
+  if (check_shape(s) != CNRF_OK || !s->keep) return 0;
+  Dims d = dims_of(s);
+  if (s->precision == CNRF_PRECISION_FP32) return saved_f32_bytes(d);
+  return 3 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M);
+}
+
+extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32_t backward) {
+  if (check_shape(s) != CNRF_OK) return 0;
+  Dims d = dims_of(s);
+  size_t b = tables_bytes(d);
+  if (s->precision == CNRF_PRECISION_FP32) {
+    if (!backward) return b + (s->keep ? 0 : saved_f32_bytes(d));     // inference still needs the activation buffers
+    return b + 2 * al(d.M * max_sz(d.H, d.C + 1)) + al(d.N * d.C);
+  }
+  return b + al(d.N * d.C) + (s->keep || backward ? 0 : 3 * al(d.N * d.C)) + cnrf_tc_workspace_bytes(d.N, d.M, backward);
+}
+
+// tensor-core per-sample chain (mlp_tc.cu).  x_xyz == nullptr means "encode pts in-kernel" (field mode).
+struct TcChainArgs {
+  int64_t N, M; int S, pairing, dx, dd;
+  const cnrf_codenerf_params* p;
+  const float* x_xyz; int64_t ld_xyz;         // pre-embedded input, or
+  const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;   // points to encode
+  const float *b2, *bo, *br, *bd;             // per-ray bias tables [N,256],[N,257],[N,3],[N,256]
+};
+int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
+                      cudaStream_t st);
+int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* saved, size_t saved_bytes,
+                      const cnrf_codenerf_grads* g, float* d_b2, float* d_bo, float* d_br, float* d_bd,
+                      float* g_x_xyz /*[M,dx] or NULL*/, void* ws, size_t ws_bytes, cudaStream_t st);
+
+namespace {
+
+struct FieldIn {   // everything the two entry-point families share
+  const float* x_xyz; int64_t ld_xyz; const float* x_dir; int64_t ld_dir;
+  const float* z_s; int64_t ld_zs; const float* z_t; int64_t ld_zt;
+  const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;     // only for the fused bf16 field path
+};
+
+int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const FieldIn& in, float* raw,
+                      void* saved, size_t saved_bytes, void* ws, size_t ws_bytes, cudaStream_t st) {
+  Dims d = dims_of(s);
+  Arena w(ws, ws_bytes);
+  Tables t;
+  carve_tables(d, w, t);
+  if (!w.ok) return CNRF_E_WORKSPACE;
+  if (s->precision == CNRF_PRECISION_FP32) {
+    SavedF32 sv;
+    if (s->keep) {
+      if (!saved || !carve_saved(d, saved, saved_bytes, sv)) return CNRF_E_WORKSPACE;
+    } else {
+      size_t need = saved_f32_bytes(d);
+      if (w.off + need > w.cap) return CNRF_E_WORKSPACE;
+      carve_saved(d, w.base + w.off, need, sv);
+    }
+    RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, sv.as1, sv.as2, sv.at, t, st));
+    return chain_fwd_f32(d, p, in.x_xyz, in.ld_xyz, t, sv, raw, st);
+  }
+  // bf16 tensor-core chain: needs H = C = 256
+  if (d.H != 256 || d.C != 256 || d.dx > 64 || d.dd > 64) return CNRF_E_UNSUPPORTED;
+  float *as1, *as2, *at;
+  char* tc_saved = nullptr; size_t tc_saved_bytes = 0;
+  if (s->keep) {
+    if (!saved) return CNRF_E_WORKSPACE;
+    Arena sa(saved, saved_bytes);
+    as1 = sa.take(d.N * d.C); as2 = sa.take(d.N * d.C); at = sa.take(d.N * d.C);
+    if (!sa.ok) return CNRF_E_WORKSPACE;
+    tc_saved = sa.base + sa.off; tc_saved_bytes = sa.cap - sa.off;
+  } else {
+    as1 = w.take(d.N * d.C); as2 = w.take(d.N * d.C); at = w.take(d.N * d.C);
+    if (!w.ok) return CNRF_E_WORKSPACE;
+  }
+  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, t, st));
+  TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
+                in.inc_xyz, t.b2, t.bo, t.br, t.bd};
+  return cnrf_tc_chain_fwd(a, raw, tc_saved, tc_saved_bytes, w.base + w.off, w.cap - w.off, st);
+}
+
+int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const FieldIn& in, const float* g_raw,
+                      const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t,
+                      float* g_x_xyz, float* g_x_dir, void* ws, size_t ws_bytes, cudaStream_t st) {
+  Dims d = dims_of(s);
+  if (!s->keep || !saved) return CNRF_E_WORKSPACE;
+  Arena w(ws, ws_bytes);
+  Tables dt;
+  carve_tables(d, w, dt);
+  float* tmp = w.take(d.N * d.C);
+  if (!w.ok) return CNRF_E_WORKSPACE;
+  RUN(zero_weight_grads(d, g, st));
+  if (s->precision == CNRF_PRECISION_FP32) {
+    SavedF32 sv;
+    if (!carve_saved(d, const_cast<void*>(saved), saved_bytes, sv)) return CNRF_E_WORKSPACE;
+    size_t wide = max_sz(d.H, d.C + 1);
+    float* ga = w.take(d.M * wide);
+    float* gb = w.take(d.M * wide);
+    if (!w.ok) return CNRF_E_WORKSPACE;
+    RUN(chain_bwd_f32(d, p, g, in.x_xyz, in.ld_xyz, g_raw, sv, ga, gb, dt, g_x_xyz, st));
+    return per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, sv.as1, sv.as2, sv.at, dt,
+                       tmp, g_z_s, g_z_t, g_x_dir, st);
+  }
+  if (d.H != 256 || d.C != 256 || d.dx > 64 || d.dd > 64) return CNRF_E_UNSUPPORTED;
+  Arena sa(const_cast<void*>(saved), saved_bytes);
+  float* as1 = sa.take(d.N * d.C); float* as2 = sa.take(d.N * d.C); float* at = sa.take(d.N * d.C);
+  if (!sa.ok) return CNRF_E_WORKSPACE;
+  TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
+                in.inc_xyz, nullptr, nullptr, nullptr, nullptr};
+  RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, dt.bd, g_x_xyz,
+                        w.base + w.off, w.cap - w.off, st));
+  return per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, dt, tmp, g_z_s,
+                     g_z_t, g_x_dir, st);
+}
+
+int check_common(const cnrf_field_shape* s, const cnrf_codenerf_params* p) {
+  int rc = check_shape(s);
+  if (rc) return rc;
+  if (!p) return CNRF_E_NULL;
+  for (int l = 0; l < CNRF_NUM_LAYERS; ++l)
+    if (!p->weight[l] || !p->bias[l]) return CNRF_E_NULL;
+  return CNRF_OK;
+}
+
+}  // namespace
+
+extern "C" int cnrf_codenerf_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* x_xyz,
+                                 int64_t ld_xyz, const float* x_dir, int64_t ld_dir, const float* z_s, int64_t ld_zs,
+                                 const float* z_t, int64_t ld_zt, float* raw, void* saved, size_t saved_bytes,
+                                 void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+  RUN(check_common(s, p));
+  CNRF_REQUIRE(x_xyz && x_dir && z_s && z_t && raw && workspace, CNRF_E_NULL);
+  FieldIn in{x_xyz, ld_xyz, x_dir, ld_dir, z_s, ld_zs, z_t, ld_zt, nullptr, nullptr, 0, 0};
+  return codenerf_fwd_impl(s, p, in, raw, saved, saved_bytes, workspace, workspace_bytes, as_stream(stream));
+}
+
+extern "C" int cnrf_codenerf_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* x_xyz,
+                                 int64_t ld_xyz, const float* x_dir, int64_t ld_dir, const float* z_s, int64_t ld_zs,
+                                 const float* z_t, int64_t ld_zt, const float* g_raw, const void* saved,
+                                 size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t,
+                                 float* g_x_xyz, float* g_x_dir, void* workspace, size_t workspace_bytes,
+                                 cnrf_stream_t stream) {
+  RUN(check_common(s, p));
+  CNRF_REQUIRE(x_xyz && x_dir && z_s && z_t && g_raw && g && g_z_s && g_z_t && workspace, CNRF_E_NULL);
+  FieldIn in{x_xyz, ld_xyz, x_dir, ld_dir, z_s, ld_zs, z_t, ld_zt, nullptr, nullptr, 0, 0};
+  return codenerf_bwd_impl(s, p, in, g_raw, saved, saved_bytes, g, g_z_s, g_z_t, g_x_xyz, g_x_dir, workspace,
+                           workspace_bytes, as_stream(stream));
+}
+
+// ---- forward_pass: encode + pair + field (view_synthesis/nerf/__init__.py:116-134) ------------------------------
+namespace {
+
+// viewdirs = rd / ||rd||   (nerf/__init__.py:126)
+__global__ void normalize_dirs_kernel(const float* __restrict__ rd, int64_t N, float* __restrict__ out) {
+  int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float x = rd[n * 3], y = rd[n * 3 + 1], z = rd[n * 3 + 2];
+  float nr = sqrtf(x * x + y * y + z * z);
+  out[n * 3] = __fdiv_rn(x, nr); out[n * 3 + 1] = __fdiv_rn(y, nr); out[n * 3 + 2] = __fdiv_rn(z, nr);
+}
+// g_rd = (g - d^ (d^ . g)) / ||rd||
+__global__ void normalize_dirs_bwd_kernel(const float* __restrict__ rd, const float* __restrict__ g, int64_t N,
+                                          float* __restrict__ g_rd) {
+  int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= N) return;
+  float x = rd[n * 3], y = rd[n * 3 + 1], z = rd[n * 3 + 2];
+  float nr = sqrtf(x * x + y * y + z * z), inv = 1.0f / nr;
+  float ux = x * inv, uy = y * inv, uz = z * inv;
+  float gx = g[n * 3], gy = g[n * 3 + 1], gz = g[n * 3 + 2];
+  float dot = ux * gx + uy * gy + uz * gz;
+  g_rd[n * 3] = (gx - ux * dot) * inv; g_rd[n * 3 + 1] = (gy - uy * dot) * inv; g_rd[n * 3 + 2] = (gz - uz * dot) * inv;
+}
+
+struct FieldScratch { float *dirn, *demb, *xemb, *g_dirn, *g_demb, *g_xemb; };
+inline size_t field_scratch_bytes(const Dims& d, int precision, int backward) {
+  size_t b = al(d.N * 3) + al(d.N * d.dd);
+  if (precision == CNRF_PRECISION_FP32) b += al(d.M * d.dx);
+  if (backward) b += al(d.N * 3) + al(d.N * d.dd) + al(d.M * d.dx);
+  return b;
+}
+inline void carve_field(const Dims& d, int precision, int backward, Arena& a, FieldScratch& f) {
+  f.dirn = a.take(d.N * 3); f.demb = a.take(d.N * d.dd);
+  f.xemb = precision == CNRF_PRECISION_FP32 ? a.take(d.M * d.dx) : nullptr;
+  f.g_dirn = f.g_demb = f.g_xemb = nullptr;
+  if (backward) { f.g_dirn = a.take(d.N * 3); f.g_demb = a.take(d.N * d.dd); f.g_xemb = a.take(d.M * d.dx); }
+}
+
+int field_encode(const Dims& d, int precision, const float* pts, const float* rd, const float* fx, int Lx, int incx,
+                 const float* fd, int Ld, int incd, const FieldScratch& f, cudaStream_t st) {
+  normalize_dirs_kernel<<<grid_for(d.N, 256), 256, 0, st>>>(rd, d.N, f.dirn);
+  CNRF_LAUNCH_CHECK();
+  RUN(cnrf_pos_embed_fwd_ld(f.dirn, d.N, 3, fd, Ld, incd, d.dd, f.demb, st));
+  if (precision == CNRF_PRECISION_FP32) RUN(cnrf_pos_embed_fwd_ld(pts, d.M, 3, fx, Lx, incx, d.dx, f.xemb, st));
+  return CNRF_OK;
+}
+
+int check_field(const cnrf_field_shape* s, int Lx, int Ld, int& incx, int& incd) {
+  if (Lx <= 0 || Ld <= 0) return CNRF_E_SHAPE;
+  incx = s->dim_xyz - 6 * Lx; incd = s->dim_dir - 6 * Ld;        // dim = 3*(include_input + 2L)
+  if ((incx != 0 && incx != 3) || (incd != 0 && incd != 3)) return CNRF_E_SHAPE;
+  incx /= 3; incd /= 3;
+  return CNRF_OK;
+}
+
+}  // namespace
+
+extern "C" size_t cnrf_field_workspace_bytes(const cnrf_field_shape* s, int32_t backward) {
+  if (check_shape(s) != CNRF_OK) return 0;
+  return field_scratch_bytes(dims_of(s), s->precision, backward) + cnrf_codenerf_workspace_bytes(s, backward);
+}
+
+extern "C" int cnrf_field_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
+                              const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
+                              int32_t L_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
+                              float* raw, void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes,
+                              cnrf_stream_t stream) {
+  RUN(check_common(s, p));
+  CNRF_REQUIRE(pts && rd && freqs_xyz && freqs_dir && z_s && z_t && raw && workspace, CNRF_E_NULL);
+  int incx, incd;
+  RUN(check_field(s, L_xyz, L_dir, incx, incd));
+  cudaStream_t st = as_stream(stream);
+  Dims d = dims_of(s);
+  Arena w(workspace, workspace_bytes);
+  FieldScratch f;
+  carve_field(d, s->precision, 0, w, f);
+  if (!w.ok) return CNRF_E_WORKSPACE;
+  RUN(field_encode(d, s->precision, pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
+  FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx};
+  return codenerf_fwd_impl(s, p, in, raw, saved, saved_bytes, w.base + w.off, w.cap - w.off, st);
+}
+
+extern "C" int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
+                              const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
+                              int32_t L_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
+                              const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g,
+                              float* g_z_s, float* g_z_t, float* g_pts, float* g_rd, void* workspace,
+                              size_t workspace_bytes, cnrf_stream_t stream) {
+  RUN(check_common(s, p));
+  CNRF_REQUIRE(pts && rd && freqs_xyz && freqs_dir && z_s && z_t && g_raw && g && g_z_s && g_z_t && workspace,
+               CNRF_E_NULL);
+  int incx, incd;
+  RUN(check_field(s, L_xyz, L_dir, incx, incd));
+  cudaStream_t st = as_stream(stream);
+  Dims d = dims_of(s);
+  Arena w(workspace, workspace_bytes);
+  FieldScratch f;
+  carve_field(d, s->precision, 1, w, f);
+  if (!w.ok) return CNRF_E_WORKSPACE;
+  RUN(field_encode(d, s->precision, pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
+  FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx};
+  RUN(codenerf_bwd_impl(s, p, in, g_raw, saved, saved_bytes, g, g_z_s, g_z_t, g_pts ? f.g_xemb : nullptr,
+                        g_rd ? f.g_demb : nullptr, w.base + w.off, w.cap - w.off, st));
+  if (g_pts) RUN(cnrf_pos_embed_bwd_ld(pts, f.g_xemb, d.M, 3, freqs_xyz, L_xyz, incx, d.dx, g_pts, st));
+  if (g_rd) {
+    RUN(cnrf_pos_embed_bwd_ld(f.dirn, f.g_demb, d.N, 3, freqs_dir, L_dir, incd, d.dd, f.g_dirn, st));
+    normalize_dirs_bwd_kernel<<<grid_for(d.N, 256), 256, 0, st>>>(rd, f.g_dirn, d.N, g_rd);
+    CNRF_LAUNCH_CHECK();
+  }
+  return CNRF_OK;
+}

@@ -1,0 +1,107 @@
+"""Networks of the hot path -- constructor signatures, parameter names and shapes of the reference's
+view_synthesis/models/model.py:79-194, so reference checkpoints load both ways and DDP / optimizer param groups see
+the same modules.  The arithmetic runs in libcnrf.so."""
+from typing import Tuple
+
+import torch
+
+from codenerf_b200 import _lib, ops
+
+__all__ = ["CodeNeRFModel", "ShapeTextureEmbedding", "get_params_tensor"]
+
+
+def get_params_tensor(model, is_distributed):
+    """models/model.py:79-84."""
+    if is_distributed:
+        shape_params, texture_params = model.module.get_params_tensor()
+    else:
+        shape_params, texture_params = model.get_params_tensor()
+    return shape_params, texture_params
+
+
+class ShapeTextureEmbedding(torch.nn.Module):
+    """Two nn.Embedding tables (models/model.py:87-120).  The row gather and its sparse scatter backward stay in
+    torch: the render kernels consume per-ray codes and return per-ray code gradients."""
+
+    def __init__(self, num_embeddings, shape_code_size=128, texture_code_size=128):
+        super(ShapeTextureEmbedding, self).__init__()
+        self.num_embeddings = num_embeddings
+        self.shape_code_size = shape_code_size
+        self.texture_code_size = texture_code_size
+        self.shape_embedding = torch.nn.Embedding(self.num_embeddings, self.shape_code_size)
+        self.texture_embedding = torch.nn.Embedding(self.num_embeddings, self.texture_code_size)
+
+    def forward(self, object_ids: torch.Tensor):
+        return self.shape_embedding(object_ids), self.texture_embedding(object_ids)
+
+    def get_all_embeddings(self, device):
+        all_idx = torch.arange(0, self.num_embeddings, dtype=int, device=device)
+        return self.shape_embedding(all_idx), self.texture_embedding(all_idx)
+
+    def get_params_tensor(self) -> Tuple[torch.Tensor, torch.Tensor]:
+        shape_params, texture_params = None, None
+        for name, params in self.named_parameters():
+            if 'shape' in name:
+                shape_params = torch.cat([x.view(-1) for x in params.data])
+            if 'texture' in name:
+                texture_params = torch.cat([x.view(-1) for x in params.data])
+        return shape_params, texture_params
+
+
+class CodeNeRFModel(torch.nn.Module):
+    """CodeNeRF MLP conditioned on shape / texture codes (models/model.py:123-194).
+
+    The nine torch.nn.Linear modules only HOLD the parameters (names, shapes and default init as the reference);
+    forward never calls them.  forward(z_s, z_t, x) accepts
+      * x: a view_synthesis.nerf.FieldQuery (what forward_pass passes): z_s / z_t are per-RAY (N, C) -> (N, S, 4);
+      * x: a tensor (M, dim_xyz + dim_dir) with per-sample codes (M, C), the reference's literal signature -> (M, 4).
+    """
+
+    def __init__(self, hidden_size=128, num_embeddings=1, shape_code_size=128, texture_code_size=128,
+                 num_encoding_fn_xyz=6, num_encoding_fn_dir=4, include_input_xyz=True, include_input_dir=True):
+        super(CodeNeRFModel, self).__init__()
+        self.hidden_size = hidden_size
+        self.shape_code_size = shape_code_size
+        self.texture_code_size = texture_code_size
+        include_input_xyz = 3 if include_input_xyz else 0
+        include_input_dir = 3 if include_input_dir else 0
+        self.dim_xyz = include_input_xyz + 2 * 3 * num_encoding_fn_xyz
+        self.dim_dir = include_input_dir + 2 * 3 * num_encoding_fn_dir
+
+        self.layer_xyz1 = torch.nn.Linear(self.dim_xyz, self.hidden_size)
+        self.layer_xyz2 = torch.nn.Linear(self.hidden_size + self.shape_code_size, self.hidden_size)
+        self.fc_out = torch.nn.Linear(self.hidden_size + self.shape_code_size, self.shape_code_size + 1)
+        self.shape_code_layer1 = torch.nn.Linear(self.shape_code_size, self.shape_code_size)
+        self.shape_code_layer2 = torch.nn.Linear(self.shape_code_size, self.shape_code_size)
+        self.texture_code_layer1 = torch.nn.Linear(self.shape_code_size, self.shape_code_size)
+        self.layer_dir1 = torch.nn.Linear(self.dim_dir + self.shape_code_size, self.hidden_size)
+        self.layer_dir2 = torch.nn.Linear(self.hidden_size, self.hidden_size)
+        self.fc_rgb = torch.nn.Linear(self.hidden_size + self.texture_code_size, 3)
+        self.activation = torch.nn.functional.relu
+
+    def _param_list(self):
+        out = []
+        for name in _lib.LAYER_NAMES:
+            layer = getattr(self, name)
+            out += [layer.weight, layer.bias]
+        return out
+
+    def forward(self, z_s: torch.Tensor, z_t: torch.Tensor, x):
+        from ..nerf import FieldQuery
+        if self.shape_code_size != self.texture_code_size:
+            raise ValueError("CodeNeRFModel needs shape_code_size == texture_code_size (models/model.py:150,153)")
+        params = self._param_list()
+        if isinstance(x, FieldQuery):
+            ex, ed = x.embedder_xyz, x.embedder_dir
+            assert 3 * ex.out_dim_per_channel == self.dim_xyz and 3 * ed.out_dim_per_channel == self.dim_dir, \
+                "embedder widths do not match the model's dim_xyz / dim_dir"
+            precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[x.precision]
+            pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
+            return ops.codenerf_field(params, x.pts, x.rd, z_s, z_t, ex.frequency_bands, ed.frequency_bands,
+                                      self.hidden_size, self.shape_code_size, self.dim_xyz, self.dim_dir,
+                                      pairing=pairing, precision=precision)
+        lead = x.shape[:-1]
+        out = ops.codenerf_model(params, z_s.reshape(-1, z_s.shape[-1]), z_t.reshape(-1, z_t.shape[-1]),
+                                 x.reshape(-1, x.shape[-1]), self.hidden_size, self.shape_code_size, self.dim_xyz,
+                                 self.dim_dir, precision=_lib.PRECISION_FP32)
+        return out.reshape(*lead, 4)

@@ -1,0 +1,115 @@
+"""Host-side logic of the drop-in package (no GPU): module surface, parameter names, split arithmetic, gloo gather."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from oracle import codenerf_oracle as orc
+
+
+def test_module_surface_matches_reference_names():
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    for n in ("RaySampler", "PointSampler", "PositionalEmbedder", "volume_render", "prepare_samplers",
+              "prepare_embedders", "predict_radiance_and_render", "forward_pass", "parallel_image_render"):
+        assert hasattr(nerf, n)
+    for n in ("CodeNeRFModel", "ShapeTextureEmbedding", "get_params_tensor"):
+        assert hasattr(models, n)
+    import view_synthesis
+    assert os.path.realpath(nerf.__file__).startswith(os.path.realpath(os.path.join(os.path.dirname(__file__), "..", "code-nerf_b200")))
+
+
+def test_state_dict_names_and_shapes():
+    import view_synthesis.models as models
+    m = models.CodeNeRFModel(256, 1, 256, 256, 10, 4, True, True)
+    sd = m.state_dict()
+    shapes = orc.codenerf_shapes(256, 256, 63, 27)
+    assert sorted(sd) == sorted([f"{k}.weight" for k in shapes] + [f"{k}.bias" for k in shapes])
+    for k, (o, i) in shapes.items():
+        assert tuple(sd[k + ".weight"].shape) == (o, i) and tuple(sd[k + ".bias"].shape) == (o,)
+    assert sum(p.numel() for p in m.parameters()) == 616964
+    e = models.ShapeTextureEmbedding(7, 256, 256)
+    assert sorted(e.state_dict()) == ["shape_embedding.weight", "texture_embedding.weight"]
+    s, t = e.get_params_tensor()
+    assert s.numel() == 7 * 256 and not s.requires_grad                          # F10: detached regulariser
+    assert models.get_params_tensor(e, False)[1].numel() == 7 * 256
+
+
+def test_constructor_asserts():
+    import view_synthesis.nerf as nerf
+    cpu, f32 = torch.device("cpu"), torch.float32
+    with pytest.raises(AssertionError):
+        nerf.PointSampler(8, 8, 2.0, 1.0, "lindepth", False, f32, cpu)
+    with pytest.raises(AssertionError):
+        nerf.PositionalEmbedder(0, True, True, f32, cpu)
+    with pytest.raises(AssertionError):
+        nerf.RaySampler(4, 4, torch.eye(4), 17, cpu, f32)
+    with pytest.raises(AssertionError):
+        nerf.RaySampler(4, 4, torch.eye(3), 4, cpu, f32)
+    ps = nerf.PointSampler(8, 16, 0.8, 1.8, "lindepth", True, f32, cpu)
+    z, lo, up = orc.depth_tables(8, 0.8, 1.8, "lindepth")
+    assert torch.equal(ps.z_vals, z) and torch.equal(ps.lower, lo) and torch.equal(ps.upper, up)
+    pe = nerf.PositionalEmbedder(10, True, True, f32, cpu)
+    assert pe.frequency_bands.tolist() == [float(2 ** i) for i in range(10)]
+
+
+def test_rng_draw_is_the_reference_draw():
+    """sample_uniform draws torch.rand((N,S)); the reference draws rand_like(upper.expand(N,S)) (point_sampler.py:64)."""
+    up = torch.arange(5.0)
+    torch.manual_seed(3)
+    a = torch.rand_like(up.expand(7, 5), dtype=torch.float32)
+    torch.manual_seed(3)
+    b = torch.rand((7, 5), dtype=torch.float32)
+    assert torch.equal(a, b)
+
+
+def test_render_split(golden_dir):
+    import view_synthesis.nerf as nerf
+    g = np.load(os.path.join(golden_dir, "render_split.npz"), allow_pickle=True)
+    for num_rays, n_gpus, per, pad in g["cases"]:
+        p, q = nerf.render_split(int(num_rays), int(n_gpus))
+        assert p == list(per) and q == list(pad)
+
+
+class _Cfg(dict):
+    __getattr__ = dict.__getitem__
+
+
+def _fake_render(rays, point_sampler, embedders, mc, mf, latent):
+    ro, rd = rays
+    return None, rd * 2.0 + ro
+
+
+def _worker(rank, world, port, H, W, out):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import view_synthesis.nerf as nerf
+    nerf.predict_radiance_and_render = _fake_render
+
+    class FakeRays:
+        def get_bundle(self, tform_cam2world):
+            rd = torch.arange(H * W * 3, dtype=torch.float32).reshape(1, H, W, 3)
+            return torch.ones_like(rd), rd
+    cfg = _Cfg(is_distributed=True, gpus=world, nerf=_Cfg(validation=_Cfg(chunksize=5)))
+    models = {"nerf_coarse": torch.nn.Identity(), "nerf_fine": torch.nn.Identity()}
+    rgb = nerf.parallel_image_render(cfg, torch.eye(4)[None], [torch.zeros(1, 4), torch.zeros(1, 4)], models,
+                                     (FakeRays(), None), (None, None), torch.device("cpu"))
+    if rank == 0:
+        torch.save(rgb, out)
+    else:
+        assert rgb is None
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("H,W", [(3, 5), (4, 4)])
+def test_parallel_image_render_two_ranks_gloo(tmp_path, H, W):
+    out = str(tmp_path / "rgb.pt")
+    port = 29500 + (os.getpid() % 2000) + H
+    mp.spawn(_worker, args=(2, port, H, W, out), nprocs=2, join=True)
+    rgb = torch.load(out)
+    want = torch.arange(H * W * 3, dtype=torch.float32).reshape(-1, 3) * 2.0 + 1.0
+    assert torch.equal(rgb, want)          # ordering and trimming of the padded all_gather (nerf/__init__.py:212-226)
