@@ -1,6 +1,9 @@
 // Library-level entry points of libcnrf.so.
 #include "common.cuh"
 
+long long g_cnrf_launches = 0;
+extern "C" int64_t cnrf_launch_count(void) { return (int64_t)g_cnrf_launches; }
+
 extern "C" int cnrf_abi_version(void) { return CNRF_ABI_VERSION; }
 
 extern "C" const char* cnrf_error_string(int code) {

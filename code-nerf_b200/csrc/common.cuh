@@ -10,8 +10,10 @@
   } while (0)
 
 // Launch-error check that never synchronises: reports bad configurations, not asynchronous faults.
+extern long long g_cnrf_launches;   // api.cu: kernels launched by this library (bench.py's gpu_launches claim)
 #define CNRF_LAUNCH_CHECK()                      \
   do {                                           \
+    ++g_cnrf_launches;                           \
     cudaError_t e__ = cudaGetLastError();        \
     if (e__ != cudaSuccess) return (int)e__;     \
   } while (0)

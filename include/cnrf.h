@@ -42,6 +42,8 @@ int cnrf_abi_version(void);
 const char* cnrf_error_string(int code);
 /* 0 when the current device can run the tcgen05 kernels (compute capability 10.x), else CNRF_E_DEVICE. */
 int cnrf_device_check(void);
+/* Number of kernels this library has launched in the calling process (bench.py reports it as gpu_launches). */
+int64_t cnrf_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------------
  * Ray generation.  RaySampler.__init__ / get_bundle / sample, view_synthesis/nerf/ray_sampler.py:31-51,84-99,66-80.

@@ -1,0 +1,169 @@
+"""Parity of the CodeNeRF field and of the whole predict_radiance_and_render pipeline (CUDA, through the drop-in
+package and the C ABI) against the golden fixtures and the CPU oracle.  fp32 mode carries the 1e-3 gate."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import codenerf_oracle as orc
+
+pytestmark = pytest.mark.gpu
+T = torch.from_numpy
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch.device("cuda", 0)
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name), allow_pickle=True)
+
+
+def close(a, b, tol=1e-6, rtol=None):
+    a = a.detach().cpu().numpy() if torch.is_tensor(a) else np.asarray(a)
+    b = b.detach().cpu().numpy() if torch.is_tensor(b) else np.asarray(b)
+    np.testing.assert_allclose(a, b, rtol=tol if rtol is None else rtol, atol=tol)
+
+
+def model_from(params, dev, hidden, code):
+    import view_synthesis.models as models
+    m = models.CodeNeRFModel(hidden, 1, code, code, 10, 4, True, True)
+    m.load_state_dict({k: v.detach().clone() for k, v in params.items()})
+    return m.to(dev)
+
+
+def embedders(dev):
+    import view_synthesis.nerf as nerf
+    return (nerf.PositionalEmbedder(10, True, True, torch.float32, dev),
+            nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+
+
+@pytest.mark.parametrize("tag", ["h64", "h256"])
+def test_codenerf_model_golden(golden_dir, dev, tag):
+    """CodeNeRFModel.forward(z_s, z_t, x) with per-sample codes, forward + every gradient."""
+    g = load(golden_dir, f"codenerf_{tag}.npz")
+    hidden, code = int(g["hidden"]), int(g["code"])
+    m = model_from(orc.make_codenerf_params(int(g["seed"]), hidden, code), dev, hidden, code)
+    zs, zt, x = (T(g[k]).to(dev).requires_grad_(True) for k in ("z_s", "z_t", "x"))
+    y = m(zs, zt, x)
+    close(y, g["y"], 3e-5)
+    y.backward(T(g["gy"]).to(dev))
+    close(zs.grad, g["g_z_s"], 3e-5); close(zt.grad, g["g_z_t"], 3e-5); close(x.grad, g["g_x"], 3e-5)
+    for name, prm in m.named_parameters():
+        gr = prm.grad.cpu().numpy()
+        np.testing.assert_allclose(gr.reshape(-1)[::97], g["gprobe_" + name], rtol=1e-4, atol=3e-5)
+        np.testing.assert_allclose(gr.astype(np.float64).sum(), float(g["gsum_" + name]), rtol=1e-3, atol=2e-3)
+
+
+@pytest.mark.parametrize("tag", ["h64", "h256"])
+def test_forward_pass_golden_pairing(golden_dir, dev, tag):
+    import view_synthesis.nerf as nerf
+    g = load(golden_dir, f"codenerf_{tag}.npz")
+    hidden, code = int(g["hidden"]), int(g["code"])
+    m = model_from(orc.make_codenerf_params(int(g["seed"]), hidden, code), dev, hidden, code)
+    nerf.set_precision("fp32")
+    args = (T(g["fp_rd"]).to(dev), T(g["fp_pts"]).to(dev), (T(g["fp_z_s"]).to(dev), T(g["fp_z_t"]).to(dev)))
+    with torch.no_grad():
+        nerf.set_pairing("reference")
+        raw = nerf.forward_pass(m, embedders(dev), *args)
+        nerf.set_pairing("correct")
+        raw_ok = nerf.forward_pass(m, embedders(dev), *args)
+        nerf.set_pairing("reference")
+    close(raw, g["fp_raw"], 3e-5)                                       # bug-compatible by default (F6)
+    assert not np.allclose(raw_ok.cpu().numpy(), g["fp_raw"], atol=1e-4)
+
+
+def _pipeline(golden_dir, dev, precision):
+    import view_synthesis.nerf as nerf
+    from codenerf_b200 import ops
+    g = load(golden_dir, "pipeline.npz")
+    hidden, Sc, Nf = int(g["hidden"]), int(g["Sc"]), int(g["Nf"])
+    mc = model_from(orc.make_codenerf_params(int(g["seed_c"]), hidden, hidden), dev, hidden, hidden)
+    mf = model_from(orc.make_codenerf_params(int(g["seed_f"]), hidden, hidden), dev, hidden, hidden)
+    ps = nerf.PointSampler(Sc, Nf, 0.8, 1.8, "lindepth", True, torch.float32, dev)
+    draws = [T(g["t_rand"]).to(dev), T(g["u"]).to(dev)]
+    real_rand = torch.rand
+    torch.rand = lambda *a, **k: draws.pop(0)                           # inject the reference's two device draws (H5)
+    nerf.set_precision(precision)
+    try:
+        ro, rd, zs, zt = (T(g[k]).to(dev).requires_grad_(True) for k in ("ro", "rd", "z_s", "z_t"))
+        rgb_c, rgb_f = nerf.predict_radiance_and_render((ro, rd), ps, embedders(dev), mc, mf, (zs, zt))
+    finally:
+        torch.rand = real_rand
+    tgt = T(g["target"]).to(dev)
+    loss = torch.nn.functional.mse_loss(rgb_c, tgt) + torch.nn.functional.mse_loss(rgb_f, tgt)
+    loss.backward()
+    return g, rgb_c, rgb_f, loss, (ro, rd, zs, zt), (mc, mf)
+
+
+def test_pipeline_golden_fp32(golden_dir, dev):
+    """End to end with pose gradients (C3-style): rgb within 1e-3 abs (measured ~1e-6), all gradients."""
+    g, rgb_c, rgb_f, loss, (ro, rd, zs, zt), (mc, mf) = _pipeline(golden_dir, dev, "fp32")
+    close(rgb_c, g["rgb_coarse"], 1e-3); close(rgb_f, g["rgb_fine"], 1e-3)      # the north_star gate
+    close(rgb_c, g["rgb_coarse"], 3e-5); close(rgb_f, g["rgb_fine"], 3e-5)      # what fp32 actually achieves
+    np.testing.assert_allclose(loss.item(), float(g["loss"]), rtol=1e-4)
+    close(ro.grad, g["g_ro"], 3e-5, rtol=1e-3); close(rd.grad, g["g_rd"], 3e-5, rtol=1e-3)
+    close(zs.grad, g["g_z_s"], 3e-5, rtol=1e-3); close(zt.grad, g["g_z_t"], 3e-5, rtol=1e-3)
+    for tag, m in (("c", mc), ("f", mf)):
+        for name, prm in m.named_parameters():
+            np.testing.assert_allclose(prm.grad.cpu().numpy().reshape(-1)[::53], g[f"gprobe_{tag}_{name}"], rtol=2e-3,
+                                       atol=3e-6)
+
+
+def test_field_vs_oracle_c1_shapes_fp32(dev):
+    """C1 layer shapes (hidden 256, codes 256, 32 and 160 samples) on 96 rays, both pairings, broadcast codes."""
+    import view_synthesis.nerf as nerf
+    nerf.set_precision("fp32")
+    rng = np.random.default_rng(7)
+    p = orc.make_codenerf_params(5, 256, 256)
+    m = model_from(p, dev, 256, 256)
+    fx, fd = orc.frequency_bands(10, True), orc.frequency_bands(4, True)
+    for N, S, pairing, bcast in ((96, 32, "reference", False), (40, 160, "correct", False), (33, 7, "reference", True)):
+        nerf.set_pairing(pairing)
+        pts = T(rng.uniform(-1.5, 1.5, size=(N, S, 3)).astype(np.float32))
+        rd = T(rng.normal(size=(N, 3)).astype(np.float32))
+        zs = T(rng.normal(size=(1 if bcast else N, 256)).astype(np.float32))
+        zt = T(rng.normal(size=(1 if bcast else N, 256)).astype(np.float32))
+        graw = T(rng.normal(size=(N, S, 4)).astype(np.float32))
+        d_in = [t.clone().to(dev).requires_grad_(True) for t in (pts, rd, zs, zt)]
+        raw = nerf.forward_pass(m, embedders(dev), d_in[1], d_in[0], (d_in[2].expand(N, -1), d_in[3].expand(N, -1)))
+        m.zero_grad()
+        raw.backward(graw.to(dev))
+        c_in = [t.clone().requires_grad_(True) for t in (pts, rd, zs, zt)]
+        pc = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+        raw_c = orc.forward_pass(pc, c_in[1], c_in[0], c_in[2].expand(N, -1), c_in[3].expand(N, -1), fx, fd,
+                                 pairing=pairing)
+        raw_c.backward(graw)
+        close(raw, raw_c, 1e-4)
+        for a, b in zip(d_in, c_in):
+            s = max(1.0, float(b.grad.abs().max()))
+            np.testing.assert_allclose(a.grad.cpu().numpy(), b.grad.numpy(), rtol=2e-3, atol=2e-5 * s)
+        for name, prm in m.named_parameters():
+            s = max(1.0, float(pc[name].grad.abs().max()))
+            np.testing.assert_allclose(prm.grad.cpu().numpy(), pc[name].grad.numpy(), rtol=2e-3, atol=2e-5 * s)
+    nerf.set_pairing("reference")
+
+
+def test_no_grad_inference_and_ddp_style_call(dev):
+    """no_grad path keeps nothing; a wrapper module exposing .module (as DistributedDataParallel does) still fuses."""
+    import view_synthesis.nerf as nerf
+    nerf.set_precision("fp32")
+    m = model_from(orc.make_codenerf_params(3, 64, 64), dev, 64, 64)
+
+    class Wrap(torch.nn.Module):
+        def __init__(self, mod):
+            super().__init__()
+            self.module = mod
+
+        def forward(self, *a):
+            return self.module(*a)
+    pts, rd = torch.randn(10, 5, 3, device=dev), torch.randn(10, 3, device=dev)
+    zs, zt = torch.randn(10, 64, device=dev), torch.randn(10, 64, device=dev)
+    with torch.no_grad():
+        a = nerf.forward_pass(m, embedders(dev), rd, pts, (zs, zt))
+        b = nerf.forward_pass(Wrap(m), embedders(dev), rd, pts, (zs, zt))
+    assert a.shape == (10, 5, 4) and torch.equal(a, b) and not a.requires_grad
