@@ -191,6 +191,14 @@ int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
                    size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t, float* g_pts,
                    float* g_rd, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------------
+ * Diagnostics (used by tests only).  One-CTA tcgen05 GEMM over the 128-byte-swizzled shared-memory image the fused
+ * MLP kernels use.  mode 0: D[128,N] = A[128,K] B[N,K]^T (K-major operands); mode 1: D[128,N] = A[K,128]^T B[K,N]
+ * (MN-major operands, the dW = dY^T X form).  *err is set to 1 if the kernel's bounded barrier wait timed out.
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_debug_umma(int32_t mode, const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t* err,
+                    cnrf_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
