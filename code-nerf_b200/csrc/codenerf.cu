@@ -239,7 +239,7 @@ extern "C" size_t cnrf_codenerf_saved_bytes(const cnrf_field_shape* s) {
   if (check_shape(s) != CNRF_OK || !s->keep) return 0;
   Dims d = dims_of(s);
   if (s->precision == CNRF_PRECISION_FP32) return saved_f32_bytes(d);
-  return 3 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M);
+  return 3 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M) + 2048;
 }
 
 extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32_t backward) {

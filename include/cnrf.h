@@ -196,6 +196,8 @@ int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
  * MLP kernels use.  mode 0: D[128,N] = A[128,K] B[N,K]^T (K-major operands); mode 1: D[128,N] = A[K,128]^T B[K,N]
  * (MN-major operands, the dW = dY^T X form).  *err is set to 1 if the kernel's bounded barrier wait timed out.
  * ---------------------------------------------------------------------------------------------------- */
+/* Synchronises the device; returns 1 if a tensor-core kernel of this process hit its bounded barrier-wait timeout. */
+int cnrf_debug_tc_error(void);
 int cnrf_debug_umma(int32_t mode, const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t* err,
                     cnrf_stream_t stream);
 
