@@ -61,10 +61,11 @@ inline bool carve_saved(const Dims& d, void* p, size_t bytes, SavedF32& s) {
   return a.ok;
 }
 // per-ray bias tables (forward workspace) and their gradients (backward workspace)
-struct Tables { float *b2, *bo, *br, *bd; };
-inline size_t tables_bytes(const Dims& d) { return 2 * al(d.N * d.H) + al(d.N * (d.C + 1)) + al(d.N * 3); }
+struct Tables { float *b2, *bo, *br, *bd, *bof, *bos; };   // bof/bos: fc_out table split (aligned feat / sigma) for the tc path
+inline size_t tables_bytes(const Dims& d) { return 2 * al(d.N * d.H) + al(d.N * (d.C + 1)) + al(d.N * 3) + al(d.N * d.C) + al(d.N); }
 inline void carve_tables(const Dims& d, Arena& a, Tables& t) {
   t.b2 = a.take(d.N * d.H); t.bo = a.take(d.N * (d.C + 1)); t.br = a.take(d.N * 3); t.bd = a.take(d.N * d.H);
+  t.bof = a.take(d.N * d.C); t.bos = a.take(d.N);
 }
 
 #define RUN(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
@@ -116,14 +117,19 @@ inline void pair_index(const Dims& d, int64_t& div, int64_t& mod) {
 // ---- per-ray layers ------------------------------------------------------------------------------------------
 int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir, int64_t ld_dir, const float* z_s,
                 int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
-                cudaStream_t st) {
+                bool split_bo, cudaStream_t st) {
   const int H = d.H, C = d.C;
   const int64_t INF = INT64_MAX;
   RUN(lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 0, 1, INF, 1, st));   // model.py:174
   RUN(lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 0, 1, INF, 1, st));   // :175
   RUN(lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 0, 1, INF, 1, st));// :177
   RUN(lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0, 1, INF, 0, st));
-  RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+  if (split_bo) {   // tensor-core chain: 16-byte aligned feature rows + a separate sigma column
+    RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, t.bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0, 1, INF, 0, st));
+    RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+  } else {
+    RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+  }
   RUN(lin(at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0, 1, INF, 0, st));
   RUN(lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0, 1, INF, 0, st));
   return CNRF_OK;
@@ -260,6 +266,7 @@ struct TcChainArgs {
   const float* x_xyz; int64_t ld_xyz;         // pre-embedded input, or
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;   // points to encode
   const float *b2, *bo, *br, *bd;             // per-ray bias tables [N,256],[N,257],[N,3],[N,256]
+  const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
 };
 int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
                       cudaStream_t st);
@@ -291,7 +298,7 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
       if (w.off + need > w.cap) return CNRF_E_WORKSPACE;
       carve_saved(d, w.base + w.off, need, sv);
     }
-    RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, sv.as1, sv.as2, sv.at, t, st));
+    RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, sv.as1, sv.as2, sv.at, t, false, st));
     return chain_fwd_f32(d, p, in.x_xyz, in.ld_xyz, t, sv, raw, st);
   }
   // bf16 tensor-core chain: needs H = C = 256
@@ -308,9 +315,9 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
     as1 = w.take(d.N * d.C); as2 = w.take(d.N * d.C); at = w.take(d.N * d.C);
     if (!w.ok) return CNRF_E_WORKSPACE;
   }
-  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, t, st));
+  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, t, true, st));
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, t.b2, t.bo, t.br, t.bd};
+                in.inc_xyz, t.b2, t.bo, t.br, t.bd, t.bof, t.bos};
   return cnrf_tc_chain_fwd(a, raw, tc_saved, tc_saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
 
@@ -341,7 +348,7 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   float* as1 = sa.take(d.N * d.C); float* as2 = sa.take(d.N * d.C); float* at = sa.take(d.N * d.C);
   if (!sa.ok) return CNRF_E_WORKSPACE;
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, nullptr, nullptr, nullptr, nullptr};
+                in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
   RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, dt.bd, g_x_xyz,
                         w.base + w.off, w.cap - w.off, st));
   return per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, dt, tmp, g_z_s,

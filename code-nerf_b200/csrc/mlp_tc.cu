@@ -25,7 +25,8 @@ constexpr int RING = 3;
 constexpr int NTHREADS = 320;
 constexpr int FWD_CHUNKS = 17;            // 1 (layer_xyz1, K=64) + 4 x 4
 constexpr int BWD_CHUNKS = 16;            // 4 x 4 transposed
-constexpr int SMEM_BYTES = 2 * TILE_BYTES + RING * CHUNK + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int CONST_BYTES = 4 * 256 * 2;    // bf16 [w_sigma | w_rgb(3)] staged in shared memory
+constexpr int SMEM_BYTES = 2 * TILE_BYTES + RING * CHUNK + CONST_BYTES + 256 /*barriers*/;
 
 // Packed weights (bf16 images + fp32 vectors), rebuilt from the fp32 parameters at every call (they change each step).
 struct Packed {
@@ -34,8 +35,10 @@ struct Packed {
   float* w_sigma;    // [256]  fc_out row 0, hidden half
   float* w_rgb;      // [3][256] fc_rgb, hidden half
   float* b_dir2;     // [256]
+  float* zeros;      // [256]
+  uint16_t* wsr_bf16; // [4][256] bf16: w_sigma, w_rgb r/g/b (staged into shared memory by the forward kernel)
 };
-constexpr size_t PACKED_BYTES = (size_t)(FWD_CHUNKS + BWD_CHUNKS) * CHUNK + (256 + 768 + 256) * sizeof(float);
+constexpr size_t PACKED_BYTES = (size_t)(FWD_CHUNKS + BWD_CHUNKS) * CHUNK + (256 + 768 + 256 + 256) * sizeof(float) + 2048;
 }  // namespace tcc
 using namespace tcc;
 
@@ -73,7 +76,12 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, int dx, int dd, Pack
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
       pk.w_sigma[i] = p.weight[CNRF_L_FC_OUT][i];
       pk.b_dir2[i] = p.bias[CNRF_L_DIR2][i];
-      for (int c = 0; c < 3; ++c) pk.w_rgb[c * 256 + i] = p.weight[CNRF_L_FC_RGB][c * 512 + i];
+      pk.zeros[i] = 0.f;
+      reinterpret_cast<__nv_bfloat16*>(pk.wsr_bf16)[i] = __float2bfloat16(p.weight[CNRF_L_FC_OUT][i]);
+      for (int c = 0; c < 3; ++c) {
+        pk.w_rgb[c * 256 + i] = p.weight[CNRF_L_FC_RGB][c * 512 + i];
+        reinterpret_cast<__nv_bfloat16*>(pk.wsr_bf16)[(1 + c) * 256 + i] = __float2bfloat16(p.weight[CNRF_L_FC_RGB][c * 512 + i]);
+      }
     }
   }
 }
@@ -128,7 +136,7 @@ struct FwdArgs {
   int64_t N, M; int S, pairing, dx;
   const float* pts; const float* x_xyz; int64_t ld_xyz;
   const float* freqs; int L; int inc;
-  const float *b2, *bo, *br, *bd;
+  const float *b2, *bof, *bos, *br, *bd;   // per-ray bias tables: [N,256], [N,256] (fc_out feat), [N] (sigma), [N,3], [N,256]
   Packed pk;
   float* raw;
   uint8_t* saved;      // nullptr: inference
@@ -169,11 +177,11 @@ __device__ __forceinline__ void build_input_row(const FwdArgs& a, int64_t m, boo
 }
 
 __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem[];   // 128-byte-swizzled images need 1024-byte alignment
   uint8_t* tiles = smem;                              // 2 x 64 KB
   uint8_t* ring = smem + 2 * TILE_BYTES;              // RING x 32 KB
-  Bars* bars = reinterpret_cast<Bars*>(ring + RING * CHUNK);
+  const __nv_bfloat162* wsr = reinterpret_cast<const __nv_bfloat162*>(ring + RING * CHUNK);   // [4][128] bf16x2
+  Bars* bars = reinterpret_cast<Bars*>(ring + RING * CHUNK + CONST_BYTES);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t num_tiles = (a.M + TILE - 1) / TILE;
   const int64_t num_pairs = (num_tiles + 1) / 2;
@@ -182,8 +190,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     for (int i = 0; i < RING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
     for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
     bars->abort_flag = 0;
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
     mbar_fence_init();
   }
+  for (int i = tid; i < CONST_BYTES / 4; i += NTHREADS)
+    reinterpret_cast<uint32_t*>(ring + RING * CHUNK)[i] = reinterpret_cast<const uint32_t*>(a.pk.wsr_bf16)[i];
   if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
@@ -265,17 +276,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
         tc_fence_after();
         if (elected) bulk_wait_read0();               // image store of the previous layer no longer reads this tile
         named_bar_sync(bar_id, 128);
-        const float* bias = e == 1 ? a.b2 + ray * 256 : e == 2 ? a.bo + ray * 257 + 1 : e == 3 ? a.bd + pair * 256
-                                                                                        : e == 4 ? a.pk.b_dir2 : nullptr;
+        const float4* bias = reinterpret_cast<const float4*>(e == 1 ? a.b2 + ray * 256 : e == 2 ? a.bof + ray * 256
+                                                             : e == 3 ? a.bd + pair * 256 : e == 4 ? a.pk.b_dir2 : a.pk.zeros);
         float rgb[3] = {0.f, 0.f, 0.f};
+        float4 bq[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) bq[j] = __ldg(bias + j);
 #pragma unroll 1
         for (int cb = 0; cb < 8; ++cb) {
           uint32_t v[32];
           tmem_ld32(tacc + cb * 32, v);
+          float4 bn[8];                               // next block's bias rows travel while this block is converted
+          const int nb = cb < 7 ? cb + 1 : 7;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bn[j] = __ldg(bias + nb * 8 + j);
           tmem_ld_wait();
           float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) + (bias ? __ldg(bias + cb * 32 + j) : 0.f);
+          for (int j = 0; j < 8; ++j) {
+            f[4 * j] = __uint_as_float(v[4 * j]) + bq[j].x;
+            f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + bq[j].y;
+            f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + bq[j].z;
+            f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + bq[j].w;
+          }
           uint32_t pk[16];
           if (e == 2) {
 #pragma unroll
@@ -286,19 +309,28 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
           }
           if (e == 1) {                               // sigma_raw = w_sigma . h2 + betao[ray][0]   (fc_out row 0)
 #pragma unroll
-            for (int j = 0; j < 32; ++j) sigma = fmaf(fmaxf(f[j], 0.f), __ldg(a.pk.w_sigma + cb * 32 + j), sigma);
+            for (int j = 0; j < 16; ++j) {
+              const float2 w = __bfloat1622float2(wsr[cb * 16 + j]);
+              sigma = fmaf(fmaxf(f[2 * j], 0.f), w.x, sigma);
+              sigma = fmaf(fmaxf(f[2 * j + 1], 0.f), w.y, sigma);
+            }
           }
           if (e == 4) {                               // rgb_raw = Wrv v2 + betar[ray]                (fc_rgb)
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const float x = fmaxf(f[j], 0.f);
+            for (int j = 0; j < 16; ++j) {
+              const float x0 = fmaxf(f[2 * j], 0.f), x1 = fmaxf(f[2 * j + 1], 0.f);
 #pragma unroll
-              for (int c = 0; c < 3; ++c) rgb[c] = fmaf(x, __ldg(a.pk.w_rgb + c * 256 + cb * 32 + j), rgb[c]);
+              for (int c = 0; c < 3; ++c) {
+                const float2 w = __bfloat1622float2(wsr[(1 + c) * 128 + cb * 16 + j]);
+                rgb[c] = fmaf(x0, w.x, fmaf(x1, w.y, rgb[c]));
+              }
             }
           }
           store_row_block(tile, r, cb, pk);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bq[j] = bn[j];
         }
-        if (e == 1 && valid) sigma += a.bo[ray * 257];
+        if (e == 1 && valid) sigma += a.bos[ray];
         if (e == 4 && valid) {
           float4 o = make_float4(rgb[0] + a.br[ray * 3], rgb[1] + a.br[ray * 3 + 1], rgb[2] + a.br[ray * 3 + 2], sigma);
           reinterpret_cast<float4*>(a.raw)[m] = o;   // [rgb_raw | sigma_raw]   models/model.py:194
@@ -329,6 +361,7 @@ struct TcChainArgs {   // mirrors the declaration in codenerf.cu
   const float* x_xyz; int64_t ld_xyz;
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;
   const float *b2, *bo, *br, *bd;
+  const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
 };
 
 static inline size_t up1k(size_t b) { return (b + 1023) & ~size_t(1023); }
@@ -347,7 +380,8 @@ static Packed carve_packed(uint8_t* base) {
   pk.fwd = base;
   pk.bwd = base + (size_t)FWD_CHUNKS * CHUNK;
   float* f = reinterpret_cast<float*>(base + (size_t)(FWD_CHUNKS + BWD_CHUNKS) * CHUNK);
-  pk.w_sigma = f; pk.w_rgb = f + 256; pk.b_dir2 = f + 1024;
+  pk.w_sigma = f; pk.w_rgb = f + 256; pk.b_dir2 = f + 1024; pk.zeros = f + 1280;
+  pk.wsr_bf16 = reinterpret_cast<uint16_t*>(f + 1536);
   return pk;
 }
 static int* tc_error_ptr() {
@@ -369,7 +403,7 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   FwdArgs f;
   f.N = a.N; f.M = a.M; f.S = a.S; f.pairing = a.pairing; f.dx = a.dx;
   f.pts = a.pts; f.x_xyz = a.x_xyz; f.ld_xyz = a.ld_xyz; f.freqs = a.freqs_xyz; f.L = a.L_xyz; f.inc = a.inc_xyz;
-  f.b2 = a.b2; f.bo = a.bo; f.br = a.br; f.bd = a.bd; f.pk = pk; f.raw = raw;
+  f.b2 = a.b2; f.bof = a.bof; f.bos = a.bos; f.br = a.br; f.bd = a.bd; f.pk = pk; f.raw = raw;
   f.saved = saved ? reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(saved))) : nullptr;
   f.err = tc_error_ptr();
   static bool attr_set = false;

@@ -1,0 +1,34 @@
+"""Time the field forward (and backward when available) at C1 shapes; prints ms and TFLOP/s."""
+import os, sys, time
+import torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "code-nerf_b200")); sys.path.insert(0, ROOT)
+import view_synthesis.nerf as nerf, view_synthesis.models as models
+from codenerf_b200 import _lib
+dev = torch.device("cuda", 0)
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+S = int(sys.argv[2]) if len(sys.argv) > 2 else 160
+mode = sys.argv[3] if len(sys.argv) > 3 else "fwd"
+prec = sys.argv[4] if len(sys.argv) > 4 else "bf16"
+nerf.set_precision(prec)
+m = models.CodeNeRFModel(256, 1, 256, 256, 10, 4, True, True).to(dev)
+emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+pts, rd = torch.randn(N, S, 3, device=dev), torch.randn(N, 3, device=dev)
+zs, zt = torch.randn(N, 256, device=dev, requires_grad=(mode != "fwd")), torch.randn(N, 256, device=dev)
+FS = 2 * (63 * 256 + 256 * 256 + 256 * 257 + 256 * 256 + 256 * 256 + 256 * 3)
+def step():
+    if mode == "fwd":
+        with torch.no_grad():
+            return nerf.forward_pass(m, emb, rd, pts, (zs, zt))
+    raw = nerf.forward_pass(m, emb, rd, pts, (zs, zt))
+    raw.backward(torch.ones_like(raw))
+for _ in range(3): step()
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+reps = 10
+e0.record()
+for _ in range(reps): step()
+e1.record(); torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / reps
+fl = N * S * FS * (1 if mode == "fwd" else 3)
+print(f"{prec} {mode} N={N} S={S}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s  tc_err={_lib.load().cnrf_debug_tc_error()}")
