@@ -419,20 +419,425 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   return CNRF_OK;
 }
 
-size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
-  (void)N; (void)M; (void)backward;
-  return PACKED_BYTES + 2048;
-}
-
-int cnrf_tc_chain_bwd(const TcChainArgs&, const float*, const void*, size_t, const cnrf_codenerf_grads*, float*, float*,
-                      float*, float*, float*, void*, size_t, cudaStream_t) {
-  return CNRF_E_UNSUPPORTED;
-}
-
 // Synchronous diagnostic: 1 if any tensor-core kernel of this process hit its barrier-wait timeout.
 extern "C" int cnrf_debug_tc_error(void) {
   int v = 0;
   cudaDeviceSynchronize();
   cudaMemcpyFromSymbol(&v, g_tc_error, sizeof(int));
   return v;
+}
+
+// =====================================================================================================================
+// Backward-data chain.  Per tile pair: stage 0 on CUDA cores (d v2 = g_rgb Wrv, masked), then four tensor-core stages
+//   d v1 = (d v2p Wd2) * [v1>0],  d feat = d v1p Wdf,  d h2 = (d feat Woh' + d sigma w_sigma) * [h2>0],  d h1 = (d h2p W2h) * [h1>0]
+// with W^T streamed as B operands.  Every masked gradient tile is stored as a bf16 image (same layout as the forward's
+// activation images) for the weight-gradient kernel.
+// =====================================================================================================================
+constexpr size_t DY_PER_TILE = 5 * (size_t)TILE_BYTES;      // d v2p, d v1p, d feat, d h2p, d h1p
+
+struct BwdArgs {
+  int64_t M;
+  const float* g_raw;          // [M,4]
+  const uint8_t* saved;        // forward images
+  uint8_t* dy;                 // gradient images out
+  Packed pk;
+  int* err;
+};
+
+// mask source image index (within the forward's saved tile: 0 h1, 1 h2, 2 feat, 3 v1, 4 v2) for epilogue stage s
+__device__ __forceinline__ const uint8_t* saved_image(const uint8_t* sv, int img) { return sv + SAVED_GAMMA + (size_t)img * TILE_BYTES; }
+
+__global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* tiles = smem;
+  uint8_t* ring = smem + 2 * TILE_BYTES;
+  const __nv_bfloat162* wsr = reinterpret_cast<const __nv_bfloat162*>(ring + RING * CHUNK);
+  Bars* bars = reinterpret_cast<Bars*>(ring + RING * CHUNK + CONST_BYTES);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t num_tiles = (a.M + TILE - 1) / TILE;
+  const int64_t num_pairs = (num_tiles + 1) / 2;
+
+  if (tid == 0) {
+    for (int i = 0; i < RING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
+    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
+    bars->abort_flag = 0;
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
+    mbar_fence_init();
+  }
+  for (int i = tid; i < CONST_BYTES / 4; i += NTHREADS)
+    reinterpret_cast<uint32_t*>(ring + RING * CHUNK)[i] = reinterpret_cast<const uint32_t*>(a.pk.wsr_bf16)[i];
+  if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+        for (int ch = 0; ch < BWD_CHUNKS; ++ch, ++g) {
+          const int slot = g % RING;
+          if (!wait_bar(&bars->w_empty[slot], ((g / RING) & 1) ^ 1, bars, a.err)) goto done;
+          mbar_arrive_expect_tx(&bars->w_full[slot], CHUNK);
+          bulk_g2s(ring + slot * CHUNK, a.pk.bwd + (size_t)ch * CHUNK, CHUNK, &bars->w_full[slot]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(128, 256, 0, 0);
+      uint32_t g = 0, na = 0;
+      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+        for (int stage = 0; stage < 4; ++stage, ++na) {
+          for (int c = 0; c < 4; ++c, ++g) {
+            const int slot = g % RING;
+            if (!wait_bar(&bars->w_full[slot], (g / RING) & 1, bars, a.err)) goto done;
+            for (int t = 0; t < 2; ++t) {
+              if (c == 0 && !wait_bar(&bars->a_ready[t], na & 1, bars, a.err)) goto done;
+              tc_fence_after();
+              const uint32_t a_base = smem_u32(tiles + t * TILE_BYTES + c * SLAB);
+              const uint32_t b_base = smem_u32(ring + slot * CHUNK);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                umma_bf16(tmem + t * 256, smem_desc(a_base + k * 32, 16, 1024, SWIZZLE_128B),
+                          smem_desc(b_base + k * 32, 16, 1024, SWIZZLE_128B), idesc, (c | k) != 0);
+              }
+              if (c == 3) umma_commit(&bars->acc_full[t]);
+            }
+            umma_commit(&bars->w_empty[slot]);
+          }
+        }
+      }
+    }
+  } else {
+    const int t = (warp - 2) >> 2;
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const bool elected = ((warp - 2) & 3) == 0 && lane == 0;
+    const int bar_id = 1 + t;
+    uint8_t* tile = tiles + t * TILE_BYTES;
+    const uint32_t tacc = tmem + t * 256 + ((uint32_t)(q * 32) << 16);
+    uint32_t na = 0;
+    for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+      const int64_t tile_idx = pr * 2 + t;
+      const bool tile_ok = tile_idx < num_tiles;
+      const int64_t m = tile_idx * TILE + r;
+      const bool valid = m < a.M;
+      const uint8_t* sv = a.saved + (size_t)(tile_ok ? tile_idx : 0) * SAVED_PER_TILE;
+      uint8_t* dy = a.dy + (size_t)(tile_ok ? tile_idx : 0) * DY_PER_TILE;
+      const float4 g = valid ? reinterpret_cast<const float4*>(a.g_raw)[m] : make_float4(0.f, 0.f, 0.f, 0.f);
+      // ---- stage 0: d v2p = (g_rgb Wrv) * [v2 > 0] on CUDA cores ----
+      if (elected) bulk_wait_read0();
+      named_bar_sync(bar_id, 128);
+      {
+        const uint8_t* mrow = saved_image(sv, 4) + r * 128;
+#pragma unroll 1
+        for (int cb = 0; cb < 8; ++cb) {
+          uint4 mk[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            mk[j] = __ldg(reinterpret_cast<const uint4*>(mrow + (cb >> 1) * SLAB + (((((cb & 1) * 4) + j) ^ (r & 7)) << 4)));
+          const uint32_t* mw = reinterpret_cast<const uint32_t*>(mk);
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int col2 = cb * 16 + j;
+            const float2 w0 = __bfloat1622float2(wsr[128 + col2]), w1 = __bfloat1622float2(wsr[256 + col2]),
+                         w2 = __bfloat1622float2(wsr[384 + col2]);
+            float lo = g.x * w0.x + g.y * w1.x + g.z * w2.x, hi = g.x * w0.y + g.y * w1.y + g.z * w2.y;
+            if ((mw[j] & 0xFFFFu) == 0u) lo = 0.f;            // relu output stored as bf16: > 0  <=>  bits != 0
+            if ((mw[j] >> 16) == 0u) hi = 0.f;
+            pk[j] = pack_bf16(lo, hi);
+          }
+          store_row_block(tile, r, cb, pk);
+        }
+      }
+      fence_proxy_async();
+      named_bar_sync(bar_id, 128);
+      if (elected) {
+        if (tile_ok) { bulk_s2g(dy, tile, TILE_BYTES); bulk_commit(); }
+        mbar_arrive(&bars->a_ready[t]);
+      }
+      // ---- four tensor-core stages ----
+      for (int s = 0; s < 4; ++s, ++na) {
+        if (!wait_bar(&bars->acc_full[t], na & 1, bars, a.err)) goto done;
+        tc_fence_after();
+        if (elected) bulk_wait_read0();
+        named_bar_sync(bar_id, 128);
+        const int mask_img = s == 0 ? 3 : s == 2 ? 1 : s == 3 ? 0 : -1;        // v1, -, h2, h1
+        const uint8_t* mrow = saved_image(sv, mask_img < 0 ? 0 : mask_img) + r * 128;
+#pragma unroll 1
+        for (int cb = 0; cb < 8; ++cb) {
+          uint32_t v[32];
+          tmem_ld32(tacc + cb * 32, v);
+          uint4 mk[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            mk[j] = __ldg(reinterpret_cast<const uint4*>(mrow + (cb >> 1) * SLAB + (((((cb & 1) * 4) + j) ^ (r & 7)) << 4)));
+          const uint32_t* mw = reinterpret_cast<const uint32_t*>(mk);
+          tmem_ld_wait();
+          uint32_t pk[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float lo = __uint_as_float(v[2 * j]), hi = __uint_as_float(v[2 * j + 1]);
+            if (s == 2) {                                     // + d sigma * w_sigma  (fc_out row 0)
+              const float2 w = __bfloat1622float2(wsr[cb * 16 + j]);
+              lo = fmaf(g.w, w.x, lo); hi = fmaf(g.w, w.y, hi);
+            }
+            if (mask_img >= 0) {
+              if ((mw[j] & 0xFFFFu) == 0u) lo = 0.f;
+              if ((mw[j] >> 16) == 0u) hi = 0.f;
+            }
+            pk[j] = pack_bf16(lo, hi);
+          }
+          store_row_block(tile, r, cb, pk);
+        }
+        fence_proxy_async();
+        tc_fence_before();
+        named_bar_sync(bar_id, 128);
+        if (elected) {
+          if (tile_ok) { bulk_s2g(dy + (size_t)(s + 1) * TILE_BYTES, tile, TILE_BYTES); bulk_commit(); }
+          if (s < 3) mbar_arrive(&bars->a_ready[t]);
+        }
+      }
+    }
+    if (elected) bulk_wait0();
+  }
+done:
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// =====================================================================================================================
+// Weight gradients: dW[n][k] = sum_m dY[m][n] X[m][k] on tensor cores, operands read as MN-major straight from the saved
+// bf16 images (the sample index is the contraction dimension, so the very same image is its own transpose).
+// grid = (ctas per job, 5 jobs); a CTA accumulates its share of the tiles in TMEM (2 x [128 x N] fp32) and adds it to
+// the fp32 gradient with red.global.add.
+// =====================================================================================================================
+constexpr int DW_THREADS = 192;
+constexpr int DW_STAGE = 8 * 8192;          // 64 rows x (256 + 256) bf16
+constexpr int DW_RING = 3;
+constexpr int DW_SMEM = DW_RING * DW_STAGE + 256;
+
+struct DwJob { int dy_img; int x_img; /* -1: gamma slab */ int n_cols; float* out; int ld; int k_valid; float* bias_out; };
+struct DwArgs {
+  int64_t M;
+  const uint8_t* saved;
+  const uint8_t* dy;
+  DwJob job[5];
+  int* err;
+};
+
+struct DwBars { uint64_t full[DW_RING], empty[DW_RING], acc_full; uint32_t tmem_slot; int abort_flag; };
+
+__device__ __forceinline__ bool dw_wait(uint64_t* bar, uint32_t parity, DwBars* b, int* err) {
+  if (mbar_try_wait(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (true) {
+    if (mbar_try_wait(bar, parity)) return true;
+    if (*(volatile int*)&b->abort_flag) return false;
+    if (clock64() - t0 > 2000000000LL) { b->abort_flag = 1; atomicExch(err, 1); return false; }
+  }
+}
+
+__global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  DwBars* bars = reinterpret_cast<DwBars*>(smem + DW_RING * DW_STAGE);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const DwJob job = a.job[blockIdx.y];
+  const int nslabB = job.x_img < 0 ? 1 : 4;
+  const int64_t num_tiles = (a.M + TILE - 1) / TILE;
+  const int64_t num_halves = num_tiles * 2;
+  if (tid == 0) {
+    for (int i = 0; i < DW_RING; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
+    mbar_init(&bars->acc_full, 1);
+    bars->abort_flag = 0;
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
+    mbar_fence_init();
+  }
+  if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_slot;
+  const bool has_work = (int64_t)blockIdx.x < num_halves;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int64_t h = blockIdx.x; h < num_halves; h += gridDim.x, ++g) {
+        const int slot = g % DW_RING;
+        if (!dw_wait(&bars->empty[slot], ((g / DW_RING) & 1) ^ 1, bars, a.err)) goto done;
+        const int64_t tile = h >> 1;
+        const int half = (int)(h & 1);
+        const uint8_t* src_a = a.dy + (size_t)tile * DY_PER_TILE + (size_t)job.dy_img * TILE_BYTES + half * 8192;
+        const uint8_t* src_b = a.saved + (size_t)tile * SAVED_PER_TILE +
+                               (job.x_img < 0 ? 0 : SAVED_GAMMA + (size_t)job.x_img * TILE_BYTES) + half * 8192;
+        uint8_t* dst = smem + slot * DW_STAGE;
+        mbar_arrive_expect_tx(&bars->full[slot], (4 + nslabB) * 8192);
+        for (int s = 0; s < 4; ++s) bulk_g2s(dst + s * 8192, src_a + (size_t)s * SLAB, 8192, &bars->full[slot]);
+        for (int s = 0; s < nslabB; ++s) bulk_g2s(dst + (4 + s) * 8192, src_b + (size_t)s * SLAB, 8192, &bars->full[slot]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && has_work) {
+      const uint32_t idesc = idesc_bf16(128, job.n_cols, 1, 1);
+      uint32_t g = 0;
+      for (int64_t h = blockIdx.x; h < num_halves; h += gridDim.x, ++g) {
+        const int slot = g % DW_RING;
+        if (!dw_wait(&bars->full[slot], (g / DW_RING) & 1, bars, a.err)) goto done;
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + slot * DW_STAGE), sb = sa + 4 * 8192;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const uint64_t bd = smem_desc(sb + k * 2048, 8192, 1024, SWIZZLE_128B);
+          umma_bf16(tmem, smem_desc(sa + k * 2048, 8192, 1024, SWIZZLE_128B), bd, idesc, (g | k) != 0);
+          umma_bf16(tmem + 256, smem_desc(sa + 2 * 8192 + k * 2048, 8192, 1024, SWIZZLE_128B), bd, idesc, (g | k) != 0);
+        }
+        umma_commit(&bars->empty[slot]);
+      }
+      umma_commit(&bars->acc_full);
+    }
+  } else if (has_work) {
+    const int q = warp & 3;
+    if (dw_wait(&bars->acc_full, 0, bars, a.err)) {
+      tc_fence_after();
+      for (int mh = 0; mh < 2; ++mh) {
+        const int n = mh * 128 + q * 32 + lane;
+        for (int c0 = 0; c0 < job.n_cols; c0 += 32) {
+          uint32_t v[32];
+          tmem_ld32(tmem + mh * 256 + ((uint32_t)(q * 32) << 16) + c0, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int k = c0 + j;
+            if (k < job.k_valid) atomicAdd(job.out + (size_t)n * job.ld + k, __uint_as_float(v[j]));
+            else if (job.bias_out && k == 63) atomicAdd(job.bias_out + n, __uint_as_float(v[j]));
+          }
+        }
+      }
+    }
+  }
+done:
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+
+// ---- SIMT reductions over the bf16 images --------------------------------------------------------------------------------
+// element pair (row m, columns 2w, 2w+1) of an image set: tile stride `per_tile`, image offset `off`
+__device__ __forceinline__ float2 img_pair(const uint8_t* base, size_t per_tile, size_t off, int64_t m, int w) {
+  const int r = (int)(m & 127);
+  const uint8_t* p = base + (size_t)(m >> 7) * per_tile + off + (w >> 5) * SLAB + r * 128 +
+                     ((((w >> 2) & 7) ^ (r & 7)) << 4) + ((w & 3) << 2);
+  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+}
+// out[g*ld + col] = sum_{q<Q} img[g*g_stride + q*q_stride][col]        (per-ray sums of a gradient image)
+__global__ void img_group_sum_kernel(const uint8_t* base, size_t per_tile, size_t off, int64_t G, int64_t g_stride,
+                                     int64_t Q, int64_t q_stride, float* out, int64_t ld) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= G * 128) return;
+  const int64_t g = i >> 7;
+  const int w = (int)(i & 127);
+  float2 s = make_float2(0.f, 0.f);
+  for (int64_t q = 0; q < Q; ++q) {
+    float2 v = img_pair(base, per_tile, off, g * g_stride + q * q_stride, w);
+    s.x += v.x; s.y += v.y;
+  }
+  out[g * ld + 2 * w] = s.x; out[g * ld + 2 * w + 1] = s.y;
+}
+// out[c*ld + col] += sum_m wgt[m*wstride + c] * img[m][col], c < NW          (column sums / tiny-N weight gradients)
+template <int NW>
+__global__ void img_weighted_colsum_kernel(const uint8_t* base, size_t per_tile, size_t off, int64_t M,
+                                           const float* wgt, int wstride, float* out, int64_t ld) {
+  const int w = threadIdx.x;           // 128 threads: column pair
+  const int64_t m0 = (int64_t)blockIdx.x * 512, m1 = m0 + 512 < M ? m0 + 512 : M;
+  float2 s[NW];
+#pragma unroll
+  for (int c = 0; c < NW; ++c) s[c] = make_float2(0.f, 0.f);
+  for (int64_t m = m0; m < m1; ++m) {
+    float2 v = img_pair(base, per_tile, off, m, w);
+#pragma unroll
+    for (int c = 0; c < NW; ++c) {
+      const float g = wgt ? wgt[m * wstride + c] : 1.0f;
+      s[c].x = fmaf(g, v.x, s[c].x); s[c].y = fmaf(g, v.y, s[c].y);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < NW; ++c) { atomicAdd(out + c * ld + 2 * w, s[c].x); atomicAdd(out + c * ld + 2 * w + 1, s[c].y); }
+}
+
+size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
+  (void)N;
+  size_t b = PACKED_BYTES + 4096;
+  if (backward) b += (size_t)((M + TILE - 1) / TILE) * DY_PER_TILE;
+  return b;
+}
+
+int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* saved, size_t saved_bytes,
+                      const cnrf_codenerf_grads* g, float* d_b2, float* d_bo, float* d_br, float* d_bd, float* g_x_xyz,
+                      void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (g_x_xyz) return CNRF_E_UNSUPPORTED;     // input gradients (pose optimisation) run in CNRF_PRECISION_FP32 for now
+  const int64_t tiles = (a.M + TILE - 1) / TILE;
+  uint8_t* w = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(ws)));
+  if (w + PACKED_BYTES + 1024 + (size_t)tiles * DY_PER_TILE > reinterpret_cast<uint8_t*>(ws) + ws_bytes) return CNRF_E_WORKSPACE;
+  if (saved_bytes < cnrf_tc_saved_bytes(a.M) + 1024) return CNRF_E_WORKSPACE;
+  const uint8_t* sv = reinterpret_cast<const uint8_t*>(up1k(reinterpret_cast<size_t>(saved)));
+  Packed pk = carve_packed(w);
+  uint8_t* dy = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
+  pack_weights_kernel<<<FWD_CHUNKS + BWD_CHUNKS, 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
+  CNRF_LAUNCH_CHECK();
+  int rc;
+  if ((rc = cnrf_fill_zero(g->bias[CNRF_L_XYZ1], 256 * sizeof(float), st))) return rc;
+  if ((rc = cnrf_fill_zero(g->bias[CNRF_L_DIR2], 256 * sizeof(float), st))) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return (int)e;
+    e = cudaFuncSetAttribute(mlp_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  BwdArgs b;
+  b.M = a.M; b.g_raw = g_raw; b.saved = sv; b.dy = dy; b.pk = pk; b.err = tc_error_ptr();
+  const int64_t pairs = (tiles + 1) / 2;
+  mlp_bwd_tc_kernel<<<(int)(pairs < sm_count() ? pairs : sm_count()), NTHREADS, SMEM_BYTES, st>>>(b);
+  CNRF_LAUNCH_CHECK();
+
+  DwArgs d;
+  d.M = a.M; d.saved = sv; d.dy = dy; d.err = tc_error_ptr();
+  d.job[0] = {0, 3, 256, g->weight[CNRF_L_DIR2], 256, 256, nullptr};                       // d v2p^T v1
+  d.job[1] = {1, 2, 256, g->weight[CNRF_L_DIR1], 256 + a.dd, 256, nullptr};                // d v1p^T feat
+  d.job[2] = {2, 1, 256, g->weight[CNRF_L_FC_OUT] + 512, 512, 256, nullptr};               // d feat^T h2   (rows 1..256)
+  d.job[3] = {3, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nullptr};                       // d h2p^T h1
+  d.job[4] = {4, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1]};        // d h1p^T [gamma | 1]
+  const int64_t halves = tiles * 2;
+  const int per_job = (int)(halves < (sm_count() / 5) ? halves : (sm_count() / 5));
+  mlp_dw_tc_kernel<<<dim3(per_job, 5), DW_THREADS, DW_SMEM, st>>>(d);
+  CNRF_LAUNCH_CHECK();
+
+  const unsigned cs_grid = (unsigned)((a.M + 511) / 512);
+  img_weighted_colsum_kernel<1><<<cs_grid, 128, 0, st>>>(dy, DY_PER_TILE, 0, a.M, nullptr, 0, g->bias[CNRF_L_DIR2], 0);
+  CNRF_LAUNCH_CHECK();
+  img_weighted_colsum_kernel<1><<<cs_grid, 128, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 1 * (size_t)TILE_BYTES, a.M,
+                                                         g_raw + 3, 4, g->weight[CNRF_L_FC_OUT], 0);
+  CNRF_LAUNCH_CHECK();
+  img_weighted_colsum_kernel<3><<<cs_grid, 128, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 4 * (size_t)TILE_BYTES, a.M,
+                                                         g_raw, 4, g->weight[CNRF_L_FC_RGB], 512);
+  CNRF_LAUNCH_CHECK();
+  const unsigned gs_grid = (unsigned)((a.N * 128 + 255) / 256);
+  img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 3 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_b2, 256);
+  CNRF_LAUNCH_CHECK();
+  img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 2 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_bo + 1, 257);
+  CNRF_LAUNCH_CHECK();
+  if (a.pairing == CNRF_PAIRING_REFERENCE)
+    img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 1 * (size_t)TILE_BYTES, a.N, 1, a.S, a.N, d_bd, 256);
+  else
+    img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 1 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_bd, 256);
+  CNRF_LAUNCH_CHECK();
+  if ((rc = cnrf_strided_rowsum(g_raw, 4, a.N, a.S, a.S, 1, 3, d_br, 3, st))) return rc;
+  if ((rc = cnrf_strided_rowsum(g_raw + 3, 4, a.N, a.S, a.S, 1, 1, d_bo, 257, st))) return rc;
+  return CNRF_OK;
 }
