@@ -159,7 +159,8 @@ class _SamplePdf(torch.autograd.Function):
 
 
 def sample_pdf(ro, rd, weights, z_coarse, num_fine, u, debug=False):
-    return _SamplePdf.apply(ro, rd, weights, z_coarse, int(num_fine), u, bool(debug))
+    # the samples carry no gradient back to the weights or depths (point_sampler.py:115 detaches them)
+    return _SamplePdf.apply(ro, rd, weights.detach(), z_coarse.detach(), int(num_fine), u, bool(debug))
 
 
 def invert_cdf(cdf, bins, u):
