@@ -32,11 +32,13 @@ inline size_t al(size_t nfloat) { return (nfloat * sizeof(float) + 255) & ~size_
 struct Dims {
   int H, C, dx, dd, S, pairing;
   int64_t N, M;
+  bool tc;   // per-ray GEMMs on the tensor cores (gemm_tc.cu) instead of the fp32 SIMT toolkit
 };
 inline Dims dims_of(const cnrf_field_shape* s) {
   Dims d;
   d.H = s->hidden; d.C = s->code; d.dx = s->dim_xyz; d.dd = s->dim_dir; d.S = s->num_samples; d.pairing = s->pairing;
   d.N = s->num_rays; d.M = s->num_rays * (int64_t)s->num_samples;
+  d.tc = s->precision == CNRF_PRECISION_BF16;
   return d;
 }
 inline int check_shape(const cnrf_field_shape* s) {
@@ -70,24 +72,32 @@ inline void carve_tables(const Dims& d, Arena& a, Tables& t) {
 
 #define RUN(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
 
+int run_gemm(bool tc, const GemmArgs& g, cudaStream_t st) {
+  if (tc) {
+    int rc = cnrf_gemm_tc(g, st);
+    if (rc != CNRF_E_UNSUPPORTED) return rc;
+  }
+  return cnrf_sgemm(g, st);
+}
+
 // Y[rows,Nout] = act(X[rows,K] W[Nout,K]^T + bias[(m/div)%mod])
-int lin(const float* X, int64_t ldx, int64_t rows, int K, const float* W, int64_t ldw, int Nout, float* Y, int64_t ldy,
+int lin(bool tc, const float* X, int64_t ldx, int64_t rows, int K, const float* W, int64_t ldw, int Nout, float* Y, int64_t ldy,
         const float* bias, int64_t ld_bias, int64_t div, int64_t mod, int relu, cudaStream_t st) {
   GemmArgs g;
   g.A = X; g.a_rs = ldx; g.a_cs = 1; g.B = W; g.b_rs = 1; g.b_cs = ldw; g.C = Y; g.ldc = ldy;
   g.M = rows; g.N = Nout; g.K = K; g.bias = bias; g.ld_bias = ld_bias; g.bias_div = div; g.bias_mod = mod; g.relu = relu;
-  return cnrf_sgemm(g, st);
+  return run_gemm(tc, g, st);
 }
 // dX[rows,K] (+)= (dY[rows,Nout] W[Nout,K]) * (mask > 0)
-int dgrad(const float* dY, int64_t ldy, int64_t rows, int Nout, const float* W, int64_t ldw, int K, float* dX,
+int dgrad(bool tc, const float* dY, int64_t ldy, int64_t rows, int Nout, const float* W, int64_t ldw, int K, float* dX,
           int64_t ldx, const float* mask, int64_t ldm, int accumulate, cudaStream_t st) {
   GemmArgs g;
   g.A = dY; g.a_rs = ldy; g.a_cs = 1; g.B = W; g.b_rs = ldw; g.b_cs = 1; g.C = dX; g.ldc = ldx;
   g.M = rows; g.N = K; g.K = Nout; g.mask = mask; g.ld_mask = ldm; g.accumulate = accumulate;
-  return cnrf_sgemm(g, st);
+  return run_gemm(tc, g, st);
 }
 // dW[Nout,K] = dY[rows,Nout]^T X[rows,K]   (dW must be zero-filled: split-K partials are added atomically)
-int wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int64_t rows, int Nout, int K, float* dW,
+int wgrad(bool tc, const float* dY, int64_t ldy, const float* X, int64_t ldx, int64_t rows, int Nout, int K, float* dW,
           int64_t ldw, cudaStream_t st) {
   GemmArgs g;
   g.A = dY; g.a_rs = 1; g.a_cs = ldy; g.B = X; g.b_rs = ldx; g.b_cs = 1; g.C = dW; g.ldc = ldw;
@@ -96,7 +106,7 @@ int wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int64_t row
   int64_t want = (1184 + tiles - 1) / tiles, cap = (rows + 511) / 512;
   g.split_k = (int)std::max<int64_t>(1, std::min<int64_t>(want, cap));
   if (g.split_k == 1) g.accumulate = 1;   // still += into the zero-filled buffer
-  return cnrf_sgemm(g, st);
+  return run_gemm(tc, g, st);
 }
 
 __global__ void copy_col_kernel(const float* __restrict__ src, int64_t ld_src, float* __restrict__ dst, int64_t ld_dst,
@@ -120,18 +130,18 @@ int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir
                 bool split_bo, cudaStream_t st) {
   const int H = d.H, C = d.C;
   const int64_t INF = INT64_MAX;
-  RUN(lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 0, 1, INF, 1, st));   // model.py:174
-  RUN(lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 0, 1, INF, 1, st));   // :175
-  RUN(lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 0, 1, INF, 1, st));// :177
-  RUN(lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0, 1, INF, 0, st));
+  RUN(lin(d.tc, z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 0, 1, INF, 1, st));   // model.py:174
+  RUN(lin(d.tc, z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 0, 1, INF, 1, st));   // :175
+  RUN(lin(d.tc, z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 0, 1, INF, 1, st));// :177
+  RUN(lin(d.tc, as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0, 1, INF, 0, st));
   if (split_bo) {   // tensor-core chain: 16-byte aligned feature rows + a separate sigma column
-    RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, t.bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0, 1, INF, 0, st));
-    RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+    RUN(lin(d.tc, as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, t.bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0, 1, INF, 0, st));
+    RUN(lin(d.tc, as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
   } else {
-    RUN(lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+    RUN(lin(d.tc, as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
   }
-  RUN(lin(at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0, 1, INF, 0, st));
-  RUN(lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0, 1, INF, 0, st));
+  RUN(lin(d.tc, at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0, 1, INF, 0, st));
+  RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0, 1, INF, 0, st));
   return CNRF_OK;
 }
 
@@ -143,29 +153,29 @@ int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codener
   const int H = d.H, C = d.C;
   // texture branch: betar = Wrt at + br
   RUN(cnrf_colsum(dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB], st));
-  RUN(wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C, st));
-  RUN(dgrad(dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp, C, at, C, 0, st));
-  RUN(wgrad(tmp, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C, st));
+  RUN(wgrad(d.tc, dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C, st));
+  RUN(dgrad(d.tc, dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp, C, at, C, 0, st));
+  RUN(wgrad(d.tc, tmp, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C, st));
   RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_TEXTURE1], st));
-  RUN(dgrad(tmp, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, 0, st));
+  RUN(dgrad(d.tc, tmp, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, 0, st));
   // shape branch 2: betao = Woc as2 + bo
   RUN(cnrf_colsum(dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT], st));
-  RUN(wgrad(dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C, st));
-  RUN(dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp, C, as2, C, 0, st));
-  RUN(wgrad(tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C, st));
+  RUN(wgrad(d.tc, dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C, st));
+  RUN(dgrad(d.tc, dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp, C, as2, C, 0, st));
+  RUN(wgrad(d.tc, tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C, st));
   RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_SHAPE2], st));
-  RUN(dgrad(tmp, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, 0, st));
+  RUN(dgrad(d.tc, tmp, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, 0, st));
   // shape branch 1: beta2 = W2c as1 + b2
   RUN(cnrf_colsum(dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2], st));
-  RUN(wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C, st));
-  RUN(dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp, C, as1, C, 0, st));
-  RUN(wgrad(tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C, st));
+  RUN(wgrad(d.tc, dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C, st));
+  RUN(dgrad(d.tc, dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp, C, as1, C, 0, st));
+  RUN(wgrad(d.tc, tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C, st));
   RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_SHAPE1], st));
-  RUN(dgrad(tmp, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1, st));
+  RUN(dgrad(d.tc, tmp, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1, st));
   // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
   RUN(cnrf_colsum(dt.bd, H, d.N, H, g->bias[CNRF_L_DIR1], st));
-  RUN(wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd, st));
-  if (g_x_dir) RUN(dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0, st));
+  RUN(wgrad(d.tc, dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd, st));
+  if (g_x_dir) RUN(dgrad(d.tc, dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0, st));
   return CNRF_OK;
 }
 
@@ -176,12 +186,12 @@ int chain_fwd_f32(const Dims& d, const cnrf_codenerf_params* p, const float* x_x
   const int64_t INF = INT64_MAX;
   int64_t pdiv, pmod;
   pair_index(d, pdiv, pmod);
-  RUN(lin(x_xyz, ld_xyz, d.M, d.dx, p->weight[CNRF_L_XYZ1], d.dx, H, s.h1, H, p->bias[CNRF_L_XYZ1], 0, 1, INF, 1, st)); // model.py:179
-  RUN(lin(s.h1, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, s.h2, H, t.b2, H, d.S, INF, 1, st));                        // :180-181
-  RUN(lin(s.h2, H, d.M, H, p->weight[CNRF_L_FC_OUT], H + C, C + 1, s.o, C + 1, t.bo, C + 1, d.S, INF, 0, st));           // :182-184
-  RUN(lin(s.o + 1, C + 1, d.M, C, p->weight[CNRF_L_DIR1], C + d.dd, H, s.v1, H, t.bd, H, pdiv, pmod, 1, st));            // :186-189
-  RUN(lin(s.v1, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, s.v2, H, p->bias[CNRF_L_DIR2], 0, 1, INF, 1, st));              // :190
-  RUN(lin(s.v2, H, d.M, H, p->weight[CNRF_L_FC_RGB], H + C, 3, raw, 4, t.br, 3, d.S, INF, 0, st));                       // :191-192
+  RUN(lin(false, x_xyz, ld_xyz, d.M, d.dx, p->weight[CNRF_L_XYZ1], d.dx, H, s.h1, H, p->bias[CNRF_L_XYZ1], 0, 1, INF, 1, st)); // model.py:179
+  RUN(lin(false, s.h1, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, s.h2, H, t.b2, H, d.S, INF, 1, st));                        // :180-181
+  RUN(lin(false, s.h2, H, d.M, H, p->weight[CNRF_L_FC_OUT], H + C, C + 1, s.o, C + 1, t.bo, C + 1, d.S, INF, 0, st));           // :182-184
+  RUN(lin(false, s.o + 1, C + 1, d.M, C, p->weight[CNRF_L_DIR1], C + d.dd, H, s.v1, H, t.bd, H, pdiv, pmod, 1, st));            // :186-189
+  RUN(lin(false, s.v1, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, s.v2, H, p->bias[CNRF_L_DIR2], 0, 1, INF, 1, st));              // :190
+  RUN(lin(false, s.v2, H, d.M, H, p->weight[CNRF_L_FC_RGB], H + C, 3, raw, 4, t.br, 3, d.S, INF, 0, st));                       // :191-192
   RUN(copy_col(s.o, C + 1, raw + 3, 4, d.M, st));                                                                       // :194  [rgb | sigma]
   return CNRF_OK;
 }
@@ -193,31 +203,31 @@ int chain_bwd_f32(const Dims& d, const cnrf_codenerf_params* p, const cnrf_coden
                   float* g_x_xyz, cudaStream_t st) {
   const int H = d.H, C = d.C;
   // fc_rgb
-  RUN(wgrad(g_raw, 4, s.v2, H, d.M, 3, H, g->weight[CNRF_L_FC_RGB], H + C, st));
+  RUN(wgrad(false, g_raw, 4, s.v2, H, d.M, 3, H, g->weight[CNRF_L_FC_RGB], H + C, st));
   RUN(cnrf_strided_rowsum(g_raw, 4, d.N, d.S, d.S, 1, 3, dt.br, 3, st));
-  RUN(dgrad(g_raw, 4, d.M, 3, p->weight[CNRF_L_FC_RGB], H + C, H, ga, H, s.v2, H, 0, st));
+  RUN(dgrad(false, g_raw, 4, d.M, 3, p->weight[CNRF_L_FC_RGB], H + C, H, ga, H, s.v2, H, 0, st));
   // layer_dir2
-  RUN(wgrad(ga, H, s.v1, H, d.M, H, H, g->weight[CNRF_L_DIR2], H, st));
+  RUN(wgrad(false, ga, H, s.v1, H, d.M, H, H, g->weight[CNRF_L_DIR2], H, st));
   RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_DIR2], st));
-  RUN(dgrad(ga, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, gb, H, s.v1, H, 0, st));
+  RUN(dgrad(false, ga, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, gb, H, s.v1, H, 0, st));
   // layer_dir1 (feature half)
-  RUN(wgrad(gb, H, s.o + 1, C + 1, d.M, H, C, g->weight[CNRF_L_DIR1], C + d.dd, st));
+  RUN(wgrad(false, gb, H, s.o + 1, C + 1, d.M, H, C, g->weight[CNRF_L_DIR1], C + d.dd, st));
   if (d.pairing == CNRF_PAIRING_REFERENCE) RUN(cnrf_strided_rowsum(gb, H, d.N, 1, d.S, d.N, H, dt.bd, H, st));
   else RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.bd, H, st));
-  RUN(dgrad(gb, H, d.M, H, p->weight[CNRF_L_DIR1], C + d.dd, C, ga + 1, C + 1, nullptr, 0, 0, st));
+  RUN(dgrad(false, gb, H, d.M, H, p->weight[CNRF_L_DIR1], C + d.dd, C, ga + 1, C + 1, nullptr, 0, 0, st));
   RUN(copy_col(g_raw + 3, 4, ga, C + 1, d.M, st));                       // d sigma_raw -> column 0 of d o
   // fc_out
-  RUN(wgrad(ga, C + 1, s.h2, H, d.M, C + 1, H, g->weight[CNRF_L_FC_OUT], H + C, st));
+  RUN(wgrad(false, ga, C + 1, s.h2, H, d.M, C + 1, H, g->weight[CNRF_L_FC_OUT], H + C, st));
   RUN(cnrf_strided_rowsum(ga, C + 1, d.N, d.S, d.S, 1, C + 1, dt.bo, C + 1, st));
-  RUN(dgrad(ga, C + 1, d.M, C + 1, p->weight[CNRF_L_FC_OUT], H + C, H, gb, H, s.h2, H, 0, st));
+  RUN(dgrad(false, ga, C + 1, d.M, C + 1, p->weight[CNRF_L_FC_OUT], H + C, H, gb, H, s.h2, H, 0, st));
   // layer_xyz2
-  RUN(wgrad(gb, H, s.h1, H, d.M, H, H, g->weight[CNRF_L_XYZ2], H + C, st));
+  RUN(wgrad(false, gb, H, s.h1, H, d.M, H, H, g->weight[CNRF_L_XYZ2], H + C, st));
   RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.b2, H, st));
-  RUN(dgrad(gb, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, ga, H, s.h1, H, 0, st));
+  RUN(dgrad(false, gb, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, ga, H, s.h1, H, 0, st));
   // layer_xyz1
-  RUN(wgrad(ga, H, x_xyz, ld_xyz, d.M, H, d.dx, g->weight[CNRF_L_XYZ1], d.dx, st));
+  RUN(wgrad(false, ga, H, x_xyz, ld_xyz, d.M, H, d.dx, g->weight[CNRF_L_XYZ1], d.dx, st));
   RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_XYZ1], st));
-  if (g_x_xyz) RUN(dgrad(ga, H, d.M, H, p->weight[CNRF_L_XYZ1], d.dx, d.dx, g_x_xyz, d.dx, nullptr, 0, 0, st));
+  if (g_x_xyz) RUN(dgrad(false, ga, H, d.M, H, p->weight[CNRF_L_XYZ1], d.dx, d.dx, g_x_xyz, d.dx, nullptr, 0, 0, st));
   return CNRF_OK;
 }
 

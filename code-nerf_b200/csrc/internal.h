@@ -18,6 +18,9 @@ struct GemmArgs {
   int split_k = 1;      // > 1: partial sums are atomically added into C, which the caller zero-fills
 };
 int cnrf_sgemm(const GemmArgs& a, cudaStream_t st);
+// gemm_tc.cu: the same contract on the tensor cores (bf16 operands, fp32 accumulate); CNRF_E_UNSUPPORTED when neither
+// stride of an operand is 1 or K > 320 without split-K permission -- the caller then uses cnrf_sgemm.
+int cnrf_gemm_tc(const GemmArgs& a, cudaStream_t st);
 // out[g*ld_out + n] = sum_{q<Q} X[(g*g_stride + q*q_stride)*ld_x + n],  g < G, n < N
 int cnrf_strided_rowsum(const float* X, int64_t ld_x, int64_t G, int64_t g_stride, int64_t Q, int64_t q_stride, int N,
                         float* out, int64_t ld_out, cudaStream_t st);

@@ -46,7 +46,7 @@ using namespace tcc;
 // chunk image element (row r in [0,256), col c in [0,64)) of chunk `ch`.
 __global__ void pack_weights_kernel(cnrf_codenerf_params p, int dx, int dd, Packed pk) {
   const int ch = blockIdx.x;                  // 0 .. FWD_CHUNKS+BWD_CHUNKS-1
-  for (int i = threadIdx.x; i < 256 * 64; i += blockDim.x) {
+  for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < 256 * 64; i += gridDim.y * blockDim.x) {
     int r = i >> 6, c = i & 63;
     float v;
     uint8_t* base;
@@ -72,7 +72,7 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, int dx, int dd, Pack
     }
     *reinterpret_cast<__nv_bfloat16*>(base + slab_offset(r, c)) = __float2bfloat16(v);
   }
-  if (ch == 0) {
+  if (ch == 0 && blockIdx.y == 0) {
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
       pk.w_sigma[i] = p.weight[CNRF_L_FC_OUT][i];
       pk.b_dir2[i] = p.bias[CNRF_L_DIR2][i];
@@ -398,7 +398,7 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   if (w + PACKED_BYTES > reinterpret_cast<uint8_t*>(ws) + ws_bytes) return CNRF_E_WORKSPACE;
   if (saved && saved_bytes < cnrf_tc_saved_bytes(a.M) + 1024) return CNRF_E_WORKSPACE;
   Packed pk = carve_packed(w);
-  pack_weights_kernel<<<FWD_CHUNKS + BWD_CHUNKS, 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
+  pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
   CNRF_LAUNCH_CHECK();
   FwdArgs f;
   f.N = a.N; f.M = a.M; f.S = a.S; f.pairing = a.pairing; f.dx = a.dx;
@@ -726,6 +726,7 @@ done:
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
+constexpr int CSUM_ROWS = 256;   // rows per block of the column-sum kernels
 // ---- SIMT reductions over the bf16 images --------------------------------------------------------------------------------
 // element pair (row m, columns 2w, 2w+1) of an image set: tile stride `per_tile`, image offset `off`
 __device__ __forceinline__ float2 img_pair(const uint8_t* base, size_t per_tile, size_t off, int64_t m, int w) {
@@ -741,23 +742,49 @@ __global__ void img_group_sum_kernel(const uint8_t* base, size_t per_tile, size_
   if (i >= G * 128) return;
   const int64_t g = i >> 7;
   const int w = (int)(i & 127);
-  float2 s = make_float2(0.f, 0.f);
-  for (int64_t q = 0; q < Q; ++q) {
-    float2 v = img_pair(base, per_tile, off, g * g_stride + q * q_stride, w);
-    s.x += v.x; s.y += v.y;
+  float2 s[4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) s[u] = make_float2(0.f, 0.f);
+  const int64_t m0 = g * g_stride;
+  int64_t q = 0;
+  for (; q + 8 <= Q; q += 8) {          // 8 independent loads in flight per thread
+    float2 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = img_pair(base, per_tile, off, m0 + (q + u) * q_stride, w);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { s[u & 3].x += v[u].x; s[u & 3].y += v[u].y; }
   }
-  out[g * ld + 2 * w] = s.x; out[g * ld + 2 * w + 1] = s.y;
+  for (; q < Q; ++q) {
+    float2 v = img_pair(base, per_tile, off, m0 + q * q_stride, w);
+    s[0].x += v.x; s[0].y += v.y;
+  }
+  out[g * ld + 2 * w] = (s[0].x + s[1].x) + (s[2].x + s[3].x);
+  out[g * ld + 2 * w + 1] = (s[0].y + s[1].y) + (s[2].y + s[3].y);
 }
 // out[c*ld + col] += sum_m wgt[m*wstride + c] * img[m][col], c < NW          (column sums / tiny-N weight gradients)
 template <int NW>
 __global__ void img_weighted_colsum_kernel(const uint8_t* base, size_t per_tile, size_t off, int64_t M,
                                            const float* wgt, int wstride, float* out, int64_t ld) {
   const int w = threadIdx.x;           // 128 threads: column pair
-  const int64_t m0 = (int64_t)blockIdx.x * 512, m1 = m0 + 512 < M ? m0 + 512 : M;
+  const int64_t m0 = (int64_t)blockIdx.x * CSUM_ROWS, m1 = m0 + CSUM_ROWS < M ? m0 + CSUM_ROWS : M;
   float2 s[NW];
 #pragma unroll
   for (int c = 0; c < NW; ++c) s[c] = make_float2(0.f, 0.f);
-  for (int64_t m = m0; m < m1; ++m) {
+  int64_t m = m0;
+  for (; m + 8 <= m1; m += 8) {        // 8 independent image loads in flight per thread
+    float2 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) v[u] = img_pair(base, per_tile, off, m + u, w);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+#pragma unroll
+      for (int c = 0; c < NW; ++c) {
+        const float g = wgt ? __ldg(wgt + (m + u) * wstride + c) : 1.0f;
+        s[c].x = fmaf(g, v[u].x, s[c].x); s[c].y = fmaf(g, v[u].y, s[c].y);
+      }
+    }
+  }
+  for (; m < m1; ++m) {
     float2 v = img_pair(base, per_tile, off, m, w);
 #pragma unroll
     for (int c = 0; c < NW; ++c) {
@@ -787,7 +814,7 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   const uint8_t* sv = reinterpret_cast<const uint8_t*>(up1k(reinterpret_cast<size_t>(saved)));
   Packed pk = carve_packed(w);
   uint8_t* dy = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
-  pack_weights_kernel<<<FWD_CHUNKS + BWD_CHUNKS, 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
+  pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
   CNRF_LAUNCH_CHECK();
   int rc;
   if ((rc = cnrf_fill_zero(g->bias[CNRF_L_XYZ1], 256 * sizeof(float), st))) return rc;
@@ -818,7 +845,7 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   mlp_dw_tc_kernel<<<dim3(per_job, 5), DW_THREADS, DW_SMEM, st>>>(d);
   CNRF_LAUNCH_CHECK();
 
-  const unsigned cs_grid = (unsigned)((a.M + 511) / 512);
+  const unsigned cs_grid = (unsigned)((a.M + CSUM_ROWS - 1) / CSUM_ROWS);
   img_weighted_colsum_kernel<1><<<cs_grid, 128, 0, st>>>(dy, DY_PER_TILE, 0, a.M, nullptr, 0, g->bias[CNRF_L_DIR2], 0);
   CNRF_LAUNCH_CHECK();
   img_weighted_colsum_kernel<1><<<cs_grid, 128, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 1 * (size_t)TILE_BYTES, a.M,

@@ -110,7 +110,7 @@ int cnrf_strided_rowsum(const float* X, int64_t ld_x, int64_t G, int64_t g_strid
   return CNRF_OK;
 }
 
-constexpr int CS_ROWS = 256;
+constexpr int CS_ROWS = 32;
 __global__ void colsum_kernel(const float* __restrict__ X, int64_t ld_x, int64_t M, int N, float* __restrict__ out) {
   int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= N) return;

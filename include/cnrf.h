@@ -198,6 +198,11 @@ int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
  * ---------------------------------------------------------------------------------------------------- */
 /* Synchronises the device; returns 1 if a tensor-core kernel of this process hit its bounded barrier-wait timeout. */
 int cnrf_debug_tc_error(void);
+/* C[M,N] (row stride ldc) = sum_k A[m*a_rs + k*a_cs] * B[k*b_rs + n*b_cs] through the per-ray GEMM toolkit:
+ * tc = 0 the fp32 CUDA-core kernel (sgemm.cu), tc = 1 the tcgen05 kernel (gemm_tc.cu, bf16 operands).  accumulate = 1
+ * adds into C.  Lets tests pin every operand-majorness combination the per-ray layers use. */
+int cnrf_debug_gemm(int32_t tc, const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs, int64_t b_cs,
+                    float* C, int64_t ldc, int64_t M, int32_t N, int64_t K, int32_t accumulate, cnrf_stream_t stream);
 int cnrf_debug_umma(int32_t mode, const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t* err,
                     cnrf_stream_t stream);
 

@@ -134,7 +134,8 @@ def test_tc_backward_matches_fp32(dev, N, S, pairing):
                 fro[k] = ((a - b).norm() / b.norm().clamp_min(1e-30)).item()
                 cos[k] = (torch.dot(a, b) / (a.norm() * b.norm()).clamp_min(1e-30)).item()
             print(f"\n[{kind}] worst max-normalised {max(mx.values()):.2e}, worst Frobenius {max(fro.values()):.2e}, "
-                  f"worst cosine {min(cos.values()):.4f}")
+                  f"worst cosine {min(cos.values()):.4f}; largest: "
+                  + ", ".join(f"{k}={v:.2e}" for k, v in sorted(mx.items(), key=lambda kv: -kv[1])[:4]))
             if kind == "coherent":
                 assert max(mx.values()) < 3e-2, {k: f"{v:.2e}" for k, v in mx.items()}
             else:
@@ -142,3 +143,43 @@ def test_tc_backward_matches_fp32(dev, N, S, pairing):
     finally:
         nerf.set_pairing("reference")
         nerf.set_precision("fp32")
+
+
+# ---- generic tcgen05 GEMM of the per-ray layers (gemm_tc.cu) against the fp32 SIMT kernel and torch ------------------
+def _gemm(dev, tc, A, a_rs, a_cs, B, b_rs, b_cs, M, N, K, C=None, accumulate=0):
+    import ctypes as Ct
+    from codenerf_b200 import _lib
+    lib = _lib.load()
+    out = torch.zeros(M, N, device=dev) if C is None else C
+    _lib.check(lib.cnrf_debug_gemm(tc, Ct.c_void_p(A.data_ptr()), a_rs, a_cs, Ct.c_void_p(B.data_ptr()), b_rs, b_cs,
+                                   Ct.c_void_p(out.data_ptr()), out.stride(0), M, N, K, accumulate,
+                                   Ct.c_void_p(torch.cuda.current_stream().cuda_stream)), "cnrf_debug_gemm")
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K", [(4096, 256, 256), (300, 257, 256), (4096, 256, 257), (200, 3, 256), (4096, 256, 27),
+                                   (130, 27, 256), (128, 64, 16)])
+def test_gemm_tc_forms(dev, M, N, K):
+    """The three operand forms of the per-ray layers: X W^T (K-major / K-major), dY W (K-major / MN-major) and
+    dY^T X (MN-major / MN-major, split-K over the rows).  Split-bf16 (hi*hi + hi*lo + lo*hi): ~16 mantissa bits, so
+    the comparison is against the plain fp32 product."""
+    g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K)
+    bf = lambda t: t
+    torch.backends.cuda.matmul.allow_tf32 = False
+    # lin: C[M,N] = X[M,K] W[N,K]^T
+    X, W = torch.randn(M, K, generator=g).to(dev), torch.randn(N, K, generator=g).to(dev)
+    ref = bf(X) @ bf(W).t()
+    got = _gemm(dev, 1, X, K, 1, W, 1, K, M, N, K)
+    assert torch.allclose(got, ref, atol=2e-4 * K ** 0.5, rtol=1e-4)
+    assert torch.allclose(_gemm(dev, 0, X, K, 1, W, 1, K, M, N, K), X @ W.t(), atol=1e-3, rtol=1e-4)
+    # dgrad: dX[M,K] = dY[M,N] W[N,K]      (contraction over N)
+    dY = torch.randn(M, N, generator=g).to(dev)
+    got = _gemm(dev, 1, dY, N, 1, W, K, 1, M, K, N)
+    assert torch.allclose(got, bf(dY) @ bf(W), atol=2e-4 * N ** 0.5, rtol=1e-4)
+    # wgrad: dW[N,K] += dY[M,N]^T X[M,K]   (contraction over the M rows; split-K when M > 320)
+    acc = torch.ones(N, K, device=dev)
+    got = _gemm(dev, 1, dY, 1, N, X, K, 1, N, K, M, C=acc, accumulate=1)
+    assert torch.allclose(got, 1.0 + bf(dY).t() @ bf(X), atol=2e-4 * M ** 0.5, rtol=1e-4)
+    from codenerf_b200 import _lib
+    assert _lib.load().cnrf_debug_tc_error() == 0
