@@ -125,57 +125,131 @@ inline void pair_index(const Dims& d, int64_t& div, int64_t& mod) {
 }
 
 // ---- per-ray layers ------------------------------------------------------------------------------------------
+// Mutually independent GEMMs are collected and issued as ONE tcgen05 launch (gemm_tc.cu) in the bf16 mode; the fp32
+// mode runs them one by one through the SIMT kernel.
+GemmArgs mk_lin(const float* X, int64_t ldx, int64_t rows, int K, const float* W, int64_t ldw, int Nout, float* Y,
+                int64_t ldy, const float* bias, int relu) {
+  GemmArgs g;
+  g.A = X; g.a_rs = ldx; g.a_cs = 1; g.B = W; g.b_rs = 1; g.b_cs = ldw; g.C = Y; g.ldc = ldy;
+  g.M = rows; g.N = Nout; g.K = K; g.bias = bias; g.ld_bias = 0; g.relu = relu;
+  return g;
+}
+GemmArgs mk_dgrad(const float* dY, int64_t ldy, int64_t rows, int Nout, const float* W, int64_t ldw, int K, float* dX,
+                  int64_t ldx, const float* mask, int64_t ldm, int accumulate) {
+  GemmArgs g;
+  g.A = dY; g.a_rs = ldy; g.a_cs = 1; g.B = W; g.b_rs = ldw; g.b_cs = 1; g.C = dX; g.ldc = ldx;
+  g.M = rows; g.N = K; g.K = Nout; g.mask = mask; g.ld_mask = ldm; g.accumulate = accumulate;
+  return g;
+}
+GemmArgs mk_wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int64_t rows, int Nout, int K, float* dW,
+                  int64_t ldw) {
+  GemmArgs g;
+  g.A = dY; g.a_rs = 1; g.a_cs = ldy; g.B = X; g.b_rs = ldx; g.b_cs = 1; g.C = dW; g.ldc = ldw;
+  g.M = Nout; g.N = K; g.K = rows;
+  int64_t tiles = ((Nout + 63) / 64) * (int64_t)((K + 63) / 64);
+  int64_t want = (1184 + tiles - 1) / tiles, cap = (rows + 511) / 512;
+  g.split_k = (int)std::max<int64_t>(1, std::min<int64_t>(want, cap));
+  if (g.split_k == 1) g.accumulate = 1;   // += into the zero-filled buffer
+  return g;
+}
+// out[0, n] += sum_m X[m, n] as ones^T X (out zero-filled by the caller)
+GemmArgs mk_colsum(const float* ones, const float* X, int64_t ldx, int64_t rows, int N, float* out) {
+  return mk_wgrad(ones, 1, X, ldx, rows, 1, N, out, N);
+}
+struct Batch {
+  GemmArgs g[CNRF_GEMM_BATCH_MAX];
+  int n = 0;
+  void add(const GemmArgs& a) { g[n++] = a; }
+  int flush(bool tc, cudaStream_t st) {
+    int rc = tc ? cnrf_gemm_tc_batch(g, n, st) : CNRF_E_UNSUPPORTED;
+    if (rc == CNRF_E_UNSUPPORTED) {
+      rc = CNRF_OK;
+      for (int i = 0; i < n && rc == CNRF_OK; ++i) rc = cnrf_sgemm(g[i], st);
+    }
+    n = 0;
+    return rc;
+  }
+};
+
 int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir, int64_t ld_dir, const float* z_s,
                 int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
                 bool split_bo, cudaStream_t st) {
   const int H = d.H, C = d.C;
-  const int64_t INF = INT64_MAX;
-  RUN(lin(d.tc, z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 0, 1, INF, 1, st));   // model.py:174
-  RUN(lin(d.tc, z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 0, 1, INF, 1, st));   // :175
-  RUN(lin(d.tc, z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 0, 1, INF, 1, st));// :177
-  RUN(lin(d.tc, as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0, 1, INF, 0, st));
+  Batch b;
+  b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 1));     // model.py:174
+  b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 1));     // :175
+  b.add(mk_lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 1));  // :177
+  b.add(mk_lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0));
+  RUN(b.flush(d.tc, st));
+  b.add(mk_lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0));
   if (split_bo) {   // tensor-core chain: 16-byte aligned feature rows + a separate sigma column
-    RUN(lin(d.tc, as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, t.bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0, 1, INF, 0, st));
-    RUN(lin(d.tc, as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, t.bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0));
+    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0));
   } else {
-    RUN(lin(d.tc, as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0, 1, INF, 0, st));
+    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0));
   }
-  RUN(lin(d.tc, at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0, 1, INF, 0, st));
-  RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0, 1, INF, 0, st));
-  return CNRF_OK;
+  b.add(mk_lin(at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0));
+  return b.flush(d.tc, st);
 }
 
-// gradients of the bias tables -> code-layer weights, code halves of the split layers, z_s / z_t / x_dir
+// gradients of the bias tables -> code-layer weights, code halves of the split layers, z_s / z_t / x_dir.
+// tmp: 3 x [N,C] scratch + [N] (a ones vector for the bias-gradient column sums of the tensor-core mode).
 int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codenerf_grads* g, const float* x_dir,
                 int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* as1,
-                const float* as2, const float* at, const Tables& dt, float* tmp /*[N,C]*/, float* g_z_s, float* g_z_t,
+                const float* as2, const float* at, const Tables& dt, float* tmp, float* g_z_s, float* g_z_t,
                 float* g_x_dir, cudaStream_t st) {
   const int H = d.H, C = d.C;
-  // texture branch: betar = Wrt at + br
-  RUN(cnrf_colsum(dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB], st));
-  RUN(wgrad(d.tc, dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C, st));
-  RUN(dgrad(d.tc, dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp, C, at, C, 0, st));
-  RUN(wgrad(d.tc, tmp, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C, st));
-  RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_TEXTURE1], st));
-  RUN(dgrad(d.tc, tmp, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, 0, st));
-  // shape branch 2: betao = Woc as2 + bo
-  RUN(cnrf_colsum(dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT], st));
-  RUN(wgrad(d.tc, dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C, st));
-  RUN(dgrad(d.tc, dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp, C, as2, C, 0, st));
-  RUN(wgrad(d.tc, tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C, st));
-  RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_SHAPE2], st));
-  RUN(dgrad(d.tc, tmp, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, 0, st));
-  // shape branch 1: beta2 = W2c as1 + b2
-  RUN(cnrf_colsum(dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2], st));
-  RUN(wgrad(d.tc, dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C, st));
-  RUN(dgrad(d.tc, dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp, C, as1, C, 0, st));
-  RUN(wgrad(d.tc, tmp, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C, st));
-  RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_SHAPE1], st));
-  RUN(dgrad(d.tc, tmp, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1, st));
+  const size_t nc = al(d.N * C) / sizeof(float);
+  float *tmp_t = tmp, *tmp_s2 = tmp + nc, *tmp_s1 = tmp + 2 * nc, *ones = tmp + 3 * nc;
+  if (d.tc) {       // bias gradients were zero-filled with the weights (zero_weight_grads)
+    FillBatch f;
+    f.add(g_z_s, d.N * C);
+    f.add(ones, d.N, 1.0f);
+    RUN(cnrf_fill_batch(f, st));
+  }
+  Batch b;
+  // texture branch: betar = Wrt at + br;   shape branch 2: betao = Woc as2 + bo;   shape branch 1: beta2 = W2c as1 + b2;
   // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
-  RUN(cnrf_colsum(dt.bd, H, d.N, H, g->bias[CNRF_L_DIR1], st));
-  RUN(wgrad(d.tc, dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd, st));
-  if (g_x_dir) RUN(dgrad(d.tc, dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0, st));
+  b.add(mk_wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C));
+  b.add(mk_dgrad(dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp_t, C, at, C, 0));
+  b.add(mk_wgrad(dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C));
+  b.add(mk_dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp_s2, C, as2, C, 0));
+  b.add(mk_wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C));
+  b.add(mk_dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp_s1, C, as1, C, 0));
+  b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
+  if (g_x_dir) b.add(mk_dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0));
+  if (d.tc) {
+    b.add(mk_colsum(ones, dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB]));
+    b.add(mk_colsum(ones, dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT]));
+    b.add(mk_colsum(ones, dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2]));
+    b.add(mk_colsum(ones, dt.bd, H, d.N, H, g->bias[CNRF_L_DIR1]));
+  }
+  RUN(b.flush(d.tc, st));
+  if (!d.tc) {
+    RUN(cnrf_colsum(dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB], st));
+    RUN(cnrf_colsum(dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT], st));
+    RUN(cnrf_colsum(dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2], st));
+    RUN(cnrf_colsum(dt.bd, H, d.N, H, g->bias[CNRF_L_DIR1], st));
+  }
+  // the three latent-code layers
+  b.add(mk_wgrad(tmp_t, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C));
+  b.add(mk_dgrad(tmp_t, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, 0));
+  b.add(mk_wgrad(tmp_s2, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C));
+  b.add(mk_wgrad(tmp_s1, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C));
+  // both shape branches land in g_z_s: added atomically onto the zero-filled buffer when they share a launch
+  b.add(mk_dgrad(tmp_s2, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, d.tc ? 1 : 0));
+  b.add(mk_dgrad(tmp_s1, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1));
+  if (d.tc) {
+    b.add(mk_colsum(ones, tmp_t, C, d.N, C, g->bias[CNRF_L_TEXTURE1]));
+    b.add(mk_colsum(ones, tmp_s2, C, d.N, C, g->bias[CNRF_L_SHAPE2]));
+    b.add(mk_colsum(ones, tmp_s1, C, d.N, C, g->bias[CNRF_L_SHAPE1]));
+  }
+  RUN(b.flush(d.tc, st));
+  if (!d.tc) {
+    RUN(cnrf_colsum(tmp_t, C, d.N, C, g->bias[CNRF_L_TEXTURE1], st));
+    RUN(cnrf_colsum(tmp_s2, C, d.N, C, g->bias[CNRF_L_SHAPE2], st));
+    RUN(cnrf_colsum(tmp_s1, C, d.N, C, g->bias[CNRF_L_SHAPE1], st));
+  }
   return CNRF_OK;
 }
 
@@ -236,11 +310,15 @@ int zero_weight_grads(const Dims& d, const cnrf_codenerf_grads* g, cudaStream_t 
   const size_t n[CNRF_NUM_LAYERS] = {(size_t)H * d.dx, (size_t)H * (H + C), (size_t)(C + 1) * (H + C), (size_t)C * C,
                                      (size_t)C * C, (size_t)C * C, (size_t)H * (C + d.dd), (size_t)H * H,
                                      (size_t)3 * (H + C)};
+  const size_t nb[CNRF_NUM_LAYERS] = {(size_t)H, (size_t)H, (size_t)C + 1, (size_t)C, (size_t)C, (size_t)C, (size_t)H,
+                                      (size_t)H, 3};
+  FillBatch f;
   for (int l = 0; l < CNRF_NUM_LAYERS; ++l) {
     if (!g->weight[l] || !g->bias[l]) return CNRF_E_NULL;
-    RUN(cnrf_fill_zero(g->weight[l], n[l] * sizeof(float), st));
+    f.add(g->weight[l], (int64_t)n[l]);
+    f.add(g->bias[l], (int64_t)nb[l]);
   }
-  return CNRF_OK;
+  return cnrf_fill_batch(f, st);
 }
 
 inline size_t max_sz(size_t a, size_t b) { return a > b ? a : b; }
@@ -264,9 +342,9 @@ extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32
   size_t b = tables_bytes(d);
   if (s->precision == CNRF_PRECISION_FP32) {
     if (!backward) return b + (s->keep ? 0 : saved_f32_bytes(d));     // inference still needs the activation buffers
-    return b + 2 * al(d.M * max_sz(d.H, d.C + 1)) + al(d.N * d.C);
+    return b + 2 * al(d.M * max_sz(d.H, d.C + 1)) + 3 * al(d.N * d.C) + al(d.N);
   }
-  return b + al(d.N * d.C) + (s->keep || backward ? 0 : 3 * al(d.N * d.C)) + cnrf_tc_workspace_bytes(d.N, d.M, backward);
+  return b + 3 * al(d.N * d.C) + al(d.N) + (s->keep || backward ? 0 : 3 * al(d.N * d.C)) + cnrf_tc_workspace_bytes(d.N, d.M, backward);
 }
 
 // tensor-core per-sample chain (mlp_tc.cu).  x_xyz == nullptr means "encode pts in-kernel" (field mode).
@@ -339,7 +417,8 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   Arena w(ws, ws_bytes);
   Tables dt;
   carve_tables(d, w, dt);
-  float* tmp = w.take(d.N * d.C);
+  float* tmp = w.take(d.N * d.C);          // 3 x [N,C] + [N], contiguous (per_ray_bwd)
+  w.take(d.N * d.C); w.take(d.N * d.C); w.take(d.N);
   if (!w.ok) return CNRF_E_WORKSPACE;
   RUN(zero_weight_grads(d, g, st));
   if (s->precision == CNRF_PRECISION_FP32) {

@@ -1,16 +1,17 @@
-// Generic tcgen05 GEMM for the per-RAY layers of the bf16 mode (latent-code layers, folded-bias tables and their
+// Batched tcgen05 GEMM for the per-RAY layers of the bf16 mode (latent-code layers, folded-bias tables and their
 // backward: models/model.py:174-177 and the code halves of :180-192).  Same contract as the SIMT cnrf_sgemm (internal.h):
 //     C(m,n) = epi( sum_k A(m,k) B(k,n) ),   A(m,k) = A[m*a_rs + k*a_cs],   B(k,n) = B[k*b_rs + n*b_cs]
 // but the contraction runs on the tensor cores as split-bf16: every fp32 operand value is carried as hi + lo (two bf16
 // images) and hi*hi + hi*lo + lo*hi is accumulated in fp32 TMEM (~16 mantissa bits, 3 MMAs per K step -- these GEMMs
 // are 5% of the step's FLOPs, and fp32-grade code layers keep their ReLU masks identical to the parity mode's).
 //
-// One CTA = one 128 x 64 output tile; K is walked in chunks of 256 (long K of the weight-gradient form: split over
-// grid.z, partials added atomically -- its output is zero-filled by the caller).  These problems are
-// small (M = rays of a chunk, N,K <= 320, or K = rays for dW), so the kernel is deliberately simple: all threads convert
-// the fp32 operands to bf16 straight into the 128-byte-swizzled shared-memory image (rows = the strided index, columns =
-// the contiguous index), ONE thread issues the K/16 MMAs, the operand majorness is chosen by the descriptor
-// (K-major when k is the contiguous index, MN-major otherwise -- no transposed copies), all 8 warps run the epilogue.
+// These problems are small (M = rays of a chunk, N,K <= 320, or K = rays for dW) and latency-bound, so up to 16 mutually
+// independent problems share ONE launch (grid = sum of their tiles).  One CTA = one 128 x 64 output tile; K is walked in
+// chunks of 256 (long K of the weight-gradient form: split over CTAs, partials added atomically -- its output is
+// zero-filled by the caller).  All threads convert the fp32 operands to bf16 straight into the 128-byte-swizzled
+// shared-memory image (rows = the strided index, columns = the contiguous index), ONE thread issues the MMAs, the
+// operand majorness is chosen by the descriptor (K-major when k is the contiguous index, MN-major otherwise -- no
+// transposed copies), 8 warps run the epilogue with 16-byte stores / vector reductions.
 #include "common.cuh"
 #include "internal.h"
 #include "tc_common.cuh"
@@ -18,45 +19,73 @@
 using namespace tc;
 
 namespace {
-constexpr int GBM = 128, GBN = 64, GKC = 256, GTHREADS = 256;
+constexpr int GBM = 128, GBN = 64, GKC = 256, GTHREADS = 512;
 constexpr int A_BYTES = GBM * GKC * 2;      // one bf16 image of the A tile for a 256-wide K chunk (64 KB)
 constexpr int B_BYTES = GBN * GKC * 2;      // ... of the B tile (32 KB)
 constexpr int G_SMEM = 2 * (A_BYTES + B_BYTES) + 1024 /*alignment slack*/;   // hi and lo images
 
+struct GemmBatch {
+  GemmArgs g[CNRF_GEMM_BATCH_MAX];
+  int64_t kslice[CNRF_GEMM_BATCH_MAX];
+  int a_mn[CNRF_GEMM_BATCH_MAX], b_mn[CNRF_GEMM_BATCH_MAX];
+  int mt[CNRF_GEMM_BATCH_MAX], nt[CNRF_GEMM_BATCH_MAX];
+  int first[CNRF_GEMM_BATCH_MAX + 1];   // first CTA of each problem
+  int count;
+};
+
 // image(r, c) = src[(r0 + r) * row_stride + c0 + c] (0 outside rows_valid x cols_valid); columns are the contiguous index.
 // Slab s holds columns [64 s, 64 s + 64) of every row, rows 128 bytes apart, 128-byte swizzle (tc_common.cuh).
-// The fp32 value is split as hi = bf16(x), lo = bf16(x - hi): hi*hi + hi*lo + lo*hi on the tensor cores carries ~16
-// mantissa bits, so the per-ray layers (and the ReLU masks of the latent-code layers) match the fp32 path closely.
-__device__ __forceinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int rows_tile, int cols_tile,
-                                           uint32_t slab_stride, const float* __restrict__ src, int64_t row_stride,
-                                           int64_t r0, int64_t c0, int64_t rows_valid, int64_t cols_valid, int tid) {
+// hi = bf16(x), lo = bf16(x - hi).
+__device__ __noinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int rows_tile, int cols_tile,
+                                        uint32_t slab_stride, const float* __restrict__ src, int64_t row_stride,
+                                        int64_t r0, int64_t c0, int64_t rows_valid, int64_t cols_valid, int tid) {
   const int groups = cols_tile >> 2;
+  const int gshift = 31 - __clz(groups);               // cols_tile is 64, 128, 192 or 256: not always a power of two
+  const bool pow2 = (groups & (groups - 1)) == 0;
+  const int total = rows_tile * groups;
   const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((row_stride & 3) == 0) && ((c0 & 3) == 0);
-  for (int i = tid; i < rows_tile * groups; i += GTHREADS) {
-    const int r = i / groups, c = (i - r * groups) << 2;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    const int64_t gr = r0 + r, gc = c0 + c;
-    if (gr < rows_valid && gc < cols_valid) {
-      const float* p = src + gr * row_stride + gc;
-      if (vec && gc + 3 < cols_valid) {
-        v = __ldg(reinterpret_cast<const float4*>(p));
-      } else {
-        v.x = __ldg(p);
-        if (gc + 1 < cols_valid) v.y = __ldg(p + 1);
-        if (gc + 2 < cols_valid) v.z = __ldg(p + 2);
-        if (gc + 3 < cols_valid) v.w = __ldg(p + 3);
+  constexpr int U = 16;                                // independent global loads in flight per thread: a whole
+                                                       // 128 x 256 tile is ONE round trip (cold misses cost ~2.5 us each)
+#pragma unroll 1
+  for (int base = tid; base < total; base += GTHREADS * U) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = base + u * GTHREADS;
+      v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (i < total) {
+        const int r = pow2 ? (i >> gshift) : (i / groups), c = (i - r * groups) << 2;
+        const int64_t gr = r0 + r, gc = c0 + c;
+        if (gr < rows_valid && gc < cols_valid) {
+          const float* p = src + gr * row_stride + gc;
+          if (vec && gc + 3 < cols_valid) {
+            v[u] = __ldg(reinterpret_cast<const float4*>(p));
+          } else {
+            v[u].x = __ldg(p);
+            if (gc + 1 < cols_valid) v[u].y = __ldg(p + 1);
+            if (gc + 2 < cols_valid) v[u].z = __ldg(p + 2);
+            if (gc + 3 < cols_valid) v[u].w = __ldg(p + 3);
+          }
+        }
       }
     }
-    const float hx = __bfloat162float(__float2bfloat16(v.x)), hy = __bfloat162float(__float2bfloat16(v.y));
-    const float hz = __bfloat162float(__float2bfloat16(v.z)), hw = __bfloat162float(__float2bfloat16(v.w));
-    const uint32_t off = (c >> 6) * slab_stride + slab_offset(r, c & 63);
-    *reinterpret_cast<uint2*>(img_hi + off) = make_uint2(pack_bf16(hx, hy), pack_bf16(hz, hw));
-    *reinterpret_cast<uint2*>(img_lo + off) = make_uint2(pack_bf16(v.x - hx, v.y - hy), pack_bf16(v.z - hz, v.w - hw));
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int i = base + u * GTHREADS;
+      if (i < total) {
+        const int r = pow2 ? (i >> gshift) : (i / groups), c = (i - r * groups) << 2;
+        const float hx = __bfloat162float(__float2bfloat16(v[u].x)), hy = __bfloat162float(__float2bfloat16(v[u].y));
+        const float hz = __bfloat162float(__float2bfloat16(v[u].z)), hw = __bfloat162float(__float2bfloat16(v[u].w));
+        const uint32_t off = (c >> 6) * slab_stride + slab_offset(r, c & 63);
+        *reinterpret_cast<uint2*>(img_hi + off) = make_uint2(pack_bf16(hx, hy), pack_bf16(hz, hw));
+        *reinterpret_cast<uint2*>(img_lo + off) =
+            make_uint2(pack_bf16(v[u].x - hx, v[u].y - hy), pack_bf16(v[u].z - hz, v[u].w - hw));
+      }
+    }
   }
 }
 
-// grid = (M tiles, N tiles, K slices); a CTA walks its K slice [kbeg, kend) in chunks of 256.
-__global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_kernel(GemmArgs g, int a_mn, int b_mn, int64_t kslice, int* err) {
+__global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_batch_kernel(const __grid_constant__ GemmBatch b, int* err) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -66,10 +95,18 @@ __global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_kernel(GemmArgs g, int a_
   uint8_t* b_hi = smem + 2 * A_BYTES;
   uint8_t* b_lo = smem + 2 * A_BYTES + B_BYTES;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int64_t m0 = (int64_t)blockIdx.x * GBM;
-  const int64_t n0 = (int64_t)blockIdx.y * GBN;
-  const int64_t kbeg = (int64_t)blockIdx.z * kslice;
-  const int64_t kend = min(g.K, kbeg + kslice);
+  int p = 0;
+  while (p + 1 < b.count && (int)blockIdx.x >= b.first[p + 1]) ++p;
+  const GemmArgs& g = b.g[p];
+  const int a_mn = b.a_mn[p], b_mn = b.b_mn[p];
+  const int local = blockIdx.x - b.first[p];
+  const int mx = local % b.mt[p], rest = local / b.mt[p];
+  const int ny = rest % b.nt[p], kz = rest / b.nt[p];
+  const bool multi_k = (g.K + b.kslice[p] - 1) / b.kslice[p] > 1;
+  const int64_t m0 = (int64_t)mx * GBM;
+  const int64_t n0 = (int64_t)ny * GBN;
+  const int64_t kbeg = (int64_t)kz * b.kslice[p];
+  const int64_t kend = min(g.K, kbeg + b.kslice[p]);
 
   if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
   if (warp == 1) tmem_alloc(&tmem_slot, 64);
@@ -80,6 +117,7 @@ __global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_kernel(GemmArgs g, int a_
   const uint32_t idesc = idesc_bf16(GBM, GBN, a_mn, b_mn);
   bool ok = true;
   uint32_t phase = 0;
+#pragma unroll 1
   for (int64_t k0 = kbeg; k0 < kend; k0 += GKC) {
     const int kc = (int)min((int64_t)GKC, kend - k0);
     const int kpad = (kc + 15) & ~15;
@@ -101,9 +139,10 @@ __global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_kernel(GemmArgs g, int a_
     if (tid == 0 && ok) {
       tc_fence_after();
       const uint32_t sa[2] = {smem_u32(a_hi), smem_u32(a_lo)}, sb[2] = {smem_u32(b_hi), smem_u32(b_lo)};
-#pragma unroll
+#pragma unroll 1
       for (int term = 0; term < 3; ++term) {           // hi*hi, hi*lo, lo*hi
         const uint32_t pa = sa[term == 2], pb = sb[term == 1];
+#pragma unroll 1
         for (int j = 0; j < kpad / 16; ++j) {
           const uint64_t ad = a_mn ? smem_desc(pa + j * 2048, a_slab, 1024, SWIZZLE_128B)
                                    : smem_desc(pa + (j >> 2) * a_slab + (j & 3) * 32, 16, 1024, SWIZZLE_128B);
@@ -117,27 +156,46 @@ __global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_kernel(GemmArgs g, int a_
   }
   ok = ok && mbar_wait(&bar, phase, err);
   tc_fence_after();
-  if (ok) {
+  if (ok && warp < 8) {
     const int q = warp & 3, half = warp >> 2;          // TMEM lane quarter, column half of the 64-wide tile
     const int64_t m = m0 + q * 32 + lane;
     uint32_t v[32];
     tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + half * 32, v);
     tmem_ld_wait();
     if (m < g.M) {
-      const bool add = g.split_k > 1 || g.accumulate || gridDim.z > 1;
+      const bool add = g.split_k > 1 || g.accumulate || multi_k;
       const float* brow = g.bias ? g.bias + ((m / g.bias_div) % g.bias_mod) * g.ld_bias : nullptr;
       float* crow = g.C + m * g.ldc;
       const float* mrow = g.mask ? g.mask + m * g.ld_mask : nullptr;
+      const bool al16 = ((reinterpret_cast<uintptr_t>(crow) & 15) == 0) &&
+                        (!brow || (reinterpret_cast<uintptr_t>(brow) & 15) == 0) &&
+                        (!mrow || (reinterpret_cast<uintptr_t>(mrow) & 15) == 0);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
+      for (int j = 0; j < 32; j += 4) {
         const int64_t n = n0 + half * 32 + j;
         if (n >= g.N) break;
-        float x = __uint_as_float(v[j]);
-        if (add) { atomicAdd(crow + n, x); continue; }
-        if (brow) x += brow[n];
-        if (g.relu) x = fmaxf(x, 0.f);
-        if (mrow) x = mrow[n] > 0.f ? x : 0.f;
-        crow[n] = x;
+        float x[4] = {__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])};
+        if (al16 && n + 3 < g.N) {
+          if (add) { atomicAdd(reinterpret_cast<float4*>(crow + n), make_float4(x[0], x[1], x[2], x[3])); continue; }
+          if (brow) { const float4 t = __ldg(reinterpret_cast<const float4*>(brow + n)); x[0] += t.x; x[1] += t.y; x[2] += t.z; x[3] += t.w; }
+          if (g.relu) { x[0] = fmaxf(x[0], 0.f); x[1] = fmaxf(x[1], 0.f); x[2] = fmaxf(x[2], 0.f); x[3] = fmaxf(x[3], 0.f); }
+          if (mrow) {
+            const float4 t = __ldg(reinterpret_cast<const float4*>(mrow + n));
+            x[0] = t.x > 0.f ? x[0] : 0.f; x[1] = t.y > 0.f ? x[1] : 0.f; x[2] = t.z > 0.f ? x[2] : 0.f; x[3] = t.w > 0.f ? x[3] : 0.f;
+          }
+          *reinterpret_cast<float4*>(crow + n) = make_float4(x[0], x[1], x[2], x[3]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            if (n + i >= g.N) break;
+            float y = x[i];
+            if (add) { atomicAdd(crow + n + i, y); continue; }
+            if (brow) y += brow[n + i];
+            if (g.relu) y = fmaxf(y, 0.f);
+            if (mrow) y = mrow[n + i] > 0.f ? y : 0.f;
+            crow[n + i] = y;
+          }
+        }
       }
     }
   }
@@ -145,40 +203,51 @@ __global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_kernel(GemmArgs g, int a_
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem, 64);
 }
-
-int* gemm_err_ptr();
 }  // namespace
 
 __device__ int g_gemm_tc_error = 0;
-namespace {
-int* gemm_err_ptr() {
+static int* gemm_err_ptr() {
   static int* p = nullptr;
   if (!p) cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gemm_tc_error);
   return p;
 }
-}  // namespace
 
-// Returns CNRF_E_UNSUPPORTED when neither stride of an operand is 1 (caller falls back to cnrf_sgemm).
-int cnrf_gemm_tc(const GemmArgs& a, cudaStream_t st) {
-  if (!a.A || !a.B || !a.C) return CNRF_E_NULL;
-  if (a.M <= 0 || a.N <= 0 || a.K <= 0 || a.split_k < 1) return CNRF_E_SHAPE;
-  int a_mn, b_mn;
-  if (a.a_cs == 1) a_mn = 0; else if (a.a_rs == 1) a_mn = 1; else return CNRF_E_UNSUPPORTED;
-  if (a.b_rs == 1) b_mn = 0; else if (a.b_cs == 1) b_mn = 1; else return CNRF_E_UNSUPPORTED;
-  // split K over CTAs only where the caller already adds into C (weight gradients: K = rays of the chunk)
-  const bool may_split = a.split_k > 1 || a.accumulate;
-  const int64_t kslice = (may_split && a.K > 2 * GKC) ? GKC : a.K;
+// Returns CNRF_E_UNSUPPORTED (nothing launched) when some operand has neither stride equal to 1: the caller then runs
+// the problems through cnrf_sgemm.  The problems of one call must not depend on each other.
+int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
+  if (count <= 0) return CNRF_OK;
+  if (!list || count > CNRF_GEMM_BATCH_MAX) return CNRF_E_SHAPE;
+  GemmBatch b;
+  b.count = count;
+  int total = 0;
+  for (int i = 0; i < count; ++i) {
+    const GemmArgs& a = list[i];
+    if (!a.A || !a.B || !a.C) return CNRF_E_NULL;
+    if (a.M <= 0 || a.N <= 0 || a.K <= 0 || a.split_k < 1) return CNRF_E_SHAPE;
+    if (a.a_cs == 1) b.a_mn[i] = 0; else if (a.a_rs == 1) b.a_mn[i] = 1; else return CNRF_E_UNSUPPORTED;
+    if (a.b_rs == 1) b.b_mn[i] = 0; else if (a.b_cs == 1) b.b_mn[i] = 1; else return CNRF_E_UNSUPPORTED;
+    // split K over CTAs only where the caller already adds into C (weight gradients: K = rays of the chunk)
+    const bool may_split = a.split_k > 1 || a.accumulate;
+    b.kslice[i] = (may_split && a.K > 2 * GKC) ? GKC : a.K;
+    b.g[i] = a;
+    b.mt[i] = (int)((a.M + GBM - 1) / GBM);
+    b.nt[i] = (a.N + GBN - 1) / GBN;
+    b.first[i] = total;
+    total += b.mt[i] * b.nt[i] * (int)((a.K + b.kslice[i] - 1) / b.kslice[i]);
+  }
+  b.first[count] = total;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  dim3 grid((unsigned)((a.M + GBM - 1) / GBM), (unsigned)((a.N + GBN - 1) / GBN), (unsigned)((a.K + kslice - 1) / kslice));
-  gemm_tc_kernel<<<grid, GTHREADS, G_SMEM, st>>>(a, a_mn, b_mn, kslice, gemm_err_ptr());
+  gemm_tc_batch_kernel<<<total, GTHREADS, G_SMEM, st>>>(b, gemm_err_ptr());
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }
+
+int cnrf_gemm_tc(const GemmArgs& a, cudaStream_t st) { return cnrf_gemm_tc_batch(&a, 1, st); }
 
 extern "C" int cnrf_debug_gemm(int32_t tc, const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs,
                                int64_t b_cs, float* C, int64_t ldc, int64_t M, int32_t N, int64_t K, int32_t accumulate,

@@ -21,6 +21,14 @@ int cnrf_sgemm(const GemmArgs& a, cudaStream_t st);
 // gemm_tc.cu: the same contract on the tensor cores (bf16 operands, fp32 accumulate); CNRF_E_UNSUPPORTED when neither
 // stride of an operand is 1 or K > 320 without split-K permission -- the caller then uses cnrf_sgemm.
 int cnrf_gemm_tc(const GemmArgs& a, cudaStream_t st);
+// up to CNRF_GEMM_BATCH_MAX mutually independent problems in one launch
+constexpr int CNRF_GEMM_BATCH_MAX = 16;
+int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st);
+// one launch: dst[i][0..n[i]) = value[i]  (zero-filling gradient buffers, ones vectors)
+constexpr int CNRF_FILL_BATCH_MAX = 24;
+struct FillBatch { float* dst[CNRF_FILL_BATCH_MAX]; int64_t n[CNRF_FILL_BATCH_MAX]; float value[CNRF_FILL_BATCH_MAX]; int count = 0;
+  void add(float* p, int64_t cnt, float v = 0.f) { dst[count] = p; n[count] = cnt; value[count] = v; ++count; } };
+int cnrf_fill_batch(const FillBatch& b, cudaStream_t st);
 // out[g*ld_out + n] = sum_{q<Q} X[(g*g_stride + q*q_stride)*ld_x + n],  g < G, n < N
 int cnrf_strided_rowsum(const float* X, int64_t ld_x, int64_t G, int64_t g_stride, int64_t Q, int64_t q_stride, int N,
                         float* out, int64_t ld_out, cudaStream_t st);

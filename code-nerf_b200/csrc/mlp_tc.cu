@@ -98,6 +98,7 @@ struct Bars {
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 __device__ __forceinline__ uint32_t cvt_relu_bf16x2(float lo, float hi) {
   uint32_t d;
   asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
@@ -272,12 +273,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       }
       float sigma = 0.f;
       for (int e = 0; e < 5; ++e, ++na) {
+        const float4* bias = reinterpret_cast<const float4*>(e == 1 ? a.b2 + ray * 256 : e == 2 ? a.bof + ray * 256
+                                                             : e == 3 ? a.bd + pair * 256 : e == 4 ? a.pk.b_dir2 : a.pk.zeros);
+        {   // pull this row's bias lines into L1 while the tensor core is still working on the layer.  Rows of a warp share
+            // their ray (1-2 distinct 1 KB rows per warp) except for the reference pairing of layer_dir1, whose 32 distinct
+            // rows per warp would not fit: there only the first lines are prefetched.
+          const int nl = (e == 3 && a.pairing == CNRF_PAIRING_REFERENCE) ? 2 : 8;
+          for (int j = 0; j < nl; ++j) prefetch_l1(bias + j * 8);
+        }
         if (!wait_bar(&bars->acc_full[t], na & 1, bars, a.err)) goto done;
         tc_fence_after();
         if (elected) bulk_wait_read0();               // image store of the previous layer no longer reads this tile
         named_bar_sync(bar_id, 128);
-        const float4* bias = reinterpret_cast<const float4*>(e == 1 ? a.b2 + ray * 256 : e == 2 ? a.bof + ray * 256
-                                                             : e == 3 ? a.bd + pair * 256 : e == 4 ? a.pk.b_dir2 : a.pk.zeros);
         float rgb[3] = {0.f, 0.f, 0.f};
         float4 bq[8];
 #pragma unroll

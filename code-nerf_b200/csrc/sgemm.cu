@@ -133,3 +133,17 @@ int cnrf_colsum(const float* X, int64_t ld_x, int64_t M, int N, float* out, cuda
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }
+
+__global__ void fill_batch_kernel(const __grid_constant__ FillBatch b) {
+  const int i = blockIdx.y;
+  float* d = b.dst[i];
+  const float v = b.value[i];
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < b.n[i]; j += (int64_t)gridDim.x * blockDim.x) d[j] = v;
+}
+int cnrf_fill_batch(const FillBatch& b, cudaStream_t st) {
+  if (b.count <= 0) return CNRF_OK;
+  if (b.count > CNRF_FILL_BATCH_MAX) return CNRF_E_SHAPE;
+  fill_batch_kernel<<<dim3(64, b.count), 256, 0, st>>>(b);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
