@@ -1,0 +1,332 @@
+// Forward chain of the fused bf16 tensor-core field (CNRF_PRECISION_BF16), models/model.py:179-194 code-folded:
+//   h1 = relu(W1 gamma(x) + b1) -> h2 = relu(W2h h1 + beta2[ray]) -> o = Woh h2 + betao[ray] -> v1 = relu(Wdf o[1:] +
+//   betad[pair]) -> v2 = relu(Wd2 v1 + bd2) -> rgb = Wrv v2 + betar[ray]
+// One persistent CTA per SM walks PAIRS of 128-row sample tiles (T0, T1) through the five layers in lockstep, so every
+// weight image fetched from L2 feeds 256 rows.
+//   TMEM   : 2 x 256 fp32 accumulator columns (all 512).
+//   smem   : 2 x 64 KB activation tiles (4 slabs of [128 x 64] bf16, 128-byte swizzle, overwritten in place layer by
+//            layer) + a ring of five 16 KB weight images ([128 out-features x 64 in-features]: the N-half of a K chunk,
+//            streamed by TMA bulk copies) + fp32 head vectors (fc_out row 0, fc_rgb, layer_dir2 bias) + a per-tile
+//            staging area for the per-ray bias rows of the current layer (cp.async, prefetched one layer ahead).
+//   warps  : 0 = TMA producer, 1 = MMA issuer (one lane), 2-5 = epilogue of T0, 6-9 = epilogue of T1 (thread = one sample
+//            row, TMEM lane quarter = warp_id % 4).
+// The epilogue is specialised per layer at compile time and fully unrolled: TMEM -> registers -> + bias -> ReLU -> bf16
+// -> swizzled smem (the next layer's A operand, also TMA-stored as the image the backward needs).
+#include "mlp_tc.cuh"
+
+__device__ long long g_fwd_dbg[16];
+#define FDBG(i, dt) do { if (blockIdx.x == 0) atomicAdd((unsigned long long*)&g_fwd_dbg[i], (unsigned long long)(dt)); } while (0)
+namespace {
+constexpr int HALF = 128 * 128;             // bytes of one [128 x 64] bf16 weight image
+constexpr int FRING = 5;
+constexpr int RMAX = 4;                     // rays one tile may span for its per-ray biases to be staged in smem
+constexpr int HEAD_FLOATS = 256 + 768 + 256;   // w_sigma | w_rgb[3] | b_dir2   (contiguous in Packed)
+constexpr int STAGE_FLOATS = RMAX * 256;       // per tile
+constexpr int OFF_RING = 2 * TILE_BYTES;
+constexpr int OFF_HEADS = OFF_RING + FRING * HALF;
+constexpr int OFF_STAGE = OFF_HEADS + HEAD_FLOATS * 4;
+constexpr int OFF_BARS = OFF_STAGE + 2 * STAGE_FLOATS * 4;
+constexpr int FWD_SMEM = OFF_BARS + 256;
+
+struct FBars {
+  uint64_t w_full[FRING], w_empty[FRING];
+  uint64_t a_ready[2];     // epilogue -> MMA : tile's operand image written
+  uint64_t acc_full[2];    // MMA -> epilogue : tile's accumulator complete
+  uint32_t tmem_slot;
+  int abort_flag;
+};
+
+// Bounded mbarrier wait (about a second): a protocol bug must end the kernel, never hang the GPU.
+__device__ __forceinline__ bool fwait(uint64_t* bar, uint32_t parity, FBars* b, int* err) {
+  if (mbar_try_wait(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (true) {
+    if (mbar_try_wait(bar, parity)) return true;
+    if (*(volatile int*)&b->abort_flag) return false;
+    if (clock64() - t0 > 2000000000LL) {
+      b->abort_flag = 1;
+      if (err) atomicExch(err, 1);
+      return false;
+    }
+  }
+}
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+struct Epi {               // per-thread state of an epilogue thread for the current tile
+  FBars* bars;
+  uint8_t* tile;
+  const float* heads;      // smem: w_sigma[256] | w_rgb[3][256] | b_dir2[256]
+  float* stage;            // smem: [RMAX][256] bias rows of this tile's rays
+  uint32_t tacc;
+  int r, bar_id, slot, nrays;
+  bool elected, valid, staged;
+  int64_t m, ray, pair, ray0;
+  uint8_t* sv;
+  float sigma;
+};
+
+// copy the `nrays` bias rows [ray0, ray0 + nrays) of a [N,256] fp32 table into the tile's staging area (128 threads)
+__device__ __forceinline__ void stage_rows(const Epi& c, const float* table) {
+  if (c.staged) {
+    for (int piece = c.r; piece < c.nrays * 64; piece += 128)
+      cp_async16(c.stage + piece * 4, table + (c.ray0 + (piece >> 6)) * 256 + (piece & 63) * 4);
+  }
+  cp_async_commit();
+}
+
+// One layer's epilogue for one tile.  E: 0 layer_xyz1, 1 layer_xyz2 (+ sigma head), 2 fc_out features (no ReLU),
+// 3 layer_dir1, 4 layer_dir2 (+ rgb head).  GB: bias row comes from global memory (register double buffer) instead of
+// shared memory.
+template <int E, bool GB>
+__device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint32_t parity) {
+  const float4* gb = nullptr;
+  const float4* sb = nullptr;
+  if (E == 1) { if (GB) gb = reinterpret_cast<const float4*>(a.b2 + c.ray * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
+  if (E == 2) { if (GB) gb = reinterpret_cast<const float4*>(a.bof + c.ray * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
+  if (E == 3) gb = reinterpret_cast<const float4*>(a.bd + c.pair * 256);
+  if (E == 4) sb = reinterpret_cast<const float4*>(c.heads + 1024);
+  float4 bcur[8], bnxt[8];
+  float tail0 = 0.f, tail1 = 0.f, tail2 = 0.f;
+  if (GB) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bcur[j] = __ldg(gb + j);
+  }
+  if (E == 1 && c.valid) tail0 = __ldg(a.bos + c.ray);
+  if (E == 4 && c.valid) { tail0 = __ldg(a.br + c.ray * 3); tail1 = __ldg(a.br + c.ray * 3 + 1); tail2 = __ldg(a.br + c.ray * 3 + 2); }
+  const long long tw0 = clock64();
+  if (!fwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
+  const long long tw1 = clock64();
+  tc_fence_after();
+  if (c.elected) bulk_wait_read0();                 // the previous image store no longer reads this tile
+  if ((E == 1 || E == 2) && !GB) cp_async_wait_all();
+  named_bar_sync(c.bar_id, 128);
+  const float4* hw = reinterpret_cast<const float4*>(c.heads);
+  float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f;
+#pragma unroll
+  for (int cb = 0; cb < 8; ++cb) {
+    uint32_t v[32];
+    tmem_ld32(c.tacc + cb * 32, v);
+    if (GB && cb < 7) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bnxt[j] = __ldg(gb + (cb + 1) * 8 + j);
+    }
+    if (!GB && E != 0) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bcur[j] = sb[cb * 8 + j];
+    }
+    tmem_ld_wait();
+    float f[32];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (E == 0) {
+        f[4 * j] = __uint_as_float(v[4 * j]); f[4 * j + 1] = __uint_as_float(v[4 * j + 1]);
+        f[4 * j + 2] = __uint_as_float(v[4 * j + 2]); f[4 * j + 3] = __uint_as_float(v[4 * j + 3]);
+      } else {
+        f[4 * j] = __uint_as_float(v[4 * j]) + bcur[j].x; f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + bcur[j].y;
+        f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + bcur[j].z; f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + bcur[j].w;
+      }
+    }
+    if (E == 1) {                                   // sigma_raw = w_sigma . h2 + betao[ray][0]   (fc_out row 0)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 w = hw[cb * 8 + j];
+        c.sigma = fmaf(fmaxf(f[4 * j], 0.f), w.x, c.sigma); c.sigma = fmaf(fmaxf(f[4 * j + 1], 0.f), w.y, c.sigma);
+        c.sigma = fmaf(fmaxf(f[4 * j + 2], 0.f), w.z, c.sigma); c.sigma = fmaf(fmaxf(f[4 * j + 3], 0.f), w.w, c.sigma);
+      }
+    }
+    if (E == 4) {                                   // rgb_raw = Wrv v2 + betar[ray]                (fc_rgb)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float x0 = fmaxf(f[4 * j], 0.f), x1 = fmaxf(f[4 * j + 1], 0.f), x2 = fmaxf(f[4 * j + 2], 0.f),
+                    x3 = fmaxf(f[4 * j + 3], 0.f);
+        const float4 w0 = hw[64 + cb * 8 + j], w1 = hw[128 + cb * 8 + j], w2 = hw[192 + cb * 8 + j];
+        rgb0 = fmaf(x0, w0.x, fmaf(x1, w0.y, fmaf(x2, w0.z, fmaf(x3, w0.w, rgb0))));
+        rgb1 = fmaf(x0, w1.x, fmaf(x1, w1.y, fmaf(x2, w1.z, fmaf(x3, w1.w, rgb1))));
+        rgb2 = fmaf(x0, w2.x, fmaf(x1, w2.y, fmaf(x2, w2.z, fmaf(x3, w2.w, rgb2))));
+      }
+    }
+    uint32_t pk[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pk[j] = (E == 2) ? pack_bf16(f[2 * j], f[2 * j + 1]) : cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
+    store_row_block(c.tile, c.r, cb, pk);
+    if (GB) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) bcur[j] = bnxt[j];
+    }
+  }
+  if (E == 1) c.sigma += tail0;
+  if (E == 4 && c.valid)                            // [rgb_raw | sigma_raw]   models/model.py:194
+    reinterpret_cast<float4*>(a.raw)[c.m] = make_float4(rgb0 + tail0, rgb1 + tail1, rgb2 + tail2, c.sigma);
+  fence_proxy_async();
+  tc_fence_before();
+  named_bar_sync(c.bar_id, 128);
+  if (c.elected) {
+    if (c.sv) { bulk_s2g(c.sv + SAVED_GAMMA + (size_t)E * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
+    if (E < 4) mbar_arrive(&c.bars->a_ready[t]);
+    if (t == 0) { FDBG(0, tw1 - tw0); FDBG(1 + E, clock64() - tw1); }
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];   // 128-byte-swizzled images need 1024-byte alignment
+  uint8_t* tiles = smem;
+  uint8_t* ring = smem + OFF_RING;
+  float* heads = reinterpret_cast<float*>(smem + OFF_HEADS);
+  float* stage = reinterpret_cast<float*>(smem + OFF_STAGE);
+  FBars* bars = reinterpret_cast<FBars*>(smem + OFF_BARS);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t num_tiles = (a.M + TILE - 1) / TILE;
+  const int64_t num_pairs = (num_tiles + 1) / 2;
+
+  if (tid == 0) {
+    for (int i = 0; i < FRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
+    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
+    bars->abort_flag = 0;
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
+    mbar_fence_init();
+  }
+  for (int i = tid; i < HEAD_FLOATS; i += NTHREADS) heads[i] = a.pk.w_sigma[i];   // w_sigma | w_rgb | b_dir2 are contiguous
+  if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: stream the 17 K-chunks x 2 N-halves of every tile pair through the ring =====
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+        for (int hc = 0; hc < 2 * FWD_CHUNKS; ++hc, ++g) {
+          const int slot = g % FRING;
+          if (!fwait(&bars->w_empty[slot], ((g / FRING) & 1) ^ 1, bars, a.err)) break;
+          mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
+          bulk_g2s(ring + slot * HALF, a.pk.fwd + (size_t)hc * HALF, HALF, &bars->w_full[slot]);
+        }
+        if (*(volatile int*)&bars->abort_flag) break;
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
+      // descriptors differ only in their 14-bit start-address field (bytes >> 4): precompute the bases, add offsets
+      const uint64_t a_desc0 = smem_desc(smem_u32(tiles), 16, 1024, SWIZZLE_128B);
+      const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
+      uint32_t g = 0, na = 0;
+      bool ok = true;
+      for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+        for (int layer = 0; layer < 5 && ok; ++layer, ++na) {
+          const int nch = layer == 0 ? 1 : 4;
+          for (int c = 0; c < nch && ok; ++c) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h, ++g) {
+              if (!ok) continue;
+              const int slot = g % FRING;
+              const long long m0 = clock64();
+              if (!fwait(&bars->w_full[slot], (g / FRING) & 1, bars, a.err)) { ok = false; continue; }
+              FDBG(8, clock64() - m0);
+              if (c == 0 && h == 0) {
+                const long long m1 = clock64();
+                if (!fwait(&bars->a_ready[0], na & 1, bars, a.err) || !fwait(&bars->a_ready[1], na & 1, bars, a.err)) { ok = false; continue; }
+                FDBG(9, clock64() - m1);
+              }
+              tc_fence_after();
+              const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
+#pragma unroll
+              for (int t = 0; t < 2; ++t) {
+                const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
+                const uint32_t d = tmem + t * 256 + h * 128;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(d, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
+                if (c == nch - 1 && h == 1) umma_commit(&bars->acc_full[t]);
+              }
+              umma_commit(&bars->w_empty[slot]);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warps: thread = one sample row =====
+    const int t = (warp - 2) >> 2;                    // tile of the pair
+    const int q = warp & 3;                           // TMEM lane quarter this warp may read
+    Epi c;
+    c.bars = bars;
+    c.tile = tiles + t * TILE_BYTES;
+    c.heads = heads;
+    c.stage = stage + t * STAGE_FLOATS;
+    c.r = q * 32 + lane;
+    c.bar_id = 1 + t;
+    c.elected = ((warp - 2) & 3) == 0 && lane == 0;
+    c.tacc = tmem + t * 256 + ((uint32_t)(q * 32) << 16);
+    uint32_t na = 0;
+    for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+      const int64_t tile_idx = pr * 2 + t;
+      const int64_t first = tile_idx * TILE;
+      c.m = first + c.r;
+      c.valid = c.m < a.M;
+      c.ray = c.valid ? c.m / a.S : 0;
+      c.pair = c.valid ? (a.pairing == CNRF_PAIRING_REFERENCE ? c.m % a.N : c.ray) : 0;
+      c.ray0 = first < a.M ? first / a.S : 0;
+      const int64_t last = (first + TILE - 1 < a.M ? first + TILE - 1 : a.M - 1);
+      c.nrays = first < a.M ? (int)(last / a.S - c.ray0) + 1 : 0;
+      c.staged = c.nrays <= RMAX;
+      c.slot = c.valid ? (int)(c.ray - c.ray0) : 0;
+      c.sv = (a.saved && tile_idx < num_tiles) ? a.saved + (size_t)tile_idx * SAVED_PER_TILE : nullptr;
+      c.sigma = 0.f;
+      // ---- input image: gamma(x); the bias rows of layer_xyz2 travel to smem meanwhile ----
+      const long long tb0 = clock64();
+      if (c.elected) bulk_wait_read0();               // the previous pair's last image store has finished reading smem
+      named_bar_sync(c.bar_id, 128);
+      stage_rows(c, a.b2);
+      build_input_row(a, c.m, c.valid, c.tile, c.r);
+      fence_proxy_async();
+      named_bar_sync(c.bar_id, 128);
+      if (c.elected) {
+        if (c.sv) { bulk_s2g(c.sv, c.tile, SLAB); bulk_commit(); }
+        mbar_arrive(&bars->a_ready[t]);
+        if (t == 0) { FDBG(6, clock64() - tb0); FDBG(7, 1); }
+      }
+      bool ok = epi_layer<0, false>(a, c, t, na & 1); ++na;
+      if (ok) { ok = c.staged ? epi_layer<1, false>(a, c, t, na & 1) : epi_layer<1, true>(a, c, t, na & 1); ++na; }
+      if (ok) {
+        stage_rows(c, a.bof);                         // every thread of the tile is past its reads of the beta2 rows
+        ok = c.staged ? epi_layer<2, false>(a, c, t, na & 1) : epi_layer<2, true>(a, c, t, na & 1); ++na;
+      }
+      if (ok) { ok = epi_layer<3, true>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = epi_layer<4, false>(a, c, t, na & 1); ++na; }
+      if (!ok) break;
+    }
+    cp_async_wait_all();
+    if (c.elected) bulk_wait0();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+}  // namespace
+
+int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  mlp_fwd_tc_kernel<<<grid, NTHREADS, FWD_SMEM, st>>>(f);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
+extern "C" int cnrf_debug_fwd_times(long long* host_out, int reset) {
+  cudaDeviceSynchronize();
+  int rc = (int)cudaMemcpyFromSymbol(host_out, g_fwd_dbg, 16 * sizeof(long long));
+  if (reset) { long long z[16] = {0}; cudaMemcpyToSymbol(g_fwd_dbg, z, sizeof(z)); }
+  return rc;
+}

@@ -1,0 +1,128 @@
+// Shared declarations of the fused tensor-core chain kernels (mlp_fwd_tc.cu, mlp_tc.cu).
+#pragma once
+#include "common.cuh"
+#include "internal.h"
+#include "tc_common.cuh"
+
+using namespace tc;
+
+namespace tcc {
+constexpr int TILE = 128;                 // rows per tile
+constexpr int SLAB = TILE * 128;          // bytes of one [128 x 64] bf16 slab
+constexpr int TILE_BYTES = 4 * SLAB;      // 64 KB: one [128 x 256] activation tile image
+constexpr int CHUNK = 256 * 128;          // 32 KB: one [256 x 64] weight chunk image
+constexpr int RING = 3;
+constexpr int NTHREADS = 320;
+constexpr int FWD_CHUNKS = 17;            // 1 (layer_xyz1, K=64) + 4 x 4
+constexpr int BWD_CHUNKS = 16;            // 4 x 4 transposed
+constexpr int CONST_BYTES = 4 * 256 * 2;    // bf16 [w_sigma | w_rgb(3)] staged in shared memory
+constexpr int SMEM_BYTES = 2 * TILE_BYTES + RING * CHUNK + CONST_BYTES + 256 /*barriers*/;
+
+// Packed weights (bf16 images + fp32 vectors), rebuilt from the fp32 parameters at every call (they change each step).
+struct Packed {
+  uint8_t* fwd;      // FWD_CHUNKS x 32 KB: [W1|b1], W2h, Woh[1:], Wdf, Wd2   (rows = out feature, cols = in feature)
+  uint8_t* bwd;      // BWD_CHUNKS x 32 KB: Wd2^T, Wdf^T, Woh[1:]^T, W2h^T     (rows = in feature,  cols = out feature)
+  float* w_sigma;    // [256]  fc_out row 0, hidden half
+  float* w_rgb;      // [3][256] fc_rgb, hidden half
+  float* b_dir2;     // [256]
+  float* zeros;      // [256]
+  uint16_t* wsr_bf16; // [4][256] bf16: w_sigma, w_rgb r/g/b (staged into shared memory by the forward kernel)
+};
+constexpr size_t PACKED_BYTES = (size_t)(FWD_CHUNKS + BWD_CHUNKS) * CHUNK + (256 + 768 + 256 + 256) * sizeof(float) + 2048;
+}  // namespace tcc
+using namespace tcc;
+
+// ---- shared pieces of the fused kernels ----------------------------------------------------------------------------------
+struct Bars {
+  uint64_t w_full[RING], w_empty[RING];
+  uint64_t a_ready[2];     // epilogue -> MMA : tile's operand image written (count 1, elected thread after a named barrier)
+  uint64_t acc_full[2];    // MMA -> epilogue : tile's accumulator complete
+  uint32_t tmem_slot;
+  int abort_flag;
+};
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+__device__ __forceinline__ uint32_t cvt_relu_bf16x2(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+// write 32 consecutive columns [cb*32, cb*32+32) of row r of a tile image (8 bf16 per 16-byte chunk)
+__device__ __forceinline__ void store_row_block(uint8_t* tile, int r, int cb, const uint32_t (&pk)[16]) {
+  uint8_t* slab = tile + (cb >> 1) * SLAB + r * 128;
+  const int c0 = (cb & 1) * 4;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    uint4 v = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+    *reinterpret_cast<uint4*>(slab + (((c0 + j) ^ (r & 7)) << 4)) = v;
+  }
+}
+
+// Bounded mbarrier wait (about a second): a protocol bug must end the kernel, never hang the GPU.
+__device__ __forceinline__ bool wait_bar(uint64_t* bar, uint32_t parity, Bars* b, int* err) {
+  if (mbar_try_wait(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (true) {
+    if (mbar_try_wait(bar, parity)) return true;
+    if (*(volatile int*)&b->abort_flag) return false;
+    if (clock64() - t0 > 2000000000LL) {
+      b->abort_flag = 1;
+      if (err) atomicExch(err, 1);
+      return false;
+    }
+  }
+}
+
+constexpr size_t SAVED_GAMMA = SLAB;                          // gamma(x) slab (K = 64)
+constexpr size_t SAVED_PER_TILE = SAVED_GAMMA + 5 * (size_t)TILE_BYTES;   // + h1, h2, feat, v1, v2 images
+
+struct FwdArgs {
+  int64_t N, M; int S, pairing, dx;
+  const float* pts; const float* x_xyz; int64_t ld_xyz;
+  const float* freqs; int L; int inc;
+  const float *b2, *bof, *bos, *br, *bd;   // per-ray bias tables: [N,256], [N,256] (fc_out feat), [N] (sigma), [N,3], [N,256]
+  Packed pk;
+  float* raw;
+  uint8_t* saved;      // nullptr: inference
+  int* err;
+};
+
+// gamma(x) row -> 64 bf16 (col 63 = 1 carries layer_xyz1's bias), written to slab 0 of the tile
+__device__ __forceinline__ void put_bf16(uint8_t* row, int r, int i, float v) {
+  *reinterpret_cast<__nv_bfloat16*>(row + ((((i >> 3) ^ (r & 7)) << 4) | ((i & 7) << 1))) = __float2bfloat16(v);
+}
+__device__ __forceinline__ void build_input_row(const FwdArgs& a, int64_t m, bool valid, uint8_t* tile, int r) {
+  uint8_t* row = tile + r * 128;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(row + (j << 4)) = make_uint4(0u, 0u, 0u, 0u);
+  if (!valid) return;
+  if (a.pts) {
+    float x[3] = {a.pts[m * 3], a.pts[m * 3 + 1], a.pts[m * 3 + 2]};
+    int o = 0;
+    if (a.inc) { put_bf16(row, r, 0, x[0]); put_bf16(row, r, 1, x[1]); put_bf16(row, r, 2, x[2]); o = 3; }
+    float s[3], c[3], fprev = 0.f;
+    for (int k = 0; k < a.L; ++k) {
+      float f = a.freqs[k];
+      if (k > 0 && f == 2.0f * fprev) {   // octave step: angle doubling; the error doubles per octave (<= 2^9 * 1e-7),
+#pragma unroll                            // far below the 4e-3 rounding of the bf16 operand it feeds
+        for (int d = 0; d < 3; ++d) { float s2 = 2.f * s[d] * c[d]; c[d] = 1.f - 2.f * s[d] * s[d]; s[d] = s2; }
+      } else {
+#pragma unroll
+        for (int d = 0; d < 3; ++d) sincosf(x[d] * f, &s[d], &c[d]);
+      }
+      fprev = f;
+#pragma unroll
+      for (int d = 0; d < 3; ++d) { put_bf16(row, r, o + 6 * k + d, s[d]); put_bf16(row, r, o + 6 * k + 3 + d, c[d]); }
+    }
+  } else {
+    for (int i = 0; i < a.dx; ++i) put_bf16(row, r, i, a.x_xyz[m * a.ld_xyz + i]);
+  }
+  put_bf16(row, r, 63, 1.0f);
+}
+
+
+// mlp_fwd_tc.cu
+int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st);

@@ -32,3 +32,15 @@ e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / reps
 fl = N * S * FS * (1 if mode == "fwd" else 3)
 print(f"{prec} {mode} N={N} S={S}: {ms:.3f} ms  {fl / ms / 1e9:.1f} TFLOP/s  tc_err={_lib.load().cnrf_debug_tc_error()}")
+try:
+    import numpy as np, ctypes
+    lib = _lib.load()
+    buf = np.zeros(16, dtype=np.int64)
+    lib.cnrf_debug_fwd_times(ctypes.c_void_p(buf.ctypes.data), 1)
+    step(); torch.cuda.synchronize()
+    lib.cnrf_debug_fwd_times(ctypes.c_void_p(buf.ctypes.data), 1)
+    n = max(1, int(buf[7]))
+    print("block0/tile0 per pair [clk]: wait_acc(total of 5) %d | epi L0..L4 %s | build %d | MMA-warp waits: weights %d, a_ready %d | pairs %d" %
+          (buf[0] // n, [int(buf[1 + i] // n) for i in range(5)], buf[6] // n, buf[8] // n, buf[9] // n, n))
+except Exception as e:
+    print("no fwd debug times:", e)
