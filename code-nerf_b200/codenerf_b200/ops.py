@@ -323,6 +323,8 @@ class _Field(torch.autograd.Function):
 def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code, dim_xyz, dim_dir,
                    pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_BF16):
     """params: the 18 tensors (weight, bias per layer) in _lib.LAYER_NAMES order."""
+    if precision == _lib.PRECISION_BF16 and (pts.requires_grad or rd.requires_grad) and torch.is_grad_enabled():
+        precision = _lib.PRECISION_FP32   # ray / point gradients (camera-pose optimisation, eval.py:129-168) run in fp32
     cfg = (hidden, code, dim_xyz, dim_dir, pairing, precision)
     return _Field.apply(cfg, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, *params)
 

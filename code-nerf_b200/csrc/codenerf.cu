@@ -179,7 +179,8 @@ int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 1));     // model.py:174
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 1));     // :175
   b.add(mk_lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 1));  // :177
-  b.add(mk_lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0));
+  // the tensor-core chain applies the view-direction half of layer_dir1 as 32 extra input columns instead of a bias table
+  if (!d.tc) b.add(mk_lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0));
   RUN(b.flush(d.tc, st));
   b.add(mk_lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0));
   if (split_bo) {   // tensor-core chain: 16-byte aligned feature rows + a separate sigma column
@@ -216,13 +217,13 @@ int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codener
   b.add(mk_dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp_s2, C, as2, C, 0));
   b.add(mk_wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C));
   b.add(mk_dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp_s1, C, as1, C, 0));
-  b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
+  if (d.tc && g_x_dir) return CNRF_E_UNSUPPORTED;   // ray-direction gradients (pose optimisation) run in the fp32 mode
+  if (!d.tc) b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
   if (g_x_dir) b.add(mk_dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0));
   if (d.tc) {
     b.add(mk_colsum(ones, dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB]));
     b.add(mk_colsum(ones, dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT]));
     b.add(mk_colsum(ones, dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2]));
-    b.add(mk_colsum(ones, dt.bd, H, d.N, H, g->bias[CNRF_L_DIR1]));
   }
   RUN(b.flush(d.tc, st));
   if (!d.tc) {
@@ -355,6 +356,7 @@ struct TcChainArgs {
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;   // points to encode
   const float *b2, *bo, *br, *bd;             // per-ray bias tables [N,256],[N,257],[N,3],[N,256]
   const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
+  const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
 };
 int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
                       cudaStream_t st);
@@ -390,7 +392,7 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
     return chain_fwd_f32(d, p, in.x_xyz, in.ld_xyz, t, sv, raw, st);
   }
   // bf16 tensor-core chain: needs H = C = 256
-  if (d.H != 256 || d.C != 256 || d.dx > 64 || d.dd > 64) return CNRF_E_UNSUPPORTED;
+  if (d.H != 256 || d.C != 256 || d.dx > 63 || d.dd > 31) return CNRF_E_UNSUPPORTED;
   float *as1, *as2, *at;
   char* tc_saved = nullptr; size_t tc_saved_bytes = 0;
   if (s->keep) {
@@ -405,7 +407,7 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   }
   RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, t, true, st));
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, t.b2, t.bo, t.br, t.bd, t.bof, t.bos};
+                in.inc_xyz, t.b2, t.bo, t.br, t.bd, t.bof, t.bos, in.x_dir, in.ld_dir};
   return cnrf_tc_chain_fwd(a, raw, tc_saved, tc_saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
 
@@ -432,12 +434,12 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
     return per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, sv.as1, sv.as2, sv.at, dt,
                        tmp, g_z_s, g_z_t, g_x_dir, st);
   }
-  if (d.H != 256 || d.C != 256 || d.dx > 64 || d.dd > 64) return CNRF_E_UNSUPPORTED;
+  if (d.H != 256 || d.C != 256 || d.dx > 63 || d.dd > 31) return CNRF_E_UNSUPPORTED;
   Arena sa(const_cast<void*>(saved), saved_bytes);
   float* as1 = sa.take(d.N * d.C); float* as2 = sa.take(d.N * d.C); float* at = sa.take(d.N * d.C);
   if (!sa.ok) return CNRF_E_WORKSPACE;
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+                in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, in.x_dir, in.ld_dir};
   RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, dt.bd, g_x_xyz,
                         w.base + w.off, w.cap - w.off, st));
   return per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, dt, tmp, g_z_s,

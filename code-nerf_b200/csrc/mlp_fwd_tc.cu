@@ -79,7 +79,7 @@ __device__ __forceinline__ void stage_rows(const Epi& c, const float* table) {
 }
 
 // One layer's epilogue for one tile.  E: 0 layer_xyz1, 1 layer_xyz2 (+ sigma head), 2 fc_out features (no ReLU),
-// 3 layer_dir1, 4 layer_dir2 (+ rgb head).  GB: bias row comes from global memory (register double buffer) instead of
+// 3 layer_dir1 (its bias and view-direction half arrive through the MMA), 4 layer_dir2 (+ rgb head).  GB: bias row comes from global memory (register double buffer) instead of
 // shared memory.
 template <int E, bool GB>
 __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint32_t parity) {
@@ -87,7 +87,6 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   const float4* sb = nullptr;
   if (E == 1) { if (GB) gb = reinterpret_cast<const float4*>(a.b2 + c.ray * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
   if (E == 2) { if (GB) gb = reinterpret_cast<const float4*>(a.bof + c.ray * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
-  if (E == 3) gb = reinterpret_cast<const float4*>(a.bd + c.pair * 256);
   if (E == 4) sb = reinterpret_cast<const float4*>(c.heads + 1024);
   float4 bcur[8], bnxt[8];
   float tail0 = 0.f, tail1 = 0.f, tail2 = 0.f;
@@ -114,7 +113,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
 #pragma unroll
       for (int j = 0; j < 8; ++j) bnxt[j] = __ldg(gb + (cb + 1) * 8 + j);
     }
-    if (!GB && E != 0) {
+    if (!GB && E != 0 && E != 3) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) bcur[j] = sb[cb * 8 + j];
     }
@@ -122,7 +121,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
     float f[32];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      if (E == 0) {
+      if (E == 0 || E == 3) {
         f[4 * j] = __uint_as_float(v[4 * j]); f[4 * j + 1] = __uint_as_float(v[4 * j + 1]);
         f[4 * j + 2] = __uint_as_float(v[4 * j + 2]); f[4 * j + 3] = __uint_as_float(v[4 * j + 3]);
       } else {
@@ -202,11 +201,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     if (lane == 0) {
       uint32_t g = 0;
       for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
-        for (int hc = 0; hc < 2 * FWD_CHUNKS; ++hc, ++g) {
+        // 37 images per pair: K-chunks 0..12 (layers xyz1, xyz2, fc_out, dir1) as N-halves, then layer_dir1's extension
+        // (this pair's [gamma(d) | 1] slab, then the two halves of [Wdv | b_dir1]), then K-chunks 13..16 (layer_dir2)
+        for (int step = 0; step < 37; ++step, ++g) {
           const int slot = g % FRING;
           if (!fwait(&bars->w_empty[slot], ((g / FRING) & 1) ^ 1, bars, a.err)) break;
+          const uint8_t* src = step < 26 ? a.pk.fwd + (size_t)step * HALF
+                             : step == 26 ? a.ext + (size_t)pr * SLAB
+                             : step < 29 ? a.pk.fwd + (size_t)EXT_CHUNK * CHUNK + (size_t)(step - 27) * HALF
+                                         : a.pk.fwd + (size_t)(step - 3) * HALF;
           mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
-          bulk_g2s(ring + slot * HALF, a.pk.fwd + (size_t)hc * HALF, HALF, &bars->w_full[slot]);
+          bulk_g2s(ring + slot * HALF, src, HALF, &bars->w_full[slot]);
         }
         if (*(volatile int*)&bars->abort_flag) break;
       }
@@ -244,10 +249,32 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
                 const uint32_t d = tmem + t * 256 + h * 128;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_bf16(d, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
-                if (c == nch - 1 && h == 1) umma_commit(&bars->acc_full[t]);
+                if (c == nch - 1 && h == 1 && layer != 3) umma_commit(&bars->acc_full[t]);
               }
               umma_commit(&bars->w_empty[slot]);
             }
+          }
+          if (layer == 3 && ok) {          // += [gamma(d_pair) | 1] [Wdv | b_dir1]^T : K = 32 columns per tile of the shared slab
+            const int slot_x = g % FRING;
+            if (!fwait(&bars->w_full[slot_x], (g / FRING) & 1, bars, a.err)) { ok = false; break; }
+            ++g;
+            const uint64_t xd = b_desc0 + (uint64_t)((slot_x * HALF) >> 4);
+#pragma unroll
+            for (int h = 0; h < 2; ++h, ++g) {
+              if (!ok) continue;
+              const int slot = g % FRING;
+              if (!fwait(&bars->w_full[slot], (g / FRING) & 1, bars, a.err)) { ok = false; continue; }
+              tc_fence_after();
+              const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
+#pragma unroll
+              for (int t = 0; t < 2; ++t) {
+#pragma unroll
+                for (int k = 0; k < 2; ++k) umma_bf16(tmem + t * 256 + h * 128, xd + 2 * (2 * t + k), bd + 2 * k, idesc, 1);
+                if (h == 1) umma_commit(&bars->acc_full[t]);
+              }
+              umma_commit(&bars->w_empty[slot]);
+            }
+            if (ok) umma_commit(&bars->w_empty[slot_x]);
           }
         }
       }
@@ -299,7 +326,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
         stage_rows(c, a.bof);                         // every thread of the tile is past its reads of the beta2 rows
         ok = c.staged ? epi_layer<2, false>(a, c, t, na & 1) : epi_layer<2, true>(a, c, t, na & 1); ++na;
       }
-      if (ok) { ok = epi_layer<3, true>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = epi_layer<3, false>(a, c, t, na & 1); ++na; }
       if (ok) { ok = epi_layer<4, false>(a, c, t, na & 1); ++na; }
       if (!ok) break;
     }

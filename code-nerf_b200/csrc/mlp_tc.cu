@@ -24,6 +24,8 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, int dx, int dd, Pack
       base = pk.fwd + (size_t)ch * CHUNK;
       if (ch == 0) {                          // layer_xyz1 [256, dx] with the bias in column 63 (the input's ones column)
         v = c < dx ? p.weight[CNRF_L_XYZ1][r * dx + c] : (c == 63 ? p.bias[CNRF_L_XYZ1][r] : 0.f);
+      } else if (ch == EXT_CHUNK) {           // view-direction half of layer_dir1 + its bias (the extension's ones column)
+        v = c < dd ? p.weight[CNRF_L_DIR1][r * (256 + dd) + 256 + c] : (c == dd ? p.bias[CNRF_L_DIR1][r] : 0.f);
       } else {
         int l = (ch - 1) >> 2, k = ((ch - 1) & 3) * 64 + c;   // l: 0 W2h, 1 Woh[1:], 2 Wdf, 3 Wd2
         if (l == 0) v = p.weight[CNRF_L_XYZ2][r * 512 + k];
@@ -66,6 +68,7 @@ struct TcChainArgs {   // mirrors the declaration in codenerf.cu
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;
   const float *b2, *bo, *br, *bd;
   const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
+  const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
 };
 
 static inline size_t up1k(size_t b) { return (b + 1023) & ~size_t(1023); }
@@ -94,21 +97,61 @@ static int* tc_error_ptr() {
   return p;
 }
 
-size_t cnrf_tc_saved_bytes(int64_t M) { return (size_t)((M + TILE - 1) / TILE) * SAVED_PER_TILE; }
+static inline int64_t tiles_of(int64_t M) { return (M + TILE - 1) / TILE; }
+static inline int64_t pairs_of(int64_t M) { return (tiles_of(M) + 1) / 2; }
+// per tile: the activation images; then per tile pair: the view-direction extension slab
+size_t cnrf_tc_saved_bytes(int64_t M) { return (size_t)tiles_of(M) * SAVED_PER_TILE + (size_t)pairs_of(M) * SLAB; }
+
+// Extension slab of every tile pair (the K = 32 extra input columns of layer_dir1): row r, columns 32t .. 32t+31 =
+// [gamma(d^ of the ray paired with sample row r of tile t) | 1 | 0].  The pairing reproduces nerf/__init__.py:127
+// (flat row m -> ray m mod N) unless CNRF_PAIRING_CORRECT (m / S).
+__global__ void build_ext_kernel(const float* __restrict__ x_dir, int64_t ld, int dd, int64_t N, int64_t M, int S,
+                                 int pairing, uint8_t* __restrict__ ext, int64_t num_pairs) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= num_pairs * 256) return;
+  const int r = (int)(i & 127), t = (int)((i >> 7) & 1);
+  const int64_t pr = i >> 8;
+  const int64_t m = (pr * 2 + t) * TILE + r;
+  uint32_t w[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) w[j] = 0u;
+  if (m < M) {
+    const float* src = x_dir + (pairing == CNRF_PAIRING_REFERENCE ? m % N : m / S) * ld;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const int c0 = 2 * j, c1 = 2 * j + 1;
+      const float lo = c0 < dd ? __ldg(src + c0) : (c0 == dd ? 1.0f : 0.0f);
+      const float hi = c1 < dd ? __ldg(src + c1) : (c1 == dd ? 1.0f : 0.0f);
+      w[j] = pack_bf16(lo, hi);
+    }
+  }
+  uint8_t* row = ext + (size_t)pr * SLAB + r * 128;
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    *reinterpret_cast<uint4*>(row + (((4 * t + j) ^ (r & 7)) << 4)) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+}
 
 int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
                       cudaStream_t st) {
   uint8_t* w = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(ws)));
-  if (w + PACKED_BYTES > reinterpret_cast<uint8_t*>(ws) + ws_bytes) return CNRF_E_WORKSPACE;
+  if (w + PACKED_BYTES + 1024 + (size_t)pairs_of(a.M) * SLAB > reinterpret_cast<uint8_t*>(ws) + ws_bytes) return CNRF_E_WORKSPACE;
   if (saved && saved_bytes < cnrf_tc_saved_bytes(a.M) + 1024) return CNRF_E_WORKSPACE;
+  if (a.dd > 31) return CNRF_E_UNSUPPORTED;
   Packed pk = carve_packed(w);
+  uint8_t* saved_al = saved ? reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(saved))) : nullptr;
+  // the extension slabs live with the saved images when a backward follows (the weight-gradient kernel reads them)
+  uint8_t* ext = saved_al ? saved_al + (size_t)tiles_of(a.M) * SAVED_PER_TILE
+                          : reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
+  build_ext_kernel<<<grid_for(pairs_of(a.M) * 256, 256), 256, 0, st>>>(a.x_dir, a.ld_dir, a.dd, a.N, a.M, a.S, a.pairing,
+                                                                      ext, pairs_of(a.M));
+  CNRF_LAUNCH_CHECK();
   pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
   CNRF_LAUNCH_CHECK();
   FwdArgs f;
   f.N = a.N; f.M = a.M; f.S = a.S; f.pairing = a.pairing; f.dx = a.dx;
   f.pts = a.pts; f.x_xyz = a.x_xyz; f.ld_xyz = a.ld_xyz; f.freqs = a.freqs_xyz; f.L = a.L_xyz; f.inc = a.inc_xyz;
-  f.b2 = a.b2; f.bof = a.bof; f.bos = a.bos; f.br = a.br; f.bd = a.bd; f.pk = pk; f.raw = raw;
-  f.saved = saved ? reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(saved))) : nullptr;
+  f.b2 = a.b2; f.bof = a.bof; f.bos = a.bos; f.br = a.br; f.ext = ext; f.pk = pk; f.raw = raw;
+  f.saved = saved_al;
   f.err = tc_error_ptr();
   const int64_t pairs = ((a.M + TILE - 1) / TILE + 1) / 2;
   const int grid = (int)(pairs < sm_count() ? pairs : sm_count());
@@ -317,12 +360,15 @@ constexpr int DW_STAGE = 8 * 8192;          // 64 rows x (256 + 256) bf16
 constexpr int DW_RING = 3;
 constexpr int DW_SMEM = DW_RING * DW_STAGE + 256;
 
-struct DwJob { int dy_img; int x_img; /* -1: gamma slab */ int n_cols; float* out; int ld; int k_valid; float* bias_out; };
+struct DwJob { int dy_img; int x_img; /* -1: gamma slab, -2: view-direction extension slab of the tile pair */ int n_cols;
+               float* out; int ld; int k_valid; float* bias_out; int bias_col; };
 struct DwArgs {
   int64_t M;
   const uint8_t* saved;
   const uint8_t* dy;
-  DwJob job[5];
+  const uint8_t* ext;
+  DwJob job[6];
+  int first[7];          // first CTA of each job (1-D grid)
   int* err;
 };
 
@@ -342,7 +388,11 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
   extern __shared__ __align__(1024) uint8_t smem[];
   DwBars* bars = reinterpret_cast<DwBars*>(smem + DW_RING * DW_STAGE);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const DwJob job = a.job[blockIdx.y];
+  int ji = 0;
+  while (ji < 5 && (int)blockIdx.x >= a.first[ji + 1]) ++ji;
+  const DwJob job = a.job[ji];
+  const int bx = blockIdx.x - a.first[ji], nb = a.first[ji + 1] - a.first[ji];
+  const bool is_ext = job.x_img == -2;
   const int nslabB = job.x_img < 0 ? 1 : 4;
   const int64_t num_tiles = (a.M + TILE - 1) / TILE;
   const int64_t num_halves = num_tiles * 2;
@@ -358,19 +408,20 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = bars->tmem_slot;
-  const bool has_work = (int64_t)blockIdx.x < num_halves;
+  const bool has_work = (int64_t)bx < num_halves;
 
   if (warp == 0) {
     if (lane == 0) {
       uint32_t g = 0;
-      for (int64_t h = blockIdx.x; h < num_halves; h += gridDim.x, ++g) {
+      for (int64_t h = bx; h < num_halves; h += nb, ++g) {
         const int slot = g % DW_RING;
         if (!dw_wait(&bars->empty[slot], ((g / DW_RING) & 1) ^ 1, bars, a.err)) goto done;
         const int64_t tile = h >> 1;
         const int half = (int)(h & 1);
         const uint8_t* src_a = a.dy + (size_t)tile * DY_PER_TILE + (size_t)job.dy_img * TILE_BYTES + half * 8192;
-        const uint8_t* src_b = a.saved + (size_t)tile * SAVED_PER_TILE +
-                               (job.x_img < 0 ? 0 : SAVED_GAMMA + (size_t)job.x_img * TILE_BYTES) + half * 8192;
+        const uint8_t* src_b = is_ext ? a.ext + (size_t)(tile >> 1) * SLAB + half * 8192
+                                      : a.saved + (size_t)tile * SAVED_PER_TILE +
+                                            (job.x_img < 0 ? 0 : SAVED_GAMMA + (size_t)job.x_img * TILE_BYTES) + half * 8192;
         uint8_t* dst = smem + slot * DW_STAGE;
         mbar_arrive_expect_tx(&bars->full[slot], (4 + nslabB) * 8192);
         for (int s = 0; s < 4; ++s) bulk_g2s(dst + s * 8192, src_a + (size_t)s * SLAB, 8192, &bars->full[slot]);
@@ -381,16 +432,22 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
     if (lane == 0 && has_work) {
       const uint32_t idesc = idesc_bf16(128, job.n_cols, 1, 1);
       uint32_t g = 0;
-      for (int64_t h = blockIdx.x; h < num_halves; h += gridDim.x, ++g) {
+      uint32_t seen = 0;               // extension job: tile parities whose accumulator pair has been started
+      for (int64_t h = bx; h < num_halves; h += nb, ++g) {
         const int slot = g % DW_RING;
         if (!dw_wait(&bars->full[slot], (g / DW_RING) & 1, bars, a.err)) goto done;
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + slot * DW_STAGE), sb = sa + 4 * 8192;
+        // the extension slab serves both tiles of a pair (columns 32 t ..): one accumulator pair per tile parity
+        const uint32_t par = is_ext ? (uint32_t)((h >> 1) & 1) : 0u;
+        const bool fresh = is_ext ? ((seen >> par) & 1u) == 0u : g == 0;
+        seen |= 1u << par;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const uint64_t bd = smem_desc(sb + k * 2048, 8192, 1024, SWIZZLE_128B);
-          umma_bf16(tmem, smem_desc(sa + k * 2048, 8192, 1024, SWIZZLE_128B), bd, idesc, (g | k) != 0);
-          umma_bf16(tmem + 256, smem_desc(sa + 2 * 8192 + k * 2048, 8192, 1024, SWIZZLE_128B), bd, idesc, (g | k) != 0);
+          umma_bf16(tmem + par * 64, smem_desc(sa + k * 2048, 8192, 1024, SWIZZLE_128B), bd, idesc, !(fresh && k == 0));
+          umma_bf16(tmem + 256 + par * 64, smem_desc(sa + 2 * 8192 + k * 2048, 8192, 1024, SWIZZLE_128B), bd, idesc,
+                    !(fresh && k == 0));
         }
         umma_commit(&bars->empty[slot]);
       }
@@ -400,8 +457,24 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
     const int q = warp & 3;
     if (dw_wait(&bars->acc_full, 0, bars, a.err)) {
       tc_fence_after();
+      uint32_t seen = 0;
+      if (is_ext) for (int64_t h = bx; h < num_halves; h += nb) seen |= 1u << ((h >> 1) & 1);
       for (int mh = 0; mh < 2; ++mh) {
         const int n = mh * 128 + q * 32 + lane;
+        if (is_ext) {                  // tile parity p: columns 32 p .. 32 p + 31 of its own accumulator pair
+          for (int p = 0; p < 2; ++p) {
+            if (!((seen >> p) & 1u)) continue;
+            uint32_t v[32];
+            tmem_ld32(tmem + mh * 256 + ((uint32_t)(q * 32) << 16) + p * 64 + p * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int k = 0; k < 32; ++k) {
+              if (k < job.k_valid) atomicAdd(job.out + (size_t)n * job.ld + k, __uint_as_float(v[k]));
+              else if (k == job.bias_col) atomicAdd(job.bias_out + n, __uint_as_float(v[k]));
+            }
+          }
+          continue;
+        }
         for (int c0 = 0; c0 < job.n_cols; c0 += 32) {
           uint32_t v[32];
           tmem_ld32(tmem + mh * 256 + ((uint32_t)(q * 32) << 16) + c0, v);
@@ -410,7 +483,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
           for (int j = 0; j < 32; ++j) {
             const int k = c0 + j;
             if (k < job.k_valid) atomicAdd(job.out + (size_t)n * job.ld + k, __uint_as_float(v[j]));
-            else if (job.bias_out && k == 63) atomicAdd(job.bias_out + n, __uint_as_float(v[j]));
+            else if (job.bias_out && k == job.bias_col) atomicAdd(job.bias_out + n, __uint_as_float(v[j]));
           }
         }
       }
@@ -494,7 +567,7 @@ __global__ void img_weighted_colsum_kernel(const uint8_t* base, size_t per_tile,
 
 size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
   (void)N;
-  size_t b = PACKED_BYTES + 4096;
+  size_t b = PACKED_BYTES + 4096 + (size_t)pairs_of(M) * SLAB;
   if (backward) b += (size_t)((M + TILE - 1) / TILE) * DY_PER_TILE;
   return b;
 }
@@ -531,15 +604,27 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
 
   DwArgs d;
   d.M = a.M; d.saved = sv; d.dy = dy; d.err = tc_error_ptr();
-  d.job[0] = {0, 3, 256, g->weight[CNRF_L_DIR2], 256, 256, nullptr};                       // d v2p^T v1
-  d.job[1] = {1, 2, 256, g->weight[CNRF_L_DIR1], 256 + a.dd, 256, nullptr};                // d v1p^T feat
-  d.job[2] = {2, 1, 256, g->weight[CNRF_L_FC_OUT] + 512, 512, 256, nullptr};               // d feat^T h2   (rows 1..256)
-  d.job[3] = {3, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nullptr};                       // d h2p^T h1
-  d.job[4] = {4, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1]};        // d h1p^T [gamma | 1]
-  const int64_t halves = tiles * 2;
-  const int per_job = (int)(halves < (sm_count() / 5) ? halves : (sm_count() / 5));
-  mlp_dw_tc_kernel<<<dim3(per_job, 5), DW_THREADS, DW_SMEM, st>>>(d);
-  CNRF_LAUNCH_CHECK();
+  d.ext = sv + (size_t)tiles * SAVED_PER_TILE;
+  d.job[0] = {0, 3, 256, g->weight[CNRF_L_DIR2], 256, 256, nullptr, -1};                       // d v2p^T v1
+  d.job[1] = {1, 2, 256, g->weight[CNRF_L_DIR1], 256 + a.dd, 256, nullptr, -1};                // d v1p^T feat
+  d.job[2] = {2, 1, 256, g->weight[CNRF_L_FC_OUT] + 512, 512, 256, nullptr, -1};               // d feat^T h2   (rows 1..256)
+  d.job[3] = {3, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nullptr, -1};                       // d h2p^T h1
+  d.job[4] = {4, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1], 63};        // d h1p^T [gamma | 1]
+  d.job[5] = {1, -2, 64, g->weight[CNRF_L_DIR1] + 256, 256 + a.dd, a.dd, g->bias[CNRF_L_DIR1], a.dd};   // d v1p^T [gamma(d) | 1]
+  {   // one CTA per SM: the four 256-wide jobs share most of them, the two 64-wide jobs get ~1/15 each
+    const int64_t halves = tiles * 2;
+    const int light = sm_count() / 15 > 0 ? sm_count() / 15 : 1;
+    const int heavy = (sm_count() - 2 * light) / 4 > 0 ? (sm_count() - 2 * light) / 4 : 1;
+    int at = 0;
+    for (int j = 0; j < 6; ++j) {
+      d.first[j] = at;
+      const int want = j < 4 ? heavy : light;
+      at += (int)(halves < want ? halves : want);
+    }
+    d.first[6] = at;
+    mlp_dw_tc_kernel<<<at, DW_THREADS, DW_SMEM, st>>>(d);
+    CNRF_LAUNCH_CHECK();
+  }
 
   const unsigned cs_grid = (unsigned)((a.M + CSUM_ROWS - 1) / CSUM_ROWS);
   img_weighted_colsum_kernel<1><<<cs_grid, 128, 0, st>>>(dy, DY_PER_TILE, 0, a.M, nullptr, 0, g->bias[CNRF_L_DIR2], 0);
@@ -555,11 +640,7 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   CNRF_LAUNCH_CHECK();
   img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 2 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_bo + 1, 257);
   CNRF_LAUNCH_CHECK();
-  if (a.pairing == CNRF_PAIRING_REFERENCE)
-    img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 1 * (size_t)TILE_BYTES, a.N, 1, a.S, a.N, d_bd, 256);
-  else
-    img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 1 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_bd, 256);
-  CNRF_LAUNCH_CHECK();
+  (void)d_bd;   // layer_dir1's view-direction half and bias get their gradients from the extension job above
   if ((rc = cnrf_strided_rowsum(g_raw, 4, a.N, a.S, a.S, 1, 3, d_br, 3, st))) return rc;
   if ((rc = cnrf_strided_rowsum(g_raw + 3, 4, a.N, a.S, a.S, 1, 1, d_bo, 257, st))) return rc;
   return CNRF_OK;

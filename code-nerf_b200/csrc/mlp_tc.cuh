@@ -13,7 +13,8 @@ constexpr int TILE_BYTES = 4 * SLAB;      // 64 KB: one [128 x 256] activation t
 constexpr int CHUNK = 256 * 128;          // 32 KB: one [256 x 64] weight chunk image
 constexpr int RING = 3;
 constexpr int NTHREADS = 320;
-constexpr int FWD_CHUNKS = 17;            // 1 (layer_xyz1, K=64) + 4 x 4
+constexpr int FWD_CHUNKS = 18;            // 1 (layer_xyz1, K=64) + 4 x 4 + 1 (view-direction extension of layer_dir1)
+constexpr int EXT_CHUNK = 17;             // [Wdv | b_dir1 | 0]: K = dim_dir + 1 <= 32 columns of a [256 x 64] image
 constexpr int BWD_CHUNKS = 16;            // 4 x 4 transposed
 constexpr int CONST_BYTES = 4 * 256 * 2;    // bf16 [w_sigma | w_rgb(3)] staged in shared memory
 constexpr int SMEM_BYTES = 2 * TILE_BYTES + RING * CHUNK + CONST_BYTES + 256 /*barriers*/;
@@ -83,7 +84,8 @@ struct FwdArgs {
   int64_t N, M; int S, pairing, dx;
   const float* pts; const float* x_xyz; int64_t ld_xyz;
   const float* freqs; int L; int inc;
-  const float *b2, *bof, *bos, *br, *bd;   // per-ray bias tables: [N,256], [N,256] (fc_out feat), [N] (sigma), [N,3], [N,256]
+  const float *b2, *bof, *bos, *br;        // per-ray bias tables: [N,256], [N,256] (fc_out feat), [N] (sigma), [N,3]
+  const uint8_t* ext;                      // per tile PAIR: [128 x 64] bf16 slab, columns 32t..32t+31 = [gamma(d_pair) | 1 | 0] of tile t
   Packed pk;
   float* raw;
   uint8_t* saved;      // nullptr: inference
