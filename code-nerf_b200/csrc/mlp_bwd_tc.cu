@@ -1,0 +1,235 @@
+// Backward-data chain of the fused bf16 tensor-core field.  Per tile pair: stage "-1" on CUDA cores
+// (d v2 = g_rgb Wrv, masked), then four tensor-core stages
+//   d v1 = (d v2p Wd2) * [v1>0],  d feat = d v1p Wdf,  d h2 = (d feat Woh' + d sigma w_sigma) * [h2>0],  d h1 = (d h2p W2h) * [h1>0]
+// with W^T streamed as B operands (16 KB N-half images through a 5-slot TMA ring, as in the forward).  Every masked
+// gradient tile is TMA-stored as a bf16 image (same layout as the forward's activation images) for the weight-gradient
+// kernel.  The ReLU masks are the 1-bit sign words the forward saved (32 B per row and layer), loaded before the
+// accumulator wait; the epilogue is specialised per stage at compile time and fully unrolled.
+// Geometry, warp roles and barrier protocol are those of mlp_fwd_tc.cu.
+#include "mlp_tc.cuh"
+
+namespace {
+constexpr int HALF = 128 * 128;             // bytes of one [128 x 64] bf16 weight image
+constexpr int BRING = 5;
+constexpr int HEAD_FLOATS = 256 + 768;      // w_sigma | w_rgb[3]   (contiguous in Packed)
+constexpr int OFF_RING = 2 * TILE_BYTES;
+constexpr int OFF_HEADS = OFF_RING + BRING * HALF;
+constexpr int OFF_BARS = OFF_HEADS + HEAD_FLOATS * 4;
+constexpr int BWD_SMEM = OFF_BARS + 256;
+
+struct BBars {
+  uint64_t w_full[BRING], w_empty[BRING];
+  uint64_t a_ready[2], acc_full[2];
+  uint32_t tmem_slot;
+  int abort_flag;
+};
+
+__device__ __forceinline__ bool bwait(uint64_t* bar, uint32_t parity, BBars* b, int* err) {
+  if (mbar_try_wait(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (true) {
+    if (mbar_try_wait(bar, parity)) return true;
+    if (*(volatile int*)&b->abort_flag) return false;
+    if (clock64() - t0 > 2000000000LL) {
+      b->abort_flag = 1;
+      if (err) atomicExch(err, 1);
+      return false;
+    }
+  }
+}
+
+struct BEpi {
+  BBars* bars;
+  uint8_t* tile;
+  const float* heads;      // smem: w_sigma[256] | w_rgb[3][256]
+  uint32_t tacc;
+  int r, bar_id;
+  bool elected, tile_ok;
+  const uint8_t* masks;    // this tile's sign words: [4][128 rows][8]
+  uint8_t* dy;
+  float4 g;                // upstream gradient of this row's (r, g, b, sigma)
+};
+
+// S = -1: d v2p from g_rgb on CUDA cores; S = 0..3: the tensor-core stages.  Output image index = S + 1.
+template <int S>
+__device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint32_t parity) {
+  constexpr int MK = S == -1 ? 3 : S == 0 ? 2 : S == 2 ? 1 : S == 3 ? 0 : -1;   // v2, v1, -, h2, h1
+  uint32_t mw[8];
+  if (MK >= 0) {
+    const uint4* mp = reinterpret_cast<const uint4*>(c.masks + (size_t)MK * MASK_BYTES + c.r * 32);
+    const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
+    mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
+  }
+  if (S >= 0) {
+    if (!bwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
+    tc_fence_after();
+  }
+  if (c.elected) bulk_wait_read0();                 // the previous image store no longer reads this tile
+  named_bar_sync(c.bar_id, 128);
+  const float4* hw = reinterpret_cast<const float4*>(c.heads);
+#pragma unroll
+  for (int cb = 0; cb < 8; ++cb) {
+    float f[32];
+    if (S >= 0) {
+      uint32_t v[32];
+      tmem_ld32(c.tacc + cb * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 w0 = hw[64 + cb * 8 + j], w1 = hw[128 + cb * 8 + j], w2 = hw[192 + cb * 8 + j];
+        f[4 * j] = fmaf(c.g.x, w0.x, fmaf(c.g.y, w1.x, c.g.z * w2.x));
+        f[4 * j + 1] = fmaf(c.g.x, w0.y, fmaf(c.g.y, w1.y, c.g.z * w2.y));
+        f[4 * j + 2] = fmaf(c.g.x, w0.z, fmaf(c.g.y, w1.z, c.g.z * w2.z));
+        f[4 * j + 3] = fmaf(c.g.x, w0.w, fmaf(c.g.y, w1.w, c.g.z * w2.w));
+      }
+    }
+    if (S == 2) {                                   // + d sigma * w_sigma  (fc_out row 0)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const float4 w = hw[cb * 8 + j];
+        f[4 * j] = fmaf(c.g.w, w.x, f[4 * j]); f[4 * j + 1] = fmaf(c.g.w, w.y, f[4 * j + 1]);
+        f[4 * j + 2] = fmaf(c.g.w, w.z, f[4 * j + 2]); f[4 * j + 3] = fmaf(c.g.w, w.w, f[4 * j + 3]);
+      }
+    }
+    if (MK >= 0) {
+      const uint32_t w = mw[cb];                    // bit 31-j set: pre-activation of column 32 cb + j was <= 0
+#pragma unroll
+      for (int j = 0; j < 32; ++j) f[j] = (w & (0x80000000u >> j)) ? 0.f : f[j];
+    }
+    uint32_t pk[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
+    store_row_block(c.tile, c.r, cb, pk);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  named_bar_sync(c.bar_id, 128);
+  if (c.elected) {
+    if (c.tile_ok) { bulk_s2g(c.dy + (size_t)(S + 1) * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
+    if (S < 3) mbar_arrive(&c.bars->a_ready[t]);
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* tiles = smem;
+  uint8_t* ring = smem + OFF_RING;
+  float* heads = reinterpret_cast<float*>(smem + OFF_HEADS);
+  BBars* bars = reinterpret_cast<BBars*>(smem + OFF_BARS);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int64_t num_tiles = (a.M + TILE - 1) / TILE;
+  const int64_t num_pairs = (num_tiles + 1) / 2;
+
+  if (tid == 0) {
+    for (int i = 0; i < BRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
+    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
+    bars->abort_flag = 0;
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
+    mbar_fence_init();
+  }
+  for (int i = tid; i < HEAD_FLOATS; i += NTHREADS) heads[i] = a.pk.w_sigma[i];   // w_sigma | w_rgb are contiguous
+  if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = bars->tmem_slot;
+
+  if (warp == 0) {
+    // ===== TMA producer: 16 transposed K-chunks x 2 N-halves per pair =====
+    if (lane == 0) {
+      uint32_t g = 0;
+      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+        for (int hc = 0; hc < 2 * BWD_CHUNKS; ++hc, ++g) {
+          const int slot = g % BRING;
+          if (!bwait(&bars->w_empty[slot], ((g / BRING) & 1) ^ 1, bars, a.err)) break;
+          mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
+          bulk_g2s(ring + slot * HALF, a.pk.bwd + (size_t)hc * HALF, HALF, &bars->w_full[slot]);
+        }
+        if (*(volatile int*)&bars->abort_flag) break;
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
+      const uint64_t a_desc0 = smem_desc(smem_u32(tiles), 16, 1024, SWIZZLE_128B);
+      const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
+      uint32_t g = 0, na = 0;
+      bool ok = true;
+      for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+        for (int stage = 0; stage < 4 && ok; ++stage, ++na) {
+          for (int c = 0; c < 4 && ok; ++c) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h, ++g) {
+              if (!ok) continue;
+              const int slot = g % BRING;
+              if (!bwait(&bars->w_full[slot], (g / BRING) & 1, bars, a.err)) { ok = false; continue; }
+              if (c == 0 && h == 0) {
+                if (!bwait(&bars->a_ready[0], na & 1, bars, a.err) || !bwait(&bars->a_ready[1], na & 1, bars, a.err)) { ok = false; continue; }
+              }
+              tc_fence_after();
+              const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
+#pragma unroll
+              for (int t = 0; t < 2; ++t) {
+                const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
+                const uint32_t d = tmem + t * 256 + h * 128;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(d, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
+                if (c == 3 && h == 1) umma_commit(&bars->acc_full[t]);
+              }
+              umma_commit(&bars->w_empty[slot]);
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warps: thread = one sample row =====
+    const int t = (warp - 2) >> 2;
+    const int q = warp & 3;
+    BEpi c;
+    c.bars = bars;
+    c.tile = tiles + t * TILE_BYTES;
+    c.heads = heads;
+    c.r = q * 32 + lane;
+    c.bar_id = 1 + t;
+    c.elected = ((warp - 2) & 3) == 0 && lane == 0;
+    c.tacc = tmem + t * 256 + ((uint32_t)(q * 32) << 16);
+    uint32_t na = 0;
+    for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+      const int64_t tile_idx = pr * 2 + t;
+      c.tile_ok = tile_idx < num_tiles;
+      const int64_t m = tile_idx * TILE + c.r;
+      c.masks = a.saved + (size_t)(c.tile_ok ? tile_idx : 0) * SAVED_PER_TILE + SAVED_MASKS;
+      c.dy = a.dy + (size_t)(c.tile_ok ? tile_idx : 0) * DY_PER_TILE;
+      c.g = m < a.M ? __ldg(reinterpret_cast<const float4*>(a.g_raw) + m) : make_float4(0.f, 0.f, 0.f, 0.f);
+      bool ok = bwd_stage<-1>(a, c, t, 0);
+      if (ok) { ok = bwd_stage<0>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = bwd_stage<1>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = bwd_stage<2>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = bwd_stage<3>(a, c, t, na & 1); ++na; }
+      if (!ok) break;
+    }
+    if (c.elected) bulk_wait0();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}
+}  // namespace
+
+int cnrf_tc_launch_bwd(const BwdArgs& b, int grid, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  mlp_bwd_tc_kernel<<<grid, NTHREADS, BWD_SMEM, st>>>(b);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}

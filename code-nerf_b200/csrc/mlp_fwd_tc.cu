@@ -105,6 +105,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   named_bar_sync(c.bar_id, 128);
   const float4* hw = reinterpret_cast<const float4*>(c.heads);
   float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f;
+  uint32_t sgn[8];                                  // sign bits of the pre-activations (the backward's ReLU mask)
 #pragma unroll
   for (int cb = 0; cb < 8; ++cb) {
     uint32_t v[32];
@@ -148,6 +149,12 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
         rgb2 = fmaf(x0, w2.x, fmaf(x1, w2.y, fmaf(x2, w2.z, fmaf(x3, w2.w, rgb2))));
       }
     }
+    if (E != 2) {
+      uint32_t w = 0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) w = __funnelshift_l(__float_as_uint(f[j]), w, 1);   // (w << 1) | sign(f[j])
+      sgn[cb] = w;
+    }
     uint32_t pk[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) pk[j] = (E == 2) ? pack_bf16(f[2 * j], f[2 * j + 1]) : cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
@@ -156,6 +163,11 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
 #pragma unroll
       for (int j = 0; j < 8; ++j) bcur[j] = bnxt[j];
     }
+  }
+  if (E != 2 && c.sv) {
+    uint4* mp = reinterpret_cast<uint4*>(c.sv + SAVED_MASKS + (size_t)(E == 0 ? 0 : E == 1 ? 1 : E == 3 ? 2 : 3) * MASK_BYTES + c.r * 32);
+    mp[0] = make_uint4(sgn[0], sgn[1], sgn[2], sgn[3]);
+    mp[1] = make_uint4(sgn[4], sgn[5], sgn[6], sgn[7]);
   }
   if (E == 1) c.sigma += tail0;
   if (E == 4 && c.valid)                            // [rgb_raw | sigma_raw]   models/model.py:194

@@ -167,189 +167,6 @@ extern "C" int cnrf_debug_tc_error(void) {
 }
 
 // =====================================================================================================================
-// Backward-data chain.  Per tile pair: stage 0 on CUDA cores (d v2 = g_rgb Wrv, masked), then four tensor-core stages
-//   d v1 = (d v2p Wd2) * [v1>0],  d feat = d v1p Wdf,  d h2 = (d feat Woh' + d sigma w_sigma) * [h2>0],  d h1 = (d h2p W2h) * [h1>0]
-// with W^T streamed as B operands.  Every masked gradient tile is stored as a bf16 image (same layout as the forward's
-// activation images) for the weight-gradient kernel.
-// =====================================================================================================================
-constexpr size_t DY_PER_TILE = 5 * (size_t)TILE_BYTES;      // d v2p, d v1p, d feat, d h2p, d h1p
-
-struct BwdArgs {
-  int64_t M;
-  const float* g_raw;          // [M,4]
-  const uint8_t* saved;        // forward images
-  uint8_t* dy;                 // gradient images out
-  Packed pk;
-  int* err;
-};
-
-// mask source image index (within the forward's saved tile: 0 h1, 1 h2, 2 feat, 3 v1, 4 v2) for epilogue stage s
-__device__ __forceinline__ const uint8_t* saved_image(const uint8_t* sv, int img) { return sv + SAVED_GAMMA + (size_t)img * TILE_BYTES; }
-
-__global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a) {
-  extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* tiles = smem;
-  uint8_t* ring = smem + 2 * TILE_BYTES;
-  const __nv_bfloat162* wsr = reinterpret_cast<const __nv_bfloat162*>(ring + RING * CHUNK);
-  Bars* bars = reinterpret_cast<Bars*>(ring + RING * CHUNK + CONST_BYTES);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int64_t num_tiles = (a.M + TILE - 1) / TILE;
-  const int64_t num_pairs = (num_tiles + 1) / 2;
-
-  if (tid == 0) {
-    for (int i = 0; i < RING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
-    bars->abort_flag = 0;
-    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
-    mbar_fence_init();
-  }
-  for (int i = tid; i < CONST_BYTES / 4; i += NTHREADS)
-    reinterpret_cast<uint32_t*>(ring + RING * CHUNK)[i] = reinterpret_cast<const uint32_t*>(a.pk.wsr_bf16)[i];
-  if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = bars->tmem_slot;
-
-  if (warp == 0) {
-    if (lane == 0) {
-      uint32_t g = 0;
-      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
-        for (int ch = 0; ch < BWD_CHUNKS; ++ch, ++g) {
-          const int slot = g % RING;
-          if (!wait_bar(&bars->w_empty[slot], ((g / RING) & 1) ^ 1, bars, a.err)) goto done;
-          mbar_arrive_expect_tx(&bars->w_full[slot], CHUNK);
-          bulk_g2s(ring + slot * CHUNK, a.pk.bwd + (size_t)ch * CHUNK, CHUNK, &bars->w_full[slot]);
-        }
-      }
-    }
-  } else if (warp == 1) {
-    if (lane == 0) {
-      const uint32_t idesc = idesc_bf16(128, 256, 0, 0);
-      uint32_t g = 0, na = 0;
-      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
-        for (int stage = 0; stage < 4; ++stage, ++na) {
-          for (int c = 0; c < 4; ++c, ++g) {
-            const int slot = g % RING;
-            if (!wait_bar(&bars->w_full[slot], (g / RING) & 1, bars, a.err)) goto done;
-            for (int t = 0; t < 2; ++t) {
-              if (c == 0 && !wait_bar(&bars->a_ready[t], na & 1, bars, a.err)) goto done;
-              tc_fence_after();
-              const uint32_t a_base = smem_u32(tiles + t * TILE_BYTES + c * SLAB);
-              const uint32_t b_base = smem_u32(ring + slot * CHUNK);
-#pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                umma_bf16(tmem + t * 256, smem_desc(a_base + k * 32, 16, 1024, SWIZZLE_128B),
-                          smem_desc(b_base + k * 32, 16, 1024, SWIZZLE_128B), idesc, (c | k) != 0);
-              }
-              if (c == 3) umma_commit(&bars->acc_full[t]);
-            }
-            umma_commit(&bars->w_empty[slot]);
-          }
-        }
-      }
-    }
-  } else {
-    const int t = (warp - 2) >> 2;
-    const int q = warp & 3;
-    const int r = q * 32 + lane;
-    const bool elected = ((warp - 2) & 3) == 0 && lane == 0;
-    const int bar_id = 1 + t;
-    uint8_t* tile = tiles + t * TILE_BYTES;
-    const uint32_t tacc = tmem + t * 256 + ((uint32_t)(q * 32) << 16);
-    uint32_t na = 0;
-    for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
-      const int64_t tile_idx = pr * 2 + t;
-      const bool tile_ok = tile_idx < num_tiles;
-      const int64_t m = tile_idx * TILE + r;
-      const bool valid = m < a.M;
-      const uint8_t* sv = a.saved + (size_t)(tile_ok ? tile_idx : 0) * SAVED_PER_TILE;
-      uint8_t* dy = a.dy + (size_t)(tile_ok ? tile_idx : 0) * DY_PER_TILE;
-      const float4 g = valid ? reinterpret_cast<const float4*>(a.g_raw)[m] : make_float4(0.f, 0.f, 0.f, 0.f);
-      // ---- stage 0: d v2p = (g_rgb Wrv) * [v2 > 0] on CUDA cores ----
-      if (elected) bulk_wait_read0();
-      named_bar_sync(bar_id, 128);
-      {
-        const uint8_t* mrow = saved_image(sv, 4) + r * 128;
-#pragma unroll 1
-        for (int cb = 0; cb < 8; ++cb) {
-          uint4 mk[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            mk[j] = __ldg(reinterpret_cast<const uint4*>(mrow + (cb >> 1) * SLAB + (((((cb & 1) * 4) + j) ^ (r & 7)) << 4)));
-          const uint32_t* mw = reinterpret_cast<const uint32_t*>(mk);
-          uint32_t pk[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const int col2 = cb * 16 + j;
-            const float2 w0 = __bfloat1622float2(wsr[128 + col2]), w1 = __bfloat1622float2(wsr[256 + col2]),
-                         w2 = __bfloat1622float2(wsr[384 + col2]);
-            float lo = g.x * w0.x + g.y * w1.x + g.z * w2.x, hi = g.x * w0.y + g.y * w1.y + g.z * w2.y;
-            if ((mw[j] & 0xFFFFu) == 0u) lo = 0.f;            // relu output stored as bf16: > 0  <=>  bits != 0
-            if ((mw[j] >> 16) == 0u) hi = 0.f;
-            pk[j] = pack_bf16(lo, hi);
-          }
-          store_row_block(tile, r, cb, pk);
-        }
-      }
-      fence_proxy_async();
-      named_bar_sync(bar_id, 128);
-      if (elected) {
-        if (tile_ok) { bulk_s2g(dy, tile, TILE_BYTES); bulk_commit(); }
-        mbar_arrive(&bars->a_ready[t]);
-      }
-      // ---- four tensor-core stages ----
-      for (int s = 0; s < 4; ++s, ++na) {
-        if (!wait_bar(&bars->acc_full[t], na & 1, bars, a.err)) goto done;
-        tc_fence_after();
-        if (elected) bulk_wait_read0();
-        named_bar_sync(bar_id, 128);
-        const int mask_img = s == 0 ? 3 : s == 2 ? 1 : s == 3 ? 0 : -1;        // v1, -, h2, h1
-        const uint8_t* mrow = saved_image(sv, mask_img < 0 ? 0 : mask_img) + r * 128;
-#pragma unroll 1
-        for (int cb = 0; cb < 8; ++cb) {
-          uint32_t v[32];
-          tmem_ld32(tacc + cb * 32, v);
-          uint4 mk[4];
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            mk[j] = __ldg(reinterpret_cast<const uint4*>(mrow + (cb >> 1) * SLAB + (((((cb & 1) * 4) + j) ^ (r & 7)) << 4)));
-          const uint32_t* mw = reinterpret_cast<const uint32_t*>(mk);
-          tmem_ld_wait();
-          uint32_t pk[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            float lo = __uint_as_float(v[2 * j]), hi = __uint_as_float(v[2 * j + 1]);
-            if (s == 2) {                                     // + d sigma * w_sigma  (fc_out row 0)
-              const float2 w = __bfloat1622float2(wsr[cb * 16 + j]);
-              lo = fmaf(g.w, w.x, lo); hi = fmaf(g.w, w.y, hi);
-            }
-            if (mask_img >= 0) {
-              if ((mw[j] & 0xFFFFu) == 0u) lo = 0.f;
-              if ((mw[j] >> 16) == 0u) hi = 0.f;
-            }
-            pk[j] = pack_bf16(lo, hi);
-          }
-          store_row_block(tile, r, cb, pk);
-        }
-        fence_proxy_async();
-        tc_fence_before();
-        named_bar_sync(bar_id, 128);
-        if (elected) {
-          if (tile_ok) { bulk_s2g(dy + (size_t)(s + 1) * TILE_BYTES, tile, TILE_BYTES); bulk_commit(); }
-          if (s < 3) mbar_arrive(&bars->a_ready[t]);
-        }
-      }
-    }
-    if (elected) bulk_wait0();
-  }
-done:
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 512);
-}
-
-// =====================================================================================================================
 // Weight gradients: dW[n][k] = sum_m dY[m][n] X[m][k] on tensor cores, operands read as MN-major straight from the saved
 // bf16 images (the sample index is the contraction dimension, so the very same image is its own transpose).
 // grid = (ctas per job, 5 jobs); a CTA accumulates its share of the tiles in TMEM (2 x [128 x N] fp32) and adds it to
@@ -590,17 +407,14 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   if ((rc = cnrf_fill_zero(g->bias[CNRF_L_DIR2], 256 * sizeof(float), st))) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(mlp_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(mlp_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM);
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
   BwdArgs b;
   b.M = a.M; b.g_raw = g_raw; b.saved = sv; b.dy = dy; b.pk = pk; b.err = tc_error_ptr();
   const int64_t pairs = (tiles + 1) / 2;
-  mlp_bwd_tc_kernel<<<(int)(pairs < sm_count() ? pairs : sm_count()), NTHREADS, SMEM_BYTES, st>>>(b);
-  CNRF_LAUNCH_CHECK();
+  if ((rc = cnrf_tc_launch_bwd(b, (int)(pairs < sm_count() ? pairs : sm_count()), st))) return rc;
 
   DwArgs d;
   d.M = a.M; d.saved = sv; d.dy = dy; d.err = tc_error_ptr();
@@ -611,9 +425,10 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   d.job[3] = {3, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nullptr, -1};                       // d h2p^T h1
   d.job[4] = {4, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1], 63};        // d h1p^T [gamma | 1]
   d.job[5] = {1, -2, 64, g->weight[CNRF_L_DIR1] + 256, 256 + a.dd, a.dd, g->bias[CNRF_L_DIR1], a.dd};   // d v1p^T [gamma(d) | 1]
-  {   // one CTA per SM: the four 256-wide jobs share most of them, the two 64-wide jobs get ~1/15 each
+  {   // one CTA per SM, shared in proportion to the bytes a job streams per tile (128 KB for the four 256-wide jobs,
+      // 80 KB and 72 KB for the two 64-wide ones): the kernel is HBM-bound and a single SM only pulls ~45 GB/s
     const int64_t halves = tiles * 2;
-    const int light = sm_count() / 15 > 0 ? sm_count() / 15 : 1;
+    const int light = sm_count() * 18 / 148 > 0 ? sm_count() * 18 / 148 : 1;
     const int heavy = (sm_count() - 2 * light) / 4 > 0 ? (sm_count() - 2 * light) / 4 : 1;
     int at = 0;
     for (int j = 0; j < 6; ++j) {

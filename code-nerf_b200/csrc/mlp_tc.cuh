@@ -78,7 +78,11 @@ __device__ __forceinline__ bool wait_bar(uint64_t* bar, uint32_t parity, Bars* b
 }
 
 constexpr size_t SAVED_GAMMA = SLAB;                          // gamma(x) slab (K = 64)
-constexpr size_t SAVED_PER_TILE = SAVED_GAMMA + 5 * (size_t)TILE_BYTES;   // + h1, h2, feat, v1, v2 images
+constexpr size_t SAVED_MASKS = SAVED_GAMMA + 5 * (size_t)TILE_BYTES;      // after the h1, h2, feat, v1, v2 images
+constexpr size_t MASK_BYTES = 128 * 32;                                   // one layer's sign bits: 8 words per sample row
+// 4 x 4 KB of sign-bit words (h1, h2, v1, v2 pre-activations; bit 31-j of word cb = column 32 cb + j is <= 0): the
+// backward reads 32 B per row and layer instead of re-reading the 64 KB activation image for its ReLU mask
+constexpr size_t SAVED_PER_TILE = SAVED_MASKS + 4 * MASK_BYTES;
 
 struct FwdArgs {
   int64_t N, M; int S, pairing, dx;
@@ -128,3 +132,15 @@ __device__ __forceinline__ void build_input_row(const FwdArgs& a, int64_t m, boo
 
 // mlp_fwd_tc.cu
 int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st);
+
+// Backward-data chain (mlp_bwd_tc.cu)
+constexpr size_t DY_PER_TILE = 5 * (size_t)TILE_BYTES;      // d v2p, d v1p, d feat, d h2p, d h1p
+struct BwdArgs {
+  int64_t M;
+  const float* g_raw;          // [M,4]
+  const uint8_t* saved;        // forward images + sign-bit masks
+  uint8_t* dy;                 // gradient images out
+  Packed pk;
+  int* err;
+};
+int cnrf_tc_launch_bwd(const BwdArgs& b, int grid, cudaStream_t st);
