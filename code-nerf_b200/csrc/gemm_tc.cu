@@ -7,7 +7,7 @@
 //
 // These problems are small (M = rays of a chunk, N,K <= 320, or K = rays for dW) and latency-bound, so up to 16 mutually
 // independent problems share ONE launch (grid = sum of their tiles).  One CTA = one 128 x 64 output tile; K is walked in
-// chunks of 256 (long K of the weight-gradient form: split over CTAs, partials added atomically -- its output is
+// chunks of 64 (long K of the weight-gradient form: split over CTAs, partials added atomically -- its output is
 // zero-filled by the caller).  All threads convert the fp32 operands to bf16 straight into the 128-byte-swizzled
 // shared-memory image (rows = the strided index, columns = the contiguous index), ONE thread issues the MMAs, the
 // operand majorness is chosen by the descriptor (K-major when k is the contiguous index, MN-major otherwise -- no
@@ -19,10 +19,11 @@
 using namespace tc;
 
 namespace {
-constexpr int GBM = 128, GBN = 64, GKC = 256, GTHREADS = 512;
-constexpr int A_BYTES = GBM * GKC * 2;      // one bf16 image of the A tile for a 256-wide K chunk (64 KB)
-constexpr int B_BYTES = GBN * GKC * 2;      // ... of the B tile (32 KB)
-constexpr int G_SMEM = 2 * (A_BYTES + B_BYTES) + 1024 /*alignment slack*/;   // hi and lo images
+constexpr int GBM = 128, GBN = 64, GKC = 64, GKSLICE = 256, GTHREADS = 256, GOCC = 4;
+constexpr int A_BYTES = GBM * GKC * 2;      // one bf16 image of the A tile for a 64-wide K chunk (16 KB)
+constexpr int B_BYTES = GBN * GKC * 2;      // ... of the B tile (8 KB)
+constexpr int G_SMEM = 2 * (A_BYTES + B_BYTES) + 1024 /*alignment slack*/;   // hi and lo images: 49 KB -> four CTAs per SM
+                                                                          // hide each other's load round trips
 
 struct GemmBatch {
   GemmArgs g[CNRF_GEMM_BATCH_MAX];
@@ -44,8 +45,8 @@ __device__ __noinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int ro
   const bool pow2 = (groups & (groups - 1)) == 0;
   const int total = rows_tile * groups;
   const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((row_stride & 3) == 0) && ((c0 & 3) == 0);
-  constexpr int U = 16;                                // independent global loads in flight per thread: a whole
-                                                       // 128 x 256 tile is ONE round trip (cold misses cost ~2.5 us each)
+  constexpr int U = 8;                                 // independent global loads in flight per thread: a whole
+                                                       // 128 x 64 chunk is ONE round trip (cold misses cost ~2.5 us each)
 #pragma unroll 1
   for (int base = tid; base < total; base += GTHREADS * U) {
     float4 v[U];
@@ -85,7 +86,7 @@ __device__ __noinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int ro
   }
 }
 
-__global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_batch_kernel(const __grid_constant__ GemmBatch b, int* err) {
+__global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __grid_constant__ GemmBatch b, int* err) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -156,7 +157,7 @@ __global__ void __launch_bounds__(GTHREADS, 1) gemm_tc_batch_kernel(const __grid
   }
   ok = ok && mbar_wait(&bar, phase, err);
   tc_fence_after();
-  if (ok && warp < 8) {
+  if (ok) {
     const int q = warp & 3, half = warp >> 2;          // TMEM lane quarter, column half of the 64-wide tile
     const int64_t m = m0 + q * 32 + lane;
     uint32_t v[32];
@@ -228,7 +229,7 @@ int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
     if (a.b_rs == 1) b.b_mn[i] = 0; else if (a.b_cs == 1) b.b_mn[i] = 1; else return CNRF_E_UNSUPPORTED;
     // split K over CTAs only where the caller already adds into C (weight gradients: K = rays of the chunk)
     const bool may_split = a.split_k > 1 || a.accumulate;
-    b.kslice[i] = (may_split && a.K > 2 * GKC) ? GKC : a.K;
+    b.kslice[i] = (may_split && a.K > 2 * GKSLICE) ? GKSLICE : a.K;
     b.g[i] = a;
     b.mt[i] = (int)((a.M + GBM - 1) / GBM);
     b.nt[i] = (a.N + GBN - 1) / GBN;

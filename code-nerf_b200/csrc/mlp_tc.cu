@@ -348,38 +348,53 @@ __global__ void img_group_sum_kernel(const uint8_t* base, size_t per_tile, size_
   out[g * ld + 2 * w + 1] = (s[0].y + s[1].y) + (s[2].y + s[3].y);
 }
 // out[c*ld + col] += sum_m wgt[m*wstride + c] * img[m][col], c < NW          (column sums / tiny-N weight gradients)
+// One block = 4 tiles; a warp reads whole 512-byte image rows (16 B per lane: slab lane/8, chunk lane%8 un-swizzled by
+// the row), 8 warps interleave the rows; per-warp partial sums meet in shared memory, one atomic per column and block.
 template <int NW>
-__global__ void img_weighted_colsum_kernel(const uint8_t* base, size_t per_tile, size_t off, int64_t M,
-                                           const float* wgt, int wstride, float* out, int64_t ld) {
-  const int w = threadIdx.x;           // 128 threads: column pair
-  const int64_t m0 = (int64_t)blockIdx.x * CSUM_ROWS, m1 = m0 + CSUM_ROWS < M ? m0 + CSUM_ROWS : M;
-  float2 s[NW];
+__global__ void __launch_bounds__(256) img_weighted_colsum_kernel(const uint8_t* __restrict__ base, size_t per_tile,
+                                                                  size_t off, int64_t M, const float* __restrict__ wgt,
+                                                                  int wstride, float* __restrict__ out, int64_t ld) {
+  __shared__ float red[8][NW][256];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float acc[NW][8];
 #pragma unroll
-  for (int c = 0; c < NW; ++c) s[c] = make_float2(0.f, 0.f);
-  int64_t m = m0;
-  for (; m + 8 <= m1; m += 8) {        // 8 independent image loads in flight per thread
-    float2 v[8];
+  for (int c = 0; c < NW; ++c)
 #pragma unroll
-    for (int u = 0; u < 8; ++u) v[u] = img_pair(base, per_tile, off, m + u, w);
+    for (int j = 0; j < 8; ++j) acc[c][j] = 0.f;
+  for (int tt = 0; tt < 4; ++tt) {
+    const int64_t tile = (int64_t)blockIdx.x * 4 + tt;
+    if (tile * TILE >= M) break;
+    const uint8_t* tb = base + (size_t)tile * per_tile + off + (lane >> 3) * SLAB;
+#pragma unroll 4
+    for (int rr = warp; rr < TILE; rr += 8) {
+      const int64_t m = tile * TILE + rr;
+      if (m >= M) continue;
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(tb + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4)));
+      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+      float x[8];
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
+      for (int j = 0; j < 4; ++j) { x[2 * j] = __uint_as_float(u[j] << 16); x[2 * j + 1] = __uint_as_float(u[j] & 0xFFFF0000u); }
 #pragma unroll
       for (int c = 0; c < NW; ++c) {
-        const float g = wgt ? __ldg(wgt + (m + u) * wstride + c) : 1.0f;
-        s[c].x = fmaf(g, v[u].x, s[c].x); s[c].y = fmaf(g, v[u].y, s[c].y);
+        const float g = wgt ? __ldg(wgt + m * wstride + c) : 1.0f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[c][j] = fmaf(g, x[j], acc[c][j]);
       }
     }
   }
-  for (; m < m1; ++m) {
-    float2 v = img_pair(base, per_tile, off, m, w);
 #pragma unroll
-    for (int c = 0; c < NW; ++c) {
-      const float g = wgt ? wgt[m * wstride + c] : 1.0f;
-      s[c].x = fmaf(g, v.x, s[c].x); s[c].y = fmaf(g, v.y, s[c].y);
-    }
+  for (int c = 0; c < NW; ++c)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp][c][lane * 8 + j] = acc[c][j];
+  __syncthreads();
+  const int col = threadIdx.x;
+#pragma unroll
+  for (int c = 0; c < NW; ++c) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += red[w][c][col];
+    atomicAdd(out + c * ld + col, s);
   }
-#pragma unroll
-  for (int c = 0; c < NW; ++c) { atomicAdd(out + c * ld + 2 * w, s[c].x); atomicAdd(out + c * ld + 2 * w + 1, s[c].y); }
 }
 
 size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
@@ -441,13 +456,13 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
     CNRF_LAUNCH_CHECK();
   }
 
-  const unsigned cs_grid = (unsigned)((a.M + CSUM_ROWS - 1) / CSUM_ROWS);
-  img_weighted_colsum_kernel<1><<<cs_grid, 128, 0, st>>>(dy, DY_PER_TILE, 0, a.M, nullptr, 0, g->bias[CNRF_L_DIR2], 0);
+  const unsigned cs_grid = (unsigned)((tiles + 3) / 4);
+  img_weighted_colsum_kernel<1><<<cs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 0, a.M, nullptr, 0, g->bias[CNRF_L_DIR2], 0);
   CNRF_LAUNCH_CHECK();
-  img_weighted_colsum_kernel<1><<<cs_grid, 128, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 1 * (size_t)TILE_BYTES, a.M,
+  img_weighted_colsum_kernel<1><<<cs_grid, 256, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 1 * (size_t)TILE_BYTES, a.M,
                                                          g_raw + 3, 4, g->weight[CNRF_L_FC_OUT], 0);
   CNRF_LAUNCH_CHECK();
-  img_weighted_colsum_kernel<3><<<cs_grid, 128, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 4 * (size_t)TILE_BYTES, a.M,
+  img_weighted_colsum_kernel<3><<<cs_grid, 256, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 4 * (size_t)TILE_BYTES, a.M,
                                                          g_raw, 4, g->weight[CNRF_L_FC_RGB], 512);
   CNRF_LAUNCH_CHECK();
   const unsigned gs_grid = (unsigned)((a.N * 128 + 255) / 256);

@@ -198,6 +198,11 @@ int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
  * ---------------------------------------------------------------------------------------------------- */
 /* Synchronises the device; returns 1 if a tensor-core kernel of this process hit its bounded barrier-wait timeout. */
 int cnrf_debug_tc_error(void);
+/* Phase timers of the forward-chain kernel (block 0, clock64 sums; 16 slots) and CUDA-event timing of its launches:
+ * cnrf_debug_fwd_kernel_ms(min_rows > 0) starts timing every launch over >= min_rows rows (statistics reset),
+ * (0) stops; each call returns the mean duration in ms of the launches timed so far. */
+int cnrf_debug_fwd_times(long long* host_out16, int reset);
+double cnrf_debug_fwd_kernel_ms(int64_t min_rows, int64_t* launches, int64_t* rows);
 /* C[M,N] (row stride ldc) = sum_k A[m*a_rs + k*a_cs] * B[k*b_rs + n*b_cs] through the per-ray GEMM toolkit:
  * tc = 0 the fp32 CUDA-core kernel (sgemm.cu), tc = 1 the tcgen05 kernel (gemm_tc.cu, bf16 operands).  accumulate = 1
  * adds into C.  Lets tests pin every operand-majorness combination the per-ray layers use. */
