@@ -37,6 +37,7 @@ _SIGS = {
     "cnrf_debug_umma": (C.c_int, [c_i32, c_f32p, c_f32p, c_f32p, c_i32, c_i32, c_f32p, C.c_void_p]),
     "cnrf_debug_fwd_times": (C.c_int, [C.c_void_p, C.c_int]),
     "cnrf_debug_fwd_kernel_ms": (C.c_double, [c_i64, C.c_void_p, C.c_void_p]),
+    "cnrf_debug_kernel_ms": (C.c_double, [c_i32, c_i64, C.c_void_p, C.c_void_p]),
     "cnrf_debug_gemm": (C.c_int, [c_i32, c_f32p, c_i64, c_i64, c_f32p, c_i64, c_i64, c_f32p, c_i64, c_i64, c_i32, c_i64, c_i32,
                                   C.c_void_p]),
     "cnrf_ray_bundle_fwd": (C.c_int, [c_f32p, c_i64, c_i32, c_i32, c_f, c_f, c_f, c_f32p, c_i64, c_f32p, c_f32p, C.c_void_p]),

@@ -41,3 +41,8 @@ int cnrf_pos_embed_fwd_ld(const float* x, int64_t M, int D, const float* freqs, 
                           float* out, cudaStream_t st);
 int cnrf_pos_embed_bwd_ld(const float* x, const float* g_out, int64_t M, int D, const float* freqs, int L, int inc,
                           int64_t ld_g, float* g_x, cudaStream_t st);
+
+// ---- ktimer.cu: CUDA-event timers around the tensor-core kernels (debug / bench) ----------------------------------------
+enum { CNRF_KT_FWD = 0, CNRF_KT_BWD = 1, CNRF_KT_DW = 2, CNRF_KT_COUNT = 3 };
+bool cnrf_ktimer_begin(int which, int64_t rows, cudaStream_t st);   // true: timing, call cnrf_ktimer_end after the launch
+void cnrf_ktimer_end(int which, cudaStream_t st);

@@ -229,7 +229,9 @@ int cnrf_tc_launch_bwd(const BwdArgs& b, int grid, cudaStream_t st) {
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
+  const bool timed = cnrf_ktimer_begin(CNRF_KT_BWD, b.M, st);
   mlp_bwd_tc_kernel<<<grid, NTHREADS, BWD_SMEM, st>>>(b);
   CNRF_LAUNCH_CHECK();
+  if (timed) cnrf_ktimer_end(CNRF_KT_BWD, st);
   return CNRF_OK;
 }

@@ -351,25 +351,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
 }
 }  // namespace
 
-// bench.py's roofline leg: CUDA events around the forward-chain kernel on its launching stream (off by default)
-static int g_time_fwd = 0;
-constexpr int EV_MAX = 512;                 // launches per timing window; no host synchronisation until the query
-static cudaEvent_t g_ev[EV_MAX][2];
-static int g_ev_made = 0, g_ev_used = 0;
-static double g_fwd_ms_sum = 0.0;
-static long long g_fwd_samples = 0, g_fwd_last_rows = 0;
-
-static void fwd_timer_collect() {
-  for (int i = 0; i < g_ev_used; ++i) {
-    float ms = 0.f;
-    if (cudaEventSynchronize(g_ev[i][1]) == cudaSuccess && cudaEventElapsedTime(&ms, g_ev[i][0], g_ev[i][1]) == cudaSuccess) {
-      g_fwd_ms_sum += ms;
-      ++g_fwd_samples;
-    }
-  }
-  g_ev_used = 0;
-}
-
 int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
@@ -377,26 +358,11 @@ int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  const bool timed = g_time_fwd && f.M >= g_time_fwd && g_ev_used < EV_MAX;
-  if (timed) {
-    if (g_ev_used == g_ev_made) { cudaEventCreate(&g_ev[g_ev_made][0]); cudaEventCreate(&g_ev[g_ev_made][1]); ++g_ev_made; }
-    cudaEventRecord(g_ev[g_ev_used][0], st);
-  }
+  const bool timed = cnrf_ktimer_begin(CNRF_KT_FWD, f.M, st);
   mlp_fwd_tc_kernel<<<grid, NTHREADS, FWD_SMEM, st>>>(f);
   CNRF_LAUNCH_CHECK();
-  if (timed) { cudaEventRecord(g_ev[g_ev_used][1], st); ++g_ev_used; g_fwd_last_rows = f.M; }
+  if (timed) cnrf_ktimer_end(CNRF_KT_FWD, st);
   return CNRF_OK;
-}
-
-// min_rows > 0: time every forward-chain launch over at least min_rows sample rows from now on (resets the statistics);
-// min_rows = 0: stop.  Returns the mean kernel duration in ms of the launches timed so far (synchronises on the last one).
-extern "C" double cnrf_debug_fwd_kernel_ms(int64_t min_rows, int64_t* launches, int64_t* rows) {
-  fwd_timer_collect();
-  const double mean = g_fwd_samples ? g_fwd_ms_sum / (double)g_fwd_samples : 0.0;
-  if (launches) *launches = g_fwd_samples;
-  if (rows) *rows = g_fwd_last_rows;
-  if (min_rows >= 0) { g_time_fwd = (int)min_rows; g_fwd_ms_sum = 0.0; g_fwd_samples = 0; }
-  return mean;
 }
 
 extern "C" int cnrf_debug_fwd_times(long long* host_out, int reset) {

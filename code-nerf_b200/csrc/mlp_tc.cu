@@ -10,6 +10,8 @@
 // tiles (4 slabs of [128 rows x 64 bf16], 128-byte swizzle) + 3 x 32 KB weight ring.
 // Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane), warps 2-5 = epilogue of T0, 6-9 = epilogue
 // of T1 (thread = one sample row; TMEM lane quarter = warp_id % 4).
+#include <cstdlib>
+#include <cstring>
 #include "mlp_tc.cuh"
 
 // ---- weight packing ------------------------------------------------------------------------------------------------
@@ -175,17 +177,30 @@ extern "C" int cnrf_debug_tc_error(void) {
 constexpr int DW_THREADS = 192;
 constexpr int DW_STAGE = 8 * 8192;          // 64 rows x (256 + 256) bf16
 constexpr int DW_RING = 3;
-constexpr int DW_SMEM = DW_RING * DW_STAGE + 256;
+constexpr int DW_SMEM = DW_RING * DW_STAGE + 256 + 2 * 64 * 16;   // ring + barriers + raw-gradient staging
 
-struct DwJob { int dy_img; int x_img; /* -1: gamma slab, -2: view-direction extension slab of the tile pair */ int n_cols;
-               float* out; int ld; int k_valid; float* bias_out; int bias_col; };
+// Reductions the four otherwise idle epilogue warps run on every stage while it sits in shared memory (thread = column
+// pair of the 256-wide A image): column sums (a bias gradient), per-ray sums (the gradient of a folded per-ray bias
+// table), the same plus the sigma-weighted column sums of the B image (fc_out row 0), or the three rgb-weighted column
+// sums of a streamed-only image (fc_rgb).
+enum { RED_NONE = 0, RED_COLSUM = 1, RED_RAY = 2, RED_RAY_SIGMA = 3, RED_RGB = 4 };
+constexpr int DW_JOBS = 7;
+struct DwJob { int dy_img;   /* >= 0: image of the gradient set; < 0: image -1-dy_img of the saved set */
+               int x_img;    /* -1: gamma slab, -2: view-direction extension slab of the tile pair */
+               int n_cols;   /* 0: no GEMM, reduction only */
+               float* out; int ld; int k_valid; float* bias_out; int bias_col;
+               int red; float* red_out; int red_ld; float* red2_out; };
 struct DwArgs {
   int64_t M;
+  int S;
   const uint8_t* saved;
   const uint8_t* dy;
   const uint8_t* ext;
-  DwJob job[6];
-  int first[7];          // first CTA of each job (1-D grid)
+  const float* g_raw;
+  float* d_br;             // [N][3] per-ray sums of the rgb gradients   } accumulated by the RED_RGB job
+  float* d_bo;             // [N][257], column 0 = per-ray sums of the sigma gradients
+  DwJob job[DW_JOBS];
+  int first[DW_JOBS + 1];          // first CTA of each job (1-D grid)
   int* err;
 };
 
@@ -201,20 +216,59 @@ __device__ __forceinline__ bool dw_wait(uint64_t* bar, uint32_t parity, DwBars* 
   }
 }
 
+// ---- reducer-warp helpers: 8 bf16 columns (one 16-byte chunk) of a row --------------------------------------------------
+__device__ __forceinline__ void acc8(float* s, const uint4 v) {
+  const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) { s[2 * j] += __uint_as_float(u[j] << 16); s[2 * j + 1] += __uint_as_float(u[j] & 0xFFFF0000u); }
+}
+__device__ __forceinline__ void fma8(float* s, float g, const uint4 v) {
+  const uint32_t u[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    s[2 * j] = fmaf(g, __uint_as_float(u[j] << 16), s[2 * j]);
+    s[2 * j + 1] = fmaf(g, __uint_as_float(u[j] & 0xFFFF0000u), s[2 * j + 1]);
+  }
+}
+// Sum the 8 partial columns of the four row phases (lane bits 3, 4) and leave two of them in every lane; returns the
+// column (within the 64-column slab) of o0, o1 = that column + 1.
+__device__ __forceinline__ int rs_rows(const float* s, int lane, float& o0, float& o1) {
+  const bool b1 = (lane & 16) != 0, b0 = (lane & 8) != 0;
+  float k[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const float snd = b1 ? s[j] : s[4 + j], kp = b1 ? s[4 + j] : s[j];
+    k[j] = kp + __shfl_xor_sync(0xFFFFFFFFu, snd, 16);
+  }
+  {
+    const float snd = b0 ? k[0] : k[2], kp = b0 ? k[2] : k[0];
+    o0 = kp + __shfl_xor_sync(0xFFFFFFFFu, snd, 8);
+  }
+  {
+    const float snd = b0 ? k[1] : k[3], kp = b0 ? k[3] : k[1];
+    o1 = kp + __shfl_xor_sync(0xFFFFFFFFu, snd, 8);
+  }
+  return (lane & 7) * 8 + (b1 ? 4 : 0) + (b0 ? 2 : 0);
+}
+
 __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   DwBars* bars = reinterpret_cast<DwBars*>(smem + DW_RING * DW_STAGE);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   int ji = 0;
-  while (ji < 5 && (int)blockIdx.x >= a.first[ji + 1]) ++ji;
+  while (ji < DW_JOBS - 1 && (int)blockIdx.x >= a.first[ji + 1]) ++ji;
   const DwJob job = a.job[ji];
   const int bx = blockIdx.x - a.first[ji], nb = a.first[ji + 1] - a.first[ji];
   const bool is_ext = job.x_img == -2;
-  const int nslabB = job.x_img < 0 ? 1 : 4;
+  const bool has_mma = job.n_cols > 0;
+  const int nslabB = !has_mma ? 0 : job.x_img < 0 ? 1 : 4;
   const int64_t num_tiles = (a.M + TILE - 1) / TILE;
   const int64_t num_halves = num_tiles * 2;
   if (tid == 0) {
-    for (int i = 0; i < DW_RING; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
+    for (int i = 0; i < DW_RING; ++i) {
+      mbar_init(&bars->full[i], 1);
+      mbar_init(&bars->empty[i], (has_mma ? 1 : 0) + (job.red != RED_NONE ? 4 : 0));   // MMA commit + one per reducer warp
+    }
     mbar_init(&bars->acc_full, 1);
     bars->abort_flag = 0;
     if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
@@ -235,7 +289,9 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
         if (!dw_wait(&bars->empty[slot], ((g / DW_RING) & 1) ^ 1, bars, a.err)) goto done;
         const int64_t tile = h >> 1;
         const int half = (int)(h & 1);
-        const uint8_t* src_a = a.dy + (size_t)tile * DY_PER_TILE + (size_t)job.dy_img * TILE_BYTES + half * 8192;
+        const uint8_t* src_a = job.dy_img >= 0
+            ? a.dy + (size_t)tile * DY_PER_TILE + (size_t)job.dy_img * TILE_BYTES + half * 8192
+            : a.saved + (size_t)tile * SAVED_PER_TILE + SAVED_GAMMA + (size_t)(-1 - job.dy_img) * TILE_BYTES + half * 8192;
         const uint8_t* src_b = is_ext ? a.ext + (size_t)(tile >> 1) * SLAB + half * 8192
                                       : a.saved + (size_t)tile * SAVED_PER_TILE +
                                             (job.x_img < 0 ? 0 : SAVED_GAMMA + (size_t)job.x_img * TILE_BYTES) + half * 8192;
@@ -246,7 +302,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && has_work) {
+    if (lane == 0 && has_work && has_mma) {
       const uint32_t idesc = idesc_bf16(128, job.n_cols, 1, 1);
       uint32_t g = 0;
       uint32_t seen = 0;               // extension job: tile parities whose accumulator pair has been started
@@ -272,7 +328,155 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
     }
   } else if (has_work) {
     const int q = warp & 3;
-    if (dw_wait(&bars->acc_full, 0, bars, a.err)) {
+    if (job.red != RED_NONE) {
+      // warp = 64-column slab of the image, lane = (16-byte chunk c, row phase ph): a thread reads rows ph, ph+4, ... of
+      // its 8 columns with one conflict-free LDS.128 per row; the four row phases meet in a shuffle reduce-scatter
+      const int rw = warp - 2, w = tid - 64;
+      const int c = lane & 7, ph = lane >> 3;
+      const bool needs_g = job.red == RED_RAY_SIGMA || job.red == RED_RGB;
+      float4* gbuf = reinterpret_cast<float4*>(smem + DW_RING * DW_STAGE + 256);      // [2][64] raw gradients of a stage
+      float c0[8], c1[8], c2[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) c0[j] = c1[j] = c2[j] = 0.f;
+      float4 gpre = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (needs_g && w < 64 && (int64_t)bx * 64 + w < a.M) gpre = __ldg(reinterpret_cast<const float4*>(a.g_raw) + (int64_t)bx * 64 + w);
+      uint32_t g = 0;
+      for (int64_t h = bx; h < num_halves; h += nb, ++g) {
+        const int slot = g % DW_RING;
+        const int64_t m0 = h * 64;
+        const int rows = (int)(a.M - m0 < 64 ? (a.M - m0 > 0 ? a.M - m0 : 0) : 64);
+        const float4* gs = gbuf + (g & 1) * 64;
+        if (needs_g) {       // raw gradients of this stage (fetched one stage ahead) -> shared memory
+          if (w < 64) gbuf[(g & 1) * 64 + w] = gpre;
+          named_bar_sync(2, 128);
+          const int64_t mn = (h + nb) * 64 + w;
+          gpre = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (w < 64 && h + nb < num_halves && mn < a.M) gpre = __ldg(reinterpret_cast<const float4*>(a.g_raw) + mn);
+        }
+        // first ray of the stage and the row at which it ends (32-bit division when the row count allows)
+        const int64_t ray0 = a.M < (1ll << 31) ? (int64_t)((uint32_t)m0 / (uint32_t)a.S) : m0 / a.S;
+        const int seg_end0 = (int)((ray0 + 1) * a.S - m0);
+        if (!dw_wait(&bars->full[slot], (g / DW_RING) & 1, bars, a.err)) goto done;
+        const uint8_t* sa = smem + slot * DW_STAGE + rw * 8192;
+        // rows ph + 4 i of this thread: chunk (c ^ (row & 7)) alternates between two values
+        const uint8_t* sp = sa + ph * 128;
+        const uint32_t x0 = (uint32_t)((c ^ ph) << 4), x1 = x0 ^ 64u;
+        const bool full_stage = rows == 64;
+#define DW_ROW(i) (sp + (i) * 512 + (((i) & 1) ? x1 : x0))
+        if (job.red == RED_COLSUM) {
+          if (full_stage) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) acc8(c0, *reinterpret_cast<const uint4*>(DW_ROW(i)));
+          } else {
+            for (int i = 0; ph + 4 * i < rows; ++i) acc8(c0, *reinterpret_cast<const uint4*>(DW_ROW(i)));
+          }
+        } else if (job.red == RED_RGB) {
+          // the rgb-weighted column sums do not care about ray boundaries
+          if (full_stage) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const uint4 v = *reinterpret_cast<const uint4*>(DW_ROW(i));
+              const float4 gr = gs[ph + 4 * i];
+              fma8(c0, gr.x, v); fma8(c1, gr.y, v); fma8(c2, gr.z, v);
+            }
+          } else {
+            for (int i = 0; ph + 4 * i < rows; ++i) {
+              const uint4 v = *reinterpret_cast<const uint4*>(DW_ROW(i));
+              const float4 gr = gs[ph + 4 * i];
+              fma8(c0, gr.x, v); fma8(c1, gr.y, v); fma8(c2, gr.z, v);
+            }
+          }
+          // per-ray sums of the raw gradients themselves: warp rw takes component rw
+          const float* gf = reinterpret_cast<const float*>(gs);
+          int64_t ray = ray0;
+          int seg_end = seg_end0;
+          int r0 = 0;
+          while (r0 < rows) {
+            const int r1 = seg_end < rows ? seg_end : rows;
+            float t = 0.f;
+            if (lane >= r0 && lane < r1) t = gf[lane * 4 + rw];
+            if (lane + 32 >= r0 && lane + 32 < r1) t += gf[(lane + 32) * 4 + rw];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xFFFFFFFFu, t, o);
+            if (lane == 0) atomicAdd(rw < 3 ? a.d_br + ray * 3 + rw : a.d_bo + ray * 257, t);
+            r0 = r1; ++ray; seg_end += a.S;
+          }
+        } else {
+          if (job.red == RED_RAY_SIGMA) {       // sigma-weighted column sums of the B image: no ray boundaries either
+            if (full_stage) {
+#pragma unroll
+              for (int i = 0; i < 16; ++i) fma8(c0, gs[ph + 4 * i].w, *reinterpret_cast<const uint4*>(DW_ROW(i) + 4 * 8192));
+            } else {
+              for (int i = 0; ph + 4 * i < rows; ++i)
+                fma8(c0, gs[ph + 4 * i].w, *reinterpret_cast<const uint4*>(DW_ROW(i) + 4 * 8192));
+            }
+          }
+          // per-ray sums of the A image, 16 rows at a time; a ray boundary inside a 16-row group takes the slow path
+          int64_t ray = ray0;
+          int next_b = seg_end0;
+          float sum[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) sum[j] = 0.f;
+          bool dirty = false;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const int lo = 16 * q, hi = rows < lo + 16 ? rows : lo + 16;
+            if (lo < rows) {
+              if (next_b >= hi && hi - lo == 16) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc8(sum, *reinterpret_cast<const uint4*>(DW_ROW(4 * q + i)));
+                dirty = true;
+              } else {
+                int cur = lo;
+                while (cur < hi) {
+                  const int r1 = next_b < hi ? next_b : hi;
+#pragma unroll
+                  for (int i = 0; i < 4; ++i) {
+                    const int r = lo + ph + 4 * i;
+                    if (r >= cur && r < r1) acc8(sum, *reinterpret_cast<const uint4*>(DW_ROW(4 * q + i)));
+                  }
+                  dirty = true;
+                  cur = r1;
+                  if (cur == next_b && cur < hi) {
+                    float o0, o1;
+                    const int col = rw * 64 + rs_rows(sum, lane, o0, o1);
+                    float* o = job.red_out + ray * job.red_ld + col;
+                    atomicAdd(o, o0); atomicAdd(o + 1, o1);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) sum[j] = 0.f;
+                    dirty = false; ++ray; next_b += a.S;
+                  }
+                }
+              }
+              if (next_b == hi || (hi == rows && dirty)) {      // the ray (or the stage) ends with this group
+                float o0, o1;
+                const int col = rw * 64 + rs_rows(sum, lane, o0, o1);
+                float* o = job.red_out + ray * job.red_ld + col;
+                atomicAdd(o, o0); atomicAdd(o + 1, o1);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sum[j] = 0.f;
+                dirty = false;
+                if (next_b == hi) { ++ray; next_b += a.S; }
+              }
+            }
+          }
+        }
+#undef DW_ROW
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->empty[slot]);
+      }
+      float o0, o1;
+      const int col = rw * 64 + rs_rows(c0, lane, o0, o1);
+      float* fo = job.red == RED_RAY_SIGMA ? job.red2_out : job.red_out;
+      if (job.red != RED_RAY) { atomicAdd(fo + col, o0); atomicAdd(fo + col + 1, o1); }
+      if (job.red == RED_RGB) {
+        rs_rows(c1, lane, o0, o1);
+        atomicAdd(fo + job.red_ld + col, o0); atomicAdd(fo + job.red_ld + col + 1, o1);
+        rs_rows(c2, lane, o0, o1);
+        atomicAdd(fo + 2 * job.red_ld + col, o0); atomicAdd(fo + 2 * job.red_ld + col + 1, o1);
+      }
+    }
+    if (has_mma && dw_wait(&bars->acc_full, 0, bars, a.err)) {
       tc_fence_after();
       uint32_t seen = 0;
       if (is_ext) for (int64_t h = bx; h < num_halves; h += nb) seen |= 1u << ((h >> 1) & 1);
@@ -312,91 +516,6 @@ done:
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
-constexpr int CSUM_ROWS = 256;   // rows per block of the column-sum kernels
-// ---- SIMT reductions over the bf16 images --------------------------------------------------------------------------------
-// element pair (row m, columns 2w, 2w+1) of an image set: tile stride `per_tile`, image offset `off`
-__device__ __forceinline__ float2 img_pair(const uint8_t* base, size_t per_tile, size_t off, int64_t m, int w) {
-  const int r = (int)(m & 127);
-  const uint8_t* p = base + (size_t)(m >> 7) * per_tile + off + (w >> 5) * SLAB + r * 128 +
-                     ((((w >> 2) & 7) ^ (r & 7)) << 4) + ((w & 3) << 2);
-  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
-}
-// out[g*ld + col] = sum_{q<Q} img[g*g_stride + q*q_stride][col]        (per-ray sums of a gradient image)
-__global__ void img_group_sum_kernel(const uint8_t* base, size_t per_tile, size_t off, int64_t G, int64_t g_stride,
-                                     int64_t Q, int64_t q_stride, float* out, int64_t ld) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= G * 128) return;
-  const int64_t g = i >> 7;
-  const int w = (int)(i & 127);
-  float2 s[4];
-#pragma unroll
-  for (int u = 0; u < 4; ++u) s[u] = make_float2(0.f, 0.f);
-  const int64_t m0 = g * g_stride;
-  int64_t q = 0;
-  for (; q + 8 <= Q; q += 8) {          // 8 independent loads in flight per thread
-    float2 v[8];
-#pragma unroll
-    for (int u = 0; u < 8; ++u) v[u] = img_pair(base, per_tile, off, m0 + (q + u) * q_stride, w);
-#pragma unroll
-    for (int u = 0; u < 8; ++u) { s[u & 3].x += v[u].x; s[u & 3].y += v[u].y; }
-  }
-  for (; q < Q; ++q) {
-    float2 v = img_pair(base, per_tile, off, m0 + q * q_stride, w);
-    s[0].x += v.x; s[0].y += v.y;
-  }
-  out[g * ld + 2 * w] = (s[0].x + s[1].x) + (s[2].x + s[3].x);
-  out[g * ld + 2 * w + 1] = (s[0].y + s[1].y) + (s[2].y + s[3].y);
-}
-// out[c*ld + col] += sum_m wgt[m*wstride + c] * img[m][col], c < NW          (column sums / tiny-N weight gradients)
-// One block = 4 tiles; a warp reads whole 512-byte image rows (16 B per lane: slab lane/8, chunk lane%8 un-swizzled by
-// the row), 8 warps interleave the rows; per-warp partial sums meet in shared memory, one atomic per column and block.
-template <int NW>
-__global__ void __launch_bounds__(256) img_weighted_colsum_kernel(const uint8_t* __restrict__ base, size_t per_tile,
-                                                                  size_t off, int64_t M, const float* __restrict__ wgt,
-                                                                  int wstride, float* __restrict__ out, int64_t ld) {
-  __shared__ float red[8][NW][256];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float acc[NW][8];
-#pragma unroll
-  for (int c = 0; c < NW; ++c)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) acc[c][j] = 0.f;
-  for (int tt = 0; tt < 4; ++tt) {
-    const int64_t tile = (int64_t)blockIdx.x * 4 + tt;
-    if (tile * TILE >= M) break;
-    const uint8_t* tb = base + (size_t)tile * per_tile + off + (lane >> 3) * SLAB;
-#pragma unroll 4
-    for (int rr = warp; rr < TILE; rr += 8) {
-      const int64_t m = tile * TILE + rr;
-      if (m >= M) continue;
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(tb + rr * 128 + (((lane & 7) ^ (rr & 7)) << 4)));
-      const uint32_t u[4] = {v.x, v.y, v.z, v.w};
-      float x[8];
-#pragma unroll
-      for (int j = 0; j < 4; ++j) { x[2 * j] = __uint_as_float(u[j] << 16); x[2 * j + 1] = __uint_as_float(u[j] & 0xFFFF0000u); }
-#pragma unroll
-      for (int c = 0; c < NW; ++c) {
-        const float g = wgt ? __ldg(wgt + m * wstride + c) : 1.0f;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[c][j] = fmaf(g, x[j], acc[c][j]);
-      }
-    }
-  }
-#pragma unroll
-  for (int c = 0; c < NW; ++c)
-#pragma unroll
-    for (int j = 0; j < 8; ++j) red[warp][c][lane * 8 + j] = acc[c][j];
-  __syncthreads();
-  const int col = threadIdx.x;
-#pragma unroll
-  for (int c = 0; c < NW; ++c) {
-    float s = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) s += red[w][c][col];
-    atomicAdd(out + c * ld + col, s);
-  }
-}
-
 size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
   (void)N;
   size_t b = PACKED_BYTES + 4096 + (size_t)pairs_of(M) * SLAB;
@@ -432,46 +551,50 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   if ((rc = cnrf_tc_launch_bwd(b, (int)(pairs < sm_count() ? pairs : sm_count()), st))) return rc;
 
   DwArgs d;
-  d.M = a.M; d.saved = sv; d.dy = dy; d.err = tc_error_ptr();
+  d.M = a.M; d.S = a.S; d.saved = sv; d.dy = dy; d.g_raw = g_raw; d.d_br = d_br; d.d_bo = d_bo; d.err = tc_error_ptr();
   d.ext = sv + (size_t)tiles * SAVED_PER_TILE;
-  d.job[0] = {0, 3, 256, g->weight[CNRF_L_DIR2], 256, 256, nullptr, -1};                       // d v2p^T v1
-  d.job[1] = {1, 2, 256, g->weight[CNRF_L_DIR1], 256 + a.dd, 256, nullptr, -1};                // d v1p^T feat
-  d.job[2] = {2, 1, 256, g->weight[CNRF_L_FC_OUT] + 512, 512, 256, nullptr, -1};               // d feat^T h2   (rows 1..256)
-  d.job[3] = {3, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nullptr, -1};                       // d h2p^T h1
-  d.job[4] = {4, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1], 63};        // d h1p^T [gamma | 1]
-  d.job[5] = {1, -2, 64, g->weight[CNRF_L_DIR1] + 256, 256 + a.dd, a.dd, g->bias[CNRF_L_DIR1], a.dd};   // d v1p^T [gamma(d) | 1]
+  // the per-ray tables are accumulated by the reducer warps
+  if ((rc = cnrf_fill_zero(d_b2, (size_t)a.N * 256 * sizeof(float), st))) return rc;
+  if ((rc = cnrf_fill_zero(d_bo, (size_t)a.N * 257 * sizeof(float), st))) return rc;
+  if ((rc = cnrf_fill_zero(d_br, (size_t)a.N * 3 * sizeof(float), st))) return rc;
+  float* const nil = nullptr;
+  d.job[0] = {0, 3, 256, g->weight[CNRF_L_DIR2], 256, 256, nil, -1, RED_COLSUM, g->bias[CNRF_L_DIR2], 0, nil};   // d v2p^T v1
+  d.job[1] = {1, 2, 256, g->weight[CNRF_L_DIR1], 256 + a.dd, 256, nil, -1, RED_NONE, nil, 0, nil};              // d v1p^T feat
+  d.job[2] = {2, 1, 256, g->weight[CNRF_L_FC_OUT] + 512, 512, 256, nil, -1, RED_RAY_SIGMA, d_bo + 1, 257,
+              g->weight[CNRF_L_FC_OUT]};                                                       // d feat^T h2   (rows 1..256)
+  d.job[3] = {3, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nil, -1, RED_RAY, d_b2, 256, nil};  // d h2p^T h1
+  d.job[4] = {4, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1], 63, RED_NONE, nil, 0, nil};   // d h1p^T [gamma | 1]
+  d.job[5] = {1, -2, 64, g->weight[CNRF_L_DIR1] + 256, 256 + a.dd, a.dd, g->bias[CNRF_L_DIR1], a.dd, RED_NONE, nil, 0,
+              nil};                                                                            // d v1p^T [gamma(d) | 1]
+  d.job[6] = {-1 - 4, 0, 0, nil, 0, 0, nil, -1, RED_RGB, g->weight[CNRF_L_FC_RGB], 512, nil};  // g_rgb^T v2 (no GEMM)
   {   // one CTA per SM, shared in proportion to the bytes a job streams per tile (128 KB for the four 256-wide jobs,
-      // 80 KB and 72 KB for the two 64-wide ones): the kernel is HBM-bound and a single SM only pulls ~45 GB/s
+      // 80, 72 and 64 KB for the other three): the kernel is HBM-bound and a single SM only pulls ~45 GB/s
     const int64_t halves = tiles * 2;
-    const int light = sm_count() * 18 / 148 > 0 ? sm_count() * 18 / 148 : 1;
-    const int heavy = (sm_count() - 2 * light) / 4 > 0 ? (sm_count() - 2 * light) / 4 : 1;
+    // measured shares (B200, S = 160): reducer-heavy jobs are bound by their four reducer warps, not by their bytes
+    static const int share148[DW_JOBS] = {20, 18, 30, 25, 14, 14, 26};
+    static int shares[DW_JOBS] = {0};
+    if (!shares[0]) {
+      const char* e = getenv("CNRF_DW_SHARES");       // tuning aid: seven comma-separated CTA counts
+      for (int j = 0; j < DW_JOBS; ++j) {
+        int v = share148[j] * sm_count() / 148;
+        if (e) { v = atoi(e); const char* n = strchr(e, ','); e = n ? n + 1 : nullptr; }
+        shares[j] = v > 0 ? v : 1;
+      }
+    }
+    static int job_mask = -1;      // tuning aid: CNRF_DW_JOBMASK runs a subset of the jobs (wrong gradients, right timing)
+    if (job_mask < 0) { const char* e = getenv("CNRF_DW_JOBMASK"); job_mask = e ? atoi(e) : (1 << DW_JOBS) - 1; }
     int at = 0;
-    for (int j = 0; j < 6; ++j) {
+    for (int j = 0; j < DW_JOBS; ++j) {
       d.first[j] = at;
-      const int want = j < 4 ? heavy : light;
+      const int want = !((job_mask >> j) & 1) ? 0 : shares[j];
       at += (int)(halves < want ? halves : want);
     }
-    d.first[6] = at;
+    d.first[DW_JOBS] = at;
+    const bool timed = cnrf_ktimer_begin(CNRF_KT_DW, a.M, st);
     mlp_dw_tc_kernel<<<at, DW_THREADS, DW_SMEM, st>>>(d);
     CNRF_LAUNCH_CHECK();
+    if (timed) cnrf_ktimer_end(CNRF_KT_DW, st);
   }
-
-  const unsigned cs_grid = (unsigned)((tiles + 3) / 4);
-  img_weighted_colsum_kernel<1><<<cs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 0, a.M, nullptr, 0, g->bias[CNRF_L_DIR2], 0);
-  CNRF_LAUNCH_CHECK();
-  img_weighted_colsum_kernel<1><<<cs_grid, 256, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 1 * (size_t)TILE_BYTES, a.M,
-                                                         g_raw + 3, 4, g->weight[CNRF_L_FC_OUT], 0);
-  CNRF_LAUNCH_CHECK();
-  img_weighted_colsum_kernel<3><<<cs_grid, 256, 0, st>>>(sv, SAVED_PER_TILE, SAVED_GAMMA + 4 * (size_t)TILE_BYTES, a.M,
-                                                         g_raw, 4, g->weight[CNRF_L_FC_RGB], 512);
-  CNRF_LAUNCH_CHECK();
-  const unsigned gs_grid = (unsigned)((a.N * 128 + 255) / 256);
-  img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 3 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_b2, 256);
-  CNRF_LAUNCH_CHECK();
-  img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 2 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_bo + 1, 257);
-  CNRF_LAUNCH_CHECK();
   (void)d_bd;   // layer_dir1's view-direction half and bias get their gradients from the extension job above
-  if ((rc = cnrf_strided_rowsum(g_raw, 4, a.N, a.S, a.S, 1, 3, d_br, 3, st))) return rc;
-  if ((rc = cnrf_strided_rowsum(g_raw + 3, 4, a.N, a.S, a.S, 1, 1, d_bo, 257, st))) return rc;
   return CNRF_OK;
 }

@@ -203,6 +203,9 @@ int cnrf_debug_tc_error(void);
  * (0) stops; each call returns the mean duration in ms of the launches timed so far. */
 int cnrf_debug_fwd_times(long long* host_out16, int reset);
 double cnrf_debug_fwd_kernel_ms(int64_t min_rows, int64_t* launches, int64_t* rows);
+/* The same for any of the three tensor-core kernels: which = 0 forward chain, 1 backward-data chain, 2 weight gradients;
+ * min_rows < 0 only queries. */
+double cnrf_debug_kernel_ms(int which, int64_t min_rows, int64_t* launches, int64_t* rows);
 /* C[M,N] (row stride ldc) = sum_k A[m*a_rs + k*a_cs] * B[k*b_rs + n*b_cs] through the per-ray GEMM toolkit:
  * tc = 0 the fp32 CUDA-core kernel (sgemm.cu), tc = 1 the tcgen05 kernel (gemm_tc.cu, bf16 operands).  accumulate = 1
  * adds into C.  Lets tests pin every operand-majorness combination the per-ray layers use. */
