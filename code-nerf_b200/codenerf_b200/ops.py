@@ -320,12 +320,74 @@ class _Field(torch.autograd.Function):
         return (None, g_pts, g_rd, g_zs, g_zt, None, None) + grads
 
 
+class _FieldIds(torch.autograd.Function):
+    """forward_pass with the embedding lookup of train.py:96 folded in: ids (N,) int64, tab_s / tab_t (num_codes, C) are
+    the ShapeTextureEmbedding tables.  Rays with the same id as their predecessor share the code-layer work, and the
+    backward returns dense table gradients directly (what torch.nn.Embedding's backward accumulates)."""
+
+    @staticmethod
+    def forward(ctx, cfg, pts, rd, ids, tab_s, tab_t, freqs_xyz, freqs_dir, *params):
+        _req_cuda(pts, rd, ids, tab_s, tab_t, *params)
+        lib = _lib.load()
+        hidden, code, dim_xyz, dim_dir, pairing, precision = cfg
+        pts, rd, ids = _c(pts), _c(rd), ids.contiguous()
+        tab_s, ld_s = _rows(tab_s)
+        tab_t, ld_t = _rows(tab_t)
+        params = tuple(_c(p) for p in params)
+        N, S = pts.shape[0], pts.shape[1]
+        assert ids.dtype == torch.int64 and ids.shape == (N,), "ids must be (N,) int64"
+        assert tab_s.shape[0] == tab_t.shape[0], "shape and texture tables must have the same number of rows"
+        keep = int(any(ctx.needs_input_grad))
+        shp = _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, keep)
+        saved = _bytes(lib.cnrf_codenerf_saved_bytes(C.byref(shp)), pts.device)
+        ws = _bytes(lib.cnrf_field_workspace_bytes(C.byref(shp), 0), pts.device)
+        raw = torch.empty((N, S, 4), dtype=_f32, device=pts.device)
+        tab = _ptr_table(params)
+        check(lib.cnrf_field_fwd_ids(C.byref(shp), C.byref(tab), _p(pts), _p(rd), _p(freqs_xyz), freqs_xyz.shape[0],
+                                     _p(freqs_dir), freqs_dir.shape[0], _p(ids), tab_s.shape[0], _p(tab_s), ld_s,
+                                     _p(tab_t), ld_t, _p(raw), _p(saved) if keep else None, saved.numel() if keep else 0,
+                                     _p(ws), ws.numel(), _stream()), "cnrf_field_fwd_ids")
+        if keep:
+            ctx.save_for_backward(pts, rd, ids, tab_s, tab_t, freqs_xyz, freqs_dir, saved, *params)
+            ctx.cfg, ctx.lds = cfg, (ld_s, ld_t)
+        return raw
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_raw):
+        pts, rd, ids, tab_s, tab_t, freqs_xyz, freqs_dir, saved, *params = ctx.saved_tensors
+        lib = _lib.load()
+        hidden, code, dim_xyz, dim_dir, pairing, precision = ctx.cfg
+        ld_s, ld_t = ctx.lds
+        N, S = pts.shape[0], pts.shape[1]
+        shp = _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, 1)
+        g_raw = _c(g_raw)
+        dev = pts.device
+        grads = tuple(torch.empty_like(p) for p in params)
+        g_ts = torch.empty((tab_s.shape[0], code), dtype=_f32, device=dev)
+        g_tt = torch.empty((tab_t.shape[0], code), dtype=_f32, device=dev)
+        ws = _bytes(lib.cnrf_field_workspace_bytes(C.byref(shp), 1), dev)
+        tab, gtab = _ptr_table(params), _ptr_table(grads)
+        check(lib.cnrf_field_bwd_ids(C.byref(shp), C.byref(tab), _p(pts), _p(rd), _p(freqs_xyz), freqs_xyz.shape[0],
+                                     _p(freqs_dir), freqs_dir.shape[0], _p(ids), tab_s.shape[0], _p(tab_s), ld_s,
+                                     _p(tab_t), ld_t, _p(g_raw), _p(saved), saved.numel(), C.byref(gtab), _p(g_ts),
+                                     _p(g_tt), _p(ws), ws.numel(), _stream()), "cnrf_field_bwd_ids")
+        return (None, None, None, None, g_ts, g_tt, None, None) + grads
+
+
 def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code, dim_xyz, dim_dir,
-                   pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_BF16):
-    """params: the 18 tensors (weight, bias per layer) in _lib.LAYER_NAMES order."""
+                   pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_BF16, code_source=None):
+    """params: the 18 tensors (weight, bias per layer) in _lib.LAYER_NAMES order.
+
+    code_source = (ids, shape_table, texture_table): z_s / z_t are the rows ids of those tables (ShapeTextureEmbedding's
+    output); the bf16 path then shares the code-layer work between rays of equal id (_FieldIds)."""
     if precision == _lib.PRECISION_BF16 and (pts.requires_grad or rd.requires_grad) and torch.is_grad_enabled():
         precision = _lib.PRECISION_FP32   # ray / point gradients (camera-pose optimisation, eval.py:129-168) run in fp32
     cfg = (hidden, code, dim_xyz, dim_dir, pairing, precision)
+    if code_source is not None and precision == _lib.PRECISION_BF16:
+        ids, tab_s, tab_t = code_source
+        if ids.dim() == 1 and ids.shape[0] == pts.shape[0] and ids.dtype == torch.int64:
+            return _FieldIds.apply(cfg, pts, rd, ids, tab_s, tab_t, freqs_xyz, freqs_dir, *params)
     return _Field.apply(cfg, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, *params)
 
 

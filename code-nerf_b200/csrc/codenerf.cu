@@ -33,6 +33,7 @@ struct Dims {
   int H, C, dx, dd, S, pairing;
   int64_t N, M;
   bool tc;   // per-ray GEMMs on the tensor cores (gemm_tc.cu) instead of the fp32 SIMT toolkit
+  const int32_t* rows_dev = nullptr;   // shared-code mode: device-resident number of code runs (<= N), see code_runs.cu
 };
 inline Dims dims_of(const cnrf_field_shape* s) {
   Dims d;
@@ -132,6 +133,7 @@ GemmArgs mk_lin(const float* X, int64_t ldx, int64_t rows, int K, const float* W
   GemmArgs g;
   g.A = X; g.a_rs = ldx; g.a_cs = 1; g.B = W; g.b_rs = 1; g.b_cs = ldw; g.C = Y; g.ldc = ldy;
   g.M = rows; g.N = Nout; g.K = K; g.bias = bias; g.ld_bias = 0; g.relu = relu;
+  g.rows_dim = 1;
   return g;
 }
 GemmArgs mk_dgrad(const float* dY, int64_t ldy, int64_t rows, int Nout, const float* W, int64_t ldw, int K, float* dX,
@@ -139,6 +141,7 @@ GemmArgs mk_dgrad(const float* dY, int64_t ldy, int64_t rows, int Nout, const fl
   GemmArgs g;
   g.A = dY; g.a_rs = ldy; g.a_cs = 1; g.B = W; g.b_rs = ldw; g.b_cs = 1; g.C = dX; g.ldc = ldx;
   g.M = rows; g.N = K; g.K = Nout; g.mask = mask; g.ld_mask = ldm; g.accumulate = accumulate;
+  g.rows_dim = 1;
   return g;
 }
 GemmArgs mk_wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int64_t rows, int Nout, int K, float* dW,
@@ -150,6 +153,7 @@ GemmArgs mk_wgrad(const float* dY, int64_t ldy, const float* X, int64_t ldx, int
   int64_t want = (1184 + tiles - 1) / tiles, cap = (rows + 511) / 512;
   g.split_k = (int)std::max<int64_t>(1, std::min<int64_t>(want, cap));
   if (g.split_k == 1) g.accumulate = 1;   // += into the zero-filled buffer
+  g.rows_dim = 2;
   return g;
 }
 // out[0, n] += sum_m X[m, n] as ones^T X (out zero-filled by the caller)
@@ -159,9 +163,12 @@ GemmArgs mk_colsum(const float* ones, const float* X, int64_t ldx, int64_t rows,
 struct Batch {
   GemmArgs g[CNRF_GEMM_BATCH_MAX];
   int n = 0;
-  void add(const GemmArgs& a) { g[n++] = a; }
+  const int32_t* rows_dev = nullptr;       // every problem of the batch runs over this many rows (device-resident)
+  explicit Batch(const int32_t* rd = nullptr) : rows_dev(rd) {}
+  void add(const GemmArgs& a) { g[n] = a; g[n].rows_dev = rows_dev; ++n; }
   int flush(bool tc, cudaStream_t st) {
     int rc = tc ? cnrf_gemm_tc_batch(g, n, st) : CNRF_E_UNSUPPORTED;
+    if (rc == CNRF_E_UNSUPPORTED && rows_dev) return rc;      // only the tensor-core kernel reads a device-side row count
     if (rc == CNRF_E_UNSUPPORTED) {
       rc = CNRF_OK;
       for (int i = 0; i < n && rc == CNRF_OK; ++i) rc = cnrf_sgemm(g[i], st);
@@ -175,7 +182,7 @@ int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir
                 int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
                 bool split_bo, cudaStream_t st) {
   const int H = d.H, C = d.C;
-  Batch b;
+  Batch b(d.rows_dev);
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 1));     // model.py:174
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 1));     // :175
   b.add(mk_lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 1));  // :177
@@ -208,7 +215,7 @@ int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codener
     f.add(ones, d.N, 1.0f);
     RUN(cnrf_fill_batch(f, st));
   }
-  Batch b;
+  Batch b(d.rows_dev);
   // texture branch: betar = Wrt at + br;   shape branch 2: betao = Woc as2 + bo;   shape branch 1: beta2 = W2c as1 + b2;
   // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
   b.add(mk_wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C));
@@ -345,7 +352,8 @@ extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32
     if (!backward) return b + (s->keep ? 0 : saved_f32_bytes(d));     // inference still needs the activation buffers
     return b + 2 * al(d.M * max_sz(d.H, d.C + 1)) + 3 * al(d.N * d.C) + al(d.N);
   }
-  return b + 3 * al(d.N * d.C) + al(d.N) + (s->keep || backward ? 0 : 3 * al(d.N * d.C)) + cnrf_tc_workspace_bytes(d.N, d.M, backward);
+  return b + 3 * al(d.N * d.C) + al(d.N) + (s->keep || backward ? 0 : 3 * al(d.N * d.C)) + cnrf_tc_workspace_bytes(d.N, d.M, backward) +
+         cnrf_code_runs_bytes(d.N) + 256 + 4 * al(d.N * d.C);      // shared-code mode: runs, one code row and gradient row per run
 }
 
 // tensor-core per-sample chain (mlp_tc.cu).  x_xyz == nullptr means "encode pts in-kernel" (field mode).
@@ -357,6 +365,7 @@ struct TcChainArgs {
   const float *b2, *bo, *br, *bd;             // per-ray bias tables [N,256],[N,257],[N,3],[N,256]
   const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
+  const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
 };
 int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
                       cudaStream_t st);
@@ -370,7 +379,25 @@ struct FieldIn {   // everything the two entry-point families share
   const float* x_xyz; int64_t ld_xyz; const float* x_dir; int64_t ld_dir;
   const float* z_s; int64_t ld_zs; const float* z_t; int64_t ld_zt;
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;     // only for the fused bf16 field path
+  // shared-code mode (bf16 only): z_s / z_t are TABLES [num_codes, C] indexed by ids[ray]; g_z_s / g_z_t of the backward
+  // are table-shaped dense gradients
+  const int64_t* ids = nullptr; int64_t num_codes = 0;
 };
+
+// shared-code mode: find the runs of equal ids and gather one code row per run
+struct SharedCodes { CodeRuns runs; float *zc_s, *zc_t; };
+int setup_shared_codes(Dims& d, const FieldIn& in, Arena& w, SharedCodes& sc, cudaStream_t st) {
+  size_t rb = cnrf_code_runs_bytes(d.N);
+  float* rbase = w.take(rb / sizeof(float));
+  sc.zc_s = w.take(d.N * d.C); sc.zc_t = w.take(d.N * d.C);
+  if (!w.ok) return CNRF_E_WORKSPACE;
+  sc.runs = cnrf_code_runs_carve(rbase, d.N);
+  RUN(cnrf_code_runs(in.ids, d.N, in.num_codes, sc.runs, st));
+  RUN(cnrf_gather_codes(in.ids, sc.runs, d.N, d.C, in.z_s, in.ld_zs, sc.zc_s, st));
+  RUN(cnrf_gather_codes(in.ids, sc.runs, d.N, d.C, in.z_t, in.ld_zt, sc.zc_t, st));
+  d.rows_dev = sc.runs.count;
+  return CNRF_OK;
+}
 
 int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const FieldIn& in, float* raw,
                       void* saved, size_t saved_bytes, void* ws, size_t ws_bytes, cudaStream_t st) {
@@ -379,6 +406,7 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   Tables t;
   carve_tables(d, w, t);
   if (!w.ok) return CNRF_E_WORKSPACE;
+  if (in.ids && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
   if (s->precision == CNRF_PRECISION_FP32) {
     SavedF32 sv;
     if (s->keep) {
@@ -405,9 +433,16 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
     as1 = w.take(d.N * d.C); as2 = w.take(d.N * d.C); at = w.take(d.N * d.C);
     if (!w.ok) return CNRF_E_WORKSPACE;
   }
-  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, t, true, st));
+  const float *zs = in.z_s, *zt = in.z_t;
+  int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
+  SharedCodes sc;
+  if (in.ids) {
+    RUN(setup_shared_codes(d, in, w, sc, st));
+    zs = sc.zc_s; zt = sc.zc_t; ld_zs = ld_zt = d.C;
+  }
+  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, t, true, st));
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, t.b2, t.bo, t.br, t.bd, t.bof, t.bos, in.x_dir, in.ld_dir};
+                in.inc_xyz, t.b2, t.bo, t.br, t.bd, t.bof, t.bos, in.x_dir, in.ld_dir, in.ids ? sc.runs.gid : nullptr};
   return cnrf_tc_chain_fwd(a, raw, tc_saved, tc_saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
 
@@ -422,6 +457,7 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   float* tmp = w.take(d.N * d.C);          // 3 x [N,C] + [N], contiguous (per_ray_bwd)
   w.take(d.N * d.C); w.take(d.N * d.C); w.take(d.N);
   if (!w.ok) return CNRF_E_WORKSPACE;
+  if (in.ids && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
   RUN(zero_weight_grads(d, g, st));
   if (s->precision == CNRF_PRECISION_FP32) {
     SavedF32 sv;
@@ -438,12 +474,31 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   Arena sa(const_cast<void*>(saved), saved_bytes);
   float* as1 = sa.take(d.N * d.C); float* as2 = sa.take(d.N * d.C); float* at = sa.take(d.N * d.C);
   if (!sa.ok) return CNRF_E_WORKSPACE;
+  const float *zs = in.z_s, *zt = in.z_t;
+  int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
+  float *gz_s = g_z_s, *gz_t = g_z_t;
+  SharedCodes sc;
+  if (in.ids) {          // the runs are cheap to find again; nothing of them is kept between the passes
+    RUN(setup_shared_codes(d, in, w, sc, st));
+    zs = sc.zc_s; zt = sc.zc_t; ld_zs = ld_zt = d.C;
+    gz_s = w.take(d.N * d.C); gz_t = w.take(d.N * d.C);
+    if (!w.ok) return CNRF_E_WORKSPACE;
+  }
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, in.x_dir, in.ld_dir};
+                in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, in.x_dir, in.ld_dir,
+                in.ids ? sc.runs.gid : nullptr};
   RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, dt.bd, g_x_xyz,
                         w.base + w.off, w.cap - w.off, st));
-  return per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, in.z_s, in.ld_zs, in.z_t, in.ld_zt, as1, as2, at, dt, tmp, g_z_s,
-                     g_z_t, g_x_dir, st);
+  RUN(per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, dt, tmp, gz_s, gz_t, g_x_dir, st));
+  if (in.ids) {          // one row per run -> dense table gradients (what torch.nn.Embedding's backward produces)
+    FillBatch f;
+    f.add(g_z_s, in.num_codes * d.C);
+    f.add(g_z_t, in.num_codes * d.C);
+    RUN(cnrf_fill_batch(f, st));
+    RUN(cnrf_scatter_code_grads(in.ids, sc.runs, d.N, d.C, gz_s, g_z_s, d.C, st));
+    RUN(cnrf_scatter_code_grads(in.ids, sc.runs, d.N, d.C, gz_t, g_z_t, d.C, st));
+  }
+  return CNRF_OK;
 }
 
 int check_common(const cnrf_field_shape* s, const cnrf_codenerf_params* p) {
@@ -542,45 +597,42 @@ extern "C" size_t cnrf_field_workspace_bytes(const cnrf_field_shape* s, int32_t 
   return field_scratch_bytes(dims_of(s), s->precision, backward) + cnrf_codenerf_workspace_bytes(s, backward);
 }
 
-extern "C" int cnrf_field_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
-                              const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
-                              int32_t L_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
-                              float* raw, void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes,
-                              cnrf_stream_t stream) {
+namespace {
+int field_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                   const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
+                   int64_t num_codes, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, float* raw,
+                   void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   RUN(check_common(s, p));
   CNRF_REQUIRE(pts && rd && freqs_xyz && freqs_dir && z_s && z_t && raw && workspace, CNRF_E_NULL);
   int incx, incd;
   RUN(check_field(s, L_xyz, L_dir, incx, incd));
-  cudaStream_t st = as_stream(stream);
   Dims d = dims_of(s);
   Arena w(workspace, workspace_bytes);
   FieldScratch f;
   carve_field(d, s->precision, 0, w, f);
   if (!w.ok) return CNRF_E_WORKSPACE;
   RUN(field_encode(d, s->precision, pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
-  FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx};
+  FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx, ids, num_codes};
   return codenerf_fwd_impl(s, p, in, raw, saved, saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
 
-extern "C" int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
-                              const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
-                              int32_t L_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
-                              const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g,
-                              float* g_z_s, float* g_z_t, float* g_pts, float* g_rd, void* workspace,
-                              size_t workspace_bytes, cnrf_stream_t stream) {
+int field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                   const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
+                   int64_t num_codes, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
+                   const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s,
+                   float* g_z_t, float* g_pts, float* g_rd, void* workspace, size_t workspace_bytes, cudaStream_t st) {
   RUN(check_common(s, p));
   CNRF_REQUIRE(pts && rd && freqs_xyz && freqs_dir && z_s && z_t && g_raw && g && g_z_s && g_z_t && workspace,
                CNRF_E_NULL);
   int incx, incd;
   RUN(check_field(s, L_xyz, L_dir, incx, incd));
-  cudaStream_t st = as_stream(stream);
   Dims d = dims_of(s);
   Arena w(workspace, workspace_bytes);
   FieldScratch f;
   carve_field(d, s->precision, 1, w, f);
   if (!w.ok) return CNRF_E_WORKSPACE;
   RUN(field_encode(d, s->precision, pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
-  FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx};
+  FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx, ids, num_codes};
   RUN(codenerf_bwd_impl(s, p, in, g_raw, saved, saved_bytes, g, g_z_s, g_z_t, g_pts ? f.g_xemb : nullptr,
                         g_rd ? f.g_demb : nullptr, w.base + w.off, w.cap - w.off, st));
   if (g_pts) RUN(cnrf_pos_embed_bwd_ld(pts, f.g_xemb, d.M, 3, freqs_xyz, L_xyz, incx, d.dx, g_pts, st));
@@ -590,4 +642,50 @@ extern "C" int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_par
     CNRF_LAUNCH_CHECK();
   }
   return CNRF_OK;
+}
+}  // namespace
+
+extern "C" int cnrf_field_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
+                              const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
+                              int32_t L_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
+                              float* raw, void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes,
+                              cnrf_stream_t stream) {
+  return field_fwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, nullptr, 0, z_s, ld_zs, z_t, ld_zt, raw, saved,
+                        saved_bytes, workspace, workspace_bytes, as_stream(stream));
+}
+
+extern "C" int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
+                              const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
+                              int32_t L_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
+                              const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g,
+                              float* g_z_s, float* g_z_t, float* g_pts, float* g_rd, void* workspace,
+                              size_t workspace_bytes, cnrf_stream_t stream) {
+  return field_bwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, nullptr, 0, z_s, ld_zs, z_t, ld_zt, g_raw, saved,
+                        saved_bytes, g, g_z_s, g_z_t, g_pts, g_rd, workspace, workspace_bytes, as_stream(stream));
+}
+
+// Shared-code variants: the embedding lookup of train.py:96 (ShapeTextureEmbedding.forward, models/model.py:100-103)
+// fused into the field.  ids [N] int64 on the device; tab_s / tab_t [num_codes, C] are the two embedding tables.
+extern "C" int cnrf_field_fwd_ids(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
+                                  const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
+                                  int32_t L_dir, const int64_t* ids, int64_t num_codes, const float* tab_s, int64_t ld_s,
+                                  const float* tab_t, int64_t ld_t, float* raw, void* saved, size_t saved_bytes,
+                                  void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+  CNRF_REQUIRE(ids, CNRF_E_NULL);
+  CNRF_REQUIRE(num_codes > 0, CNRF_E_SHAPE);
+  return field_fwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, ids, num_codes, tab_s, ld_s, tab_t, ld_t, raw,
+                        saved, saved_bytes, workspace, workspace_bytes, as_stream(stream));
+}
+
+extern "C" int cnrf_field_bwd_ids(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
+                                  const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
+                                  int32_t L_dir, const int64_t* ids, int64_t num_codes, const float* tab_s, int64_t ld_s,
+                                  const float* tab_t, int64_t ld_t, const float* g_raw, const void* saved,
+                                  size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_tab_s, float* g_tab_t,
+                                  void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+  CNRF_REQUIRE(ids, CNRF_E_NULL);
+  CNRF_REQUIRE(num_codes > 0, CNRF_E_SHAPE);
+  return field_bwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, ids, num_codes, tab_s, ld_s, tab_t, ld_t, g_raw,
+                        saved, saved_bytes, g, g_tab_s, g_tab_t, nullptr, nullptr, workspace, workspace_bytes,
+                        as_stream(stream));
 }

@@ -98,16 +98,21 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   int p = 0;
   while (p + 1 < b.count && (int)blockIdx.x >= b.first[p + 1]) ++p;
-  const GemmArgs& g = b.g[p];
+  GemmArgs g = b.g[p];
+  const bool multi_k = (g.K + b.kslice[p] - 1) / b.kslice[p] > 1;      // decided by the worst-case K the host saw
+  if (g.rows_dev) {                                    // run-time row count (code_runs.cu): idle CTAs leave at once
+    const int64_t rows = *g.rows_dev;
+    if (g.rows_dim == 1) g.M = min(g.M, rows); else g.K = min(g.K, rows);
+  }
   const int a_mn = b.a_mn[p], b_mn = b.b_mn[p];
   const int local = blockIdx.x - b.first[p];
   const int mx = local % b.mt[p], rest = local / b.mt[p];
   const int ny = rest % b.nt[p], kz = rest / b.nt[p];
-  const bool multi_k = (g.K + b.kslice[p] - 1) / b.kslice[p] > 1;
   const int64_t m0 = (int64_t)mx * GBM;
   const int64_t n0 = (int64_t)ny * GBN;
   const int64_t kbeg = (int64_t)kz * b.kslice[p];
   const int64_t kend = min(g.K, kbeg + b.kslice[p]);
+  if (m0 >= g.M || kbeg >= g.K) return;
 
   if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
   if (warp == 1) tmem_alloc(&tmem_slot, 64);

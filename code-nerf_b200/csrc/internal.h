@@ -16,6 +16,9 @@ struct GemmArgs {
   const float* mask = nullptr; int64_t ld_mask = 0;
   int accumulate = 0;   // C += result (no bias/relu/mask)
   int split_k = 1;      // > 1: partial sums are atomically added into C, which the caller zero-fills
+  // tensor-core kernel only: a device-resident row count that shrinks M (rows_dim = 1) or K (rows_dim = 2) at run time;
+  // M / K above are then the worst case the launch is sized for (code_runs.cu)
+  const int32_t* rows_dev = nullptr; int rows_dim = 0;
 };
 int cnrf_sgemm(const GemmArgs& a, cudaStream_t st);
 // gemm_tc.cu: the same contract on the tensor cores (bf16 operands, fp32 accumulate); CNRF_E_UNSUPPORTED when neither
@@ -46,3 +49,13 @@ int cnrf_pos_embed_bwd_ld(const float* x, const float* g_out, int64_t M, int D, 
 enum { CNRF_KT_FWD = 0, CNRF_KT_BWD = 1, CNRF_KT_DW = 2, CNRF_KT_COUNT = 3 };
 bool cnrf_ktimer_begin(int which, int64_t rows, cudaStream_t st);   // true: timing, call cnrf_ktimer_end after the launch
 void cnrf_ktimer_end(int which, cudaStream_t st);
+
+// ---- code_runs.cu: runs of rays that share one latent-code row (device-resident run count) ------------------------------
+struct CodeRuns { int32_t* gid = nullptr; int32_t* rep = nullptr; int32_t* count = nullptr; };
+size_t cnrf_code_runs_bytes(int64_t N);
+CodeRuns cnrf_code_runs_carve(void* base /*256-byte aligned*/, int64_t N);
+int cnrf_code_runs(const int64_t* ids, int64_t N, int64_t num_codes, const CodeRuns& r, cudaStream_t st);
+int cnrf_gather_codes(const int64_t* ids, const CodeRuns& r, int64_t N, int C, const float* tab, int64_t ld, float* out,
+                      cudaStream_t st);
+int cnrf_scatter_code_grads(const int64_t* ids, const CodeRuns& r, int64_t N, int C, const float* g_codes, float* g_tab,
+                            int64_t ld, cudaStream_t st);

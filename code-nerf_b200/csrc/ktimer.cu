@@ -1,5 +1,6 @@
 // Kernel timers for bench.py's roofline leg and the tuning scripts: CUDA events around one of the three tensor-core
 // kernels on its launching stream (off by default; no host synchronisation until the query).
+#include "common.cuh"
 #include "internal.h"
 
 namespace {

@@ -64,16 +64,20 @@ struct Epi {               // per-thread state of an epilogue thread for the cur
   uint32_t tacc;
   int r, bar_id, slot, nrays;
   bool elected, valid, staged;
-  int64_t m, ray, pair, ray0;
+  int64_t m, ray0;
+  int row;                 // this thread's row of the per-ray bias tables (its ray, or the ray's code run)
   uint8_t* sv;
   float sigma;
+  float px, py, pz;        // this row's sample point of the NEXT pair (prefetched while the current pair runs)
 };
 
 // copy the `nrays` bias rows [ray0, ray0 + nrays) of a [N,256] fp32 table into the tile's staging area (128 threads)
-__device__ __forceinline__ void stage_rows(const Epi& c, const float* table) {
+__device__ __forceinline__ void stage_rows(const Epi& c, const float* table, const int32_t* gid) {
   if (c.staged) {
-    for (int piece = c.r; piece < c.nrays * 64; piece += 128)
-      cp_async16(c.stage + piece * 4, table + (c.ray0 + (piece >> 6)) * 256 + (piece & 63) * 4);
+    for (int piece = c.r; piece < c.nrays * 64; piece += 128) {
+      const int64_t ray = c.ray0 + (piece >> 6);
+      cp_async16(c.stage + piece * 4, table + (gid ? (int64_t)__ldg(gid + ray) : ray) * 256 + (piece & 63) * 4);
+    }
   }
   cp_async_commit();
 }
@@ -85,8 +89,8 @@ template <int E, bool GB>
 __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint32_t parity) {
   const float4* gb = nullptr;
   const float4* sb = nullptr;
-  if (E == 1) { if (GB) gb = reinterpret_cast<const float4*>(a.b2 + c.ray * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
-  if (E == 2) { if (GB) gb = reinterpret_cast<const float4*>(a.bof + c.ray * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
+  if (E == 1) { if (GB) gb = reinterpret_cast<const float4*>(a.b2 + (int64_t)c.row * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
+  if (E == 2) { if (GB) gb = reinterpret_cast<const float4*>(a.bof + (int64_t)c.row * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
   if (E == 4) sb = reinterpret_cast<const float4*>(c.heads + 1024);
   float4 bcur[8], bnxt[8];
   float tail0 = 0.f, tail1 = 0.f, tail2 = 0.f;
@@ -94,8 +98,8 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
 #pragma unroll
     for (int j = 0; j < 8; ++j) bcur[j] = __ldg(gb + j);
   }
-  if (E == 1 && c.valid) tail0 = __ldg(a.bos + c.ray);
-  if (E == 4 && c.valid) { tail0 = __ldg(a.br + c.ray * 3); tail1 = __ldg(a.br + c.ray * 3 + 1); tail2 = __ldg(a.br + c.ray * 3 + 2); }
+  if (E == 1 && c.valid) tail0 = __ldg(a.bos + c.row);
+  if (E == 4 && c.valid) { const float* brp = a.br + (int64_t)c.row * 3; tail0 = __ldg(brp); tail1 = __ldg(brp + 1); tail2 = __ldg(brp + 2); }
   const long long tw0 = clock64();
   if (!fwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
   const long long tw1 = clock64();
@@ -104,7 +108,8 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if ((E == 1 || E == 2) && !GB) cp_async_wait_all();
   named_bar_sync(c.bar_id, 128);
   const float4* hw = reinterpret_cast<const float4*>(c.heads);
-  float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f;
+  float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f, rgb3 = 0.f, rgb4 = 0.f, rgb5 = 0.f;   // two partial sums per channel
+  float sg0 = 0.f, sg1 = 0.f, sg2 = 0.f, sg3 = 0.f;                               // four partial sums of the sigma head
   uint32_t sgn[8];                                  // sign bits of the pre-activations (the backward's ReLU mask)
 #pragma unroll
   for (int cb = 0; cb < 8; ++cb) {
@@ -134,8 +139,8 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 w = hw[cb * 8 + j];
-        c.sigma = fmaf(fmaxf(f[4 * j], 0.f), w.x, c.sigma); c.sigma = fmaf(fmaxf(f[4 * j + 1], 0.f), w.y, c.sigma);
-        c.sigma = fmaf(fmaxf(f[4 * j + 2], 0.f), w.z, c.sigma); c.sigma = fmaf(fmaxf(f[4 * j + 3], 0.f), w.w, c.sigma);
+        sg0 = fmaf(fmaxf(f[4 * j], 0.f), w.x, sg0); sg1 = fmaf(fmaxf(f[4 * j + 1], 0.f), w.y, sg1);
+        sg2 = fmaf(fmaxf(f[4 * j + 2], 0.f), w.z, sg2); sg3 = fmaf(fmaxf(f[4 * j + 3], 0.f), w.w, sg3);
       }
     }
     if (E == 4) {                                   // rgb_raw = Wrv v2 + betar[ray]                (fc_rgb)
@@ -144,9 +149,9 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
         const float x0 = fmaxf(f[4 * j], 0.f), x1 = fmaxf(f[4 * j + 1], 0.f), x2 = fmaxf(f[4 * j + 2], 0.f),
                     x3 = fmaxf(f[4 * j + 3], 0.f);
         const float4 w0 = hw[64 + cb * 8 + j], w1 = hw[128 + cb * 8 + j], w2 = hw[192 + cb * 8 + j];
-        rgb0 = fmaf(x0, w0.x, fmaf(x1, w0.y, fmaf(x2, w0.z, fmaf(x3, w0.w, rgb0))));
-        rgb1 = fmaf(x0, w1.x, fmaf(x1, w1.y, fmaf(x2, w1.z, fmaf(x3, w1.w, rgb1))));
-        rgb2 = fmaf(x0, w2.x, fmaf(x1, w2.y, fmaf(x2, w2.z, fmaf(x3, w2.w, rgb2))));
+        rgb0 = fmaf(x0, w0.x, fmaf(x1, w0.y, rgb0)); rgb3 = fmaf(x2, w0.z, fmaf(x3, w0.w, rgb3));
+        rgb1 = fmaf(x0, w1.x, fmaf(x1, w1.y, rgb1)); rgb4 = fmaf(x2, w1.z, fmaf(x3, w1.w, rgb4));
+        rgb2 = fmaf(x0, w2.x, fmaf(x1, w2.y, rgb2)); rgb5 = fmaf(x2, w2.z, fmaf(x3, w2.w, rgb5));
       }
     }
     if (E != 2) {
@@ -169,9 +174,9 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
     mp[0] = make_uint4(sgn[0], sgn[1], sgn[2], sgn[3]);
     mp[1] = make_uint4(sgn[4], sgn[5], sgn[6], sgn[7]);
   }
-  if (E == 1) c.sigma += tail0;
+  if (E == 1) c.sigma = (sg0 + sg1) + (sg2 + sg3) + tail0;
   if (E == 4 && c.valid)                            // [rgb_raw | sigma_raw]   models/model.py:194
-    reinterpret_cast<float4*>(a.raw)[c.m] = make_float4(rgb0 + tail0, rgb1 + tail1, rgb2 + tail2, c.sigma);
+    reinterpret_cast<float4*>(a.raw)[c.m] = make_float4(rgb0 + rgb3 + tail0, rgb1 + rgb4 + tail1, rgb2 + rgb5 + tail2, c.sigma);
   fence_proxy_async();
   tc_fence_before();
   named_bar_sync(c.bar_id, 128);
@@ -305,26 +310,54 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     c.elected = ((warp - 2) & 3) == 0 && lane == 0;
     c.tacc = tmem + t * 256 + ((uint32_t)(q * 32) << 16);
     uint32_t na = 0;
+    // the usual encoding (include_input, L = 10 octaves from 1.0) is built in registers from prefetched points
+    bool pe_fast = a.pts != nullptr && a.inc && a.L == 10;
+    if (pe_fast) {
+#pragma unroll
+      for (int k = 0; k < 10; ++k) pe_fast = pe_fast && __ldg(a.freqs + k) == (float)(1 << k);
+    }
+    c.px = c.py = c.pz = 0.f;
+    if (pe_fast) {
+      const int64_t m1 = ((int64_t)blockIdx.x * 2 + t) * TILE + c.r;
+      if (m1 < a.M) { c.px = __ldg(a.pts + m1 * 3); c.py = __ldg(a.pts + m1 * 3 + 1); c.pz = __ldg(a.pts + m1 * 3 + 2); }
+    }
     for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
       const int64_t tile_idx = pr * 2 + t;
       const int64_t first = tile_idx * TILE;
       c.m = first + c.r;
       c.valid = c.m < a.M;
-      c.ray = c.valid ? c.m / a.S : 0;
-      c.pair = c.valid ? (a.pairing == CNRF_PAIRING_REFERENCE ? c.m % a.N : c.ray) : 0;
-      c.ray0 = first < a.M ? first / a.S : 0;
+      // rays of this tile (32-bit arithmetic whenever the row count allows: these divisions sit on every tile's start)
+      int64_t ray, last_ray;
       const int64_t last = (first + TILE - 1 < a.M ? first + TILE - 1 : a.M - 1);
-      c.nrays = first < a.M ? (int)(last / a.S - c.ray0) + 1 : 0;
+      if (a.M < (1ll << 31)) {
+        const uint32_t S = (uint32_t)a.S;
+        ray = c.valid ? (uint32_t)c.m / S : 0;
+        c.ray0 = first < a.M ? (uint32_t)first / S : 0;
+        last_ray = first < a.M ? (uint32_t)last / S : 0;
+      } else {
+        ray = c.valid ? c.m / a.S : 0;
+        c.ray0 = first < a.M ? first / a.S : 0;
+        last_ray = first < a.M ? last / a.S : 0;
+      }
+      c.row = (int)((a.gid && c.valid) ? (int64_t)__ldg(a.gid + ray) : ray);
+      c.nrays = first < a.M ? (int)(last_ray - c.ray0) + 1 : 0;
       c.staged = c.nrays <= RMAX;
-      c.slot = c.valid ? (int)(c.ray - c.ray0) : 0;
+      c.slot = c.valid ? (int)(ray - c.ray0) : 0;
       c.sv = (a.saved && tile_idx < num_tiles) ? a.saved + (size_t)tile_idx * SAVED_PER_TILE : nullptr;
       c.sigma = 0.f;
       // ---- input image: gamma(x); the bias rows of layer_xyz2 travel to smem meanwhile ----
       const long long tb0 = clock64();
       if (c.elected) bulk_wait_read0();               // the previous pair's last image store has finished reading smem
       named_bar_sync(c.bar_id, 128);
-      stage_rows(c, a.b2);
-      build_input_row(a, c.m, c.valid, c.tile, c.r);
+      stage_rows(c, a.b2, a.gid);
+      if (pe_fast) {
+        const float x[3] = {c.px, c.py, c.pz};
+        build_input_row_octaves<10>(x, c.valid, c.tile, c.r);
+        const int64_t mn = c.m + (int64_t)gridDim.x * 2 * TILE;          // same row of this CTA's next pair
+        if (mn < a.M) { c.px = __ldg(a.pts + mn * 3); c.py = __ldg(a.pts + mn * 3 + 1); c.pz = __ldg(a.pts + mn * 3 + 2); }
+      } else {
+        build_input_row(a, c.m, c.valid, c.tile, c.r);
+      }
       fence_proxy_async();
       named_bar_sync(c.bar_id, 128);
       if (c.elected) {
@@ -335,7 +368,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       bool ok = epi_layer<0, false>(a, c, t, na & 1); ++na;
       if (ok) { ok = c.staged ? epi_layer<1, false>(a, c, t, na & 1) : epi_layer<1, true>(a, c, t, na & 1); ++na; }
       if (ok) {
-        stage_rows(c, a.bof);                         // every thread of the tile is past its reads of the beta2 rows
+        stage_rows(c, a.bof, a.gid);                       // every thread of the tile is past its reads of the beta2 rows
         ok = c.staged ? epi_layer<2, false>(a, c, t, na & 1) : epi_layer<2, true>(a, c, t, na & 1); ++na;
       }
       if (ok) { ok = epi_layer<3, false>(a, c, t, na & 1); ++na; }

@@ -71,6 +71,7 @@ struct TcChainArgs {   // mirrors the declaration in codenerf.cu
   const float *b2, *bo, *br, *bd;
   const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
+  const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
 };
 
 static inline size_t up1k(size_t b) { return (b + 1023) & ~size_t(1023); }
@@ -152,7 +153,7 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   FwdArgs f;
   f.N = a.N; f.M = a.M; f.S = a.S; f.pairing = a.pairing; f.dx = a.dx;
   f.pts = a.pts; f.x_xyz = a.x_xyz; f.ld_xyz = a.ld_xyz; f.freqs = a.freqs_xyz; f.L = a.L_xyz; f.inc = a.inc_xyz;
-  f.b2 = a.b2; f.bof = a.bof; f.bos = a.bos; f.br = a.br; f.ext = ext; f.pk = pk; f.raw = raw;
+  f.b2 = a.b2; f.bof = a.bof; f.bos = a.bos; f.br = a.br; f.gid = a.gid; f.ext = ext; f.pk = pk; f.raw = raw;
   f.saved = saved_al;
   f.err = tc_error_ptr();
   const int64_t pairs = ((a.M + TILE - 1) / TILE + 1) / 2;
@@ -197,6 +198,7 @@ struct DwArgs {
   const uint8_t* dy;
   const uint8_t* ext;
   const float* g_raw;
+  const int32_t* gid;      // shared-code mode: row of the per-ray tables that ray r accumulates into (NULL: r)
   float* d_br;             // [N][3] per-ray sums of the rgb gradients   } accumulated by the RED_RGB job
   float* d_bo;             // [N][257], column 0 = per-ray sums of the sigma gradients
   DwJob job[DW_JOBS];
@@ -338,6 +340,34 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
       float c0[8], c1[8], c2[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) c0[j] = c1[j] = c2[j] = 0.f;
+      // per-ray sums stay in registers while consecutive rays (and stages) add into the same table row -- one flush per
+      // ray in the plain mode, one per run of rays that share a code row in the shared-code mode
+      float sum[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) sum[j] = 0.f;
+      float tsum = 0.f;                    // RED_RGB: this lane's part of the per-ray raw-gradient sum, component rw
+      int64_t cur_row = -1;
+      auto flush_row = [&]() {
+        if (job.red == RED_RGB) {
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) tsum += __shfl_xor_sync(0xFFFFFFFFu, tsum, o);
+          if (lane == 0) atomicAdd(rw < 3 ? a.d_br + cur_row * 3 + rw : a.d_bo + cur_row * 257, tsum);
+          tsum = 0.f;
+        } else {
+          float o0, o1;
+          const int col = rw * 64 + rs_rows(sum, lane, o0, o1);
+          float* o = job.red_out + cur_row * job.red_ld + col;
+          atomicAdd(o, o0); atomicAdd(o + 1, o1);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) sum[j] = 0.f;
+        }
+      };
+      auto enter_ray = [&](int64_t row) {   // uniform over the warp
+        if (row != cur_row) {
+          if (cur_row >= 0) flush_row();
+          cur_row = row;
+        }
+      };
       float4 gpre = make_float4(0.f, 0.f, 0.f, 0.f);
       if (needs_g && w < 64 && (int64_t)bx * 64 + w < a.M) gpre = __ldg(reinterpret_cast<const float4*>(a.g_raw) + (int64_t)bx * 64 + w);
       uint32_t g = 0;
@@ -356,6 +386,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
         // first ray of the stage and the row at which it ends (32-bit division when the row count allows)
         const int64_t ray0 = a.M < (1ll << 31) ? (int64_t)((uint32_t)m0 / (uint32_t)a.S) : m0 / a.S;
         const int seg_end0 = (int)((ray0 + 1) * a.S - m0);
+        const int64_t row0 = (a.gid && rows > 0) ? (int64_t)__ldg(a.gid + ray0) : ray0;
         if (!dw_wait(&bars->full[slot], (g / DW_RING) & 1, bars, a.err)) goto done;
         const uint8_t* sa = smem + slot * DW_STAGE + rw * 8192;
         // rows ph + 4 i of this thread: chunk (c ^ (row & 7)) alternates between two values
@@ -386,20 +417,18 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
               fma8(c0, gr.x, v); fma8(c1, gr.y, v); fma8(c2, gr.z, v);
             }
           }
-          // per-ray sums of the raw gradients themselves: warp rw takes component rw
+          // per-ray sums of the raw gradients themselves: warp rw takes component rw, a lane rows lane and lane + 32
           const float* gf = reinterpret_cast<const float*>(gs);
           int64_t ray = ray0;
           int seg_end = seg_end0;
           int r0 = 0;
+          if (rows > 0) enter_ray(row0);
           while (r0 < rows) {
             const int r1 = seg_end < rows ? seg_end : rows;
-            float t = 0.f;
-            if (lane >= r0 && lane < r1) t = gf[lane * 4 + rw];
-            if (lane + 32 >= r0 && lane + 32 < r1) t += gf[(lane + 32) * 4 + rw];
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xFFFFFFFFu, t, o);
-            if (lane == 0) atomicAdd(rw < 3 ? a.d_br + ray * 3 + rw : a.d_bo + ray * 257, t);
+            if (lane >= r0 && lane < r1) tsum += gf[lane * 4 + rw];
+            if (lane + 32 >= r0 && lane + 32 < r1) tsum += gf[(lane + 32) * 4 + rw];
             r0 = r1; ++ray; seg_end += a.S;
+            if (r0 < rows) enter_ray(a.gid ? (int64_t)__ldg(a.gid + ray) : ray);
           }
         } else {
           if (job.red == RED_RAY_SIGMA) {       // sigma-weighted column sums of the B image: no ray boundaries either
@@ -414,10 +443,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
           // per-ray sums of the A image, 16 rows at a time; a ray boundary inside a 16-row group takes the slow path
           int64_t ray = ray0;
           int next_b = seg_end0;
-          float sum[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) sum[j] = 0.f;
-          bool dirty = false;
+          if (rows > 0) enter_ray(row0);
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
             const int lo = 16 * q, hi = rows < lo + 16 ? rows : lo + 16;
@@ -425,7 +451,6 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
               if (next_b >= hi && hi - lo == 16) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) acc8(sum, *reinterpret_cast<const uint4*>(DW_ROW(4 * q + i)));
-                dirty = true;
               } else {
                 int cur = lo;
                 while (cur < hi) {
@@ -435,28 +460,16 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
                     const int r = lo + ph + 4 * i;
                     if (r >= cur && r < r1) acc8(sum, *reinterpret_cast<const uint4*>(DW_ROW(4 * q + i)));
                   }
-                  dirty = true;
                   cur = r1;
                   if (cur == next_b && cur < hi) {
-                    float o0, o1;
-                    const int col = rw * 64 + rs_rows(sum, lane, o0, o1);
-                    float* o = job.red_out + ray * job.red_ld + col;
-                    atomicAdd(o, o0); atomicAdd(o + 1, o1);
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) sum[j] = 0.f;
-                    dirty = false; ++ray; next_b += a.S;
+                    ++ray; next_b += a.S;
+                    enter_ray(a.gid ? (int64_t)__ldg(a.gid + ray) : ray);
                   }
                 }
               }
-              if (next_b == hi || (hi == rows && dirty)) {      // the ray (or the stage) ends with this group
-                float o0, o1;
-                const int col = rw * 64 + rs_rows(sum, lane, o0, o1);
-                float* o = job.red_out + ray * job.red_ld + col;
-                atomicAdd(o, o0); atomicAdd(o + 1, o1);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) sum[j] = 0.f;
-                dirty = false;
-                if (next_b == hi) { ++ray; next_b += a.S; }
+              if (next_b == hi) {                // the ray ends with this group
+                ++ray; next_b += a.S;
+                if (hi < rows) enter_ray(a.gid ? (int64_t)__ldg(a.gid + ray) : ray);
               }
             }
           }
@@ -465,6 +478,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
         __syncwarp();
         if (lane == 0) mbar_arrive(&bars->empty[slot]);
       }
+      if (cur_row >= 0) flush_row();
       float o0, o1;
       const int col = rw * 64 + rs_rows(c0, lane, o0, o1);
       float* fo = job.red == RED_RAY_SIGMA ? job.red2_out : job.red_out;
@@ -551,7 +565,7 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   if ((rc = cnrf_tc_launch_bwd(b, (int)(pairs < sm_count() ? pairs : sm_count()), st))) return rc;
 
   DwArgs d;
-  d.M = a.M; d.S = a.S; d.saved = sv; d.dy = dy; d.g_raw = g_raw; d.d_br = d_br; d.d_bo = d_bo; d.err = tc_error_ptr();
+  d.M = a.M; d.S = a.S; d.saved = sv; d.dy = dy; d.g_raw = g_raw; d.gid = a.gid; d.d_br = d_br; d.d_bo = d_bo; d.err = tc_error_ptr();
   d.ext = sv + (size_t)tiles * SAVED_PER_TILE;
   // the per-ray tables are accumulated by the reducer warps
   if ((rc = cnrf_fill_zero(d_b2, (size_t)a.N * 256 * sizeof(float), st))) return rc;

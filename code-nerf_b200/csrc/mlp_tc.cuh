@@ -89,6 +89,7 @@ struct FwdArgs {
   const float* pts; const float* x_xyz; int64_t ld_xyz;
   const float* freqs; int L; int inc;
   const float *b2, *bof, *bos, *br;        // per-ray bias tables: [N,256], [N,256] (fc_out feat), [N] (sigma), [N,3]
+  const int32_t* gid;                      // row of those tables that ray r uses (NULL: r) -- shared-code mode
   const uint8_t* ext;                      // per tile PAIR: [128 x 64] bf16 slab, columns 32t..32t+31 = [gamma(d_pair) | 1 | 0] of tile t
   Packed pk;
   float* raw;
@@ -128,7 +129,38 @@ __device__ __forceinline__ void build_input_row(const FwdArgs& a, int64_t m, boo
   }
   put_bf16(row, r, 63, 1.0f);
 }
-
+// The same row for the standard encoding [x | sin(2^k x), cos(2^k x), k < L] (position_embed.py:35-53 with include_input
+// and octave bands): all 64 values stay in registers (compile-time indices) and leave as eight 16-byte stores.
+template <int L>
+__device__ __forceinline__ void build_input_row_octaves(const float x[3], bool valid, uint8_t* tile, int r) {
+  static_assert(3 + 6 * L <= 63, "row holds 63 inputs + the bias column");
+  uint8_t* row = tile + r * 128;
+  float v[64];
+#pragma unroll
+  for (int i = 0; i < 64; ++i) v[i] = 0.f;
+  if (valid) {
+    float s[3], c[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) { v[d] = x[d]; sincosf(x[d], &s[d], &c[d]); }
+#pragma unroll
+    for (int k = 0; k < L; ++k) {
+      if (k > 0) {                         // octave step by angle doubling (error analysis: build_input_row)
+#pragma unroll
+        for (int d = 0; d < 3; ++d) { const float s2 = 2.f * s[d] * c[d]; c[d] = 1.f - 2.f * s[d] * s[d]; s[d] = s2; }
+      }
+#pragma unroll
+      for (int d = 0; d < 3; ++d) { v[3 + 6 * k + d] = s[d]; v[3 + 6 * k + 3 + d] = c[d]; }
+    }
+    v[63] = 1.0f;
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    uint4 q;
+    q.x = pack_bf16(v[8 * j], v[8 * j + 1]); q.y = pack_bf16(v[8 * j + 2], v[8 * j + 3]);
+    q.z = pack_bf16(v[8 * j + 4], v[8 * j + 5]); q.w = pack_bf16(v[8 * j + 6], v[8 * j + 7]);
+    *reinterpret_cast<uint4*>(row + ((j ^ (r & 7)) << 4)) = q;
+  }
+}
 
 // mlp_fwd_tc.cu
 int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st);

@@ -19,6 +19,12 @@ def get_params_tensor(model, is_distributed):
     return shape_params, texture_params
 
 
+def _share_codes() -> bool:
+    """CODENERF_SHARE_CODES=0 keeps the per-ray code path even when the ids are known (tests, A/B timing)."""
+    import os
+    return os.environ.get("CODENERF_SHARE_CODES", "1") != "0"
+
+
 class ShapeTextureEmbedding(torch.nn.Module):
     """Two nn.Embedding tables (models/model.py:87-120).  The row gather and its sparse scatter backward stay in
     torch: the render kernels consume per-ray codes and return per-ray code gradients."""
@@ -32,7 +38,14 @@ class ShapeTextureEmbedding(torch.nn.Module):
         self.texture_embedding = torch.nn.Embedding(self.num_embeddings, self.texture_code_size)
 
     def forward(self, object_ids: torch.Tensor):
-        return self.shape_embedding(object_ids), self.texture_embedding(object_ids)
+        z_s, z_t = self.shape_embedding(object_ids), self.texture_embedding(object_ids)
+        # Where the codes came from travels with them: CodeNeRFModel's fused field then looks the rows up itself and
+        # shares the code layers between the rays of one object (train.py:78 gives a whole image one id).  Any other
+        # consumer sees two ordinary tensors.
+        src = (object_ids, self.shape_embedding.weight, self.texture_embedding.weight)
+        z_s._cnrf_code_source = src
+        z_t._cnrf_code_source = src
+        return z_s, z_t
 
     def get_all_embeddings(self, device):
         all_idx = torch.arange(0, self.num_embeddings, dtype=int, device=device)
@@ -97,9 +110,12 @@ class CodeNeRFModel(torch.nn.Module):
                 "embedder widths do not match the model's dim_xyz / dim_dir"
             precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[x.precision]
             pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
+            src = getattr(z_s, "_cnrf_code_source", None)
+            if src is None or getattr(z_t, "_cnrf_code_source", None) is not src or not _share_codes():
+                src = None
             return ops.codenerf_field(params, x.pts, x.rd, z_s, z_t, ex.frequency_bands, ed.frequency_bands,
                                       self.hidden_size, self.shape_code_size, self.dim_xyz, self.dim_dir,
-                                      pairing=pairing, precision=precision)
+                                      pairing=pairing, precision=precision, code_source=src)
         lead = x.shape[:-1]
         out = ops.codenerf_model(params, z_s.reshape(-1, z_s.shape[-1]), z_t.reshape(-1, z_t.shape[-1]),
                                  x.reshape(-1, x.shape[-1]), self.hidden_size, self.shape_code_size, self.dim_xyz,

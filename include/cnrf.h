@@ -191,6 +191,24 @@ int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
                    size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t, float* g_pts,
                    float* g_rd, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
 
+/* Shared latent codes: train.py:78-96 gives every ray of an image the image's object id and looks the codes up per ray
+ * (ShapeTextureEmbedding.forward, models/model.py:100-103).  These variants take the ids and the two embedding TABLES
+ * instead of per-ray code rows: ids [N] int64 (device), tab_s / tab_t [num_codes, C] (row strides ld_s / ld_t).  The code
+ * layers and the gradients of their bias tables are evaluated once per run of equal consecutive ids (found on the device,
+ * no host synchronisation).  g_tab_s / g_tab_t [num_codes, C] receive the dense table gradients (overwritten), i.e. what
+ * torch.nn.Embedding's backward would have accumulated.  CNRF_PRECISION_BF16 only (CNRF_E_UNSUPPORTED otherwise); saved /
+ * workspace sizes are those of cnrf_codenerf_saved_bytes / cnrf_field_workspace_bytes. */
+int cnrf_field_fwd_ids(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                       const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
+                       int64_t num_codes, const float* tab_s, int64_t ld_s, const float* tab_t, int64_t ld_t,
+                       float* raw /*[N,S,4]*/, void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes,
+                       cnrf_stream_t stream);
+int cnrf_field_bwd_ids(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                       const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
+                       int64_t num_codes, const float* tab_s, int64_t ld_s, const float* tab_t, int64_t ld_t,
+                       const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g,
+                       float* g_tab_s, float* g_tab_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------------
  * Diagnostics (used by tests only).  One-CTA tcgen05 GEMM over the 128-byte-swizzled shared-memory image the fused
  * MLP kernels use.  mode 0: D[128,N] = A[128,K] B[N,K]^T (K-major operands); mode 1: D[128,N] = A[K,128]^T B[K,N]

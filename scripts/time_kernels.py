@@ -27,7 +27,7 @@ emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.Positio
 ro = torch.tensor([0.0, 0.0, 1.3], device=dev).expand(N, 3).contiguous() + 0.01 * torch.randn(N, 3, device=dev)
 rd = torch.nn.functional.normalize(torch.randn(N, 3, device=dev) * 0.3 + torch.tensor([0.0, 0.0, -1.0], device=dev), dim=-1)
 tgt = torch.rand(N, 3, device=dev)
-oid = torch.randint(0, 2458, (N,), device=dev)
+oid = torch.full((N,), 1234, dtype=torch.int64, device=dev) if os.environ.get("CHUNK_IDS", "image") == "image" else torch.randint(0, 2458, (N,), device=dev)   # train.py:78: one object id per image
 lib = _lib.load()
 
 

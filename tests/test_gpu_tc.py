@@ -183,3 +183,53 @@ def test_gemm_tc_forms(dev, M, N, K):
     assert torch.allclose(got, 1.0 + bf(dY).t() @ bf(X), atol=2e-4 * M ** 0.5, rtol=1e-4)
     from codenerf_b200 import _lib
     assert _lib.load().cnrf_debug_tc_error() == 0
+
+
+# ---- shared latent codes (code_runs.cu, cnrf_field_*_ids) against the per-ray code path -------------------------------
+def _id_patterns(N, num_codes, g):
+    runs = torch.randint(0, num_codes, (N,), generator=g)
+    return {
+        "one_object": torch.full((N,), 3, dtype=torch.int64),
+        "four_images": torch.arange(4).repeat_interleave((N + 3) // 4)[:N],
+        "ragged_runs_with_repeats": torch.repeat_interleave(torch.tensor([5, 1, 5, 0, 2, 2]), torch.tensor(
+            [max(N // 6, 1)] * 5 + [max(N - 5 * max(N // 6, 1), 1)]))[:N],
+        "all_distinct_neighbours": runs,
+    }
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("N,S", [(96, 160), (37, 32), (1500, 32)])
+def test_shared_codes_match_per_ray_codes(dev, N, S, monkeypatch):
+    """The fused embedding-lookup path (one evaluation of the code layers per run of equal ids, dense table gradients)
+    against the same bf16 kernels fed per-ray code rows through torch.nn.Embedding: same raw output bit for bit (identical
+    bias-table rows), gradients equal up to fp32 summation order."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    g = torch.Generator().manual_seed(N * 13 + S)
+    pts = (torch.rand(N, S, 3, generator=g) * 3 - 1.5).to(dev)
+    rd = torch.randn(N, 3, generator=g).to(dev)
+    graw = (torch.rand(N, S, 4, generator=g) + 0.5).to(dev)
+    nerf.set_precision("bf16")
+    try:
+        for name, ids in _id_patterns(N, 8, g).items():
+            assert ids.shape == (N,), name
+            res = {}
+            for share in ("0", "1"):
+                monkeypatch.setenv("CODENERF_SHARE_CODES", share)
+                torch.manual_seed(11)
+                emb = models.ShapeTextureEmbedding(8, 256, 256).to(dev)
+                m = _models(dev)
+                codes = emb(ids.to(dev))
+                raw = nerf.forward_pass(m, _embedders(dev), rd, pts, codes)
+                raw.backward(graw)
+                _tc_ok()
+                res[share] = {"raw": raw.detach(), **{"emb." + k: p.grad for k, p in emb.named_parameters()},
+                              **{k: p.grad for k, p in m.named_parameters()}}
+            assert torch.equal(res["0"]["raw"], res["1"]["raw"]), name
+            for k in res["0"]:
+                a, b = res["1"][k].double(), res["0"][k].double()
+                assert torch.isfinite(a).all(), (name, k)
+                err = ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+                assert err < 2e-4, (name, k, err)
+    finally:
+        nerf.set_precision("fp32")
