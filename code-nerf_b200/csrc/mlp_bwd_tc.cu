@@ -4,7 +4,7 @@
 // with W^T streamed as B operands (16 KB N-half images through a 5-slot TMA ring, as in the forward).  Every masked
 // gradient tile is TMA-stored as a bf16 image (same layout as the forward's activation images) for the weight-gradient
 // kernel.  The ReLU masks are the 1-bit sign words the forward saved (32 B per row and layer), loaded before the
-// accumulator wait; the epilogue is specialised per stage at compile time and fully unrolled.
+// accumulator wait; the epilogue is specialised per stage at compile time.
 // Geometry, warp roles and barrier protocol are those of mlp_fwd_tc.cu.
 #include "mlp_tc.cuh"
 
@@ -50,16 +50,20 @@ struct BEpi {
   float4 g;                // upstream gradient of this row's (r, g, b, sigma)
 };
 
+// warp-wide wait whose result the compiler can prove uniform (keeps the MMA issuer's state in uniform registers)
+__device__ __forceinline__ bool uwait(uint64_t* bar, uint32_t parity, BBars* b, int* err) {
+  return __all_sync(0xFFFFFFFFu, bwait(bar, parity, b, err));
+}
+
 // S = -1: d v2p from g_rgb on CUDA cores; S = 0..3: the tensor-core stages.  Output image index = S + 1.
+// The 32-column blocks are processed two per loop iteration with the next block's TMEM load (and mask word) in flight;
+// the loop is deliberately not unrolled further (instruction-cache footprint of five specialised stages).
 template <int S>
 __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint32_t parity) {
   constexpr int MK = S == -1 ? 3 : S == 0 ? 2 : S == 2 ? 1 : S == 3 ? 0 : -1;   // v2, v1, -, h2, h1
-  uint32_t mw[8];
-  if (MK >= 0) {
-    const uint4* mp = reinterpret_cast<const uint4*>(c.masks + (size_t)MK * MASK_BYTES + c.r * 32);
-    const uint4 m0 = __ldg(mp), m1 = __ldg(mp + 1);
-    mw[0] = m0.x; mw[1] = m0.y; mw[2] = m0.z; mw[3] = m0.w; mw[4] = m1.x; mw[5] = m1.y; mw[6] = m1.z; mw[7] = m1.w;
-  }
+  const uint32_t* mp = reinterpret_cast<const uint32_t*>(c.masks + (size_t)(MK >= 0 ? MK : 0) * MASK_BYTES + c.r * 32);
+  uint32_t m_a = 0, m_b = 0;
+  if (MK >= 0) m_a = __ldg(mp);
   if (S >= 0) {
     if (!bwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
     tc_fence_after();
@@ -67,13 +71,9 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
   if (c.elected) bulk_wait_read0();                 // the previous image store no longer reads this tile
   named_bar_sync(c.bar_id, 128);
   const float4* hw = reinterpret_cast<const float4*>(c.heads);
-#pragma unroll
-  for (int cb = 0; cb < 8; ++cb) {
+  auto block = [&](int cb, uint32_t (&v)[32], uint32_t w) {
     float f[32];
     if (S >= 0) {
-      uint32_t v[32];
-      tmem_ld32(c.tacc + cb * 32, v);
-      tmem_ld_wait();
 #pragma unroll
       for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
     } else {
@@ -89,13 +89,12 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
     if (S == 2) {                                   // + d sigma * w_sigma  (fc_out row 0)
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
-        const float4 w = hw[cb * 8 + j];
-        f[4 * j] = fmaf(c.g.w, w.x, f[4 * j]); f[4 * j + 1] = fmaf(c.g.w, w.y, f[4 * j + 1]);
-        f[4 * j + 2] = fmaf(c.g.w, w.z, f[4 * j + 2]); f[4 * j + 3] = fmaf(c.g.w, w.w, f[4 * j + 3]);
+        const float4 ws = hw[cb * 8 + j];
+        f[4 * j] = fmaf(c.g.w, ws.x, f[4 * j]); f[4 * j + 1] = fmaf(c.g.w, ws.y, f[4 * j + 1]);
+        f[4 * j + 2] = fmaf(c.g.w, ws.z, f[4 * j + 2]); f[4 * j + 3] = fmaf(c.g.w, ws.w, f[4 * j + 3]);
       }
     }
-    if (MK >= 0) {
-      const uint32_t w = mw[cb];                    // bit 31-j set: pre-activation of column 32 cb + j was <= 0
+    if (MK >= 0) {                                  // bit 31-j set: pre-activation of column 32 cb + j was <= 0
 #pragma unroll
       for (int j = 0; j < 32; ++j) f[j] = (w & (0x80000000u >> j)) ? 0.f : f[j];
     }
@@ -103,6 +102,20 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
 #pragma unroll
     for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
     store_row_block(c.tile, c.r, cb, pk);
+  };
+  uint32_t va[32], vb[32];
+  if (S >= 0) tmem_ld32(c.tacc, va);
+#pragma unroll 1
+  for (int cb = 0; cb < 8; cb += 2) {
+    if (S >= 0) { tmem_ld_wait(); tmem_ld32(c.tacc + (cb + 1) * 32, vb); }
+    if (MK >= 0) m_b = __ldg(mp + cb + 1);
+    block(cb, va, m_a);
+    if (S >= 0) tmem_ld_wait();
+    if (cb + 2 < 8) {
+      if (S >= 0) tmem_ld32(c.tacc + (cb + 2) * 32, va);
+      if (MK >= 0) m_a = __ldg(mp + cb + 2);
+    }
+    block(cb + 1, vb, m_b);
   }
   fence_proxy_async();
   tc_fence_before();
@@ -139,50 +152,62 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
   const uint32_t tmem = bars->tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer: 16 transposed K-chunks x 2 N-halves per pair =====
+    // ===== TMA producer: per (stage, tile) the 4 transposed K-chunks x 2 N-halves of that stage =====
+    // The two tiles of a pair run half a stage apart (one tile's MMAs under the other's epilogue), so the L2-resident
+    // weight images pass through the ring once per tile.
     if (lane == 0) {
-      uint32_t g = 0;
-      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
-        for (int hc = 0; hc < 2 * BWD_CHUNKS; ++hc, ++g) {
-          const int slot = g % BRING;
-          if (!bwait(&bars->w_empty[slot], ((g / BRING) & 1) ^ 1, bars, a.err)) break;
-          mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
-          bulk_g2s(ring + slot * HALF, a.pk.bwd + (size_t)hc * HALF, HALF, &bars->w_full[slot]);
+      uint32_t slot = 0, epar = 1;
+      bool ok = true;
+      for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+        for (int stage = 0; stage < 4 && ok; ++stage) {
+          for (int t = 0; t < 2 && ok; ++t) {
+            for (int i = 0; i < 8; ++i) {
+              if (!bwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
+              mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
+              bulk_g2s(ring + slot * HALF, a.pk.bwd + (size_t)(stage * 8 + i) * HALF, HALF, &bars->w_full[slot]);
+              if (++slot == BRING) { slot = 0; epar ^= 1u; }
+            }
+          }
         }
         if (*(volatile int*)&bars->abort_flag) break;
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer: warp-uniform control flow, one elected lane issues (see mlp_fwd_tc.cu) =====
+    {
+      const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);
       const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
       const uint64_t a_desc0 = smem_desc(smem_u32(tiles), 16, 1024, SWIZZLE_128B);
       const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
-      uint32_t g = 0, na = 0;
+      uint32_t slot = 0, wpar = 0, na = 0;
       bool ok = true;
       for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+#pragma unroll 1
         for (int stage = 0; stage < 4 && ok; ++stage, ++na) {
-          for (int c = 0; c < 4 && ok; ++c) {
+#pragma unroll 1
+          for (int t = 0; t < 2 && ok; ++t) {
+            if (!uwait(&bars->a_ready[t], na & 1, bars, a.err)) { ok = false; break; }
+            const uint32_t d0 = tmem_u + t * 256;
+#pragma unroll 1
+            for (int c = 0; c < 4 && ok; ++c) {
+              const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
 #pragma unroll
-            for (int h = 0; h < 2; ++h, ++g) {
-              if (!ok) continue;
-              const int slot = g % BRING;
-              if (!bwait(&bars->w_full[slot], (g / BRING) & 1, bars, a.err)) { ok = false; continue; }
-              if (c == 0 && h == 0) {
-                if (!bwait(&bars->a_ready[0], na & 1, bars, a.err) || !bwait(&bars->a_ready[1], na & 1, bars, a.err)) { ok = false; continue; }
+              for (int h = 0; h < 2; ++h) {
+                if (!ok) continue;
+                if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; continue; }
+                tc_fence_after();
+                const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
+                if (elect_one()) {
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) umma_bf16(d0 + h * 128, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
+                  umma_commit(&bars->w_empty[slot]);
+                }
+                __syncwarp();
+                if (++slot == BRING) { slot = 0; wpar ^= 1u; }
               }
-              tc_fence_after();
-              const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
-#pragma unroll
-              for (int t = 0; t < 2; ++t) {
-                const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
-                const uint32_t d = tmem + t * 256 + h * 128;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(d, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
-                if (c == 3 && h == 1) umma_commit(&bars->acc_full[t]);
-              }
-              umma_commit(&bars->w_empty[slot]);
             }
+            if (ok && elect_one()) umma_commit(&bars->acc_full[t]);
+            __syncwarp();
           }
         }
       }

@@ -1,8 +1,8 @@
 // Forward chain of the fused bf16 tensor-core field (CNRF_PRECISION_BF16), models/model.py:179-194 code-folded:
 //   h1 = relu(W1 gamma(x) + b1) -> h2 = relu(W2h h1 + beta2[ray]) -> o = Woh h2 + betao[ray] -> v1 = relu(Wdf o[1:] +
 //   betad[pair]) -> v2 = relu(Wd2 v1 + bd2) -> rgb = Wrv v2 + betar[ray]
-// One persistent CTA per SM walks PAIRS of 128-row sample tiles (T0, T1) through the five layers in lockstep, so every
-// weight image fetched from L2 feeds 256 rows.
+// One persistent CTA per SM walks PAIRS of 128-row sample tiles (T0, T1) through the five layers half a layer apart: the
+// MMAs of one tile run under the epilogue of the other (weights are L2-resident and pass through the ring once per tile).
 //   TMEM   : 2 x 256 fp32 accumulator columns (all 512).
 //   smem   : 2 x 64 KB activation tiles (4 slabs of [128 x 64] bf16, 128-byte swizzle, overwritten in place layer by
 //            layer) + a ring of five 16 KB weight images ([128 out-features x 64 in-features]: the N-half of a K chunk,
@@ -15,7 +15,14 @@
 #include "mlp_tc.cuh"
 
 __device__ long long g_fwd_dbg[16];
+// Phase timers of block 0 (scripts/time_field.py): compiled in only with -DCNRF_FWD_TIMERS, they cost issue slots
+#ifdef CNRF_FWD_TIMERS
 #define FDBG(i, dt) do { if (blockIdx.x == 0) atomicAdd((unsigned long long*)&g_fwd_dbg[i], (unsigned long long)(dt)); } while (0)
+#define FCLK() clock64()
+#else
+#define FDBG(i, dt) do { } while (0)
+#define FCLK() 0ll
+#endif
 namespace {
 constexpr int HALF = 128 * 128;             // bytes of one [128 x 64] bf16 weight image
 constexpr int FRING = 5;
@@ -49,6 +56,11 @@ __device__ __forceinline__ bool fwait(uint64_t* bar, uint32_t parity, FBars* b, 
       return false;
     }
   }
+}
+// the same for a whole warp, with a result the compiler can prove warp-uniform (keeps the MMA issuer's state in uniform
+// registers)
+__device__ __forceinline__ bool uwait(uint64_t* bar, uint32_t parity, FBars* b, int* err) {
+  return __all_sync(0xFFFFFFFFu, fwait(bar, parity, b, err));
 }
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
@@ -92,17 +104,12 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if (E == 1) { if (GB) gb = reinterpret_cast<const float4*>(a.b2 + (int64_t)c.row * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
   if (E == 2) { if (GB) gb = reinterpret_cast<const float4*>(a.bof + (int64_t)c.row * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
   if (E == 4) sb = reinterpret_cast<const float4*>(c.heads + 1024);
-  float4 bcur[8], bnxt[8];
   float tail0 = 0.f, tail1 = 0.f, tail2 = 0.f;
-  if (GB) {
-#pragma unroll
-    for (int j = 0; j < 8; ++j) bcur[j] = __ldg(gb + j);
-  }
   if (E == 1 && c.valid) tail0 = __ldg(a.bos + c.row);
   if (E == 4 && c.valid) { const float* brp = a.br + (int64_t)c.row * 3; tail0 = __ldg(brp); tail1 = __ldg(brp + 1); tail2 = __ldg(brp + 2); }
-  const long long tw0 = clock64();
+  const long long tw0 = FCLK();
   if (!fwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
-  const long long tw1 = clock64();
+  const long long tw1 = FCLK();
   tc_fence_after();
   if (c.elected) bulk_wait_read0();                 // the previous image store no longer reads this tile
   if ((E == 1 || E == 2) && !GB) cp_async_wait_all();
@@ -110,20 +117,18 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   const float4* hw = reinterpret_cast<const float4*>(c.heads);
   float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f, rgb3 = 0.f, rgb4 = 0.f, rgb5 = 0.f;   // two partial sums per channel
   float sg0 = 0.f, sg1 = 0.f, sg2 = 0.f, sg3 = 0.f;                               // four partial sums of the sigma head
-  uint32_t sgn[8];                                  // sign bits of the pre-activations (the backward's ReLU mask)
+  // sign bits of the pre-activations (the backward's ReLU mask): one 32-bit word per 32-column block
+  uint32_t* mp = (E != 2 && c.sv) ? reinterpret_cast<uint32_t*>(c.sv + SAVED_MASKS + (size_t)(E == 0 ? 0 : E == 1 ? 1 : E == 3 ? 2 : 3) * MASK_BYTES + c.r * 32)
+                                  : nullptr;
+  // One 32-column block: + bias, heads, sign word, ReLU, bf16, swizzled store.  The loop below keeps the next block's
+  // TMEM load in flight while this one is processed, and is NOT unrolled further: five specialised layers unrolled eight
+  // times each overflowed the instruction cache (16% of the kernel's stall samples were instruction fetches).
+  auto block = [&](int cb, uint32_t (&v)[32]) {
+    float4 bcur[8];
+    if (E == 1 || E == 2 || E == 4) {
 #pragma unroll
-  for (int cb = 0; cb < 8; ++cb) {
-    uint32_t v[32];
-    tmem_ld32(c.tacc + cb * 32, v);
-    if (GB && cb < 7) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) bnxt[j] = __ldg(gb + (cb + 1) * 8 + j);
+      for (int j = 0; j < 8; ++j) bcur[j] = GB ? __ldg(gb + cb * 8 + j) : sb[cb * 8 + j];
     }
-    if (!GB && E != 0 && E != 3) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) bcur[j] = sb[cb * 8 + j];
-    }
-    tmem_ld_wait();
     float f[32];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -158,21 +163,23 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
       uint32_t w = 0;
 #pragma unroll
       for (int j = 0; j < 32; ++j) w = __funnelshift_l(__float_as_uint(f[j]), w, 1);   // (w << 1) | sign(f[j])
-      sgn[cb] = w;
+      if (mp) mp[cb] = w;
     }
     uint32_t pk[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) pk[j] = (E == 2) ? pack_bf16(f[2 * j], f[2 * j + 1]) : cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
     store_row_block(c.tile, c.r, cb, pk);
-    if (GB) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) bcur[j] = bnxt[j];
-    }
-  }
-  if (E != 2 && c.sv) {
-    uint4* mp = reinterpret_cast<uint4*>(c.sv + SAVED_MASKS + (size_t)(E == 0 ? 0 : E == 1 ? 1 : E == 3 ? 2 : 3) * MASK_BYTES + c.r * 32);
-    mp[0] = make_uint4(sgn[0], sgn[1], sgn[2], sgn[3]);
-    mp[1] = make_uint4(sgn[4], sgn[5], sgn[6], sgn[7]);
+  };
+  uint32_t va[32], vb[32];
+  tmem_ld32(c.tacc, va);
+#pragma unroll 1
+  for (int cb = 0; cb < 8; cb += 2) {
+    tmem_ld_wait();
+    tmem_ld32(c.tacc + (cb + 1) * 32, vb);
+    block(cb, va);
+    tmem_ld_wait();
+    if (cb + 2 < 8) tmem_ld32(c.tacc + (cb + 2) * 32, va);
+    block(cb + 1, vb);
   }
   if (E == 1) c.sigma = (sg0 + sg1) + (sg2 + sg3) + tail0;
   if (E == 4 && c.valid)                            // [rgb_raw | sigma_raw]   models/model.py:194
@@ -183,7 +190,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if (c.elected) {
     if (c.sv) { bulk_s2g(c.sv + SAVED_GAMMA + (size_t)E * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
     if (E < 4) mbar_arrive(&c.bars->a_ready[t]);
-    if (t == 0) { FDBG(0, tw1 - tw0); FDBG(1 + E, clock64() - tw1); }
+    if (t == 0) { FDBG(0, tw1 - tw0); FDBG(1 + E, FCLK() - tw1); }
   }
   return true;
 }
@@ -214,87 +221,103 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
   const uint32_t tmem = bars->tmem_slot;
 
   if (warp == 0) {
-    // ===== TMA producer: stream the 17 K-chunks x 2 N-halves of every tile pair through the ring =====
+    // ===== TMA producer =====
+    // The two tiles of a pair run half a layer apart (T1's MMAs overlap T0's epilogue), so a layer's weight images pass
+    // through the ring once per tile: per (layer, tile) the N-halves of its K-chunks in order; layer_dir1 is followed by
+    // its extension (this pair's [gamma(d) | 1] slab, then the two halves of [Wdv | b_dir1]).
     if (lane == 0) {
-      uint32_t g = 0;
-      for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
-        // 37 images per pair: K-chunks 0..12 (layers xyz1, xyz2, fc_out, dir1) as N-halves, then layer_dir1's extension
-        // (this pair's [gamma(d) | 1] slab, then the two halves of [Wdv | b_dir1]), then K-chunks 13..16 (layer_dir2)
-        for (int step = 0; step < 37; ++step, ++g) {
-          const int slot = g % FRING;
-          if (!fwait(&bars->w_empty[slot], ((g / FRING) & 1) ^ 1, bars, a.err)) break;
-          const uint8_t* src = step < 26 ? a.pk.fwd + (size_t)step * HALF
-                             : step == 26 ? a.ext + (size_t)pr * SLAB
-                             : step < 29 ? a.pk.fwd + (size_t)EXT_CHUNK * CHUNK + (size_t)(step - 27) * HALF
-                                         : a.pk.fwd + (size_t)(step - 3) * HALF;
-          mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
-          bulk_g2s(ring + slot * HALF, src, HALF, &bars->w_full[slot]);
+      uint32_t slot = 0, epar = 1;          // ring slot and the parity its w_empty barrier is waited with
+      bool ok = true;
+      for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+        for (int layer = 0; layer < 5 && ok; ++layer) {
+          const int first = layer == 0 ? 0 : 2 + 8 * (layer - 1);          // half-image index in a.pk.fwd
+          const int count = (layer == 0 ? 2 : 8) + (layer == 3 ? 3 : 0);
+          for (int t = 0; t < 2 && ok; ++t) {
+            for (int i = 0; i < count; ++i) {
+              if (!fwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
+              const uint8_t* src = (layer == 3 && i == 8) ? a.ext + (size_t)pr * SLAB
+                                 : (layer == 3 && i > 8) ? a.pk.fwd + (size_t)EXT_CHUNK * CHUNK + (size_t)(i - 9) * HALF
+                                                         : a.pk.fwd + (size_t)(first + i) * HALF;
+              mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
+              bulk_g2s(ring + slot * HALF, src, HALF, &bars->w_full[slot]);
+              if (++slot == FRING) { slot = 0; epar ^= 1u; }
+            }
+          }
         }
         if (*(volatile int*)&bars->abort_flag) break;
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
-    if (lane == 0) {
+    // Every lane runs the (warp-uniform) control flow so that ring counters, descriptors and TMEM addresses live in
+    // uniform registers; one elected lane issues tcgen05.mma / tcgen05.commit.  (With the whole loop under `if (lane == 0)`
+    // ptxas keeps that state in vector registers and pays an R2UR chain per MMA: ~125 instructions per weight image.)
+    {
+      const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);       // provably warp-uniform copy
       const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
       // descriptors differ only in their 14-bit start-address field (bytes >> 4): precompute the bases, add offsets
       const uint64_t a_desc0 = smem_desc(smem_u32(tiles), 16, 1024, SWIZZLE_128B);
       const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
-      uint32_t g = 0, na = 0;
+      uint32_t slot = 0, wpar = 0, na = 0;        // ring slot, its w_full parity, a_ready parity counter
       bool ok = true;
+#define NEXT_SLOT() do { if (++slot == FRING) { slot = 0; wpar ^= 1u; } } while (0)
       for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+#pragma unroll 1
         for (int layer = 0; layer < 5 && ok; ++layer, ++na) {
           const int nch = layer == 0 ? 1 : 4;
-          for (int c = 0; c < nch && ok; ++c) {
+#pragma unroll 1
+          for (int t = 0; t < 2 && ok; ++t) {
+            const long long m1 = FCLK();
+            if (!uwait(&bars->a_ready[t], na & 1, bars, a.err)) { ok = false; break; }
+            FDBG(9, FCLK() - m1);
+            const uint32_t d0 = tmem_u + t * 256;
+#pragma unroll 1
+            for (int c = 0; c < nch && ok; ++c) {
+              const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
 #pragma unroll
-            for (int h = 0; h < 2; ++h, ++g) {
-              if (!ok) continue;
-              const int slot = g % FRING;
-              const long long m0 = clock64();
-              if (!fwait(&bars->w_full[slot], (g / FRING) & 1, bars, a.err)) { ok = false; continue; }
-              FDBG(8, clock64() - m0);
-              if (c == 0 && h == 0) {
-                const long long m1 = clock64();
-                if (!fwait(&bars->a_ready[0], na & 1, bars, a.err) || !fwait(&bars->a_ready[1], na & 1, bars, a.err)) { ok = false; continue; }
-                FDBG(9, clock64() - m1);
+              for (int h = 0; h < 2; ++h) {
+                if (!ok) continue;
+                const long long m0 = FCLK();
+                if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; continue; }
+                FDBG(8, FCLK() - m0);
+                tc_fence_after();
+                const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
+                if (elect_one()) {
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) umma_bf16(d0 + h * 128, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
+                  umma_commit(&bars->w_empty[slot]);
+                }
+                __syncwarp();
+                NEXT_SLOT();
               }
-              tc_fence_after();
-              const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
-#pragma unroll
-              for (int t = 0; t < 2; ++t) {
-                const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
-                const uint32_t d = tmem + t * 256 + h * 128;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) umma_bf16(d, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
-                if (c == nch - 1 && h == 1 && layer != 3) umma_commit(&bars->acc_full[t]);
-              }
-              umma_commit(&bars->w_empty[slot]);
             }
-          }
-          if (layer == 3 && ok) {          // += [gamma(d_pair) | 1] [Wdv | b_dir1]^T : K = 32 columns per tile of the shared slab
-            const int slot_x = g % FRING;
-            if (!fwait(&bars->w_full[slot_x], (g / FRING) & 1, bars, a.err)) { ok = false; break; }
-            ++g;
-            const uint64_t xd = b_desc0 + (uint64_t)((slot_x * HALF) >> 4);
+            if (layer == 3 && ok) {        // += [gamma(d_pair) | 1] [Wdv | b_dir1]^T : K = 32 columns per tile of the shared slab
+              const uint32_t slot_x = slot;
+              if (!uwait(&bars->w_full[slot_x], wpar, bars, a.err)) { ok = false; break; }
+              NEXT_SLOT();
+              const uint64_t xd = b_desc0 + (uint64_t)((slot_x * HALF) >> 4);
 #pragma unroll
-            for (int h = 0; h < 2; ++h, ++g) {
-              if (!ok) continue;
-              const int slot = g % FRING;
-              if (!fwait(&bars->w_full[slot], (g / FRING) & 1, bars, a.err)) { ok = false; continue; }
-              tc_fence_after();
-              const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
+              for (int h = 0; h < 2; ++h) {
+                if (!ok) continue;
+                if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; continue; }
+                tc_fence_after();
+                const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
+                if (elect_one()) {
 #pragma unroll
-              for (int t = 0; t < 2; ++t) {
-#pragma unroll
-                for (int k = 0; k < 2; ++k) umma_bf16(tmem + t * 256 + h * 128, xd + 2 * (2 * t + k), bd + 2 * k, idesc, 1);
-                if (h == 1) umma_commit(&bars->acc_full[t]);
+                  for (int k = 0; k < 2; ++k) umma_bf16(d0 + h * 128, xd + 2 * (2 * t + k), bd + 2 * k, idesc, 1);
+                  umma_commit(&bars->w_empty[slot]);
+                }
+                __syncwarp();
+                NEXT_SLOT();
               }
-              umma_commit(&bars->w_empty[slot]);
+              if (ok && elect_one()) umma_commit(&bars->w_empty[slot_x]);
             }
-            if (ok) umma_commit(&bars->w_empty[slot_x]);
+            if (ok && elect_one()) umma_commit(&bars->acc_full[t]);
+            __syncwarp();
           }
         }
       }
+#undef NEXT_SLOT
     }
   } else {
     // ===== epilogue warps: thread = one sample row =====
@@ -346,7 +369,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       c.sv = (a.saved && tile_idx < num_tiles) ? a.saved + (size_t)tile_idx * SAVED_PER_TILE : nullptr;
       c.sigma = 0.f;
       // ---- input image: gamma(x); the bias rows of layer_xyz2 travel to smem meanwhile ----
-      const long long tb0 = clock64();
+      const long long tb0 = FCLK();
       if (c.elected) bulk_wait_read0();               // the previous pair's last image store has finished reading smem
       named_bar_sync(c.bar_id, 128);
       stage_rows(c, a.b2, a.gid);
@@ -363,7 +386,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       if (c.elected) {
         if (c.sv) { bulk_s2g(c.sv, c.tile, SLAB); bulk_commit(); }
         mbar_arrive(&bars->a_ready[t]);
-        if (t == 0) { FDBG(6, clock64() - tb0); FDBG(7, 1); }
+        if (t == 0) { FDBG(6, FCLK() - tb0); FDBG(7, 1); }
       }
       bool ok = epi_layer<0, false>(a, c, t, na & 1); ++na;
       if (ok) { ok = c.staged ? epi_layer<1, false>(a, c, t, na & 1) : epi_layer<1, true>(a, c, t, na & 1); ++na; }

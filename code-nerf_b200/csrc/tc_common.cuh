@@ -75,6 +75,17 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
 }
 
 // D[tmem] (+)= A[smem desc] * B[smem desc]; one thread issues for the CTA.
+// One lane of a converged warp (elect.sync): ptxas keeps the operands of instructions predicated this way in uniform
+// registers, which `if (lane == 0)` does not allow (it falls back to an R2UR waterfall around every tcgen05.mma).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xFFFFFFFF;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
                                           uint32_t accumulate) {
   asm volatile(
