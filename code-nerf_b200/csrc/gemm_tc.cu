@@ -86,6 +86,79 @@ __device__ __noinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int ro
   }
 }
 
+
+// ---- few-row problems (shared-code mode: one code row per run of rays, typically ONE per chunk) -------------------------
+// With a device-side row count of at most SMALL_ROWS the tile is a handful of dot products: plain fp32 on the CUDA cores,
+// no operand images, no TMEM -- a launch then costs a few microseconds instead of four MMA round trips.
+constexpr int SMALL_ROWS = 8;
+
+__device__ __forceinline__ void small_epilogue(const GemmArgs& g, bool add, int64_t m, int64_t n, float y) {
+  float* c = g.C + m * g.ldc + n;
+  if (add) { atomicAdd(c, y); return; }
+  if (g.bias) y += g.bias[((m / g.bias_div) % g.bias_mod) * g.ld_bias + n];
+  if (g.relu) y = fmaxf(y, 0.f);
+  if (g.mask) y = g.mask[m * g.ld_mask + n] > 0.f ? y : 0.f;
+  *c = y;
+}
+
+// rows_dim == 1: M <= SMALL_ROWS output rows, this CTA owns columns [n0, n0 + 64) and k in [kbeg, kend)
+__device__ void small_m_tile(const GemmArgs& g, bool add, int64_t n0, int64_t kbeg, int64_t kend, float* sm, int tid) {
+  const int M = (int)g.M, KK = (int)(kend - kbeg);
+  float* a_s = sm;                                   // [SMALL_ROWS][KK]
+  float* red = sm + SMALL_ROWS * KK;                 // [4][SMALL_ROWS][64]
+  for (int i = tid; i < SMALL_ROWS * KK; i += GTHREADS) {
+    const int m = i / KK, k = i - m * KK;
+    a_s[i] = m < M ? __ldg(g.A + (int64_t)m * g.a_rs + (kbeg + k) * g.a_cs) : 0.f;
+  }
+  __syncthreads();
+  const int nl = tid & 63, kq = tid >> 6;
+  const int64_t n = n0 + nl;
+  const int kper = (KK + 3) / 4, k0 = kq * kper, k1 = min(KK, k0 + kper);
+  float acc[SMALL_ROWS];
+#pragma unroll
+  for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = 0.f;
+  if (n < g.N) {
+    const float* bp = g.B + n * g.b_cs + kbeg * g.b_rs;
+#pragma unroll 4
+    for (int k = k0; k < k1; ++k) {
+      const float bv = __ldg(bp + (int64_t)k * g.b_rs);
+#pragma unroll
+      for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = fmaf(a_s[m * KK + k], bv, acc[m]);
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < SMALL_ROWS; ++m) red[(kq * SMALL_ROWS + m) * 64 + nl] = acc[m];
+  __syncthreads();
+  for (int i = tid; i < SMALL_ROWS * 64; i += GTHREADS) {
+    const int m = i >> 6, c = i & 63;
+    if (m < M && n0 + c < g.N) {
+      const float y = (red[(0 * SMALL_ROWS + m) * 64 + c] + red[(1 * SMALL_ROWS + m) * 64 + c]) +
+                      (red[(2 * SMALL_ROWS + m) * 64 + c] + red[(3 * SMALL_ROWS + m) * 64 + c]);
+      small_epilogue(g, add, m, n0 + c, y);
+    }
+  }
+}
+
+// rows_dim == 2: K <= SMALL_ROWS contraction rows, this CTA owns the 128 x 64 output tile at (m0, n0)
+__device__ void small_k_tile(const GemmArgs& g, bool add, int64_t m0, int64_t n0, int tid) {
+  const int K = (int)g.K;
+  const int nl = tid & 63, mq = tid >> 6;
+  const int64_t n = n0 + nl;
+  if (n >= g.N) return;
+  float bv[SMALL_ROWS];
+#pragma unroll
+  for (int k = 0; k < SMALL_ROWS; ++k) bv[k] = k < K ? __ldg(g.B + (int64_t)k * g.b_rs + n * g.b_cs) : 0.f;
+  for (int i = 0; i < GBM / 4; ++i) {
+    const int64_t m = m0 + mq + 4 * i;
+    if (m >= g.M) break;
+    float y = 0.f;
+#pragma unroll
+    for (int k = 0; k < SMALL_ROWS; ++k)
+      if (k < K) y = fmaf(__ldg(g.A + m * g.a_rs + (int64_t)k * g.a_cs), bv[k], y);
+    small_epilogue(g, add, m, n, y);
+  }
+}
+
 __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __grid_constant__ GemmBatch b, int* err) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -113,6 +186,15 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   const int64_t kbeg = (int64_t)kz * b.kslice[p];
   const int64_t kend = min(g.K, kbeg + b.kslice[p]);
   if (m0 >= g.M || kbeg >= g.K) return;
+  if (g.rows_dev) {
+    const bool add = g.split_k > 1 || g.accumulate || multi_k;
+    // the staging buffers of the small-row path must fit the operand-image area: 8 x K + 4 x 8 x 64 floats
+    if (g.rows_dim == 1 && g.M <= SMALL_ROWS && (kend - kbeg) * SMALL_ROWS + 4 * SMALL_ROWS * 64 <= (2 * (A_BYTES + B_BYTES)) / 4) {
+      small_m_tile(g, add, n0, kbeg, kend, reinterpret_cast<float*>(smem), tid);
+      return;
+    }
+    if (g.rows_dim == 2 && g.K <= SMALL_ROWS) { small_k_tile(g, add, m0, n0, tid); return; }
+  }
 
   if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
   if (warp == 1) tmem_alloc(&tmem_slot, 64);

@@ -201,8 +201,10 @@ def _id_patterns(N, num_codes, g):
 @pytest.mark.parametrize("N,S", [(96, 160), (37, 32), (1500, 32)])
 def test_shared_codes_match_per_ray_codes(dev, N, S, monkeypatch):
     """The fused embedding-lookup path (one evaluation of the code layers per run of equal ids, dense table gradients)
-    against the same bf16 kernels fed per-ray code rows through torch.nn.Embedding: same raw output bit for bit (identical
-    bias-table rows), gradients equal up to fp32 summation order."""
+    against the same bf16 kernels fed per-ray code rows through torch.nn.Embedding.  The bias-table rows agree to fp32
+    rounding (<= 8 code rows take the exact-fp32 few-row path of gemm_tc.cu, the per-ray path the split-bf16 tensor-core
+    one), so an activation may land on the other side of a bf16 rounding boundary now and then: raw within 2e-3 absolute,
+    every gradient within 5e-3 of its largest magnitude (the stated bf16 bound against fp32 is 3e-2)."""
     import view_synthesis.nerf as nerf
     import view_synthesis.models as models
     g = torch.Generator().manual_seed(N * 13 + S)
@@ -225,11 +227,11 @@ def test_shared_codes_match_per_ray_codes(dev, N, S, monkeypatch):
                 _tc_ok()
                 res[share] = {"raw": raw.detach(), **{"emb." + k: p.grad for k, p in emb.named_parameters()},
                               **{k: p.grad for k, p in m.named_parameters()}}
-            assert torch.equal(res["0"]["raw"], res["1"]["raw"]), name
+            assert (res["0"]["raw"] - res["1"]["raw"]).abs().max().item() < 2e-3, name
             for k in res["0"]:
                 a, b = res["1"][k].double(), res["0"][k].double()
                 assert torch.isfinite(a).all(), (name, k)
                 err = ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
-                assert err < 2e-4, (name, k, err)
+                assert err < 5e-3, (name, k, err)
     finally:
         nerf.set_precision("fp32")
