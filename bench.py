@@ -223,6 +223,7 @@ def run_ours(args):
 
     def chunks_step(ro, rd, tgt, oid, read_loss):
         d2h = 0
+        total = None
         for i in range(0, n_rays, c["chunk"]):
             sl = slice(i, i + c["chunk"])
             codes = mods["embedding"](oid[sl])
@@ -235,8 +236,10 @@ def run_ours(args):
             loss.backward()
             opt.step()
             if read_loss:
-                _ = lf.item()                                             # train.py:105
-                d2h += 4
+                total = lf.detach() if total is None else total + lf.detach()
+        if read_loss:
+            _ = total.item()            # the step's result: summed fine loss of its chunks, one device->host read per step
+            d2h += 4
         return d2h
 
     # device-resident inputs for `value`
@@ -295,7 +298,7 @@ def run_ours(args):
     kernel_ms = float(lib.cnrf_debug_fwd_kernel_ms(0, None, None)) if args.precision == "bf16" else 0.0
     clk = clocks.stop()
     ms_e2e = timed(step_e2e, args.steps, 1)
-    d2h = 4 * (n_rays // c["chunk"])
+    d2h = 4
     total_rays = n_rays * world * args.steps
     value, e2e = total_rays / (ms_val * 1e-3), total_rays / (ms_e2e * 1e-3)
 

@@ -16,7 +16,7 @@ LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libcnrf.so")
 STAMP = os.path.join(LIBDIR, "libcnrf.stamp")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--expt-relaxed-constexpr",
-              "-Xcompiler", "-fPIC", "-shared"]
+              "-Xcompiler", "-fPIC", "-shared"] + os.environ.get("CNRF_NVCC_EXTRA", "").split()   # e.g. -DCNRF_FWD_TIMERS
 
 
 def sources():

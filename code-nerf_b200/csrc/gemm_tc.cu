@@ -119,11 +119,17 @@ __device__ void small_m_tile(const GemmArgs& g, bool add, int64_t n0, int64_t kb
   for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = 0.f;
   if (n < g.N) {
     const float* bp = g.B + n * g.b_cs + kbeg * g.b_rs;
-#pragma unroll 4
-    for (int k = k0; k < k1; ++k) {
-      const float bv = __ldg(bp + (int64_t)k * g.b_rs);
+    constexpr int U = 16;                              // loads in flight per thread: the loop is pure latency
+    for (int kb = k0; kb < k1; kb += U) {
+      float bv[U];
 #pragma unroll
-      for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = fmaf(a_s[m * KK + k], bv, acc[m]);
+      for (int u = 0; u < U; ++u) bv[u] = kb + u < k1 ? __ldg(bp + (int64_t)(kb + u) * g.b_rs) : 0.f;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int k = kb + u < k1 ? kb + u : k0;       // bv is 0 past the end
+#pragma unroll
+        for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = fmaf(a_s[m * KK + k], bv[u], acc[m]);
+      }
     }
   }
 #pragma unroll
