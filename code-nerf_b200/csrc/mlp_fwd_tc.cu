@@ -12,6 +12,7 @@
 //            row, TMEM lane quarter = warp_id % 4).
 // The epilogue is specialised per layer at compile time and fully unrolled: TMEM -> registers -> + bias -> ReLU -> bf16
 // -> swizzled smem (the next layer's A operand, also TMA-stored as the image the backward needs).
+#include <cstdlib>
 #include "mlp_tc.cuh"
 
 __device__ long long g_fwd_dbg[16];
@@ -39,6 +40,7 @@ struct FBars {
   uint64_t w_full[FRING], w_empty[FRING];
   uint64_t a_ready[2];     // epilogue -> MMA : tile's operand image written
   uint64_t acc_full[2];    // MMA -> epilogue : tile's accumulator complete
+  uint64_t w_peer[FRING];  // CTA pairs: the other CTA's half of the weight image has landed (forwarded by its warp 1)
   uint32_t tmem_slot;
   int abort_flag;
 };
@@ -56,6 +58,23 @@ __device__ __forceinline__ bool fwait(uint64_t* bar, uint32_t parity, FBars* b, 
       return false;
     }
   }
+}
+// the same against arrivals from the other CTA of a pair (cluster-scope acquire)
+__device__ __forceinline__ bool fwait_cluster(uint64_t* bar, uint32_t parity, FBars* b, int* err) {
+  if (mbar_try_wait_cluster(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (true) {
+    if (mbar_try_wait_cluster(bar, parity)) return true;
+    if (*(volatile int*)&b->abort_flag) return false;
+    if (clock64() - t0 > 2000000000LL) {
+      b->abort_flag = 1;
+      if (err) atomicExch(err, 1);
+      return false;
+    }
+  }
+}
+__device__ __forceinline__ bool uwait_cluster(uint64_t* bar, uint32_t parity, FBars* b, int* err) {
+  return __all_sync(0xFFFFFFFFu, fwait_cluster(bar, parity, b, err));
 }
 // the same for a whole warp, with a result the compiler can prove warp-uniform (keeps the MMA issuer's state in uniform
 // registers)
@@ -81,6 +100,7 @@ struct Epi {               // per-thread state of an epilogue thread for the cur
   uint8_t* sv;
   float sigma;
   float px, py, pz;        // this row's sample point of the NEXT pair (prefetched while the current pair runs)
+  uint32_t ar_cluster;     // CTA pairs: shared::cluster address of the LEADER's a_ready barrier of this tile (0: single CTA)
 };
 
 // copy the `nrays` bias rows [ray0, ray0 + nrays) of a [N,256] fp32 table into the tile's staging area (128 threads)
@@ -114,6 +134,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if (c.elected) bulk_wait_read0();                 // the previous image store no longer reads this tile
   if ((E == 1 || E == 2) && !GB) cp_async_wait_all();
   named_bar_sync(c.bar_id, 128);
+  const long long tw2 = FCLK();
   const float4* hw = reinterpret_cast<const float4*>(c.heads);
   float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f, rgb3 = 0.f, rgb4 = 0.f, rgb5 = 0.f;   // two partial sums per channel
   float sg0 = 0.f, sg1 = 0.f, sg2 = 0.f, sg3 = 0.f;                               // four partial sums of the sigma head
@@ -184,17 +205,28 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if (E == 1) c.sigma = (sg0 + sg1) + (sg2 + sg3) + tail0;
   if (E == 4 && c.valid)                            // [rgb_raw | sigma_raw]   models/model.py:194
     reinterpret_cast<float4*>(a.raw)[c.m] = make_float4(rgb0 + rgb3 + tail0, rgb1 + rgb4 + tail1, rgb2 + rgb5 + tail2, c.sigma);
+  const long long tw3 = FCLK();
   fence_proxy_async();
   tc_fence_before();
   named_bar_sync(c.bar_id, 128);
+  const long long tw4 = FCLK();
+  if (c.elected && t == 0) { FDBG(10, tw2 - tw1); FDBG(11, tw3 - tw2); FDBG(12, tw4 - tw3); }
   if (c.elected) {
+    // the hand-off first: a cluster-scope release issued after the bulk store waits for that store (~3.5 k clk)
+    if (E < 4) { if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&c.bars->a_ready[t]); }
     if (c.sv) { bulk_s2g(c.sv + SAVED_GAMMA + (size_t)E * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
-    if (E < 4) mbar_arrive(&c.bars->a_ready[t]);
-    if (t == 0) { FDBG(0, tw1 - tw0); FDBG(1 + E, FCLK() - tw1); }
+    if (t == 0) { FDBG(0, tw1 - tw0); FDBG(1 + E, FCLK() - tw1); FDBG(13, FCLK() - tw4); }
   }
   return true;
 }
 
+// CG = 1: one CTA per SM on its own.  CG = 2: the CTAs of a cluster of two (the SMs of one TPC) run ONE tcgen05.mma of
+// M = 256 per step (cta_group::2): each CTA keeps its own pair of 128-row tiles and streams only HALF of every weight
+// image (its 128 of the 256 output features), so a whole layer (4 x 16 KB) fits the 5-slot ring ahead of time -- the
+// single-CTA kernel waits one L2 round trip per (layer, tile) for the images the ring cannot hold -- and the tensor core
+// reads half as many operand bytes from shared memory per FLOP.  The leader CTA (cluster rank 0) issues; the other CTA's
+// warp 1 forwards "my half has landed" to the leader, and both CTAs' epilogues report to the leader's a_ready barriers.
+template <int CG>
 __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];   // 128-byte-swizzled images need 1024-byte alignment
   uint8_t* tiles = smem;
@@ -205,39 +237,47 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t num_tiles = (a.M + TILE - 1) / TILE;
   const int64_t num_pairs = (num_tiles + 1) / 2;
+  const uint32_t rank = CG == 2 ? cluster_ctarank() : 0u;
+  // both CTAs of a pair run the same number of iterations: pair index = pair_base + rank (possibly past the end: an
+  // all-padding pair that computes on zeros and stores nothing)
+  const int64_t pair_first = (int64_t)blockIdx.x - rank;
 
   if (tid == 0) {
-    for (int i = 0; i < FRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
+    for (int i = 0; i < FRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); mbar_init(&bars->w_peer[i], 1); }
+    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], CG); mbar_init(&bars->acc_full[t], 1); }
     bars->abort_flag = 0;
     if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
     mbar_fence_init();
   }
   for (int i = tid; i < HEAD_FLOATS; i += NTHREADS) heads[i] = a.pk.w_sigma[i];   // w_sigma | w_rgb | b_dir2 are contiguous
-  if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
+  if (warp == 1) { if (CG == 2) tmem_alloc2(&bars->tmem_slot, 512); else tmem_alloc(&bars->tmem_slot, 512); }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();                      // the peer's barriers exist before anyone arrives on them
   tc_fence_after();
   const uint32_t tmem = bars->tmem_slot;
 
   if (warp == 0) {
     // ===== TMA producer =====
     // The two tiles of a pair run half a layer apart (T1's MMAs overlap T0's epilogue), so a layer's weight images pass
-    // through the ring once per tile: per (layer, tile) the N-halves of its K-chunks in order; layer_dir1 is followed by
-    // its extension (this pair's [gamma(d) | 1] slab, then the two halves of [Wdv | b_dir1]).
+    // through the ring once per tile: per (layer, tile) the N-halves of its K-chunks in order (CG = 2: only this CTA's
+    // half); layer_dir1 is followed by its extension (this pair's [gamma(d) | 1] slab, then [Wdv | b_dir1]).
     if (lane == 0) {
       uint32_t slot = 0, epar = 1;          // ring slot and the parity its w_empty barrier is waited with
       bool ok = true;
-      for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+      for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
+        const int64_t pr = pb + rank < num_pairs ? pb + rank : num_pairs - 1;    // padding pair: any valid slab will do
         for (int layer = 0; layer < 5 && ok; ++layer) {
           const int first = layer == 0 ? 0 : 2 + 8 * (layer - 1);          // half-image index in a.pk.fwd
-          const int count = (layer == 0 ? 2 : 8) + (layer == 3 ? 3 : 0);
+          const int nmain = (layer == 0 ? 2 : 8) / CG;                       // weight images of the layer proper
+          const int count = nmain + (layer == 3 ? 1 + 2 / CG : 0);
           for (int t = 0; t < 2 && ok; ++t) {
             for (int i = 0; i < count; ++i) {
               if (!fwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
-              const uint8_t* src = (layer == 3 && i == 8) ? a.ext + (size_t)pr * SLAB
-                                 : (layer == 3 && i > 8) ? a.pk.fwd + (size_t)EXT_CHUNK * CHUNK + (size_t)(i - 9) * HALF
-                                                         : a.pk.fwd + (size_t)(first + i) * HALF;
+              const uint8_t* src;
+              if (i < nmain) src = a.pk.fwd + (size_t)(first + (CG == 2 ? 2 * i + (int)rank : i)) * HALF;
+              else if (i == nmain) src = a.ext + (size_t)pr * SLAB;
+              else src = a.pk.fwd + (size_t)EXT_CHUNK * CHUNK + (size_t)(CG == 2 ? (int)rank : i - nmain - 1) * HALF;
               mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
               bulk_g2s(ring + slot * HALF, src, HALF, &bars->w_full[slot]);
               if (++slot == FRING) { slot = 0; epar ^= 1u; }
@@ -247,6 +287,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
         if (*(volatile int*)&bars->abort_flag) break;
       }
     }
+  } else if (warp == 1 && CG == 2 && rank != 0) {
+    // ===== CTA pairs, second CTA: tell the leader when this CTA's half of each weight image has landed =====
+    {
+      uint32_t slot = 0, wpar = 0;
+      bool ok = true;
+      for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
+#pragma unroll 1
+        for (int layer = 0; layer < 5 && ok; ++layer) {
+          const int count = 2 * ((layer == 0 ? 1 : 4) + (layer == 3 ? 2 : 0));     // both tiles
+#pragma unroll 1
+          for (int i = 0; i < count && ok; ++i) {
+            if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; break; }
+            if (elect_one()) mbar_arrive_cluster(mapa_u32(smem_u32(&bars->w_peer[slot]), 0));
+            __syncwarp();
+            if (++slot == FRING) { slot = 0; wpar ^= 1u; }
+          }
+        }
+      }
+    }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     // Every lane runs the (warp-uniform) control flow so that ring counters, descriptors and TMEM addresses live in
@@ -254,38 +313,41 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     // ptxas keeps that state in vector registers and pays an R2UR chain per MMA: ~125 instructions per weight image.)
     {
       const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);       // provably warp-uniform copy
-      const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
+      const uint32_t idesc = CG == 2 ? idesc_bf16(256, 256, 0, 0) : idesc_bf16(128, 128, 0, 0);
       // descriptors differ only in their 14-bit start-address field (bytes >> 4): precompute the bases, add offsets
       const uint64_t a_desc0 = smem_desc(smem_u32(tiles), 16, 1024, SWIZZLE_128B);
       const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
       uint32_t slot = 0, wpar = 0, na = 0;        // ring slot, its w_full parity, a_ready parity counter
       bool ok = true;
 #define NEXT_SLOT() do { if (++slot == FRING) { slot = 0; wpar ^= 1u; } } while (0)
-      for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+#define WAIT_IMAGE() (uwait(&bars->w_full[slot], wpar, bars, a.err) && (CG == 1 || uwait_cluster(&bars->w_peer[slot], wpar, bars, a.err)))
+#define MMA(d, ad, bd, acc) do { if (CG == 2) umma_bf16_2cta(d, ad, bd, idesc, acc); else umma_bf16(d, ad, bd, idesc, acc); } while (0)
+#define COMMIT(bar) do { if (CG == 2) umma_commit_2cta(bar); else umma_commit(bar); } while (0)
+      for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
 #pragma unroll 1
         for (int layer = 0; layer < 5 && ok; ++layer, ++na) {
           const int nch = layer == 0 ? 1 : 4;
 #pragma unroll 1
           for (int t = 0; t < 2 && ok; ++t) {
             const long long m1 = FCLK();
-            if (!uwait(&bars->a_ready[t], na & 1, bars, a.err)) { ok = false; break; }
+            if (!(CG == 2 ? uwait_cluster(&bars->a_ready[t], na & 1, bars, a.err) : uwait(&bars->a_ready[t], na & 1, bars, a.err))) { ok = false; break; }
             FDBG(9, FCLK() - m1);
             const uint32_t d0 = tmem_u + t * 256;
 #pragma unroll 1
             for (int c = 0; c < nch && ok; ++c) {
               const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
 #pragma unroll
-              for (int h = 0; h < 2; ++h) {
+              for (int h = 0; h < 2 / CG; ++h) {      // CG = 1: the two N-halves of the chunk; CG = 2: one MMA of N = 256
                 if (!ok) continue;
                 const long long m0 = FCLK();
-                if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; continue; }
+                if (!WAIT_IMAGE()) { ok = false; continue; }
                 FDBG(8, FCLK() - m0);
                 tc_fence_after();
                 const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
                 if (elect_one()) {
 #pragma unroll
-                  for (int k = 0; k < 4; ++k) umma_bf16(d0 + h * 128, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
-                  umma_commit(&bars->w_empty[slot]);
+                  for (int k = 0; k < 4; ++k) MMA(d0 + h * 128, ad + 2 * k, bd + 2 * k, (c | k) != 0);
+                  COMMIT(&bars->w_empty[slot]);
                 }
                 __syncwarp();
                 NEXT_SLOT();
@@ -293,31 +355,34 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
             }
             if (layer == 3 && ok) {        // += [gamma(d_pair) | 1] [Wdv | b_dir1]^T : K = 32 columns per tile of the shared slab
               const uint32_t slot_x = slot;
-              if (!uwait(&bars->w_full[slot_x], wpar, bars, a.err)) { ok = false; break; }
+              if (!WAIT_IMAGE()) { ok = false; break; }
               NEXT_SLOT();
               const uint64_t xd = b_desc0 + (uint64_t)((slot_x * HALF) >> 4);
 #pragma unroll
-              for (int h = 0; h < 2; ++h) {
+              for (int h = 0; h < 2 / CG; ++h) {
                 if (!ok) continue;
-                if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; continue; }
+                if (!WAIT_IMAGE()) { ok = false; continue; }
                 tc_fence_after();
                 const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
                 if (elect_one()) {
 #pragma unroll
-                  for (int k = 0; k < 2; ++k) umma_bf16(d0 + h * 128, xd + 2 * (2 * t + k), bd + 2 * k, idesc, 1);
-                  umma_commit(&bars->w_empty[slot]);
+                  for (int k = 0; k < 2; ++k) MMA(d0 + h * 128, xd + 2 * (2 * t + k), bd + 2 * k, 1);
+                  COMMIT(&bars->w_empty[slot]);
                 }
                 __syncwarp();
                 NEXT_SLOT();
               }
-              if (ok && elect_one()) umma_commit(&bars->w_empty[slot_x]);
+              if (ok && elect_one()) COMMIT(&bars->w_empty[slot_x]);
             }
-            if (ok && elect_one()) umma_commit(&bars->acc_full[t]);
+            if (ok && elect_one()) COMMIT(&bars->acc_full[t]);
             __syncwarp();
           }
         }
       }
 #undef NEXT_SLOT
+#undef WAIT_IMAGE
+#undef MMA
+#undef COMMIT
     }
   } else {
     // ===== epilogue warps: thread = one sample row =====
@@ -332,6 +397,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     c.bar_id = 1 + t;
     c.elected = ((warp - 2) & 3) == 0 && lane == 0;
     c.tacc = tmem + t * 256 + ((uint32_t)(q * 32) << 16);
+    c.ar_cluster = CG == 2 ? mapa_u32(smem_u32(&bars->a_ready[t]), 0) : 0u;
     uint32_t na = 0;
     // the usual encoding (include_input, L = 10 octaves from 1.0) is built in registers from prefetched points
     bool pe_fast = a.pts != nullptr && a.inc && a.L == 10;
@@ -341,10 +407,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     }
     c.px = c.py = c.pz = 0.f;
     if (pe_fast) {
-      const int64_t m1 = ((int64_t)blockIdx.x * 2 + t) * TILE + c.r;
+      const int64_t m1 = ((int64_t)blockIdx.x * 2 + t) * TILE + c.r;      // blockIdx.x = pair_first + rank
       if (m1 < a.M) { c.px = __ldg(a.pts + m1 * 3); c.py = __ldg(a.pts + m1 * 3 + 1); c.pz = __ldg(a.pts + m1 * 3 + 2); }
     }
-    for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
+    for (int64_t pb = pair_first; pb < num_pairs; pb += gridDim.x) {
+      const int64_t pr = pb + rank;
       const int64_t tile_idx = pr * 2 + t;
       const int64_t first = tile_idx * TILE;
       c.m = first + c.r;
@@ -384,8 +451,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       fence_proxy_async();
       named_bar_sync(c.bar_id, 128);
       if (c.elected) {
+        if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&bars->a_ready[t]);
         if (c.sv) { bulk_s2g(c.sv, c.tile, SLAB); bulk_commit(); }
-        mbar_arrive(&bars->a_ready[t]);
         if (t == 0) { FDBG(6, FCLK() - tb0); FDBG(7, 1); }
       }
       bool ok = epi_layer<0, false>(a, c, t, na & 1); ++na;
@@ -403,20 +470,44 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 512);
+  if (CG == 2) cluster_sync_all();                      // nobody leaves while the peer may still arrive on its barriers
+  if (warp == 1) { if (CG == 2) tmem_dealloc2(tmem, 512); else tmem_dealloc(tmem, 512); }
 }
 }  // namespace
 
 int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
-    if (e != cudaSuccess) return (int)e;
-    attr_set = true;
+  // CNRF_FWD_CTA_PAIRS=1 selects the cta_group::2 kernel.  Measured on B200 (fine pass, 655,360 rows): 585 us against
+  // 574 us for the single-CTA kernel -- the pair halves the weight traffic and the accumulator wait (37 k -> 20 k clk per
+  // tile pair) but pays ~1 k clk per cluster-scope hand-off (five per tile), so it is not the default yet.
+  static int pair_mode = -1;
+  if (pair_mode < 0) {
+    const char* e = getenv("CNRF_FWD_CTA_PAIRS");
+    pair_mode = e ? atoi(e) != 0 : 0;
+    cudaError_t e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    cudaError_t e2 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+    if (e1 != cudaSuccess || e2 != cudaSuccess) { pair_mode = -1; return (int)(e1 != cudaSuccess ? e1 : e2); }
   }
+  { static int g_override = -1; if (g_override < 0) { const char* e = getenv("CNRF_FWD_GRID"); g_override = e ? atoi(e) : 0; }
+    if (g_override > 0 && g_override < grid) grid = g_override; }       // tuning aid: fewer CTAs
   const bool timed = cnrf_ktimer_begin(CNRF_KT_FWD, f.M, st);
-  mlp_fwd_tc_kernel<<<grid, NTHREADS, FWD_SMEM, st>>>(f);
-  CNRF_LAUNCH_CHECK();
+  if (pair_mode && grid >= 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(grid & ~1));         // whole clusters only
+    cfg.blockDim = dim3(NTHREADS);
+    cfg.dynamicSmemBytes = FWD_SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, mlp_fwd_tc_kernel<2>, f);
+    if (e != cudaSuccess) return (int)e;
+    ++g_cnrf_launches;
+  } else {
+    mlp_fwd_tc_kernel<1><<<grid, NTHREADS, FWD_SMEM, st>>>(f);
+    CNRF_LAUNCH_CHECK();
+  }
   if (timed) cnrf_ktimer_end(CNRF_KT_FWD, st);
   return CNRF_OK;
 }

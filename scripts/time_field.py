@@ -42,5 +42,7 @@ try:
     n = max(1, int(buf[7]))
     print("block0/tile0 per pair [clk]: wait_acc(total of 5) %d | epi L0..L4 %s | build %d | MMA-warp waits: weights %d, a_ready %d | pairs %d" %
           (buf[0] // n, [int(buf[1 + i] // n) for i in range(5)], buf[6] // n, buf[8] // n, buf[9] // n, n))
+    print("  epilogue split per pair (5 layers): store-drain + barrier %d | blocks %d | closing barrier %d | store issue + arrive %d" %
+          (buf[10] // n, buf[11] // n, buf[12] // n, buf[13] // n))
 except Exception as e:
     print("no fwd debug times:", e)

@@ -235,3 +235,41 @@ def test_shared_codes_match_per_ray_codes(dev, N, S, monkeypatch):
                 assert err < 5e-3, (name, k, err)
     finally:
         nerf.set_precision("fp32")
+
+
+@pytest.mark.gpu
+def test_forward_cta_pair_kernel_matches_single_cta(dev):
+    """The cta_group::2 forward kernel (two CTAs of a cluster share one M = 256 tcgen05.mma; CNRF_FWD_CTA_PAIRS=1, read at
+    the first launch) against the default single-CTA kernel: same weights, same rows -> the raw field must agree to the
+    last bit except for the accumulation order inside the tensor core (none: the K order is identical), so exact."""
+    import subprocess, sys, os
+    code = r'''
+import sys, os, torch
+sys.path.insert(0, os.path.join(os.getcwd(), "code-nerf_b200")); sys.path.insert(0, os.getcwd())
+import view_synthesis.nerf as nerf, view_synthesis.models as models
+from codenerf_b200 import _lib
+dev = torch.device("cuda", 0)
+torch.manual_seed(3)
+nerf.set_precision("bf16")
+m = models.CodeNeRFModel(256, 1, 256, 256, 10, 4, True, True).to(dev)
+emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+g = torch.Generator().manual_seed(1)
+N, S = 700, 160
+pts = (torch.rand(N, S, 3, generator=g) * 3 - 1.5).to(dev); rd = torch.randn(N, 3, generator=g).to(dev)
+zs = torch.randn(N, 256, generator=g).to(dev).requires_grad_(True); zt = torch.randn(N, 256, generator=g).to(dev)
+raw = nerf.forward_pass(m, emb, rd, pts, (zs, zt))
+raw.backward(torch.ones_like(raw))
+assert _lib.load().cnrf_debug_tc_error() == 0
+torch.save({"raw": raw.detach().cpu(), "g": zs.grad.cpu(), "w": m.layer_xyz2.weight.grad.cpu()}, sys.argv[1])
+'''
+    import tempfile
+    out = {}
+    with tempfile.TemporaryDirectory() as d:
+        for mode in ("0", "1"):
+            env = dict(os.environ, CNRF_FWD_CTA_PAIRS=mode)
+            path = os.path.join(d, f"o{mode}.pt")
+            subprocess.run([sys.executable, "-c", code, path], check=True, env=env, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+            out[mode] = torch.load(path)
+    assert torch.equal(out["0"]["raw"], out["1"]["raw"])
+    assert torch.equal(out["0"]["g"], out["1"]["g"])
+    assert torch.allclose(out["0"]["w"], out["1"]["w"], rtol=1e-4, atol=1e-5)     # atomics: summation order
