@@ -63,6 +63,7 @@ _SIGS = {
     "cnrf_field_bwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
                                  c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.POINTER(PtrTable), c_f32p,
                                  c_f32p, c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_adamw_step": (C.c_int, [C.c_void_p, c_i32, c_f, c_f, c_f, C.c_void_p]),
     "cnrf_field_fwd_ids": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
                                      C.c_void_p, c_i64, c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.c_void_p,
                                      c_sz, C.c_void_p]),

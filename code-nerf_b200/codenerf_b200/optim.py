@@ -1,0 +1,71 @@
+"""Fused AdamW for the training step of train.py:111-114 ("next" row f3).
+
+`FusedAdamW` is a drop-in for `torch.optim.AdamW` (same constructor arguments, same per-parameter state keys `step`,
+`exp_avg`, `exp_avg_sq`, so `state_dict()` / `load_state_dict()` interchange with the reference's checkpoints,
+`utils/util.py:147-172`).  `step()` updates every CUDA fp32 parameter that has a gradient with ONE libcnrf launch
+(csrc/adamw.cu); it never synchronises.  Anything else (CPU tensors, other dtypes, sparse gradients, amsgrad / maximize)
+is refused loudly -- there is no silent fallback.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+
+class _AdamWTensor(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("numel", C.c_int64), ("lr", C.c_float), ("weight_decay", C.c_float), ("step", C.c_float)]
+
+
+class FusedAdamW(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, amsgrad=False, maximize=False):
+        if amsgrad or maximize:
+            raise ValueError("FusedAdamW implements plain AdamW only (amsgrad=False, maximize=False)")
+        if not 0.0 <= lr or not 0.0 <= eps or not 0.0 <= betas[0] < 1.0 or not 0.0 <= betas[1] < 1.0 or not 0.0 <= weight_decay:
+            raise ValueError("invalid AdamW hyper-parameter")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=False,
+                                      maximize=False))
+        self._table = None          # cached ctypes array: parameter / state pointers do not change between steps
+
+    def _init_state(self, p):
+        st = self.state[p]
+        if len(st) == 0:
+            st["step"] = torch.tensor(0.0, dtype=torch.float32)
+            st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+            st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+        return st
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        lib = _lib.load()
+        by_betas = {}
+        for group in self.param_groups:
+            key = (float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]))
+            rows = by_betas.setdefault(key, [])
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                g = p.grad
+                if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()) or g.is_sparse or g.dtype != torch.float32:
+                    raise _lib.CnrfError("FusedAdamW needs contiguous CUDA fp32 parameters with dense fp32 gradients")
+                st = self._init_state(p)
+                st["step"] += 1
+                rows.append((p, g if g.is_contiguous() else g.contiguous(), st, float(group["lr"]),
+                             float(group["weight_decay"])))
+        stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        for (b1, b2, eps), rows in by_betas.items():
+            if not rows:
+                continue
+            tab = (_AdamWTensor * len(rows))()
+            for i, (p, g, st, lr, wd) in enumerate(rows):
+                t = tab[i]
+                t.param, t.grad = p.data_ptr(), g.data_ptr()
+                t.exp_avg, t.exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+                t.numel, t.lr, t.weight_decay, t.step = p.numel(), lr, wd, float(st["step"])
+            _lib.check(lib.cnrf_adamw_step(C.cast(tab, C.c_void_p), len(rows), b1, b2, eps, stream), "cnrf_adamw_step")
+        return loss

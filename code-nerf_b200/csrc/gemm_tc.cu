@@ -151,17 +151,25 @@ __device__ void small_k_tile(const GemmArgs& g, bool add, int64_t m0, int64_t n0
   const int nl = tid & 63, mq = tid >> 6;
   const int64_t n = n0 + nl;
   if (n >= g.N) return;
-  float bv[SMALL_ROWS];
+  // all loads of a k step are issued before they are used: 32 independent rows per thread, no atomics in between
+  float y[GBM / 4];
 #pragma unroll
-  for (int k = 0; k < SMALL_ROWS; ++k) bv[k] = k < K ? __ldg(g.B + (int64_t)k * g.b_rs + n * g.b_cs) : 0.f;
+  for (int i = 0; i < GBM / 4; ++i) y[i] = 0.f;
+  for (int k = 0; k < K; ++k) {
+    float av[GBM / 4];
+#pragma unroll
+    for (int i = 0; i < GBM / 4; ++i) {
+      const int64_t m = m0 + mq + 4 * i;
+      av[i] = m < g.M ? __ldg(g.A + m * g.a_rs + (int64_t)k * g.a_cs) : 0.f;
+    }
+    const float b = __ldg(g.B + (int64_t)k * g.b_rs + n * g.b_cs);
+#pragma unroll
+    for (int i = 0; i < GBM / 4; ++i) y[i] = fmaf(av[i], b, y[i]);
+  }
+#pragma unroll
   for (int i = 0; i < GBM / 4; ++i) {
     const int64_t m = m0 + mq + 4 * i;
-    if (m >= g.M) break;
-    float y = 0.f;
-#pragma unroll
-    for (int k = 0; k < SMALL_ROWS; ++k)
-      if (k < K) y = fmaf(__ldg(g.A + m * g.a_rs + (int64_t)k * g.a_cs), bv[k], y);
-    small_epilogue(g, add, m, n, y);
+    if (m < g.M) small_epilogue(g, add, m, n, y[i]);
   }
 }
 

@@ -210,6 +210,21 @@ int cnrf_field_bwd_ids(const cnrf_field_shape* s, const cnrf_codenerf_params* p,
                        float* g_tab_s, float* g_tab_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Optimiser step (SURVEY section 8 "next" row f3): torch.optim.AdamW as train.py:111-114 runs it, every parameter tensor
+ * of the step in one launch.  `tensors` is a HOST array; all pointers inside are device fp32 buffers of `numel` elements.
+ * step >= 1 is the 1-based step count of that tensor (bias correction).  Arithmetic per element:
+ *   p -= lr*wd*p;  m += (g-m)(1-beta1);  v = beta2 v + (1-beta2) g^2;
+ *   p -= lr/(1-beta1^step) * m / (sqrt(v)/sqrt(1-beta2^step) + eps)
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct {
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+  int64_t numel;
+  float lr, weight_decay, step;
+} cnrf_adamw_tensor;
+int cnrf_adamw_step(const cnrf_adamw_tensor* tensors, int32_t count, float beta1, float beta2, float eps,
+                    cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Diagnostics (used by tests only).  One-CTA tcgen05 GEMM over the 128-byte-swizzled shared-memory image the fused
  * MLP kernels use.  mode 0: D[128,N] = A[128,K] B[N,K]^T (K-major operands); mode 1: D[128,N] = A[K,128]^T B[K,N]
  * (MN-major operands, the dW = dY^T X form).  *err is set to 1 if the kernel's bounded barrier wait timed out.

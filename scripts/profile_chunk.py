@@ -21,8 +21,9 @@ torch.manual_seed(0); np.random.seed(0)
 mods = {"embedding": models.ShapeTextureEmbedding(2458, 256, 256).to(dev),
         "nerf_coarse": models.CodeNeRFModel(256, 2458, 256, 256, 10, 4).to(dev),
         "nerf_fine": models.CodeNeRFModel(256, 2458, 256, 256, 10, 4).to(dev)}
-opt = torch.optim.AdamW([{"params": mods["nerf_coarse"].parameters()}, {"params": mods["nerf_fine"].parameters()},
-                         {"params": mods["embedding"].parameters(), "lr": 1e-3}], lr=1e-4, fused=True)
+from codenerf_b200.optim import FusedAdamW
+opt = FusedAdamW([{"params": mods["nerf_coarse"].parameters()}, {"params": mods["nerf_fine"].parameters()},
+                         {"params": mods["embedding"].parameters(), "lr": 1e-3}], lr=1e-4)
 ps = nerf.PointSampler(32, 128, 0.8, 1.8, "lindepth", True, torch.float32, dev)
 emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
 ro = torch.tensor([0.0, 0.0, 1.3], device=dev).expand(N, 3).contiguous() + 0.01 * torch.randn(N, 3, device=dev)
