@@ -101,47 +101,53 @@ __device__ __forceinline__ void small_epilogue(const GemmArgs& g, bool add, int6
   *c = y;
 }
 
-// rows_dim == 1: M <= SMALL_ROWS output rows, this CTA owns columns [n0, n0 + 64) and k in [kbeg, kend)
-__device__ void small_m_tile(const GemmArgs& g, bool add, int64_t n0, int64_t kbeg, int64_t kend, float* sm, int tid) {
+// rows_dim == 1: M <= SMALL_ROWS output rows.  The launch was sized for the worst case (one row tile per 128 rays), so
+// the row tiles mx = 1..3 of a column tile are idle CTAs: they take a quarter of its 64 columns each (nsub = 4), and a
+// CTA's 256 threads split K sixteen ways -- every thread issues its <= 16 weight loads in one go (the whole tile is a
+// single global-memory round trip) and the partial sums meet in shared memory.
+__device__ void small_m_tile(const GemmArgs& g, bool add, int64_t n0, int ncols, int64_t kbeg, int64_t kend, float* sm, int tid) {
   const int M = (int)g.M, KK = (int)(kend - kbeg);
   float* a_s = sm;                                   // [SMALL_ROWS][KK]
-  float* red = sm + SMALL_ROWS * KK;                 // [4][SMALL_ROWS][64]
+  float* red = sm + SMALL_ROWS * KK;                 // [16][SMALL_ROWS][16]
   for (int i = tid; i < SMALL_ROWS * KK; i += GTHREADS) {
     const int m = i / KK, k = i - m * KK;
     a_s[i] = m < M ? __ldg(g.A + (int64_t)m * g.a_rs + (kbeg + k) * g.a_cs) : 0.f;
   }
   __syncthreads();
-  const int nl = tid & 63, kq = tid >> 6;
-  const int64_t n = n0 + nl;
-  const int kper = (KK + 3) / 4, k0 = kq * kper, k1 = min(KK, k0 + kper);
-  float acc[SMALL_ROWS];
+  constexpr int U = 16;
+  for (int c0 = 0; c0 < ncols; c0 += 16) {            // one pass when the column tile is shared by four CTAs
+    const int nl = tid & 15, ks = tid >> 4;
+    const int64_t n = n0 + c0 + nl;
+    float acc[SMALL_ROWS];
 #pragma unroll
-  for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = 0.f;
-  if (n < g.N) {
-    const float* bp = g.B + n * g.b_cs + kbeg * g.b_rs;
-    constexpr int U = 16;                              // loads in flight per thread: the loop is pure latency
-    for (int kb = k0; kb < k1; kb += U) {
-      float bv[U];
+    for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = 0.f;
+    if (nl + c0 < ncols && n < g.N) {
+      const float* bp = g.B + n * g.b_cs + kbeg * g.b_rs;
+      for (int kb = ks * U; kb < KK; kb += 16 * U) {
+        float bv[U];
 #pragma unroll
-      for (int u = 0; u < U; ++u) bv[u] = kb + u < k1 ? __ldg(bp + (int64_t)(kb + u) * g.b_rs) : 0.f;
+        for (int u = 0; u < U; ++u) bv[u] = kb + u < KK ? __ldg(bp + (int64_t)(kb + u) * g.b_rs) : 0.f;
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int k = kb + u < k1 ? kb + u : k0;       // bv is 0 past the end
+        for (int u = 0; u < U; ++u) {
+          const int k = kb + u < KK ? kb + u : 0;      // bv is 0 past the end
 #pragma unroll
-        for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = fmaf(a_s[m * KK + k], bv[u], acc[m]);
+          for (int m = 0; m < SMALL_ROWS; ++m) acc[m] = fmaf(a_s[m * KK + k], bv[u], acc[m]);
+        }
       }
     }
-  }
 #pragma unroll
-  for (int m = 0; m < SMALL_ROWS; ++m) red[(kq * SMALL_ROWS + m) * 64 + nl] = acc[m];
-  __syncthreads();
-  for (int i = tid; i < SMALL_ROWS * 64; i += GTHREADS) {
-    const int m = i >> 6, c = i & 63;
-    if (m < M && n0 + c < g.N) {
-      const float y = (red[(0 * SMALL_ROWS + m) * 64 + c] + red[(1 * SMALL_ROWS + m) * 64 + c]) +
-                      (red[(2 * SMALL_ROWS + m) * 64 + c] + red[(3 * SMALL_ROWS + m) * 64 + c]);
-      small_epilogue(g, add, m, n0 + c, y);
+    for (int m = 0; m < SMALL_ROWS; ++m) red[(ks * SMALL_ROWS + m) * 16 + nl] = acc[m];
+    __syncthreads();
+    if (tid < SMALL_ROWS * 16) {
+      const int m = tid >> 4, c = tid & 15;
+      if (m < M && c0 + c < ncols && n0 + c0 + c < g.N) {
+        float y = 0.f;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) y += red[(q * SMALL_ROWS + m) * 16 + c];
+        small_epilogue(g, add, m, n0 + c0 + c, y);
+      }
     }
+    __syncthreads();
   }
 }
 
@@ -199,16 +205,20 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   const int64_t n0 = (int64_t)ny * GBN;
   const int64_t kbeg = (int64_t)kz * b.kslice[p];
   const int64_t kend = min(g.K, kbeg + b.kslice[p]);
-  if (m0 >= g.M || kbeg >= g.K) return;
   if (g.rows_dev) {
     const bool add = g.split_k > 1 || g.accumulate || multi_k;
-    // the staging buffers of the small-row path must fit the operand-image area: 8 x K + 4 x 8 x 64 floats
-    if (g.rows_dim == 1 && g.M <= SMALL_ROWS && (kend - kbeg) * SMALL_ROWS + 4 * SMALL_ROWS * 64 <= (2 * (A_BYTES + B_BYTES)) / 4) {
-      small_m_tile(g, add, n0, kbeg, kend, reinterpret_cast<float*>(smem), tid);
+    // the staging buffers of the few-row path must fit the operand-image area: 8 x K + 16 x 8 x 16 floats
+    if (g.rows_dim == 1 && g.M <= SMALL_ROWS && kbeg < g.K &&
+        (kend - kbeg) * SMALL_ROWS + 16 * SMALL_ROWS * 16 <= (2 * (A_BYTES + B_BYTES)) / 4) {
+      const int nsub = b.mt[p] >= 4 ? 4 : 1;           // idle row tiles share the column tile
+      if (mx >= nsub) return;
+      small_m_tile(g, add, n0 + (nsub == 4 ? 16 * mx : 0), nsub == 4 ? 16 : GBN, kbeg, kend, reinterpret_cast<float*>(smem), tid);
       return;
     }
+    if (m0 >= g.M || kbeg >= g.K) return;
     if (g.rows_dim == 2 && g.K <= SMALL_ROWS) { small_k_tile(g, add, m0, n0, tid); return; }
   }
+  if (m0 >= g.M || kbeg >= g.K) return;
 
   if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
   if (warp == 1) tmem_alloc(&tmem_slot, 64);

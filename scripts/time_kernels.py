@@ -48,11 +48,14 @@ fine_rows = N * 160
 for k in range(3):
     lib.cnrf_debug_kernel_ms(k, fine_rows, None, None)
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+import time
+t_host0 = time.perf_counter()
 e0.record()
 for _ in range(reps):
     step()
 e1.record()
+t_host = (time.perf_counter() - t_host0) / reps * 1e3       # host time to ENQUEUE one chunk (no synchronisation)
 torch.cuda.synchronize()
 ms = [lib.cnrf_debug_kernel_ms(k, 0, None, None) for k in range(3)]
-print(f"mask={os.environ.get('CNRF_DW_JOBMASK', 'all')} chunk {e0.elapsed_time(e1) / reps:.3f} ms | fine launches: fwd {ms[0] * 1e3:.0f} us, "
+print(f"mask={os.environ.get('CNRF_DW_JOBMASK', 'all')} chunk {e0.elapsed_time(e1) / reps:.3f} ms (host enqueue {t_host:.3f} ms) | fine launches: fwd {ms[0] * 1e3:.0f} us, "
       f"bwd {ms[1] * 1e3:.0f} us, dW {ms[2] * 1e3:.0f} us | tc_err={lib.cnrf_debug_tc_error()}")
