@@ -585,7 +585,7 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
       // 80, 72 and 64 KB for the other three): the kernel is HBM-bound and a single SM only pulls ~45 GB/s
     const int64_t halves = tiles * 2;
     // measured shares (B200, S = 160): reducer-heavy jobs are bound by their four reducer warps, not by their bytes
-    static const int share148[DW_JOBS] = {20, 18, 30, 25, 14, 14, 26};
+    static const int share148[DW_JOBS] = {22, 19, 31, 26, 13, 13, 24};
     static int shares[DW_JOBS] = {0};
     if (!shares[0]) {
       const char* e = getenv("CNRF_DW_SHARES");       // tuning aid: seven comma-separated CTA counts
