@@ -4,6 +4,7 @@ torch is plumbing here: it owns device memory, the current stream and the autogr
 operation of the hot path happens inside libcnrf.so; a non-CUDA tensor or a missing library raises.
 """
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -381,8 +382,15 @@ def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code
 
     code_source = (ids, shape_table, texture_table): z_s / z_t are the rows ids of those tables (ShapeTextureEmbedding's
     output); the bf16 path then shares the code-layer work between rays of equal id (_FieldIds)."""
-    if precision == _lib.PRECISION_BF16 and (pts.requires_grad or rd.requires_grad) and torch.is_grad_enabled():
-        precision = _lib.PRECISION_FP32   # ray / point gradients (camera-pose optimisation, eval.py:129-168) run in fp32
+    pose_grad = (pts.requires_grad or rd.requires_grad) and torch.is_grad_enabled()
+    if precision == _lib.PRECISION_BF16 and pose_grad and os.environ.get("CODENERF_POSE_GRAD_PRECISION", "fp32") != "bf16":
+        # camera-pose optimisation (eval.py:129-168) defaults to the fp32 parity mode: the point gradient sums encoding
+        # terms weighted by frequencies up to 512, and the bf16 chain's fifth backward stage reproduces the fp32 ray
+        # gradients only to ~4 % (cosine 0.999, tests/test_gpu_tc.py::test_tc_pose_gradients_match_fp32).
+        # CODENERF_POSE_GRAD_PRECISION=bf16 opts into the tensor-core path (~50x faster).
+        precision = _lib.PRECISION_FP32
+    if pose_grad:
+        code_source = None                # the shared-code path carries no ray / point gradients
     cfg = (hidden, code, dim_xyz, dim_dir, pairing, precision)
     if code_source is not None and precision == _lib.PRECISION_BF16:
         ids, tab_s, tab_t = code_source

@@ -224,7 +224,7 @@ int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codener
   b.add(mk_dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp_s2, C, as2, C, 0));
   b.add(mk_wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C));
   b.add(mk_dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp_s1, C, as1, C, 0));
-  if (d.tc && g_x_dir) return CNRF_E_UNSUPPORTED;   // ray-direction gradients (pose optimisation) run in the fp32 mode
+  if (d.rows_dev && g_x_dir) return CNRF_E_UNSUPPORTED;   // shared-code rays carry no pose gradient
   if (!d.tc) b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
   if (g_x_dir) b.add(mk_dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0));
   if (d.tc) {
@@ -487,7 +487,7 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
                 in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, in.x_dir, in.ld_dir,
                 in.ids ? sc.runs.gid : nullptr};
-  RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, dt.bd, g_x_xyz,
+  RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, g_x_dir ? dt.bd : nullptr, g_x_xyz,
                         w.base + w.off, w.cap - w.off, st));
   RUN(per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, dt, tmp, gz_s, gz_t, g_x_dir, st));
   if (in.ids) {          // one row per run -> dense table gradients (what torch.nn.Embedding's backward produces)

@@ -58,7 +58,7 @@ __device__ __forceinline__ bool uwait(uint64_t* bar, uint32_t parity, BBars* b, 
 // S = -1: d v2p from g_rgb on CUDA cores; S = 0..3: the tensor-core stages.  Output image index = S + 1.
 // The 32-column blocks are processed two per loop iteration with the next block's TMEM load (and mask word) in flight;
 // the loop is deliberately not unrolled further (instruction-cache footprint of five specialised stages).
-template <int S>
+template <int S, bool XG>
 __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint32_t parity) {
   constexpr int MK = S == -1 ? 3 : S == 0 ? 2 : S == 2 ? 1 : S == 3 ? 0 : -1;   // v2, v1, -, h2, h1
   const uint32_t* mp = reinterpret_cast<const uint32_t*>(c.masks + (size_t)(MK >= 0 ? MK : 0) * MASK_BYTES + c.r * 32);
@@ -122,11 +122,33 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
   named_bar_sync(c.bar_id, 128);
   if (c.elected) {
     if (c.tile_ok) { bulk_s2g(c.dy + (size_t)(S + 1) * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
-    if (S < 3) mbar_arrive(&c.bars->a_ready[t]);
+    if (S < 3 || XG) mbar_arrive(&c.bars->a_ready[t]);     // XG: the input-gradient stage reads d h1p as its A operand
   }
   return true;
 }
 
+// Input-gradient stage (pose optimisation, eval.py:129-168): d gamma(x)[m][0..dx) = d h1p[m] W1, 64 accumulator columns,
+// written as fp32 rows of g_x [M, dx] for the positional-encoding backward.
+__device__ __forceinline__ bool bwd_stage_x(const BwdArgs& a, BEpi& c, int t, uint32_t parity, int64_t m) {
+  if (!bwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
+  tc_fence_after();
+  uint32_t va[32], vb[32];
+  tmem_ld32(c.tacc, va);
+  tmem_ld32(c.tacc + 32, vb);
+  tmem_ld_wait();
+  if (m < a.M) {
+    float* o = a.g_x + m * a.dx;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (j < a.dx) o[j] = __uint_as_float(va[j]);
+#pragma unroll
+    for (int j = 0; j < 32; ++j) if (32 + j < a.dx) o[32 + j] = __uint_as_float(vb[j]);
+  }
+  tc_fence_before();
+  named_bar_sync(c.bar_id, 128);          // every row of the tile has drained its accumulator columns
+  return true;
+}
+
+template <bool XG>
 __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* tiles = smem;
@@ -159,9 +181,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
       uint32_t slot = 0, epar = 1;
       bool ok = true;
       for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
-        for (int stage = 0; stage < 4 && ok; ++stage) {
+        for (int stage = 0; stage < (XG ? 5 : 4) && ok; ++stage) {
           for (int t = 0; t < 2 && ok; ++t) {
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < (stage == 4 ? 2 : 8); ++i) {      // stage 4: W1^T, one 32 KB image = two ring slots
               if (!bwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
               mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
               bulk_g2s(ring + slot * HALF, a.pk.bwd + (size_t)(stage * 8 + i) * HALF, HALF, &bars->w_full[slot]);
@@ -210,6 +232,35 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
             __syncwarp();
           }
         }
+        if (XG) {                          // d gamma(x) = d h1p W1: N = 64, the four K-chunks sit two per ring image
+          const uint32_t idesc_x = idesc_bf16(128, 64, 0, 0);
+#pragma unroll 1
+          for (int t = 0; t < 2 && ok; ++t) {
+            if (!uwait(&bars->a_ready[t], na & 1, bars, a.err)) { ok = false; break; }
+            const uint32_t d0 = tmem_u + t * 256;
+#pragma unroll
+            for (int hi = 0; hi < 2; ++hi) {
+              if (!ok) continue;
+              if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; continue; }
+              tc_fence_after();
+              if (elect_one()) {
+#pragma unroll
+                for (int q = 0; q < 2; ++q) {
+                  const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + (2 * hi + q) * SLAB) >> 4);
+                  const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF + q * 8192) >> 4);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) umma_bf16(d0, ad + 2 * k, bd + 2 * k, idesc_x, (hi | q | k) != 0);
+                }
+                umma_commit(&bars->w_empty[slot]);
+              }
+              __syncwarp();
+              if (++slot == BRING) { slot = 0; wpar ^= 1u; }
+            }
+            if (ok && elect_one()) umma_commit(&bars->acc_full[t]);
+            __syncwarp();
+          }
+          ++na;
+        }
       }
     }
   } else {
@@ -232,11 +283,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
       c.masks = a.saved + (size_t)(c.tile_ok ? tile_idx : 0) * SAVED_PER_TILE + SAVED_MASKS;
       c.dy = a.dy + (size_t)(c.tile_ok ? tile_idx : 0) * DY_PER_TILE;
       c.g = m < a.M ? __ldg(reinterpret_cast<const float4*>(a.g_raw) + m) : make_float4(0.f, 0.f, 0.f, 0.f);
-      bool ok = bwd_stage<-1>(a, c, t, 0);
-      if (ok) { ok = bwd_stage<0>(a, c, t, na & 1); ++na; }
-      if (ok) { ok = bwd_stage<1>(a, c, t, na & 1); ++na; }
-      if (ok) { ok = bwd_stage<2>(a, c, t, na & 1); ++na; }
-      if (ok) { ok = bwd_stage<3>(a, c, t, na & 1); ++na; }
+      bool ok = bwd_stage<-1, XG>(a, c, t, 0);
+      if (ok) { ok = bwd_stage<0, XG>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = bwd_stage<1, XG>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = bwd_stage<2, XG>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = bwd_stage<3, XG>(a, c, t, na & 1); ++na; }
+      if (XG && ok) { ok = bwd_stage_x(a, c, t, na & 1, m); ++na; }
       if (!ok) break;
     }
     if (c.elected) bulk_wait0();
@@ -250,12 +302,15 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
 int cnrf_tc_launch_bwd(const BwdArgs& b, int grid, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    cudaError_t e = cudaFuncSetAttribute(mlp_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(mlp_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
+  if (b.g_x && (b.dx < 1 || b.dx > 64)) return CNRF_E_UNSUPPORTED;
   const bool timed = cnrf_ktimer_begin(CNRF_KT_BWD, b.M, st);
-  mlp_bwd_tc_kernel<<<grid, NTHREADS, BWD_SMEM, st>>>(b);
+  if (b.g_x) mlp_bwd_tc_kernel<true><<<grid, NTHREADS, BWD_SMEM, st>>>(b);
+  else mlp_bwd_tc_kernel<false><<<grid, NTHREADS, BWD_SMEM, st>>>(b);
   CNRF_LAUNCH_CHECK();
   if (timed) cnrf_ktimer_end(CNRF_KT_BWD, st);
   return CNRF_OK;

@@ -39,7 +39,10 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, int dx, int dd, Pack
       int b = ch - FWD_CHUNKS;
       base = pk.bwd + (size_t)b * CHUNK;
       int l = b >> 2, n = (b & 3) * 64 + c;   // image[k = r][n]: l: 0 Wd2^T, 1 Wdf^T, 2 Woh[1:]^T, 3 W2h^T
-      if (l == 0) v = p.weight[CNRF_L_DIR2][n * 256 + r];
+      if (b == BWD_X_CHUNK) {                 // W1^T: rows 64 q + n (input feature n), column c = hidden unit 64 q + c
+        const int q = r >> 6, nin = r & 63;
+        v = nin < dx ? p.weight[CNRF_L_XYZ1][(q * 64 + c) * dx + nin] : 0.f;
+      } else if (l == 0) v = p.weight[CNRF_L_DIR2][n * 256 + r];
       else if (l == 1) v = p.weight[CNRF_L_DIR1][n * (256 + dd) + r];
       else if (l == 2) v = p.weight[CNRF_L_FC_OUT][(n + 1) * 512 + r];
       else v = p.weight[CNRF_L_XYZ2][n * 512 + r];
@@ -530,6 +533,28 @@ done:
   if (warp == 1) tmem_dealloc(tmem, 512);
 }
 
+// out[g*ld + col] = sum_{q<Q} img[g*g_stride + q*q_stride][col]: per-ray sums of a gradient image whose rows of one ray are
+// NOT consecutive (the reference's view-direction pairing, row m <-> ray m mod N) -- only the pose-optimisation backward
+// needs it (gradient of the per-ray view-direction encoding); the consecutive-row sums live in the dW reducers.
+__global__ void img_group_sum_kernel(const uint8_t* base, size_t per_tile, size_t off, int64_t G, int64_t g_stride,
+                                     int64_t Q, int64_t q_stride, float* out, int64_t ld) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= G * 128) return;
+  const int64_t g = i >> 7;
+  const int w = (int)(i & 127);                       // column pair 2w, 2w+1
+  float sx = 0.f, sy = 0.f;
+  for (int64_t q = 0; q < Q; ++q) {
+    const int64_t m = g * g_stride + q * q_stride;
+    const int r = (int)(m & 127);
+    const uint8_t* p = base + (size_t)(m >> 7) * per_tile + off + (w >> 5) * SLAB + r * 128 + ((((w >> 2) & 7) ^ (r & 7)) << 4) +
+                       ((w & 3) << 2);
+    const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(p));
+    sx += __uint_as_float(v << 16); sy += __uint_as_float(v & 0xFFFF0000u);
+  }
+  out[g * ld + 2 * w] = sx;
+  out[g * ld + 2 * w + 1] = sy;
+}
+
 size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
   (void)N;
   size_t b = PACKED_BYTES + 4096 + (size_t)pairs_of(M) * SLAB;
@@ -540,7 +565,9 @@ size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
 int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* saved, size_t saved_bytes,
                       const cnrf_codenerf_grads* g, float* d_b2, float* d_bo, float* d_br, float* d_bd, float* g_x_xyz,
                       void* ws, size_t ws_bytes, cudaStream_t st) {
-  if (g_x_xyz) return CNRF_E_UNSUPPORTED;     // input gradients (pose optimisation) run in CNRF_PRECISION_FP32 for now
+  // d_bd != NULL: also the per-ray sums of d v1p (the caller turns them into the gradient of the view-direction encoding);
+  // g_x_xyz != NULL: the backward chain runs its fifth stage, d gamma(x) = d h1p W1   (pose optimisation, eval.py:129-168)
+  if ((d_bd || g_x_xyz) && a.gid) return CNRF_E_UNSUPPORTED;      // rays with shared codes carry no pose gradient
   const int64_t tiles = (a.M + TILE - 1) / TILE;
   uint8_t* w = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(ws)));
   if (w + PACKED_BYTES + 1024 + (size_t)tiles * DY_PER_TILE > reinterpret_cast<uint8_t*>(ws) + ws_bytes) return CNRF_E_WORKSPACE;
@@ -560,7 +587,7 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
     attr_set = true;
   }
   BwdArgs b;
-  b.M = a.M; b.g_raw = g_raw; b.saved = sv; b.dy = dy; b.pk = pk; b.err = tc_error_ptr();
+  b.M = a.M; b.g_raw = g_raw; b.saved = sv; b.dy = dy; b.g_x = g_x_xyz; b.dx = a.dx; b.pk = pk; b.err = tc_error_ptr();
   const int64_t pairs = (tiles + 1) / 2;
   if ((rc = cnrf_tc_launch_bwd(b, (int)(pairs < sm_count() ? pairs : sm_count()), st))) return rc;
 
@@ -609,6 +636,15 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
     CNRF_LAUNCH_CHECK();
     if (timed) cnrf_ktimer_end(CNRF_KT_DW, st);
   }
-  (void)d_bd;   // layer_dir1's view-direction half and bias get their gradients from the extension job above
+  // layer_dir1's view-direction half and bias get their gradients from the extension job above; the per-ray sums of
+  // d v1p are only needed for the gradient of the view directions themselves
+  if (d_bd) {
+    const unsigned gs_grid = (unsigned)((a.N * 128 + 255) / 256);
+    if (a.pairing == CNRF_PAIRING_REFERENCE)
+      img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 1 * (size_t)TILE_BYTES, a.N, 1, a.S, a.N, d_bd, 256);
+    else
+      img_group_sum_kernel<<<gs_grid, 256, 0, st>>>(dy, DY_PER_TILE, 1 * (size_t)TILE_BYTES, a.N, a.S, a.S, 1, d_bd, 256);
+    CNRF_LAUNCH_CHECK();
+  }
   return CNRF_OK;
 }

@@ -15,14 +15,15 @@ constexpr int RING = 3;
 constexpr int NTHREADS = 320;
 constexpr int FWD_CHUNKS = 18;            // 1 (layer_xyz1, K=64) + 4 x 4 + 1 (view-direction extension of layer_dir1)
 constexpr int EXT_CHUNK = 17;             // [Wdv | b_dir1 | 0]: K = dim_dir + 1 <= 32 columns of a [256 x 64] image
-constexpr int BWD_CHUNKS = 16;            // 4 x 4 transposed
+constexpr int BWD_CHUNKS = 17;            // 4 x 4 transposed + W1^T (four [64 in x 64 hidden] K-chunks stacked in one image)
+constexpr int BWD_X_CHUNK = 16;           // ... its index: B operand of the input-gradient stage d gamma(x) = d h1p W1
 constexpr int CONST_BYTES = 4 * 256 * 2;    // bf16 [w_sigma | w_rgb(3)] staged in shared memory
 constexpr int SMEM_BYTES = 2 * TILE_BYTES + RING * CHUNK + CONST_BYTES + 256 /*barriers*/;
 
 // Packed weights (bf16 images + fp32 vectors), rebuilt from the fp32 parameters at every call (they change each step).
 struct Packed {
   uint8_t* fwd;      // FWD_CHUNKS x 32 KB: [W1|b1], W2h, Woh[1:], Wdf, Wd2   (rows = out feature, cols = in feature)
-  uint8_t* bwd;      // BWD_CHUNKS x 32 KB: Wd2^T, Wdf^T, Woh[1:]^T, W2h^T     (rows = in feature,  cols = out feature)
+  uint8_t* bwd;      // BWD_CHUNKS x 32 KB: Wd2^T, Wdf^T, Woh[1:]^T, W2h^T, W1^T (rows = in feature,  cols = out feature)
   float* w_sigma;    // [256]  fc_out row 0, hidden half
   float* w_rgb;      // [3][256] fc_rgb, hidden half
   float* b_dir2;     // [256]
@@ -172,6 +173,8 @@ struct BwdArgs {
   const float* g_raw;          // [M,4]
   const uint8_t* saved;        // forward images + sign-bit masks
   uint8_t* dy;                 // gradient images out
+  float* g_x;                  // [M, dx] gradient of the embedded points (pose optimisation, eval.py:129-168) or NULL
+  int dx;
   Packed pk;
   int* err;
 };
