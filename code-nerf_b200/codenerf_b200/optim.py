@@ -42,7 +42,6 @@ class FusedAdamW(torch.optim.Optimizer):
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        lib = _lib.load()
         by_betas = {}
         for group in self.param_groups:
             key = (float(group["betas"][0]), float(group["betas"][1]), float(group["eps"]))
@@ -57,6 +56,9 @@ class FusedAdamW(torch.optim.Optimizer):
                 st["step"] += 1
                 rows.append((p, g if g.is_contiguous() else g.contiguous(), st, float(group["lr"]),
                              float(group["weight_decay"])))
+        if not any(by_betas.values()):
+            return loss
+        lib = _lib.load()
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         for (b1, b2, eps), rows in by_betas.items():
             if not rows:

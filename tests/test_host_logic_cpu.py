@@ -113,3 +113,42 @@ def test_parallel_image_render_two_ranks_gloo(tmp_path, H, W):
     rgb = torch.load(out)
     want = torch.arange(H * W * 3, dtype=torch.float32).reshape(-1, 3) * 2.0 + 1.0
     assert torch.equal(rgb, want)          # ordering and trimming of the padded all_gather (nerf/__init__.py:212-226)
+
+
+def test_embedding_output_carries_its_source_and_equals_nn_embedding():
+    """ShapeTextureEmbedding.forward returns what the reference returns (two nn.Embedding lookups, models/model.py:100-103)
+    and tags both tensors with (ids, shape table, texture table) so the fused field can share the code layers between
+    rays of one object; slicing or any other op drops the tag (-> per-ray path)."""
+    import view_synthesis.models as models
+    torch.manual_seed(0)
+    emb = models.ShapeTextureEmbedding(7, 16, 16)
+    ids = torch.tensor([3, 3, 3, 5, 5, 0])
+    z_s, z_t = emb(ids)
+    assert torch.equal(z_s, emb.shape_embedding.weight[ids]) and torch.equal(z_t, emb.texture_embedding.weight[ids])
+    src = z_s._cnrf_code_source
+    assert src is z_t._cnrf_code_source and src[0] is ids
+    assert src[1] is emb.shape_embedding.weight and src[2] is emb.texture_embedding.weight
+    assert not hasattr(z_s[:4], "_cnrf_code_source")
+    (z_s.sum() + z_t.sum()).backward()                       # the ordinary autograd path still works
+    assert emb.shape_embedding.weight.grad[3].eq(3).all() and emb.shape_embedding.weight.grad[1].eq(0).all()
+
+
+def test_fused_adamw_constructor_and_cpu_refusal():
+    """FusedAdamW takes torch.optim.AdamW's arguments, keeps its param-group defaults, refuses the options it does not
+    implement and refuses CPU parameters loudly (no fallback)."""
+    from codenerf_b200.optim import FusedAdamW
+    from codenerf_b200 import _lib
+    p = torch.zeros(4, requires_grad=True)
+    opt = FusedAdamW([{"params": [p]}], lr=1e-4, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2)
+    ref = torch.optim.AdamW([torch.zeros(4, requires_grad=True)], lr=1e-4)
+    for k in ("lr", "betas", "eps", "weight_decay"):
+        assert opt.param_groups[0][k] == ref.param_groups[0][k], k
+    with pytest.raises(ValueError):
+        FusedAdamW([p], amsgrad=True)
+    with pytest.raises(ValueError):
+        FusedAdamW([p], lr=-1.0)
+    p.grad = torch.ones(4)
+    with pytest.raises(_lib.CnrfError):
+        opt.step()
+    opt.zero_grad()
+    opt.step()                                               # nothing has a gradient: a no-op that needs no GPU
