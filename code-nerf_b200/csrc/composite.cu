@@ -1,192 +1,291 @@
 // Alpha compositing forward and backward: volume_render (view_synthesis/nerf/volumetric_render.py:36-66).
-// One warp per ray, one pass over HBM: lane l of chunk c owns sample 32c+l, (r,g,b,sigma) arrives as one float4 per
-// lane (512 B per warp request), transmittance is an exclusive warp scan of sigma*delta with a carry between chunks.
-// The backward keeps every per-sample intermediate of the ray in registers (NCH chunks, compile-time), so raw/z are
-// read exactly once and g_raw written exactly once; the suffix sum sum_{j>i} gw_j w_j runs as a reverse warp scan.
+// One warp per ray (R rays per warp when a ray is a single 32-sample chunk), one pass over HBM: lane l of chunk c owns
+// sample 32c+l, (r,g,b,sigma) arrives as one float4 per lane (512 B per warp request).  EVERY load of the warp's rays is
+// issued before the first dependent instruction (the kernel is a stream: bytes in flight per SM are what set its
+// speed), the next-sample depth comes from a shuffle instead of a second load, transmittance is an exclusive warp scan
+// of sigma*delta with a carry between chunks.  The backward keeps the per-sample intermediates of the ray in registers
+// (NCH chunks, compile-time), so raw/z are read exactly once and g_raw written exactly once; the suffix sum
+// sum_{j>i} gw_j w_j runs as a reverse warp scan.
+//
+// Transcendentals: the first version used expf / log1pf / IEEE division everywhere and was ISSUE-bound (~250 executed
+// instructions per 32 samples, 0.3-0.5 of the HBM peak).  exp(-x) of sigmoid, alpha and transmittance now go through
+// ex2.approx (__expf: |error| <= 2 ulp + 1.2e-7*|x| relative, results <= 1 so <= 1e-7 absolute), reciprocals through
+// rcp.approx (1 ulp), softplus through lg2.approx above e^x = 1/32 and a 4-term log1p series below it (relative error
+// < 2e-7; exp(raw-1) itself stays the accurate expf because the LAST sample multiplies sigma by 1e10, :43).  Parity with
+// the reference stays within 1e-6 absolute (tests/test_gpu_parity.py::test_volume_render_*: 2e-6 abs on every output).
 #include "common.cuh"
 
-constexpr int CW = 4;  // warps (rays) per block
+constexpr int CWARPS = 8;  // warps per block
 
-struct Sample {
-  float sr, sg, sb;   // sigmoid(raw rgb)
-  float sigma, delta, dist, z;
-  float T, E;         // transmittance before the sample, exp(-sigma*delta)
-  float dsig;         // d softplus(x-1) / dx
-  bool valid;
-};
-
-__device__ __forceinline__ Sample load_sample(const float4* __restrict__ raw4, const float* __restrict__ z, int i, int S,
-                                              float norm) {
-  Sample s;
-  s.valid = i < S;
-  float4 r = s.valid ? raw4[i] : make_float4(0.f, 0.f, 0.f, 0.f);
-  s.z = s.valid ? z[i] : 0.f;
-  float zn = (i + 1 < S) ? z[i + 1] : 0.f;
-  s.dist = (i + 1 < S) ? __fsub_rn(zn, s.z) : 1e10f;        // last distance forced to 1e10   volumetric_render.py:41-43
-  s.delta = __fmul_rn(s.dist, norm);                         // dists * ||rd||                 :45
-  float x = __fsub_rn(r.w, 1.0f);
-  s.sigma = s.valid ? softplus_t20(x) : 0.f;                 // shifted_softplus               :32-33,48
-  s.dsig = x > 20.0f ? 1.0f : sigmoidf_(x);
-  s.sr = sigmoidf_(r.x); s.sg = sigmoidf_(r.y); s.sb = sigmoidf_(r.z);
-  s.E = expf(-__fmul_rn(s.sigma, s.delta));
-  s.T = 1.f;
-  return s;
-}
+__device__ __forceinline__ float rcp_fast(float x) { return __fdividef(1.0f, x); }
+__device__ __forceinline__ float sigmoid_fast(float x) { return rcp_fast(1.0f + __expf(-x)); }
 __device__ __forceinline__ float widen(float sg) { return __fsub_rn(__fmul_rn(sg, 1.002f), 0.001f); }  // :28-29
 
-// Forward over one ray.  Leaves T in every Sample, returns the five reductions.
-template <int NCH>
-__device__ __forceinline__ void ray_forward(const float4* __restrict__ raw4, const float* __restrict__ z, int S,
-                                            float norm, int lane, Sample (&sm)[NCH], float& R, float& G, float& B,
-                                            float& D, float& A) {
-  float carry = 0.f;
-  R = G = B = D = A = 0.f;
-#pragma unroll
-  for (int c = 0; c < NCH; ++c) {
-    Sample s = load_sample(raw4, z, c * 32 + lane, S, norm);
-    float sd = s.valid ? __fmul_rn(s.sigma, s.delta) : 0.f;
-    float inc = warp_scan_inclusive(sd, lane);
-    float prev = __shfl_up_sync(FULL_MASK, inc, 1);
-    float excl = carry + (lane > 0 ? prev : 0.f);            // exclusive cumsum             :52-55
-    carry += __shfl_sync(FULL_MASK, inc, 31);
-    s.T = expf(-excl);
-    float w = s.valid ? __fmul_rn(__fsub_rn(1.0f, s.E), s.T) : 0.f;  // alpha * transmittance :56-57
-    R += w * widen(s.sr); G += w * widen(s.sg); B += w * widen(s.sb);
-    D += w * s.z; A += w;
-    sm[c] = s;
-  }
-  R = warp_sum(R); G = warp_sum(G); B = warp_sum(B); D = warp_sum(D); A = warp_sum(A);
+// sigma = softplus(x) with torch's threshold 20 (:32-33,48); dsig = d sigma / dx
+template <bool WANT_D>
+__device__ __forceinline__ void softplus_fast(float x, float& sigma, float& dsig) {
+  const float e = expf(x);
+  const float u = 1.0f + e;
+  const float series = e * fmaf(e, fmaf(e, fmaf(e, -0.25f, 0.33333334f), -0.5f), 1.0f);   // log1p(e), e < 1/32
+  const float sp = e < 0.03125f ? series : __logf(u);
+  sigma = x > 20.0f ? x : sp;
+  if (WANT_D) dsig = x > 20.0f ? 1.0f : __fdividef(e, u);
 }
 
+// The registers of one ray: NCH chunks of 32 samples.
 template <int NCH>
-__global__ void __launch_bounds__(CW * 32)
+struct RayRegs {
+  float4 raw[NCH];
+  float z[NCH];
+};
+
+template <int NCH>
+__device__ __forceinline__ void ray_load(RayRegs<NCH>& q, const float* __restrict__ raw, const float* __restrict__ z,
+                                         int64_t n, int S, int lane, bool live) {
+  const float4* raw4 = reinterpret_cast<const float4*>(raw) + n * (int64_t)S;
+  const float* zr = z + n * (int64_t)S;
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int i = c * 32 + lane;
+    const bool ok = live && i < S;
+    q.raw[c] = ok ? __ldg(raw4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    q.z[c] = ok ? __ldg(zr + i) : 0.f;
+  }
+}
+
+// dists (:41-43): z[i+1] - z[i], the last one forced to 1e10.  z[i+1] of lane 31 is lane 0 of the next chunk.
+template <int NCH>
+__device__ __forceinline__ float next_dist(const RayRegs<NCH>& q, int c, int S, int lane) {
+  float zn = __shfl_down_sync(FULL_MASK, q.z[c], 1);
+  if (c + 1 < NCH) {
+    const float first = __shfl_sync(FULL_MASK, q.z[c + 1], 0);
+    zn = lane == 31 ? first : zn;
+  }
+  const int i = c * 32 + lane;
+  return (i + 1 < S) ? __fsub_rn(zn, q.z[c]) : 1e10f;
+}
+
+struct Sums { float R, G, B, D, A; };
+
+// ---------------------------------------------------------------------------------------------------------------
+template <int NCH, int R>
+__global__ void __launch_bounds__(CWARPS * 32)
 composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rd,
                      int64_t N, int S, float* __restrict__ rgb, float* __restrict__ disp, float* __restrict__ acc,
                      float* __restrict__ weights, float* __restrict__ depth) {
-  int lane = threadIdx.x & 31;
-  int64_t n = (int64_t)blockIdx.x * CW + (threadIdx.x >> 5);
-  if (n >= N) return;
-  float dx = rd[n * 3], dy = rd[n * 3 + 1], dz = rd[n * 3 + 2];
-  float norm = sqrtf(dx * dx + dy * dy + dz * dz);
-  const float4* raw4 = reinterpret_cast<const float4*>(raw) + n * (int64_t)S;
-  const float* zr = z + n * (int64_t)S;
-  Sample sm[NCH];
-  float R, G, B, D, A;
-  ray_forward<NCH>(raw4, zr, S, norm, lane, sm, R, G, B, D, A);
-  if (weights) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n0 = ((int64_t)blockIdx.x * CWARPS + (threadIdx.x >> 5)) * R;
+  if (n0 >= N) return;
+  RayRegs<NCH> q[R];
+  float nrm[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r) ray_load<NCH>(q[r], raw, z, n0 + r, S, lane, n0 + r < N);
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int64_t n = min(n0 + r, N - 1);
+    const float dx = __ldg(rd + n * 3), dy = __ldg(rd + n * 3 + 1), dz = __ldg(rd + n * 3 + 2);
+    nrm[r] = sqrtf(dx * dx + dy * dy + dz * dz);
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int64_t n = n0 + r;
+    if (n >= N) break;
+    float carry = 0.f;
+    Sums s = {0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
-      int i = c * 32 + lane;
-      if (i < S) weights[n * (int64_t)S + i] = __fmul_rn(__fsub_rn(1.0f, sm[c].E), sm[c].T);
+      const int i = c * 32 + lane;
+      const bool valid = i < S;
+      const float4 rw = q[r].raw[c];
+      const float delta = __fmul_rn(next_dist<NCH>(q[r], c, S, lane), nrm[r]);      // dists * ||rd||      :45
+      float sigma, unused;
+      softplus_fast<false>(__fsub_rn(rw.w, 1.0f), sigma, unused);
+      const float sd = valid ? __fmul_rn(sigma, delta) : 0.f;
+      const float E = __expf(-sd);
+      const float inc = warp_scan_inclusive(sd, lane);
+      const float prev = __shfl_up_sync(FULL_MASK, inc, 1);
+      const float excl = carry + (lane > 0 ? prev : 0.f);                            // exclusive cumsum    :52-55
+      carry += __shfl_sync(FULL_MASK, inc, 31);
+      const float T = __expf(-excl);
+      const float w = valid ? __fmul_rn(__fsub_rn(1.0f, E), T) : 0.f;                // alpha * T           :56-57
+      s.R = fmaf(w, widen(sigmoid_fast(rw.x)), s.R);
+      s.G = fmaf(w, widen(sigmoid_fast(rw.y)), s.G);
+      s.B = fmaf(w, widen(sigmoid_fast(rw.z)), s.B);
+      s.D = fmaf(w, q[r].z[c], s.D);
+      s.A += w;
+      if (weights && valid) weights[n * (int64_t)S + i] = w;
     }
-  }
-  if (lane == 0) {
-    if (rgb) { rgb[n * 3] = R; rgb[n * 3 + 1] = G; rgb[n * 3 + 2] = B; }
-    if (depth) depth[n] = D;
-    if (acc) acc[n] = A;
-    if (disp) disp[n] = __fdiv_rn(1.0f, fmaxf(1e-10f, __fdiv_rn(D, A)));   // :64
+    s.R = warp_sum(s.R); s.G = warp_sum(s.G); s.B = warp_sum(s.B); s.D = warp_sum(s.D); s.A = warp_sum(s.A);
+    if (lane == 0) {
+      if (rgb) { rgb[n * 3] = s.R; rgb[n * 3 + 1] = s.G; rgb[n * 3 + 2] = s.B; }
+      if (depth) depth[n] = s.D;
+      if (acc) acc[n] = s.A;
+      if (disp) disp[n] = __fdiv_rn(1.0f, fmaxf(1e-10f, __fdiv_rn(s.D, s.A)));      // :64
+    }
   }
 }
 
-template <int NCH>
-__global__ void __launch_bounds__(CW * 32)
+// ---------------------------------------------------------------------------------------------------------------
+// GEO: the caller wants g_z and / or g_rd (camera-pose optimisation); training needs neither.
+template <int NCH, int R, bool GEO>
+__global__ void __launch_bounds__(CWARPS * 32)
 composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rd,
                      int64_t N, int S, const float* __restrict__ g_rgb, const float* __restrict__ g_disp,
                      const float* __restrict__ g_acc, const float* __restrict__ g_weights,
                      const float* __restrict__ g_depth, float* __restrict__ g_raw, float* __restrict__ g_z,
                      float* __restrict__ g_rd) {
-  int lane = threadIdx.x & 31;
-  int64_t n = (int64_t)blockIdx.x * CW + (threadIdx.x >> 5);
-  if (n >= N) return;
-  float dx = rd[n * 3], dy = rd[n * 3 + 1], dz = rd[n * 3 + 2];
-  float norm = sqrtf(dx * dx + dy * dy + dz * dz);
-  const float4* raw4 = reinterpret_cast<const float4*>(raw) + n * (int64_t)S;
-  const float* zr = z + n * (int64_t)S;
-  Sample sm[NCH];
-  float R, G, B, D, A;
-  ray_forward<NCH>(raw4, zr, S, norm, lane, sm, R, G, B, D, A);
-
-  float gR = g_rgb ? g_rgb[n * 3] : 0.f, gG = g_rgb ? g_rgb[n * 3 + 1] : 0.f, gB = g_rgb ? g_rgb[n * 3 + 2] : 0.f;
-  float gD = g_depth ? g_depth[n] : 0.f, gA = g_acc ? g_acc[n] : 0.f;
-  if (g_disp) {                                               // disp = 1 / max(1e-10, D/A)
-    float q = D / A;
-    if (q > 1e-10f) {
-      float gq = -g_disp[n] / (q * q);
-      gD += gq / A;
-      gA -= gq * D / (A * A);
-    }
-  }
-  // reverse pass: suffix_i = sum_{j>i} gw_j w_j
-  float carry = 0.f, g_norm = 0.f;
-  float ddist[NCH];       // d L / d dists_i, kept for the g_z sweep below
+  const int lane = threadIdx.x & 31;
+  const int64_t n0 = ((int64_t)blockIdx.x * CWARPS + (threadIdx.x >> 5)) * R;
+  if (n0 >= N) return;
+  RayRegs<NCH> q[R];
+  float gwt[R][NCH];
 #pragma unroll
-  for (int c = NCH - 1; c >= 0; --c) {
-    const Sample& s = sm[c];
-    int i = c * 32 + lane;
-    float w = s.valid ? (1.0f - s.E) * s.T : 0.f;
-    float cr = widen(s.sr), cg = widen(s.sg), cb = widen(s.sb);
-    float gw = gR * cr + gG * cg + gB * cb + gD * s.z + gA + ((g_weights && s.valid) ? g_weights[n * (int64_t)S + i] : 0.f);
-    float v = s.valid ? gw * w : 0.f;
-    // inclusive suffix scan within the warp
-    float sfx = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      float t = __shfl_down_sync(FULL_MASK, sfx, o);
-      if (lane + o < 32) sfx += t;
-    }
-    float excl_sfx = sfx - v + carry;
-    carry += __shfl_sync(FULL_MASK, sfx, 0);
-    float ds = gw * s.T * s.E - excl_sfx;                     // dL / d(sigma*delta)
-    float dsigma = ds * s.delta, ddelta = ds * s.sigma;
-    ddist[c] = (s.valid && i + 1 < S) ? ddelta * norm : 0.f;
-    if (s.valid) {
-      g_norm += ddelta * s.dist;
-      float4 o4;
-      o4.x = gR * w * 1.002f * s.sr * (1.0f - s.sr);
-      o4.y = gG * w * 1.002f * s.sg * (1.0f - s.sg);
-      o4.z = gB * w * 1.002f * s.sb * (1.0f - s.sb);
-      o4.w = dsigma * s.dsig;
-      reinterpret_cast<float4*>(g_raw)[n * (int64_t)S + i] = o4;
-    }
-  }
-  if (g_z) {   // dists_i = z_{i+1} - z_i  ->  g_z[i] = gD*w_i - ddist_i + ddist_{i-1}
-    float prev_last = 0.f;
+  for (int r = 0; r < R; ++r) {
+    const int64_t n = n0 + r;
+    ray_load<NCH>(q[r], raw, z, n, S, lane, n < N);
 #pragma unroll
     for (int c = 0; c < NCH; ++c) {
-      int i = c * 32 + lane;
-      float up = __shfl_up_sync(FULL_MASK, ddist[c], 1);
-      float below = lane > 0 ? up : prev_last;
-      prev_last = __shfl_sync(FULL_MASK, ddist[c], 31);
-      if (i < S) g_z[n * (int64_t)S + i] = gD * (1.0f - sm[c].E) * sm[c].T - ddist[c] + below;
+      const int i = c * 32 + lane;
+      gwt[r][c] = (g_weights && n < N && i < S) ? __ldg(g_weights + n * (int64_t)S + i) : 0.f;
     }
   }
-  if (g_rd) {
-    g_norm = warp_sum(g_norm);
-    if (lane == 0) {
-      float k = norm > 0.f ? g_norm / norm : 0.f;
-      g_rd[n * 3] = k * dx; g_rd[n * 3 + 1] = k * dy; g_rd[n * 3 + 2] = k * dz;
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int64_t n = n0 + r;
+    if (n >= N) break;
+    const float dx = __ldg(rd + n * 3), dy = __ldg(rd + n * 3 + 1), dz = __ldg(rd + n * 3 + 2);
+    const float norm = sqrtf(dx * dx + dy * dy + dz * dz);
+    float gR = g_rgb ? __ldg(g_rgb + n * 3) : 0.f, gG = g_rgb ? __ldg(g_rgb + n * 3 + 1) : 0.f,
+          gB = g_rgb ? __ldg(g_rgb + n * 3 + 2) : 0.f;
+    float gD = g_depth ? __ldg(g_depth + n) : 0.f, gA = g_acc ? __ldg(g_acc + n) : 0.f;
+
+    // ---- forward sweep: per-sample state stays in registers
+    float sr[NCH], sg[NCH], sb[NCH], sigma[NCH], dsig[NCH], delta[NCH], T[NCH], E[NCH];
+    float carry = 0.f, D = 0.f, A = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int i = c * 32 + lane;
+      const bool valid = i < S;
+      const float4 rw = q[r].raw[c];
+      delta[c] = __fmul_rn(next_dist<NCH>(q[r], c, S, lane), norm);
+      softplus_fast<true>(__fsub_rn(rw.w, 1.0f), sigma[c], dsig[c]);
+      const float sd = valid ? __fmul_rn(sigma[c], delta[c]) : 0.f;
+      E[c] = __expf(-sd);
+      const float inc = warp_scan_inclusive(sd, lane);
+      const float prev = __shfl_up_sync(FULL_MASK, inc, 1);
+      const float excl = carry + (lane > 0 ? prev : 0.f);
+      carry += __shfl_sync(FULL_MASK, inc, 31);
+      T[c] = __expf(-excl);
+      sr[c] = sigmoid_fast(rw.x); sg[c] = sigmoid_fast(rw.y); sb[c] = sigmoid_fast(rw.z);
+      if (g_disp) {
+        const float w = valid ? (1.0f - E[c]) * T[c] : 0.f;
+        D = fmaf(w, q[r].z[c], D); A += w;
+      }
+    }
+    if (g_disp) {                                               // disp = 1 / max(1e-10, D/A)
+      D = warp_sum(D); A = warp_sum(A);
+      const float qq = D / A;
+      if (qq > 1e-10f) {
+        const float gq = -__ldg(g_disp + n) / (qq * qq);
+        gD += gq / A;
+        gA -= gq * D / (A * A);
+      }
+    }
+    // ---- reverse sweep: suffix_i = sum_{j>i} gw_j w_j
+    float rcarry = 0.f, g_norm = 0.f;
+    float ddist[GEO ? NCH : 1];       // d L / d dists_i, kept for the g_z sweep below
+#pragma unroll
+    for (int c = NCH - 1; c >= 0; --c) {
+      const int i = c * 32 + lane;
+      const bool valid = i < S;
+      const float w = valid ? (1.0f - E[c]) * T[c] : 0.f;
+      const float gw = gR * widen(sr[c]) + gG * widen(sg[c]) + gB * widen(sb[c]) + gD * q[r].z[c] + gA + gwt[r][c];
+      const float v = gw * w;
+      float sfx = v;                                            // inclusive suffix scan within the warp
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const float t = __shfl_down_sync(FULL_MASK, sfx, o);
+        if (lane + o < 32) sfx += t;
+      }
+      const float excl_sfx = sfx - v + rcarry;
+      rcarry += __shfl_sync(FULL_MASK, sfx, 0);
+      const float ds = gw * T[c] * E[c] - excl_sfx;             // dL / d(sigma*delta)
+      const float ddelta = ds * sigma[c];
+      if constexpr (GEO) {
+        ddist[c] = (valid && i + 1 < S) ? ddelta * norm : 0.f;
+        if (valid) g_norm += ddelta * (delta[c] / norm);        // * dists_i
+      }
+      if (valid) {
+        float4 o4;
+        o4.x = gR * w * 1.002f * sr[c] * (1.0f - sr[c]);
+        o4.y = gG * w * 1.002f * sg[c] * (1.0f - sg[c]);
+        o4.z = gB * w * 1.002f * sb[c] * (1.0f - sb[c]);
+        o4.w = ds * delta[c] * dsig[c];
+        reinterpret_cast<float4*>(g_raw)[n * (int64_t)S + i] = o4;
+      }
+    }
+    if constexpr (GEO) {
+      if (g_z) {   // dists_i = z_{i+1} - z_i  ->  g_z[i] = gD*w_i - ddist_i + ddist_{i-1}
+        float prev_last = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          const int i = c * 32 + lane;
+          const float up = __shfl_up_sync(FULL_MASK, ddist[c], 1);
+          const float below = lane > 0 ? up : prev_last;
+          prev_last = __shfl_sync(FULL_MASK, ddist[c], 31);
+          if (i < S) g_z[n * (int64_t)S + i] = gD * (1.0f - E[c]) * T[c] - ddist[c] + below;
+        }
+      }
+      if (g_rd) {
+        g_norm = warp_sum(g_norm);
+        if (lane == 0) {
+          const float k = norm > 0.f ? g_norm / norm : 0.f;
+          g_rd[n * 3] = k * dx; g_rd[n * 3 + 1] = k * dy; g_rd[n * 3 + 2] = k * dz;
+        }
+      }
     }
   }
 }
 
-#define DISPATCH_NCH(S, CALL)                                  \
-  switch (((S) + 31) / 32) {                                   \
-    case 1: { constexpr int NCH = 1; CALL; } break;            \
-    case 2: { constexpr int NCH = 2; CALL; } break;            \
-    case 3: { constexpr int NCH = 3; CALL; } break;            \
-    case 4: { constexpr int NCH = 4; CALL; } break;            \
-    case 5: { constexpr int NCH = 5; CALL; } break;            \
-    case 6: { constexpr int NCH = 6; CALL; } break;            \
-    case 7: case 8: { constexpr int NCH = 8; CALL; } break;    \
-    default: return CNRF_E_SHAPE;                              \
+template <int NCH, int R>
+static void launch_fwd(const float* raw, const float* z, const float* rd, int64_t N, int S, float* rgb, float* disp,
+                       float* acc, float* weights, float* depth, cudaStream_t st) {
+  composite_fwd_kernel<NCH, R><<<grid_for(N, CWARPS * R), CWARPS * 32, 0, st>>>(raw, z, rd, N, S, rgb, disp, acc, weights,
+                                                                                 depth);
+}
+template <int NCH, int R>
+static void launch_bwd(const float* raw, const float* z, const float* rd, int64_t N, int S, const float* g_rgb,
+                       const float* g_disp, const float* g_acc, const float* g_weights, const float* g_depth,
+                       float* g_raw, float* g_z, float* g_rd, cudaStream_t st) {
+  const unsigned grid = grid_for(N, CWARPS * R);
+  if (g_z || g_rd)
+    composite_bwd_kernel<NCH, R, true><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
+                                                                      g_depth, g_raw, g_z, g_rd);
+  else
+    composite_bwd_kernel<NCH, R, false><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
+                                                                       g_depth, g_raw, g_z, g_rd);
+}
+
+// chunks of 32 samples per ray -> (NCH, rays per warp forward, rays per warp backward)
+#define DISPATCH_NCH(S, FWD_OR_BWD, ...)                                  \
+  switch (((S) + 31) / 32) {                                              \
+    case 1: FWD_OR_BWD(1, 4, 2, __VA_ARGS__); break;                      \
+    case 2: FWD_OR_BWD(2, 2, 1, __VA_ARGS__); break;                      \
+    case 3: FWD_OR_BWD(3, 1, 1, __VA_ARGS__); break;                      \
+    case 4: FWD_OR_BWD(4, 1, 1, __VA_ARGS__); break;                      \
+    case 5: FWD_OR_BWD(5, 1, 1, __VA_ARGS__); break;                      \
+    case 6: FWD_OR_BWD(6, 1, 1, __VA_ARGS__); break;                      \
+    case 7: case 8: FWD_OR_BWD(8, 1, 1, __VA_ARGS__); break;              \
+    default: return CNRF_E_SHAPE;                                         \
   }
+#define CALL_FWD(NCH, RF, RB, ...) launch_fwd<NCH, RF>(__VA_ARGS__)
+#define CALL_BWD(NCH, RF, RB, ...) launch_bwd<NCH, RB>(__VA_ARGS__)
 
 extern "C" int cnrf_composite_fwd(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, float* rgb,
                                   float* disp, float* acc, float* weights, float* depth, cnrf_stream_t stream) {
   CNRF_REQUIRE(raw && z && rd, CNRF_E_NULL);
   CNRF_REQUIRE(N > 0 && S > 0 && S <= 256, CNRF_E_SHAPE);
-  DISPATCH_NCH(S, (composite_fwd_kernel<NCH><<<grid_for(N, CW), CW * 32, 0, as_stream(stream)>>>(
-                      raw, z, rd, N, S, rgb, disp, acc, weights, depth)));
+  DISPATCH_NCH(S, CALL_FWD, raw, z, rd, N, S, rgb, disp, acc, weights, depth, as_stream(stream));
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }
@@ -196,8 +295,8 @@ extern "C" int cnrf_composite_bwd(const float* raw, const float* z, const float*
                                   const float* g_depth, float* g_raw, float* g_z, float* g_rd, cnrf_stream_t stream) {
   CNRF_REQUIRE(raw && z && rd && g_raw, CNRF_E_NULL);
   CNRF_REQUIRE(N > 0 && S > 0 && S <= 256, CNRF_E_SHAPE);
-  DISPATCH_NCH(S, (composite_bwd_kernel<NCH><<<grid_for(N, CW), CW * 32, 0, as_stream(stream)>>>(
-                      raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights, g_depth, g_raw, g_z, g_rd)));
+  DISPATCH_NCH(S, CALL_BWD, raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights, g_depth, g_raw, g_z, g_rd,
+               as_stream(stream));
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }

@@ -10,24 +10,83 @@
 
 constexpr int WARPS_PER_BLOCK = 4;
 
-// pts row writer: the ray's S*3 floats are contiguous; element e -> (s = e/3, c = e%3).
+// pts row writer: the ray's S*3 floats are contiguous; element e -> (s = e/3, c = e%3).  One float4 covers floats
+// 4q..4q+3 = samples s = 4(q/3) + q%3 and s+1, components rotated by q%3: no per-float division.
 __device__ __forceinline__ void write_points(float* __restrict__ dst, const float* zsm, int S, float ro0, float ro1,
                                              float ro2, float rd0, float rd1, float rd2, int lane) {
   const int total = S * 3;
-  auto val = [&](int e) {
-    int s = e / 3, c = e - 3 * s;
-    float o = c == 0 ? ro0 : (c == 1 ? ro1 : ro2);
-    float d = c == 0 ? rd0 : (c == 1 ? rd1 : rd2);
-    return __fadd_rn(o, __fmul_rn(d, zsm[s]));           // ro + rd * z  (point_sampler.py:70,118)
-  };
   if ((total & 3) == 0 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
     float4* d4 = reinterpret_cast<float4*>(dst);
     for (int q = lane; q < total / 4; q += 32) {
-      int e = q * 4;
-      d4[q] = make_float4(val(e), val(e + 1), val(e + 2), val(e + 3));
+      const int m = q / 3, rem = q - 3 * m, s = 4 * m + rem;
+      const float za = zsm[s], zb = zsm[s + 1];
+      const float oA = rem == 0 ? ro0 : (rem == 1 ? ro1 : ro2), dA = rem == 0 ? rd0 : (rem == 1 ? rd1 : rd2);
+      const float oB = rem == 0 ? ro1 : (rem == 1 ? ro2 : ro0), dB = rem == 0 ? rd1 : (rem == 1 ? rd2 : rd0);
+      const float oC = rem == 0 ? ro2 : (rem == 1 ? ro0 : ro1), dC = rem == 0 ? rd2 : (rem == 1 ? rd0 : rd1);
+      const float z2 = rem == 2 ? zb : za, z3 = rem == 0 ? za : zb;
+      d4[q] = make_float4(__fadd_rn(oA, __fmul_rn(dA, za)), __fadd_rn(oB, __fmul_rn(dB, z2)),      // ro + rd * z
+                          __fadd_rn(oC, __fmul_rn(dC, z3)), __fadd_rn(oA, __fmul_rn(dA, zb)));      // (point_sampler.py:70,118)
     }
   } else {
-    for (int e = lane; e < total; e += 32) dst[e] = val(e);
+    for (int e = lane; e < total; e += 32) {
+      const int s = e / 3, c = e - 3 * s;
+      const float o = c == 0 ? ro0 : (c == 1 ? ro1 : ro2);
+      const float d = c == 0 ? rd0 : (c == 1 ? rd1 : rd2);
+      dst[e] = __fadd_rn(o, __fmul_rn(d, zsm[s]));
+    }
+  }
+}
+
+// Fast path of sample_uniform for S <= 32*NCH: R rays per warp, every load issued before the first store.
+constexpr int SU_WARPS = 8;
+template <int NCH, int R>
+__global__ void __launch_bounds__(SU_WARPS * 32)
+sample_uniform_fast_kernel(const float* __restrict__ ro, const float* __restrict__ rd, int64_t N, int S,
+                           const float* __restrict__ z_table, const float* __restrict__ lower,
+                           const float* __restrict__ upper, const float* __restrict__ t_rand, float* __restrict__ pts,
+                           float* __restrict__ z_out) {
+  __shared__ float smem[SU_WARPS * R * NCH * 32];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int64_t n0 = ((int64_t)blockIdx.x * SU_WARPS + wid) * R;
+  if (n0 >= N) return;
+  float t[R][NCH], o[R][3], d[R][3], lo[NCH], up[NCH];
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int64_t n = min(n0 + r, N - 1);
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int s = c * 32 + lane;
+      t[r][c] = (t_rand && s < S) ? __ldg(t_rand + n * S + s) : 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { o[r][k] = __ldg(ro + n * 3 + k); d[r][k] = __ldg(rd + n * 3 + k); }
+  }
+#pragma unroll
+  for (int c = 0; c < NCH; ++c) {
+    const int s = c * 32 + lane;
+    if (t_rand) { lo[c] = s < S ? __ldg(lower + s) : 0.f; up[c] = s < S ? __ldg(upper + s) : 0.f; }
+    else { lo[c] = s < S ? __ldg(z_table + s) : 0.f; up[c] = lo[c]; }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int64_t n = n0 + r;
+    if (n >= N) break;
+    float* zsm = smem + (size_t)(wid * R + r) * NCH * 32;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const int s = c * 32 + lane;
+      const float z = t_rand ? __fadd_rn(lo[c], __fmul_rn(__fsub_rn(up[c], lo[c]), t[r][c])) : lo[c];   // :65 / :67
+      zsm[s] = z;
+      if (s < S) z_out[n * S + s] = z;
+    }
+  }
+  __syncwarp();
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    const int64_t n = n0 + r;
+    if (n >= N) break;
+    write_points(pts + n * (int64_t)S * 3, smem + (size_t)(wid * R + r) * NCH * 32, S, o[r][0], o[r][1], o[r][2], d[r][0],
+                 d[r][1], d[r][2], lane);
   }
 }
 
@@ -205,6 +264,159 @@ invert_cdf_kernel(const float* __restrict__ cdf_g, const float* __restrict__ bin
   }
 }
 
+// ---- fast hierarchical sampling (Nf <= 256): no full-width sort ---------------------------------------------------------
+// The first version bitonic-sorted all next_pow2(Sc+Nf) depths in shared memory: 36 stages x 8 elements per lane of
+// LDS/STS + __syncwarp = ~4,000 instructions per ray, 0.08 of the HBM peak.  z_coarse is already ascending
+// (stratified bins), so only the Nf new samples are sorted -- EPL per lane in REGISTERS (element i = lane*EPL + e:
+// exchange distances below EPL stay inside the lane, the others are one shfl_xor) -- and the two ascending lists are
+// merged by rank: output slot of sample p = p + #{coarse <= v}, of coarse j = j + #{samples < c} (binary searches in
+// shared memory).  Same arithmetic per sample as above, so given an identical CDF the depths are bit-identical.
+constexpr int SP_WARPS = 8;
+
+template <int EPL>
+__device__ __forceinline__ void bitonic_sort_regs(float (&a)[EPL], int lane) {
+  constexpr int P = EPL * 32;
+#pragma unroll
+  for (int k = 2; k <= P; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j >= EPL) {
+        const int lj = j / EPL;
+        const bool lower = (lane & lj) == 0;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) {
+          const float y = __shfl_xor_sync(FULL_MASK, a[e], lj);
+          const bool up = (((lane * EPL + e) & k) == 0);
+          a[e] = (lower == up) ? fminf(a[e], y) : fmaxf(a[e], y);
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) {
+          const int l = e ^ j;
+          if (l > e) {
+            const bool up = (((lane * EPL + e) & k) == 0);
+            const float x = a[e], y = a[l];
+            const float mn = fminf(x, y), mx = fmaxf(x, y);
+            a[e] = up ? mn : mx;
+            a[l] = up ? mx : mn;
+          }
+        }
+      }
+    }
+  }
+}
+
+// number of entries < v (strict) / <= v (!strict) in an ascending shared-memory row of n floats
+template <bool STRICT>
+__device__ __forceinline__ int count_below(const float* a, int n, float v) {
+  int lo = 0, hi = n;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    const bool go = STRICT ? (a[mid] < v) : (a[mid] <= v);
+    if (go) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+template <int EPL>
+__global__ void __launch_bounds__(SP_WARPS * 32)
+sample_pdf_fast_kernel(const float* __restrict__ ro, const float* __restrict__ rd, const float* __restrict__ weights,
+                       int64_t w_stride, const float* __restrict__ z_coarse, int64_t N, int Sc, int Nf,
+                       const float* __restrict__ u_in, float* __restrict__ pts, float* __restrict__ z_out,
+                       float* __restrict__ cdf_out, int64_t* __restrict__ inds_out) {
+  extern __shared__ float smem[];
+  constexpr int P = EPL * 32;
+  const int C = Sc - 1, S = Sc + Nf;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  float* cdf = smem + (size_t)wid * (2 * C + Sc + P + S + 1);
+  float* bins = cdf + C;
+  float* zcs = bins + C;        // Sc coarse depths
+  float* ss = zcs + Sc;         // P sorted new samples (+inf padded)
+  float* zs = ss + P;           // S merged depths
+  const int64_t n = (int64_t)blockIdx.x * SP_WARPS + wid;
+  if (n >= N) return;
+  const float* w = weights + n * w_stride;
+  const float* zc = z_coarse + n * (int64_t)Sc;
+
+  // every global load of the ray first: the uniform draws, the coarse depths, the weights, the ray
+  float u[EPL];
+  const bool vec4 = EPL == 4 && u_in && Nf == P && ((reinterpret_cast<uintptr_t>(u_in) & 15) == 0);
+  if (vec4) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(u_in + n * (int64_t)Nf) + lane);
+    u[0] = t.x; u[1 % EPL] = t.y; u[2 % EPL] = t.z; u[3 % EPL] = t.w;
+  } else {
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      const int k = lane * EPL + e;
+      if (u_in) {
+        u[e] = k < Nf ? __ldg(u_in + n * (int64_t)Nf + k) : 0.f;
+      } else {   // linspace(0,1,Nf) (:95): torch computes start + step*k below the midpoint, end - step*(Nf-1-k) above it
+        const float step = Nf > 1 ? __fdiv_rn(1.0f, (float)(Nf - 1)) : 0.f;
+        u[e] = (k < Nf / 2) ? __fmul_rn(step, (float)k) : __fsub_rn(1.0f, __fmul_rn(step, (float)(Nf - 1 - k)));
+      }
+    }
+  }
+  const float o0 = __ldg(ro + n * 3), o1 = __ldg(ro + n * 3 + 1), o2 = __ldg(ro + n * 3 + 2);
+  const float d0 = __ldg(rd + n * 3), d1 = __ldg(rd + n * 3 + 1), d2 = __ldg(rd + n * 3 + 2);
+  for (int j = lane; j < Sc; j += 32) zcs[j] = __ldg(zc + j);
+
+  // pdf normaliser sum(w + 1e-5) (:86-87), cdf = [0, cumsum(pdf)] (:88-89): chunked warp scan with carry
+  float part = 0.f;
+  for (int j = lane; j < C - 1; j += 32) part += __fadd_rn(__ldg(w + j), 1e-5f);
+  const float total = warp_sum(part);
+  if (lane == 0) cdf[0] = 0.f;
+  float carry = 0.f;
+  for (int base = 0; base < C - 1; base += 32) {
+    const int j = base + lane;
+    const float p = j < C - 1 ? __fdiv_rn(__fadd_rn(__ldg(w + j), 1e-5f), total) : 0.f;
+    const float inc = warp_scan_inclusive(p, lane) + carry;
+    if (j < C - 1) cdf[j + 1] = inc;
+    carry = __shfl_sync(FULL_MASK, inc, 31);
+  }
+  __syncwarp();
+  for (int j = lane; j < C; j += 32) bins[j] = __fmul_rn(0.5f, __fadd_rn(zcs[j + 1], zcs[j]));  // :85
+  __syncwarp();
+  if (cdf_out) for (int j = lane; j < C; j += 32) cdf_out[n * C + j] = cdf[j];
+
+  float a[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) {
+    const int k = lane * EPL + e;
+    int ind = 0;
+    const float v = invert_one(cdf, bins, C, u[e], &ind);
+    a[e] = k < Nf ? v : CUDART_INF_F;
+    if (inds_out && k < Nf) inds_out[n * (int64_t)Nf + k] = ind;
+  }
+  bitonic_sort_regs<EPL>(a, lane);
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) ss[lane * EPL + e] = a[e];
+  __syncwarp();
+  // merge by rank (ties: coarse first -- only the values are observable, :116 keeps the sorted values alone)
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) {
+    const int k = lane * EPL + e;
+    if (k < Nf) zs[k + count_below<false>(zcs, Sc, a[e])] = a[e];
+  }
+  for (int j = lane; j < Sc; j += 32) {
+    const float c = zcs[j];
+    zs[j + count_below<true>(ss, Nf, c)] = c;
+  }
+  __syncwarp();
+  for (int j = lane; j < S; j += 32) z_out[n * (int64_t)S + j] = zs[j];
+  write_points(pts + n * (int64_t)S * 3, zs, S, o0, o1, o2, d0, d1, d2, lane);
+}
+
+template <int EPL>
+static int launch_sample_pdf_fast(const float* ro, const float* rd, const float* weights, int64_t w_stride,
+                                  const float* z_coarse, int64_t N, int Sc, int Nf, const float* u, float* pts, float* z,
+                                  float* cdf_out, int64_t* inds_out, cudaStream_t st) {
+  const size_t smem = (size_t)SP_WARPS * (2 * (Sc - 1) + Sc + EPL * 32 + Sc + Nf + 1) * sizeof(float);
+  if (smem > 48 * 1024) return CNRF_E_UNSUPPORTED;
+  sample_pdf_fast_kernel<EPL><<<grid_for(N, SP_WARPS), SP_WARPS * 32, smem, st>>>(ro, rd, weights, w_stride, z_coarse, N, Sc,
+                                                                                  Nf, u, pts, z, cdf_out, inds_out);
+  return CNRF_OK;
+}
+
 static int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 
 extern "C" int cnrf_sample_uniform_fwd(const float* ro, const float* rd, int64_t N, int32_t S, const float* z_table,
@@ -213,6 +425,18 @@ extern "C" int cnrf_sample_uniform_fwd(const float* ro, const float* rd, int64_t
   CNRF_REQUIRE(ro && rd && pts && z, CNRF_E_NULL);
   CNRF_REQUIRE(t_rand ? (lower && upper) : (z_table != nullptr), CNRF_E_NULL);
   CNRF_REQUIRE(N > 0 && S > 0 && S <= 4096, CNRF_E_SHAPE);
+  if (S <= 32) {
+    sample_uniform_fast_kernel<1, 4><<<grid_for(N, SU_WARPS * 4), SU_WARPS * 32, 0, as_stream(stream)>>>(
+        ro, rd, N, S, z_table, lower, upper, t_rand, pts, z);
+    CNRF_LAUNCH_CHECK();
+    return CNRF_OK;
+  }
+  if (S <= 64) {
+    sample_uniform_fast_kernel<2, 2><<<grid_for(N, SU_WARPS * 2), SU_WARPS * 32, 0, as_stream(stream)>>>(
+        ro, rd, N, S, z_table, lower, upper, t_rand, pts, z);
+    CNRF_LAUNCH_CHECK();
+    return CNRF_OK;
+  }
   size_t smem = (size_t)WARPS_PER_BLOCK * S * sizeof(float);
   sample_uniform_kernel<<<grid_for(N, WARPS_PER_BLOCK), WARPS_PER_BLOCK * 32, smem, as_stream(stream)>>>(
       ro, rd, N, S, z_table, lower, upper, t_rand, pts, z);
@@ -235,6 +459,17 @@ extern "C" int cnrf_sample_pdf_fwd(const float* ro, const float* rd, const float
                                    float* z, float* cdf_out, int64_t* inds_out, cnrf_stream_t stream) {
   CNRF_REQUIRE(ro && rd && weights && z_coarse && pts && z, CNRF_E_NULL);
   CNRF_REQUIRE(N > 0 && Sc >= 3 && Nf > 0 && Sc + Nf <= 2048, CNRF_E_SHAPE);
+  if (Nf <= 256) {
+    const int epl = next_pow2((Nf + 31) / 32);
+    int rc = CNRF_E_UNSUPPORTED;
+#define SP_ARGS ro, rd, weights, w_stride, z_coarse, N, Sc, Nf, u, pts, z, cdf_out, inds_out, as_stream(stream)
+    if (epl == 1) rc = launch_sample_pdf_fast<1>(SP_ARGS);
+    else if (epl == 2) rc = launch_sample_pdf_fast<2>(SP_ARGS);
+    else if (epl == 4) rc = launch_sample_pdf_fast<4>(SP_ARGS);
+    else if (epl == 8) rc = launch_sample_pdf_fast<8>(SP_ARGS);
+#undef SP_ARGS
+    if (rc == CNRF_OK) { CNRF_LAUNCH_CHECK(); return CNRF_OK; }
+  }
   int P = next_pow2(Sc + Nf);
   size_t smem = (size_t)WARPS_PER_BLOCK * (2 * (Sc - 1) + P) * sizeof(float);
   CNRF_REQUIRE(smem <= 48 * 1024, CNRF_E_SHAPE);
