@@ -17,9 +17,34 @@
 
 constexpr int CWARPS = 8;  // warps per block
 
-__device__ __forceinline__ float rcp_fast(float x) { return __fdividef(1.0f, x); }
-__device__ __forceinline__ float sigmoid_fast(float x) { return rcp_fast(1.0f + __expf(-x)); }
+// single-instruction SFU forms (flush-to-zero: a subnormal exp(-x) or alpha is 0 to every tolerance used here)
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float lg2_ftz(float x) { float y; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_fast(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float exp_neg(float x) { return ex2_ftz(x * -1.4426950408889634f); }       // exp(-x)
+__device__ __forceinline__ float sigmoid_fast(float x) { return rcp_fast(1.0f + exp_neg(x)); }
 __device__ __forceinline__ float widen(float sg) { return __fsub_rn(__fmul_rn(sg, 1.002f), 0.001f); }  // :28-29
+
+// Sum K (power of two <= 32) per-lane values over the warp with K-1 + log2(32/K) shuffles instead of 5K: at every
+// halving step a lane keeps one value of each pair and sends the other to its partner.  Lane l returns the total of
+// value index  bit0 = l&16, bit1 = l&8, bit2 = l&4, bit3 = l&2, bit4 = l&1  (as far as K reaches).
+template <int K>
+__device__ __forceinline__ float warp_reduce_multi(float (&v)[K], int lane) {
+  int off = 16;
+#pragma unroll
+  for (int k = K; k > 1; k >>= 1, off >>= 1) {
+    const bool hi = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < k / 2; ++i) {
+      const float keep = hi ? v[2 * i + 1] : v[2 * i], send = hi ? v[2 * i] : v[2 * i + 1];
+      v[i] = keep + __shfl_xor_sync(FULL_MASK, send, off);
+    }
+  }
+  float c = v[0];
+#pragma unroll
+  for (; off > 0; off >>= 1) c += __shfl_xor_sync(FULL_MASK, c, off);
+  return c;
+}
 
 // sigma = softplus(x) with torch's threshold 20 (:32-33,48); dsig = d sigma / dx
 template <bool WANT_D>
@@ -27,9 +52,9 @@ __device__ __forceinline__ void softplus_fast(float x, float& sigma, float& dsig
   const float e = expf(x);
   const float u = 1.0f + e;
   const float series = e * fmaf(e, fmaf(e, fmaf(e, -0.25f, 0.33333334f), -0.5f), 1.0f);   // log1p(e), e < 1/32
-  const float sp = e < 0.03125f ? series : __logf(u);
+  const float sp = e < 0.03125f ? series : lg2_ftz(u) * 0.6931471805599453f;
   sigma = x > 20.0f ? x : sp;
-  if (WANT_D) dsig = x > 20.0f ? 1.0f : __fdividef(e, u);
+  if (WANT_D) dsig = x > 20.0f ? 1.0f : e * rcp_fast(u);
 }
 
 // The registers of one ray: NCH chunks of 32 samples.
@@ -86,42 +111,54 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     const float dx = __ldg(rd + n * 3), dy = __ldg(rd + n * 3 + 1), dz = __ldg(rd + n * 3 + 2);
     nrm[r] = sqrtf(dx * dx + dy * dy + dz * dz);
   }
+  float sums[R * 8];     // per ray: R, G, B, depth, acc, 0, 0, 0
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int64_t n = n0 + r;
-    if (n >= N) break;
     float carry = 0.f;
     Sums s = {0.f, 0.f, 0.f, 0.f, 0.f};
+    {   // rays past N compute on zero-filled registers (no divergent region around the shuffles); only stores are guarded
 #pragma unroll
-    for (int c = 0; c < NCH; ++c) {
-      const int i = c * 32 + lane;
-      const bool valid = i < S;
-      const float4 rw = q[r].raw[c];
-      const float delta = __fmul_rn(next_dist<NCH>(q[r], c, S, lane), nrm[r]);      // dists * ||rd||      :45
-      float sigma, unused;
-      softplus_fast<false>(__fsub_rn(rw.w, 1.0f), sigma, unused);
-      const float sd = valid ? __fmul_rn(sigma, delta) : 0.f;
-      const float E = __expf(-sd);
-      const float inc = warp_scan_inclusive(sd, lane);
-      const float prev = __shfl_up_sync(FULL_MASK, inc, 1);
-      const float excl = carry + (lane > 0 ? prev : 0.f);                            // exclusive cumsum    :52-55
-      carry += __shfl_sync(FULL_MASK, inc, 31);
-      const float T = __expf(-excl);
-      const float w = valid ? __fmul_rn(__fsub_rn(1.0f, E), T) : 0.f;                // alpha * T           :56-57
-      s.R = fmaf(w, widen(sigmoid_fast(rw.x)), s.R);
-      s.G = fmaf(w, widen(sigmoid_fast(rw.y)), s.G);
-      s.B = fmaf(w, widen(sigmoid_fast(rw.z)), s.B);
-      s.D = fmaf(w, q[r].z[c], s.D);
-      s.A += w;
-      if (weights && valid) weights[n * (int64_t)S + i] = w;
+      for (int c = 0; c < NCH; ++c) {
+        const int i = c * 32 + lane;
+        const bool valid = i < S;
+        const float4 rw = q[r].raw[c];
+        const float delta = __fmul_rn(next_dist<NCH>(q[r], c, S, lane), nrm[r]);      // dists * ||rd||      :45
+        float sigma, unused;
+        softplus_fast<false>(__fsub_rn(rw.w, 1.0f), sigma, unused);
+        const float sd = valid ? __fmul_rn(sigma, delta) : 0.f;
+        const float E = exp_neg(sd);
+        const float inc = warp_scan_inclusive(sd, lane);
+        const float prev = __shfl_up_sync(FULL_MASK, inc, 1);
+        const float excl = carry + (lane > 0 ? prev : 0.f);                            // exclusive cumsum    :52-55
+        carry += __shfl_sync(FULL_MASK, inc, 31);
+        const float T = exp_neg(excl);
+        const float w = valid ? __fmul_rn(__fsub_rn(1.0f, E), T) : 0.f;                // alpha * T           :56-57
+        s.R = fmaf(w, widen(sigmoid_fast(rw.x)), s.R);
+        s.G = fmaf(w, widen(sigmoid_fast(rw.y)), s.G);
+        s.B = fmaf(w, widen(sigmoid_fast(rw.z)), s.B);
+        s.D = fmaf(w, q[r].z[c], s.D);
+        s.A += w;
+        if (weights && valid && n < N) weights[n * (int64_t)S + i] = w;
+      }
     }
-    s.R = warp_sum(s.R); s.G = warp_sum(s.G); s.B = warp_sum(s.B); s.D = warp_sum(s.D); s.A = warp_sum(s.A);
-    if (lane == 0) {
-      if (rgb) { rgb[n * 3] = s.R; rgb[n * 3 + 1] = s.G; rgb[n * 3 + 2] = s.B; }
-      if (depth) depth[n] = s.D;
-      if (acc) acc[n] = s.A;
-      if (disp) disp[n] = __fdiv_rn(1.0f, fmaxf(1e-10f, __fdiv_rn(s.D, s.A)));      // :64
-    }
+    sums[r * 8 + 0] = s.R; sums[r * 8 + 1] = s.G; sums[r * 8 + 2] = s.B; sums[r * 8 + 3] = s.D; sums[r * 8 + 4] = s.A;
+    sums[r * 8 + 5] = 0.f; sums[r * 8 + 6] = 0.f; sums[r * 8 + 7] = 0.f;
+  }
+  // one joint reduction: lane l ends with quantity qn = (l>>4 & 1) | (l>>3 & 1) << 1 | (l>>2 & 1) << 2 of ray
+  // r = (l>>1 & 1) | (l & 1) << 1 (for R = 4; fewer ray bits for smaller R); the other lanes hold copies.
+  const float tot = warp_reduce_multi<R * 8>(sums, lane);
+  const int qn = ((lane >> 4) & 1) | (((lane >> 3) & 1) << 1) | (((lane >> 2) & 1) << 2);
+  const int rr = R == 1 ? 0 : (R == 2 ? ((lane >> 1) & 1) : (((lane >> 1) & 1) | ((lane & 1) << 1)));
+  const bool writer = R == 1 ? (lane & 3) == 0 : (R == 2 ? (lane & 1) == 0 : true);
+  const float other = __shfl_xor_sync(FULL_MASK, tot, 28);          // depth lane (qn 3) <-> acc lane (qn 4)
+  const int64_t n = n0 + rr;
+  if (writer && n < N) {
+    if (qn < 3) { if (rgb) rgb[n * 3 + qn] = tot; }
+    else if (qn == 3) {
+      if (depth) depth[n] = tot;
+      if (disp) disp[n] = rcp_fast(fmaxf(1e-10f, tot * rcp_fast(other)));             // 1 / max(1e-10, depth / acc)  :64
+    } else if (qn == 4) { if (acc) acc[n] = tot; }
   }
 }
 
@@ -170,12 +207,12 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
       delta[c] = __fmul_rn(next_dist<NCH>(q[r], c, S, lane), norm);
       softplus_fast<true>(__fsub_rn(rw.w, 1.0f), sigma[c], dsig[c]);
       const float sd = valid ? __fmul_rn(sigma[c], delta[c]) : 0.f;
-      E[c] = __expf(-sd);
+      E[c] = exp_neg(sd);
       const float inc = warp_scan_inclusive(sd, lane);
       const float prev = __shfl_up_sync(FULL_MASK, inc, 1);
       const float excl = carry + (lane > 0 ? prev : 0.f);
       carry += __shfl_sync(FULL_MASK, inc, 31);
-      T[c] = __expf(-excl);
+      T[c] = exp_neg(excl);
       sr[c] = sigmoid_fast(rw.x); sg[c] = sigmoid_fast(rw.y); sb[c] = sigmoid_fast(rw.z);
       if (g_disp) {
         const float w = valid ? (1.0f - E[c]) * T[c] : 0.f;

@@ -149,13 +149,14 @@ points_bwd_kernel(const float* __restrict__ g_pts, const float* __restrict__ z, 
 }
 
 // searchsorted(cdf, u, right=True): number of entries <= u in a non-decreasing row (point_sampler.py:101).
+// Branch-free descent with a warp-uniform trip count (the row length), so the lanes of a warp never diverge.
 __device__ __forceinline__ int upper_bound_smem(const float* cdf, int C, float u) {
-  int lo = 0, hi = C;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
+  int pos = 0;
+  for (int step = 1 << (31 - __clz(C)); step > 0; step >>= 1) {
+    const int np = pos + step;
+    if (np <= C && cdf[np - 1] <= u) pos = np;
   }
-  return lo;
+  return pos;
 }
 
 // inverse-CDF sample for one u given the row's cdf and bins in shared memory (point_sampler.py:101-113)
@@ -309,13 +310,12 @@ __device__ __forceinline__ void bitonic_sort_regs(float (&a)[EPL], int lane) {
 // number of entries < v (strict) / <= v (!strict) in an ascending shared-memory row of n floats
 template <bool STRICT>
 __device__ __forceinline__ int count_below(const float* a, int n, float v) {
-  int lo = 0, hi = n;
-  while (lo < hi) {
-    const int mid = (lo + hi) >> 1;
-    const bool go = STRICT ? (a[mid] < v) : (a[mid] <= v);
-    if (go) lo = mid + 1; else hi = mid;
+  int pos = 0;
+  for (int step = 1 << (31 - __clz(n)); step > 0; step >>= 1) {
+    const int np = pos + step;
+    if (np <= n && (STRICT ? (a[np - 1] < v) : (a[np - 1] <= v))) pos = np;
   }
-  return lo;
+  return pos;
 }
 
 template <int EPL>
