@@ -37,6 +37,18 @@ __device__ __forceinline__ void write_points(float* __restrict__ dst, const floa
   }
 }
 
+// Four consecutive samples = 12 floats = three float4 stores from one lane (one LDS.128 for the depths, no selects).
+__device__ __forceinline__ void write_point_group(float* __restrict__ dst /*16-byte aligned, 12 floats*/, float4 z, float o0,
+                                                  float o1, float o2, float d0, float d1, float d2) {
+  float4* d4 = reinterpret_cast<float4*>(dst);
+  d4[0] = make_float4(__fadd_rn(o0, __fmul_rn(d0, z.x)), __fadd_rn(o1, __fmul_rn(d1, z.x)), __fadd_rn(o2, __fmul_rn(d2, z.x)),
+                      __fadd_rn(o0, __fmul_rn(d0, z.y)));
+  d4[1] = make_float4(__fadd_rn(o1, __fmul_rn(d1, z.y)), __fadd_rn(o2, __fmul_rn(d2, z.y)), __fadd_rn(o0, __fmul_rn(d0, z.z)),
+                      __fadd_rn(o1, __fmul_rn(d1, z.z)));
+  d4[2] = make_float4(__fadd_rn(o2, __fmul_rn(d2, z.z)), __fadd_rn(o0, __fmul_rn(d0, z.w)), __fadd_rn(o1, __fmul_rn(d1, z.w)),
+                      __fadd_rn(o2, __fmul_rn(d2, z.w)));
+}
+
 // Fast path of sample_uniform for S <= 32*NCH: R rays per warp, every load issued before the first store.
 constexpr int SU_WARPS = 8;
 template <int NCH, int R>
@@ -45,11 +57,12 @@ sample_uniform_fast_kernel(const float* __restrict__ ro, const float* __restrict
                            const float* __restrict__ z_table, const float* __restrict__ lower,
                            const float* __restrict__ upper, const float* __restrict__ t_rand, float* __restrict__ pts,
                            float* __restrict__ z_out) {
-  __shared__ float smem[SU_WARPS * R * NCH * 32];
+  __shared__ __align__(16) float smem[SU_WARPS * R * NCH * 32];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int64_t n0 = ((int64_t)blockIdx.x * SU_WARPS + wid) * R;
   if (n0 >= N) return;
-  float t[R][NCH], o[R][3], d[R][3], lo[NCH], up[NCH];
+  const bool grouped = S == NCH * 32 && (reinterpret_cast<uintptr_t>(pts) & 15) == 0;   // one group of 4 samples per lane
+  float t[R][NCH], o[R][3] = {}, d[R][3] = {}, lo[NCH], up[NCH];
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int64_t n = min(n0 + r, N - 1);
@@ -58,8 +71,10 @@ sample_uniform_fast_kernel(const float* __restrict__ ro, const float* __restrict
       const int s = c * 32 + lane;
       t[r][c] = (t_rand && s < S) ? __ldg(t_rand + n * S + s) : 0.f;
     }
+    if (!grouped) {
 #pragma unroll
-    for (int k = 0; k < 3; ++k) { o[r][k] = __ldg(ro + n * 3 + k); d[r][k] = __ldg(rd + n * 3 + k); }
+      for (int k = 0; k < 3; ++k) { o[r][k] = __ldg(ro + n * 3 + k); d[r][k] = __ldg(rd + n * 3 + k); }
+    }
   }
 #pragma unroll
   for (int c = 0; c < NCH; ++c) {
@@ -81,6 +96,18 @@ sample_uniform_fast_kernel(const float* __restrict__ ro, const float* __restrict
     }
   }
   __syncwarp();
+  if (grouped) {
+    // R rays x NCH*8 groups of four samples = exactly 32 groups: one group per lane, ray and origin re-read per lane
+    constexpr int GPR = NCH * 8;
+    const int r = lane / GPR, g = lane % GPR;
+    const int64_t n = n0 + r;
+    if (n < N) {
+      const float4 zq = *reinterpret_cast<const float4*>(smem + (size_t)(wid * R + r) * NCH * 32 + 4 * g);
+      write_point_group(pts + (n * (int64_t)S + 4 * g) * 3, zq, __ldg(ro + n * 3), __ldg(ro + n * 3 + 1), __ldg(ro + n * 3 + 2),
+                        __ldg(rd + n * 3), __ldg(rd + n * 3 + 1), __ldg(rd + n * 3 + 2));
+    }
+    return;
+  }
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     const int64_t n = n0 + r;
@@ -406,6 +433,192 @@ sample_pdf_fast_kernel(const float* __restrict__ ro, const float* __restrict__ r
   write_points(pts + n * (int64_t)S * 3, zs, S, o0, o1, o2, d0, d1, d2, lane);
 }
 
+// ---- compile-time shapes (the live configs: 32+128, 64+64, 64+128): every loop unrolled, searches padded ------------
+// ncu on the runtime-shape kernel above: 2,070 executed instructions per ray at IPC 3.4 -- issue-bound, a quarter of the
+// HBM peak; the searches (runtime trip counts, bounds checks), the generic loop prologues and the select-heavy
+// compare-exchange were most of it.  Here the cdf / coarse-depth rows are padded to a power of two with +inf, so a
+// search is log2 steps of (LDS, FSETP, predicated add) with immediate offsets.
+template <int SC, int NF>
+struct __align__(16) SpdfSmem {
+  float zs[SC + NF];    // merged depths (first: 16-byte aligned for LDS.128)
+  float cdf[SC];        // C = SC-1 entries, then +inf
+  float bins[SC];
+  float zc[SC];
+  float ss[NF];         // sorted new samples
+};
+
+template <int EPL>
+__device__ __forceinline__ void bitonic_sort_regs_v2(float (&a)[EPL], int lane) {
+  constexpr int P = EPL * 32;
+#pragma unroll
+  for (int k = 2; k <= P; k <<= 1) {
+#pragma unroll
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      if (j >= EPL) {                       // partner in another lane; direction and side are per-lane predicates
+        const int lj = j / EPL;
+        const bool take_min = ((lane & lj) == 0) == ((lane & (k / EPL)) == 0);
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) {
+          const float y = __shfl_xor_sync(FULL_MASK, a[e], lj);
+          a[e] = take_min ? fminf(a[e], y) : fmaxf(a[e], y);
+        }
+      } else if (k >= EPL) {                // in-lane pair; bit k of (lane*EPL + e) is bit k/EPL of the lane
+        const bool up = (lane & (k / EPL)) == 0;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) {
+          const int l = e ^ j;
+          if (l > e) {
+            const float x = a[e], y = a[l];
+            a[e] = up ? fminf(x, y) : fmaxf(x, y);
+            a[l] = up ? fmaxf(x, y) : fminf(x, y);
+          }
+        }
+      } else {                              // k < EPL: direction is a compile-time function of e
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) {
+          const int l = e ^ j;
+          if (l > e) {
+            const float x = a[e], y = a[l];
+            const bool up = (e & k) == 0;
+            a[e] = up ? fminf(x, y) : fmaxf(x, y);
+            a[l] = up ? fmaxf(x, y) : fminf(x, y);
+          }
+        }
+      }
+    }
+  }
+}
+
+// #entries <= v (or < v) among the first LEN (power of two) floats of an ascending row; rows are +inf padded
+template <int LEN, bool STRICT>
+__device__ __forceinline__ int count_pow2(const float* a, float v) {
+  int pos = 0;
+#pragma unroll
+  for (int step = LEN / 2; step > 0; step >>= 1) {
+    const float t = a[pos + step - 1];
+    if (STRICT ? (t < v) : (t <= v)) pos += step;
+  }
+  const float t = a[pos];
+  pos += (STRICT ? (t < v) : (t <= v)) ? 1 : 0;
+  return pos;
+}
+
+template <int SC, int NF>
+__global__ void __launch_bounds__(SP_WARPS * 32)
+sample_pdf_static_kernel(const float* __restrict__ ro, const float* __restrict__ rd, const float* __restrict__ weights,
+                         int64_t w_stride, const float* __restrict__ z_coarse, int64_t N, const float* __restrict__ u_in,
+                         float* __restrict__ pts, float* __restrict__ z_out, float* __restrict__ cdf_out,
+                         int64_t* __restrict__ inds_out) {
+  static_assert(SC % 32 == 0 && NF % 32 == 0 && (NF & (NF - 1)) == 0 && (SC & (SC - 1)) == 0, "shape");
+  constexpr int C = SC - 1, S = SC + NF, EPL = NF / 32, NCC = SC / 32;
+  __shared__ SpdfSmem<SC, NF> sm_all[SP_WARPS];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  SpdfSmem<SC, NF>& sm = sm_all[wid];
+  const int64_t n = (int64_t)blockIdx.x * SP_WARPS + wid;
+  if (n >= N) return;
+  const float* w = weights + n * w_stride;
+  const float* zc = z_coarse + n * (int64_t)SC;
+
+  // ---- every global load of the ray first
+  float u[EPL];
+  if (u_in) {
+    const float* ur = u_in + n * (int64_t)NF;
+    if (EPL % 4 == 0 && (reinterpret_cast<uintptr_t>(u_in) & 15) == 0) {
+#pragma unroll
+      for (int e4 = 0; e4 < EPL / 4; ++e4) {
+        const float4 t = __ldg(reinterpret_cast<const float4*>(ur) + lane * (EPL / 4) + e4);
+        u[e4 * 4] = t.x; u[(e4 * 4 + 1) % EPL] = t.y; u[(e4 * 4 + 2) % EPL] = t.z; u[(e4 * 4 + 3) % EPL] = t.w;
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < EPL; ++e) u[e] = __ldg(ur + lane * EPL + e);
+    }
+  } else {   // linspace(0,1,NF) (:95): torch computes start + step*k below the midpoint, end - step*(NF-1-k) above it
+    const float step = __fdiv_rn(1.0f, (float)(NF - 1));
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) {
+      const int k = lane * EPL + e;
+      u[e] = (k < NF / 2) ? __fmul_rn(step, (float)k) : __fsub_rn(1.0f, __fmul_rn(step, (float)(NF - 1 - k)));
+    }
+  }
+  float zcr[NCC], wr[NCC];
+#pragma unroll
+  for (int c = 0; c < NCC; ++c) {
+    const int j = c * 32 + lane;
+    zcr[c] = __ldg(zc + j);
+    wr[c] = j < C - 1 ? __ldg(w + j) : 0.f;
+  }
+  const float o0 = __ldg(ro + n * 3), o1 = __ldg(ro + n * 3 + 1), o2 = __ldg(ro + n * 3 + 2);
+  const float d0 = __ldg(rd + n * 3), d1 = __ldg(rd + n * 3 + 1), d2 = __ldg(rd + n * 3 + 2);
+
+  // ---- pdf normaliser sum(w + 1e-5) (:86-87); cdf = [0, cumsum(pdf)] (:88-89); bins = mids of z_coarse (:85)
+  float part = 0.f;
+#pragma unroll
+  for (int c = 0; c < NCC; ++c) if (c * 32 + lane < C - 1) part += __fadd_rn(wr[c], 1e-5f);
+  const float total = warp_sum(part);
+  if (lane == 0) sm.cdf[0] = 0.f;
+  float carry = 0.f;
+#pragma unroll
+  for (int c = 0; c < NCC; ++c) {
+    const int j = c * 32 + lane;
+    const float p = j < C - 1 ? __fdiv_rn(__fadd_rn(wr[c], 1e-5f), total) : 0.f;
+    const float inc = warp_scan_inclusive(p, lane) + carry;
+    if (j < C - 1) sm.cdf[j + 1] = inc;
+    carry = __shfl_sync(FULL_MASK, inc, 31);
+    sm.zc[j] = zcr[c];
+    float zn = __shfl_down_sync(FULL_MASK, zcr[c], 1);
+    if (c + 1 < NCC) { const float first = __shfl_sync(FULL_MASK, zcr[c + 1 < NCC ? c + 1 : c], 0); zn = lane == 31 ? first : zn; }
+    if (j < C) sm.bins[j] = __fmul_rn(0.5f, __fadd_rn(zn, zcr[c]));
+  }
+  if (lane == 0) { sm.cdf[C] = CUDART_INF_F; sm.bins[C] = 0.f; }
+  __syncwarp();
+  if (cdf_out) {
+#pragma unroll
+    for (int c = 0; c < NCC; ++c) if (c * 32 + lane < C) cdf_out[n * C + c * 32 + lane] = sm.cdf[c * 32 + lane];
+  }
+
+  // ---- inverse CDF (:101-113)
+  float a[EPL];
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) {
+    // searchsorted(cdf, u, right=True): entries <= u; the +inf pad keeps the descent inside the C real entries
+    int ind = 0;
+#pragma unroll
+    for (int step = SC / 2; step > 0; step >>= 1) if (sm.cdf[ind + step - 1] <= u[e]) ind += step;
+    const int below = max(0, ind - 1), above = min(C - 1, ind);
+    const float cb = sm.cdf[below], ca = sm.cdf[above], bb = sm.bins[below], ba = sm.bins[above];
+    float denom = __fsub_rn(ca, cb);
+    denom = denom < 1e-5f ? 1.0f : denom;
+    const float t = __fdiv_rn(__fsub_rn(u[e], cb), denom);
+    a[e] = __fadd_rn(bb, __fmul_rn(t, __fsub_rn(ba, bb)));
+    if (inds_out) inds_out[n * (int64_t)NF + lane * EPL + e] = ind;
+  }
+  bitonic_sort_regs_v2<EPL>(a, lane);
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) sm.ss[lane * EPL + e] = a[e];
+  __syncwarp();
+  // ---- merge by rank (ties: coarse first -- only the values are observable, :116 keeps the sorted values alone)
+#pragma unroll
+  for (int e = 0; e < EPL; ++e) sm.zs[lane * EPL + e + count_pow2<SC, false>(sm.zc, a[e])] = a[e];
+#pragma unroll
+  for (int c = 0; c < NCC; ++c) sm.zs[c * 32 + lane + count_pow2<NF, true>(sm.ss, zcr[c])] = zcr[c];
+  __syncwarp();
+  float* zo = z_out + n * (int64_t)S;
+#pragma unroll
+  for (int c = 0; c < S / 32; ++c) zo[c * 32 + lane] = sm.zs[c * 32 + lane];
+  if ((reinterpret_cast<uintptr_t>(pts) & 15) == 0) {
+#pragma unroll
+    for (int g0 = 0; g0 < S / 4; g0 += 32) {
+      const int g = g0 + lane;
+      if (g < S / 4)
+        write_point_group(pts + (n * (int64_t)S + 4 * g) * 3, *reinterpret_cast<const float4*>(sm.zs + 4 * g), o0, o1, o2, d0,
+                          d1, d2);
+    }
+  } else {
+    write_points(pts + n * (int64_t)S * 3, sm.zs, S, o0, o1, o2, d0, d1, d2, lane);
+  }
+}
+
 template <int EPL>
 static int launch_sample_pdf_fast(const float* ro, const float* rd, const float* weights, int64_t w_stride,
                                   const float* z_coarse, int64_t N, int Sc, int Nf, const float* u, float* pts, float* z,
@@ -459,6 +672,15 @@ extern "C" int cnrf_sample_pdf_fwd(const float* ro, const float* rd, const float
                                    float* z, float* cdf_out, int64_t* inds_out, cnrf_stream_t stream) {
   CNRF_REQUIRE(ro && rd && weights && z_coarse && pts && z, CNRF_E_NULL);
   CNRF_REQUIRE(N > 0 && Sc >= 3 && Nf > 0 && Sc + Nf <= 2048, CNRF_E_SHAPE);
+#define SP_STATIC(SC_, NF_)                                                                                          \
+  if (Sc == SC_ && Nf == NF_) {                                                                                      \
+    sample_pdf_static_kernel<SC_, NF_><<<grid_for(N, SP_WARPS), SP_WARPS * 32, 0, as_stream(stream)>>>(             \
+        ro, rd, weights, w_stride, z_coarse, N, u, pts, z, cdf_out, inds_out);                                      \
+    CNRF_LAUNCH_CHECK();                                                                                             \
+    return CNRF_OK;                                                                                                  \
+  }
+  SP_STATIC(32, 128) SP_STATIC(64, 64) SP_STATIC(64, 128)
+#undef SP_STATIC
   if (Nf <= 256) {
     const int epl = next_pow2((Nf + 31) / 32);
     int rc = CNRF_E_UNSUPPORTED;

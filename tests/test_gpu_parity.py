@@ -135,11 +135,14 @@ def test_searchsorted_indices_bit_exact(golden_dir, dev):
     assert np.array_equal(orc.searchsorted_right_np(cdf.numpy()[:8], u.numpy()[:8]), inds.cpu().numpy()[:8])
 
 
-def test_sample_pdf_properties_full_size(dev):
-    """C1 shapes (4096 rays, 32+128): sortedness, coarse depths retained, points on the ray; vs oracle values."""
+@pytest.mark.parametrize("N,Sc,Nf", [(4096, 32, 128), (2048, 64, 64), (1024, 64, 128), (513, 24, 40), (300, 64, 192),
+                                     (129, 8, 300)])
+def test_sample_pdf_properties_full_size(dev, N, Sc, Nf):
+    """C1 shapes (4096 rays, 32+128), C3 (64+64), C5-like (64+128) -- the compile-time-shape kernels -- and odd shapes on the
+    runtime-shape kernels (register sort up to 256 new samples, shared-memory sort above): sortedness, coarse depths
+    retained, points on the ray; vs oracle values."""
     from codenerf_b200 import ops
     torch.manual_seed(0)
-    N, Sc, Nf = 4096, 32, 128
     z_t, lo, up = (t.to(dev) for t in orc.depth_tables(Sc, 0.8, 1.8, "lindepth"))
     ro, rd = torch.randn(N, 3, device=dev), torch.randn(N, 3, device=dev)
     pts_c, z_c = ops.sample_uniform(ro, rd, z_t, lo, up, torch.rand(N, Sc, device=dev))
