@@ -28,6 +28,20 @@ class PtrTable(C.Structure):   # cnrf_codenerf_params and cnrf_codenerf_grads sh
     _fields_ = [("weight", C.c_void_p * NUM_LAYERS), ("bias", C.c_void_p * NUM_LAYERS)]
 
 
+FLEX_MAX_XYZ_LAYERS = 15
+
+
+class FlexShape(C.Structure):   # cnrf_flex_shape
+    _fields_ = [("num_layers", c_i32), ("hidden", c_i32), ("dim_xyz", c_i32), ("dim_dir", c_i32), ("skip_mask", C.c_uint32),
+                ("num_rays", c_i64), ("num_samples", c_i32), ("pairing", c_i32), ("precision", c_i32), ("keep", c_i32)]
+
+
+class FlexPtrs(C.Structure):    # cnrf_flex_params and cnrf_flex_grads share this layout
+    _fields_ = [("w_layer1", C.c_void_p), ("b_layer1", C.c_void_p), ("w_xyz", C.c_void_p * FLEX_MAX_XYZ_LAYERS),
+                ("b_xyz", C.c_void_p * FLEX_MAX_XYZ_LAYERS), ("w_feat", C.c_void_p), ("b_feat", C.c_void_p),
+                ("w_dir", C.c_void_p), ("b_dir", C.c_void_p), ("w_alpha", C.c_void_p), ("b_alpha", C.c_void_p),
+                ("w_rgb", C.c_void_p), ("b_rgb", C.c_void_p)]
+
 _SIGS = {
     "cnrf_abi_version": (C.c_int, []),
     "cnrf_error_string": (C.c_char_p, [C.c_int]),
@@ -63,6 +77,12 @@ _SIGS = {
     "cnrf_field_bwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
                                  c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.POINTER(PtrTable), c_f32p,
                                  c_f32p, c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_flexnerf_saved_bytes": (c_sz, [C.POINTER(FlexShape)]),
+    "cnrf_flexnerf_workspace_bytes": (c_sz, [C.POINTER(FlexShape), c_i32]),
+    "cnrf_flexnerf_fwd": (C.c_int, [C.POINTER(FlexShape), C.POINTER(FlexPtrs), c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p,
+                                    c_sz, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_flexnerf_bwd": (C.c_int, [C.POINTER(FlexShape), C.POINTER(FlexPtrs), c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p,
+                                    c_sz, C.POINTER(FlexPtrs), c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
     "cnrf_adamw_step": (C.c_int, [C.c_void_p, c_i32, c_f, c_f, c_f, C.c_void_p]),
     "cnrf_field_fwd_ids": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
                                      C.c_void_p, c_i64, c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.c_void_p,

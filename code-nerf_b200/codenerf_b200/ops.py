@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import FieldShape, PtrTable, check
+from ._lib import FieldShape, FlexPtrs, FlexShape, PtrTable, check
 
 _f32 = torch.float32
 
@@ -458,3 +458,81 @@ class _Model(torch.autograd.Function):
 def codenerf_model(params, z_s, z_t, x, hidden, code, dim_xyz, dim_dir, precision=_lib.PRECISION_FP32):
     cfg = (hidden, code, dim_xyz, dim_dir, precision)
     return _Model.apply(cfg, z_s, z_t, x, *params)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Vanilla NeRF field (FlexibleNeRFModel, models/model.py:5-76)
+# ----------------------------------------------------------------------------------------------------------
+def _flex_ptrs(tensors, num_xyz):
+    """tensors: (w,b) pairs in state_dict order -- layer1, layers_xyz[0..], fc_feat, layers_dir[0], fc_alpha, fc_rgb."""
+    t = FlexPtrs()
+    it = iter(tensors)
+    t.w_layer1, t.b_layer1 = next(it).data_ptr(), next(it).data_ptr()
+    for i in range(num_xyz):
+        t.w_xyz[i], t.b_xyz[i] = next(it).data_ptr(), next(it).data_ptr()
+    t.w_feat, t.b_feat = next(it).data_ptr(), next(it).data_ptr()
+    t.w_dir, t.b_dir = next(it).data_ptr(), next(it).data_ptr()
+    t.w_alpha, t.b_alpha = next(it).data_ptr(), next(it).data_ptr()
+    t.w_rgb, t.b_rgb = next(it).data_ptr(), next(it).data_ptr()
+    return t
+
+
+class _FlexNerf(torch.autograd.Function):
+    """x_xyz (M, dim_xyz) embedded points, x_dir (N, dim_dir) embedded per-ray directions, M = N*S -> raw (M, 4)."""
+
+    @staticmethod
+    def forward(ctx, cfg, x_xyz, x_dir, *params):
+        _req_cuda(x_xyz, x_dir, *params)
+        lib = _lib.load()
+        num_layers, hidden, dim_xyz, dim_dir, skip_mask, S, pairing, precision = cfg
+        x_xyz, ld_xyz = _rows(x_xyz)
+        x_dir, ld_dir = _rows(x_dir)
+        if ld_xyz == 0:
+            x_xyz, ld_xyz = x_xyz.contiguous(), x_xyz.shape[1]
+        if ld_dir == 0:
+            x_dir, ld_dir = x_dir.contiguous(), x_dir.shape[1]
+        params = tuple(_c(p) for p in params)
+        M, N = x_xyz.shape[0], x_dir.shape[0]
+        assert M == N * S, "FlexibleNeRF field: rows of x_xyz must be rays x samples"
+        keep = int(any(ctx.needs_input_grad))
+        shp = FlexShape(num_layers, hidden, dim_xyz, dim_dir, skip_mask, N, S, pairing, precision, keep)
+        dev = x_xyz.device
+        saved = _bytes(lib.cnrf_flexnerf_saved_bytes(C.byref(shp)), dev)
+        ws = _bytes(lib.cnrf_flexnerf_workspace_bytes(C.byref(shp), 0), dev)
+        raw = torch.empty((M, 4), dtype=_f32, device=dev)
+        tab = _flex_ptrs(params, num_layers - 1)
+        check(lib.cnrf_flexnerf_fwd(C.byref(shp), C.byref(tab), _p(x_xyz), ld_xyz, _p(x_dir), ld_dir, _p(raw),
+                                    _p(saved) if keep else None, saved.numel() if keep else 0, _p(ws), ws.numel(), _stream()),
+              "cnrf_flexnerf_fwd")
+        if keep:
+            ctx.save_for_backward(x_xyz, x_dir, saved, *params)
+            ctx.cfg, ctx.lds = cfg, (ld_xyz, ld_dir)
+        return raw
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_raw):
+        x_xyz, x_dir, saved, *params = ctx.saved_tensors
+        lib = _lib.load()
+        num_layers, hidden, dim_xyz, dim_dir, skip_mask, S, pairing, precision = ctx.cfg
+        ld_xyz, ld_dir = ctx.lds
+        M, N = x_xyz.shape[0], x_dir.shape[0]
+        shp = FlexShape(num_layers, hidden, dim_xyz, dim_dir, skip_mask, N, S, pairing, precision, 1)
+        dev = x_xyz.device
+        g_raw = _c(g_raw)
+        grads = tuple(torch.empty_like(p) for p in params)
+        g_xyz = torch.empty((M, dim_xyz), dtype=_f32, device=dev) if ctx.needs_input_grad[1] else None
+        g_dir = torch.empty((N, dim_dir), dtype=_f32, device=dev) if ctx.needs_input_grad[2] else None
+        ws = _bytes(lib.cnrf_flexnerf_workspace_bytes(C.byref(shp), 1), dev)
+        tab, gtab = _flex_ptrs(params, num_layers - 1), _flex_ptrs(grads, num_layers - 1)
+        check(lib.cnrf_flexnerf_bwd(C.byref(shp), C.byref(tab), _p(x_xyz), ld_xyz, _p(x_dir), ld_dir, _p(g_raw), _p(saved),
+                                    saved.numel(), C.byref(gtab), _p(g_xyz), _p(g_dir), _p(ws), ws.numel(), _stream()),
+              "cnrf_flexnerf_bwd")
+        return (None, g_xyz, g_dir) + grads
+
+
+def flexnerf(params, x_xyz, x_dir, num_layers, hidden, dim_xyz, dim_dir, skip_mask, num_samples,
+             pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_FP32):
+    cfg = (int(num_layers), int(hidden), int(dim_xyz), int(dim_dir), int(skip_mask), int(num_samples), int(pairing),
+           int(precision))
+    return _FlexNerf.apply(cfg, x_xyz, x_dir, *params)

@@ -7,7 +7,79 @@ import torch
 
 from codenerf_b200 import _lib, ops
 
-__all__ = ["CodeNeRFModel", "ShapeTextureEmbedding", "get_params_tensor"]
+__all__ = ["FlexibleNeRFModel", "CodeNeRFModel", "ShapeTextureEmbedding", "get_params_tensor"]
+
+
+class FlexibleNeRFModel(torch.nn.Module):
+    """Vanilla NeRF MLP (models/model.py:5-76; config/lego.yml: 8 x 256, skip_connect_ids [4]).  Same constructor, module
+    names (layer1, layers_xyz.N, fc_feat, layers_dir.0, fc_alpha, fc_rgb) and parameter shapes as the reference, so its
+    checkpoints load both ways; the Linear modules only HOLD the parameters, the arithmetic runs in libcnrf.so
+    (cnrf_flexnerf_fwd / _bwd).  forward(x) accepts
+      * x: a tensor (..., dim_xyz + dim_dir) of embedded inputs -- the reference's literal signature -> (..., 4);
+      * x: a view_synthesis.nerf.FieldQuery (what our forward_pass passes): points and ray directions are embedded by the
+        CUDA operator and the view-direction half of layers_dir[0] is evaluated once per ray -> (N, S, 4).
+    The use_viewdirs=False variant (fc_out head, :47-48,75-76) is not on the hot path of any config and raises."""
+
+    def __init__(self, num_layers=4, hidden_size=128, skip_connect_ids=[4], num_encoding_fn_xyz=6, num_encoding_fn_dir=4,
+                 include_input_xyz=True, include_input_dir=True, use_viewdirs=True):
+        super(FlexibleNeRFModel, self).__init__()
+        if not use_viewdirs:
+            raise NotImplementedError("FlexibleNeRFModel(use_viewdirs=False) has no libcnrf kernel path")
+        self.num_layers = num_layers
+        self.hidden_size = hidden_size
+        self.skip_connect_ids = skip_connect_ids
+        include_input_xyz = 3 if include_input_xyz else 0
+        include_input_dir = 3 if include_input_dir else 0
+        self.use_viewdirs = use_viewdirs
+        self.dim_xyz = include_input_xyz + 2 * 3 * num_encoding_fn_xyz
+        self.dim_dir = include_input_dir + 2 * 3 * num_encoding_fn_dir
+        assert num_layers - 1 <= _lib.FLEX_MAX_XYZ_LAYERS and hidden_size % 2 == 0
+        self.layer1 = torch.nn.Linear(self.dim_xyz, hidden_size)
+        self.layers_xyz = torch.nn.ModuleList()
+        for i in range(self.num_layers - 1):
+            if i in self.skip_connect_ids:
+                self.layers_xyz.append(torch.nn.Linear(self.dim_xyz + hidden_size, hidden_size))
+            else:
+                self.layers_xyz.append(torch.nn.Linear(hidden_size, hidden_size))
+        self.fc_feat = torch.nn.Linear(hidden_size, hidden_size)
+        self.layers_dir = torch.nn.ModuleList()
+        self.layers_dir.append(torch.nn.Linear(self.dim_dir + hidden_size, hidden_size // 2))
+        self.fc_alpha = torch.nn.Linear(hidden_size, 1)
+        self.fc_rgb = torch.nn.Linear(hidden_size // 2, 3)
+        self.relu = torch.nn.functional.relu
+
+    def _param_list(self):
+        layers = [self.layer1] + list(self.layers_xyz) + [self.fc_feat, self.layers_dir[0], self.fc_alpha, self.fc_rgb]
+        out = []
+        for layer in layers:
+            out += [layer.weight, layer.bias]
+        return out
+
+    def _skip_mask(self):
+        return sum(1 << i for i in range(self.num_layers - 1) if i in self.skip_connect_ids)
+
+    def forward(self, x):
+        from ..nerf import FieldQuery
+        params = self._param_list()
+        if isinstance(x, FieldQuery):
+            ex, ed = x.embedder_xyz, x.embedder_dir
+            assert 3 * ex.out_dim_per_channel == self.dim_xyz and 3 * ed.out_dim_per_channel == self.dim_dir, \
+                "embedder widths do not match the model's dim_xyz / dim_dir"
+            N, S = x.pts.shape[0], x.pts.shape[1]
+            x_xyz = ex.embed(x.pts.reshape(-1, x.pts.shape[-1]))
+            viewdirs = x.rd / x.rd.norm(p=2, dim=-1).unsqueeze(-1)                       # nerf/__init__.py:126
+            x_dir = ed.embed(viewdirs)
+            precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[x.precision]
+            pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
+            raw = ops.flexnerf(params, x_xyz, x_dir, self.num_layers, self.hidden_size, self.dim_xyz, self.dim_dir,
+                               self._skip_mask(), S, pairing=pairing, precision=precision)
+            return raw.reshape(N, S, 4)
+        lead = x.shape[:-1]
+        x2 = x.reshape(-1, x.shape[-1])
+        raw = ops.flexnerf(params, x2[:, : self.dim_xyz], x2[:, self.dim_xyz:], self.num_layers, self.hidden_size,
+                           self.dim_xyz, self.dim_dir, self._skip_mask(), 1, pairing=_lib.PAIRING_CORRECT,
+                           precision=_lib.PRECISION_FP32)
+        return raw.reshape(*lead, 4)
 
 
 def get_params_tensor(model, is_distributed):

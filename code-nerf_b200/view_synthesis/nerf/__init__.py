@@ -111,13 +111,18 @@ def forward_pass(model: torch.nn.Module, embedders, rd, pts: torch.Tensor, objec
     tensor (:123-130) and the per-sample evaluation of the code layers never materialise: the model receives a
     FieldQuery and runs the fused kernels.  Any other module gets the reference's composition verbatim (the encodings
     still come from the CUDA operator)."""
-    from ..models.model import CodeNeRFModel
+    from ..models.model import CodeNeRFModel, FlexibleNeRFModel
     num_rays, num_samples = pts.shape[0], pts.shape[1]
     [shape_embedding, texture_embedding] = object_embedding
     embedder_xyz, embedder_dir = embedders
     if isinstance(_unwrap(model), CodeNeRFModel) and rd is not None and embedder_dir is not None:
         query = FieldQuery(pts, rd, embedder_xyz, embedder_dir, _state["precision"], _state["pairing"])
         return model(shape_embedding, texture_embedding, query)
+    if isinstance(_unwrap(model), FlexibleNeRFModel) and rd is not None and embedder_dir is not None:
+        # The reference cannot reach this class from forward_pass (it calls model(z_s, z_t, x) on a one-argument forward:
+        # TypeError, SURVEY F11); the drop-in runs it -- the codes are ignored, as the 3-line adapter of SURVEY 8(c) would.
+        query = FieldQuery(pts, rd, embedder_xyz, embedder_dir, _state["precision"], _state["pairing"])
+        return model(query)
 
     shape_embedding = shape_embedding[:, None, :].expand(-1, num_samples, -1)
     texture_embedding = texture_embedding[:, None, :].expand(-1, num_samples, -1)

@@ -210,6 +210,54 @@ int cnrf_field_bwd_ids(const cnrf_field_shape* s, const cnrf_codenerf_params* p,
                        float* g_tab_s, float* g_tab_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Vanilla NeRF field.  FlexibleNeRFModel.forward (use_viewdirs=True), view_synthesis/models/model.py:51-74 -- SURVEY
+ * section 8 row a15 / f1 (config/lego.yml: num_layers 8, hidden 256, skip_connect_ids [4]).
+ *   h = relu(layer1 x_xyz); for i < num_layers-1: h = relu(layers_xyz[i] (skip i ? cat(h, x_xyz) : h));
+ *   feat = relu(fc_feat h); sigma = fc_alpha feat; v = relu(layers_dir[0] cat(feat, x_dir)); rgb = fc_rgb v;
+ *   raw = [rgb | sigma].
+ * Inputs as cnrf_codenerf_fwd: x_xyz [M, dim_xyz] (row stride ld_xyz), x_dir [N, dim_dir] per RAY (row stride ld_dir; the
+ * pairing assigns rows to samples -- the view-direction half of layers_dir[0] is evaluated once per ray and enters the
+ * per-sample layer as a bias row), M = num_rays * num_samples.  FlexibleNeRFModel.forward(x) on an already-embedded
+ * [M, dim_xyz+dim_dir] tensor is the case num_rays = M, num_samples = 1.  Every layer is one GEMM of the per-ray toolkit
+ * (sgemm.cu in CNRF_PRECISION_FP32, gemm_tc.cu split-bf16 tcgen05 in CNRF_PRECISION_BF16); there is no fused chain yet.
+ * ---------------------------------------------------------------------------------------------------- */
+#define CNRF_FLEX_MAX_XYZ_LAYERS 15
+typedef struct {
+  int32_t num_layers;   /* constructor argument: layer1 + (num_layers - 1) layers_xyz                    */
+  int32_t hidden;       /* H, even (layers_dir[0] has H/2 outputs)                                         */
+  int32_t dim_xyz;
+  int32_t dim_dir;
+  uint32_t skip_mask;   /* bit i set: layers_xyz[i] takes cat(h, x_xyz) (models/model.py:33-37,61-64)      */
+  int64_t num_rays;
+  int32_t num_samples;
+  int32_t pairing;      /* CNRF_PAIRING_*   */
+  int32_t precision;    /* CNRF_PRECISION_* */
+  int32_t keep;         /* 1: fill `saved` for a later backward */
+} cnrf_flex_shape;
+typedef struct {   /* torch.nn.Linear layout [out][in]; state_dict order of models/model.py:31-46 */
+  const float *w_layer1, *b_layer1;
+  const float* w_xyz[CNRF_FLEX_MAX_XYZ_LAYERS];
+  const float* b_xyz[CNRF_FLEX_MAX_XYZ_LAYERS];
+  const float *w_feat, *b_feat, *w_dir, *b_dir, *w_alpha, *b_alpha, *w_rgb, *b_rgb;
+} cnrf_flex_params;
+typedef struct {   /* same shapes as the parameters; every buffer is fully overwritten */
+  float *w_layer1, *b_layer1;
+  float* w_xyz[CNRF_FLEX_MAX_XYZ_LAYERS];
+  float* b_xyz[CNRF_FLEX_MAX_XYZ_LAYERS];
+  float *w_feat, *b_feat, *w_dir, *b_dir, *w_alpha, *b_alpha, *w_rgb, *b_rgb;
+} cnrf_flex_grads;
+size_t cnrf_flexnerf_saved_bytes(const cnrf_flex_shape* s);
+size_t cnrf_flexnerf_workspace_bytes(const cnrf_flex_shape* s, int32_t backward);
+int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
+                      const float* x_dir, int64_t ld_dir, float* raw /*[M,4]*/, void* saved, size_t saved_bytes,
+                      void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+/* g_x_xyz [M, dim_xyz] / g_x_dir [N, dim_dir] (dense) may be NULL when the inputs carry no gradient. */
+int cnrf_flexnerf_bwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
+                      const float* x_dir, int64_t ld_dir, const float* g_raw /*[M,4]*/, const void* saved,
+                      size_t saved_bytes, const cnrf_flex_grads* g, float* g_x_xyz, float* g_x_dir, void* workspace,
+                      size_t workspace_bytes, cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Optimiser step (SURVEY section 8 "next" row f3): torch.optim.AdamW as train.py:111-114 runs it, every parameter tensor
  * of the step in one launch.  `tensors` is a HOST array; all pointers inside are device fp32 buffers of `numel` elements.
  * step >= 1 is the 1-based step count of that tensor (bias correction).  Arithmetic per element:

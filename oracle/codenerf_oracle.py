@@ -373,6 +373,47 @@ def flexible_nerf_mlp(p: Dict[str, Tensor], x: Tensor, dim_xyz: int, num_layers:
     return torch.cat((rgb, sigma), dim=-1)
 
 
+def flexible_nerf_shapes(num_layers: int, hidden: int, skip_connect_ids: Sequence[int], dim_xyz: int,
+                         dim_dir: int) -> Dict[str, Tuple[int, int]]:
+    """(out, in) of every Linear of FlexibleNeRFModel(use_viewdirs=True), in state_dict order.  models/model.py:31-46."""
+    shapes = {"layer1": (hidden, dim_xyz)}
+    for i in range(num_layers - 1):
+        shapes[f"layers_xyz.{i}"] = (hidden, hidden + dim_xyz) if i in skip_connect_ids else (hidden, hidden)
+    shapes["fc_feat"] = (hidden, hidden)
+    shapes["layers_dir.0"] = (hidden // 2, dim_dir + hidden)
+    shapes["fc_alpha"] = (1, hidden)
+    shapes["fc_rgb"] = (3, hidden // 2)
+    return shapes
+
+
+def make_flexible_nerf_params(seed: int, num_layers: int = 8, hidden: int = 256, skip_connect_ids: Sequence[int] = (4,),
+                              dim_xyz: int = 63, dim_dir: int = 27) -> Dict[str, Tensor]:
+    """Deterministic FlexibleNeRFModel parameters (numpy PCG64, torch.nn.Linear's default init range)."""
+    rng = np.random.default_rng(seed)
+    out: Dict[str, Tensor] = {}
+    for name, (o, i) in flexible_nerf_shapes(num_layers, hidden, skip_connect_ids, dim_xyz, dim_dir).items():
+        bound = 1.0 / math.sqrt(i)
+        out[name + ".weight"] = torch.from_numpy(rng.uniform(-bound, bound, size=(o, i)).astype(np.float32))
+        out[name + ".bias"] = torch.from_numpy(rng.uniform(-bound, bound, size=(o,)).astype(np.float32))
+    return out
+
+
+def flexible_forward_pass(p: Dict[str, Tensor], rd: Tensor, pts: Tensor, freqs_xyz: Tensor, freqs_dir: Tensor,
+                          num_layers: int, skip_connect_ids: Sequence[int], pairing: str = "reference") -> Tensor:
+    """forward_pass (nerf/__init__.py:116-134) around a FlexibleNeRFModel: same embedding and the same view-direction
+    tiling (F6); the latent codes are expanded and then ignored by the 3-line adapter SURVEY F11 describes."""
+    n, s = pts.shape[0], pts.shape[1]
+    emb = pos_embed(pts.reshape(-1, 3), freqs_xyz, True)
+    dim_xyz = emb.shape[-1]
+    viewdirs = rd / rd.norm(p=2, dim=-1).unsqueeze(-1)
+    if pairing == "reference":
+        dirs_flat = viewdirs.repeat([1, s, 1]).reshape(-1, 3)
+    else:
+        dirs_flat = viewdirs[:, None, :].expand(-1, s, -1).reshape(-1, 3)
+    emb = torch.cat((emb, pos_embed(dirs_flat, freqs_dir, True)), dim=-1)
+    return flexible_nerf_mlp(p, emb, dim_xyz, num_layers, skip_connect_ids).reshape(n, s, 4)
+
+
 def mse2psnr(mse_val: float) -> float:
     """utils/util.py:216-227."""
     if mse_val == 0:

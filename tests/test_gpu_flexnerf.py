@@ -1,0 +1,104 @@
+"""GPU parity of the vanilla NeRF field (FlexibleNeRFModel) through the drop-in class and the C ABI:
+against fixtures produced by the live reference (tests/golden/flexnerf.npz) and against the CPU oracle at lego.yml shapes."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import codenerf_oracle as orc
+
+pytestmark = pytest.mark.gpu
+T = torch.from_numpy
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available()
+    return torch.device("cuda", 0)
+
+
+def build(models, p, L, H, skips, dev):
+    m = models.FlexibleNeRFModel(L, H, list(skips), 10, 4, True, True, True)
+    m.load_state_dict({k: v.detach().clone() for k, v in p.items()})
+    return m.to(dev)
+
+
+@pytest.mark.parametrize("tag", ["small", "lego"])
+def test_flexible_model_golden(golden_dir, dev, tag):
+    """FlexibleNeRFModel.forward(x) on embedded inputs: outputs, input gradients and parameter gradients vs the reference."""
+    import view_synthesis.models as models
+    g = np.load(os.path.join(golden_dir, "flexnerf.npz"))
+    L, H, skips = int(g[f"{tag}_L"]), int(g[f"{tag}_H"]), tuple(int(v) for v in g[f"{tag}_skips"])
+    p = orc.make_flexible_nerf_params(31, L, H, skips)
+    assert list(p) == list(models.FlexibleNeRFModel(L, H, list(skips), 10, 4).state_dict())   # same names, same order
+    m = build(models, p, L, H, skips, dev)
+    x = T(g[f"{tag}_x"]).to(dev).requires_grad_(True)
+    y = m(x)
+    np.testing.assert_allclose(y.detach().cpu().numpy(), g[f"{tag}_y"], rtol=1e-4, atol=1e-4)     # fp32: 1e-3 gate
+    (y * T(g[f"{tag}_gy"]).to(dev)).sum().backward()
+    np.testing.assert_allclose(x.grad.cpu().numpy(), g[f"{tag}_gx"], rtol=1e-3, atol=1e-4)
+    for name, prm in m.named_parameters():
+        want = g[f"{tag}_g_{name}"]
+        np.testing.assert_allclose(prm.grad.cpu().numpy().reshape(-1)[::97], want, rtol=1e-3,
+                                   atol=1e-4 * max(1.0, float(np.abs(want).max())))
+        assert abs(float(prm.grad.double().sum()) - float(g[f"{tag}_gsum_{name}"])) < 1e-3 * max(1.0, float(prm.grad.abs().sum()))
+
+
+@pytest.mark.parametrize("tag", ["small", "lego"])
+def test_flexible_forward_pass_golden_pairing(golden_dir, dev, tag):
+    """forward_pass around the class reproduces the reference's view-direction tiling (F6) in both precisions."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    g = np.load(os.path.join(golden_dir, "flexnerf.npz"))
+    L, H, skips = int(g[f"{tag}_L"]), int(g[f"{tag}_H"]), tuple(int(v) for v in g[f"{tag}_skips"])
+    m = build(models, orc.make_flexible_nerf_params(31, L, H, skips), L, H, skips, dev)
+    emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+    rd, pts = T(g[f"{tag}_fp_rd"]).to(dev), T(g[f"{tag}_fp_pts"]).to(dev)
+    old = nerf.get_precision()
+    try:
+        for precision, tol in (("fp32", 1e-4), ("bf16", 2e-3)):
+            nerf.set_precision(precision)
+            with torch.no_grad():
+                raw = nerf.forward_pass(m, emb, rd, pts, (torch.zeros(5, 1, device=dev), torch.zeros(5, 1, device=dev)))
+            np.testing.assert_allclose(raw.cpu().numpy(), g[f"{tag}_fp_raw"], rtol=tol, atol=tol)
+    finally:
+        nerf.set_precision(old)
+
+
+@pytest.mark.parametrize("precision,N,S", [("fp32", 96, 64), ("bf16", 96, 64), ("bf16", 300, 192)])
+def test_flexible_field_vs_oracle_lego_shapes(dev, precision, N, S):
+    """lego.yml network (8 x 256, skip [4]) on N rays x S samples: field output and every gradient vs the CPU oracle."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    L, H, skips = 8, 256, (4,)
+    rng = np.random.default_rng(S)
+    p = orc.make_flexible_nerf_params(7, L, H, skips)
+    m = build(models, p, L, H, skips, dev)
+    emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+    rd_n = rng.normal(size=(N, 3)).astype(np.float32)
+    pts_n = rng.uniform(-1.5, 1.5, size=(N, S, 3)).astype(np.float32)
+    gy_n = rng.normal(size=(N, S, 4)).astype(np.float32)
+    old = nerf.get_precision()
+    nerf.set_precision(precision)
+    try:
+        rd, pts = T(rd_n).to(dev).requires_grad_(True), T(pts_n).to(dev).requires_grad_(True)
+        raw = nerf.forward_pass(m, emb, rd, pts, (None, None))
+        (raw * T(gy_n).to(dev)).sum().backward()
+    finally:
+        nerf.set_precision(old)
+    po = {k: v.clone().requires_grad_(True) for k, v in p.items()}
+    rd_o, pts_o = T(rd_n).requires_grad_(True), T(pts_n).requires_grad_(True)
+    raw_o = orc.flexible_forward_pass(po, rd_o, pts_o, orc.frequency_bands(10, True), orc.frequency_bands(4, True), L, skips)
+    (raw_o * T(gy_n)).sum().backward()
+    # fp32: the north-star 1e-3 gate.  bf16 (tensor-core GEMM toolkit, bf16 operand images): 3e-3 on the field output,
+    # gradients within 1e-2 of each tensor's largest entry (ten layers of bf16-rounded operands).
+    tol = 1e-3 if precision == "fp32" else 3e-3
+    gtol, grtol = (1e-3, 5e-3) if precision == "fp32" else (1e-2, 3e-2)
+    np.testing.assert_allclose(raw.detach().cpu().numpy(), raw_o.detach().numpy(), rtol=tol, atol=tol)
+    for (name, prm), (_, ref) in zip(m.named_parameters(), po.items()):
+        scale = max(1.0, float(ref.grad.abs().max()))
+        np.testing.assert_allclose(prm.grad.cpu().numpy(), ref.grad.numpy(), rtol=grtol, atol=gtol * scale, err_msg=name)
+    for got, ref in ((rd.grad, rd_o.grad), (pts.grad, pts_o.grad)):
+        scale = max(1.0, float(ref.abs().max()))
+        np.testing.assert_allclose(got.cpu().numpy(), ref.numpy(), rtol=grtol, atol=gtol * scale)

@@ -143,3 +143,22 @@ def test_render_split(golden_dir):
     for num_rays, n_gpus, per, pad in g["cases"]:
         p, q = orc.render_split_np(int(num_rays), int(n_gpus))
         assert p.tolist() == list(per) and q.tolist() == list(pad)
+
+
+def test_flexible_nerf_model(golden_dir):
+    """a15: oracle restatement of FlexibleNeRFModel (models/model.py:51-74) and of forward_pass around it, against
+    outputs of the live reference class (oracle/make_golden_flex.py)."""
+    g = load(golden_dir, "flexnerf.npz")
+    for tag in ("small", "lego"):
+        L, H, skips = int(g[f"{tag}_L"]), int(g[f"{tag}_H"]), tuple(int(v) for v in g[f"{tag}_skips"])
+        p = {k: v.requires_grad_(True) for k, v in orc.make_flexible_nerf_params(31, L, H, skips).items()}
+        x = T(g[f"{tag}_x"]).requires_grad_(True)
+        y = orc.flexible_nerf_mlp(p, x, 63, L, skips)
+        close(y, g[f"{tag}_y"], 2e-5)
+        (y * T(g[f"{tag}_gy"])).sum().backward()
+        close(x.grad, g[f"{tag}_gx"], 2e-5)
+        for name, prm in p.items():
+            np.testing.assert_allclose(prm.grad.numpy().reshape(-1)[::97], g[f"{tag}_g_{name}"], rtol=1e-4, atol=2e-5)
+        raw = orc.flexible_forward_pass({k: v.detach() for k, v in p.items()}, T(g[f"{tag}_fp_rd"]), T(g[f"{tag}_fp_pts"]),
+                                        orc.frequency_bands(10, True), orc.frequency_bands(4, True), L, skips)
+        close(raw, g[f"{tag}_fp_raw"], 2e-5)
