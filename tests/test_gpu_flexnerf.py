@@ -101,4 +101,13 @@ def test_flexible_field_vs_oracle_lego_shapes(dev, precision, N, S):
         np.testing.assert_allclose(prm.grad.cpu().numpy(), ref.grad.numpy(), rtol=grtol, atol=gtol * scale, err_msg=name)
     for got, ref in ((rd.grad, rd_o.grad), (pts.grad, pts_o.grad)):
         scale = max(1.0, float(ref.abs().max()))
-        np.testing.assert_allclose(got.cpu().numpy(), ref.numpy(), rtol=grtol, atol=gtol * scale)
+        got = got.cpu()
+        if precision == "fp32":
+            np.testing.assert_allclose(got.numpy(), ref.numpy(), rtol=grtol, atol=gtol * scale)
+        else:
+            # input gradients weight encoding terms by frequencies up to 512: a ReLU whose pre-activation rounds across 0 in
+            # bf16 moves single entries visibly; the tensor as a whole must still agree (same criterion as the CodeNeRF
+            # pose-gradient test, tests/test_gpu_tc.py::test_tc_pose_gradients_match_fp32)
+            bad = ((got - ref).abs() > gtol * scale + grtol * ref.abs()).float().mean()
+            cos = torch.nn.functional.cosine_similarity(got.flatten(), ref.flatten(), dim=0)
+            assert float(bad) < 2e-3 and float(cos) > 0.999, (float(bad), float(cos))
