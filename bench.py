@@ -321,6 +321,18 @@ def run_ours(args):
                 "gpu_launches": roof.pop("launches_per_step"), "roofline": roof,
                 "model_flops_per_ray": FLOP_PER_RAY_TRAIN,
                 "achieved_tflops_whole_step": value * FLOP_PER_RAY_TRAIN / 1e12 / world}
+        if world == 1:
+            # standalone rooflines of the HBM-bound stages (north_star: compositing / sampling vs the HBM peak): one launch
+            # per repetition over 524,288 rays (working sets > L2), CUDA events, algorithmic bytes of SURVEY section 8(d)
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("time_hbm_kernels", os.path.join(ROOT, "scripts", "time_hbm_kernels.py"))
+            thk = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(thk)
+            line["hbm_kernels"] = [{k: (round(r[k], 4) if isinstance(r[k], float) else r[k]) for k in
+                                    ("kernel", "rays", "bytes_per_ray", "ms", "GBps", "frac")}
+                                   for r in thk.measure(524288, 10, dev, verbose=False)]
+            line["hbm_kernels_peak"] = {"GBps": thk.hbm_peak()[0], "source": thk.hbm_peak()[1]}
+            torch.cuda.empty_cache()
         if world == 1 and not args.no_cpu_baseline:
             rps, threads, sec = cpu_reference_rays_per_s(args.cpu_sample_rays, 2, 1)
             line["cpu_baseline"] = {"value": rps, "unit": "rays/s", "cores": threads, "kind": "port",

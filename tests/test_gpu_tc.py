@@ -271,7 +271,8 @@ torch.save({"raw": raw.detach().cpu(), "g": zs.grad.cpu(), "w": m.layer_xyz2.wei
             subprocess.run([sys.executable, "-c", code, path], check=True, env=env, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
             out[mode] = torch.load(path)
     assert torch.equal(out["0"]["raw"], out["1"]["raw"])
-    assert torch.equal(out["0"]["g"], out["1"]["g"])
+    # code gradients pass through red.global.add partial sums (weight-gradient kernel reducers): equal up to summation order
+    assert torch.allclose(out["0"]["g"], out["1"]["g"], rtol=1e-4, atol=1e-5 * float(out["0"]["g"].abs().max()))
     assert torch.allclose(out["0"]["w"], out["1"]["w"], rtol=1e-4, atol=1e-5)     # atomics: summation order
 
 
