@@ -199,8 +199,10 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   }
   const int a_mn = b.a_mn[p], b_mn = b.b_mn[p];
   const int local = blockIdx.x - b.first[p];
-  const int mx = local % b.mt[p], rest = local / b.mt[p];
-  const int ny = rest % b.nt[p], kz = rest / b.nt[p];
+  // column tiles fastest: the (up to 5) CTAs that share a 128-row A tile are neighbours in the grid, so for the per-SAMPLE
+  // layers of the vanilla field (M = millions of rows, flexnerf.cu) A comes from HBM once and from L2 afterwards
+  const int ny = local % b.nt[p], rest = local / b.nt[p];
+  const int mx = rest % b.mt[p], kz = rest / b.mt[p];
   const int64_t m0 = (int64_t)mx * GBM;
   const int64_t n0 = (int64_t)ny * GBN;
   const int64_t kbeg = (int64_t)kz * b.kslice[p];
