@@ -13,6 +13,17 @@ from . import _lib
 from ._lib import FieldShape, FlexPtrs, FlexShape, PtrTable, check
 
 _f32 = torch.float32
+# Grad mode of the CALLER: inside Function.forward autograd is always off, and ctx.needs_input_grad ignores no_grad, so the
+# public wrappers record torch.is_grad_enabled() here before .apply (a no_grad render must not write backward images).
+_OUTER_GRAD = [True]
+
+
+def _apply(fn, *args):
+    _OUTER_GRAD[0] = torch.is_grad_enabled()
+    try:
+        return fn.apply(*args)
+    finally:
+        _OUTER_GRAD[0] = True
 
 
 def _stream():
@@ -280,7 +291,7 @@ class _Field(torch.autograd.Function):
         z_t, ld_zt = _rows(z_t)
         params = tuple(_c(p) for p in params)
         N, S = pts.shape[0], pts.shape[1]
-        keep = int(any(ctx.needs_input_grad))
+        keep = int(_OUTER_GRAD[0] and any(ctx.needs_input_grad))   # under no_grad (rendering) nothing is saved
         shp = _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, keep)
         saved = _bytes(lib.cnrf_codenerf_saved_bytes(C.byref(shp)), pts.device)
         ws_bytes = lib.cnrf_field_workspace_bytes(C.byref(shp), 0)
@@ -338,7 +349,7 @@ class _FieldIds(torch.autograd.Function):
         N, S = pts.shape[0], pts.shape[1]
         assert ids.dtype == torch.int64 and ids.shape == (N,), "ids must be (N,) int64"
         assert tab_s.shape[0] == tab_t.shape[0], "shape and texture tables must have the same number of rows"
-        keep = int(any(ctx.needs_input_grad))
+        keep = int(_OUTER_GRAD[0] and any(ctx.needs_input_grad))   # under no_grad (rendering) nothing is saved
         shp = _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, keep)
         saved = _bytes(lib.cnrf_codenerf_saved_bytes(C.byref(shp)), pts.device)
         ws = _bytes(lib.cnrf_field_workspace_bytes(C.byref(shp), 0), pts.device)
@@ -395,8 +406,8 @@ def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code
     if code_source is not None and precision == _lib.PRECISION_BF16:
         ids, tab_s, tab_t = code_source
         if ids.dim() == 1 and ids.shape[0] == pts.shape[0] and ids.dtype == torch.int64:
-            return _FieldIds.apply(cfg, pts, rd, ids, tab_s, tab_t, freqs_xyz, freqs_dir, *params)
-    return _Field.apply(cfg, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, *params)
+            return _apply(_FieldIds, cfg, pts, rd, ids, tab_s, tab_t, freqs_xyz, freqs_dir, *params)
+    return _apply(_Field, cfg, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, *params)
 
 
 class _Model(torch.autograd.Function):
@@ -412,7 +423,7 @@ class _Model(torch.autograd.Function):
         z_t, ld_zt = _rows(z_t)
         params = tuple(_c(p) for p in params)
         M = x.shape[0]
-        keep = int(any(ctx.needs_input_grad))
+        keep = int(_OUTER_GRAD[0] and any(ctx.needs_input_grad))   # under no_grad (rendering) nothing is saved
         shp = _shape(hidden, code, dim_xyz, dim_dir, M, 1, _lib.PAIRING_CORRECT, precision, keep)
         saved = _bytes(lib.cnrf_codenerf_saved_bytes(C.byref(shp)), x.device)
         ws = _bytes(lib.cnrf_codenerf_workspace_bytes(C.byref(shp), 0), x.device)
@@ -457,7 +468,7 @@ class _Model(torch.autograd.Function):
 
 def codenerf_model(params, z_s, z_t, x, hidden, code, dim_xyz, dim_dir, precision=_lib.PRECISION_FP32):
     cfg = (hidden, code, dim_xyz, dim_dir, precision)
-    return _Model.apply(cfg, z_s, z_t, x, *params)
+    return _apply(_Model, cfg, z_s, z_t, x, *params)
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -494,7 +505,7 @@ class _FlexNerf(torch.autograd.Function):
         params = tuple(_c(p) for p in params)
         M, N = x_xyz.shape[0], x_dir.shape[0]
         assert M == N * S, "FlexibleNeRF field: rows of x_xyz must be rays x samples"
-        keep = int(any(ctx.needs_input_grad))
+        keep = int(_OUTER_GRAD[0] and any(ctx.needs_input_grad))   # under no_grad (rendering) nothing is saved
         shp = FlexShape(num_layers, hidden, dim_xyz, dim_dir, skip_mask, N, S, pairing, precision, keep)
         dev = x_xyz.device
         saved = _bytes(lib.cnrf_flexnerf_saved_bytes(C.byref(shp)), dev)
@@ -535,4 +546,4 @@ def flexnerf(params, x_xyz, x_dir, num_layers, hidden, dim_xyz, dim_dir, skip_ma
              pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_FP32):
     cfg = (int(num_layers), int(hidden), int(dim_xyz), int(dim_dir), int(skip_mask), int(num_samples), int(pairing),
            int(precision))
-    return _FlexNerf.apply(cfg, x_xyz, x_dir, *params)
+    return _apply(_FlexNerf, cfg, x_xyz, x_dir, *params)

@@ -1,0 +1,334 @@
+// Fused tcgen05 forward chain of the vanilla NeRF field (FlexibleNeRFModel, view_synthesis/models/model.py:51-74) for
+// inference: config/lego.yml's full-image render is forward-only, 640,000 rays x 256 samples per frame.
+//
+// One persistent CTA per SM takes 128-sample tiles through ALL layers without leaving the SM:
+//   smem  : five activation slabs [128 x 64] bf16 (128-byte swizzle): slabs 0-3 = the 256 hidden features, overwritten in
+//           place layer by layer; slab 4 = gamma(x) (63 columns + a zero), kept for the skip layer, whose K is simply five
+//           slabs instead of four -- cat(h, xyz) (models/model.py:63) never exists.  A ring of three 32 KB weight slabs
+//           ([256 out x 64 in] bf16, pre-swizzled in global memory by pack_flex_weights_kernel, so one slab is ONE 1-D TMA
+//           bulk copy) runs ahead of the MMAs across layers and tiles.
+//   TMEM  : one [128 x 256] fp32 accumulator.
+//   warps : 0-7 epilogue (tcgen05.ld -> + bias -> ReLU -> bf16 -> swizzled smem = next layer's A operand), 8 = TMA
+//           producer, 9 = MMA issuer (elect.sync lane, M128 N256 K16).
+// Heads: fc_alpha rides in the layers_dir[0] GEMM as output row 128 (N = 144), so sigma costs nothing; the view-direction
+// half of layers_dir[0] arrives as a per-ray fp32 bias row (pairing as nerf/__init__.py:127); fc_rgb (128 -> 3) is a
+// CUDA-core dot product in that layer's epilogue.  bf16 operands / fp32 accumulation, like the CodeNeRF chain.
+#include <algorithm>
+#include "common.cuh"
+#include "internal.h"
+#include "tc_common.cuh"
+
+using namespace tc;
+
+namespace {
+constexpr int FT_ROWS = 128, FT_THREADS = 320, FT_EPI_WARPS = 8;
+constexpr int SLAB_A = FT_ROWS * 128;          // 16 KB activation slab
+constexpr int SLAB_W = 256 * 128;              // 32 KB weight slab (N = 256)
+constexpr int SLAB_WD = 144 * 128;             // 18 KB weight slab of the direction layer (N = 128 + sigma row, padded to 144)
+constexpr int RING = 3;
+constexpr int FT_MAX_LAYERS = 18;
+constexpr int FT_SMEM = 5 * SLAB_A + RING * SLAB_W + FT_MAX_LAYERS * 256 * 4 /*biases*/ + 3 * 128 * 4 /*w_rgb*/ +
+                        128 * 4 * 4 /*rgb partials*/ + 256 /*barriers*/ + 1024 /*alignment*/;
+
+struct FlexLayer {
+  uint32_t wofs;      // byte offset of the layer's first weight slab in the packed image
+  int16_t kslabs;     // K slabs of 64
+  int16_t a_first;    // first activation slab: 0 (hidden) or 4 (layer1 reads gamma(x))
+  int16_t skip;       // 1: the last K slab is gamma(x) (slab 4)
+  int16_t n_out;      // 256, or 144 for the direction layer
+};
+struct FlexFwdArgs {
+  FlexLayer layer[FT_MAX_LAYERS];
+  int nlayers;                       // layer1, layers_xyz..., fc_feat, layers_dir[0]
+  const uint8_t* packed;
+  const float* bias[FT_MAX_LAYERS];  // fp32 [256] (unused for the direction layer: its bias is inside betad)
+  const float* x_xyz; int64_t ld_xyz; int dx;
+  const float* betad;                // [N, 128] per-ray: Wdir[:, H:] gamma(d) + b_dir
+  const float* w_rgb; const float* b_rgb; const float* b_alpha;
+  float* raw;                        // [M, 4]
+  int64_t M, N; int S, pairing;
+  int* err;
+};
+
+struct PackJob { const float* w; int ldw; int rows; int k0; int kcols; uint32_t ofs; int nrows_slab; };
+struct PackArgs { PackJob job[FT_MAX_LAYERS * 5 + 4]; int count; uint8_t* out; };
+
+// one block per slab: element (n, kk) of the slab <- W[n][k0 + kk] (0 outside), bf16, 128-byte swizzled
+__global__ void pack_flex_weights_kernel(const __grid_constant__ PackArgs a) {
+  const PackJob& j = a.job[blockIdx.x];
+  uint8_t* dst = a.out + j.ofs;
+  for (int i = threadIdx.x; i < j.nrows_slab * 8; i += blockDim.x) {       // 16-byte chunks
+    const int n = i >> 3, c = i & 7;
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int kk = c * 8 + e;
+      v[e] = (n < j.rows && kk < j.kcols) ? __ldg(j.w + (int64_t)n * j.ldw + j.k0 + kk) : 0.f;
+    }
+    const uint4 p = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+    *reinterpret_cast<uint4*>(dst + n * 128 + ((c ^ (n & 7)) << 4)) = p;
+  }
+}
+
+__device__ __forceinline__ void epi_arrive(uint64_t* bar, int lane) {
+  fence_proxy_async();            // generic-proxy smem writes -> visible to the tensor core's async proxy
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(bar);
+}
+
+__global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid_constant__ FlexFwdArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* act = smem;                                     // 5 slabs
+  uint8_t* ring = smem + 5 * SLAB_A;                       // RING x 32 KB
+  float* bias_sm = reinterpret_cast<float*>(ring + RING * SLAB_W);
+  float* wrgb_sm = bias_sm + FT_MAX_LAYERS * 256;
+  float* part_sm = wrgb_sm + 3 * 128;                      // [128][4]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(part_sm + 128 * 4);
+  uint64_t *full = bars, *empty = bars + RING, *acc_bar = bars + 2 * RING, *act_bar = bars + 2 * RING + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RING + 2);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int i = 0; i < RING; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(acc_bar, 1);
+    mbar_init(act_bar, FT_EPI_WARPS);
+    mbar_fence_init();
+  }
+  for (int i = tid; i < a.nlayers * 256; i += FT_THREADS) {
+    const int l = i >> 8;
+    bias_sm[i] = a.bias[l] ? __ldg(a.bias[l] + (i & 255)) : 0.f;
+  }
+  for (int i = tid; i < 3 * 128; i += FT_THREADS) wrgb_sm[i] = __ldg(a.w_rgb + i);
+  if (warp == 9) tmem_alloc(tmem_slot, 256);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const int64_t ntiles = (a.M + FT_ROWS - 1) / FT_ROWS;
+  bool ok = true;
+
+  if (warp == 8) {
+    // ---- TMA producer: the global sequence of weight slabs (tile-major, layer, K slab) through the ring
+    uint32_t s = 0;
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+      for (int l = 0; l < a.nlayers && ok; ++l) {
+        const FlexLayer L = a.layer[l];
+        const uint32_t bytes = L.n_out == 256 ? SLAB_W : SLAB_WD;
+        for (int j = 0; j < L.kslabs && ok; ++j, ++s) {
+          const uint32_t slot = s % RING, ph = (s / RING) & 1;
+          ok = mbar_wait(&empty[slot], ph ^ 1, a.err);
+          if (ok && elect_one()) {
+            mbar_arrive_expect_tx(&full[slot], bytes);
+            bulk_g2s(ring + slot * SLAB_W, a.packed + L.wofs + (size_t)j * bytes, bytes, &full[slot]);
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else if (warp == 9) {
+    // ---- MMA issuer
+    uint32_t s = 0, act_ph = 0;
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+      for (int l = 0; l < a.nlayers && ok; ++l) {
+        const FlexLayer L = a.layer[l];
+        const uint32_t idesc = idesc_bf16(FT_ROWS, L.n_out, 0, 0);
+        ok = mbar_wait(act_bar, act_ph, a.err);            // this layer's A operand is in shared memory
+        act_ph ^= 1;
+        tc_fence_after();
+        for (int j = 0; j < L.kslabs && ok; ++j, ++s) {
+          const uint32_t slot = s % RING, ph = (s / RING) & 1;
+          ok = mbar_wait(&full[slot], ph, a.err);
+          tc_fence_after();
+          const int aslab = (L.skip && j == L.kslabs - 1) ? 4 : L.a_first + j;
+          const uint32_t pa = smem_u32(act + aslab * SLAB_A), pb = smem_u32(ring + slot * SLAB_W);
+          if (ok && elect_one()) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_bf16(tmem, smem_desc(pa + k * 32, 16, 1024, SWIZZLE_128B), smem_desc(pb + k * 32, 16, 1024, SWIZZLE_128B),
+                        idesc, (j > 0 || k > 0) ? 1u : 0u);
+            umma_commit(&empty[slot]);                      // the slot is free once these MMAs have read it
+          }
+          __syncwarp();
+        }
+        if (ok && elect_one()) umma_commit(acc_bar);
+        __syncwarp();
+      }
+    }
+  } else {
+    // ---- epilogue warps: warp w owns TMEM lanes / rows 32 (w & 3) .. +31 and column half w >> 2
+    const int q = warp & 3, h = warp >> 2;
+    const int row = q * 32 + lane;
+    uint32_t acc_ph = 0;
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+      const int64_t m = t * FT_ROWS + row;
+      // gamma(x) -> slab 4: this thread converts columns [32 h, 32 h + 32) of its row
+      {
+        const float* xr = a.x_xyz + (m < a.M ? m : 0) * a.ld_xyz;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          float v[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int col = h * 32 + c * 8 + e;
+            v[e] = (m < a.M && col < a.dx) ? __ldg(xr + col) : 0.f;
+          }
+          const uint4 p = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
+          *reinterpret_cast<uint4*>(act + 4 * SLAB_A + row * 128 + (((h * 4 + c) ^ (row & 7)) << 4)) = p;
+        }
+      }
+      epi_arrive(act_bar, lane);
+      for (int l = 0; l < a.nlayers && ok; ++l) {
+        ok = mbar_wait(acc_bar, acc_ph, a.err);
+        acc_ph ^= 1;
+        tc_fence_after();
+        if (!ok) break;
+        if (l + 1 < a.nlayers) {
+          // hidden layer: 128 columns of this warp's half, 32 at a time -> bias, ReLU, bf16, slab (col >> 6)
+          const float* b = bias_sm + l * 256;
+#pragma unroll 1
+          for (int cb = 0; cb < 4; ++cb) {
+            const int col0 = h * 128 + cb * 32;
+            uint32_t v[32];
+            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + col0, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              float x[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) x[e] = fmaxf(__uint_as_float(v[c * 8 + e]) + b[col0 + c * 8 + e], 0.f);
+              const uint4 p = make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]), pack_bf16(x[6], x[7]));
+              const int col = col0 + c * 8;
+              *reinterpret_cast<uint4*>(act + (col >> 6) * SLAB_A + row * 128 + ((((col & 63) >> 3) ^ (row & 7)) << 4)) = p;
+            }
+          }
+          epi_arrive(act_bar, lane);
+        } else {
+          // direction layer: columns [64 h, 64 h + 64) -> + betad[ray] -> ReLU -> fc_rgb partial sums; column 128 = sigma
+          const int64_t ray = a.pairing == CNRF_PAIRING_REFERENCE ? (m % a.N) : (m / a.S);
+          const float* bd = a.betad + (m < a.M ? ray : 0) * 128 + h * 64;
+          float r = 0.f, g = 0.f, bl = 0.f;
+#pragma unroll 1
+          for (int cb = 0; cb < 2; ++cb) {
+            uint32_t v[32];
+            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + h * 64 + cb * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int e = 0; e < 32; e += 4) {
+              const float4 bb = __ldg(reinterpret_cast<const float4*>(bd + cb * 32 + e));
+              const float add[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int n = h * 64 + cb * 32 + e + i;
+                const float x = fmaxf(__uint_as_float(v[e + i]) + add[i], 0.f);
+                r = fmaf(x, wrgb_sm[n], r); g = fmaf(x, wrgb_sm[128 + n], g); bl = fmaf(x, wrgb_sm[256 + n], bl);
+              }
+            }
+          }
+          float sigma = 0.f;
+          if (h == 0) {
+            uint32_t v[32];
+            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + 128, v);
+            tmem_ld_wait();
+            sigma = __uint_as_float(v[0]) + __ldg(a.b_alpha);
+          } else {
+            part_sm[row * 4 + 0] = r; part_sm[row * 4 + 1] = g; part_sm[row * 4 + 2] = bl;
+          }
+          tc_fence_before();
+          asm volatile("bar.sync 1, 256;" ::: "memory");     // the eight epilogue warps only
+          if (h == 0 && m < a.M) {
+            const float4 o = make_float4(r + part_sm[row * 4 + 0] + __ldg(a.b_rgb), g + part_sm[row * 4 + 1] + __ldg(a.b_rgb + 1),
+                                         bl + part_sm[row * 4 + 2] + __ldg(a.b_rgb + 2), sigma);
+            *reinterpret_cast<float4*>(a.raw + m * 4) = o;     // raw = [rgb | sigma]  (models/model.py:73)
+          }
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) tmem_dealloc(tmem, 256);
+}
+
+__device__ int g_flex_tc_error = 0;
+}  // namespace
+
+// 1 if the fused vanilla-field kernel hit a bounded barrier-wait timeout (folded into cnrf_debug_tc_error)
+int cnrf_flex_fused_error() {
+  int v = 0;
+  cudaMemcpyFromSymbol(&v, g_flex_tc_error, sizeof(int));
+  return v;
+}
+
+size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers) {
+  return (size_t)SLAB_W * (1 + 5 * (size_t)num_xyz_layers + 4) + (size_t)SLAB_WD * 4 + 1024;
+}
+
+bool cnrf_flex_fused_eligible(const cnrf_flex_shape* s) {
+  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->hidden == 256 && s->dim_xyz <= 64 && s->num_layers + 1 <= FT_MAX_LAYERS;
+}
+
+// betad: [N,128] fp32 already computed; packed: cnrf_flex_fused_packed_bytes() of 1024-byte aligned workspace
+int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
+                        const float* betad, float* raw, uint8_t* packed, cudaStream_t st) {
+  const int H = 256, L = s->num_layers - 1, dx = s->dim_xyz, dd = s->dim_dir;
+  FlexFwdArgs a = {};
+  PackArgs pk = {};
+  pk.out = packed;
+  uint32_t ofs = 0;
+  auto add_job = [&](const float* w, int ldw, int rows, int k0, int kcols, int nrows_slab) {
+    PackJob& j = pk.job[pk.count++];
+    j.w = w; j.ldw = ldw; j.rows = rows; j.k0 = k0; j.kcols = kcols; j.ofs = ofs; j.nrows_slab = nrows_slab;
+    ofs += (uint32_t)nrows_slab * 128;
+  };
+  int nl = 0;
+  a.layer[nl] = {ofs, 1, 4, 0, 256}; a.bias[nl] = p->b_layer1; ++nl;                       // layer1: A = gamma(x)
+  add_job(p->w_layer1, dx, H, 0, dx, 256);
+  for (int i = 0; i < L; ++i) {
+    const bool skip = (s->skip_mask >> i) & 1u;
+    const int K = skip ? H + dx : H;
+    a.layer[nl] = {ofs, (int16_t)(skip ? 5 : 4), 0, (int16_t)skip, 256}; a.bias[nl] = p->b_xyz[i]; ++nl;
+    for (int j = 0; j < 4; ++j) add_job(p->w_xyz[i], K, H, 64 * j, 64, 256);
+    if (skip) add_job(p->w_xyz[i], K, H, H, dx, 256);
+  }
+  a.layer[nl] = {ofs, 4, 0, 0, 256}; a.bias[nl] = p->b_feat; ++nl;
+  for (int j = 0; j < 4; ++j) add_job(p->w_feat, H, H, 64 * j, 64, 256);
+  a.layer[nl] = {ofs, 4, 0, 0, 144}; a.bias[nl] = nullptr; ++nl;                            // layers_dir[0] (+ fc_alpha row)
+  const uint32_t dir_ofs = ofs;
+  for (int j = 0; j < 4; ++j) add_job(p->w_dir, H + dd, 128, 64 * j, 64, 144);
+  a.nlayers = nl;
+  pack_flex_weights_kernel<<<pk.count, 256, 0, st>>>(pk);
+  CNRF_LAUNCH_CHECK();
+  {   // fc_alpha as output row 128 of every direction-layer slab
+    PackArgs pa = {};
+    pa.out = packed;
+    for (int j = 0; j < 4; ++j) {
+      PackJob& jb = pa.job[pa.count++];
+      jb.w = p->w_alpha; jb.ldw = H; jb.rows = 1; jb.k0 = 64 * j; jb.kcols = 64; jb.ofs = dir_ofs + j * SLAB_WD + 128 * 128;
+      jb.nrows_slab = 1;
+    }
+    pack_flex_weights_kernel<<<pa.count, 32, 0, st>>>(pa);
+    CNRF_LAUNCH_CHECK();
+  }
+  a.packed = packed;
+  a.x_xyz = x_xyz; a.ld_xyz = ld_xyz; a.dx = dx;
+  a.betad = betad; a.w_rgb = p->w_rgb; a.b_rgb = p->b_rgb; a.b_alpha = p->b_alpha;
+  a.raw = raw; a.M = s->num_rays * (int64_t)s->num_samples; a.N = s->num_rays; a.S = s->num_samples; a.pairing = s->pairing;
+  cudaGetSymbolAddress(reinterpret_cast<void**>(&a.err), g_flex_tc_error);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(flex_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int64_t ntiles = (a.M + FT_ROWS - 1) / FT_ROWS;
+  const int grid = (int)std::min<int64_t>(ntiles, sms);
+  flex_fwd_tc_kernel<<<grid, FT_THREADS, FT_SMEM, st>>>(a);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}

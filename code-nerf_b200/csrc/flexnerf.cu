@@ -8,6 +8,7 @@
 // skip layer is written straight into the left part of a [M, H + dim_xyz] buffer whose right part holds gamma(x), so
 // cat(h, xyz) (models/model.py:63) never runs as a copy of h.
 #include <algorithm>
+#include <stdlib.h>
 #include "common.cuh"
 #include "internal.h"
 
@@ -137,6 +138,8 @@ extern "C" size_t cnrf_flexnerf_workspace_bytes(const cnrf_flex_shape* s, int32_
   if (dims_of(s, d) != CNRF_OK) return 0;
   const size_t betad = al(d.N * (d.H / 2));
   // inference: two ping-pong activation buffers wide enough for a skip input, + feat + v live in the workspace
+  if (!backward && cnrf_flex_fused_eligible(s))            // fused chain: betad + the packed bf16 weight image only
+    return betad + 1024 + cnrf_flex_fused_packed_bytes(d.L);
   if (!backward) return betad + (s->keep ? 0 : 2 * al(d.M * (d.H + d.dx)) + al(d.M * d.H) + al(d.M * (d.H / 2)));
   // backward: two ping-pong [M,H] gradient buffers, d v [M,H/2], d betad [N,H/2], ones [M]
   return 2 * al(d.M * d.H) + al(d.M * (d.H / 2)) + betad + al(d.M);
@@ -165,6 +168,15 @@ extern "C" int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_param
   const int H = d.H, H2 = d.H / 2;
   Arena ws(workspace, workspace_bytes);
   float* betad = ws.take(d.N * H2);
+  static const bool no_fused = getenv("CNRF_FLEX_NO_FUSED") != nullptr;      // A/B switch: per-layer toolkit GEMMs
+  if (cnrf_flex_fused_eligible(s) && !no_fused) {
+    // inference in bf16: the whole per-sample chain is ONE persistent tcgen05 kernel (flex_fwd_tc.cu)
+    float* pk = ws.take((cnrf_flex_fused_packed_bytes(d.L) + 1024) / sizeof(float));
+    CNRF_REQUIRE(ws.ok, CNRF_E_WORKSPACE);
+    uint8_t* packed = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(pk) + 1023) & ~uintptr_t(1023));
+    RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->w_dir + H, H + d.dd, H2, betad, H2, p->b_dir, 0, 1, INT64_MAX, 0, st));
+    return cnrf_flex_fused_fwd(s, p, x_xyz, ld_xyz, betad, raw, packed, st);
+  }
   Saved sv;
   if (s->keep) {
     CNRF_REQUIRE(saved, CNRF_E_NULL);
