@@ -70,6 +70,13 @@ __global__ void pack_flex_weights_kernel(const __grid_constant__ PackArgs a) {
   }
 }
 
+// bf16x2 of (max(lo, 0), max(hi, 0)), `lo` in the low half: one F2FP with the .relu modifier
+__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
+
 __device__ __forceinline__ void epi_arrive(uint64_t* bar, int lane) {
   fence_proxy_async();            // generic-proxy smem writes -> visible to the tensor core's async proxy
   tc_fence_before();
@@ -186,20 +193,26 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
         if (!ok) break;
         if (l + 1 < a.nlayers) {
           // hidden layer: 128 columns of this warp's half, 32 at a time -> bias, ReLU, bf16, slab (col >> 6)
-          const float* b = bias_sm + l * 256;
-#pragma unroll 1
+          const float* b = bias_sm + l * 256 + h * 128;
+          const uint32_t t0 = tmem + ((uint32_t)(q * 32) << 16) + h * 128;
+          uint32_t v[2][32];
+          tmem_ld32(t0, v[0]);
+#pragma unroll
           for (int cb = 0; cb < 4; ++cb) {
-            const int col0 = h * 128 + cb * 32;
-            uint32_t v[32];
-            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + col0, v);
             tmem_ld_wait();
+            if (cb + 1 < 4) tmem_ld32(t0 + (cb + 1) * 32, v[(cb + 1) & 1]);      // next block in flight under this one
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
+              const float4 b0 = *reinterpret_cast<const float4*>(b + cb * 32 + c * 8);       // warp-uniform: LDS broadcast
+              const float4 b1 = *reinterpret_cast<const float4*>(b + cb * 32 + c * 8 + 4);
+              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
               float x[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) x[e] = fmaxf(__uint_as_float(v[c * 8 + e]) + b[col0 + c * 8 + e], 0.f);
-              const uint4 p = make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]), pack_bf16(x[6], x[7]));
-              const int col = col0 + c * 8;
+              for (int e = 0; e < 8; ++e) x[e] = __uint_as_float(v[cb & 1][c * 8 + e]) + bb[e];
+              // ReLU rides in the conversion (cvt.rn.relu.bf16x2.f32): no FMNMX per element
+              const uint4 p = make_uint4(pack_bf16_relu(x[0], x[1]), pack_bf16_relu(x[2], x[3]), pack_bf16_relu(x[4], x[5]),
+                                         pack_bf16_relu(x[6], x[7]));
+              const int col = h * 128 + cb * 32 + c * 8;
               *reinterpret_cast<uint4*>(act + (col >> 6) * SLAB_A + row * 128 + ((((col & 63) >> 3) ^ (row & 7)) << 4)) = p;
             }
           }
