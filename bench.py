@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--precision", default=os.environ.get("CODENERF_PRECISION", "bf16"), choices=["bf16", "fp32"])
     ap.add_argument("--cpu-sample-rays", type=int, default=1024)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ddp", action="store_true", help="N > 1: wrap the modules in DistributedDataParallel as "
+                    "utils/util.py:139-142 does, instead of codenerf_b200.parallel.GradAllReduce")
     return ap.parse_args()
 
 
@@ -176,7 +178,10 @@ def workload_config(precision):
                         "samples, CodeNeRF hidden 256 / codes 256, PE L=10/4, per chunk: embedding lookup + render fwd + "
                         "2 MSE + backward + AdamW step",
             "rays_per_step_per_gpu": c["B"] * c["rays_per_image"], "chunk": c["chunk"], "mlp_precision": precision,
-            "pairing": "reference", "parallelism": "ddp over rays",
+            "pairing": "reference",
+            "parallelism": "data-parallel over rays; per chunk step one flat NCCL all-reduce (mean) of all MLP and code-table "
+                           "gradients (codenerf_b200.parallel.GradAllReduce; --ddp = DistributedDataParallel wrappers as "
+                           "utils/util.py:139-142)",
             "optimizer": "AdamW (lr 1e-4, embeddings 1e-3; train.py:111-114) via codenerf_b200.optim.FusedAdamW, one launch",
             "loss_read": "summed fine loss of the step's 4 chunks, one device->host read per step (e2e leg)",
             "l2": "activations written/read per chunk (>1 GB) exceed the 126 MB L2; no explicit flush"}
@@ -207,9 +212,15 @@ def run_ours(args):
     mods = {"embedding": models.ShapeTextureEmbedding(c["num_objects"], c["code"], c["code"]).to(dev),
             "nerf_coarse": models.CodeNeRFModel(c["hidden"], c["num_objects"], c["code"], c["code"], c["Lx"], c["Ld"]).to(dev),
             "nerf_fine": models.CodeNeRFModel(c["hidden"], c["num_objects"], c["code"], c["code"], c["Lx"], c["Ld"]).to(dev)}
-    if world > 1:                                                         # utils/util.py:139-142
+    sync = None
+    if world > 1 and args.ddp:                                            # utils/util.py:139-142, as the reference wraps them
         from torch.nn.parallel import DistributedDataParallel as DDP
         mods = {k: DDP(m, device_ids=[local], output_device=local) for k, m in mods.items()}
+    elif world > 1:
+        # the same exchange (mean of every MLP-weight and code-table gradient over ranks, rank 0's initial parameters) as ONE
+        # flat NCCL all-reduce per chunk step instead of three DDP reducers: codenerf_b200/parallel.py
+        from codenerf_b200.parallel import GradAllReduce
+        sync = GradAllReduce([p for m in mods.values() for p in m.parameters()])
     from codenerf_b200.optim import FusedAdamW          # torch.optim.AdamW arithmetic, one launch
     opt = FusedAdamW([{"params": mods["nerf_coarse"].parameters()}, {"params": mods["nerf_fine"].parameters()},
                              {"params": mods["embedding"].parameters(), "lr": 1e-3}], lr=1e-4)
@@ -237,6 +248,8 @@ def run_ours(args):
             loss = lc + lf
             opt.zero_grad()
             loss.backward()
+            if sync is not None:
+                sync()
             opt.step()
             if read_loss:
                 total = lf.detach() if total is None else total + lf.detach()
@@ -321,6 +334,8 @@ def run_ours(args):
                 "gpu_launches": roof.pop("launches_per_step"), "roofline": roof,
                 "model_flops_per_ray": FLOP_PER_RAY_TRAIN,
                 "achieved_tflops_whole_step": value * FLOP_PER_RAY_TRAIN / 1e12 / world}
+        line["config"]["gradient_exchange"] = ("none (1 GPU)" if world == 1 else
+                                               "DistributedDataParallel x3" if args.ddp else "GradAllReduce (one flat all-reduce)")
         if world == 1:
             # standalone rooflines of the HBM-bound stages (north_star: compositing / sampling vs the HBM peak): one launch
             # per repetition over 524,288 rays (working sets > L2), CUDA events, algorithmic bytes of SURVEY section 8(d)

@@ -152,3 +152,37 @@ def test_fused_adamw_constructor_and_cpu_refusal():
         opt.step()
     opt.zero_grad()
     opt.step()                                               # nothing has a gradient: a no-op that needs no GPU
+
+
+def _grad_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from codenerf_b200.parallel import GradAllReduce
+    torch.manual_seed(100 + rank)                             # ranks start from different parameters, as train.py:29-31 seeds
+    lin, emb = torch.nn.Linear(5, 3), torch.nn.Embedding(4, 2)
+    frozen = torch.nn.Parameter(torch.ones(2), requires_grad=False)
+    sync = GradAllReduce(list(lin.parameters()) + list(emb.parameters()) + [frozen])
+    start = [p.detach().clone() for p in lin.parameters()]
+    x = torch.full((2, 5), float(rank + 1))
+    (lin(x).sum() * (rank + 1)).backward()                    # emb gets no gradient on any rank -> zeros
+    sync()
+    torch.save({"start": start, "gw": lin.weight.grad.clone(), "gb": lin.bias.grad.clone(), "ge": emb.weight.grad.clone(),
+                "flat_views": lin.weight.grad.data_ptr() == sync.flat.data_ptr()}, f"{out}.{rank}")
+    dist.destroy_process_group()
+
+
+def test_grad_allreduce_two_ranks_gloo(tmp_path):
+    """GradAllReduce: rank 0's parameters broadcast at construction (as DDP), gradients averaged over ranks through one
+    flat buffer, parameters left with views of it, missing gradients treated as zeros, frozen parameters skipped."""
+    out = str(tmp_path / "g.pt")
+    port = 31500 + (os.getpid() % 2000)
+    mp.spawn(_grad_worker, args=(2, port, out), nprocs=2, join=True)
+    r0, r1 = torch.load(out + ".0"), torch.load(out + ".1")
+    for a, b in zip(r0["start"], r1["start"]):
+        assert torch.equal(a, b)                              # broadcast
+    # d/dW of (rank+1) * sum(W x + b) with x = rank+1: rank 0 -> 2 rows of 1 * 1, rank 1 -> 2 rows of 2 * 2
+    want_w = torch.full((3, 5), (1 * 1 * 2 + 2 * 2 * 2) / 2.0)
+    want_b = torch.full((3,), (1 * 2 + 2 * 2) / 2.0)
+    for r in (r0, r1):
+        assert torch.equal(r["gw"], want_w) and torch.equal(r["gb"], want_b)
+        assert torch.equal(r["ge"], torch.zeros(4, 2)) and r["flat_views"]
