@@ -10,7 +10,8 @@ train.py:92-114 does: 4 chunks of 4096 rays, each chunk = embedding lookup + pre
 
 `value`  : inputs (poses, pixel indices, target pixels, object ids) already resident in HBM.
 `e2e`    : the same step through the public drop-in API from HOST buffers: pinned images + poses copied H2D, host numpy
-           permutation (ray_sampler.sample), target gather, per-chunk loss.item() D2H -- train.py's loop body.
+           permutation (ray_sampler.sample), target gather, one loss.item() D2H per step -- train.py's loop body, with the
+           next step's inputs staged before the current loss is read (--no-prefetch: train.py's order of work).
 `--impl reference`: the CPU oracle restatement of the reference path (the reference itself is Python and cannot travel to
            the GPU box; kind="port") on all host cores, bounded sample per step.
 """
@@ -48,6 +49,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ddp", action="store_true", help="N > 1: wrap the modules in DistributedDataParallel as "
                     "utils/util.py:139-142 does, instead of codenerf_b200.parallel.GradAllReduce")
+    ap.add_argument("--no-prefetch", action="store_true", help="e2e leg: draw each step's pixel permutations at the start "
+                    "of the step (the reference's order of work) instead of under the previous step's kernels")
     return ap.parse_args()
 
 
@@ -184,6 +187,9 @@ def workload_config(precision):
                            "utils/util.py:139-142)",
             "optimizer": "AdamW (lr 1e-4, embeddings 1e-3; train.py:111-114) via codenerf_b200.optim.FusedAdamW, one launch",
             "loss_read": "summed fine loss of the step's 4 chunks, one device->host read per step (e2e leg)",
+            "e2e_host_overlap": "prefetching loader: the next step's inputs (pinned H2D copies, np.random.permutation draws from the same "
+                                "RNG stream, ray kernel, target gather with the device copy of select_inds) are staged after this "
+                                "step's kernels are enqueued and before its loss is read; one staging and one loss read per step",
             "l2": "activations written/read per chunk (>1 GB) exceed the 126 MB L2; no explicit flush"}
 
 
@@ -236,7 +242,6 @@ def run_ours(args):
     n_rays = c["B"] * c["rays_per_image"]
 
     def chunks_step(ro, rd, tgt, oid, read_loss):
-        d2h = 0
         total = None
         for i in range(0, n_rays, c["chunk"]):
             sl = slice(i, i + c["chunk"])
@@ -253,10 +258,7 @@ def run_ours(args):
             opt.step()
             if read_loss:
                 total = lf.detach() if total is None else total + lf.detach()
-        if read_loss:
-            _ = total.item()            # the step's result: summed fine loss of its chunks, one device->host read per step
-            d2h += 4
-        return d2h
+        return total
 
     # device-resident inputs for `value`
     imgs_d, poses_d, ids_d = imgs_pin.to(dev), poses_pin.to(dev), ids_pin.to(dev)
@@ -272,15 +274,31 @@ def run_ours(args):
 
     h2d = imgs_pin.numel() * 4 + poses_pin.numel() * 4 + ids_pin.numel() * 8 + n_rays * 8
 
-    def step_e2e():
+    staged = []
+
+    def stage_inputs():
+        """One step's host -> device work: pinned images / poses / ids H2D, ray_sampler.sample (host numpy permutation +
+        ray kernel), target-pixel gather (train.py:76-80)."""
         imgs = imgs_pin.to(dev, non_blocking=True)
         poses = poses_pin.to(dev, non_blocking=True)
         ids = ids_pin.to(dev, non_blocking=True)
-        ro, rd, sel = ray_sampler.sample(tform_cam2world=poses)          # train.py:76
+        ro, rd, _sel = ray_sampler.sample(tform_cam2world=poses)         # train.py:76
+        sel = ray_sampler.select_inds_device                             # the same indices, already on the device
         flat = imgs.flatten(1, 2)
         tgt = torch.cat([flat[k, sel[k], :] for k in range(c["B"])], dim=0)[..., :3]   # train.py:77-80
         oid = ids[:, None].expand(-1, c["rays_per_image"]).reshape(-1)
-        return chunks_step(ro, rd, tgt, oid, True)
+        staged.append((ro, rd, tgt, oid))
+
+    def step_e2e():
+        # Every step does one stage_inputs() and one loss read.  With prefetching (default) the inputs of step k+1 are staged
+        # after step k's kernels have been enqueued and before its loss is read -- a prefetching loader -- so the host
+        # permutation and the copies run under the GPU's work; --no-prefetch keeps train.py's order (stage, compute, read).
+        if args.no_prefetch or not staged:
+            stage_inputs()
+        total = chunks_step(*staged.pop(0), True)
+        if not args.no_prefetch:
+            stage_inputs()
+        _ = total.item()                   # the step's result: summed fine loss of its chunks, one device->host read per step
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -329,7 +347,8 @@ def run_ours(args):
                 "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_val / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "bf16" if args.precision == "bf16" else "f32", "data": "synthetic",
-                "config": workload_config(args.precision), "clocks": clk,
+                "config": dict(workload_config(args.precision), **({"e2e_host_overlap": "off (--no-prefetch)"} if args.no_prefetch else {})),
+                "clocks": clk,
                 "e2e": {"value": e2e, "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
                 "gpu_launches": roof.pop("launches_per_step"), "roofline": roof,
                 "model_flops_per_ray": FLOP_PER_RAY_TRAIN,
