@@ -49,6 +49,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--ddp", action="store_true", help="N > 1: wrap the modules in DistributedDataParallel as "
                     "utils/util.py:139-142 does, instead of codenerf_b200.parallel.GradAllReduce")
+    ap.add_argument("--torch-loss", action="store_true", help="2 x torch.nn.functional.mse_loss + add (train.py:103-104 verbatim) "
+                    "instead of codenerf_b200.ops.mse_pair")
     ap.add_argument("--no-prefetch", action="store_true", help="e2e leg: draw each step's pixel permutations at the start "
                     "of the step (the reference's order of work) instead of under the previous step's kernels")
     return ap.parse_args()
@@ -181,7 +183,8 @@ def workload_config(precision):
                         "samples, CodeNeRF hidden 256 / codes 256, PE L=10/4, per chunk: embedding lookup + render fwd + "
                         "2 MSE + backward + AdamW step",
             "rays_per_step_per_gpu": c["B"] * c["rays_per_image"], "chunk": c["chunk"], "mlp_precision": precision,
-            "pairing": "reference",
+            "pairing": "reference", "loss": "codenerf_b200.ops.mse_pair: both MSE means and their sum in one launch (--torch-loss: "
+                                            "2 x torch mse_loss + add)",
             "parallelism": "data-parallel over rays; per chunk step one flat NCCL all-reduce (mean) of all MLP and code-table "
                            "gradients (codenerf_b200.parallel.GradAllReduce; --ddp = DistributedDataParallel wrappers as "
                            "utils/util.py:139-142)",
@@ -248,9 +251,12 @@ def run_ours(args):
             codes = mods["embedding"](oid[sl])
             rgb_c, rgb_f = nerf.predict_radiance_and_render((ro[sl], rd[sl]), point_sampler, embedders,
                                                             mods["nerf_coarse"], mods["nerf_fine"], codes)
-            lc = torch.nn.functional.mse_loss(rgb_c[..., :3], tgt[sl])
-            lf = torch.nn.functional.mse_loss(rgb_f[..., :3], tgt[sl])
-            loss = lc + lf
+            if args.torch_loss:
+                lc = torch.nn.functional.mse_loss(rgb_c[..., :3], tgt[sl])
+                lf = torch.nn.functional.mse_loss(rgb_f[..., :3], tgt[sl])
+                loss = lc + lf
+            else:                                                        # the same three numbers, one launch
+                lc, lf, loss = ops.mse_pair(rgb_c, rgb_f, tgt[sl])
             opt.zero_grad()
             loss.backward()
             if sync is not None:

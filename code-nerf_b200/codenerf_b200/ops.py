@@ -236,6 +236,7 @@ class _Composite(torch.autograd.Function):
         check(lib.cnrf_composite_fwd(_p(raw), _p(z), _p(rd), N, S, _p(rgb), _p(disp), _p(acc), _p(weights), _p(depth),
                                      _stream()), "cnrf_composite_fwd")
         ctx.save_for_backward(raw, z, rd)
+        ctx.set_materialize_grads(False)       # unused outputs arrive as None (the kernel takes NULL), not as zero tensors
         return rgb, disp, acc, weights, depth
 
     @staticmethod
@@ -256,6 +257,49 @@ class _Composite(torch.autograd.Function):
 def composite(raw, z, rd):
     """-> (rgb, disp, acc, weights, depth), the tuple order of volume_render (volumetric_render.py:66)."""
     return _Composite.apply(raw, z, rd)
+
+
+class _MsePair(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, rgb_a, rgb_b, target):
+        _req_cuda(rgb_a, rgb_b, target)
+        lib = _lib.load()
+        a, lda = _rows(rgb_a)
+        b, ldb = _rows(rgb_b)
+        t, ldt = _rows(target)
+        N = a.shape[0]
+        assert a.shape[-1] >= 3 and b.shape == a.shape and t.shape[0] == N and t.shape[-1] >= 3
+        out = torch.empty((3,), dtype=_f32, device=a.device)
+        check(lib.cnrf_mse_pair_fwd(_p(a), lda, _p(b), ldb, _p(t), ldt, N, _p(out), _stream()), "cnrf_mse_pair_fwd")
+        ctx.save_for_backward(a, b, t)
+        ctx.lds = (lda, ldb, ldt)
+        ctx.set_materialize_grads(False)
+        return out[0], out[1], out[2]
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g0, g1, g2):
+        a, b, t = ctx.saved_tensors
+        lda, ldb, ldt = ctx.lds
+        lib = _lib.load()
+        N = a.shape[0]
+        gs = [None if g is None else _c(g.to(_f32)) for g in (g0, g1, g2)]
+        g_a = torch.empty((N, 3), dtype=_f32, device=a.device) if ctx.needs_input_grad[0] else None
+        g_b = torch.empty((N, 3), dtype=_f32, device=a.device) if ctx.needs_input_grad[1] else None
+        check(lib.cnrf_mse_pair_bwd(_p(a), lda, _p(b), ldb, _p(t), ldt, N, _p(gs[0]), _p(gs[1]), _p(gs[2]), _p(g_a), _p(g_b),
+                                    _stream()), "cnrf_mse_pair_bwd")
+        if g_a is not None and a.shape[-1] != 3:
+            g_a = torch.nn.functional.pad(g_a, (0, a.shape[-1] - 3))
+        if g_b is not None and b.shape[-1] != 3:
+            g_b = torch.nn.functional.pad(g_b, (0, b.shape[-1] - 3))
+        return g_a, g_b, None
+
+
+def mse_pair(rgb_coarse, rgb_fine, target):
+    """-> (coarse_loss, fine_loss, coarse_loss + fine_loss) of train.py:103-104 as 0-dim tensors: the two
+    torch.nn.functional.mse_loss(rgb[..., :3], target[..., :3]) calls and their sum in one launch (one more for both
+    gradients).  rgb_* are (N, >=3), target is (N, >=3) and may be a strided view (RGBA rows)."""
+    return _MsePair.apply(rgb_coarse, rgb_fine, target)
 
 
 # ----------------------------------------------------------------------------------------------------------

@@ -341,7 +341,8 @@ extern "C" size_t cnrf_codenerf_saved_bytes(const cnrf_field_shape* s) {
   if (check_shape(s) != CNRF_OK || !s->keep) return 0;
   Dims d = dims_of(s);
   if (s->precision == CNRF_PRECISION_FP32) return saved_f32_bytes(d);
-  return 3 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M) + 2048;
+  // (+ shared-code mode: the code runs and one code row per run, found once in the forward and reused by the backward)
+  return 3 * al(d.N * d.C) + cnrf_code_runs_bytes(d.N) + 256 + 2 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M) + 2048;
 }
 
 extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32_t backward) {
@@ -386,15 +387,18 @@ struct FieldIn {   // everything the two entry-point families share
 
 // shared-code mode: find the runs of equal ids and gather one code row per run
 struct SharedCodes { CodeRuns runs; float *zc_s, *zc_t; };
-int setup_shared_codes(Dims& d, const FieldIn& in, Arena& w, SharedCodes& sc, cudaStream_t st) {
+// `compute` = false: the arena already holds them (the backward, over the forward's saved buffer)
+int setup_shared_codes(Dims& d, const FieldIn& in, Arena& w, SharedCodes& sc, bool compute, cudaStream_t st) {
   size_t rb = cnrf_code_runs_bytes(d.N);
   float* rbase = w.take(rb / sizeof(float));
   sc.zc_s = w.take(d.N * d.C); sc.zc_t = w.take(d.N * d.C);
   if (!w.ok) return CNRF_E_WORKSPACE;
   sc.runs = cnrf_code_runs_carve(rbase, d.N);
-  RUN(cnrf_code_runs(in.ids, d.N, in.num_codes, sc.runs, st));
-  RUN(cnrf_gather_codes(in.ids, sc.runs, d.N, d.C, in.z_s, in.ld_zs, sc.zc_s, st));
-  RUN(cnrf_gather_codes(in.ids, sc.runs, d.N, d.C, in.z_t, in.ld_zt, sc.zc_t, st));
+  if (compute) {
+    RUN(cnrf_code_runs(in.ids, d.N, in.num_codes, sc.runs, st));
+    RUN(cnrf_gather_codes(in.ids, sc.runs, d.N, d.C, in.z_s, in.ld_zs, sc.zc_s, st));
+    RUN(cnrf_gather_codes(in.ids, sc.runs, d.N, d.C, in.z_t, in.ld_zt, sc.zc_t, st));
+  }
   d.rows_dev = sc.runs.count;
   return CNRF_OK;
 }
@@ -423,23 +427,19 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   if (d.H != 256 || d.C != 256 || d.dx > 63 || d.dd > 31) return CNRF_E_UNSUPPORTED;
   float *as1, *as2, *at;
   char* tc_saved = nullptr; size_t tc_saved_bytes = 0;
-  if (s->keep) {
-    if (!saved) return CNRF_E_WORKSPACE;
-    Arena sa(saved, saved_bytes);
-    as1 = sa.take(d.N * d.C); as2 = sa.take(d.N * d.C); at = sa.take(d.N * d.C);
-    if (!sa.ok) return CNRF_E_WORKSPACE;
-    tc_saved = sa.base + sa.off; tc_saved_bytes = sa.cap - sa.off;
-  } else {
-    as1 = w.take(d.N * d.C); as2 = w.take(d.N * d.C); at = w.take(d.N * d.C);
-    if (!w.ok) return CNRF_E_WORKSPACE;
-  }
+  if (s->keep && !saved) return CNRF_E_WORKSPACE;
+  Arena sa(s->keep ? saved : nullptr, s->keep ? saved_bytes : 0);
+  Arena& act = s->keep ? sa : w;            // what the backward needs again lives in the saved buffer
+  as1 = act.take(d.N * d.C); as2 = act.take(d.N * d.C); at = act.take(d.N * d.C);
+  if (!act.ok) return CNRF_E_WORKSPACE;
   const float *zs = in.z_s, *zt = in.z_t;
   int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
   SharedCodes sc;
   if (in.ids) {
-    RUN(setup_shared_codes(d, in, w, sc, st));
+    RUN(setup_shared_codes(d, in, act, sc, true, st));
     zs = sc.zc_s; zt = sc.zc_t; ld_zs = ld_zt = d.C;
   }
+  if (s->keep) { tc_saved = sa.base + sa.off; tc_saved_bytes = sa.cap - sa.off; }
   RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, t, true, st));
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
                 in.inc_xyz, t.b2, t.bo, t.br, t.bd, t.bof, t.bos, in.x_dir, in.ld_dir, in.ids ? sc.runs.gid : nullptr};
@@ -478,8 +478,8 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
   float *gz_s = g_z_s, *gz_t = g_z_t;
   SharedCodes sc;
-  if (in.ids) {          // the runs are cheap to find again; nothing of them is kept between the passes
-    RUN(setup_shared_codes(d, in, w, sc, st));
+  if (in.ids) {          // runs and per-run code rows: the forward left them in the saved buffer
+    RUN(setup_shared_codes(d, in, sa, sc, false, st));
     zs = sc.zc_s; zt = sc.zc_t; ld_zs = ld_zt = d.C;
     gz_s = w.take(d.N * d.C); gz_t = w.take(d.N * d.C);
     if (!w.ok) return CNRF_E_WORKSPACE;

@@ -273,6 +273,19 @@ int cnrf_adamw_step(const cnrf_adamw_tensor* tensors, int32_t count, float beta1
                     cnrf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * Photometric loss of the training loop (train.py:103-104): with a = rgb_coarse, b = rgb_fine and
+ * t = target pixels (rows of ld_* floats, first three columns used; RGBA targets: ld_t = 4),
+ *   out3[0] = mean((a - t)^2), out3[1] = mean((b - t)^2), out3[2] = out3[0] + out3[1]          (one launch)
+ * replaces 2 x torch.nn.functional.mse_loss + add.  Backward: g_loss_* are device scalars (NULL = zero), g_a / g_b dense
+ * [N,3] (either may be NULL):  g_a = (g_loss_a + g_loss_sum) * 2 (a - t) / (3N), g_b likewise              (one launch)
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_mse_pair_fwd(const float* rgb_a, int64_t ld_a, const float* rgb_b, int64_t ld_b, const float* target,
+                      int64_t ld_t, int64_t N, float* out3, cnrf_stream_t stream);
+int cnrf_mse_pair_bwd(const float* rgb_a, int64_t ld_a, const float* rgb_b, int64_t ld_b, const float* target,
+                      int64_t ld_t, int64_t N, const float* g_loss_a, const float* g_loss_b, const float* g_loss_sum,
+                      float* g_a, float* g_b, cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Diagnostics (used by tests only).  One-CTA tcgen05 GEMM over the 128-byte-swizzled shared-memory image the fused
  * MLP kernels use.  mode 0: D[128,N] = A[128,K] B[N,K]^T (K-major operands); mode 1: D[128,N] = A[K,128]^T B[K,N]
  * (MN-major operands, the dW = dY^T X form).  *err is set to 1 if the kernel's bounded barrier wait timed out.
