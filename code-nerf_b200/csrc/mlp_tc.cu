@@ -106,7 +106,8 @@ static int* tc_error_ptr() {
 static inline int64_t tiles_of(int64_t M) { return (M + TILE - 1) / TILE; }
 static inline int64_t pairs_of(int64_t M) { return (tiles_of(M) + 1) / 2; }
 // per tile: the activation images; then per tile pair: the view-direction extension slab
-size_t cnrf_tc_saved_bytes(int64_t M) { return (size_t)tiles_of(M) * SAVED_PER_TILE + (size_t)pairs_of(M) * SLAB; }
+// ... then the packed weight images of this call (the backward runs on the same weights and reuses them)
+size_t cnrf_tc_saved_bytes(int64_t M) { return (size_t)tiles_of(M) * SAVED_PER_TILE + (size_t)pairs_of(M) * SLAB + PACKED_BYTES; }
 
 // Extension slab of every tile pair (the K = 32 extra input columns of layer_dir1): row r, columns 32t .. 32t+31 =
 // [gamma(d^ of the ray paired with sample row r of tile t) | 1 | 0].  The pairing reproduces nerf/__init__.py:127
@@ -143,8 +144,8 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   if (w + PACKED_BYTES + 1024 + (size_t)pairs_of(a.M) * SLAB > reinterpret_cast<uint8_t*>(ws) + ws_bytes) return CNRF_E_WORKSPACE;
   if (saved && saved_bytes < cnrf_tc_saved_bytes(a.M) + 1024) return CNRF_E_WORKSPACE;
   if (a.dd > 31) return CNRF_E_UNSUPPORTED;
-  Packed pk = carve_packed(w);
   uint8_t* saved_al = saved ? reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(saved))) : nullptr;
+  Packed pk = carve_packed(saved_al ? saved_al + (size_t)tiles_of(a.M) * SAVED_PER_TILE + (size_t)pairs_of(a.M) * SLAB : w);
   // the extension slabs live with the saved images when a backward follows (the weight-gradient kernel reads them)
   uint8_t* ext = saved_al ? saved_al + (size_t)tiles_of(a.M) * SAVED_PER_TILE
                           : reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
@@ -573,10 +574,9 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   if (w + PACKED_BYTES + 1024 + (size_t)tiles * DY_PER_TILE > reinterpret_cast<uint8_t*>(ws) + ws_bytes) return CNRF_E_WORKSPACE;
   if (saved_bytes < cnrf_tc_saved_bytes(a.M) + 1024) return CNRF_E_WORKSPACE;
   const uint8_t* sv = reinterpret_cast<const uint8_t*>(up1k(reinterpret_cast<size_t>(saved)));
-  Packed pk = carve_packed(w);
+  // the forward packed both image sets (pack_weights_kernel) next to the saved activations
+  Packed pk = carve_packed(const_cast<uint8_t*>(sv) + (size_t)tiles * SAVED_PER_TILE + (size_t)pairs_of(a.M) * SLAB);
   uint8_t* dy = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
-  pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
-  CNRF_LAUNCH_CHECK();
   int rc;
   if ((rc = cnrf_fill_zero(g->bias[CNRF_L_XYZ1], 256 * sizeof(float), st))) return rc;
   if ((rc = cnrf_fill_zero(g->bias[CNRF_L_DIR2], 256 * sizeof(float), st))) return rc;
