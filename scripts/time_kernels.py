@@ -10,7 +10,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "code-nerf_b200")); sys.path.insert(0, ROOT)
 import view_synthesis.nerf as nerf, view_synthesis.models as models
-from codenerf_b200 import _lib
+from codenerf_b200 import _lib, ops
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 10
@@ -35,7 +35,7 @@ lib = _lib.load()
 def step():
     codes = mods["embedding"](oid)
     a, b = nerf.predict_radiance_and_render((ro, rd), ps, emb, mods["nerf_coarse"], mods["nerf_fine"], codes)
-    loss = torch.nn.functional.mse_loss(a, tgt) + torch.nn.functional.mse_loss(b, tgt)
+    _, _, loss = ops.mse_pair(a, b, tgt)          # bench.py's loss (train.py:103-104 in one launch)
     opt.zero_grad()
     loss.backward()
     opt.step()
