@@ -112,30 +112,31 @@ size_t cnrf_tc_saved_bytes(int64_t M) { return (size_t)tiles_of(M) * SAVED_PER_T
 // Extension slab of every tile pair (the K = 32 extra input columns of layer_dir1): row r, columns 32t .. 32t+31 =
 // [gamma(d^ of the ray paired with sample row r of tile t) | 1 | 0].  The pairing reproduces nerf/__init__.py:127
 // (flat row m -> ray m mod N) unless CNRF_PAIRING_CORRECT (m / S).
+// One thread per 16-byte chunk (8 bf16 columns) of a row: a warp writes four whole 128-byte rows.
 __global__ void build_ext_kernel(const float* __restrict__ x_dir, int64_t ld, int dd, int64_t N, int64_t M, int S,
                                  int pairing, uint8_t* __restrict__ ext, int64_t num_pairs) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= num_pairs * 256) return;
-  const int r = (int)(i & 127), t = (int)((i >> 7) & 1);
-  const int64_t pr = i >> 8;
+  if (i >= num_pairs * 1024) return;
+  const int c = (int)(i & 7), r = (int)((i >> 3) & 127);
+  const int t = c >> 2, j = c & 3;                    // tile of the pair, 8-column group of its 32 columns
+  const int64_t pr = i >> 10;
   const int64_t m = (pr * 2 + t) * TILE + r;
-  uint32_t w[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) w[j] = 0u;
+  uint32_t w[4] = {0u, 0u, 0u, 0u};
   if (m < M) {
-    const float* src = x_dir + (pairing == CNRF_PAIRING_REFERENCE ? m % N : m / S) * ld;
+    int64_t ray;
+    if (M < (1ll << 31)) ray = pairing == CNRF_PAIRING_REFERENCE ? (uint32_t)m % (uint32_t)N : (uint32_t)m / (uint32_t)S;
+    else ray = pairing == CNRF_PAIRING_REFERENCE ? m % N : m / S;
+    const float* src = x_dir + ray * ld;
 #pragma unroll
-    for (int j = 0; j < 16; ++j) {
-      const int c0 = 2 * j, c1 = 2 * j + 1;
+    for (int q = 0; q < 4; ++q) {
+      const int c0 = 8 * j + 2 * q, c1 = c0 + 1;
       const float lo = c0 < dd ? __ldg(src + c0) : (c0 == dd ? 1.0f : 0.0f);
       const float hi = c1 < dd ? __ldg(src + c1) : (c1 == dd ? 1.0f : 0.0f);
-      w[j] = pack_bf16(lo, hi);
+      w[q] = pack_bf16(lo, hi);
     }
   }
   uint8_t* row = ext + (size_t)pr * SLAB + r * 128;
-#pragma unroll
-  for (int j = 0; j < 4; ++j)
-    *reinterpret_cast<uint4*>(row + (((4 * t + j) ^ (r & 7)) << 4)) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+  *reinterpret_cast<uint4*>(row + ((c ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
 }
 
 int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
@@ -149,7 +150,7 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   // the extension slabs live with the saved images when a backward follows (the weight-gradient kernel reads them)
   uint8_t* ext = saved_al ? saved_al + (size_t)tiles_of(a.M) * SAVED_PER_TILE
                           : reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
-  build_ext_kernel<<<grid_for(pairs_of(a.M) * 256, 256), 256, 0, st>>>(a.x_dir, a.ld_dir, a.dd, a.N, a.M, a.S, a.pairing,
+  build_ext_kernel<<<grid_for(pairs_of(a.M) * 1024, 256), 256, 0, st>>>(a.x_dir, a.ld_dir, a.dd, a.N, a.M, a.S, a.pairing,
                                                                       ext, pairs_of(a.M));
   CNRF_LAUNCH_CHECK();
   pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
