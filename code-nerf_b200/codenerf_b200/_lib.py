@@ -118,6 +118,12 @@ def load():
     if lib.cnrf_abi_version() != 1:
         raise CnrfError("libcnrf.so ABI version mismatch")
     _lib = lib
+    if os.environ.get("CODENERF_REPORT_LAUNCHES"):
+        # evidence for callers that cannot be edited (the reference's train.py / eval.py run as subprocesses by
+        # tests/test_gpu_reference_drivers.py): how many libcnrf kernels this process launched
+        import atexit
+        atexit.register(lambda: print(f"[libcnrf] pid {os.getpid()}: {lib.cnrf_launch_count()} kernel launches from {LIB_PATH}",
+                                      flush=True))
     return lib
 
 

@@ -114,7 +114,11 @@ class ShapeTextureEmbedding(torch.nn.Module):
         # Where the codes came from travels with them: CodeNeRFModel's fused field then looks the rows up itself and
         # shares the code layers between the rays of one object (train.py:78 gives a whole image one id).  Any other
         # consumer sees two ordinary tensors.
-        src = (object_ids, self.shape_embedding.weight, self.texture_embedding.weight)
+        # The tag records the versions of the four tensors: an in-place edit of z_s / z_t (noise, clamping) or of the tables
+        # after the lookup makes CodeNeRFModel fall back to the per-ray path, which reads the VALUES of z_s / z_t as the
+        # reference does.  In shared-code mode the gradients flow to the tables directly (hooks on z_s / z_t do not fire).
+        ws, wt = self.shape_embedding.weight, self.texture_embedding.weight
+        src = (object_ids, ws, wt, (z_s._version, z_t._version, ws._version, wt._version))
         z_s._cnrf_code_source = src
         z_t._cnrf_code_source = src
         return z_s, z_t
@@ -185,6 +189,10 @@ class CodeNeRFModel(torch.nn.Module):
             src = getattr(z_s, "_cnrf_code_source", None)
             if src is None or getattr(z_t, "_cnrf_code_source", None) is not src or not _share_codes():
                 src = None
+            elif (z_s._version, z_t._version, src[1]._version, src[2]._version) != src[3]:
+                src = None                  # somebody edited the codes or the tables in place since the lookup
+            else:
+                src = src[:3]
             return ops.codenerf_field(params, x.pts, x.rd, z_s, z_t, ex.frequency_bands, ed.frequency_bands,
                                       self.hidden_size, self.shape_code_size, self.dim_xyz, self.dim_dir,
                                       pairing=pairing, precision=precision, code_source=src)

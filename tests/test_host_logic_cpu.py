@@ -131,6 +131,36 @@ def test_embedding_output_carries_its_source_and_equals_nn_embedding():
     assert not hasattr(z_s[:4], "_cnrf_code_source")
     (z_s.sum() + z_t.sum()).backward()                       # the ordinary autograd path still works
     assert emb.shape_embedding.weight.grad[3].eq(3).all() and emb.shape_embedding.weight.grad[1].eq(0).all()
+    # the tag records tensor versions: an in-place edit of the codes (or of a table) after the lookup invalidates it
+    assert src[3] == (z_s._version, z_t._version, src[1]._version, src[2]._version)
+    with torch.no_grad():
+        z_s.add_(1.0)
+    assert src[3] != (z_s._version, z_t._version, src[1]._version, src[2]._version)
+
+
+def _ddp_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import view_synthesis.models as models
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    torch.manual_seed(0)
+    emb = DDP(models.ShapeTextureEmbedding(5, 8, 8))                  # utils/util.py:140, CPU + gloo
+    ids = torch.tensor([1, 1, 4])
+    z_s, z_t = emb(ids)
+    ok = (hasattr(z_s, "_cnrf_code_source") and z_s._cnrf_code_source is z_t._cnrf_code_source
+          and z_s._cnrf_code_source[1] is emb.module.shape_embedding.weight)
+    if rank == 0:
+        torch.save(torch.tensor(int(ok)), out)
+    dist.destroy_process_group()
+
+
+def test_code_source_tag_survives_distributed_data_parallel(tmp_path):
+    """train.py --distributed wraps the embedding module in DistributedDataParallel (utils/util.py:139-142): the tag that
+    selects the shared-code path must survive DDP.forward's output handling, or every distributed run would silently take
+    the per-ray path."""
+    out = str(tmp_path / "ok.pt")
+    mp.spawn(_ddp_worker, args=(2, 29500 + (os.getpid() % 2000) + 17, out), nprocs=2, join=True)
+    assert int(torch.load(out)) == 1
 
 
 def test_fused_adamw_constructor_and_cpu_refusal():
