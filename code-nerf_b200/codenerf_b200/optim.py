@@ -52,12 +52,16 @@ class FusedAdamW(torch.optim.Optimizer):
                 g = p.grad
                 if not (p.is_cuda and p.dtype == torch.float32 and p.is_contiguous()) or g.is_sparse or g.dtype != torch.float32:
                     raise _lib.CnrfError("FusedAdamW needs contiguous CUDA fp32 parameters with dense fp32 gradients")
-                st = self._init_state(p)
-                st["step"] += 1
-                rows.append((p, g if g.is_contiguous() else g.contiguous(), st, float(group["lr"]),
+                rows.append((p, g if g.is_contiguous() else g.contiguous(), None, float(group["lr"]),
                              float(group["weight_decay"])))
         if not any(by_betas.values()):
             return loss
+        # every parameter passed validation: only now touch optimiser state (a raise above leaves all step counters alone)
+        for rows in by_betas.values():
+            for i, (p, g, _, lr, wd) in enumerate(rows):
+                st = self._init_state(p)
+                st["step"] += 1
+                rows[i] = (p, g, st, lr, wd)
         lib = _lib.load()
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         for (b1, b2, eps), rows in by_betas.items():

@@ -45,9 +45,21 @@ class GradAllReduce(object):
         contributes zeros, as DDP's find_unused_parameters would)."""
         if self.world == 1:
             return
-        grads = [p.grad.reshape(-1) if p.grad is not None else torch.zeros_like(v).reshape(-1)
-                 for p, v in zip(self.params, self.views)]
-        torch.cat(grads, out=self.flat)
+        # Contract: gradients are produced fresh by every backward (optimizer.zero_grad() with set_to_none=True, torch's
+        # default, and no accumulation over several backward passes).  A p.grad that still IS the view handed out by the
+        # previous call (zero_grad(set_to_none=False), or a parameter the backward did not reach) already lives in the flat
+        # buffer: it is left in place rather than copied onto itself, and it is averaged again -- so such callers must
+        # not rely on stale values.
+        with torch.no_grad():
+            dst, src = [], []
+            for p, v in zip(self.params, self.views):
+                if p.grad is None:
+                    v.zero_()
+                elif p.grad.data_ptr() != v.data_ptr():
+                    dst.append(v)
+                    src.append(p.grad)
+            if dst:
+                torch._foreach_copy_(dst, src)          # one multi-tensor launch, never an overlapping copy
         if self._avg:
             dist.all_reduce(self.flat, op=dist.ReduceOp.AVG, group=self.group)
         else:

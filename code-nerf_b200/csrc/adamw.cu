@@ -64,15 +64,22 @@ extern "C" int cnrf_adamw_step(const cnrf_adamw_tensor* tensors, int32_t count, 
                                cnrf_stream_t stream) {
   if (count < 0 || (count > 0 && !tensors)) return CNRF_E_NULL;
   cudaStream_t st = as_stream(stream);
-  for (int at = 0; at < count; at += AW_MAX) {
+  // validate everything before the first launch: a bad entry must not leave earlier tensors already stepped
+  for (int i = 0; i < count; ++i) {
+    const cnrf_adamw_tensor& t = tensors[i];
+    if (t.numel <= 0) continue;
+    if (!t.param || !t.grad || !t.exp_avg || !t.exp_avg_sq) return CNRF_E_NULL;
+    if (t.step < 1.0f) return CNRF_E_SHAPE;
+  }
+  // `next` is the first table row the batch did NOT consume (empty tensors are skipped without taking a batch entry, so a
+  // batch may cover more than AW_MAX rows)
+  for (int at = 0, next = 0; at < count; at = next) {
     AdamWBatch b;
     b.count = 0; b.beta1 = beta1; b.beta2 = beta2; b.eps = eps;
     int blocks = 0;
-    for (int i = at; i < count && b.count < AW_MAX; ++i) {
-      const cnrf_adamw_tensor& t = tensors[i];
+    for (next = at; next < count && b.count < AW_MAX; ++next) {
+      const cnrf_adamw_tensor& t = tensors[next];
       if (t.numel <= 0) continue;
-      if (!t.param || !t.grad || !t.exp_avg || !t.exp_avg_sq) return CNRF_E_NULL;
-      if (t.step < 1.0f) return CNRF_E_SHAPE;
       const int k = b.count++;
       b.p[k] = t.param; b.g[k] = t.grad; b.m[k] = t.exp_avg; b.v[k] = t.exp_avg_sq; b.n[k] = t.numel;
       b.lr[k] = t.lr; b.wd[k] = t.weight_decay;

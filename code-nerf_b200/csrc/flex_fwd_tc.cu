@@ -330,15 +330,13 @@ int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, con
   a.betad = betad; a.w_rgb = p->w_rgb; a.b_rgb = p->b_rgb; a.b_alpha = p->b_alpha;
   a.raw = raw; a.M = s->num_rays * (int64_t)s->num_samples; a.N = s->num_rays; a.S = s->num_samples; a.pairing = s->pairing;
   cudaGetSymbolAddress(reinterpret_cast<void**>(&a.err), g_flex_tc_error);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(flex_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_SMEM);
+  {
+    static bool attr_set[CNRF_MAX_DEVICES] = {};
+    const cudaError_t e = cnrf_once_per_device(attr_set, [] {
+      return cudaFuncSetAttribute(flex_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FT_SMEM); });
     if (e != cudaSuccess) return (int)e;
-    attr_set = true;
   }
-  int dev = 0, sms = 148;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int sms = cnrf_sm_count();
   const int64_t ntiles = (a.M + FT_ROWS - 1) / FT_ROWS;
   const int grid = (int)std::min<int64_t>(ntiles, sms);
   flex_fwd_tc_kernel<<<grid, FT_THREADS, FT_SMEM, st>>>(a);

@@ -321,9 +321,8 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
 
 __device__ int g_gemm_tc_error = 0;
 static int* gemm_err_ptr() {
-  static int* p = nullptr;
-  if (!p) cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gemm_tc_error);
-  return p;
+  static int* p[CNRF_MAX_DEVICES] = {};
+  return cnrf_symbol_ptr(p, g_gemm_tc_error);
 }
 
 // Returns CNRF_E_UNSUPPORTED (nothing launched) when some operand has neither stride equal to 1: the caller then runs
@@ -350,11 +349,11 @@ int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
     total += b.mt[i] * b.nt[i] * (int)((a.K + b.kslice[i] - 1) / b.kslice[i]);
   }
   b.first[count] = total;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tc_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+  {
+    static bool attr_set[CNRF_MAX_DEVICES] = {};
+    const cudaError_t e = cnrf_once_per_device(attr_set, [] {
+      return cudaFuncSetAttribute(gemm_tc_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM); });
     if (e != cudaSuccess) return (int)e;
-    attr_set = true;
   }
   gemm_tc_batch_kernel<<<total, GTHREADS, G_SMEM, st>>>(b, gemm_err_ptr());
   CNRF_LAUNCH_CHECK();

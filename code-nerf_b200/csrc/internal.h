@@ -3,6 +3,47 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+// ---- per-device host-side caches -----------------------------------------------------------------------------------
+// A process may drive several GPUs (eval on cuda:1 after cuda:0, a test looping over devices): function attributes
+// (dynamic shared-memory opt-in), __device__ symbol addresses and SM counts are per device, so every cache of them is an
+// array indexed by the current device ordinal.  Ordinals beyond the table are simply not cached (-1).
+constexpr int CNRF_MAX_DEVICES = 64;
+inline int cnrf_device_slot() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= CNRF_MAX_DEVICES) return -1;
+  return d;
+}
+inline int cnrf_sm_count() {
+  static int n[CNRF_MAX_DEVICES] = {};
+  const int slot = cnrf_device_slot();
+  if (slot >= 0 && n[slot] > 0) return n[slot];
+  int dev = 0, v = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+  if (v <= 0) v = 148;
+  if (slot >= 0) n[slot] = v;
+  return v;
+}
+// `done` is a function-local `static bool done[CNRF_MAX_DEVICES]`; runs `set` (-> cudaError_t) once per device
+template <class F>
+inline cudaError_t cnrf_once_per_device(bool* done, F set) {
+  const int slot = cnrf_device_slot();
+  if (slot >= 0 && done[slot]) return cudaSuccess;
+  const cudaError_t e = set();
+  if (e == cudaSuccess && slot >= 0) done[slot] = true;
+  return e;
+}
+// address of a __device__ symbol on the current device
+template <class T>
+inline T* cnrf_symbol_ptr(T** cache, const T& symbol) {
+  const int slot = cnrf_device_slot();
+  if (slot >= 0 && cache[slot]) return cache[slot];
+  T* p = nullptr;
+  cudaGetSymbolAddress(reinterpret_cast<void**>(&p), symbol);
+  if (slot >= 0) cache[slot] = p;
+  return p;
+}
+
 // ---- sgemm.cu : fp32 SIMT GEMM toolkit -------------------------------------------------------------------------
 // C(m,n) = epi( sum_k A(m,k) * B(k,n) ),  A(m,k) = A[m*a_rs + k*a_cs],  B(k,n) = B[k*b_rs + n*b_cs], C row-major (ldc).
 struct GemmArgs {

@@ -33,6 +33,7 @@ __device__ __forceinline__ bool bwait(uint64_t* bar, uint32_t parity, BBars* b, 
     if (clock64() - t0 > 2000000000LL) {
       b->abort_flag = 1;
       if (err) atomicExch(err, 1);
+      tc_fatal();
       return false;
     }
   }
@@ -163,7 +164,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
     for (int i = 0; i < BRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
     for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
     bars->abort_flag = 0;
-    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); tc_fatal(); }
     mbar_fence_init();
   }
   for (int i = tid; i < HEAD_FLOATS; i += NTHREADS) heads[i] = a.pk.w_sigma[i];   // w_sigma | w_rgb are contiguous
@@ -300,12 +301,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
 }  // namespace
 
 int cnrf_tc_launch_bwd(const BwdArgs& b, int grid, cudaStream_t st) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(mlp_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+  {
+    static bool attr_set[CNRF_MAX_DEVICES] = {};
+    const cudaError_t e = cnrf_once_per_device(attr_set, [] {
+      cudaError_t e1 = cudaFuncSetAttribute(mlp_bwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+      if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(mlp_bwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BWD_SMEM);
+      return e1; });
     if (e != cudaSuccess) return (int)e;
-    attr_set = true;
   }
   if (b.g_x && (b.dx < 1 || b.dx > 64)) return CNRF_E_UNSUPPORTED;
   const bool timed = cnrf_ktimer_begin(CNRF_KT_BWD, b.M, st);

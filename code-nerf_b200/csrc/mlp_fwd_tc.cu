@@ -55,6 +55,7 @@ __device__ __forceinline__ bool fwait(uint64_t* bar, uint32_t parity, FBars* b, 
     if (clock64() - t0 > 2000000000LL) {
       b->abort_flag = 1;
       if (err) atomicExch(err, 1);
+      tc_fatal();
       return false;
     }
   }
@@ -69,6 +70,7 @@ __device__ __forceinline__ bool fwait_cluster(uint64_t* bar, uint32_t parity, FB
     if (clock64() - t0 > 2000000000LL) {
       b->abort_flag = 1;
       if (err) atomicExch(err, 1);
+      tc_fatal();
       return false;
     }
   }
@@ -246,7 +248,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     for (int i = 0; i < FRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); mbar_init(&bars->w_peer[i], 1); }
     for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], CG); mbar_init(&bars->acc_full[t], 1); }
     bars->abort_flag = 0;
-    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); tc_fatal(); }
     mbar_fence_init();
   }
   for (int i = tid; i < HEAD_FLOATS; i += NTHREADS) heads[i] = a.pk.w_sigma[i];   // w_sigma | w_rgb | b_dir2 are contiguous
@@ -483,12 +485,19 @@ int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
   if (pair_mode < 0) {
     const char* e = getenv("CNRF_FWD_CTA_PAIRS");
     pair_mode = e ? atoi(e) != 0 : 0;
-    cudaError_t e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
-    cudaError_t e2 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
-    if (e1 != cudaSuccess || e2 != cudaSuccess) { pair_mode = -1; return (int)(e1 != cudaSuccess ? e1 : e2); }
   }
+  {
+    static bool attr_set[CNRF_MAX_DEVICES] = {};
+    const cudaError_t e = cnrf_once_per_device(attr_set, [] {
+      cudaError_t e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+      if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+      return e1; });
+    if (e != cudaSuccess) return (int)e;
+  }
+#ifdef CNRF_TUNING
   { static int g_override = -1; if (g_override < 0) { const char* e = getenv("CNRF_FWD_GRID"); g_override = e ? atoi(e) : 0; }
     if (g_override > 0 && g_override < grid) grid = g_override; }       // tuning aid: fewer CTAs
+#endif
   const bool timed = cnrf_ktimer_begin(CNRF_KT_FWD, f.M, st);
   if (pair_mode && grid >= 2) {
     cudaLaunchConfig_t cfg = {};

@@ -78,16 +78,7 @@ struct TcChainArgs {   // mirrors the declaration in codenerf.cu
 };
 
 static inline size_t up1k(size_t b) { return (b + 1023) & ~size_t(1023); }
-static int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = 148;
-  }
-  return n;
-}
+static int sm_count() { return cnrf_sm_count(); }
 static Packed carve_packed(uint8_t* base) {
   Packed pk;
   pk.fwd = base;
@@ -98,9 +89,8 @@ static Packed carve_packed(uint8_t* base) {
   return pk;
 }
 static int* tc_error_ptr() {
-  static int* p = nullptr;
-  if (!p) cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_tc_error);
-  return p;
+  static int* p[CNRF_MAX_DEVICES] = {};
+  return cnrf_symbol_ptr(p, g_tc_error);
 }
 
 static inline int64_t tiles_of(int64_t M) { return (M + TILE - 1) / TILE; }
@@ -219,7 +209,7 @@ __device__ __forceinline__ bool dw_wait(uint64_t* bar, uint32_t parity, DwBars* 
   while (true) {
     if (mbar_try_wait(bar, parity)) return true;
     if (*(volatile int*)&b->abort_flag) return false;
-    if (clock64() - t0 > 2000000000LL) { b->abort_flag = 1; atomicExch(err, 1); return false; }
+    if (clock64() - t0 > 2000000000LL) { b->abort_flag = 1; atomicExch(err, 1); tc_fatal(); return false; }
   }
 }
 
@@ -278,7 +268,7 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
     }
     mbar_init(&bars->acc_full, 1);
     bars->abort_flag = 0;
-    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); }
+    if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); tc_fatal(); }
     mbar_fence_init();
   }
   if (warp == 1) tmem_alloc(&bars->tmem_slot, 512);
@@ -581,11 +571,11 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   int rc;
   if ((rc = cnrf_fill_zero(g->bias[CNRF_L_XYZ1], 256 * sizeof(float), st))) return rc;
   if ((rc = cnrf_fill_zero(g->bias[CNRF_L_DIR2], 256 * sizeof(float), st))) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(mlp_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM);
+  {
+    static bool attr_set[CNRF_MAX_DEVICES] = {};
+    const cudaError_t e = cnrf_once_per_device(attr_set, [] {
+      return cudaFuncSetAttribute(mlp_dw_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DW_SMEM); });
     if (e != cudaSuccess) return (int)e;
-    attr_set = true;
   }
   BwdArgs b;
   b.M = a.M; b.g_raw = g_raw; b.saved = sv; b.dy = dy; b.g_x = g_x_xyz; b.dx = a.dx; b.pk = pk; b.err = tc_error_ptr();
@@ -614,17 +604,20 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
     const int64_t halves = tiles * 2;
     // measured shares (B200, S = 160): reducer-heavy jobs are bound by their four reducer warps, not by their bytes
     static const int share148[DW_JOBS] = {22, 19, 31, 26, 13, 13, 24};
-    static int shares[DW_JOBS] = {0};
-    if (!shares[0]) {
-      const char* e = getenv("CNRF_DW_SHARES");       // tuning aid: seven comma-separated CTA counts
+    int shares[DW_JOBS];
+    int job_mask = (1 << DW_JOBS) - 1;
+    {
+      const char* e = nullptr;
+#ifdef CNRF_TUNING                                    // tuning builds only: seven comma-separated CTA counts, and a job subset
+      e = getenv("CNRF_DW_SHARES");                   // (wrong gradients, right timing)
+      if (const char* m = getenv("CNRF_DW_JOBMASK")) job_mask = atoi(m);
+#endif
       for (int j = 0; j < DW_JOBS; ++j) {
         int v = share148[j] * sm_count() / 148;
         if (e) { v = atoi(e); const char* n = strchr(e, ','); e = n ? n + 1 : nullptr; }
         shares[j] = v > 0 ? v : 1;
       }
     }
-    static int job_mask = -1;      // tuning aid: CNRF_DW_JOBMASK runs a subset of the jobs (wrong gradients, right timing)
-    if (job_mask < 0) { const char* e = getenv("CNRF_DW_JOBMASK"); job_mask = e ? atoi(e) : (1 << DW_JOBS) - 1; }
     int at = 0;
     for (int j = 0; j < DW_JOBS; ++j) {
       d.first[j] = at;

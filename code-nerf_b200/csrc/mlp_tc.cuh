@@ -73,6 +73,7 @@ __device__ __forceinline__ bool wait_bar(uint64_t* bar, uint32_t parity, Bars* b
     if (clock64() - t0 > 2000000000LL) {
       b->abort_flag = 1;
       if (err) atomicExch(err, 1);
+      tc_fatal();
       return false;
     }
   }

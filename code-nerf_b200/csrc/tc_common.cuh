@@ -32,12 +32,23 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug must not hang the GPU.  On timeout the error flag is raised and the caller bails out.
-__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, int* err_flag) {
+// A bounded barrier wait that times out leaves raw outputs, saved images and gradients partially written: on the product
+// path that must be LOUD.  After the sticky device flag is set the kernel executes `trap`, so the next synchronisation of
+// the stream raises a CUDA error in the caller (torch raises at the next sync / allocation).  -DCNRF_SOFT_ABORT keeps the
+// flag-and-bail-out behaviour for debugging a protocol change (read the flag with cnrf_debug_tc_error).
+__device__ __forceinline__ void tc_fatal() {
+#ifndef CNRF_SOFT_ABORT
+  asm volatile("trap;");
+#endif
+}
+// Bounded wait: a protocol bug must not hang the GPU.  On timeout the error flag is raised and, unless `fatal` is false
+// (the one-CTA descriptor probe of the tests), the kernel traps.
+__device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, int* err_flag, bool fatal = true) {
   for (uint32_t i = 0; i < (1u << 22); ++i) {
     if (mbar_try_wait(bar, parity)) return true;
   }
   if (err_flag) atomicExch(err_flag, 1);
+  if (fatal) tc_fatal();
   return false;
 }
 

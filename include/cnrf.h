@@ -307,6 +307,11 @@ int cnrf_debug_gemm(int32_t tc, const float* A, int64_t a_rs, int64_t a_cs, cons
                     float* C, int64_t ldc, int64_t M, int32_t N, int64_t K, int32_t accumulate, cnrf_stream_t stream);
 int cnrf_debug_umma(int32_t mode, const float* A, const float* B, float* D, int32_t N, int32_t K, int32_t* err,
                     cnrf_stream_t stream);
+/* TMEM read-throughput probe: `blocks` CTAs of `warps` warps sweep all 512 TMEM columns of their lane quarter `iters`
+ * times with tcgen05.ld (mode 0: .32x32b.x32 one load in flight, 1: .x32 two in flight, 2: .x64); clocks[b] = SM clocks of
+ * block b, sink = blocks*warps*32 words of scratch.  Bytes read per block = warps * iters * 64 KB. */
+int cnrf_debug_tmem_ld(int32_t blocks, int32_t warps, int32_t iters, int32_t mode, long long* clocks, uint32_t* sink,
+                       cnrf_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -169,7 +169,7 @@ def sample_pdf(ro: Tensor, rd: Tensor, weights: Tensor, z_vals: Tensor, num_fine
     bins = 0.5 * (z_vals[..., 1:] + z_vals[..., :-1])
     cdf = pdf_to_cdf(weights)
     if u is None:
-        u = torch.linspace(0.0, 1.0, steps=num_fine, dtype=weights.dtype).expand(cdf.shape[0], num_fine)
+        u = torch.linspace(0.0, 1.0, steps=num_fine, dtype=weights.dtype, device=weights.device).expand(cdf.shape[0], num_fine)
     samples, inds = invert_cdf(cdf, bins, u)
     z_all, _ = torch.sort(torch.cat((z_vals, samples.detach()), dim=-1), dim=-1)
     pts = ro[..., None, :] + rd[..., None, :] * z_all[..., :, None]

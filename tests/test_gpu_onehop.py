@@ -1,0 +1,443 @@
+"""ONE-HOP parity of the path bench.py actually runs -- bf16 tcgen05 chain + shared latent codes (+ ops.mse_pair +
+FusedAdamW) -- against the oracle, at the bench's chunk shape (4096 rays x 32 / 160 samples), and the remaining config-shape
+cases (C3 at 2048 rays / 64+64 / 128^2 with eval.py's own in-place pose_spherical, a full 128x128 parallel_image_render).
+
+Referee: the oracle restatement of the reference (oracle/codenerf_oracle.py, device-agnostic torch) executed in **fp64** on
+cuda:0 for the field tests (so the fp32 CUDA chain and the bf16 chain are both measured against the same, more accurate,
+answer and both errors are printed side by side), in fp32 for the whole-pipeline tests (the reference's own precision).
+The measured errors are written to gpurun_out/onehop_*.json (copied into DESIGN.md section 2).
+
+Stated bounds (asserted below):
+  raw field            fp32 chain <= 1e-3 abs (north_star)      bf16 chain <= 3e-2 abs
+  gradients, coherent  fp32 chain <= 2e-3 of the tensor's max   bf16 chain <= 3e-2 of the tensor's max
+  gradients, random    fp32 chain <= 2e-3 of the tensor's max   bf16 chain cosine >= 0.985, relative Frobenius <= 0.2
+("coherent" = all-positive upstream gradient, "random" = random-sign: per-sample terms cancel, so the ~0.5 % of ReLU
+masks that bf16 rounding flips show up relative to a much smaller sum.)
+"""
+import ast
+import json
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import codenerf_oracle as orc
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+T = torch.from_numpy
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available()
+    return torch.device("cuda", 0)
+
+
+def _record(name, payload):
+    out = os.path.join(ROOT, "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, f"onehop_{name}.json"), "w") as fh:
+            json.dump(payload, fh, indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
+def _errs(got, ref):
+    a, b = got.double().flatten(), ref.double().flatten()
+    assert torch.isfinite(a).all()
+    return {"max_abs": (a - b).abs().max().item(),
+            "max_norm": ((a - b).abs().max() / b.abs().max().clamp_min(1e-300)).item(),
+            "fro": ((a - b).norm() / b.norm().clamp_min(1e-300)).item(),
+            "cos": (torch.dot(a, b) / (a.norm() * b.norm()).clamp_min(1e-300)).item()}
+
+
+def _tc_ok():
+    from codenerf_b200 import _lib
+    assert _lib.load().cnrf_debug_tc_error() == 0, "a tensor-core kernel timed out on a barrier"
+
+
+def _bench_rays(N, S, g, near=0.8, far=1.8):
+    """Rays of an SRN-cars view: camera on the radius-1.3 sphere looking at the origin, sorted depths in [near, far]."""
+    ro = torch.tensor([0.0, 0.0, 1.3]).expand(N, 3) + 0.01 * torch.randn(N, 3, generator=g)
+    rd = torch.randn(N, 3, generator=g) * 0.22 + torch.tensor([0.0, 0.0, -1.0])
+    z = torch.sort(torch.rand(N, S, generator=g) * (far - near) + near, dim=-1).values
+    return ro, rd, ro[:, None, :] + rd[:, None, :] * z[..., None]
+
+
+def _drop_in_models(dev, seeds=(1, 2)):
+    import view_synthesis.models as models
+    mods = []
+    for s in seeds:
+        m = models.CodeNeRFModel(256, 1, 256, 256, 10, 4, True, True)
+        m.load_state_dict({k: v.clone() for k, v in orc.make_codenerf_params(s).items()})
+        mods.append(m.to(dev))
+    return mods
+
+
+def _embedders(dev):
+    import view_synthesis.nerf as nerf
+    return (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+
+
+# =====================================================================================================================
+# (a) + (d): forward_pass and its full backward at the bench chunk shape, codes from ShapeTextureEmbedding
+# =====================================================================================================================
+@pytest.mark.parametrize("S", [32, 160])
+@pytest.mark.parametrize("pattern,num_objects", [("one_id", 2458), ("four_runs", 4612)])
+def test_field_bf16_shared_codes_vs_fp64_oracle_at_bench_chunk(dev, S, pattern, num_objects):
+    """train.py:78-96 gives a 4096-ray chunk the object id of its image ("one_id"); "four_runs" puts four images in a chunk
+    (chairs-sized table, C4).  Dense table gradients are compared with the autograd of the oracle's embedding_lookup."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    N = 4096
+    g = torch.Generator().manual_seed(1000 + S + num_objects)
+    ro, rd, pts = _bench_rays(N, S, g)
+    ids = (torch.full((N,), 1234, dtype=torch.int64) if pattern == "one_id" else
+           torch.tensor([7, num_objects - 1, 0, 1234]).repeat_interleave(N // 4))
+    tab_s, tab_t = torch.randn(num_objects, 256, generator=g), torch.randn(num_objects, 256, generator=g)
+    graws = {"coherent": torch.rand(N, S, 4, generator=g) + 0.5, "random": torch.randn(N, S, 4, generator=g)}
+    p0 = orc.make_codenerf_params(5)
+    f64 = torch.float64
+    report = {}
+    try:
+        for kind, graw in graws.items():
+            # ---- referee: the oracle in fp64 on the GPU
+            p = {k: v.to(dev, f64).requires_grad_(True) for k, v in p0.items()}
+            ts, tt = tab_s.to(dev, f64).requires_grad_(True), tab_t.to(dev, f64).requires_grad_(True)
+            z_s, z_t = orc.embedding_lookup(ts, tt, ids.to(dev))
+            raw = orc.forward_pass(p, rd.to(dev, f64), pts.to(dev, f64), z_s, z_t,
+                                   orc.frequency_bands(10, True, f64).to(dev), orc.frequency_bands(4, True, f64).to(dev))
+            raw.backward(graw.to(dev, f64))
+            ref = {"raw": raw.detach(), "table_s": ts.grad, "table_t": tt.grad, **{k: v.grad for k, v in p.items()}}
+            del raw, z_s, z_t
+            torch.cuda.empty_cache()
+            # ---- the drop-in, both precisions, through ShapeTextureEmbedding + forward_pass
+            for prec in ("fp32", "bf16"):
+                nerf.set_precision(prec)
+                m = models.CodeNeRFModel(256, 1, 256, 256, 10, 4, True, True)
+                m.load_state_dict({k: v.clone() for k, v in p0.items()})
+                m = m.to(dev)
+                emb = models.ShapeTextureEmbedding(num_objects, 256, 256)
+                emb.load_state_dict({"shape_embedding.weight": tab_s.clone(), "texture_embedding.weight": tab_t.clone()})
+                emb = emb.to(dev)
+                codes = emb(ids.to(dev))
+                assert hasattr(codes[0], "_cnrf_code_source")
+                out = nerf.forward_pass(m, _embedders(dev), rd.to(dev), pts.to(dev), codes)
+                out.backward(graw.to(dev))
+                _tc_ok()
+                got = {"raw": out.detach(), "table_s": emb.shape_embedding.weight.grad, "table_t": emb.texture_embedding.weight.grad,
+                       **{k: v.grad for k, v in m.named_parameters()}}
+                assert sorted(got) == sorted(ref)
+                report[f"{kind}/{prec}"] = {k: _errs(got[k], ref[k]) for k in ref}
+                # rows of the tables that no ray used stay exactly zero (dense gradient, as nn.Embedding's backward)
+                unused = torch.ones(num_objects, dtype=torch.bool, device=dev)
+                unused[ids.to(dev)] = False
+                assert float(got["table_s"][unused].abs().max()) == 0.0 and float(got["table_t"][unused].abs().max()) == 0.0
+            del ref
+            torch.cuda.empty_cache()
+    finally:
+        nerf.set_precision("fp32")
+    _record(f"field_{pattern}_S{S}", report)
+    for case, errs in report.items():
+        worst = max(errs.items(), key=lambda kv: kv[1]["max_norm"] if kv[0] != "raw" else -1)
+        print(f"\n[{pattern} S={S}] {case}: raw max abs {errs['raw']['max_abs']:.3e}; gradients: worst max-normalised "
+              f"{worst[1]['max_norm']:.3e} ({worst[0]}), worst Frobenius {max(v['fro'] for k, v in errs.items() if k != 'raw'):.3e}, "
+              f"worst cosine {min(v['cos'] for k, v in errs.items() if k != 'raw'):.5f}")
+    for case, errs in report.items():
+        kind, prec = case.split("/")
+        grads = {k: v for k, v in errs.items() if k != "raw"}
+        if prec == "fp32":
+            assert errs["raw"]["max_abs"] < 1e-3, (case, errs["raw"])
+            assert max(v["max_norm"] for v in grads.values()) < 2e-3, (case, {k: f"{v['max_norm']:.2e}" for k, v in grads.items()})
+        else:
+            assert errs["raw"]["max_abs"] < 3e-2, (case, errs["raw"])
+            if kind == "coherent":
+                assert max(v["max_norm"] for v in grads.values()) < 3e-2, (case, {k: f"{v['max_norm']:.2e}" for k, v in grads.items()})
+            else:
+                assert min(v["cos"] for v in grads.values()) > 0.985 and max(v["fro"] for v in grads.values()) < 0.2, \
+                    (case, {k: (round(v["cos"], 4), round(v["fro"], 3)) for k, v in grads.items()})
+
+
+# =====================================================================================================================
+# (b) the whole chunk step of bench.py for three optimiser steps vs the oracle + torch.optim.AdamW
+# =====================================================================================================================
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_chunk_step_three_fused_adamw_steps_vs_oracle(dev, precision):
+    """embedding lookup + predict_radiance_and_render + ops.mse_pair + backward + FusedAdamW (bench.py:247-267), three steps
+    with the config's rates (MLPs 1e-4, codes 1e-3; utils/util.py:159-164), against the oracle pipeline + two mse_loss +
+    torch.optim.AdamW on the same GPU with the same sample offsets.  AdamW's first steps move every parameter by about
+    lr * sign(gradient), so the comparison is on the losses and on the parameter UPDATE theta_3 - theta_0 of every tensor."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    from codenerf_b200 import ops
+    from codenerf_b200.optim import FusedAdamW
+    N, Sc, Nf, num_objects, steps = 4096, 32, 128, 2458, 3
+    g = torch.Generator().manual_seed(77)
+    tab_s, tab_t = torch.randn(num_objects, 256, generator=g), torch.randn(num_objects, 256, generator=g)
+    batches = []
+    for s in range(steps):
+        ro, rd, _ = _bench_rays(N, 1, g)
+        batches.append({"ro": ro.to(dev), "rd": rd.to(dev), "tgt": torch.rand(N, 3, generator=g).to(dev),
+                        "ids": torch.full((N,), 100 + s, dtype=torch.int64, device=dev),
+                        "t_rand": torch.rand(N, Sc, generator=g).to(dev), "u": torch.rand(N, Nf, generator=g).to(dev)})
+    groups = lambda a, b, c: [{"params": a}, {"params": b}, {"params": c, "lr": 1e-3}]
+
+    # ---- oracle (fp32 eager torch on the GPU: the reference's own arithmetic)
+    pc = {k: v.to(dev).requires_grad_(True) for k, v in orc.make_codenerf_params(1).items()}
+    pf = {k: v.to(dev).requires_grad_(True) for k, v in orc.make_codenerf_params(2).items()}
+    ts, tt = tab_s.to(dev).requires_grad_(True), tab_t.to(dev).requires_grad_(True)
+    cfg = orc.RenderConfig(Sc, Nf)
+    for k in ("freqs_xyz", "freqs_dir", "z", "lower", "upper"):
+        setattr(cfg, k, getattr(cfg, k).to(dev))
+    opt_o = torch.optim.AdamW(groups(list(pc.values()), list(pf.values()), [ts, tt]), lr=1e-4)
+    start = {**{"coarse." + k: v.detach().clone() for k, v in pc.items()}, **{"fine." + k: v.detach().clone() for k, v in pf.items()},
+             "table_s": ts.detach().clone(), "table_t": tt.detach().clone()}
+    losses_o = []
+    for b in batches:
+        z_s, z_t = orc.embedding_lookup(ts, tt, b["ids"])
+        rc, rf, _ = orc.predict_radiance_and_render(cfg, b["ro"], b["rd"], pc, pf, z_s, z_t, b["t_rand"], b["u"])
+        loss = torch.nn.functional.mse_loss(rc, b["tgt"]) + torch.nn.functional.mse_loss(rf, b["tgt"])
+        opt_o.zero_grad()
+        loss.backward()
+        opt_o.step()
+        losses_o.append(float(loss.detach()))
+    end_o = {**{"coarse." + k: v.detach() for k, v in pc.items()}, **{"fine." + k: v.detach() for k, v in pf.items()},
+             "table_s": ts.detach(), "table_t": tt.detach()}
+
+    # ---- the bench's chunk step
+    nerf.set_precision(precision)
+    real_rand = torch.rand
+    try:
+        mc, mf = _drop_in_models(dev)
+        emb = models.ShapeTextureEmbedding(num_objects, 256, 256)
+        emb.load_state_dict({"shape_embedding.weight": tab_s.clone(), "texture_embedding.weight": tab_t.clone()})
+        emb = emb.to(dev)
+        opt = FusedAdamW(groups(mc.parameters(), mf.parameters(), emb.parameters()), lr=1e-4)
+        ps = nerf.PointSampler(Sc, Nf, 0.8, 1.8, "lindepth", True, torch.float32, dev)
+        embedders = _embedders(dev)
+        losses = []
+        for b in batches:
+            codes = emb(b["ids"])
+            q = [b["t_rand"], b["u"]]
+            torch.rand = lambda *a, **k: q.pop(0)
+            rc, rf = nerf.predict_radiance_and_render((b["ro"], b["rd"]), ps, embedders, mc, mf, codes)
+            torch.rand = real_rand
+            lc, lf, loss = ops.mse_pair(rc, rf, b["tgt"])
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            losses.append(float(loss.detach()))
+        _tc_ok()
+    finally:
+        torch.rand = real_rand
+        nerf.set_precision("fp32")
+    end = {**{"coarse." + k: v.detach() for k, v in mc.named_parameters()}, **{"fine." + k: v.detach() for k, v in mf.named_parameters()},
+           "table_s": emb.shape_embedding.weight.detach(), "table_t": emb.texture_embedding.weight.detach()}
+    rep = {"losses": losses, "losses_oracle": losses_o, "update": {}}
+    for k in start:
+        du, do = end[k] - start[k], end_o[k] - start[k]
+        if k.startswith("table"):      # weight decay moves every table row (identically in both): checked apart from the used rows
+            used = torch.zeros(num_objects, dtype=torch.bool, device=dev)
+            used[[100, 101, 102]] = True
+            assert torch.allclose(end[k][~used], end_o[k][~used], rtol=0, atol=1e-6), k
+            du, do = du[used], do[used]
+        rep["update"][k] = dict(_errs(du, do), max_param_diff=float((end[k] - end_o[k]).abs().max()))
+    _record(f"chunk_step_{precision}", rep)
+    worst_cos = min(v["cos"] for v in rep["update"].values())
+    worst_fro = max(v["fro"] for v in rep["update"].values())
+    worst_abs = max(v["max_param_diff"] for v in rep["update"].values())
+    print(f"\n[{precision}] losses {losses} vs oracle {losses_o}; update cosine >= {worst_cos:.4f}, relative Frobenius <= "
+          f"{worst_fro:.3f}, largest parameter difference {worst_abs:.2e}")
+    rtol = 1e-4 if precision == "fp32" else 2e-2
+    np.testing.assert_allclose(losses, losses_o, rtol=rtol)
+    # three AdamW steps cannot move a parameter by more than ~3 lr (codes: lr 1e-3), so 6 lr bounds any difference; the
+    # discriminating check is the direction and size of the update of every one of the 38 tensors
+    assert worst_abs <= 6.5e-3
+    if precision == "fp32":
+        assert worst_cos > 0.99 and worst_fro < 0.15, {k: (round(v["cos"], 4), round(v["fro"], 3)) for k, v in rep["update"].items()}
+    else:
+        assert worst_cos > 0.90 and worst_fro < 0.45, {k: (round(v["cos"], 4), round(v["fro"], 3)) for k, v in rep["update"].items()}
+
+
+# =====================================================================================================================
+# (c) C3 at its config shape with eval.py's own pose_spherical
+# =====================================================================================================================
+def _reference_pose_spherical():
+    """eval.py:22-38 verbatim: the function's source is cut out of the reference copy (oracle/_ref/eval.py, or the
+    reference tree itself) and compiled -- in-place writes into torch.eye and all (CopySlices nodes in autograd)."""
+    for base in (os.path.join(ROOT, "oracle", "_ref"), os.environ.get("CODENERF_REFERENCE", "/root/reference")):
+        path = os.path.join(base, "eval.py")
+        if os.path.exists(path):
+            break
+    else:
+        pytest.fail("no reference eval.py (run `python oracle/make_ref.py` in the build container)")
+    src = open(path).read()
+    fn = next(n for n in ast.parse(src).body if isinstance(n, ast.FunctionDef) and n.name == "pose_spherical")
+    ns = {"torch": torch}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), path, "exec"), ns)
+    return ns["pose_spherical"]
+
+
+def test_c3_config_shape_with_reference_pose_spherical(dev):
+    """config/srn-cars-code-3080-val.yml: 2048 rays of a 128 x 128 view, 64 + 64 samples, AdamW on (z_s, z_t) 1e-2,
+    (theta, phi) 5e-2, rho 1e-1 (eval.py:126-138), regulariser 1e-6, 24 iterations of eval.py:140-168 -- through the
+    drop-in (pose gradients select the fp32 chain) and through the oracle, same pixel draws and sample offsets."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    pose_spherical = _reference_pose_spherical()
+    Hh = Ww = 128
+    n_rays, Sc, Nf, steps, lam = 2048, 64, 64, 24, 1e-6
+    rng = np.random.default_rng(303)
+    K = torch.tensor([[131.25, 0, Ww / 2, 0], [0, 131.25, Hh / 2, 0], [0, 0, 1, 0], [0, 0, 0, 1]], dtype=torch.float32)
+    pc, pf = orc.make_codenerf_params(41), orc.make_codenerf_params(42)
+    yy, xx = np.mgrid[0:Hh, 0:Ww].astype(np.float32)
+    inside = ((xx - 60) ** 2 / 30 ** 2 + (yy - 70) ** 2 / 18 ** 2) < 1.0
+    img = T(np.stack([np.where(inside, 0.3 + 0.2 * c + 0.3 * np.cos((xx + yy) / 17.0), 1.0) for c in range(3)], -1)
+            .astype(np.float32).reshape(-1, 3))
+    sels = [rng.permutation(Hh * Ww)[:n_rays][None] for _ in range(steps)]
+    draws = [(T(rng.uniform(size=(n_rays, Sc)).astype(np.float32)), T(rng.uniform(size=(n_rays, Nf)).astype(np.float32)))
+             for _ in range(steps)]
+    zs0, zt0 = T(rng.normal(size=(1, 256)).astype(np.float32)), T(rng.normal(size=(1, 256)).astype(np.float32))
+
+    def leaves():
+        return [t.clone().to(dev).requires_grad_(True) for t in
+                (zs0, zt0, torch.tensor([1.57]), torch.tensor([0.0]), torch.tensor([1.30]))]      # eval.py:126-131
+
+    def optimiser(lv):
+        return torch.optim.AdamW([{"params": lv[:2]}, {"params": lv[2:4], "lr": 5e-2}, {"params": lv[4:], "lr": 1e-1}], lr=1e-2)
+
+    def loss_of(rc, rf, tgt, z_s, z_t):
+        return torch.nn.functional.mse_loss(rc[..., :3], tgt) + torch.nn.functional.mse_loss(rf[..., :3], tgt) + \
+            lam * (torch.norm(z_s, p=2) + torch.norm(z_t, p=2))
+
+    # ---- oracle on the GPU (fp32)
+    cfg = orc.RenderConfig(Sc, Nf)
+    for k in ("freqs_xyz", "freqs_dir", "z", "lower", "upper"):
+        setattr(cfg, k, getattr(cfg, k).to(dev))
+    pcd = {k: v.to(dev) for k, v in pc.items()}
+    pfd = {k: v.to(dev) for k, v in pf.items()}
+    dirs = orc.camera_directions(Hh, Ww, K).to(dev)
+    lv_o = leaves()
+    opt_o = optimiser(lv_o)
+    traj_o, grads_o = [], None
+    for it in range(steps):
+        pose = pose_spherical(lv_o[2], lv_o[3], lv_o[4])[None, :]
+        ro, rd = orc.sample_rays(dirs, pose, sels[it])
+        z_s, z_t = lv_o[0].expand(n_rays, -1), lv_o[1].expand(n_rays, -1)
+        rc, rf, _ = orc.predict_radiance_and_render(cfg, ro, rd, pcd, pfd, z_s, z_t, draws[it][0].to(dev), draws[it][1].to(dev))
+        loss = loss_of(rc, rf, img[sels[it][0]].to(dev), z_s, z_t)
+        opt_o.zero_grad()
+        loss.backward()
+        if it == 0:
+            grads_o = [l.grad.clone() for l in lv_o]
+        opt_o.step()
+        traj_o.append([float(loss.detach())] + [float(l.detach().flatten()[0]) for l in lv_o[2:]])
+
+    # ---- the drop-in
+    mods = []
+    for p in (pc, pf):
+        m = models.CodeNeRFModel(256, 1, 256, 256, 10, 4, True, True)
+        m.load_state_dict({k: v.clone() for k, v in p.items()})
+        mods.append(m.to(dev))
+    rs = nerf.RaySampler(Hh, Ww, K, n_rays, dev, torch.float32)
+    ps = nerf.PointSampler(Sc, Nf, 0.8, 1.8, "lindepth", True, torch.float32, dev)
+    lv = leaves()
+    opt = optimiser(lv)
+    traj, grads = [], None
+    real_rand, real_perm = torch.rand, np.random.permutation
+    nerf.set_precision("bf16")            # the library default: the pose-gradient request must pick its own precision
+    try:
+        for it in range(steps):
+            pose = pose_spherical(lv[2], lv[3], lv[4])[None, :]                                   # eval.py:145
+            np.random.permutation = lambda a, _s=sels[it]: np.concatenate(
+                [_s[0], np.setdiff1d(np.arange(np.size(a) if np.ndim(a) else a), _s[0])])
+            ro, rd, sel = rs.sample(tform_cam2world=pose)                                          # eval.py:146
+            np.random.permutation = real_perm
+            assert np.array_equal(np.asarray(sel).reshape(-1), sels[it][0])
+            z_s, z_t = lv[0].expand(ro.shape[0], -1), lv[1].expand(ro.shape[0], -1)                # eval.py:149
+            q = [d.to(dev) for d in draws[it]]
+            torch.rand = lambda *a, **k: q.pop(0)
+            rc, rf = nerf.predict_radiance_and_render((ro, rd), ps, _embedders(dev), mods[0], mods[1], (z_s, z_t))
+            torch.rand = real_rand
+            loss = loss_of(rc, rf, img[sels[it][0]].to(dev), z_s, z_t)
+            opt.zero_grad()
+            loss.backward()
+            if it == 0:
+                grads = [l.grad.clone() for l in lv]
+            opt.step()
+            traj.append([float(loss.detach())] + [float(l.detach().flatten()[0]) for l in lv[2:]])
+        _tc_ok()
+    finally:
+        torch.rand, np.random.permutation = real_rand, real_perm
+        nerf.set_precision("fp32")
+    g_err = {n: _errs(a, b) for a, b, n in zip(grads, grads_o, ("z_s", "z_t", "theta", "phi", "rho"))}
+    traj, traj_o = np.array(traj), np.array(traj_o)
+    _record("c3_config_shape", {"first_step_gradients": g_err, "trajectory": traj.tolist(), "trajectory_oracle": traj_o.tolist()})
+    print("\nC3 first-step gradients vs oracle:", {k: f"{v['max_norm']:.2e}" for k, v in g_err.items()})
+    print("C3 (loss, theta, phi, rho) after 24 iterations:", traj[-1], "oracle:", traj_o[-1])
+    np.testing.assert_allclose(traj[0, 0], traj_o[0, 0], rtol=1e-4)
+    for n, e in g_err.items():
+        assert e["max_norm"] < 5e-3, (n, e)
+    np.testing.assert_allclose(traj[:, 0], traj_o[:, 0], rtol=1e-2)                      # 24 coupled AdamW steps stay together
+    np.testing.assert_allclose(traj[:, 1:], traj_o[:, 1:], atol=2e-2)                    # theta, phi, rho (rates 5e-2 / 1e-1)
+    codes_moved = float((lv[0].detach() - zs0.to(dev)).abs().max())
+    assert 0.05 < codes_moved < 0.5, codes_moved                                         # ~24 steps of lr 1e-2
+    assert _errs(lv[0].detach() - zs0.to(dev), lv_o[0].detach() - zs0.to(dev))["cos"] > 0.98
+
+
+# =====================================================================================================================
+# (e) a13: a full 128 x 128 view through parallel_image_render
+# =====================================================================================================================
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-3), ("bf16", 2e-2)])
+def test_parallel_image_render_full_view_vs_oracle(dev, precision, tol):
+    """nerf/__init__.py:137-226 on one GPU: get_bundle of the whole 128 x 128 image, stride-0 codes, chunks of 4096 rays,
+    perturb = False (eval.py:183 renders with the samplers it trained with; False fixes the sample offsets), against the
+    oracle pipeline on the same rays.  Bounds on rgb: 1e-3 abs in fp32 (north_star), 2e-2 abs for the bf16 chain."""
+    import view_synthesis.nerf as nerf
+    Hh = Ww = 128
+    K = torch.tensor([[131.25, 0, Ww / 2, 0], [0, 131.25, Hh / 2, 0], [0, 0, 1, 0], [0, 0, 0, 1]], dtype=torch.float32)
+    g = torch.Generator().manual_seed(9)
+    theta, phi = 0.7, -0.4
+    pose = np.eye(4, dtype=np.float32)
+    pose[0, 0], pose[1, 0] = -np.sin(phi), np.cos(phi)
+    pose[0, 1], pose[1, 1], pose[2, 1] = -np.sin(theta) * np.cos(phi), -np.sin(theta) * np.sin(phi), np.cos(theta)
+    pose[0, 2], pose[1, 2], pose[2, 2] = np.cos(theta) * np.cos(phi), np.cos(theta) * np.sin(phi), np.sin(theta)
+    pose[:3, 3] = 1.3 * pose[:3, 2]
+    pose = T(pose)[None].to(dev)
+    zs, zt = torch.randn(1, 256, generator=g).to(dev), torch.randn(1, 256, generator=g).to(dev)
+    mods = _drop_in_models(dev, seeds=(11, 12))
+    cfg = types.SimpleNamespace(nerf=types.SimpleNamespace(validation=types.SimpleNamespace(chunksize=4096)))
+    rs = nerf.RaySampler(Hh, Ww, K, 4096, dev, torch.float32)
+    ps = nerf.PointSampler(32, 128, 0.8, 1.8, "lindepth", False, torch.float32, dev)
+    nerf.set_precision(precision)
+    try:
+        rgb = nerf.parallel_image_render(cfg, pose, [zs, zt], {"nerf_coarse": mods[0], "nerf_fine": mods[1]}, (rs, ps),
+                                         _embedders(dev), dev)
+        _tc_ok()
+    finally:
+        nerf.set_precision("fp32")
+    assert rgb.shape == (Hh * Ww, 3) and not rgb.requires_grad
+    # oracle, chunk by chunk (the F6 view-direction pairing depends on the chunk a ray is rendered in)
+    ocfg = orc.RenderConfig(32, 128)
+    for k in ("freqs_xyz", "freqs_dir", "z", "lower", "upper"):
+        setattr(ocfg, k, getattr(ocfg, k).to(dev))
+    pc = {k: v.to(dev) for k, v in orc.make_codenerf_params(11).items()}
+    pf = {k: v.to(dev) for k, v in orc.make_codenerf_params(12).items()}
+    ro, rd = orc.get_bundle(orc.camera_directions(Hh, Ww, K).to(dev), pose)
+    ro, rd = ro.reshape(-1, 3), rd.reshape(-1, 3)
+    ref = []
+    with torch.no_grad():
+        for i in range(0, Hh * Ww, 4096):
+            n = min(4096, Hh * Ww - i)
+            _, rf, _ = orc.predict_radiance_and_render(ocfg, ro[i:i + n], rd[i:i + n], pc, pf, zs.expand(n, -1), zt.expand(n, -1),
+                                                       None, None)
+            ref.append(rf)
+    ref = torch.cat(ref)
+    err = (rgb - ref).abs().max().item()
+    _record(f"parallel_image_render_{precision}", {"max_abs_rgb": err, "mean_abs_rgb": (rgb - ref).abs().mean().item()})
+    print(f"\nparallel_image_render 128x128 [{precision}]: max |rgb - oracle| = {err:.3e}")
+    assert err < tol

@@ -44,3 +44,23 @@ def test_fused_adamw_refuses_cpu_parameters():
     p.grad = torch.ones(4)
     with pytest.raises(_lib.CnrfError):
         FusedAdamW([p]).step()
+
+
+@pytest.mark.gpu
+def test_fused_adamw_more_than_one_batch_with_an_empty_tensor():
+    """More parameters than one launch batch holds (40) with a zero-element tensor among them: every tensor must be stepped
+    exactly once (the batch loop resumes at the first row the previous batch did not consume)."""
+    from codenerf_b200.optim import FusedAdamW
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    shapes = [(7,), (0,), (33, 5)] + [(3 + i,) for i in range(50)]
+    ps = [torch.randn(*s, device=dev).requires_grad_(True) for s in shapes]
+    ref = [p.detach().clone().requires_grad_(True) for p in ps]
+    a, b = FusedAdamW(ps, lr=1e-2), torch.optim.AdamW(ref, lr=1e-2)
+    for _ in range(3):
+        for p, r in zip(ps, ref):
+            g = torch.randn_like(p)
+            p.grad, r.grad = g.clone(), g.clone()
+        a.step(); b.step()
+    for p, r in zip(ps, ref):
+        assert torch.allclose(p, r, rtol=1e-5, atol=1e-6)
