@@ -446,9 +446,10 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   return cnrf_tc_chain_fwd(a, raw, tc_saved, tc_saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
 
+// accumulate_tables (shared-code mode only): g_z_s / g_z_t already hold another model's table gradients -- add to them
 int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const FieldIn& in, const float* g_raw,
                       const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t,
-                      float* g_x_xyz, float* g_x_dir, void* ws, size_t ws_bytes, cudaStream_t st) {
+                      float* g_x_xyz, float* g_x_dir, void* ws, size_t ws_bytes, cudaStream_t st, bool accumulate_tables = false) {
   Dims d = dims_of(s);
   if (!s->keep || !saved) return CNRF_E_WORKSPACE;
   Arena w(ws, ws_bytes);
@@ -491,10 +492,12 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
                         w.base + w.off, w.cap - w.off, st));
   RUN(per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, dt, tmp, gz_s, gz_t, g_x_dir, st));
   if (in.ids) {          // one row per run -> dense table gradients (what torch.nn.Embedding's backward produces)
-    FillBatch f;
-    f.add(g_z_s, in.num_codes * d.C);
-    f.add(g_z_t, in.num_codes * d.C);
-    RUN(cnrf_fill_batch(f, st));
+    if (!accumulate_tables) {
+      FillBatch f;
+      f.add(g_z_s, in.num_codes * d.C);
+      f.add(g_z_t, in.num_codes * d.C);
+      RUN(cnrf_fill_batch(f, st));
+    }
     RUN(cnrf_scatter_code_grads(in.ids, sc.runs, d.N, d.C, gz_s, g_z_s, d.C, st));
     RUN(cnrf_scatter_code_grads(in.ids, sc.runs, d.N, d.C, gz_t, g_z_t, d.C, st));
   }
@@ -597,8 +600,7 @@ extern "C" size_t cnrf_field_workspace_bytes(const cnrf_field_shape* s, int32_t 
   return field_scratch_bytes(dims_of(s), s->precision, backward) + cnrf_codenerf_workspace_bytes(s, backward);
 }
 
-namespace {
-int field_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+int cnrf_field_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
                    const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
                    int64_t num_codes, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, float* raw,
                    void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes, cudaStream_t st) {
@@ -616,14 +618,16 @@ int field_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
   return codenerf_fwd_impl(s, p, in, raw, saved, saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
 
-int field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+int cnrf_field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
                    const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
                    int64_t num_codes, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
                    const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s,
-                   float* g_z_t, float* g_pts, float* g_rd, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+                   float* g_z_t, float* g_pts, float* g_rd, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                   bool accumulate_tables) {
   RUN(check_common(s, p));
-  CNRF_REQUIRE(pts && rd && freqs_xyz && freqs_dir && z_s && z_t && g_raw && g && g_z_s && g_z_t && workspace,
-               CNRF_E_NULL);
+  // the bf16 chain saved its own encoded inputs: the points are only read again in the fp32 mode or for point gradients
+  CNRF_REQUIRE((pts || (s->precision == CNRF_PRECISION_BF16 && !g_pts)) && rd && freqs_xyz && freqs_dir && z_s && z_t && g_raw &&
+               g && g_z_s && g_z_t && workspace, CNRF_E_NULL);
   int incx, incd;
   RUN(check_field(s, L_xyz, L_dir, incx, incd));
   Dims d = dims_of(s);
@@ -634,7 +638,7 @@ int field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
   RUN(field_encode(d, s->precision, pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
   FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx, ids, num_codes};
   RUN(codenerf_bwd_impl(s, p, in, g_raw, saved, saved_bytes, g, g_z_s, g_z_t, g_pts ? f.g_xemb : nullptr,
-                        g_rd ? f.g_demb : nullptr, w.base + w.off, w.cap - w.off, st));
+                        g_rd ? f.g_demb : nullptr, w.base + w.off, w.cap - w.off, st, accumulate_tables));
   if (g_pts) RUN(cnrf_pos_embed_bwd_ld(pts, f.g_xemb, d.M, 3, freqs_xyz, L_xyz, incx, d.dx, g_pts, st));
   if (g_rd) {
     RUN(cnrf_pos_embed_bwd_ld(f.dirn, f.g_demb, d.N, 3, freqs_dir, L_dir, incd, d.dd, f.g_dirn, st));
@@ -643,14 +647,13 @@ int field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
   }
   return CNRF_OK;
 }
-}  // namespace
 
 extern "C" int cnrf_field_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts,
                               const float* rd, const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir,
                               int32_t L_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
                               float* raw, void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes,
                               cnrf_stream_t stream) {
-  return field_fwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, nullptr, 0, z_s, ld_zs, z_t, ld_zt, raw, saved,
+  return cnrf_field_fwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, nullptr, 0, z_s, ld_zs, z_t, ld_zt, raw, saved,
                         saved_bytes, workspace, workspace_bytes, as_stream(stream));
 }
 
@@ -660,8 +663,8 @@ extern "C" int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_par
                               const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g,
                               float* g_z_s, float* g_z_t, float* g_pts, float* g_rd, void* workspace,
                               size_t workspace_bytes, cnrf_stream_t stream) {
-  return field_bwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, nullptr, 0, z_s, ld_zs, z_t, ld_zt, g_raw, saved,
-                        saved_bytes, g, g_z_s, g_z_t, g_pts, g_rd, workspace, workspace_bytes, as_stream(stream));
+  return cnrf_field_bwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, nullptr, 0, z_s, ld_zs, z_t, ld_zt, g_raw, saved,
+                             saved_bytes, g, g_z_s, g_z_t, g_pts, g_rd, workspace, workspace_bytes, as_stream(stream), false);
 }
 
 // Shared-code variants: the embedding lookup of train.py:96 (ShapeTextureEmbedding.forward, models/model.py:100-103)
@@ -673,7 +676,7 @@ extern "C" int cnrf_field_fwd_ids(const cnrf_field_shape* s, const cnrf_codenerf
                                   void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
   CNRF_REQUIRE(ids, CNRF_E_NULL);
   CNRF_REQUIRE(num_codes > 0, CNRF_E_SHAPE);
-  return field_fwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, ids, num_codes, tab_s, ld_s, tab_t, ld_t, raw,
+  return cnrf_field_fwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, ids, num_codes, tab_s, ld_s, tab_t, ld_t, raw,
                         saved, saved_bytes, workspace, workspace_bytes, as_stream(stream));
 }
 
@@ -685,7 +688,7 @@ extern "C" int cnrf_field_bwd_ids(const cnrf_field_shape* s, const cnrf_codenerf
                                   void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
   CNRF_REQUIRE(ids, CNRF_E_NULL);
   CNRF_REQUIRE(num_codes > 0, CNRF_E_SHAPE);
-  return field_bwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, ids, num_codes, tab_s, ld_s, tab_t, ld_t, g_raw,
-                        saved, saved_bytes, g, g_tab_s, g_tab_t, nullptr, nullptr, workspace, workspace_bytes,
-                        as_stream(stream));
+  return cnrf_field_bwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, ids, num_codes, tab_s, ld_s, tab_t, ld_t, g_raw,
+                             saved, saved_bytes, g, g_tab_s, g_tab_t, nullptr, nullptr, workspace, workspace_bytes,
+                             as_stream(stream), false);
 }

@@ -80,6 +80,19 @@ int cnrf_strided_rowsum(const float* X, int64_t ld_x, int64_t G, int64_t g_strid
 int cnrf_colsum(const float* X, int64_t ld_x, int64_t M, int N, float* out, cudaStream_t st);
 int cnrf_fill_zero(void* p, size_t bytes, cudaStream_t st);
 
+// ---- codenerf.cu: forward_pass with or without the embedding lookup folded in (ids != NULL: z_s / z_t are the tables) ------
+int cnrf_field_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                        const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
+                        int64_t num_codes, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, float* raw,
+                        void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes, cudaStream_t st);
+// accumulate_tables (ids mode): g_z_s / g_z_t already hold another model's dense table gradients; add instead of overwrite
+int cnrf_field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                        const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const int64_t* ids,
+                        int64_t num_codes, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt,
+                        const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s,
+                        float* g_z_t, float* g_pts, float* g_rd, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                        bool accumulate_tables);
+
 // ---- posembed.cu -------------------------------------------------------------------------------------------------
 int cnrf_pos_embed_fwd_ld(const float* x, int64_t M, int D, const float* freqs, int L, int inc, int64_t ld_out,
                           float* out, cudaStream_t st);

@@ -121,20 +121,20 @@ __global__ void __launch_bounds__(512) tmem_ld_probe_kernel(int iters, int mode,
   if (mode == 0) {                       // x32, one load in flight
     uint32_t v[32];
     for (int it = 0; it < iters; ++it)
-      for (int cb = 0; cb < 16; ++cb) { tmem_ld32(base + cb * 32, v); tmem_ld_wait(); acc ^= v[it & 31]; }
+      for (int cb = 0; cb < 16; ++cb) { tmem_ld32(base + cb * 32, v); tmem_ld_wait(); acc ^= v[0] ^ v[13] ^ v[31]; }
   } else if (mode == 1) {                // x32, two loads in flight (the epilogues' scheme)
     uint32_t va[32], vb[32];
     for (int it = 0; it < iters; ++it) {
       tmem_ld32(base, va);
       for (int cb = 0; cb < 16; cb += 2) {
-        tmem_ld_wait(); tmem_ld32(base + (cb + 1) * 32, vb); acc ^= va[it & 31];
-        tmem_ld_wait(); if (cb + 2 < 16) tmem_ld32(base + (cb + 2) * 32, va); acc ^= vb[it & 31];
+        tmem_ld_wait(); tmem_ld32(base + (cb + 1) * 32, vb); acc ^= va[0] ^ va[13] ^ va[31];
+        tmem_ld_wait(); if (cb + 2 < 16) tmem_ld32(base + (cb + 2) * 32, va); acc ^= vb[0] ^ vb[13] ^ vb[31];
       }
     }
   } else {                               // x64, one load in flight
     uint32_t v[64];
     for (int it = 0; it < iters; ++it)
-      for (int cb = 0; cb < 8; ++cb) { tmem_ld64_probe(base + cb * 64, v); tmem_ld_wait(); acc ^= v[it & 63]; }
+      for (int cb = 0; cb < 8; ++cb) { tmem_ld64_probe(base + cb * 64, v); tmem_ld_wait(); acc ^= v[0] ^ v[29] ^ v[63]; }
   }
   __syncthreads();
   const long long t1 = clock64();

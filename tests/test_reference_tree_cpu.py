@@ -52,3 +52,20 @@ def test_synthetic_srn_tree_loads_through_the_reference_dataset(tmp_path):
     assert r["orth"] < 1e-5 and abs(r["rho"] - 1.3) < 1e-4
     assert r["look"] > 0.999                                       # -z of the camera points at the origin (OpenGL axes)
     assert 0.02 < r["fg"] < 0.9                                    # the object is in view
+
+
+def test_pythonsafepath_lets_the_drop_in_win_over_the_script_directory(tmp_path):
+    """`python <reference>/train.py` puts the reference checkout -- which holds its own `view_synthesis` -- at sys.path[0],
+    AHEAD of PYTHONPATH, so the drop-in would never be imported.  PYTHONSAFEPATH=1 (python >= 3.11) removes that entry; the
+    recipe of INTEGRATION.md and tests/test_gpu_reference_drivers.py depends on it."""
+    ref, drop = tmp_path / "ref", tmp_path / "drop"
+    for d, tag in ((ref, "REFERENCE"), (drop, "DROPIN")):
+        (d / "view_synthesis").mkdir(parents=True)
+        (d / "view_synthesis" / "__init__.py").write_text(f"WHO = {tag!r}\n")
+    (ref / "helper.py").write_text("X = 1\n")
+    (ref / "train.py").write_text("import view_synthesis, helper\nprint(view_synthesis.WHO)\n")
+    env = dict(os.environ, PYTHONPATH=os.pathsep.join([str(drop), str(ref)]))
+    env.pop("PYTHONSAFEPATH", None)
+    run = lambda e: subprocess.run([sys.executable, str(ref / "train.py")], env=e, capture_output=True, text=True, check=True).stdout.strip()
+    assert run(env) == "REFERENCE"
+    assert run(dict(env, PYTHONSAFEPATH="1")) == "DROPIN"
