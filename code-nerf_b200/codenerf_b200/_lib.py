@@ -42,7 +42,26 @@ class FlexPtrs(C.Structure):    # cnrf_flex_params and cnrf_flex_grads share thi
                 ("w_dir", C.c_void_p), ("b_dir", C.c_void_p), ("w_alpha", C.c_void_p), ("b_alpha", C.c_void_p),
                 ("w_rgb", C.c_void_p), ("b_rgb", C.c_void_p)]
 
+class RenderShape(C.Structure):     # cnrf_render_shape
+    _fields_ = [("hidden", c_i32), ("code", c_i32), ("dim_xyz", c_i32), ("dim_dir", c_i32), ("num_rays", c_i64),
+                ("num_coarse", c_i32), ("num_fine", c_i32), ("pairing", c_i32), ("precision", c_i32), ("keep", c_i32)]
+
+
+class RenderInputs(C.Structure):    # cnrf_render_inputs
+    _fields_ = [("ro", C.c_void_p), ("rd", C.c_void_p), ("z_table", C.c_void_p), ("lower", C.c_void_p), ("upper", C.c_void_p),
+                ("t_rand", C.c_void_p), ("u", C.c_void_p), ("freqs_xyz", C.c_void_p), ("L_xyz", c_i32),
+                ("freqs_dir", C.c_void_p), ("L_dir", c_i32), ("ids", C.c_void_p), ("num_codes", c_i64),
+                ("z_s", C.c_void_p), ("ld_zs", c_i64), ("z_t", C.c_void_p), ("ld_zt", c_i64)]
+
+
 _SIGS = {
+    "cnrf_render_saved_bytes": (c_sz, [C.POINTER(RenderShape)]),
+    "cnrf_render_workspace_bytes": (c_sz, [C.POINTER(RenderShape), c_i32]),
+    "cnrf_render_fwd": (C.c_int, [C.POINTER(RenderShape), C.POINTER(PtrTable), C.POINTER(PtrTable), C.POINTER(RenderInputs),
+                                  c_f32p, c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_render_bwd": (C.c_int, [C.POINTER(RenderShape), C.POINTER(PtrTable), C.POINTER(PtrTable), C.POINTER(RenderInputs),
+                                  c_f32p, c_f32p, C.c_void_p, c_sz, C.POINTER(PtrTable), C.POINTER(PtrTable), c_f32p, c_f32p,
+                                  C.c_void_p, c_sz, C.c_void_p]),
     "cnrf_abi_version": (C.c_int, []),
     "cnrf_error_string": (C.c_char_p, [C.c_int]),
     "cnrf_device_check": (C.c_int, []),

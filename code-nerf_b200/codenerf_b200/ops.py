@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import FieldShape, FlexPtrs, FlexShape, PtrTable, check
+from ._lib import FieldShape, FlexPtrs, FlexShape, PtrTable, RenderInputs, RenderShape, check
 
 _f32 = torch.float32
 # Grad mode of the CALLER: inside Function.forward autograd is always off, and ctx.needs_input_grad ignores no_grad, so the
@@ -452,6 +452,109 @@ def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code
         if ids.dim() == 1 and ids.shape[0] == pts.shape[0] and ids.dtype == torch.int64:
             return _apply(_FieldIds, cfg, pts, rd, ids, tab_s, tab_t, freqs_xyz, freqs_dir, *params)
     return _apply(_Field, cfg, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, *params)
+
+
+# ----------------------------------------------------------------------------------------------------------
+# The whole pipeline of predict_radiance_and_render (nerf/__init__.py:74-91) as one library call per direction
+# ----------------------------------------------------------------------------------------------------------
+class RenderSpec(object):
+    """Everything about one fused render call that is not a differentiable tensor."""
+    __slots__ = ("hidden", "code", "dim_xyz", "dim_dir", "num_coarse", "num_fine", "pairing", "precision", "z_table", "lower",
+                 "upper", "freqs_xyz", "freqs_dir", "ids", "want_extras")
+
+    def __init__(self, hidden, code, dim_xyz, dim_dir, num_coarse, num_fine, pairing, precision, z_table, lower, upper,
+                 freqs_xyz, freqs_dir, ids=None, want_extras=False):
+        self.hidden, self.code, self.dim_xyz, self.dim_dir = int(hidden), int(code), int(dim_xyz), int(dim_dir)
+        self.num_coarse, self.num_fine, self.pairing, self.precision = int(num_coarse), int(num_fine), int(pairing), int(precision)
+        self.z_table, self.lower, self.upper, self.freqs_xyz, self.freqs_dir = z_table, lower, upper, freqs_xyz, freqs_dir
+        self.ids, self.want_extras = ids, bool(want_extras)
+
+
+def _render_inputs(spec, ro, rd, t_rand, u, code_a, ld_a, code_b, ld_b):
+    r = RenderInputs()
+    r.ro, r.rd = ro.data_ptr() if ro is not None else None, rd.data_ptr()
+    r.z_table, r.lower, r.upper = spec.z_table.data_ptr(), spec.lower.data_ptr(), spec.upper.data_ptr()
+    r.t_rand = t_rand.data_ptr() if t_rand is not None else None
+    r.u = u.data_ptr() if u is not None else None
+    r.freqs_xyz, r.L_xyz = spec.freqs_xyz.data_ptr(), spec.freqs_xyz.shape[0]
+    r.freqs_dir, r.L_dir = spec.freqs_dir.data_ptr(), spec.freqs_dir.shape[0]
+    r.ids = spec.ids.data_ptr() if spec.ids is not None else None
+    r.num_codes = code_a.shape[0] if spec.ids is not None else 0
+    r.z_s, r.ld_zs, r.z_t, r.ld_zt = code_a.data_ptr(), ld_a, code_b.data_ptr(), ld_b
+    return r
+
+
+class _Render(torch.autograd.Function):
+    """(ro, rd, [t_rand, u], codes, 2 x 18 parameters) -> rgb_coarse, rgb_fine [, extras_fine (3, N)].  code_a / code_b are the
+    two embedding tables when spec.ids is set (shared-code mode; dense table gradients come back), per-ray code rows
+    otherwise."""
+
+    @staticmethod
+    def forward(ctx, spec, ro, rd, t_rand, u, code_a, code_b, *params):
+        _req_cuda(ro, rd, t_rand, u, code_a, code_b, *params)
+        lib = _lib.load()
+        ro, rd = _c(ro), _c(rd)
+        t_rand = _c(t_rand) if t_rand is not None else None
+        u = _c(u) if u is not None else None
+        code_a, ld_a = _rows(code_a)
+        code_b, ld_b = _rows(code_b)
+        params = tuple(_c(p) for p in params)
+        N = ro.shape[0]
+        dev = ro.device
+        if spec.ids is not None:
+            assert spec.ids.dtype == torch.int64 and spec.ids.shape == (N,) and spec.ids.is_contiguous(), "ids must be (N,) int64"
+            assert code_a.shape[0] == code_b.shape[0], "shape and texture tables must have the same number of rows"
+        keep = int(_OUTER_GRAD[0] and any(ctx.needs_input_grad))
+        shp = RenderShape(spec.hidden, spec.code, spec.dim_xyz, spec.dim_dir, N, spec.num_coarse, spec.num_fine, spec.pairing,
+                          spec.precision, keep)
+        saved = _bytes(lib.cnrf_render_saved_bytes(C.byref(shp)), dev) if keep else None
+        ws = _bytes(lib.cnrf_render_workspace_bytes(C.byref(shp), 0), dev)
+        rgb = (torch.empty((N, 3), dtype=_f32, device=dev), torch.empty((N, 3), dtype=_f32, device=dev))
+        extras = torch.empty((3, N), dtype=_f32, device=dev) if spec.want_extras else None
+        tc, tf = _ptr_table(params[:18]), _ptr_table(params[18:])
+        inp = _render_inputs(spec, ro, rd, t_rand, u, code_a, ld_a, code_b, ld_b)
+        check(lib.cnrf_render_fwd(C.byref(shp), C.byref(tc), C.byref(tf), C.byref(inp), _p(rgb[0]), _p(rgb[1]), _p(extras),
+                                  _p(saved), saved.numel() if keep else 0, _p(ws), ws.numel(), _stream()), "cnrf_render_fwd")
+        if keep:
+            ctx.save_for_backward(rd, code_a, code_b, saved, *params)
+            ctx.spec, ctx.lds, ctx.N = spec, (ld_a, ld_b), N
+        ctx.set_materialize_grads(False)
+        if extras is not None:
+            ctx.mark_non_differentiable(extras)
+            return rgb[0], rgb[1], extras
+        return rgb[0], rgb[1]
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g_c, g_f, *_):
+        rd, code_a, code_b, saved, *params = ctx.saved_tensors
+        spec, (ld_a, ld_b), N = ctx.spec, ctx.lds, ctx.N
+        lib = _lib.load()
+        dev = rd.device
+        if g_c is None and g_f is None:
+            return (None,) * (7 + len(params))
+        g_c = _c(g_c) if g_c is not None else None
+        g_f = _c(g_f) if g_f is not None else None
+        shp = RenderShape(spec.hidden, spec.code, spec.dim_xyz, spec.dim_dir, N, spec.num_coarse, spec.num_fine, spec.pairing,
+                          spec.precision, 1)
+        sizes = [p.numel() for p in params]
+        flat = torch.empty((sum(sizes),), dtype=_f32, device=dev)          # all 36 parameter gradients: one allocation
+        grads = tuple(v.view_as(p) for v, p in zip(flat.split(sizes), params))
+        rows = code_a.shape[0] if spec.ids is not None else N
+        g_codes = torch.empty((2, rows, spec.code), dtype=_f32, device=dev)
+        ws = _bytes(lib.cnrf_render_workspace_bytes(C.byref(shp), 1), dev)
+        tc, tf = _ptr_table(params[:18]), _ptr_table(params[18:])
+        gc, gf = _ptr_table(grads[:18]), _ptr_table(grads[18:])
+        inp = _render_inputs(spec, None, rd, None, None, code_a, ld_a, code_b, ld_b)
+        check(lib.cnrf_render_bwd(C.byref(shp), C.byref(tc), C.byref(tf), C.byref(inp), _p(g_c), _p(g_f), _p(saved), saved.numel(),
+                                  C.byref(gc), C.byref(gf), _p(g_codes[0]), _p(g_codes[1]), _p(ws), ws.numel(), _stream()),
+              "cnrf_render_bwd")
+        return (None, None, None, None, None, g_codes[0], g_codes[1]) + grads
+
+
+def render(spec, ro, rd, t_rand, u, code_a, code_b, params_coarse, params_fine):
+    """predict_radiance_and_render as one library call: -> (rgb_coarse, rgb_fine[, extras_fine])."""
+    return _apply(_Render, spec, ro, rd, t_rand, u, code_a, code_b, *params_coarse, *params_fine)
 
 
 class _Model(torch.autograd.Function):

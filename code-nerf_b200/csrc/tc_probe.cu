@@ -106,7 +106,8 @@ __device__ __forceinline__ void tmem_ld64_probe(uint32_t taddr, uint32_t (&r)[64
       : "r"(taddr)
       : "memory");
 }
-__global__ void __launch_bounds__(512) tmem_ld_probe_kernel(int iters, int mode, long long* __restrict__ out,
+template <int mode>
+__global__ void __launch_bounds__(512) tmem_ld_probe_kernel(int iters, long long* __restrict__ out,
                                                            uint32_t* __restrict__ sink) {
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5;
@@ -121,6 +122,7 @@ __global__ void __launch_bounds__(512) tmem_ld_probe_kernel(int iters, int mode,
   if (mode == 0) {                       // x32, one load in flight
     uint32_t v[32];
     for (int it = 0; it < iters; ++it)
+#pragma unroll 2
       for (int cb = 0; cb < 16; ++cb) { tmem_ld32(base + cb * 32, v); tmem_ld_wait(); acc ^= v[0] ^ v[13] ^ v[31]; }
   } else if (mode == 1) {                // x32, two loads in flight (the epilogues' scheme)
     uint32_t va[32], vb[32];
@@ -134,6 +136,7 @@ __global__ void __launch_bounds__(512) tmem_ld_probe_kernel(int iters, int mode,
   } else {                               // x64, one load in flight
     uint32_t v[64];
     for (int it = 0; it < iters; ++it)
+#pragma unroll 1
       for (int cb = 0; cb < 8; ++cb) { tmem_ld64_probe(base + cb * 64, v); tmem_ld_wait(); acc ^= v[0] ^ v[29] ^ v[63]; }
   }
   __syncthreads();
@@ -151,7 +154,9 @@ extern "C" int cnrf_debug_tmem_ld(int32_t blocks, int32_t warps, int32_t iters, 
                                   cnrf_stream_t stream) {
   CNRF_REQUIRE(clocks && sink, CNRF_E_NULL);
   CNRF_REQUIRE(blocks > 0 && warps >= 1 && warps <= 16 && iters > 0 && mode >= 0 && mode <= 2, CNRF_E_SHAPE);
-  tmem_ld_probe_kernel<<<blocks, warps * 32, 0, as_stream(stream)>>>(iters, mode, clocks, sink);
+  if (mode == 0) tmem_ld_probe_kernel<0><<<blocks, warps * 32, 0, as_stream(stream)>>>(iters, clocks, sink);
+  else if (mode == 1) tmem_ld_probe_kernel<1><<<blocks, warps * 32, 0, as_stream(stream)>>>(iters, clocks, sink);
+  else tmem_ld_probe_kernel<2><<<blocks, warps * 32, 0, as_stream(stream)>>>(iters, clocks, sink);
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }

@@ -141,6 +141,24 @@ class ShapeTextureEmbedding(torch.nn.Module):
         return shape_params, texture_params
 
 
+class _RenderToken(object):
+    """What the coarse model hands to the fine one in the fused render protocol: itself and its 18 parameters."""
+    __slots__ = ("model", "params")
+
+    def __init__(self, model, params):
+        self.model, self.params = model, params
+
+
+def _code_source(z_s, z_t):
+    """(ids, shape table, texture table) when both code tensors are the untouched output of ShapeTextureEmbedding.forward."""
+    src = getattr(z_s, "_cnrf_code_source", None)
+    if src is None or getattr(z_t, "_cnrf_code_source", None) is not src or not _share_codes():
+        return None
+    if (z_s._version, z_t._version, src[1]._version, src[2]._version) != src[3]:
+        return None                      # somebody edited the codes or the tables in place since the lookup
+    return src[:3]
+
+
 class CodeNeRFModel(torch.nn.Module):
     """CodeNeRF MLP conditioned on shape / texture codes (models/model.py:123-194).
 
@@ -180,27 +198,50 @@ class CodeNeRFModel(torch.nn.Module):
         return out
 
     def forward(self, z_s: torch.Tensor, z_t: torch.Tensor, x):
-        from ..nerf import FieldQuery
+        from ..nerf import FieldQuery, RenderQuery
         if self.shape_code_size != self.texture_code_size:
             raise ValueError("CodeNeRFModel needs shape_code_size == texture_code_size (models/model.py:150,153)")
         params = self._param_list()
+        if isinstance(x, RenderQuery):
+            # predict_radiance_and_render as one library call (cnrf_render_fwd / _bwd).  The call still passes through
+            # BOTH models' __call__ (and so through DistributedDataParallel.forward when they are wrapped, utils/util.py:
+            # 139-142): the coarse model answers with its parameter list, the fine model runs the pipeline.
+            if x.coarse is None:
+                return _RenderToken(self, params)
+            return self._render(z_s, z_t, x, params)
         if isinstance(x, FieldQuery):
             ex, ed = x.embedder_xyz, x.embedder_dir
             assert 3 * ex.out_dim_per_channel == self.dim_xyz and 3 * ed.out_dim_per_channel == self.dim_dir, \
                 "embedder widths do not match the model's dim_xyz / dim_dir"
             precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[x.precision]
             pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
-            src = getattr(z_s, "_cnrf_code_source", None)
-            if src is None or getattr(z_t, "_cnrf_code_source", None) is not src or not _share_codes():
-                src = None
-            elif (z_s._version, z_t._version, src[1]._version, src[2]._version) != src[3]:
-                src = None                  # somebody edited the codes or the tables in place since the lookup
-            else:
-                src = src[:3]
+            src = _code_source(z_s, z_t)
             return ops.codenerf_field(params, x.pts, x.rd, z_s, z_t, ex.frequency_bands, ed.frequency_bands,
                                       self.hidden_size, self.shape_code_size, self.dim_xyz, self.dim_dir,
                                       pairing=pairing, precision=precision, code_source=src)
         lead = x.shape[:-1]
+        return self._as_written(params, z_s, z_t, x, lead)
+
+    def _render(self, z_s, z_t, q, params):
+        """Fine model's half of the fused render protocol: q.coarse is the coarse model's _RenderToken."""
+        coarse = q.coarse.model
+        assert (coarse.hidden_size, coarse.shape_code_size, coarse.dim_xyz, coarse.dim_dir) == \
+            (self.hidden_size, self.shape_code_size, self.dim_xyz, self.dim_dir), "coarse and fine models differ in shape"
+        ex, ed, ps = q.embedder_xyz, q.embedder_dir, q.point_sampler
+        assert 3 * ex.out_dim_per_channel == self.dim_xyz and 3 * ed.out_dim_per_channel == self.dim_dir, \
+            "embedder widths do not match the model's dim_xyz / dim_dir"
+        precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[q.precision]
+        pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[q.pairing]
+        src = _code_source(z_s, z_t) if precision == _lib.PRECISION_BF16 else None
+        ids = None
+        if src is not None and src[0].dim() == 1 and src[0].shape[0] == q.ro.shape[0] and src[0].dtype == torch.int64:
+            ids, z_s, z_t = src[0].contiguous(), src[1], src[2]
+        spec = ops.RenderSpec(self.hidden_size, self.shape_code_size, self.dim_xyz, self.dim_dir, ps.num_samples_coarse,
+                              ps.num_samples_fine, pairing, precision, ps.z_vals, ps.lower, ps.upper, ex.frequency_bands,
+                              ed.frequency_bands, ids=ids)
+        return ops.render(spec, q.ro, q.rd, q.t_rand, q.u, z_s, z_t, q.coarse.params, params)
+
+    def _as_written(self, params, z_s, z_t, x, lead):
         out = ops.codenerf_model(params, z_s.reshape(-1, z_s.shape[-1]), z_t.reshape(-1, z_t.shape[-1]),
                                  x.reshape(-1, x.shape[-1]), self.hidden_size, self.shape_code_size, self.dim_xyz,
                                  self.dim_dir, precision=_lib.PRECISION_FP32)

@@ -51,6 +51,38 @@ class FieldQuery(object):
         self.precision, self.pairing = precision, pairing
 
 
+class RenderQuery(object):
+    """The fused form of predict_radiance_and_render (cnrf_render_fwd / _bwd: one library call per direction).  Passed
+    through `coarse_model(z_s, z_t, query)` first (query.coarse is None -> the model returns its parameter token), then
+    through `fine_model(z_s, z_t, query)` with the token attached -> (rgb_coarse, rgb_fine).  Both calls go through the
+    modules' __call__, hence through DistributedDataParallel.forward when the caller wrapped them."""
+    __slots__ = ("ro", "rd", "point_sampler", "embedder_xyz", "embedder_dir", "precision", "pairing", "t_rand", "u", "coarse")
+
+    def __init__(self, ro, rd, point_sampler, embedder_xyz, embedder_dir, precision, pairing, t_rand, u):
+        self.ro, self.rd, self.point_sampler = ro, rd, point_sampler
+        self.embedder_xyz, self.embedder_dir, self.precision, self.pairing = embedder_xyz, embedder_dir, precision, pairing
+        self.t_rand, self.u, self.coarse = t_rand, u, None
+
+
+def _fused_render_ok(rays, point_sampler, embedders, coarse_model, fine_model) -> bool:
+    """The one-call pipeline serves the training / rendering case: two CodeNeRFModels, both embedders, CUDA rays that
+    carry no gradient (camera-pose optimisation, eval.py:129-168, keeps the per-stage path whose graph reaches the rays).
+    CODENERF_FUSED_RENDER=0 forces the per-stage path."""
+    from ..models.model import CodeNeRFModel
+    if os.environ.get("CODENERF_FUSED_RENDER", "1") == "0":
+        return False
+    ro, rd = rays
+    if not (torch.is_tensor(ro) and torch.is_tensor(rd) and ro.is_cuda and rd.is_cuda and ro.dim() == 2 and rd.dim() == 2):
+        return False
+    if torch.is_grad_enabled() and (ro.requires_grad or rd.requires_grad):
+        return False
+    if not (isinstance(_unwrap(coarse_model), CodeNeRFModel) and isinstance(_unwrap(fine_model), CodeNeRFModel)):
+        return False
+    if not isinstance(point_sampler, PointSampler) or embedders[0] is None or embedders[1] is None:
+        return False
+    return point_sampler.num_samples_coarse >= 3 and point_sampler.num_samples_fine > 0
+
+
 def _unwrap(model):
     return model.module if hasattr(model, "module") and isinstance(model.module, torch.nn.Module) else model
 
@@ -94,6 +126,14 @@ def predict_radiance_and_render(rays, point_sampler: PointSampler, embedders, co
                                 fine_model: torch.nn.Module, latent_embedding) -> Tuple[torch.Tensor, torch.Tensor]:
     """coarse sample -> field -> composite -> importance sample -> field -> composite (nerf/__init__.py:74-91)."""
     (ro, rd) = rays
+    if _fused_render_ok(rays, point_sampler, embedders, coarse_model, fine_model):
+        # the same two torch.rand draws, in the same order, as sample_uniform (:64) and sample_pdf (:93) make
+        t_rand, u = point_sampler.draw_offsets(ro.shape[0], ro.dtype, ro.device)
+        query = RenderQuery(ro, rd, point_sampler, embedders[0], embedders[1], _state["precision"], _state["pairing"], t_rand, u)
+        z_s, z_t = latent_embedding
+        query.coarse = coarse_model(z_s, z_t, query)
+        rgb_coarse, rgb_fine = fine_model(z_s, z_t, query)
+        return rgb_coarse, rgb_fine
     pts_coarse, z_vals_coarse = point_sampler.sample_uniform(ro, rd)
     radiance_field_coarse = forward_pass(coarse_model, embedders, rd, pts_coarse, latent_embedding)
     (rgb_coarse, _, _, weights, _) = volume_render(radiance_field_coarse, z_vals_coarse, rd)

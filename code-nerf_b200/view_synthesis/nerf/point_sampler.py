@@ -42,6 +42,15 @@ class PointSampler(object):
         assert z_vals.shape == torch.Size([num_random_rays, self.num_samples_coarse]), "Incorrect shape of depth samples z_vals"
         return pts, z_vals
 
+    def draw_offsets(self, num_rays: int, dtype, device):
+        """The two device RNG draws of one coarse + fine pass, in the reference's order (point_sampler.py:64, then :93);
+        (None, None) when perturb is off."""
+        if not self.perturb:
+            return None, None
+        t_rand = torch.rand((num_rays, self.num_samples_coarse), dtype=dtype, device=device)
+        u = torch.rand([num_rays, self.num_samples_fine], dtype=dtype, device=device)
+        return t_rand, u
+
     def sample_pdf(self, ro: torch.Tensor, rd: torch.Tensor, weights: torch.Tensor, z_vals: torch.Tensor
                    ) -> Tuple[torch.Tensor, torch.Tensor]:
         """Inverse-CDF samples merged with the coarse ones (point_sampler.py:73-120) -> pts (N, S_c+N_f, 3), z (N, S_c+N_f)."""

@@ -286,6 +286,57 @@ int cnrf_mse_pair_bwd(const float* rgb_a, int64_t ld_a, const float* rgb_b, int6
                       float* g_a, float* g_b, cnrf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * The whole render pipeline in one call per direction.  predict_radiance_and_render, view_synthesis/nerf/__init__.py:74-91:
+ *   sample_uniform (:82) -> forward_pass(coarse) (:83) -> volume_render (:84) -> sample_pdf on weights[..., 1:-1] (:87) ->
+ *   forward_pass(fine) (:88) -> volume_render (:89) -> (rgb_coarse, rgb_fine),
+ * and its backward with respect to both models' parameters and the latent codes (the samples are detached, :87 /
+ * point_sampler.py:115, so the two passes only meet in the code gradients).  Rays carry no gradient through these entry
+ * points; callers that optimise the camera pose (eval.py:129-168) use the per-stage entry points above.
+ * The kernels are exactly those of the per-stage entry points; what this removes is the host: two library calls per
+ * chunk instead of ~58 launches driven through Python.
+ *   t_rand [N,Sc] / u [N,Nf]: the torch.rand draws of point_sampler.py:64,93 (NULL = perturb off);
+ *   codes: ids != NULL: z_s / z_t are the embedding TABLES [num_codes,C] and g_z_s / g_z_t receive dense table gradients
+ *          (both models summed); ids == NULL: z_s / z_t are per-ray rows [N,C] (row stride 0 = one broadcast row) and
+ *          g_z_s / g_z_t are dense [N,C];
+ *   extras_fine: NULL, or [3,N] = disp, acc, depth of the fine pass (volumetric_render.py:62-66).
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct {
+  int32_t hidden, code, dim_xyz, dim_dir;
+  int64_t num_rays;
+  int32_t num_coarse, num_fine; /* S_c and N_f (nerf/__init__.py:28-31) */
+  int32_t pairing, precision;   /* CNRF_PAIRING_*, CNRF_PRECISION_* */
+  int32_t keep;                 /* 1: fill `saved` for cnrf_render_bwd */
+} cnrf_render_shape;
+
+typedef struct {
+  const float* ro;      /* [N,3] */
+  const float* rd;      /* [N,3], not normalised */
+  const float* z_table; /* [Sc] PointSampler.z_vals */
+  const float* lower;   /* [Sc] */
+  const float* upper;   /* [Sc] */
+  const float* t_rand;  /* [N,Sc] or NULL */
+  const float* u;       /* [N,Nf] or NULL */
+  const float* freqs_xyz; int32_t L_xyz;
+  const float* freqs_dir; int32_t L_dir;
+  const int64_t* ids;   /* [N] or NULL */
+  int64_t num_codes;
+  const float* z_s; int64_t ld_zs;
+  const float* z_t; int64_t ld_zt;
+} cnrf_render_inputs;
+
+size_t cnrf_render_saved_bytes(const cnrf_render_shape* s);
+size_t cnrf_render_workspace_bytes(const cnrf_render_shape* s, int32_t backward);
+int cnrf_render_fwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                    const cnrf_render_inputs* in, float* rgb_coarse /*[N,3]*/, float* rgb_fine /*[N,3]*/,
+                    float* extras_fine /*[3,N] or NULL*/, void* saved, size_t saved_bytes, void* workspace,
+                    size_t workspace_bytes, cnrf_stream_t stream);
+/* g_rgb_coarse / g_rgb_fine [N,3]: either may be NULL (zero).  Every buffer of g_coarse / g_fine is fully overwritten. */
+int cnrf_render_bwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                    const cnrf_render_inputs* in, const float* g_rgb_coarse, const float* g_rgb_fine, const void* saved,
+                    size_t saved_bytes, const cnrf_codenerf_grads* g_coarse, const cnrf_codenerf_grads* g_fine,
+                    float* g_z_s, float* g_z_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Diagnostics (used by tests only).  One-CTA tcgen05 GEMM over the 128-byte-swizzled shared-memory image the fused
  * MLP kernels use.  mode 0: D[128,N] = A[128,K] B[N,K]^T (K-major operands); mode 1: D[128,N] = A[K,128]^T B[K,N]
  * (MN-major operands, the dW = dY^T X form).  *err is set to 1 if the kernel's bounded barrier wait timed out.

@@ -167,3 +167,57 @@ def test_no_grad_inference_and_ddp_style_call(dev):
         a = nerf.forward_pass(m, embedders(dev), rd, pts, (zs, zt))
         b = nerf.forward_pass(Wrap(m), embedders(dev), rd, pts, (zs, zt))
     assert a.shape == (10, 5, 4) and torch.equal(a, b) and not a.requires_grad
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("codes", ["table_ids", "per_ray", "broadcast"])
+def test_fused_render_entry_equals_the_per_stage_path(precision, codes, monkeypatch):
+    """cnrf_render_fwd / _bwd (one library call per direction) against the per-stage entry points driven from Python
+    (CODENERF_FUSED_RENDER=0): the same kernels in the same order on the same stream, so rgb is bit-identical and the
+    gradients agree to atomic-summation order."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    dev = torch.device("cuda", 0)
+    N, Sc, Nf = 777, 32, 128
+    g = torch.Generator().manual_seed(4)
+    ro = (torch.tensor([0.0, 0.0, 1.3]) + 0.01 * torch.randn(N, 3, generator=g)).to(dev)
+    rd = (torch.randn(N, 3, generator=g) * 0.2 + torch.tensor([0.0, 0.0, -1.0])).to(dev)
+    t_rand, u = torch.rand(N, Sc, generator=g).to(dev), torch.rand(N, Nf, generator=g).to(dev)
+    tgt = torch.rand(N, 3, generator=g).to(dev)
+    ids = torch.tensor([3, 0, 6]).repeat_interleave(N // 3).to(dev)
+    one_code = [torch.randn(1, 256, generator=g), torch.randn(1, 256, generator=g)]
+    ps = nerf.PointSampler(Sc, Nf, 0.8, 1.8, "lindepth", True, torch.float32, dev)
+    emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+    nerf.set_precision(precision)
+    real_rand = torch.rand
+    out = {}
+    try:
+        for fused in ("1", "0"):
+            monkeypatch.setenv("CODENERF_FUSED_RENDER", fused)
+            torch.manual_seed(21)
+            mods = [models.CodeNeRFModel(256, 7, 256, 256, 10, 4).to(dev) for _ in range(2)]
+            table = models.ShapeTextureEmbedding(7, 256, 256).to(dev)
+            if codes == "table_ids":
+                z = table(ids)
+                leaves = list(table.parameters())
+            elif codes == "per_ray":
+                z = tuple(c * 1.0 for c in table(ids))                      # drops the code-source tag
+                leaves = list(table.parameters())
+            else:                                                          # eval.py:149: one code row, stride-0 expand
+                leaves = [c.clone().to(dev).requires_grad_(True) for c in one_code]
+                z = tuple(l.expand(N, -1) for l in leaves)
+            q = [t_rand, u]
+            torch.rand = lambda *a, **k: q.pop(0)
+            rc, rf = nerf.predict_radiance_and_render((ro, rd), ps, emb, mods[0], mods[1], z)
+            torch.rand = real_rand
+            (torch.nn.functional.mse_loss(rc, tgt) + 2.0 * torch.nn.functional.mse_loss(rf, tgt)).backward()
+            grads = [p.grad.clone() for m in mods for p in m.parameters()] + [l.grad.clone() for l in leaves]
+            out[fused] = (rc.detach().clone(), rf.detach().clone(), grads)
+    finally:
+        torch.rand = real_rand
+        nerf.set_precision("fp32")
+    assert torch.equal(out["1"][0], out["0"][0]) and torch.equal(out["1"][1], out["0"][1])
+    for a, b in zip(out["1"][2], out["0"][2]):
+        assert a.shape == b.shape and torch.isfinite(a).all()
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-6 + 1e-4 * float(b.abs().max()))
