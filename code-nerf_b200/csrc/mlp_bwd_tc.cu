@@ -1,6 +1,6 @@
-// Backward-data chain of the fused bf16 tensor-core field.  Per tile pair: stage "-1" on CUDA cores
-// (d v2 = g_rgb Wrv, masked), then four tensor-core stages
-//   d v1 = (d v2p Wd2) * [v1>0],  d feat = d v1p Wdf,  d h2 = (d feat Woh' + d sigma w_sigma) * [h2>0],  d h1 = (d h2p W2h) * [h1>0]
+// Backward-data chain of the fused bf16 tensor-core field (fc_out folded into layer_dir1, mlp_tc.cuh).  Per tile pair:
+// stage "-1" on CUDA cores (d v2 = g_rgb Wrv, masked), then three tensor-core stages
+//   d v1 = (d v2p Wd2) * [v1>0],  d h2 = (d v1p Wfh + d sigma w_sigma) * [h2>0],  d h1 = (d h2p W2h) * [h1>0]
 // with W^T streamed as B operands (16 KB N-half images through a 5-slot TMA ring, as in the forward).  Every masked
 // gradient tile is TMA-stored as a bf16 image (same layout as the forward's activation images) for the weight-gradient
 // kernel.  The ReLU masks are the 1-bit sign words the forward saved (32 B per row and layer), loaded before the
@@ -56,12 +56,12 @@ __device__ __forceinline__ bool uwait(uint64_t* bar, uint32_t parity, BBars* b, 
   return __all_sync(0xFFFFFFFFu, bwait(bar, parity, b, err));
 }
 
-// S = -1: d v2p from g_rgb on CUDA cores; S = 0..3: the tensor-core stages.  Output image index = S + 1.
+// S = -1: d v2p from g_rgb on CUDA cores; S = 0..2: the tensor-core stages.  Output image index = S + 1.
 // The 32-column blocks are processed two per loop iteration with the next block's TMEM load (and mask word) in flight;
 // the loop is deliberately not unrolled further (instruction-cache footprint of five specialised stages).
 template <int S, bool XG>
 __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint32_t parity) {
-  constexpr int MK = S == -1 ? 3 : S == 0 ? 2 : S == 2 ? 1 : S == 3 ? 0 : -1;   // v2, v1, -, h2, h1
+  constexpr int MK = S == -1 ? 3 : S == 0 ? 2 : S == 1 ? 1 : 0;                 // v2, v1, h2, h1
   const uint32_t* mp = reinterpret_cast<const uint32_t*>(c.masks + (size_t)(MK >= 0 ? MK : 0) * MASK_BYTES + c.r * 32);
   uint32_t m_a = 0, m_b = 0;
   if (MK >= 0) m_a = __ldg(mp);
@@ -87,7 +87,7 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
         f[4 * j + 3] = fmaf(c.g.x, w0.w, fmaf(c.g.y, w1.w, c.g.z * w2.w));
       }
     }
-    if (S == 2) {                                   // + d sigma * w_sigma  (fc_out row 0)
+    if (S == 1) {                                   // + d sigma * w_sigma  (fc_out row 0)
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float4 ws = hw[cb * 8 + j];
@@ -123,7 +123,7 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
   named_bar_sync(c.bar_id, 128);
   if (c.elected) {
     if (c.tile_ok) { bulk_s2g(c.dy + (size_t)(S + 1) * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
-    if (S < 3 || XG) mbar_arrive(&c.bars->a_ready[t]);     // XG: the input-gradient stage reads d h1p as its A operand
+    if (S < 2 || XG) mbar_arrive(&c.bars->a_ready[t]);     // XG: the input-gradient stage reads d h1p as its A operand
   }
   return true;
 }
@@ -182,9 +182,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
       uint32_t slot = 0, epar = 1;
       bool ok = true;
       for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
-        for (int stage = 0; stage < (XG ? 5 : 4) && ok; ++stage) {
+        for (int stage = 0; stage < (XG ? 4 : 3) && ok; ++stage) {
           for (int t = 0; t < 2 && ok; ++t) {
-            for (int i = 0; i < (stage == 4 ? 2 : 8); ++i) {      // stage 4: W1^T, one 32 KB image = two ring slots
+            for (int i = 0; i < (stage == 3 ? 2 : 8); ++i) {      // stage 3: W1^T, one 32 KB image = two ring slots
               if (!bwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
               mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
               bulk_g2s(ring + slot * HALF, a.pk.bwd + (size_t)(stage * 8 + i) * HALF, HALF, &bars->w_full[slot]);
@@ -206,7 +206,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
       bool ok = true;
       for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
 #pragma unroll 1
-        for (int stage = 0; stage < 4 && ok; ++stage, ++na) {
+        for (int stage = 0; stage < 3 && ok; ++stage, ++na) {
 #pragma unroll 1
           for (int t = 0; t < 2 && ok; ++t) {
             if (!uwait(&bars->a_ready[t], na & 1, bars, a.err)) { ok = false; break; }
@@ -288,7 +288,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
       if (ok) { ok = bwd_stage<0, XG>(a, c, t, na & 1); ++na; }
       if (ok) { ok = bwd_stage<1, XG>(a, c, t, na & 1); ++na; }
       if (ok) { ok = bwd_stage<2, XG>(a, c, t, na & 1); ++na; }
-      if (ok) { ok = bwd_stage<3, XG>(a, c, t, na & 1); ++na; }
       if (XG && ok) { ok = bwd_stage_x(a, c, t, na & 1, m); ++na; }
       if (!ok) break;
     }

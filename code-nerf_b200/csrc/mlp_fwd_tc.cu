@@ -1,7 +1,8 @@
-// Forward chain of the fused bf16 tensor-core field (CNRF_PRECISION_BF16), models/model.py:179-194 code-folded:
-//   h1 = relu(W1 gamma(x) + b1) -> h2 = relu(W2h h1 + beta2[ray]) -> o = Woh h2 + betao[ray] -> v1 = relu(Wdf o[1:] +
-//   betad[pair]) -> v2 = relu(Wd2 v1 + bd2) -> rgb = Wrv v2 + betar[ray]
-// One persistent CTA per SM walks PAIRS of 128-row sample tiles (T0, T1) through the five layers half a layer apart: the
+// Forward chain of the fused bf16 tensor-core field (CNRF_PRECISION_BF16), models/model.py:179-194 code-folded, with
+// fc_out folded into layer_dir1 (no activation between them, :182-189; Wfh = Wdf Wout'[:, :H] rebuilt every call):
+//   h1 = relu(W1 gamma(x) + b1) -> h2 = relu(W2h h1 + beta2[ray]), sigma = w_sigma h2 + betas[ray] ->
+//   v1 = relu(Wfh h2 + betaf[ray] + [Wdv | bd1] [gamma(d_pair) | 1]) -> v2 = relu(Wd2 v1 + bd2) -> rgb = Wrv v2 + betar[ray]
+// One persistent CTA per SM walks PAIRS of 128-row sample tiles (T0, T1) through the four layers half a layer apart: the
 // MMAs of one tile run under the epilogue of the other (weights are L2-resident and pass through the ring once per tile).
 //   TMEM   : 2 x 256 fp32 accumulator columns (all 512).
 //   smem   : 2 x 64 KB activation tiles (4 slabs of [128 x 64] bf16, 128-byte swizzle, overwritten in place layer by
@@ -116,19 +117,19 @@ __device__ __forceinline__ void stage_rows(const Epi& c, const float* table, con
   cp_async_commit();
 }
 
-// One layer's epilogue for one tile.  E: 0 layer_xyz1, 1 layer_xyz2 (+ sigma head), 2 fc_out features (no ReLU),
-// 3 layer_dir1 (its bias and view-direction half arrive through the MMA), 4 layer_dir2 (+ rgb head).  GB: bias row comes from global memory (register double buffer) instead of
-// shared memory.
+// One layer's epilogue for one tile.  E: 0 layer_xyz1 (its bias arrives through the MMA), 1 layer_xyz2 (+ sigma head),
+// 2 folded layer_dir1 (per-ray bias here; its constant bias and view-direction half arrive through the MMA),
+// 3 layer_dir2 (+ rgb head).  GB: bias row comes from global memory (register double buffer) instead of shared memory.
 template <int E, bool GB>
 __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint32_t parity) {
   const float4* gb = nullptr;
   const float4* sb = nullptr;
   if (E == 1) { if (GB) gb = reinterpret_cast<const float4*>(a.b2 + (int64_t)c.row * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
-  if (E == 2) { if (GB) gb = reinterpret_cast<const float4*>(a.bof + (int64_t)c.row * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
-  if (E == 4) sb = reinterpret_cast<const float4*>(c.heads + 1024);
+  if (E == 2) { if (GB) gb = reinterpret_cast<const float4*>(a.bf + (int64_t)c.row * 256); else sb = reinterpret_cast<const float4*>(c.stage + c.slot * 256); }
+  if (E == 3) sb = reinterpret_cast<const float4*>(c.heads + 1024);
   float tail0 = 0.f, tail1 = 0.f, tail2 = 0.f;
   if (E == 1 && c.valid) tail0 = __ldg(a.bos + c.row);
-  if (E == 4 && c.valid) { const float* brp = a.br + (int64_t)c.row * 3; tail0 = __ldg(brp); tail1 = __ldg(brp + 1); tail2 = __ldg(brp + 2); }
+  if (E == 3 && c.valid) { const float* brp = a.br + (int64_t)c.row * 3; tail0 = __ldg(brp); tail1 = __ldg(brp + 1); tail2 = __ldg(brp + 2); }
   const long long tw0 = FCLK();
   if (!fwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
   const long long tw1 = FCLK();
@@ -141,21 +142,20 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f, rgb3 = 0.f, rgb4 = 0.f, rgb5 = 0.f;   // two partial sums per channel
   float sg0 = 0.f, sg1 = 0.f, sg2 = 0.f, sg3 = 0.f;                               // four partial sums of the sigma head
   // sign bits of the pre-activations (the backward's ReLU mask): one 32-bit word per 32-column block
-  uint32_t* mp = (E != 2 && c.sv) ? reinterpret_cast<uint32_t*>(c.sv + SAVED_MASKS + (size_t)(E == 0 ? 0 : E == 1 ? 1 : E == 3 ? 2 : 3) * MASK_BYTES + c.r * 32)
-                                  : nullptr;
+  uint32_t* mp = c.sv ? reinterpret_cast<uint32_t*>(c.sv + SAVED_MASKS + (size_t)E * MASK_BYTES + c.r * 32) : nullptr;
   // One 32-column block: + bias, heads, sign word, ReLU, bf16, swizzled store.  The loop below keeps the next block's
   // TMEM load in flight while this one is processed, and is NOT unrolled further: five specialised layers unrolled eight
   // times each overflowed the instruction cache (16% of the kernel's stall samples were instruction fetches).
   auto block = [&](int cb, uint32_t (&v)[32]) {
     float4 bcur[8];
-    if (E == 1 || E == 2 || E == 4) {
+    if (E != 0) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) bcur[j] = GB ? __ldg(gb + cb * 8 + j) : sb[cb * 8 + j];
     }
     float f[32];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      if (E == 0 || E == 3) {
+      if (E == 0) {
         f[4 * j] = __uint_as_float(v[4 * j]); f[4 * j + 1] = __uint_as_float(v[4 * j + 1]);
         f[4 * j + 2] = __uint_as_float(v[4 * j + 2]); f[4 * j + 3] = __uint_as_float(v[4 * j + 3]);
       } else {
@@ -171,7 +171,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
         sg2 = fmaf(fmaxf(f[4 * j + 2], 0.f), w.z, sg2); sg3 = fmaf(fmaxf(f[4 * j + 3], 0.f), w.w, sg3);
       }
     }
-    if (E == 4) {                                   // rgb_raw = Wrv v2 + betar[ray]                (fc_rgb)
+    if (E == 3) {                                   // rgb_raw = Wrv v2 + betar[ray]                (fc_rgb)
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         const float x0 = fmaxf(f[4 * j], 0.f), x1 = fmaxf(f[4 * j + 1], 0.f), x2 = fmaxf(f[4 * j + 2], 0.f),
@@ -182,7 +182,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
         rgb2 = fmaf(x0, w2.x, fmaf(x1, w2.y, rgb2)); rgb5 = fmaf(x2, w2.z, fmaf(x3, w2.w, rgb5));
       }
     }
-    if (E != 2) {
+    {
       uint32_t w = 0;
 #pragma unroll
       for (int j = 0; j < 32; ++j) w = __funnelshift_l(__float_as_uint(f[j]), w, 1);   // (w << 1) | sign(f[j])
@@ -190,7 +190,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
     }
     uint32_t pk[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) pk[j] = (E == 2) ? pack_bf16(f[2 * j], f[2 * j + 1]) : cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
+    for (int j = 0; j < 16; ++j) pk[j] = cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
     store_row_block(c.tile, c.r, cb, pk);
   };
   uint32_t va[32], vb[32];
@@ -205,7 +205,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
     block(cb + 1, vb);
   }
   if (E == 1) c.sigma = (sg0 + sg1) + (sg2 + sg3) + tail0;
-  if (E == 4 && c.valid)                            // [rgb_raw | sigma_raw]   models/model.py:194
+  if (E == 3 && c.valid)                            // [rgb_raw | sigma_raw]   models/model.py:194
     reinterpret_cast<float4*>(a.raw)[c.m] = make_float4(rgb0 + rgb3 + tail0, rgb1 + rgb4 + tail1, rgb2 + rgb5 + tail2, c.sigma);
   const long long tw3 = FCLK();
   fence_proxy_async();
@@ -215,7 +215,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if (c.elected && t == 0) { FDBG(10, tw2 - tw1); FDBG(11, tw3 - tw2); FDBG(12, tw4 - tw3); }
   if (c.elected) {
     // the hand-off first: a cluster-scope release issued after the bulk store waits for that store (~3.5 k clk)
-    if (E < 4) { if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&c.bars->a_ready[t]); }
+    if (E < 3) { if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&c.bars->a_ready[t]); }
     if (c.sv) { bulk_s2g(c.sv + SAVED_GAMMA + (size_t)E * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
     if (t == 0) { FDBG(0, tw1 - tw0); FDBG(1 + E, FCLK() - tw1); FDBG(13, FCLK() - tw4); }
   }
@@ -269,10 +269,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       bool ok = true;
       for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
         const int64_t pr = pb + rank < num_pairs ? pb + rank : num_pairs - 1;    // padding pair: any valid slab will do
-        for (int layer = 0; layer < 5 && ok; ++layer) {
+        for (int layer = 0; layer < NUM_TC_LAYERS && ok; ++layer) {
           const int first = layer == 0 ? 0 : 2 + 8 * (layer - 1);          // half-image index in a.pk.fwd
           const int nmain = (layer == 0 ? 2 : 8) / CG;                       // weight images of the layer proper
-          const int count = nmain + (layer == 3 ? 1 + 2 / CG : 0);
+          const int count = nmain + (layer == 2 ? 1 + 2 / CG : 0);
           for (int t = 0; t < 2 && ok; ++t) {
             for (int i = 0; i < count; ++i) {
               if (!fwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
@@ -296,8 +296,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       bool ok = true;
       for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
 #pragma unroll 1
-        for (int layer = 0; layer < 5 && ok; ++layer) {
-          const int count = 2 * ((layer == 0 ? 1 : 4) + (layer == 3 ? 2 : 0));     // both tiles
+        for (int layer = 0; layer < NUM_TC_LAYERS && ok; ++layer) {
+          const int count = 2 * ((layer == 0 ? 1 : 4) + (layer == 2 ? 2 : 0));     // both tiles
 #pragma unroll 1
           for (int i = 0; i < count && ok; ++i) {
             if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; break; }
@@ -327,7 +327,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
 #define COMMIT(bar) do { if (CG == 2) umma_commit_2cta(bar); else umma_commit(bar); } while (0)
       for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
 #pragma unroll 1
-        for (int layer = 0; layer < 5 && ok; ++layer, ++na) {
+        for (int layer = 0; layer < NUM_TC_LAYERS && ok; ++layer, ++na) {
           const int nch = layer == 0 ? 1 : 4;
 #pragma unroll 1
           for (int t = 0; t < 2 && ok; ++t) {
@@ -355,7 +355,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
                 NEXT_SLOT();
               }
             }
-            if (layer == 3 && ok) {        // += [gamma(d_pair) | 1] [Wdv | b_dir1]^T : K = 32 columns per tile of the shared slab
+            if (layer == 2 && ok) {        // += [gamma(d_pair) | 1] [Wdv | b_dir1]^T : K = 32 columns per tile of the shared slab
               const uint32_t slot_x = slot;
               if (!WAIT_IMAGE()) { ok = false; break; }
               NEXT_SLOT();
@@ -460,11 +460,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       bool ok = epi_layer<0, false>(a, c, t, na & 1); ++na;
       if (ok) { ok = c.staged ? epi_layer<1, false>(a, c, t, na & 1) : epi_layer<1, true>(a, c, t, na & 1); ++na; }
       if (ok) {
-        stage_rows(c, a.bof, a.gid);                       // every thread of the tile is past its reads of the beta2 rows
+        stage_rows(c, a.bf, a.gid);                        // every thread of the tile is past its reads of the beta2 rows
         ok = c.staged ? epi_layer<2, false>(a, c, t, na & 1) : epi_layer<2, true>(a, c, t, na & 1); ++na;
       }
       if (ok) { ok = epi_layer<3, false>(a, c, t, na & 1); ++na; }
-      if (ok) { ok = epi_layer<4, false>(a, c, t, na & 1); ++na; }
       if (!ok) break;
     }
     cp_async_wait_all();

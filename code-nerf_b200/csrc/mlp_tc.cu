@@ -1,6 +1,7 @@
 // Fused bf16 tensor-core chain of the CodeNeRF field (CNRF_PRECISION_BF16): the per-sample layers
-//   h1 = relu(W1 gamma(x) + b1) -> h2 = relu(W2h h1 + beta2[ray]) -> o = Woh h2 + betao[ray] -> v1 = relu(Wdf o[1:] +
-//   betad[pair]) -> v2 = relu(Wd2 v1 + bd2) -> rgb = Wrv v2 + betar[ray]          (models/model.py:179-194, code-folded)
+//   h1 = relu(W1 gamma(x) + b1) -> h2 = relu(W2h h1 + beta2[ray]) -> v1 = relu(Wfh h2 + betaf[ray] + [Wdv|bd1][gamma(d)|1])
+//   -> v2 = relu(Wd2 v1 + bd2) -> rgb = Wrv v2 + betar[ray], sigma = w_sigma h2 + betas[ray]
+// (models/model.py:179-194, code-folded; fc_out folded into layer_dir1: Wfh = Wdf Wout'[:, :H], see codenerf.cu)
 // as ONE persistent kernel per direction.  tcgen05.mma (kind::f16, bf16 operands, fp32 accumulators in TMEM), weights
 // streamed by 1-D TMA bulk copies of pre-swizzled 32 KB chunk images into a shared-memory ring, activations never leave
 // shared memory between layers (except the bf16 tile images saved for the backward by TMA bulk stores).
@@ -16,7 +17,8 @@
 
 // ---- weight packing ------------------------------------------------------------------------------------------------
 // chunk image element (row r in [0,256), col c in [0,64)) of chunk `ch`.
-__global__ void pack_weights_kernel(cnrf_codenerf_params p, int dx, int dd, Packed pk) {
+// wf: the folded matrix Wdf Wout' [256 x 512] fp32 (its left half is the per-sample layer Wfh)
+__global__ void pack_weights_kernel(cnrf_codenerf_params p, const float* __restrict__ wf, int dx, int dd, Packed pk) {
   const int ch = blockIdx.x;                  // 0 .. FWD_CHUNKS+BWD_CHUNKS-1
   for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < 256 * 64; i += gridDim.y * blockDim.x) {
     int r = i >> 6, c = i & 63;
@@ -29,22 +31,20 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, int dx, int dd, Pack
       } else if (ch == EXT_CHUNK) {           // view-direction half of layer_dir1 + its bias (the extension's ones column)
         v = c < dd ? p.weight[CNRF_L_DIR1][r * (256 + dd) + 256 + c] : (c == dd ? p.bias[CNRF_L_DIR1][r] : 0.f);
       } else {
-        int l = (ch - 1) >> 2, k = ((ch - 1) & 3) * 64 + c;   // l: 0 W2h, 1 Woh[1:], 2 Wdf, 3 Wd2
+        int l = (ch - 1) >> 2, k = ((ch - 1) & 3) * 64 + c;   // l: 0 W2h, 1 Wfh, 2 Wd2
         if (l == 0) v = p.weight[CNRF_L_XYZ2][r * 512 + k];
-        else if (l == 1) v = p.weight[CNRF_L_FC_OUT][(r + 1) * 512 + k];
-        else if (l == 2) v = p.weight[CNRF_L_DIR1][r * (256 + dd) + k];
+        else if (l == 1) v = wf[r * 512 + k];
         else v = p.weight[CNRF_L_DIR2][r * 256 + k];
       }
     } else {
       int b = ch - FWD_CHUNKS;
       base = pk.bwd + (size_t)b * CHUNK;
-      int l = b >> 2, n = (b & 3) * 64 + c;   // image[k = r][n]: l: 0 Wd2^T, 1 Wdf^T, 2 Woh[1:]^T, 3 W2h^T
+      int l = b >> 2, n = (b & 3) * 64 + c;   // image[k = r][n]: l: 0 Wd2^T, 1 Wfh^T, 2 W2h^T
       if (b == BWD_X_CHUNK) {                 // W1^T: rows 64 q + n (input feature n), column c = hidden unit 64 q + c
         const int q = r >> 6, nin = r & 63;
         v = nin < dx ? p.weight[CNRF_L_XYZ1][(q * 64 + c) * dx + nin] : 0.f;
       } else if (l == 0) v = p.weight[CNRF_L_DIR2][n * 256 + r];
-      else if (l == 1) v = p.weight[CNRF_L_DIR1][n * (256 + dd) + r];
-      else if (l == 2) v = p.weight[CNRF_L_FC_OUT][(n + 1) * 512 + r];
+      else if (l == 1) v = wf[n * 512 + r];
       else v = p.weight[CNRF_L_XYZ2][n * 512 + r];
     }
     *reinterpret_cast<__nv_bfloat16*>(base + slab_offset(r, c)) = __float2bfloat16(v);
@@ -71,8 +71,8 @@ struct TcChainArgs {   // mirrors the declaration in codenerf.cu
   const cnrf_codenerf_params* p;
   const float* x_xyz; int64_t ld_xyz;
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;
-  const float *b2, *bo, *br, *bd;
-  const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
+  const float *b2, *bf, *bos, *br;            // per-ray bias tables [N,256], [N,256] (folded layer_dir1), [N] (sigma), [N,3]
+  const float* wf;                            // Wdf Wout' [256 x 512] fp32 (this call's fold)
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
   const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
 };
@@ -143,12 +143,12 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   build_ext_kernel<<<grid_for(pairs_of(a.M) * 1024, 256), 256, 0, st>>>(a.x_dir, a.ld_dir, a.dd, a.N, a.M, a.S, a.pairing,
                                                                       ext, pairs_of(a.M));
   CNRF_LAUNCH_CHECK();
-  pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.dx, a.dd, pk);
+  pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.wf, a.dx, a.dd, pk);
   CNRF_LAUNCH_CHECK();
   FwdArgs f;
   f.N = a.N; f.M = a.M; f.S = a.S; f.pairing = a.pairing; f.dx = a.dx;
   f.pts = a.pts; f.x_xyz = a.x_xyz; f.ld_xyz = a.ld_xyz; f.freqs = a.freqs_xyz; f.L = a.L_xyz; f.inc = a.inc_xyz;
-  f.b2 = a.b2; f.bof = a.bof; f.bos = a.bos; f.br = a.br; f.gid = a.gid; f.ext = ext; f.pk = pk; f.raw = raw;
+  f.b2 = a.b2; f.bf = a.bf; f.bos = a.bos; f.br = a.br; f.gid = a.gid; f.ext = ext; f.pk = pk; f.raw = raw;
   f.saved = saved_al;
   f.err = tc_error_ptr();
   const int64_t pairs = ((a.M + TILE - 1) / TILE + 1) / 2;
@@ -167,7 +167,7 @@ extern "C" int cnrf_debug_tc_error(void) {
 // =====================================================================================================================
 // Weight gradients: dW[n][k] = sum_m dY[m][n] X[m][k] on tensor cores, operands read as MN-major straight from the saved
 // bf16 images (the sample index is the contraction dimension, so the very same image is its own transpose).
-// grid = (ctas per job, 5 jobs); a CTA accumulates its share of the tiles in TMEM (2 x [128 x N] fp32) and adds it to
+// 1-D grid split over six jobs; a CTA accumulates its share of the tiles in TMEM (2 x [128 x N] fp32) and adds it to
 // the fp32 gradient with red.global.add.
 // =====================================================================================================================
 constexpr int DW_THREADS = 192;
@@ -180,7 +180,7 @@ constexpr int DW_SMEM = DW_RING * DW_STAGE + 256 + 2 * 64 * 16;   // ring + barr
 // table), the same plus the sigma-weighted column sums of the B image (fc_out row 0), or the three rgb-weighted column
 // sums of a streamed-only image (fc_rgb).
 enum { RED_NONE = 0, RED_COLSUM = 1, RED_RAY = 2, RED_RAY_SIGMA = 3, RED_RGB = 4 };
-constexpr int DW_JOBS = 7;
+constexpr int DW_JOBS = 6;
 struct DwJob { int dy_img;   /* >= 0: image of the gradient set; < 0: image -1-dy_img of the saved set */
                int x_img;    /* -1: gamma slab, -2: view-direction extension slab of the tile pair */
                int n_cols;   /* 0: no GEMM, reduction only */
@@ -554,9 +554,11 @@ size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward) {
   return b;
 }
 
+// d_bf [N,256]: per-ray sums of d v1p (gradient of the folded per-ray bias); dwfh [256 x 256]: gradient of the folded matrix
+// Wfh -- the caller unfolds both into fc_out and layer_dir1 (codenerf.cu).  d_bo [N,257]: only column 0 (sigma) is written.
 int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* saved, size_t saved_bytes,
-                      const cnrf_codenerf_grads* g, float* d_b2, float* d_bo, float* d_br, float* d_bd, float* g_x_xyz,
-                      void* ws, size_t ws_bytes, cudaStream_t st) {
+                      const cnrf_codenerf_grads* g, float* d_b2, float* d_bo, float* d_br, float* d_bd, float* d_bf,
+                      float* dwfh, float* g_x_xyz, void* ws, size_t ws_bytes, cudaStream_t st) {
   // d_bd != NULL: also the per-ray sums of d v1p (the caller turns them into the gradient of the view-direction encoding);
   // g_x_xyz != NULL: the backward chain runs its fifth stage, d gamma(x) = d h1p W1   (pose optimisation, eval.py:129-168)
   if ((d_bd || g_x_xyz) && a.gid) return CNRF_E_UNSUPPORTED;      // rays with shared codes carry no pose gradient
@@ -589,21 +591,23 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   if ((rc = cnrf_fill_zero(d_b2, (size_t)a.N * 256 * sizeof(float), st))) return rc;
   if ((rc = cnrf_fill_zero(d_bo, (size_t)a.N * 257 * sizeof(float), st))) return rc;
   if ((rc = cnrf_fill_zero(d_br, (size_t)a.N * 3 * sizeof(float), st))) return rc;
+  if ((rc = cnrf_fill_zero(d_bf, (size_t)a.N * 256 * sizeof(float), st))) return rc;
+  if ((rc = cnrf_fill_zero(dwfh, (size_t)256 * 256 * sizeof(float), st))) return rc;
   float* const nil = nullptr;
-  d.job[0] = {0, 3, 256, g->weight[CNRF_L_DIR2], 256, 256, nil, -1, RED_COLSUM, g->bias[CNRF_L_DIR2], 0, nil};   // d v2p^T v1
-  d.job[1] = {1, 2, 256, g->weight[CNRF_L_DIR1], 256 + a.dd, 256, nil, -1, RED_NONE, nil, 0, nil};              // d v1p^T feat
-  d.job[2] = {2, 1, 256, g->weight[CNRF_L_FC_OUT] + 512, 512, 256, nil, -1, RED_RAY_SIGMA, d_bo + 1, 257,
-              g->weight[CNRF_L_FC_OUT]};                                                       // d feat^T h2   (rows 1..256)
-  d.job[3] = {3, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nil, -1, RED_RAY, d_b2, 256, nil};  // d h2p^T h1
-  d.job[4] = {4, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1], 63, RED_NONE, nil, 0, nil};   // d h1p^T [gamma | 1]
-  d.job[5] = {1, -2, 64, g->weight[CNRF_L_DIR1] + 256, 256 + a.dd, a.dd, g->bias[CNRF_L_DIR1], a.dd, RED_NONE, nil, 0,
+  // saved images: 0 h1, 1 h2, 2 v1, 3 v2;  gradient images: 0 d v2p, 1 d v1p, 2 d h2p, 3 d h1p
+  d.job[0] = {0, 2, 256, g->weight[CNRF_L_DIR2], 256, 256, nil, -1, RED_COLSUM, g->bias[CNRF_L_DIR2], 0, nil};   // d v2p^T v1
+  d.job[1] = {1, 1, 256, dwfh, 256, 256, nil, -1, RED_RAY_SIGMA, d_bf, 256, g->weight[CNRF_L_FC_OUT]};  // d v1p^T h2 -> d Wfh; per-ray
+                                                                       // sums of d v1p; sigma-weighted column sums of h2 (fc_out row 0)
+  d.job[2] = {2, 0, 256, g->weight[CNRF_L_XYZ2], 512, 256, nil, -1, RED_RAY, d_b2, 256, nil};  // d h2p^T h1
+  d.job[3] = {3, -1, 64, g->weight[CNRF_L_XYZ1], a.dx, a.dx, g->bias[CNRF_L_XYZ1], 63, RED_NONE, nil, 0, nil};   // d h1p^T [gamma | 1]
+  d.job[4] = {1, -2, 64, g->weight[CNRF_L_DIR1] + 256, 256 + a.dd, a.dd, g->bias[CNRF_L_DIR1], a.dd, RED_NONE, nil, 0,
               nil};                                                                            // d v1p^T [gamma(d) | 1]
-  d.job[6] = {-1 - 4, 0, 0, nil, 0, 0, nil, -1, RED_RGB, g->weight[CNRF_L_FC_RGB], 512, nil};  // g_rgb^T v2 (no GEMM)
-  {   // one CTA per SM, shared in proportion to the bytes a job streams per tile (128 KB for the four 256-wide jobs,
+  d.job[5] = {-1 - 3, 0, 0, nil, 0, 0, nil, -1, RED_RGB, g->weight[CNRF_L_FC_RGB], 512, nil};  // g_rgb^T v2 (no GEMM)
+  {   // one CTA per SM, shared in proportion to the bytes a job streams per tile (128 KB for the three 256-wide jobs,
       // 80, 72 and 64 KB for the other three): the kernel is HBM-bound and a single SM only pulls ~45 GB/s
     const int64_t halves = tiles * 2;
     // measured shares (B200, S = 160): reducer-heavy jobs are bound by their four reducer warps, not by their bytes
-    static const int share148[DW_JOBS] = {22, 19, 31, 26, 13, 13, 24};
+    static const int share148[DW_JOBS] = {25, 36, 30, 15, 15, 27};
     int shares[DW_JOBS];
     int job_mask = (1 << DW_JOBS) - 1;
     {

@@ -13,17 +13,21 @@ constexpr int TILE_BYTES = 4 * SLAB;      // 64 KB: one [128 x 256] activation t
 constexpr int CHUNK = 256 * 128;          // 32 KB: one [256 x 64] weight chunk image
 constexpr int RING = 3;
 constexpr int NTHREADS = 320;
-constexpr int FWD_CHUNKS = 18;            // 1 (layer_xyz1, K=64) + 4 x 4 + 1 (view-direction extension of layer_dir1)
-constexpr int EXT_CHUNK = 17;             // [Wdv | b_dir1 | 0]: K = dim_dir + 1 <= 32 columns of a [256 x 64] image
-constexpr int BWD_CHUNKS = 17;            // 4 x 4 transposed + W1^T (four [64 in x 64 hidden] K-chunks stacked in one image)
-constexpr int BWD_X_CHUNK = 16;           // ... its index: B operand of the input-gradient stage d gamma(x) = d h1p W1
+// fc_out is FOLDED into layer_dir1 (models/model.py:182-189 apply no activation between them): the per-sample chain has four
+// 256-wide tensor-core layers  W1 | W2h | Wfh = Wdf Wout'[:, :H] | Wd2  (the fold is rebuilt from the fp32 parameters at
+// every call, codenerf.cu)
+constexpr int NUM_TC_LAYERS = 4;
+constexpr int FWD_CHUNKS = 14;            // 1 (layer_xyz1, K=64) + 3 x 4 + 1 (view-direction extension of layer_dir1)
+constexpr int EXT_CHUNK = 13;             // [Wdv | b_dir1 | 0]: K = dim_dir + 1 <= 32 columns of a [256 x 64] image
+constexpr int BWD_CHUNKS = 13;            // 3 x 4 transposed + W1^T (four [64 in x 64 hidden] K-chunks stacked in one image)
+constexpr int BWD_X_CHUNK = 12;           // ... its index: B operand of the input-gradient stage d gamma(x) = d h1p W1
 constexpr int CONST_BYTES = 4 * 256 * 2;    // bf16 [w_sigma | w_rgb(3)] staged in shared memory
 constexpr int SMEM_BYTES = 2 * TILE_BYTES + RING * CHUNK + CONST_BYTES + 256 /*barriers*/;
 
 // Packed weights (bf16 images + fp32 vectors), rebuilt from the fp32 parameters at every call (they change each step).
 struct Packed {
-  uint8_t* fwd;      // FWD_CHUNKS x 32 KB: [W1|b1], W2h, Woh[1:], Wdf, Wd2   (rows = out feature, cols = in feature)
-  uint8_t* bwd;      // BWD_CHUNKS x 32 KB: Wd2^T, Wdf^T, Woh[1:]^T, W2h^T, W1^T (rows = in feature,  cols = out feature)
+  uint8_t* fwd;      // FWD_CHUNKS x 32 KB: [W1|b1], W2h, Wfh, Wd2, [Wdv|bd1]   (rows = out feature, cols = in feature)
+  uint8_t* bwd;      // BWD_CHUNKS x 32 KB: Wd2^T, Wfh^T, W2h^T, W1^T          (rows = in feature,  cols = out feature)
   float* w_sigma;    // [256]  fc_out row 0, hidden half
   float* w_rgb;      // [3][256] fc_rgb, hidden half
   float* b_dir2;     // [256]
@@ -80,7 +84,7 @@ __device__ __forceinline__ bool wait_bar(uint64_t* bar, uint32_t parity, Bars* b
 }
 
 constexpr size_t SAVED_GAMMA = SLAB;                          // gamma(x) slab (K = 64)
-constexpr size_t SAVED_MASKS = SAVED_GAMMA + 5 * (size_t)TILE_BYTES;      // after the h1, h2, feat, v1, v2 images
+constexpr size_t SAVED_MASKS = SAVED_GAMMA + 4 * (size_t)TILE_BYTES;      // after the h1, h2, v1, v2 images
 constexpr size_t MASK_BYTES = 128 * 32;                                   // one layer's sign bits: 8 words per sample row
 // 4 x 4 KB of sign-bit words (h1, h2, v1, v2 pre-activations; bit 31-j of word cb = column 32 cb + j is <= 0): the
 // backward reads 32 B per row and layer instead of re-reading the 64 KB activation image for its ReLU mask
@@ -90,7 +94,7 @@ struct FwdArgs {
   int64_t N, M; int S, pairing, dx;
   const float* pts; const float* x_xyz; int64_t ld_xyz;
   const float* freqs; int L; int inc;
-  const float *b2, *bof, *bos, *br;        // per-ray bias tables: [N,256], [N,256] (fc_out feat), [N] (sigma), [N,3]
+  const float *b2, *bf, *bos, *br;         // per-ray bias tables: [N,256] layer_xyz2, [N,256] folded layer_dir1, [N] (sigma), [N,3]
   const int32_t* gid;                      // row of those tables that ray r uses (NULL: r) -- shared-code mode
   const uint8_t* ext;                      // per tile PAIR: [128 x 64] bf16 slab, columns 32t..32t+31 = [gamma(d_pair) | 1 | 0] of tile t
   Packed pk;
@@ -168,7 +172,7 @@ __device__ __forceinline__ void build_input_row_octaves(const float x[3], bool v
 int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st);
 
 // Backward-data chain (mlp_bwd_tc.cu)
-constexpr size_t DY_PER_TILE = 5 * (size_t)TILE_BYTES;      // d v2p, d v1p, d feat, d h2p, d h1p
+constexpr size_t DY_PER_TILE = 4 * (size_t)TILE_BYTES;      // d v2p, d v1p, d h2p, d h1p
 struct BwdArgs {
   int64_t M;
   const float* g_raw;          // [M,4]
