@@ -10,6 +10,15 @@
 // v1 = relu(Wdf o[1:] + betad[pair]), v2 = relu(Wd2 v1 + bd2), rgb = Wrv v2 + betar[ray].   `pair` reproduces the
 // reference's view-direction tiling (row k -> ray k mod N, nerf/__init__.py:127) unless CNRF_PAIRING_CORRECT.
 // The chain runs either as fp32 SIMT GEMMs (this file; parity mode) or as the fused tcgen05 kernels of mlp_tc.cu.
+//
+// fc_out fold (tensor-core mode only).  models/model.py:182-189 apply no activation between fc_out and layer_dir1, so
+//     v1 = relu(Wdf (Wout' [h2 | as2] + bo') + Wdv gamma(d) + bd1) = relu(Wfh h2 + betaf[ray] + Wdv gamma(d) + bd1),
+//     Wf = Wdf Wout' = [Wfh | Wfc]  [256 x 512],   betaf = Wfc as2 + Wdf bo'         (Wout' = fc_out rows 1.., bo' likewise)
+// and the per-sample chain has four 256-wide layers instead of five.  Wf and Wdf bo' are rebuilt from the fp32 parameters
+// at every call (two small GEMMs riding in the first per-ray launch).  The backward returns d Wfh (weight-gradient
+// kernel) and d betaf (its per-ray reducers); they are unfolded here:
+//     d Wdf = d Wfh Wout'h^T + d betaf^T betao',   d Wout'h = Wdf^T d Wfh,   d betao' = d betaf Wdf
+// after which the code halves of fc_out take the same path as before (per_ray_bwd).
 #include <algorithm>
 #include "common.cuh"
 #include "internal.h"
@@ -64,11 +73,17 @@ inline bool carve_saved(const Dims& d, void* p, size_t bytes, SavedF32& s) {
   return a.ok;
 }
 // per-ray bias tables (forward workspace) and their gradients (backward workspace)
-struct Tables { float *b2, *bo, *br, *bd, *bof, *bos; };   // bof/bos: fc_out table split (aligned feat / sigma) for the tc path
-inline size_t tables_bytes(const Dims& d) { return 2 * al(d.N * d.H) + al(d.N * (d.C + 1)) + al(d.N * 3) + al(d.N * d.C) + al(d.N); }
+// bof/bos: fc_out bias table split (aligned feat / sigma) for the tc path; bf: bias table of the folded layer_dir1 (forward)
+// or its gradient (backward); wf [H x 2H] + bfold [H]: this call's fold; dwfh [H x H]: gradient of the folded matrix
+struct Tables { float *b2, *bo, *br, *bd, *bof, *bos, *bf, *wf, *bfold, *dwfh; };
+inline size_t tables_bytes(const Dims& d) {
+  return 2 * al(d.N * d.H) + al(d.N * (d.C + 1)) + al(d.N * 3) + al(d.N * d.C) + al(d.N) + al(d.N * d.H) + al((size_t)d.H * 2 * d.H) +
+         al(d.H) + al((size_t)d.H * d.H);
+}
 inline void carve_tables(const Dims& d, Arena& a, Tables& t) {
   t.b2 = a.take(d.N * d.H); t.bo = a.take(d.N * (d.C + 1)); t.br = a.take(d.N * 3); t.bd = a.take(d.N * d.H);
   t.bof = a.take(d.N * d.C); t.bos = a.take(d.N);
+  t.bf = a.take(d.N * d.H); t.wf = a.take((size_t)d.H * 2 * d.H); t.bfold = a.take(d.H); t.dwfh = a.take((size_t)d.H * d.H);
 }
 
 #define RUN(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
@@ -166,6 +181,7 @@ struct Batch {
   const int32_t* rows_dev = nullptr;       // every problem of the batch runs over this many rows (device-resident)
   explicit Batch(const int32_t* rd = nullptr) : rows_dev(rd) {}
   void add(const GemmArgs& a) { g[n] = a; g[n].rows_dev = rows_dev; ++n; }
+  void add_fixed(const GemmArgs& a) { g[n] = a; g[n].rows_dev = nullptr; g[n].rows_dim = 0; ++n; }   // shape known on the host
   int flush(bool tc, cudaStream_t st) {
     int rc = tc ? cnrf_gemm_tc_batch(g, n, st) : CNRF_E_UNSUPPORTED;
     if (rc == CNRF_E_UNSUPPORTED && rows_dev) return rc;      // only the tensor-core kernel reads a device-side row count
@@ -178,11 +194,24 @@ struct Batch {
   }
 };
 
+// plain strided GEMM C[M,N] = A B without epilogue (the fold / unfold products)
+GemmArgs mk_mm(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs, int64_t b_cs, float* Cm, int64_t ldc,
+               int64_t M, int N, int64_t K) {
+  GemmArgs g;
+  g.A = A; g.a_rs = a_rs; g.a_cs = a_cs; g.B = B; g.b_rs = b_rs; g.b_cs = b_cs; g.C = Cm; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
+  return g;
+}
+
+// bof_keep: where the fc_out feature bias table betao' [N,C] goes in the folded mode (the backward's d Wdf needs it again)
 int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir, int64_t ld_dir, const float* z_s,
                 int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
-                bool split_bo, cudaStream_t st) {
+                bool split_bo, cudaStream_t st, float* bof_keep = nullptr) {
   const int H = d.H, C = d.C;
   Batch b(d.rows_dev);
+  if (split_bo) {   // the fold: Wf = Wdf Wout' [H x 2H], bfold = Wdf bo'   (Wout' = fc_out rows 1..C, Wdf = layer_dir1[:, :C])
+    b.add_fixed(mk_mm(p->weight[CNRF_L_DIR1], C + d.dd, 1, p->weight[CNRF_L_FC_OUT] + (H + C), H + C, 1, t.wf, 2 * H, H, 2 * H, C));
+    b.add_fixed(mk_mm(p->weight[CNRF_L_DIR1], C + d.dd, 1, p->bias[CNRF_L_FC_OUT] + 1, 1, 1, t.bfold, 1, H, 1, C));
+  }
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 1));     // model.py:174
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 1));     // :175
   b.add(mk_lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 1));  // :177
@@ -190,9 +219,10 @@ int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir
   if (!d.tc) b.add(mk_lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0));
   RUN(b.flush(d.tc, st));
   b.add(mk_lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0));
-  if (split_bo) {   // tensor-core chain: 16-byte aligned feature rows + a separate sigma column
-    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, t.bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0));
+  if (split_bo) {   // tensor-core chain: folded layer_dir1 bias rows, the sigma column, and betao' itself for the backward
+    b.add(mk_lin(as2, C, d.N, C, t.wf + H, 2 * H, H, t.bf, H, t.bfold, 0));
     b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0));
+    if (bof_keep) b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, bof_keep, C, p->bias[CNRF_L_FC_OUT] + 1, 0));
   } else {
     b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0));
   }
@@ -202,10 +232,12 @@ int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir
 
 // gradients of the bias tables -> code-layer weights, code halves of the split layers, z_s / z_t / x_dir.
 // tmp: 3 x [N,C] scratch + [N] (a ones vector for the bias-gradient column sums of the tensor-core mode).
+// bof (tensor-core mode): the forward's betao' table [N,C]; dt.bf / dt.dwfh then hold d betaf and d Wfh (see the fold
+// note at the top of the file) and dt.bo only its sigma column
 int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codenerf_grads* g, const float* x_dir,
                 int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* as1,
                 const float* as2, const float* at, const Tables& dt, float* tmp, float* g_z_s, float* g_z_t,
-                float* g_x_dir, cudaStream_t st) {
+                float* g_x_dir, cudaStream_t st, const float* bof = nullptr) {
   const int H = d.H, C = d.C;
   const size_t nc = al(d.N * C) / sizeof(float);
   float *tmp_t = tmp, *tmp_s2 = tmp + nc, *tmp_s1 = tmp + 2 * nc, *ones = tmp + 3 * nc;
@@ -216,6 +248,14 @@ int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codener
     RUN(cnrf_fill_batch(f, st));
   }
   Batch b(d.rows_dev);
+  if (d.tc) {       // unfold:  d Wdf = d Wfh Wout'h^T (+ d betaf^T betao' below),  d Wout'h = Wdf^T d Wfh,  d betao' = d betaf Wdf
+    if (!bof) return CNRF_E_NULL;
+    b.add_fixed(mk_mm(dt.dwfh, H, 1, p->weight[CNRF_L_FC_OUT] + (H + C), 1, H + C, g->weight[CNRF_L_DIR1], C + d.dd, H, C, H));
+    b.add_fixed(mk_mm(p->weight[CNRF_L_DIR1], 1, C + d.dd, dt.dwfh, H, 1, g->weight[CNRF_L_FC_OUT] + (H + C), H + C, C, H, H));
+    b.add(mk_dgrad(dt.bf, H, d.N, H, p->weight[CNRF_L_DIR1], C + d.dd, C, dt.bo + 1, C + 1, nullptr, 0, 0));
+    RUN(b.flush(true, st));
+    b.add(mk_wgrad(dt.bf, H, bof, C, d.N, H, C, g->weight[CNRF_L_DIR1], C + d.dd));     // += onto the product above
+  }
   // texture branch: betar = Wrt at + br;   shape branch 2: betao = Woc as2 + bo;   shape branch 1: beta2 = W2c as1 + b2;
   // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
   b.add(mk_wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C));
@@ -342,7 +382,7 @@ extern "C" size_t cnrf_codenerf_saved_bytes(const cnrf_field_shape* s) {
   Dims d = dims_of(s);
   if (s->precision == CNRF_PRECISION_FP32) return saved_f32_bytes(d);
   // (+ shared-code mode: the code runs and one code row per run, found once in the forward and reused by the backward)
-  return 3 * al(d.N * d.C) + cnrf_code_runs_bytes(d.N) + 256 + 2 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M) + 2048;
+  return 4 * al(d.N * d.C) + cnrf_code_runs_bytes(d.N) + 256 + 2 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M) + 2048;
 }
 
 extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32_t backward) {
@@ -353,7 +393,7 @@ extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32
     if (!backward) return b + (s->keep ? 0 : saved_f32_bytes(d));     // inference still needs the activation buffers
     return b + 2 * al(d.M * max_sz(d.H, d.C + 1)) + 3 * al(d.N * d.C) + al(d.N);
   }
-  return b + 3 * al(d.N * d.C) + al(d.N) + (s->keep || backward ? 0 : 3 * al(d.N * d.C)) + cnrf_tc_workspace_bytes(d.N, d.M, backward) +
+  return b + 3 * al(d.N * d.C) + al(d.N) + (s->keep || backward ? 0 : 4 * al(d.N * d.C)) + cnrf_tc_workspace_bytes(d.N, d.M, backward) +
          cnrf_code_runs_bytes(d.N) + 256 + 4 * al(d.N * d.C);      // shared-code mode: runs, one code row and gradient row per run
 }
 
@@ -363,16 +403,16 @@ struct TcChainArgs {
   const cnrf_codenerf_params* p;
   const float* x_xyz; int64_t ld_xyz;         // pre-embedded input, or
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;   // points to encode
-  const float *b2, *bo, *br, *bd;             // per-ray bias tables [N,256],[N,257],[N,3],[N,256]
-  const float *bof, *bos;                     // fc_out bias table split into an aligned feature part and sigma
+  const float *b2, *bf, *bos, *br;            // per-ray bias tables [N,256], [N,256] (folded layer_dir1), [N] (sigma), [N,3]
+  const float* wf;                            // Wdf Wout' [256 x 512] fp32 (this call's fold)
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
   const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
 };
 int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
                       cudaStream_t st);
 int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* saved, size_t saved_bytes,
-                      const cnrf_codenerf_grads* g, float* d_b2, float* d_bo, float* d_br, float* d_bd,
-                      float* g_x_xyz /*[M,dx] or NULL*/, void* ws, size_t ws_bytes, cudaStream_t st);
+                      const cnrf_codenerf_grads* g, float* d_b2, float* d_bo, float* d_br, float* d_bd, float* d_bf,
+                      float* dwfh, float* g_x_xyz /*[M,dx] or NULL*/, void* ws, size_t ws_bytes, cudaStream_t st);
 
 namespace {
 
@@ -431,6 +471,7 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   Arena sa(s->keep ? saved : nullptr, s->keep ? saved_bytes : 0);
   Arena& act = s->keep ? sa : w;            // what the backward needs again lives in the saved buffer
   as1 = act.take(d.N * d.C); as2 = act.take(d.N * d.C); at = act.take(d.N * d.C);
+  float* bof = act.take(d.N * d.C);         // betao' of the folded fc_out: only the backward reads it
   if (!act.ok) return CNRF_E_WORKSPACE;
   const float *zs = in.z_s, *zt = in.z_t;
   int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
@@ -440,9 +481,9 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
     zs = sc.zc_s; zt = sc.zc_t; ld_zs = ld_zt = d.C;
   }
   if (s->keep) { tc_saved = sa.base + sa.off; tc_saved_bytes = sa.cap - sa.off; }
-  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, t, true, st));
+  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, t, true, st, s->keep ? bof : nullptr));
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, t.b2, t.bo, t.br, t.bd, t.bof, t.bos, in.x_dir, in.ld_dir, in.ids ? sc.runs.gid : nullptr};
+                in.inc_xyz, t.b2, t.bf, t.bos, t.br, t.wf, in.x_dir, in.ld_dir, in.ids ? sc.runs.gid : nullptr};
   return cnrf_tc_chain_fwd(a, raw, tc_saved, tc_saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
 
@@ -474,6 +515,7 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   if (d.H != 256 || d.C != 256 || d.dx > 63 || d.dd > 31) return CNRF_E_UNSUPPORTED;
   Arena sa(const_cast<void*>(saved), saved_bytes);
   float* as1 = sa.take(d.N * d.C); float* as2 = sa.take(d.N * d.C); float* at = sa.take(d.N * d.C);
+  const float* bof = sa.take(d.N * d.C);
   if (!sa.ok) return CNRF_E_WORKSPACE;
   const float *zs = in.z_s, *zt = in.z_t;
   int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
@@ -486,11 +528,11 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
     if (!w.ok) return CNRF_E_WORKSPACE;
   }
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
-                in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, in.x_dir, in.ld_dir,
+                in.inc_xyz, nullptr, nullptr, nullptr, nullptr, nullptr, in.x_dir, in.ld_dir,
                 in.ids ? sc.runs.gid : nullptr};
-  RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, g_x_dir ? dt.bd : nullptr, g_x_xyz,
-                        w.base + w.off, w.cap - w.off, st));
-  RUN(per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, dt, tmp, gz_s, gz_t, g_x_dir, st));
+  RUN(cnrf_tc_chain_bwd(a, g_raw, sa.base + sa.off, sa.cap - sa.off, g, dt.b2, dt.bo, dt.br, g_x_dir ? dt.bd : nullptr, dt.bf,
+                        dt.dwfh, g_x_xyz, w.base + w.off, w.cap - w.off, st));
+  RUN(per_ray_bwd(d, p, g, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, dt, tmp, gz_s, gz_t, g_x_dir, st, bof));
   if (in.ids) {          // one row per run -> dense table gradients (what torch.nn.Embedding's backward produces)
     if (!accumulate_tables) {
       FillBatch f;
