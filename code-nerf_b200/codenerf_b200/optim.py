@@ -26,7 +26,8 @@ class FusedAdamW(torch.optim.Optimizer):
             raise ValueError("invalid AdamW hyper-parameter")
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=False,
                                       maximize=False))
-        self._table = None          # cached ctypes array: parameter / state pointers do not change between steps
+        self._n = {}                # python-side step counters (state["step"] tensors are refreshed lazily, see _sync_steps)
+        self._tabs = {}             # (b1, b2, eps, count) -> reusable ctypes table
 
     def _init_state(self, p):
         st = self.state[p]
@@ -35,6 +36,21 @@ class FusedAdamW(torch.optim.Optimizer):
             st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
             st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
         return st
+
+    def _sync_steps(self):
+        """torch.optim.AdamW keeps `step` as a tensor in the per-parameter state; here the counters live in Python between
+        checkpoints (38 tensor increments per step cost more host time than the optimiser launch itself)."""
+        for p, n in self._n.items():
+            if p in self.state and len(self.state[p]):
+                self.state[p]["step"] = torch.tensor(float(n), dtype=torch.float32)
+
+    def state_dict(self):
+        self._sync_steps()
+        return super().state_dict()
+
+    def load_state_dict(self, state_dict):
+        super().load_state_dict(state_dict)
+        self._n = {p: int(float(st["step"])) for p, st in self.state.items() if "step" in st}
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -57,21 +73,25 @@ class FusedAdamW(torch.optim.Optimizer):
         if not any(by_betas.values()):
             return loss
         # every parameter passed validation: only now touch optimiser state (a raise above leaves all step counters alone)
-        for rows in by_betas.values():
-            for i, (p, g, _, lr, wd) in enumerate(rows):
-                st = self._init_state(p)
-                st["step"] += 1
-                rows[i] = (p, g, st, lr, wd)
         lib = _lib.load()
         stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         for (b1, b2, eps), rows in by_betas.items():
             if not rows:
                 continue
-            tab = (_AdamWTensor * len(rows))()
-            for i, (p, g, st, lr, wd) in enumerate(rows):
+            key = (b1, b2, eps, len(rows))
+            tab = self._tabs.get(key)
+            if tab is None:
+                tab = self._tabs[key] = (_AdamWTensor * len(rows))()
+            for i, (p, g, _, lr, wd) in enumerate(rows):
+                st = self._init_state(p)
+                n = self._n.get(p)
+                if n is None:
+                    n = int(float(st["step"]))
+                n += 1
+                self._n[p] = n
                 t = tab[i]
                 t.param, t.grad = p.data_ptr(), g.data_ptr()
                 t.exp_avg, t.exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
-                t.numel, t.lr, t.weight_decay, t.step = p.numel(), lr, wd, float(st["step"])
+                t.numel, t.lr, t.weight_decay, t.step = p.numel(), lr, wd, float(n)
             _lib.check(lib.cnrf_adamw_step(C.cast(tab, C.c_void_p), len(rows), b1, b2, eps, stream), "cnrf_adamw_step")
         return loss
