@@ -94,6 +94,8 @@ _SIGS = {
                                     c_f32p, C.c_void_p, c_sz, C.c_void_p]),
     "cnrf_field_fwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
                                  c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_field_fwd_noalloc": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
+                                         c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p]),
     "cnrf_field_bwd": (C.c_int, [C.POINTER(FieldShape), C.POINTER(PtrTable), c_f32p, c_f32p, c_f32p, c_i32, c_f32p, c_i32,
                                  c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p, c_sz, C.POINTER(PtrTable), c_f32p,
                                  c_f32p, c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),

@@ -14,6 +14,7 @@ extern "C" const char* cnrf_error_string(int code) {
     case CNRF_E_WORKSPACE: return "workspace or saved buffer missing or too small";
     case CNRF_E_UNSUPPORTED: return "configuration not supported by this precision mode";
     case CNRF_E_DEVICE: return "current device is not an sm_100 (B200) GPU";
+    case CNRF_E_SCRATCH_LIMIT: return "shape needs more scratch than the fixed 64 MiB array of cnrf_field_fwd_noalloc: split the rays into smaller chunks";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown libcnrf error";
   }
 }

@@ -35,6 +35,7 @@ extern "C" {
 #define CNRF_E_WORKSPACE (-3)/* workspace / saved buffer too small    */
 #define CNRF_E_UNSUPPORTED (-4)
 #define CNRF_E_DEVICE (-5)   /* not an sm_100 device                  */
+#define CNRF_E_SCRATCH_LIMIT (-6) /* cnrf_field_fwd_noalloc: the shape needs more than CNRF_NOALLOC_SCRATCH_BYTES */
 
 typedef void* cnrf_stream_t; /* cudaStream_t */
 
@@ -190,6 +191,23 @@ int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
                    int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* g_raw, const void* saved,
                    size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s, float* g_z_t, float* g_pts,
                    float* g_rd, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+
+/* forward_pass WITHOUT a caller workspace, for callers that cannot allocate (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  This entry point has no counterpart in the reference.
+ * It is cnrf_field_fwd with s->keep == 0 (inference; keep != 0 -> CNRF_E_UNSUPPORTED):
+ * same kernels, same results.  Its scratch is a fixed __device__ array of CNRF_NOALLOC_SCRATCH_BYTES inside the library,
+ * held by every GPU that loads libcnrf.so until the process exits; the call performs no cudaMalloc / cudaFree and calls no
+ * allocating routine.  A shape with cnrf_field_workspace_bytes(s, 0) > CNRF_NOALLOC_SCRATCH_BYTES is rejected with
+ * CNRF_E_SCRATCH_LIMIT before anything is launched (64 MiB holds e.g. 2048 rays x 128 samples in CNRF_PRECISION_BF16, the
+ * validation chunk of config/srn-cars-code-3080-val.yml; split larger batches into chunks of rays).  All calls on one device
+ * share the array and find the previous call's contents in it -- nothing needs clearing, every byte read is written
+ * earlier in the same call -- so calls that OVERLAP on the GPU (two streams, two host threads) race: keep them on one
+ * stream or order them with events.  The first call on a device looks the array's address up (cudaGetSymbolAddress): make
+ * that call once outside any graph capture. */
+#define CNRF_NOALLOC_SCRATCH_BYTES (64 * 1024 * 1024)
+int cnrf_field_fwd_noalloc(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
+                           const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const float* z_s,
+                           int64_t ld_zs, const float* z_t, int64_t ld_zt, float* raw /*[N,S,4]*/, cnrf_stream_t stream);
 
 /* Shared latent codes: train.py:78-96 gives every ray of an image the image's object id and looks the codes up per ray
  * (ShapeTextureEmbedding.forward, models/model.py:100-103).  These variants take the ids and the two embedding TABLES
