@@ -13,9 +13,10 @@
 //
 // fc_out fold (tensor-core mode only).  models/model.py:182-189 apply no activation between fc_out and layer_dir1, so
 //     v1 = relu(Wdf (Wout' [h2 | as2] + bo') + Wdv gamma(d) + bd1) = relu(Wfh h2 + betaf[ray] + Wdv gamma(d) + bd1),
-//     Wf = Wdf Wout' = [Wfh | Wfc]  [256 x 512],   betaf = Wfc as2 + Wdf bo'         (Wout' = fc_out rows 1.., bo' likewise)
-// and the per-sample chain has four 256-wide layers instead of five.  Wf and Wdf bo' are rebuilt from the fp32 parameters
-// at every call (two small GEMMs riding in the first per-ray launch).  The backward returns d Wfh (weight-gradient
+//     Wfh = Wdf Wout'h  [256 x 256],   betaf = Wdf betao',   betao' = Wout'c as2 + bo'   (Wout' = fc_out rows 1.., bo' likewise)
+// and the per-sample chain has four 256-wide layers instead of five.  Wfh is rebuilt from the fp32 parameters at every
+// call as four K-slices written to separate buffers (four one-round-trip problems in the first per-ray launch) that the
+// weight packer adds in a fixed order -- the forward stays bit-reproducible.  The backward returns d Wfh (weight-gradient
 // kernel) and d betaf (its per-ray reducers); they are unfolded here:
 //     d Wdf = d Wfh Wout'h^T + d betaf^T betao',   d Wout'h = Wdf^T d Wfh,   d betao' = d betaf Wdf
 // after which the code halves of fc_out take the same path as before (per_ray_bwd).
@@ -74,16 +75,16 @@ inline bool carve_saved(const Dims& d, void* p, size_t bytes, SavedF32& s) {
 }
 // per-ray bias tables (forward workspace) and their gradients (backward workspace)
 // bof/bos: fc_out bias table split (aligned feat / sigma) for the tc path; bf: bias table of the folded layer_dir1 (forward)
-// or its gradient (backward); wf [H x 2H] + bfold [H]: this call's fold; dwfh [H x H]: gradient of the folded matrix
-struct Tables { float *b2, *bo, *br, *bd, *bof, *bos, *bf, *wf, *bfold, *dwfh; };
+// or its gradient (backward); wf [4][H x H]: the four K-slices of this call's fold Wfh; dwfh [H x H]: gradient of Wfh
+struct Tables { float *b2, *bo, *br, *bd, *bof, *bos, *bf, *wf, *dwfh; };
 inline size_t tables_bytes(const Dims& d) {
-  return 2 * al(d.N * d.H) + al(d.N * (d.C + 1)) + al(d.N * 3) + al(d.N * d.C) + al(d.N) + al(d.N * d.H) + al((size_t)d.H * 2 * d.H) +
-         al(d.H) + al((size_t)d.H * d.H);
+  return 2 * al(d.N * d.H) + al(d.N * (d.C + 1)) + al(d.N * 3) + al(d.N * d.C) + al(d.N) + al(d.N * d.H) + al((size_t)4 * d.H * d.H) +
+         al((size_t)d.H * d.H);
 }
 inline void carve_tables(const Dims& d, Arena& a, Tables& t) {
   t.b2 = a.take(d.N * d.H); t.bo = a.take(d.N * (d.C + 1)); t.br = a.take(d.N * 3); t.bd = a.take(d.N * d.H);
   t.bof = a.take(d.N * d.C); t.bos = a.take(d.N);
-  t.bf = a.take(d.N * d.H); t.wf = a.take((size_t)d.H * 2 * d.H); t.bfold = a.take(d.H); t.dwfh = a.take((size_t)d.H * d.H);
+  t.bf = a.take(d.N * d.H); t.wf = a.take((size_t)4 * d.H * d.H); t.dwfh = a.take((size_t)d.H * d.H);
 }
 
 #define RUN(x) do { int rc__ = (x); if (rc__) return rc__; } while (0)
@@ -194,23 +195,30 @@ struct Batch {
   }
 };
 
-// plain strided GEMM C[M,N] = A B without epilogue (the fold / unfold products)
+// plain strided GEMM C[M,N] += A B without epilogue (the fold / unfold products); C zero-filled by the caller
 GemmArgs mk_mm(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64_t b_rs, int64_t b_cs, float* Cm, int64_t ldc,
                int64_t M, int N, int64_t K) {
   GemmArgs g;
   g.A = A; g.a_rs = a_rs; g.a_cs = a_cs; g.B = B; g.b_rs = b_rs; g.b_cs = b_cs; g.C = Cm; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
+  g.accumulate = 1; g.k_slice = 64;      // += onto a zero-filled C, one 64-wide K slice per CTA (see GemmArgs::k_slice)
   return g;
 }
 
-// bof_keep: where the fc_out feature bias table betao' [N,C] goes in the folded mode (the backward's d Wdf needs it again)
+// bof (folded mode): the fc_out feature bias table betao' [N,C]; betaf = betao' Wdf^T follows from it, and the backward's
+// d Wdf needs it again
 int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir, int64_t ld_dir, const float* z_s,
                 int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
-                bool split_bo, cudaStream_t st, float* bof_keep = nullptr) {
+                bool split_bo, cudaStream_t st, float* bof = nullptr) {
   const int H = d.H, C = d.C;
   Batch b(d.rows_dev);
-  if (split_bo) {   // the fold: Wf = Wdf Wout' [H x 2H], bfold = Wdf bo'   (Wout' = fc_out rows 1..C, Wdf = layer_dir1[:, :C])
-    b.add_fixed(mk_mm(p->weight[CNRF_L_DIR1], C + d.dd, 1, p->weight[CNRF_L_FC_OUT] + (H + C), H + C, 1, t.wf, 2 * H, H, 2 * H, C));
-    b.add_fixed(mk_mm(p->weight[CNRF_L_DIR1], C + d.dd, 1, p->bias[CNRF_L_FC_OUT] + 1, 1, 1, t.bfold, 1, H, 1, C));
+  if (split_bo) {   // the fold Wfh = Wdf Wout'h as four K-slices (Wdf = layer_dir1[:, :C], Wout'h = fc_out[1:, :H]): slice j goes to
+    if (!bof || C % 4) return CNRF_E_NULL;      // its own [H x H] buffer (plain stores; pack_weights_kernel adds them in order)
+    for (int j = 0; j < 4; ++j) {
+      GemmArgs g = mk_mm(p->weight[CNRF_L_DIR1] + j * (C / 4), C + d.dd, 1, p->weight[CNRF_L_FC_OUT] + (int64_t)(1 + j * (C / 4)) * (H + C),
+                         H + C, 1, t.wf + (size_t)j * H * H, H, H, H, C / 4);
+      g.accumulate = 0; g.k_slice = 0;
+      b.add_fixed(g);
+    }
   }
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 1));     // model.py:174
   b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 1));     // :175
@@ -219,15 +227,19 @@ int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir
   if (!d.tc) b.add(mk_lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0));
   RUN(b.flush(d.tc, st));
   b.add(mk_lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0));
-  if (split_bo) {   // tensor-core chain: folded layer_dir1 bias rows, the sigma column, and betao' itself for the backward
-    b.add(mk_lin(as2, C, d.N, C, t.wf + H, 2 * H, H, t.bf, H, t.bfold, 0));
+  if (split_bo) {   // tensor-core chain: betao' and the sigma column here, the folded layer_dir1 bias rows one level later
+    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0));
     b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0));
-    if (bof_keep) b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, bof_keep, C, p->bias[CNRF_L_FC_OUT] + 1, 0));
   } else {
     b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0));
   }
   b.add(mk_lin(at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0));
-  return b.flush(d.tc, st);
+  RUN(b.flush(d.tc, st));
+  if (split_bo) {   // betaf = betao' Wdf^T
+    b.add(mk_lin(bof, C, d.N, C, p->weight[CNRF_L_DIR1], C + d.dd, H, t.bf, H, nullptr, 0));
+    RUN(b.flush(d.tc, st));
+  }
+  return CNRF_OK;
 }
 
 // gradients of the bias tables -> code-layer weights, code halves of the split layers, z_s / z_t / x_dir.
@@ -404,7 +416,7 @@ struct TcChainArgs {
   const float* x_xyz; int64_t ld_xyz;         // pre-embedded input, or
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;   // points to encode
   const float *b2, *bf, *bos, *br;            // per-ray bias tables [N,256], [N,256] (folded layer_dir1), [N] (sigma), [N,3]
-  const float* wf;                            // Wdf Wout' [256 x 512] fp32 (this call's fold)
+  const float* wf;                            // the four K-slices [4][256 x 256] of this call's fold Wfh = Wdf Wout'h
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
   const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
 };
@@ -481,7 +493,7 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
     zs = sc.zc_s; zt = sc.zc_t; ld_zs = ld_zt = d.C;
   }
   if (s->keep) { tc_saved = sa.base + sa.off; tc_saved_bytes = sa.cap - sa.off; }
-  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, t, true, st, s->keep ? bof : nullptr));
+  RUN(per_ray_fwd(d, p, in.x_dir, in.ld_dir, zs, ld_zs, zt, ld_zt, as1, as2, at, t, true, st, bof));
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, p, in.x_xyz, in.ld_xyz, in.pts, in.freqs_xyz, in.L_xyz,
                 in.inc_xyz, t.b2, t.bf, t.bos, t.br, t.wf, in.x_dir, in.ld_dir, in.ids ? sc.runs.gid : nullptr};
   return cnrf_tc_chain_fwd(a, raw, tc_saved, tc_saved_bytes, w.base + w.off, w.cap - w.off, st);

@@ -341,7 +341,8 @@ int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
     if (a.b_rs == 1) b.b_mn[i] = 0; else if (a.b_cs == 1) b.b_mn[i] = 1; else return CNRF_E_UNSUPPORTED;
     // split K over CTAs only where the caller already adds into C (weight gradients: K = rays of the chunk)
     const bool may_split = a.split_k > 1 || a.accumulate;
-    b.kslice[i] = (may_split && a.K > 2 * GKSLICE) ? GKSLICE : a.K;
+    if (a.k_slice > 0 && (!a.accumulate || a.k_slice % GKC)) return CNRF_E_SHAPE;
+    b.kslice[i] = a.k_slice > 0 ? a.k_slice : (may_split && a.K > 2 * GKSLICE) ? GKSLICE : a.K;
     b.g[i] = a;
     b.mt[i] = (int)((a.M + GBM - 1) / GBM);
     b.nt[i] = (a.N + GBN - 1) / GBN;

@@ -57,6 +57,10 @@ struct GemmArgs {
   const float* mask = nullptr; int64_t ld_mask = 0;
   int accumulate = 0;   // C += result (no bias/relu/mask)
   int split_k = 1;      // > 1: partial sums are atomically added into C, which the caller zero-fills
+  // tensor-core kernel only: > 0 (a multiple of 64) = contraction slice per CTA; the slices' partial sums are added
+  // atomically, so C must be zero-filled (or hold the value to add to) and `accumulate` set.  Short-and-wide problems
+  // (the fc_out fold, K = 256) are latency-bound: one load round trip per CTA instead of K / 64 serial ones.
+  int64_t k_slice = 0;
   // tensor-core kernel only: a device-resident row count that shrinks M (rows_dim = 1) or K (rows_dim = 2) at run time;
   // M / K above are then the worst case the launch is sized for (code_runs.cu)
   const int32_t* rows_dev = nullptr; int rows_dim = 0;

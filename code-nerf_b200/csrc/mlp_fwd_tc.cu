@@ -17,13 +17,19 @@
 #include "mlp_tc.cuh"
 
 __device__ long long g_fwd_dbg[16];
+// Timer builds only: absolute clock64 stamps of ONE steady-state tile pair of block 0 (its 4th), [tile][layer][event]:
+// 0 epilogue starts waiting for the accumulator, 1 accumulator seen, 2 block loop starts, 3 block loop done, 4 hand-off
+// (a_ready arrive), 5 MMA warp sees a_ready, 6 MMA warp has issued the layer's last MMA + commit, 7 gamma(x) built (layer 0)
+__device__ long long g_fwd_trace[2 * 4 * 8];
 // Phase timers of block 0 (scripts/time_field.py): compiled in only with -DCNRF_FWD_TIMERS, they cost issue slots
 #ifdef CNRF_FWD_TIMERS
 #define FDBG(i, dt) do { if (blockIdx.x == 0) atomicAdd((unsigned long long*)&g_fwd_dbg[i], (unsigned long long)(dt)); } while (0)
 #define FCLK() clock64()
+#define FTRACE(it, t, layer, ev, clk) do { if (blockIdx.x == 0 && (it) == 3) g_fwd_trace[((t) * 4 + (layer)) * 8 + (ev)] = (clk); } while (0)
 #else
 #define FDBG(i, dt) do { } while (0)
 #define FCLK() 0ll
+#define FTRACE(it, t, layer, ev, clk) do { } while (0)
 #endif
 namespace {
 constexpr int HALF = 128 * 128;             // bytes of one [128 x 64] bf16 weight image
@@ -96,7 +102,7 @@ struct Epi {               // per-thread state of an epilogue thread for the cur
   const float* heads;      // smem: w_sigma[256] | w_rgb[3][256] | b_dir2[256]
   float* stage;            // smem: [RMAX][256] bias rows of this tile's rays
   uint32_t tacc;
-  int r, bar_id, slot, nrays;
+  int r, bar_id, slot, nrays, it;
   bool elected, valid, staged;
   int64_t m, ray0;
   int row;                 // this thread's row of the per-ray bias tables (its ray, or the ray's code run)
@@ -213,6 +219,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   named_bar_sync(c.bar_id, 128);
   const long long tw4 = FCLK();
   if (c.elected && t == 0) { FDBG(10, tw2 - tw1); FDBG(11, tw3 - tw2); FDBG(12, tw4 - tw3); }
+  if (c.elected) { FTRACE(c.it, t, E, 0, tw0); FTRACE(c.it, t, E, 1, tw1); FTRACE(c.it, t, E, 2, tw2); FTRACE(c.it, t, E, 3, tw3); FTRACE(c.it, t, E, 4, tw4); }
   if (c.elected) {
     // the hand-off first: a cluster-scope release issued after the bulk store waits for that store (~3.5 k clk)
     if (E < 3) { if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&c.bars->a_ready[t]); }
@@ -321,6 +328,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
       uint32_t slot = 0, wpar = 0, na = 0;        // ring slot, its w_full parity, a_ready parity counter
       bool ok = true;
+      int it_m = 0;
 #define NEXT_SLOT() do { if (++slot == FRING) { slot = 0; wpar ^= 1u; } } while (0)
 #define WAIT_IMAGE() (uwait(&bars->w_full[slot], wpar, bars, a.err) && (CG == 1 || uwait_cluster(&bars->w_peer[slot], wpar, bars, a.err)))
 #define MMA(d, ad, bd, acc) do { if (CG == 2) umma_bf16_2cta(d, ad, bd, idesc, acc); else umma_bf16(d, ad, bd, idesc, acc); } while (0)
@@ -334,6 +342,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
             const long long m1 = FCLK();
             if (!(CG == 2 ? uwait_cluster(&bars->a_ready[t], na & 1, bars, a.err) : uwait(&bars->a_ready[t], na & 1, bars, a.err))) { ok = false; break; }
             FDBG(9, FCLK() - m1);
+            if (lane == 0) FTRACE(it_m, t, layer, 5, FCLK());
             const uint32_t d0 = tmem_u + t * 256;
 #pragma unroll 1
             for (int c = 0; c < nch && ok; ++c) {
@@ -378,8 +387,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
             }
             if (ok && elect_one()) COMMIT(&bars->acc_full[t]);
             __syncwarp();
+            if (lane == 0) FTRACE(it_m, t, layer, 6, FCLK());
           }
         }
+        ++it_m;
       }
 #undef NEXT_SLOT
 #undef WAIT_IMAGE
@@ -412,7 +423,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       const int64_t m1 = ((int64_t)blockIdx.x * 2 + t) * TILE + c.r;      // blockIdx.x = pair_first + rank
       if (m1 < a.M) { c.px = __ldg(a.pts + m1 * 3); c.py = __ldg(a.pts + m1 * 3 + 1); c.pz = __ldg(a.pts + m1 * 3 + 2); }
     }
+    c.it = -1;
     for (int64_t pb = pair_first; pb < num_pairs; pb += gridDim.x) {
+      ++c.it;
       const int64_t pr = pb + rank;
       const int64_t tile_idx = pr * 2 + t;
       const int64_t first = tile_idx * TILE;
@@ -456,6 +469,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
         if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&bars->a_ready[t]);
         if (c.sv) { bulk_s2g(c.sv, c.tile, SLAB); bulk_commit(); }
         if (t == 0) { FDBG(6, FCLK() - tb0); FDBG(7, 1); }
+        FTRACE(c.it, t, 0, 7, FCLK());
       }
       bool ok = epi_layer<0, false>(a, c, t, na & 1); ++na;
       if (ok) { ok = c.staged ? epi_layer<1, false>(a, c, t, na & 1) : epi_layer<1, true>(a, c, t, na & 1); ++na; }
@@ -518,6 +532,11 @@ int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
   }
   if (timed) cnrf_ktimer_end(CNRF_KT_FWD, st);
   return CNRF_OK;
+}
+
+extern "C" int cnrf_debug_fwd_trace(long long* host_out64) {
+  cudaDeviceSynchronize();
+  return (int)cudaMemcpyFromSymbol(host_out64, g_fwd_trace, 64 * sizeof(long long));
 }
 
 extern "C" int cnrf_debug_fwd_times(long long* host_out, int reset) {

@@ -17,7 +17,10 @@
 
 // ---- weight packing ------------------------------------------------------------------------------------------------
 // chunk image element (row r in [0,256), col c in [0,64)) of chunk `ch`.
-// wf: the folded matrix Wdf Wout' [256 x 512] fp32 (its left half is the per-sample layer Wfh)
+// wf: the folded layer Wfh = Wdf Wout'h as four K-slice partial products [4][256 x 256] fp32, added here in a fixed order
+__device__ __forceinline__ float wfh_at(const float* __restrict__ wf, int i) {
+  return ((wf[i] + wf[65536 + i]) + wf[2 * 65536 + i]) + wf[3 * 65536 + i];
+}
 __global__ void pack_weights_kernel(cnrf_codenerf_params p, const float* __restrict__ wf, int dx, int dd, Packed pk) {
   const int ch = blockIdx.x;                  // 0 .. FWD_CHUNKS+BWD_CHUNKS-1
   for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < 256 * 64; i += gridDim.y * blockDim.x) {
@@ -33,7 +36,7 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, const float* __restr
       } else {
         int l = (ch - 1) >> 2, k = ((ch - 1) & 3) * 64 + c;   // l: 0 W2h, 1 Wfh, 2 Wd2
         if (l == 0) v = p.weight[CNRF_L_XYZ2][r * 512 + k];
-        else if (l == 1) v = wf[r * 512 + k];
+        else if (l == 1) v = wfh_at(wf, r * 256 + k);
         else v = p.weight[CNRF_L_DIR2][r * 256 + k];
       }
     } else {
@@ -44,7 +47,7 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, const float* __restr
         const int q = r >> 6, nin = r & 63;
         v = nin < dx ? p.weight[CNRF_L_XYZ1][(q * 64 + c) * dx + nin] : 0.f;
       } else if (l == 0) v = p.weight[CNRF_L_DIR2][n * 256 + r];
-      else if (l == 1) v = wf[n * 512 + r];
+      else if (l == 1) v = wfh_at(wf, n * 256 + r);
       else v = p.weight[CNRF_L_XYZ2][n * 512 + r];
     }
     *reinterpret_cast<__nv_bfloat16*>(base + slab_offset(r, c)) = __float2bfloat16(v);
@@ -72,7 +75,7 @@ struct TcChainArgs {   // mirrors the declaration in codenerf.cu
   const float* x_xyz; int64_t ld_xyz;
   const float* pts; const float* freqs_xyz; int L_xyz; int inc_xyz;
   const float *b2, *bf, *bos, *br;            // per-ray bias tables [N,256], [N,256] (folded layer_dir1), [N] (sigma), [N,3]
-  const float* wf;                            // Wdf Wout' [256 x 512] fp32 (this call's fold)
+  const float* wf;                            // the four K-slices [4][256 x 256] of this call's fold Wfh = Wdf Wout'h
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
   const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
 };

@@ -365,6 +365,9 @@ int cnrf_debug_tc_error(void);
  * cnrf_debug_fwd_kernel_ms(min_rows > 0) starts timing every launch over >= min_rows rows (statistics reset),
  * (0) stops; each call returns the mean duration in ms of the launches timed so far. */
 int cnrf_debug_fwd_times(long long* host_out16, int reset);
+/* Timer builds (-DCNRF_FWD_TIMERS) only: clock64 stamps [tile 2][layer 4][event 8] of one steady-state tile pair of block 0
+ * (events: mlp_fwd_tc.cu, g_fwd_trace); all zero in ordinary builds. */
+int cnrf_debug_fwd_trace(long long* host_out64);
 double cnrf_debug_fwd_kernel_ms(int64_t min_rows, int64_t* launches, int64_t* rows);
 /* The same for any of the three tensor-core kernels: which = 0 forward chain, 1 backward-data chain, 2 weight gradients;
  * min_rows < 0 only queries. */

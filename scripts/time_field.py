@@ -44,5 +44,15 @@ try:
           (buf[0] // n, [int(buf[1 + i] // n) for i in range(5)], buf[6] // n, buf[8] // n, buf[9] // n, n))
     print("  epilogue split per pair (5 layers): store-drain + barrier %d | blocks %d | closing barrier %d | store issue + arrive %d" %
           (buf[10] // n, buf[11] // n, buf[12] // n, buf[13] // n))
+    tr = np.zeros(64, dtype=np.int64)
+    lib.cnrf_debug_fwd_trace(ctypes.c_void_p(tr.ctypes.data))
+    tr = tr.reshape(2, 4, 8)
+    if tr.any():
+        t0 = tr[tr > 0].min()
+        names = ["wait_acc", "acc_seen", "blocks_start", "blocks_done", "handoff", "mma_sees_a_ready", "mma_issued", "gamma_built"]
+        ev = sorted((int(tr[t, l, e] - t0), f"T{t} L{l} {names[e]}") for t in range(2) for l in range(4) for e in range(8) if tr[t, l, e] > 0)
+        print("timeline of block 0's 4th tile pair [clk from first event]:")
+        for clk, what in ev:
+            print(f"  {clk:7d}  {what}")
 except Exception as e:
     print("no fwd debug times:", e)
