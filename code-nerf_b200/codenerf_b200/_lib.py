@@ -68,6 +68,9 @@ _SIGS = {
     "cnrf_launch_count": (C.c_int64, []),
     "cnrf_debug_tc_error": (C.c_int, []),
     "cnrf_debug_umma": (C.c_int, [c_i32, c_f32p, c_f32p, c_f32p, c_i32, c_i32, c_f32p, C.c_void_p]),
+    "cnrf_debug_bulk_ld": (C.c_int, [c_i32, c_i32, c_i32, c_i32, C.c_void_p, c_sz, c_i32, C.c_void_p, C.c_void_p]),
+    "cnrf_debug_bulk_ld2": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, C.c_void_p, c_sz, C.c_void_p, C.c_void_p]),
+    "cnrf_debug_umma_rate": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, C.c_void_p, c_sz, C.c_void_p, C.c_void_p]),
     "cnrf_debug_tmem_ld": (C.c_int, [c_i32, c_i32, c_i32, c_i32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cnrf_debug_fwd_trace": (C.c_int, [C.c_void_p]),
     "cnrf_debug_fwd_times": (C.c_int, [C.c_void_p, C.c_int]),

@@ -174,20 +174,26 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
   tc_fence_after();
   const uint32_t tmem = bars->tmem_slot;
 
-  if (warp == 0) {
-    // ===== TMA producer: per (stage, tile) the 4 transposed K-chunks x 2 N-halves of that stage =====
+  const int prod = producer_index(warp);
+  if (prod >= 0) {
+    // ===== TMA producers: per (stage, tile) the 4 transposed K-chunks x 2 N-halves of that stage =====
     // The two tiles of a pair run half a stage apart (one tile's MMAs under the other's epilogue), so the L2-resident
-    // weight images pass through the ring once per tile.
+    // weight images pass through the ring once per tile.  NPROD producers share the image sequence round-robin (one
+    // issuing thread manages a bulk copy per ~588 clk, the tensor core eats an image in 256: mlp_tc.cuh).
     if (lane == 0) {
       uint32_t slot = 0, epar = 1;
+      uint32_t turn = 0;
       bool ok = true;
       for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
         for (int stage = 0; stage < (XG ? 4 : 3) && ok; ++stage) {
           for (int t = 0; t < 2 && ok; ++t) {
             for (int i = 0; i < (stage == 3 ? 2 : 8); ++i) {      // stage 3: W1^T, one 32 KB image = two ring slots
-              if (!bwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
-              mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
-              bulk_g2s(ring + slot * HALF, a.pk.bwd + (size_t)(stage * 8 + i) * HALF, HALF, &bars->w_full[slot]);
+              if ((int)turn == prod) {
+                if (!bwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
+                mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
+                bulk_g2s(ring + slot * HALF, a.pk.bwd + (size_t)(stage * 8 + i) * HALF, HALF, &bars->w_full[slot]);
+              }
+              if (++turn == NPROD) turn = 0;
               if (++slot == BRING) { slot = 0; epar ^= 1u; }
             }
           }
@@ -264,7 +270,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
         }
       }
     }
-  } else {
+  } else if (warp < 10) {
     // ===== epilogue warps: thread = one sample row =====
     const int t = (warp - 2) >> 2;
     const int q = warp & 3;

@@ -9,8 +9,8 @@
 //            layer) + a ring of five 16 KB weight images ([128 out-features x 64 in-features]: the N-half of a K chunk,
 //            streamed by TMA bulk copies) + fp32 head vectors (fc_out row 0, fc_rgb, layer_dir2 bias) + a per-tile
 //            staging area for the per-ray bias rows of the current layer (cp.async, prefetched one layer ahead).
-//   warps  : 0 = TMA producer, 1 = MMA issuer (one lane), 2-5 = epilogue of T0, 6-9 = epilogue of T1 (thread = one sample
-//            row, TMEM lane quarter = warp_id % 4).
+//   warps  : 0, 10, 11 = TMA producers (one lane each; the images of the stream round-robin), 1 = MMA issuer (one lane),
+//            2-5 = epilogue of T0, 6-9 = epilogue of T1 (thread = one sample row, TMEM lane quarter = warp_id % 4).
 // The epilogue is specialised per layer at compile time and fully unrolled: TMEM -> registers -> + bias -> ReLU -> bf16
 // -> swizzled smem (the next layer's A operand, also TMA-stored as the image the backward needs).
 #include <cstdlib>
@@ -21,15 +21,20 @@ __device__ long long g_fwd_dbg[16];
 // 0 epilogue starts waiting for the accumulator, 1 accumulator seen, 2 block loop starts, 3 block loop done, 4 hand-off
 // (a_ready arrive), 5 MMA warp sees a_ready, 6 MMA warp has issued the layer's last MMA + commit, 7 gamma(x) built (layer 0)
 __device__ long long g_fwd_trace[2 * 4 * 8];
+// ... and of the weight images of that pair's (layer 1, both tiles) = 16 images: [image][0 producer sees the slot empty,
+// 1 producer has issued the copy, 2 MMA warp sees the image, 3 MMA warp has issued its MMAs + commit]
+__device__ long long g_fwd_trace_img[16 * 4];
 // Phase timers of block 0 (scripts/time_field.py): compiled in only with -DCNRF_FWD_TIMERS, they cost issue slots
 #ifdef CNRF_FWD_TIMERS
 #define FDBG(i, dt) do { if (blockIdx.x == 0) atomicAdd((unsigned long long*)&g_fwd_dbg[i], (unsigned long long)(dt)); } while (0)
 #define FCLK() clock64()
 #define FTRACE(it, t, layer, ev, clk) do { if (blockIdx.x == 0 && (it) == 3) g_fwd_trace[((t) * 4 + (layer)) * 8 + (ev)] = (clk); } while (0)
+#define FTRACE_IMG(it, layer, img, ev) do { if (blockIdx.x == 0 && (it) == 3 && (layer) == 1 && (img) < 16) g_fwd_trace_img[(img) * 4 + (ev)] = clock64(); } while (0)
 #else
 #define FDBG(i, dt) do { } while (0)
 #define FCLK() 0ll
 #define FTRACE(it, t, layer, ev, clk) do { } while (0)
+#define FTRACE_IMG(it, layer, img, ev) do { } while (0)
 #endif
 namespace {
 constexpr int HALF = 128 * 128;             // bytes of one [128 x 64] bf16 weight image
@@ -90,6 +95,7 @@ __device__ __forceinline__ bool uwait_cluster(uint64_t* bar, uint32_t parity, FB
 __device__ __forceinline__ bool uwait(uint64_t* bar, uint32_t parity, FBars* b, int* err) {
   return __all_sync(0xFFFFFFFFu, fwait(bar, parity, b, err));
 }
+
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
   asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
 }
@@ -266,15 +272,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
   tc_fence_after();
   const uint32_t tmem = bars->tmem_slot;
 
-  if (warp == 0) {
-    // ===== TMA producer =====
+  const int prod = producer_index(warp);
+  if (prod >= 0) {
+    // ===== TMA producers =====
     // The two tiles of a pair run half a layer apart (T1's MMAs overlap T0's epilogue), so a layer's weight images pass
     // through the ring once per tile: per (layer, tile) the N-halves of its K-chunks in order (CG = 2: only this CTA's
     // half); layer_dir1 is followed by its extension (this pair's [gamma(d) | 1] slab, then [Wdv | b_dir1]).
+    // Every producer walks the whole image sequence (slot / parity bookkeeping) and issues the images img % NPROD == prod.
     if (lane == 0) {
       uint32_t slot = 0, epar = 1;          // ring slot and the parity its w_empty barrier is waited with
+      uint32_t turn = 0;                    // img % NPROD
       bool ok = true;
+      int it_p = -1;
       for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
+        ++it_p;
         const int64_t pr = pb + rank < num_pairs ? pb + rank : num_pairs - 1;    // padding pair: any valid slab will do
         for (int layer = 0; layer < NUM_TC_LAYERS && ok; ++layer) {
           const int first = layer == 0 ? 0 : 2 + 8 * (layer - 1);          // half-image index in a.pk.fwd
@@ -282,13 +293,18 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
           const int count = nmain + (layer == 2 ? 1 + 2 / CG : 0);
           for (int t = 0; t < 2 && ok; ++t) {
             for (int i = 0; i < count; ++i) {
-              if (!fwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
-              const uint8_t* src;
-              if (i < nmain) src = a.pk.fwd + (size_t)(first + (CG == 2 ? 2 * i + (int)rank : i)) * HALF;
-              else if (i == nmain) src = a.ext + (size_t)pr * SLAB;
-              else src = a.pk.fwd + (size_t)EXT_CHUNK * CHUNK + (size_t)(CG == 2 ? (int)rank : i - nmain - 1) * HALF;
-              mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
-              bulk_g2s(ring + slot * HALF, src, HALF, &bars->w_full[slot]);
+              if ((int)turn == prod) {
+                if (!fwait(&bars->w_empty[slot], epar, bars, a.err)) { ok = false; break; }
+                FTRACE_IMG(it_p, layer, t * count + i, 0);
+                const uint8_t* src;
+                if (i < nmain) src = a.pk.fwd + (size_t)(first + (CG == 2 ? 2 * i + (int)rank : i)) * HALF;
+                else if (i == nmain) src = a.ext + (size_t)pr * SLAB;
+                else src = a.pk.fwd + (size_t)EXT_CHUNK * CHUNK + (size_t)(CG == 2 ? (int)rank : i - nmain - 1) * HALF;
+                mbar_arrive_expect_tx(&bars->w_full[slot], HALF);
+                bulk_g2s(ring + slot * HALF, src, HALF, &bars->w_full[slot]);
+                FTRACE_IMG(it_p, layer, t * count + i, 1);
+              }
+              if (++turn == NPROD) turn = 0;
               if (++slot == FRING) { slot = 0; epar ^= 1u; }
             }
           }
@@ -353,14 +369,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
                 const long long m0 = FCLK();
                 if (!WAIT_IMAGE()) { ok = false; continue; }
                 FDBG(8, FCLK() - m0);
+                if (lane == 0) FTRACE_IMG(it_m, layer, t * 8 + c * 2 + h, 2);
+                const long long m2 = FCLK();
                 tc_fence_after();
                 const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
                 if (elect_one()) {
 #pragma unroll
                   for (int k = 0; k < 4; ++k) MMA(d0 + h * 128, ad + 2 * k, bd + 2 * k, (c | k) != 0);
+                  const long long m3 = FCLK();
                   COMMIT(&bars->w_empty[slot]);
+                  FDBG(14, m3 - m2); FDBG(15, FCLK() - m3);
                 }
                 __syncwarp();
+                if (lane == 0) FTRACE_IMG(it_m, layer, t * 8 + c * 2 + h, 3);
                 NEXT_SLOT();
               }
             }
@@ -397,7 +418,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
 #undef MMA
 #undef COMMIT
     }
-  } else {
+  } else if (warp < 10) {
     // ===== epilogue warps: thread = one sample row =====
     const int t = (warp - 2) >> 2;                    // tile of the pair
     const int q = warp & 3;                           // TMEM lane quarter this warp may read
@@ -536,7 +557,10 @@ int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
 
 extern "C" int cnrf_debug_fwd_trace(long long* host_out64) {
   cudaDeviceSynchronize();
-  return (int)cudaMemcpyFromSymbol(host_out64, g_fwd_trace, 64 * sizeof(long long));
+  // host_out64 holds 128 entries: the pair trace, then the per-image trace
+  cudaError_t e = cudaMemcpyFromSymbol(host_out64, g_fwd_trace, 64 * sizeof(long long));
+  if (e == cudaSuccess) e = cudaMemcpyFromSymbol(host_out64 + 64, g_fwd_trace_img, 64 * sizeof(long long));
+  return (int)e;
 }
 
 extern "C" int cnrf_debug_fwd_times(long long* host_out, int reset) {

@@ -12,7 +12,13 @@ constexpr int SLAB = TILE * 128;          // bytes of one [128 x 64] bf16 slab
 constexpr int TILE_BYTES = 4 * SLAB;      // 64 KB: one [128 x 256] activation tile image
 constexpr int CHUNK = 256 * 128;          // 32 KB: one [256 x 64] weight chunk image
 constexpr int RING = 3;
-constexpr int NTHREADS = 320;
+// Warps of the chain kernels: 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (4 per tile), 10.. = further TMA producers.
+// ONE thread alternating mbarrier.try_wait / expect_tx / cp.async.bulk completes a copy every ~588 clk whatever its size
+// (profiles/r02_bulk_copy_probe*.json: 2 issuing threads 294 clk, 4 threads 147 clk per copy, on 1 or 148 SMs alike), while
+// the tensor core consumes a 16 KB weight image in 256 clk: NPROD producers take the images of the stream round-robin.
+constexpr int NPROD = 3;
+constexpr int NTHREADS = 320 + 32 * (NPROD - 1);
+__device__ __forceinline__ int producer_index(int warp) { return warp == 0 ? 0 : warp >= 10 ? warp - 9 : -1; }
 // fc_out is FOLDED into layer_dir1 (models/model.py:182-189 apply no activation between them): the per-sample chain has four
 // 256-wide tensor-core layers  W1 | W2h | Wfh = Wdf Wout'[:, :H] | Wd2  (the fold is rebuilt from the fp32 parameters at
 // every call, codenerf.cu)

@@ -160,3 +160,232 @@ extern "C" int cnrf_debug_tmem_ld(int32_t blocks, int32_t warps, int32_t iters, 
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }
+
+// ---- bulk-copy ingest probe (scripts/probe_bulk.py): how fast ONE SM can pull bytes through cp.async.bulk (UBLKCP), by
+// copy size, copies in flight, number of SMs pulling at once, and whether all SMs read the same (L2-resident) bytes --
+// the forward / backward chains stream their weight images this way, the weight-gradient kernel its operand tiles.
+__global__ void __launch_bounds__(64) bulk_ld_probe_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int per_block_offset,
+                                                          int bytes, int slots, int iters, long long* __restrict__ out) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ uint64_t full[16];
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < slots; ++i) mbar_init(&full[i], 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const size_t span = src_bytes - (size_t)bytes;
+    size_t off = per_block_offset ? ((size_t)blockIdx.x * 1048576u) % (span + 1) : 0;
+    off &= ~(size_t)127;
+    const long long t0 = clock64();
+    int issued = 0, done = 0;
+    uint32_t par[16];
+    for (int i = 0; i < 16; ++i) par[i] = 0;
+    while (done < iters) {
+      while (issued < iters && issued - done < slots) {
+        const int s = issued % slots;
+        mbar_arrive_expect_tx(&full[s], (uint32_t)bytes);
+        bulk_g2s(smem_raw + (size_t)s * bytes, src + off, (uint32_t)bytes, &full[s]);
+        off += (size_t)bytes;
+        if (off > span) off = 0;
+        ++issued;
+      }
+      const int s = done % slots;
+      while (!mbar_try_wait(&full[s], par[s])) { }
+      par[s] ^= 1u;
+      ++done;
+    }
+    out[blockIdx.x] = clock64() - t0;
+  }
+}
+
+// Variants of the same question.  mode 1: `nthreads` issuing threads (one per warp), each with its own ring of `slots` copies.
+// mode 2: one thread issues `slots` copies back to back on ONE mbarrier (one expect_tx for all of them) and waits once per
+// round -- no per-copy wait on the issuing thread.  mode 3: as mode 2 but the waiting is done by a different warp.
+__global__ void __launch_bounds__(256) bulk_ld_probe2_kernel(const uint8_t* __restrict__ src, size_t src_bytes, int bytes, int slots,
+                                                            int iters, int mode, int nthreads, long long* __restrict__ out) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ uint64_t full[64];
+  __shared__ uint64_t round_done;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 64; ++i) mbar_init(&full[i], 1);
+    mbar_init(&round_done, 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  const size_t span = src_bytes - (size_t)bytes;
+  const long long t0 = clock64();
+  if (mode == 1) {
+    if (lane == 0 && warp < nthreads) {
+      size_t off = ((size_t)warp * 262144u) % (span + 1) & ~(size_t)127;
+      uint64_t* bar = full + warp * slots;
+      uint8_t* buf = smem_raw + (size_t)warp * slots * bytes;
+      uint32_t par[16];
+      for (int i = 0; i < 16; ++i) par[i] = 0;
+      int issued = 0, done = 0;
+      while (done < iters) {
+        while (issued < iters && issued - done < slots) {
+          const int s = issued % slots;
+          mbar_arrive_expect_tx(&bar[s], (uint32_t)bytes);
+          bulk_g2s(buf + (size_t)s * bytes, src + off, (uint32_t)bytes, &bar[s]);
+          off += (size_t)bytes; if (off > span) off = 0;
+          ++issued;
+        }
+        const int s = done % slots;
+        while (!mbar_try_wait(&bar[s], par[s])) { }
+        par[s] ^= 1u;
+        ++done;
+      }
+    }
+  } else {
+    const int rounds = iters / slots;
+    if (threadIdx.x == 0) {
+      size_t off = 0;
+      uint32_t par = 0;
+      for (int r = 0; r < rounds; ++r) {
+        if (mode == 3 && r > 0) { while (!mbar_try_wait(&round_done, (uint32_t)((r - 1) & 1))) { } }
+        mbar_arrive_expect_tx(&full[0], (uint32_t)(bytes * slots));
+        for (int s = 0; s < slots; ++s) {
+          bulk_g2s(smem_raw + (size_t)s * bytes, src + off, (uint32_t)bytes, &full[0]);
+          off += (size_t)bytes; if (off > span) off = 0;
+        }
+        if (mode == 2) { while (!mbar_try_wait(&full[0], par)) { } par ^= 1u; }
+      }
+    } else if (mode == 3 && threadIdx.x == 32) {
+      uint32_t par = 0;
+      for (int r = 0; r < rounds; ++r) {
+        while (!mbar_try_wait(&full[0], par)) { }
+        par ^= 1u;
+        mbar_arrive(&round_done);
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) out[blockIdx.x] = clock64() - t0;
+}
+
+extern "C" int cnrf_debug_bulk_ld2(int32_t blocks, int32_t slots, int32_t bytes, int32_t iters, int32_t mode, int32_t nthreads,
+                                   const void* src, size_t src_bytes, long long* clocks, cnrf_stream_t stream) {
+  CNRF_REQUIRE(src && clocks, CNRF_E_NULL);
+  CNRF_REQUIRE(blocks > 0 && slots >= 1 && slots <= 16 && bytes >= 128 && bytes % 128 == 0 && iters >= slots, CNRF_E_SHAPE);
+  CNRF_REQUIRE(mode >= 1 && mode <= 3 && nthreads >= 1 && nthreads <= 4, CNRF_E_SHAPE);
+  const size_t smem = (size_t)slots * bytes * (mode == 1 ? nthreads : 1);
+  CNRF_REQUIRE(smem <= 200 * 1024 && src_bytes >= (size_t)bytes, CNRF_E_SHAPE);
+  cudaError_t e = cudaFuncSetAttribute(bulk_ld_probe2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+  bulk_ld_probe2_kernel<<<blocks, 256, smem, as_stream(stream)>>>(static_cast<const uint8_t*>(src), src_bytes, bytes, slots, iters, mode,
+                                                                 nthreads, clocks);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
+// clocks[b] = SM clocks block b needed to pull iters x bytes through a ring of `slots` bulk copies in flight.
+extern "C" int cnrf_debug_bulk_ld(int32_t blocks, int32_t slots, int32_t bytes, int32_t iters, const void* src, size_t src_bytes,
+                                  int32_t per_block_offset, long long* clocks, cnrf_stream_t stream) {
+  CNRF_REQUIRE(src && clocks, CNRF_E_NULL);
+  CNRF_REQUIRE(blocks > 0 && slots >= 1 && slots <= 16 && bytes >= 128 && bytes % 128 == 0 && iters > 0, CNRF_E_SHAPE);
+  CNRF_REQUIRE((size_t)slots * bytes <= 200 * 1024 && src_bytes >= (size_t)bytes, CNRF_E_SHAPE);
+  cudaError_t e = cudaFuncSetAttribute(bulk_ld_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, slots * bytes);
+  if (e != cudaSuccess) return (int)e;
+  bulk_ld_probe_kernel<<<blocks, 64, (size_t)slots * bytes, as_stream(stream)>>>(static_cast<const uint8_t*>(src), src_bytes,
+                                                                               per_block_offset, bytes, slots, iters, clocks);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
+// ---- MMA operand-bandwidth probe (scripts/probe_umma_rate.py): the rate at which ONE SM executes tcgen05.mma (bf16, M = 128,
+// N = 128 or 256, K = 16, both operands from shared memory) over static operand images, alone and while `nprod` threads stream
+// bulk copies INTO shared memory.  An M128 N128 K16 step reads 4 KB of A and 4 KB of B for 64 clk of math (128 B/clk), an
+// N = 256 step 12 KB for 128 clk (96 B/clk): if the rate drops when copies run beside it, the chain kernels are bound by
+// shared-memory bandwidth, not by the tensor pipe.
+__global__ void __launch_bounds__(160) umma_rate_probe_kernel(int n_cols, int chunks, int nprod, int copy_bytes, const uint8_t* __restrict__ src,
+                                                             size_t src_bytes, long long* __restrict__ out) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  __shared__ uint64_t done_bar, full[4][4];
+  __shared__ uint32_t tmem_slot;
+  __shared__ int stop_flag;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  uint8_t* a_img = smem;                         // [128 x 256] bf16 tile image: 4 slabs of 16 KB
+  uint8_t* b_img = smem + 65536;                 // 2 x [256 x 64] chunk images of 32 KB
+  uint8_t* sink = smem + 65536 + 65536;          // landing area of the copies: nprod x 2 x copy_bytes <= 96 KB
+  for (int i = tid; i < 131072 / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+  if (tid == 0) {
+    mbar_init(&done_bar, 1);
+    for (int p = 0; p < 4; ++p) for (int s = 0; s < 4; ++s) mbar_init(&full[p][s], 1);
+    stop_flag = 0;
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc(&tmem_slot, 512);
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (warp == 0) {
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(128, n_cols, 0, 0);
+      const uint64_t a0 = smem_desc(smem_u32(a_img), 16, 1024, SWIZZLE_128B), b0 = smem_desc(smem_u32(b_img), 16, 1024, SWIZZLE_128B);
+      uint32_t par = 0;
+      const long long t0 = clock64();
+      for (int c = 0; c < chunks; ++c) {           // one chunk = K 64 against N 256 (as one or two MMAs per K step)
+        const uint64_t ad = a0 + (uint64_t)(((c & 3) * 16384) >> 4), bd = b0 + (uint64_t)(((c & 1) * 32768) >> 4);
+        for (int h = 0; h < 256 / n_cols; ++h)
+#pragma unroll
+          for (int k = 0; k < 4; ++k) umma_bf16(tmem + h * 128, ad + 2 * k, bd + (uint64_t)((h * 16384) >> 4) + 2 * k, idesc, 1);
+        if ((c & 7) == 7 || c == chunks - 1) {       // bound the queue: wait for the tensor pipe every 8 chunks
+          umma_commit(&done_bar);
+          while (!mbar_try_wait(&done_bar, par)) { }
+          par ^= 1u;
+        }
+      }
+      out[blockIdx.x * 2] = clock64() - t0;
+      *(volatile int*)&stop_flag = 1;
+    }
+  } else if (warp - 1 < nprod) {
+    if (lane == 0) {
+      const int p = warp - 1;
+      uint8_t* buf = sink + (size_t)p * 2 * copy_bytes;
+      const size_t span = src_bytes - (size_t)copy_bytes;
+      size_t off = ((size_t)p * 262144u) % (span + 1) & ~(size_t)127;
+      uint32_t par[2] = {0u, 0u};
+      long long copies = 0;
+      int issued = 0, done = 0;
+      while (!*(volatile int*)&stop_flag || done < issued) {
+        while (!*(volatile int*)&stop_flag && issued - done < 2) {
+          const int s = issued & 1;
+          mbar_arrive_expect_tx(&full[p][s], (uint32_t)copy_bytes);
+          bulk_g2s(buf + (size_t)s * copy_bytes, src + off, (uint32_t)copy_bytes, &full[p][s]);
+          off += (size_t)copy_bytes; if (off > span) off = 0;
+          ++issued;
+        }
+        if (done < issued) {
+          const int s = done & 1;
+          while (!mbar_try_wait(&full[p][s], par[s])) { }
+          par[s] ^= 1u; ++done; ++copies;
+        }
+      }
+      if (p == 0) out[blockIdx.x * 2 + 1] = copies;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+// out[2 b] = clocks block b needed for `chunks` K-64 x N-256 chunks of MMA; out[2 b + 1] = bulk copies producer 0 completed meanwhile
+extern "C" int cnrf_debug_umma_rate(int32_t blocks, int32_t n_cols, int32_t chunks, int32_t nprod, int32_t copy_bytes, const void* src,
+                                    size_t src_bytes, long long* out, cnrf_stream_t stream) {
+  CNRF_REQUIRE(src && out, CNRF_E_NULL);
+  CNRF_REQUIRE(blocks > 0 && (n_cols == 128 || n_cols == 256) && chunks > 0 && nprod >= 0 && nprod <= 4, CNRF_E_SHAPE);
+  CNRF_REQUIRE(copy_bytes >= 128 && copy_bytes % 128 == 0 && copy_bytes <= 16384 && src_bytes >= (size_t)copy_bytes, CNRF_E_SHAPE);
+  CNRF_REQUIRE((nprod > 0 ? nprod : 1) * 2 * copy_bytes <= 98304, CNRF_E_SHAPE);
+  const int smem = 1024 + 131072 + 98304;
+  cudaError_t e = cudaFuncSetAttribute(umma_rate_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  if (e != cudaSuccess) return (int)e;
+  umma_rate_probe_kernel<<<blocks, 160, smem, as_stream(stream)>>>(n_cols, chunks, nprod, copy_bytes, static_cast<const uint8_t*>(src),
+                                                                   src_bytes, out);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}

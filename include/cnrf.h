@@ -367,7 +367,7 @@ int cnrf_debug_tc_error(void);
 int cnrf_debug_fwd_times(long long* host_out16, int reset);
 /* Timer builds (-DCNRF_FWD_TIMERS) only: clock64 stamps [tile 2][layer 4][event 8] of one steady-state tile pair of block 0
  * (events: mlp_fwd_tc.cu, g_fwd_trace); all zero in ordinary builds. */
-int cnrf_debug_fwd_trace(long long* host_out64);
+int cnrf_debug_fwd_trace(long long* host_out128);  /* [64] pair trace, then [16 images][4 events] of its layer 1 */
 double cnrf_debug_fwd_kernel_ms(int64_t min_rows, int64_t* launches, int64_t* rows);
 /* The same for any of the three tensor-core kernels: which = 0 forward chain, 1 backward-data chain, 2 weight gradients;
  * min_rows < 0 only queries. */
@@ -382,6 +382,19 @@ int cnrf_debug_umma(int32_t mode, const float* A, const float* B, float* D, int3
 /* TMEM read-throughput probe: `blocks` CTAs of `warps` warps sweep all 512 TMEM columns of their lane quarter `iters`
  * times with tcgen05.ld (mode 0: .32x32b.x32 one load in flight, 1: .x32 two in flight, 2: .x64); clocks[b] = SM clocks of
  * block b, sink = blocks*warps*32 words of scratch.  Bytes read per block = warps * iters * 64 KB. */
+/* Bulk-copy ingest probe: `blocks` CTAs each pull iters x bytes through a ring of `slots` cp.async.bulk copies in flight from
+ * src (src_bytes long, walked cyclically; per_block_offset != 0 starts every block 1 MiB apart).  clocks[b] = SM clocks. */
+int cnrf_debug_bulk_ld(int32_t blocks, int32_t slots, int32_t bytes, int32_t iters, const void* src, size_t src_bytes,
+                       int32_t per_block_offset, long long* clocks, cnrf_stream_t stream);
+/* mode 1: nthreads issuing threads with a ring of `slots` each; 2: `slots` copies per round on one mbarrier, one wait per
+ * round; 3: as 2 with the wait on another warp.  clocks[b] covers iters copies (mode 1: per issuing thread). */
+int cnrf_debug_bulk_ld2(int32_t blocks, int32_t slots, int32_t bytes, int32_t iters, int32_t mode, int32_t nthreads,
+                        const void* src, size_t src_bytes, long long* clocks, cnrf_stream_t stream);
+/* MMA operand-bandwidth probe: `blocks` CTAs each run `chunks` K-64 x N-256 chunks of bf16 tcgen05.mma (M = 128; n_cols = 128:
+ * two MMAs per K step, 256: one) over static shared-memory operands while nprod (0-4) threads stream bulk copies of
+ * copy_bytes into shared memory.  out[2b] = SM clocks of the MMA loop, out[2b+1] = copies producer 0 completed meanwhile. */
+int cnrf_debug_umma_rate(int32_t blocks, int32_t n_cols, int32_t chunks, int32_t nprod, int32_t copy_bytes, const void* src,
+                         size_t src_bytes, long long* out, cnrf_stream_t stream);
 int cnrf_debug_tmem_ld(int32_t blocks, int32_t warps, int32_t iters, int32_t mode, long long* clocks, uint32_t* sink,
                        cnrf_stream_t stream);
 

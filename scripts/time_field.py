@@ -44,9 +44,10 @@ try:
           (buf[0] // n, [int(buf[1 + i] // n) for i in range(5)], buf[6] // n, buf[8] // n, buf[9] // n, n))
     print("  epilogue split per pair (5 layers): store-drain + barrier %d | blocks %d | closing barrier %d | store issue + arrive %d" %
           (buf[10] // n, buf[11] // n, buf[12] // n, buf[13] // n))
-    tr = np.zeros(64, dtype=np.int64)
-    lib.cnrf_debug_fwd_trace(ctypes.c_void_p(tr.ctypes.data))
-    tr = tr.reshape(2, 4, 8)
+    print("  MMA warp per pair: fence + 4 MMA issues (sum over images) %d | commits %d" % (buf[14] // n, buf[15] // n))
+    tr_all = np.zeros(128, dtype=np.int64)
+    lib.cnrf_debug_fwd_trace(ctypes.c_void_p(tr_all.ctypes.data))
+    tr, ti = tr_all[:64].reshape(2, 4, 8), tr_all[64:].reshape(16, 4)
     if tr.any():
         t0 = tr[tr > 0].min()
         names = ["wait_acc", "acc_seen", "blocks_start", "blocks_done", "handoff", "mma_sees_a_ready", "mma_issued", "gamma_built"]
@@ -54,5 +55,11 @@ try:
         print("timeline of block 0's 4th tile pair [clk from first event]:")
         for clk, what in ev:
             print(f"  {clk:7d}  {what}")
+        if ti.any():
+            print("weight images of that pair's layer 1 (T0: 0-7, T1: 8-15) [clk from the pair's first event]:")
+            print("  img  slot_empty_seen  copy_issued  image_seen_by_MMA  MMAs_issued   (issue->seen)")
+            for i in range(8):
+                a, b, c, d = (int(x - t0) if x > 0 else -1 for x in ti[i])
+                print(f"  {i:3d}  {a:15d}  {b:11d}  {c:17d}  {d:11d}   {c - b:8d}")
 except Exception as e:
     print("no fwd debug times:", e)
