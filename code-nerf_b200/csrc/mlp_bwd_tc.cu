@@ -3,7 +3,7 @@
 //   d v1 = (d v2p Wd2) * [v1>0],  d h2 = (d v1p Wfh + d sigma w_sigma) * [h2>0],  d h1 = (d h2p W2h) * [h1>0]
 // with W^T streamed as B operands (16 KB N-half images through a 5-slot TMA ring, as in the forward).  Every masked
 // gradient tile is TMA-stored as a bf16 image (same layout as the forward's activation images) for the weight-gradient
-// kernel.  The ReLU masks are the 1-bit sign words the forward saved (32 B per row and layer), loaded before the
+// kernel.  The ReLU masks are the 1-bit sign words the forward saved (32 B per row and layer), requested before the
 // accumulator wait; the epilogue is specialised per stage at compile time.
 // Geometry, warp roles and barrier protocol are those of mlp_fwd_tc.cu.
 #include "mlp_tc.cuh"
@@ -20,6 +20,7 @@ constexpr int BWD_SMEM = OFF_BARS + 256;
 struct BBars {
   uint64_t w_full[BRING], w_empty[BRING];
   uint64_t a_ready[2], acc_full[2];
+  uint64_t img_ready[2], img_saved[2];   // epilogue <-> image-store warp (mlp_tc.cuh)
   uint32_t tmem_slot;
   int abort_flag;
 };
@@ -45,9 +46,9 @@ struct BEpi {
   const float* heads;      // smem: w_sigma[256] | w_rgb[3][256]
   uint32_t tacc;
   int r, bar_id;
+  uint32_t nimg;           // gradient images of this tile handed to the store warp so far
   bool elected, tile_ok;
-  const uint8_t* masks;    // this tile's sign words: [4][128 rows][8]
-  uint8_t* dy;
+  const uint8_t* masks;    // this tile's sign words: [4 layers][8 column blocks][128 rows]
   float4 g;                // upstream gradient of this row's (r, g, b, sigma)
 };
 
@@ -62,14 +63,21 @@ __device__ __forceinline__ bool uwait(uint64_t* bar, uint32_t parity, BBars* b, 
 template <int S, bool XG>
 __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint32_t parity) {
   constexpr int MK = S == -1 ? 3 : S == 0 ? 2 : S == 1 ? 1 : 0;                 // v2, v1, h2, h1
-  const uint32_t* mp = reinterpret_cast<const uint32_t*>(c.masks + (size_t)(MK >= 0 ? MK : 0) * MASK_BYTES + c.r * 32);
-  uint32_t m_a = 0, m_b = 0;
-  if (MK >= 0) m_a = __ldg(mp);
+  // sign words, layout [layer][32-column block][row] (mlp_fwd_tc.cu): a warp reads 128 contiguous bytes per block
+  const uint32_t* mp = reinterpret_cast<const uint32_t*>(c.masks + (size_t)(MK >= 0 ? MK : 0) * MASK_BYTES) + c.r;
+  // all eight words are requested before the accumulator wait (one L2 round trip per stage, not one per block); the loop
+  // below picks its pair with selects -- the loop is not unrolled, and a dynamically indexed array would live in local memory
+  uint32_t mk[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+  if (MK >= 0) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) mk[j] = __ldg(mp + j * TILE);
+  }
   if (S >= 0) {
     if (!bwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
     tc_fence_after();
   }
-  if (c.elected) bulk_wait_read0();                 // the previous image store no longer reads this tile
+  // the store warp has read the previous image out of this tile (a failed wait has raised the abort flag)
+  if (c.elected && c.nimg) (void)bwait(&c.bars->img_saved[t], (c.nimg - 1) & 1u, c.bars, a.err);
   named_bar_sync(c.bar_id, 128);
   const float4* hw = reinterpret_cast<const float4*>(c.heads);
   auto block = [&](int cb, uint32_t (&v)[32], uint32_t w) {
@@ -109,20 +117,18 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
 #pragma unroll 1
   for (int cb = 0; cb < 8; cb += 2) {
     if (S >= 0) { tmem_ld_wait(); tmem_ld32(c.tacc + (cb + 1) * 32, vb); }
-    if (MK >= 0) m_b = __ldg(mp + cb + 1);
+    const uint32_t m_a = (cb & 4) ? ((cb & 2) ? mk[6] : mk[4]) : ((cb & 2) ? mk[2] : mk[0]);
+    const uint32_t m_b = (cb & 4) ? ((cb & 2) ? mk[7] : mk[5]) : ((cb & 2) ? mk[3] : mk[1]);
     block(cb, va, m_a);
     if (S >= 0) tmem_ld_wait();
-    if (cb + 2 < 8) {
-      if (S >= 0) tmem_ld32(c.tacc + (cb + 2) * 32, va);
-      if (MK >= 0) m_a = __ldg(mp + cb + 2);
-    }
+    if (cb + 2 < 8 && S >= 0) tmem_ld32(c.tacc + (cb + 2) * 32, va);
     block(cb + 1, vb, m_b);
   }
   fence_proxy_async();
   tc_fence_before();
   named_bar_sync(c.bar_id, 128);
   if (c.elected) {
-    if (c.tile_ok) { bulk_s2g(c.dy + (size_t)(S + 1) * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
+    mbar_arrive(&c.bars->img_ready[t]); ++c.nimg;
     if (S < 2 || XG) mbar_arrive(&c.bars->a_ready[t]);     // XG: the input-gradient stage reads d h1p as its A operand
   }
   return true;
@@ -162,7 +168,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
 
   if (tid == 0) {
     for (int i = 0; i < BRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1); }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&bars->a_ready[t], 1); mbar_init(&bars->acc_full[t], 1);
+      mbar_init(&bars->img_ready[t], 1); mbar_init(&bars->img_saved[t], 1);
+    }
     bars->abort_flag = 0;
     if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); tc_fatal(); }
     mbar_fence_init();
@@ -179,7 +188,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
     // ===== TMA producers: per (stage, tile) the 4 transposed K-chunks x 2 N-halves of that stage =====
     // The two tiles of a pair run half a stage apart (one tile's MMAs under the other's epilogue), so the L2-resident
     // weight images pass through the ring once per tile.  NPROD producers share the image sequence round-robin (one
-    // issuing thread manages a bulk copy per ~588 clk, the tensor core eats an image in 256: mlp_tc.cuh).
+    // issuing thread manages a bulk copy per ~588 clk, the tensor core eats an image in ~280: mlp_tc.cuh).
     if (lane == 0) {
       uint32_t slot = 0, epar = 1;
       uint32_t turn = 0;
@@ -205,7 +214,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
     // ===== MMA issuer: warp-uniform control flow, one elected lane issues (see mlp_fwd_tc.cu) =====
     {
       const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);
-      const uint32_t idesc = idesc_bf16(128, 128, 0, 0);
+      // two N-halves in adjacent ring slots = one [256 x 64] image: one MMA of N = 256 per K step (see mlp_fwd_tc.cu)
+      const uint32_t idesc = idesc_bf16(128, 128, 0, 0), idesc_wide = idesc_bf16(128, 256, 0, 0);
       const uint64_t a_desc0 = smem_desc(smem_u32(tiles), 16, 1024, SWIZZLE_128B);
       const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
       uint32_t slot = 0, wpar = 0, na = 0;
@@ -220,20 +230,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
 #pragma unroll 1
             for (int c = 0; c < 4 && ok; ++c) {
               const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
+              const uint32_t s0 = slot;
+              if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; break; }
+              if (++slot == BRING) { slot = 0; wpar ^= 1u; }
+              const uint32_t s1 = slot;
+              if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; break; }
+              if (++slot == BRING) { slot = 0; wpar ^= 1u; }
+              tc_fence_after();
+              const uint64_t bd0 = b_desc0 + (uint64_t)((s0 * HALF) >> 4), bd1 = b_desc0 + (uint64_t)((s1 * HALF) >> 4);
+              if (elect_one()) {
+                if (s1 == s0 + 1) {
 #pragma unroll
-              for (int h = 0; h < 2; ++h) {
-                if (!ok) continue;
-                if (!uwait(&bars->w_full[slot], wpar, bars, a.err)) { ok = false; continue; }
-                tc_fence_after();
-                const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
-                if (elect_one()) {
+                  for (int k = 0; k < 4; ++k) umma_bf16(d0, ad + 2 * k, bd0 + 2 * k, idesc_wide, (c | k) != 0);
+                  umma_commit(&bars->w_empty[s0]);
+                } else {                                // the chunk straddles the ring's wrap
 #pragma unroll
-                  for (int k = 0; k < 4; ++k) umma_bf16(d0 + h * 128, ad + 2 * k, bd + 2 * k, idesc, (c | k) != 0);
-                  umma_commit(&bars->w_empty[slot]);
+                  for (int k = 0; k < 4; ++k) umma_bf16(d0, ad + 2 * k, bd0 + 2 * k, idesc, (c | k) != 0);
+                  umma_commit(&bars->w_empty[s0]);
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) umma_bf16(d0 + 128, ad + 2 * k, bd1 + 2 * k, idesc, (c | k) != 0);
                 }
-                __syncwarp();
-                if (++slot == BRING) { slot = 0; wpar ^= 1u; }
+                umma_commit(&bars->w_empty[s1]);
               }
+              __syncwarp();
             }
             if (ok && elect_one()) umma_commit(&bars->acc_full[t]);
             __syncwarp();
@@ -270,7 +289,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
         }
       }
     }
-  } else if (warp < 10) {
+  } else if (warp == STORE_WARP) {
+    // ===== image-store warp: the four masked gradient images of both tiles, in the order the epilogues finish them =====
+    uint32_t par[2] = {0u, 0u};
+    bool ok = true;
+    for (int64_t pr = blockIdx.x; pr < num_pairs && ok; pr += gridDim.x) {
+#pragma unroll 1
+      for (int seq = 0; seq < 8 && ok; ++seq) {
+        const int k = seq >> 1, t = seq & 1;
+        const int64_t tile_idx = pr * 2 + t;
+        if (!bwait(&bars->img_ready[t], par[t], bars, a.err)) { ok = false; break; }
+        par[t] ^= 1u;
+        if (tile_idx < num_tiles)
+          warp_copy_image(a.dy + (size_t)tile_idx * DY_PER_TILE + (size_t)k * TILE_BYTES, tiles + t * TILE_BYTES, TILE_BYTES, lane);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bars->img_saved[t]);
+      }
+    }
+  } else if (warp >= 2 && warp < 10) {
     // ===== epilogue warps: thread = one sample row =====
     const int t = (warp - 2) >> 2;
     const int q = warp & 3;
@@ -283,12 +319,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
     c.elected = ((warp - 2) & 3) == 0 && lane == 0;
     c.tacc = tmem + t * 256 + ((uint32_t)(q * 32) << 16);
     uint32_t na = 0;
+    c.nimg = 0;
     for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
       const int64_t tile_idx = pr * 2 + t;
       c.tile_ok = tile_idx < num_tiles;
       const int64_t m = tile_idx * TILE + c.r;
       c.masks = a.saved + (size_t)(c.tile_ok ? tile_idx : 0) * SAVED_PER_TILE + SAVED_MASKS;
-      c.dy = a.dy + (size_t)(c.tile_ok ? tile_idx : 0) * DY_PER_TILE;
       c.g = m < a.M ? __ldg(reinterpret_cast<const float4*>(a.g_raw) + m) : make_float4(0.f, 0.f, 0.f, 0.f);
       bool ok = bwd_stage<-1, XG>(a, c, t, 0);
       if (ok) { ok = bwd_stage<0, XG>(a, c, t, na & 1); ++na; }
@@ -297,7 +333,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
       if (XG && ok) { ok = bwd_stage_x(a, c, t, na & 1, m); ++na; }
       if (!ok) break;
     }
-    if (c.elected) bulk_wait0();
   }
   tc_fence_before();
   __syncthreads();

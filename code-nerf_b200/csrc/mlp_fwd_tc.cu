@@ -53,6 +53,8 @@ struct FBars {
   uint64_t a_ready[2];     // epilogue -> MMA : tile's operand image written
   uint64_t acc_full[2];    // MMA -> epilogue : tile's accumulator complete
   uint64_t w_peer[FRING];  // CTA pairs: the other CTA's half of the weight image has landed (forwarded by its warp 1)
+  uint64_t img_ready[2];   // epilogue -> store warp : the tile holds a finished image the backward needs
+  uint64_t img_saved[2];   // store warp -> epilogue : that image has been read out of shared memory
   uint32_t tmem_slot;
   int abort_flag;
 };
@@ -109,6 +111,7 @@ struct Epi {               // per-thread state of an epilogue thread for the cur
   float* stage;            // smem: [RMAX][256] bias rows of this tile's rays
   uint32_t tacc;
   int r, bar_id, slot, nrays, it;
+  uint32_t nimg;           // images of this tile handed to the store warp so far (training forward)
   bool elected, valid, staged;
   int64_t m, ray0;
   int row;                 // this thread's row of the per-ray bias tables (its ray, or the ray's code run)
@@ -132,7 +135,8 @@ __device__ __forceinline__ void stage_rows(const Epi& c, const float* table, con
 // One layer's epilogue for one tile.  E: 0 layer_xyz1 (its bias arrives through the MMA), 1 layer_xyz2 (+ sigma head),
 // 2 folded layer_dir1 (per-ray bias here; its constant bias and view-direction half arrive through the MMA),
 // 3 layer_dir2 (+ rgb head).  GB: bias row comes from global memory (register double buffer) instead of shared memory.
-template <int E, bool GB>
+// SV: the training forward (saved images + sign words); the inference kernel compiles none of that work in.
+template <int E, bool GB, bool SV>
 __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint32_t parity) {
   const float4* gb = nullptr;
   const float4* sb = nullptr;
@@ -146,7 +150,9 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if (!fwait(&c.bars->acc_full[t], parity, c.bars, a.err)) return false;
   const long long tw1 = FCLK();
   tc_fence_after();
-  if (c.elected) bulk_wait_read0();                 // the previous image store no longer reads this tile
+  // the store warp has read the previous image out of this tile
+  // (a failed wait has raised the abort flag: every thread leaves at its next wait)
+  if (SV && c.elected && c.nimg) (void)fwait(&c.bars->img_saved[t], (c.nimg - 1) & 1u, c.bars, a.err);
   if ((E == 1 || E == 2) && !GB) cp_async_wait_all();
   named_bar_sync(c.bar_id, 128);
   const long long tw2 = FCLK();
@@ -154,7 +160,8 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   float rgb0 = 0.f, rgb1 = 0.f, rgb2 = 0.f, rgb3 = 0.f, rgb4 = 0.f, rgb5 = 0.f;   // two partial sums per channel
   float sg0 = 0.f, sg1 = 0.f, sg2 = 0.f, sg3 = 0.f;                               // four partial sums of the sigma head
   // sign bits of the pre-activations (the backward's ReLU mask): one 32-bit word per 32-column block
-  uint32_t* mp = c.sv ? reinterpret_cast<uint32_t*>(c.sv + SAVED_MASKS + (size_t)E * MASK_BYTES + c.r * 32) : nullptr;
+  // layout [layer][32-column block][row]: the 32 lanes of a warp write (and the backward reads) 128 contiguous bytes
+  uint32_t* mp = (SV && c.sv) ? reinterpret_cast<uint32_t*>(c.sv + SAVED_MASKS + (size_t)E * MASK_BYTES) + c.r : nullptr;
   // One 32-column block: + bias, heads, sign word, ReLU, bf16, swizzled store.  The loop below keeps the next block's
   // TMEM load in flight while this one is processed, and is NOT unrolled further: five specialised layers unrolled eight
   // times each overflowed the instruction cache (16% of the kernel's stall samples were instruction fetches).
@@ -194,16 +201,18 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
         rgb2 = fmaf(x0, w2.x, fmaf(x1, w2.y, rgb2)); rgb5 = fmaf(x2, w2.z, fmaf(x3, w2.w, rgb5));
       }
     }
-    {
+    if (SV) {
       uint32_t w = 0;
 #pragma unroll
       for (int j = 0; j < 32; ++j) w = __funnelshift_l(__float_as_uint(f[j]), w, 1);   // (w << 1) | sign(f[j])
-      if (mp) mp[cb] = w;
+      if (mp) mp[cb * TILE] = w;
     }
-    uint32_t pk[16];
+    if (E < 3 || SV) {                              // the last layer's image is only ever read by the backward
+      uint32_t pk[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) pk[j] = cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
-    store_row_block(c.tile, c.r, cb, pk);
+      for (int j = 0; j < 16; ++j) pk[j] = cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
+      store_row_block(c.tile, c.r, cb, pk);
+    }
   };
   uint32_t va[32], vb[32];
   tmem_ld32(c.tacc, va);
@@ -229,7 +238,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
   if (c.elected) {
     // the hand-off first: a cluster-scope release issued after the bulk store waits for that store (~3.5 k clk)
     if (E < 3) { if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&c.bars->a_ready[t]); }
-    if (c.sv) { bulk_s2g(c.sv + SAVED_GAMMA + (size_t)E * TILE_BYTES, c.tile, TILE_BYTES); bulk_commit(); }
+    if (SV) { mbar_arrive(&c.bars->img_ready[t]); ++c.nimg; }
     if (t == 0) { FDBG(0, tw1 - tw0); FDBG(1 + E, FCLK() - tw1); FDBG(13, FCLK() - tw4); }
   }
   return true;
@@ -241,7 +250,7 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
 // single-CTA kernel waits one L2 round trip per (layer, tile) for the images the ring cannot hold -- and the tensor core
 // reads half as many operand bytes from shared memory per FLOP.  The leader CTA (cluster rank 0) issues; the other CTA's
 // warp 1 forwards "my half has landed" to the leader, and both CTAs' epilogues report to the leader's a_ready barriers.
-template <int CG>
+template <int CG, bool SV>
 __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a) {
   extern __shared__ __align__(1024) uint8_t smem[];   // 128-byte-swizzled images need 1024-byte alignment
   uint8_t* tiles = smem;
@@ -259,7 +268,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
 
   if (tid == 0) {
     for (int i = 0; i < FRING; ++i) { mbar_init(&bars->w_full[i], 1); mbar_init(&bars->w_empty[i], 1); mbar_init(&bars->w_peer[i], 1); }
-    for (int t = 0; t < 2; ++t) { mbar_init(&bars->a_ready[t], CG); mbar_init(&bars->acc_full[t], 1); }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&bars->a_ready[t], CG); mbar_init(&bars->acc_full[t], 1);
+      mbar_init(&bars->img_ready[t], 1); mbar_init(&bars->img_saved[t], 1);
+    }
     bars->abort_flag = 0;
     if ((smem_u32(smem) & 1023u) != 0) { bars->abort_flag = 1; atomicExch(a.err, 2); tc_fatal(); }
     mbar_fence_init();
@@ -339,6 +351,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
     {
       const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);       // provably warp-uniform copy
       const uint32_t idesc = CG == 2 ? idesc_bf16(256, 256, 0, 0) : idesc_bf16(128, 128, 0, 0);
+      // CG = 1: when the two N-halves of a chunk sit in adjacent ring slots (4 chunks of 5: the ring has 5 slots) they form
+      // one [256 x 64] image and ONE MMA of N = 256 per K step covers both.  An M128 N128 K16 step reads 8 KB of operands
+      // from shared memory for 64 clk of math, which holds the tensor pipe at 75%; N256 reads 12 KB per 128 clk and reaches
+      // 92% (scripts/probe_umma_rate.py, profiles/r02_umma_rate_probe.json).
+      const uint32_t idesc_wide = idesc_bf16(128, 256, 0, 0);
       // descriptors differ only in their 14-bit start-address field (bytes >> 4): precompute the bases, add offsets
       const uint64_t a_desc0 = smem_desc(smem_u32(tiles), 16, 1024, SWIZZLE_128B);
       const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
@@ -363,25 +380,48 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
 #pragma unroll 1
             for (int c = 0; c < nch && ok; ++c) {
               const uint64_t ad = a_desc0 + (uint64_t)((t * TILE_BYTES + c * SLAB) >> 4);
-#pragma unroll
-              for (int h = 0; h < 2 / CG; ++h) {      // CG = 1: the two N-halves of the chunk; CG = 2: one MMA of N = 256
-                if (!ok) continue;
+              if (CG == 1) {
                 const long long m0 = FCLK();
-                if (!WAIT_IMAGE()) { ok = false; continue; }
+                const uint32_t s0 = slot;
+                if (!WAIT_IMAGE()) { ok = false; break; }
+                if (lane == 0) FTRACE_IMG(it_m, layer, t * 8 + c * 2, 2);
+                NEXT_SLOT();
+                const uint32_t s1 = slot;
+                if (!WAIT_IMAGE()) { ok = false; break; }
+                NEXT_SLOT();
                 FDBG(8, FCLK() - m0);
-                if (lane == 0) FTRACE_IMG(it_m, layer, t * 8 + c * 2 + h, 2);
+                if (lane == 0) FTRACE_IMG(it_m, layer, t * 8 + c * 2 + 1, 2);
                 const long long m2 = FCLK();
+                tc_fence_after();
+                const uint64_t bd0 = b_desc0 + (uint64_t)((s0 * HALF) >> 4), bd1 = b_desc0 + (uint64_t)((s1 * HALF) >> 4);
+                if (elect_one()) {
+                  if (s1 == s0 + 1) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(d0, ad + 2 * k, bd0 + 2 * k, idesc_wide, (c | k) != 0);
+                    umma_commit(&bars->w_empty[s0]);
+                  } else {                              // the chunk straddles the ring's wrap: two MMAs of N = 128 per K step
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(d0, ad + 2 * k, bd0 + 2 * k, idesc, (c | k) != 0);
+                    umma_commit(&bars->w_empty[s0]);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) umma_bf16(d0 + 128, ad + 2 * k, bd1 + 2 * k, idesc, (c | k) != 0);
+                  }
+                  const long long m3 = FCLK();
+                  umma_commit(&bars->w_empty[s1]);
+                  FDBG(14, m3 - m2); FDBG(15, FCLK() - m3);
+                }
+                __syncwarp();
+                if (lane == 0) { FTRACE_IMG(it_m, layer, t * 8 + c * 2, 3); FTRACE_IMG(it_m, layer, t * 8 + c * 2 + 1, 3); }
+              } else {                                  // CG = 2: one MMA of M = N = 256 over this CTA's and the peer's half
+                if (!WAIT_IMAGE()) { ok = false; break; }
                 tc_fence_after();
                 const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
                 if (elect_one()) {
 #pragma unroll
-                  for (int k = 0; k < 4; ++k) MMA(d0 + h * 128, ad + 2 * k, bd + 2 * k, (c | k) != 0);
-                  const long long m3 = FCLK();
+                  for (int k = 0; k < 4; ++k) MMA(d0, ad + 2 * k, bd + 2 * k, (c | k) != 0);
                   COMMIT(&bars->w_empty[slot]);
-                  FDBG(14, m3 - m2); FDBG(15, FCLK() - m3);
                 }
                 __syncwarp();
-                if (lane == 0) FTRACE_IMG(it_m, layer, t * 8 + c * 2 + h, 3);
                 NEXT_SLOT();
               }
             }
@@ -390,21 +430,43 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
               if (!WAIT_IMAGE()) { ok = false; break; }
               NEXT_SLOT();
               const uint64_t xd = b_desc0 + (uint64_t)((slot_x * HALF) >> 4);
+              if (CG == 1) {
+                const uint32_t s0 = slot;
+                if (!WAIT_IMAGE()) { ok = false; break; }
+                NEXT_SLOT();
+                const uint32_t s1 = slot;
+                if (!WAIT_IMAGE()) { ok = false; break; }
+                NEXT_SLOT();
+                tc_fence_after();
+                const uint64_t bd0 = b_desc0 + (uint64_t)((s0 * HALF) >> 4), bd1 = b_desc0 + (uint64_t)((s1 * HALF) >> 4);
+                if (elect_one()) {
+                  if (s1 == s0 + 1) {
 #pragma unroll
-              for (int h = 0; h < 2 / CG; ++h) {
-                if (!ok) continue;
-                if (!WAIT_IMAGE()) { ok = false; continue; }
+                    for (int k = 0; k < 2; ++k) umma_bf16(d0, xd + 2 * (2 * t + k), bd0 + 2 * k, idesc_wide, 1);
+                  } else {
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) umma_bf16(d0, xd + 2 * (2 * t + k), bd0 + 2 * k, idesc, 1);
+#pragma unroll
+                    for (int k = 0; k < 2; ++k) umma_bf16(d0 + 128, xd + 2 * (2 * t + k), bd1 + 2 * k, idesc, 1);
+                  }
+                  umma_commit(&bars->w_empty[s0]);
+                  umma_commit(&bars->w_empty[s1]);
+                  umma_commit(&bars->w_empty[slot_x]);
+                }
+                __syncwarp();
+              } else {
+                if (!WAIT_IMAGE()) { ok = false; break; }
                 tc_fence_after();
                 const uint64_t bd = b_desc0 + (uint64_t)((slot * HALF) >> 4);
                 if (elect_one()) {
 #pragma unroll
-                  for (int k = 0; k < 2; ++k) MMA(d0 + h * 128, xd + 2 * (2 * t + k), bd + 2 * k, 1);
+                  for (int k = 0; k < 2; ++k) MMA(d0, xd + 2 * (2 * t + k), bd + 2 * k, 1);
                   COMMIT(&bars->w_empty[slot]);
+                  COMMIT(&bars->w_empty[slot_x]);
                 }
                 __syncwarp();
                 NEXT_SLOT();
               }
-              if (ok && elect_one()) COMMIT(&bars->w_empty[slot_x]);
             }
             if (ok && elect_one()) COMMIT(&bars->acc_full[t]);
             __syncwarp();
@@ -418,7 +480,30 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
 #undef MMA
 #undef COMMIT
     }
-  } else if (warp < 10) {
+  } else if (warp == STORE_WARP) {
+    // ===== image-store warp (training forward): per pair gamma(x) of both tiles, then the four layer images of both =====
+    if (SV) {
+      uint32_t par[2] = {0u, 0u};
+      bool ok = true;
+      for (int64_t pb = pair_first; pb < num_pairs && ok; pb += gridDim.x) {
+        const int64_t pr = pb + rank;
+#pragma unroll 1
+        for (int seq = 0; seq < 10 && ok; ++seq) {
+          const int k = seq >> 1, t = seq & 1;
+          const int64_t tile_idx = pr * 2 + t;
+          if (!fwait(&bars->img_ready[t], par[t], bars, a.err)) { ok = false; break; }
+          par[t] ^= 1u;
+          if (a.saved && tile_idx < num_tiles) {
+            uint8_t* sv = a.saved + (size_t)tile_idx * SAVED_PER_TILE;
+            if (k == 0) warp_copy_image(sv, tiles + t * TILE_BYTES, SLAB, lane);
+            else warp_copy_image(sv + SAVED_GAMMA + (size_t)(k - 1) * TILE_BYTES, tiles + t * TILE_BYTES, TILE_BYTES, lane);
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bars->img_saved[t]);
+        }
+      }
+    }
+  } else if (warp >= 2 && warp < 10) {
     // ===== epilogue warps: thread = one sample row =====
     const int t = (warp - 2) >> 2;                    // tile of the pair
     const int q = warp & 3;                           // TMEM lane quarter this warp may read
@@ -445,6 +530,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       if (m1 < a.M) { c.px = __ldg(a.pts + m1 * 3); c.py = __ldg(a.pts + m1 * 3 + 1); c.pz = __ldg(a.pts + m1 * 3 + 2); }
     }
     c.it = -1;
+    c.nimg = 0;
     for (int64_t pb = pair_first; pb < num_pairs; pb += gridDim.x) {
       ++c.it;
       const int64_t pr = pb + rank;
@@ -469,11 +555,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       c.nrays = first < a.M ? (int)(last_ray - c.ray0) + 1 : 0;
       c.staged = c.nrays <= RMAX;
       c.slot = c.valid ? (int)(ray - c.ray0) : 0;
-      c.sv = (a.saved && tile_idx < num_tiles) ? a.saved + (size_t)tile_idx * SAVED_PER_TILE : nullptr;
+      c.sv = (SV && a.saved && tile_idx < num_tiles) ? a.saved + (size_t)tile_idx * SAVED_PER_TILE : nullptr;
       c.sigma = 0.f;
       // ---- input image: gamma(x); the bias rows of layer_xyz2 travel to smem meanwhile ----
       const long long tb0 = FCLK();
-      if (c.elected) bulk_wait_read0();               // the previous pair's last image store has finished reading smem
+      // the previous pair's last image has been read out of shared memory
+      if (SV && c.elected && c.nimg) (void)fwait(&bars->img_saved[t], (c.nimg - 1) & 1u, bars, a.err);
       named_bar_sync(c.bar_id, 128);
       stage_rows(c, a.b2, a.gid);
       if (pe_fast) {
@@ -488,21 +575,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_fwd_tc_kernel(const FwdArgs a
       named_bar_sync(c.bar_id, 128);
       if (c.elected) {
         if (c.ar_cluster) mbar_arrive_cluster(c.ar_cluster); else mbar_arrive(&bars->a_ready[t]);
-        if (c.sv) { bulk_s2g(c.sv, c.tile, SLAB); bulk_commit(); }
+        if (SV) { mbar_arrive(&bars->img_ready[t]); ++c.nimg; }
         if (t == 0) { FDBG(6, FCLK() - tb0); FDBG(7, 1); }
         FTRACE(c.it, t, 0, 7, FCLK());
       }
-      bool ok = epi_layer<0, false>(a, c, t, na & 1); ++na;
-      if (ok) { ok = c.staged ? epi_layer<1, false>(a, c, t, na & 1) : epi_layer<1, true>(a, c, t, na & 1); ++na; }
+      bool ok = epi_layer<0, false, SV>(a, c, t, na & 1); ++na;
+      if (ok) { ok = c.staged ? epi_layer<1, false, SV>(a, c, t, na & 1) : epi_layer<1, true, SV>(a, c, t, na & 1); ++na; }
       if (ok) {
         stage_rows(c, a.bf, a.gid);                        // every thread of the tile is past its reads of the beta2 rows
-        ok = c.staged ? epi_layer<2, false>(a, c, t, na & 1) : epi_layer<2, true>(a, c, t, na & 1); ++na;
+        ok = c.staged ? epi_layer<2, false, SV>(a, c, t, na & 1) : epi_layer<2, true, SV>(a, c, t, na & 1); ++na;
       }
-      if (ok) { ok = epi_layer<3, false>(a, c, t, na & 1); ++na; }
+      if (ok) { ok = epi_layer<3, false, SV>(a, c, t, na & 1); ++na; }
       if (!ok) break;
     }
     cp_async_wait_all();
-    if (c.elected) bulk_wait0();
   }
   tc_fence_before();
   __syncthreads();
@@ -523,8 +609,10 @@ int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
   {
     static bool attr_set[CNRF_MAX_DEVICES] = {};
     const cudaError_t e = cnrf_once_per_device(attr_set, [] {
-      cudaError_t e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
-      if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+      cudaError_t e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+      if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+      if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
+      if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(mlp_fwd_tc_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FWD_SMEM);
       return e1; });
     if (e != cudaSuccess) return (int)e;
   }
@@ -544,11 +632,12 @@ int cnrf_tc_launch_fwd(const FwdArgs& f, int grid, cudaStream_t st) {
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, mlp_fwd_tc_kernel<2>, f);
+    cudaError_t e = f.saved ? cudaLaunchKernelEx(&cfg, mlp_fwd_tc_kernel<2, true>, f) : cudaLaunchKernelEx(&cfg, mlp_fwd_tc_kernel<2, false>, f);
     if (e != cudaSuccess) return (int)e;
     ++g_cnrf_launches;
   } else {
-    mlp_fwd_tc_kernel<1><<<grid, NTHREADS, FWD_SMEM, st>>>(f);
+    if (f.saved) mlp_fwd_tc_kernel<1, true><<<grid, NTHREADS, FWD_SMEM, st>>>(f);
+    else mlp_fwd_tc_kernel<1, false><<<grid, NTHREADS, FWD_SMEM, st>>>(f);
     CNRF_LAUNCH_CHECK();
   }
   if (timed) cnrf_ktimer_end(CNRF_KT_FWD, st);

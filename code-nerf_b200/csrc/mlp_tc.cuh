@@ -12,13 +12,29 @@ constexpr int SLAB = TILE * 128;          // bytes of one [128 x 64] bf16 slab
 constexpr int TILE_BYTES = 4 * SLAB;      // 64 KB: one [128 x 256] activation tile image
 constexpr int CHUNK = 256 * 128;          // 32 KB: one [256 x 64] weight chunk image
 constexpr int RING = 3;
-// Warps of the chain kernels: 0 = TMA producer, 1 = MMA issuer, 2-9 = epilogue (4 per tile), 10.. = further TMA producers.
+// Warps of the chain kernels: 0 and 10 = TMA producers, 1 = MMA issuer, 2-9 = epilogue (4 per tile), 11 = image-store warp.
 // ONE thread alternating mbarrier.try_wait / expect_tx / cp.async.bulk completes a copy every ~588 clk whatever its size
 // (profiles/r02_bulk_copy_probe*.json: 2 issuing threads 294 clk, 4 threads 147 clk per copy, on 1 or 148 SMs alike), while
-// the tensor core consumes a 16 KB weight image in 256 clk: NPROD producers take the images of the stream round-robin.
-constexpr int NPROD = 3;
-constexpr int NTHREADS = 320 + 32 * (NPROD - 1);
-__device__ __forceinline__ int producer_index(int warp) { return warp == 0 ? 0 : warp >= 10 ? warp - 9 : -1; }
+// the tensor core consumes a 16 KB weight image in ~280 clk: NPROD producers take the images of the stream round-robin.
+// The images the backward needs (activations / masked gradients, 64 KB per layer and tile) are NOT stored by TMA: the
+// SM's TMA unit works through its queue in order, and a 64 KB store ahead of the weight loads starves the tensor core for
+// ~1.7 k clk (forward: 306 us without the stores, 489 us with bulk stores, whether the destination is HBM or an L2-resident
+// scratch).  Warp STORE_WARP copies them shared -> global with LDS.128 / STG.128 instead, hand-shaking with the tile's
+// epilogue warps through two mbarriers.
+constexpr int NPROD = 2;
+constexpr int NTHREADS = 384;
+constexpr int STORE_WARP = 11;
+__device__ __forceinline__ int producer_index(int warp) { return warp == 0 ? 0 : warp == 10 ? 1 : -1; }
+// one warp copies `bytes` (a multiple of 4 KB) of a shared-memory image to global memory
+__device__ __forceinline__ void warp_copy_image(uint8_t* __restrict__ dst, const uint8_t* src_smem, int bytes, int lane) {
+  for (int off = lane * 16; off < bytes; off += 8 * 512) {
+    uint4 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const uint4*>(src_smem + off + j * 512);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) __stcs(reinterpret_cast<uint4*>(dst + off + j * 512), v[j]);
+  }
+}
 // fc_out is FOLDED into layer_dir1 (models/model.py:182-189 apply no activation between them): the per-sample chain has four
 // 256-wide tensor-core layers  W1 | W2h | Wfh = Wdf Wout'[:, :H] | Wd2  (the fold is rebuilt from the fp32 parameters at
 // every call, codenerf.cu)
@@ -91,7 +107,7 @@ __device__ __forceinline__ bool wait_bar(uint64_t* bar, uint32_t parity, Bars* b
 
 constexpr size_t SAVED_GAMMA = SLAB;                          // gamma(x) slab (K = 64)
 constexpr size_t SAVED_MASKS = SAVED_GAMMA + 4 * (size_t)TILE_BYTES;      // after the h1, h2, v1, v2 images
-constexpr size_t MASK_BYTES = 128 * 32;                                   // one layer's sign bits: 8 words per sample row
+constexpr size_t MASK_BYTES = 128 * 32;                                   // one layer's sign bits: [8 column blocks][128 rows] words
 // 4 x 4 KB of sign-bit words (h1, h2, v1, v2 pre-activations; bit 31-j of word cb = column 32 cb + j is <= 0): the
 // backward reads 32 B per row and layer instead of re-reading the 64 KB activation image for its ReLU mask
 constexpr size_t SAVED_PER_TILE = SAVED_MASKS + 4 * MASK_BYTES;

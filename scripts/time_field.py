@@ -58,7 +58,7 @@ try:
         if ti.any():
             print("weight images of that pair's layer 1 (T0: 0-7, T1: 8-15) [clk from the pair's first event]:")
             print("  img  slot_empty_seen  copy_issued  image_seen_by_MMA  MMAs_issued   (issue->seen)")
-            for i in range(8):
+            for i in range(16):
                 a, b, c, d = (int(x - t0) if x > 0 else -1 for x in ti[i])
                 print(f"  {i:3d}  {a:15d}  {b:11d}  {c:17d}  {d:11d}   {c - b:8d}")
 except Exception as e:
