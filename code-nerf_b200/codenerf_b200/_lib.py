@@ -9,7 +9,7 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libcnrf.so")
 NUM_LAYERS = 9
 LAYER_NAMES = ("layer_xyz1", "layer_xyz2", "fc_out", "shape_code_layer1", "shape_code_layer2",
                "texture_code_layer1", "layer_dir1", "layer_dir2", "fc_rgb")
-PRECISION_FP32, PRECISION_BF16 = 0, 1
+PRECISION_FP32, PRECISION_BF16, PRECISION_SPLIT = 0, 1, 2
 PAIRING_REFERENCE, PAIRING_CORRECT = 0, 1
 
 c_f32p = C.c_void_p   # device pointers travel as integers
@@ -70,6 +70,9 @@ _SIGS = {
     "cnrf_debug_umma": (C.c_int, [c_i32, c_f32p, c_f32p, c_f32p, c_i32, c_i32, c_f32p, C.c_void_p]),
     "cnrf_debug_bulk_ld": (C.c_int, [c_i32, c_i32, c_i32, c_i32, C.c_void_p, c_sz, c_i32, C.c_void_p, C.c_void_p]),
     "cnrf_debug_bulk_ld2": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, C.c_void_p, c_sz, C.c_void_p, C.c_void_p]),
+    "cnrf_u8_to_unit": (C.c_int, [C.c_void_p, c_i64, C.c_void_p, C.c_void_p]),
+    "cnrf_gather_pixels_u8": (C.c_int, [C.c_void_p, c_i64, c_i64, c_i32, C.c_void_p, C.c_void_p, c_i64, c_i64, c_i32, C.c_void_p,
+                                        C.c_void_p, C.c_void_p]),
     "cnrf_debug_umma_rate": (C.c_int, [c_i32, c_i32, c_i32, c_i32, c_i32, C.c_void_p, c_sz, C.c_void_p, C.c_void_p]),
     "cnrf_debug_tmem_ld": (C.c_int, [c_i32, c_i32, c_i32, c_i32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cnrf_debug_fwd_trace": (C.c_int, [C.c_void_p]),

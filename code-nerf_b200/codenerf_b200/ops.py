@@ -431,6 +431,9 @@ class _FieldIds(torch.autograd.Function):
         return (None, None, None, None, g_ts, g_tt, None, None) + grads
 
 
+POSE_GRAD_PRECISION_DEFAULT = "split"
+
+
 def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code, dim_xyz, dim_dir,
                    pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_BF16, code_source=None):
     """params: the 18 tensors (weight, bias per layer) in _lib.LAYER_NAMES order.
@@ -438,12 +441,14 @@ def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code
     code_source = (ids, shape_table, texture_table): z_s / z_t are the rows ids of those tables (ShapeTextureEmbedding's
     output); the bf16 path then shares the code-layer work between rays of equal id (_FieldIds)."""
     pose_grad = (pts.requires_grad or rd.requires_grad) and torch.is_grad_enabled()
-    if precision == _lib.PRECISION_BF16 and pose_grad and os.environ.get("CODENERF_POSE_GRAD_PRECISION", "fp32") != "bf16":
-        # camera-pose optimisation (eval.py:129-168) defaults to the fp32 parity mode: the point gradient sums encoding
-        # terms weighted by frequencies up to 512, and the bf16 chain's fifth backward stage reproduces the fp32 ray
-        # gradients only to ~4 % (cosine 0.999, tests/test_gpu_tc.py::test_tc_pose_gradients_match_fp32).
-        # CODENERF_POSE_GRAD_PRECISION=bf16 opts into the tensor-core path (~50x faster).
-        precision = _lib.PRECISION_FP32
+    if precision == _lib.PRECISION_BF16 and pose_grad:
+        # camera-pose optimisation (eval.py:129-168): the point gradient sums encoding terms weighted by frequencies up
+        # to 512, and the bf16 chain's fifth backward stage reproduces the fp32 ray gradients only to ~4 % (cosine 0.999,
+        # tests/test_gpu_tc.py::test_tc_pose_gradients_match_fp32).  CODENERF_POSE_GRAD_PRECISION selects the chain such
+        # a call runs on: "fp32" CUDA-core FMA (the golden parity mode), "split" the same path with split-bf16
+        # tensor-core contractions (~16 mantissa bits), "bf16" the fused chain.
+        precision = {"fp32": _lib.PRECISION_FP32, "split": _lib.PRECISION_SPLIT, "bf16": _lib.PRECISION_BF16}[
+            os.environ.get("CODENERF_POSE_GRAD_PRECISION", POSE_GRAD_PRECISION_DEFAULT)]
     if pose_grad:
         code_source = None                # the shared-code path carries no ray / point gradients
     cfg = (hidden, code, dim_xyz, dim_dir, pairing, precision)

@@ -43,6 +43,7 @@ struct Dims {
   int H, C, dx, dd, S, pairing;
   int64_t N, M;
   bool tc;   // per-ray GEMMs on the tensor cores (gemm_tc.cu) instead of the fp32 SIMT toolkit
+  bool split = false;   // CNRF_PRECISION_SPLIT: the per-SAMPLE GEMMs of the fp32-layout chain as split-bf16 tensor-core GEMMs
   const int32_t* rows_dev = nullptr;   // shared-code mode: device-resident number of code runs (<= N), see code_runs.cu
 };
 inline Dims dims_of(const cnrf_field_shape* s) {
@@ -50,14 +51,20 @@ inline Dims dims_of(const cnrf_field_shape* s) {
   d.H = s->hidden; d.C = s->code; d.dx = s->dim_xyz; d.dd = s->dim_dir; d.S = s->num_samples; d.pairing = s->pairing;
   d.N = s->num_rays; d.M = s->num_rays * (int64_t)s->num_samples;
   d.tc = s->precision == CNRF_PRECISION_BF16;
+  d.split = s->precision == CNRF_PRECISION_SPLIT;
   return d;
 }
+// CNRF_PRECISION_SPLIT runs the fp32 path (same saved layout, per-layer GEMMs with fp32 activations) with the per-sample
+// contractions on the tensor cores as split-bf16 (gemm_tc.cu; SIMT where the toolkit declines a shape); the per-ray code
+// layers (1 / S of the work) stay fp32 FMA
+inline int layout_of(const cnrf_field_shape* s) { return s->precision == CNRF_PRECISION_BF16 ? CNRF_PRECISION_BF16 : CNRF_PRECISION_FP32; }
+inline bool fp32_layout(const cnrf_field_shape* s) { return s->precision != CNRF_PRECISION_BF16; }
 inline int check_shape(const cnrf_field_shape* s) {
   if (!s) return CNRF_E_NULL;
   if (s->hidden <= 0 || s->code <= 0 || s->dim_xyz <= 0 || s->dim_dir <= 0 || s->num_rays <= 0 || s->num_samples <= 0)
     return CNRF_E_SHAPE;
   if (s->pairing != CNRF_PAIRING_REFERENCE && s->pairing != CNRF_PAIRING_CORRECT) return CNRF_E_SHAPE;
-  if (s->precision != CNRF_PRECISION_FP32 && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
+  if (s->precision != CNRF_PRECISION_FP32 && s->precision != CNRF_PRECISION_BF16 && s->precision != CNRF_PRECISION_SPLIT) return CNRF_E_UNSUPPORTED;
   return CNRF_OK;
 }
 
@@ -320,12 +327,12 @@ int chain_fwd_f32(const Dims& d, const cnrf_codenerf_params* p, const float* x_x
   const int64_t INF = INT64_MAX;
   int64_t pdiv, pmod;
   pair_index(d, pdiv, pmod);
-  RUN(lin(false, x_xyz, ld_xyz, d.M, d.dx, p->weight[CNRF_L_XYZ1], d.dx, H, s.h1, H, p->bias[CNRF_L_XYZ1], 0, 1, INF, 1, st)); // model.py:179
-  RUN(lin(false, s.h1, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, s.h2, H, t.b2, H, d.S, INF, 1, st));                        // :180-181
-  RUN(lin(false, s.h2, H, d.M, H, p->weight[CNRF_L_FC_OUT], H + C, C + 1, s.o, C + 1, t.bo, C + 1, d.S, INF, 0, st));           // :182-184
-  RUN(lin(false, s.o + 1, C + 1, d.M, C, p->weight[CNRF_L_DIR1], C + d.dd, H, s.v1, H, t.bd, H, pdiv, pmod, 1, st));            // :186-189
-  RUN(lin(false, s.v1, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, s.v2, H, p->bias[CNRF_L_DIR2], 0, 1, INF, 1, st));              // :190
-  RUN(lin(false, s.v2, H, d.M, H, p->weight[CNRF_L_FC_RGB], H + C, 3, raw, 4, t.br, 3, d.S, INF, 0, st));                       // :191-192
+  RUN(lin(d.split, x_xyz, ld_xyz, d.M, d.dx, p->weight[CNRF_L_XYZ1], d.dx, H, s.h1, H, p->bias[CNRF_L_XYZ1], 0, 1, INF, 1, st)); // model.py:179
+  RUN(lin(d.split, s.h1, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, s.h2, H, t.b2, H, d.S, INF, 1, st));                        // :180-181
+  RUN(lin(d.split, s.h2, H, d.M, H, p->weight[CNRF_L_FC_OUT], H + C, C + 1, s.o, C + 1, t.bo, C + 1, d.S, INF, 0, st));           // :182-184
+  RUN(lin(d.split, s.o + 1, C + 1, d.M, C, p->weight[CNRF_L_DIR1], C + d.dd, H, s.v1, H, t.bd, H, pdiv, pmod, 1, st));            // :186-189
+  RUN(lin(d.split, s.v1, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, s.v2, H, p->bias[CNRF_L_DIR2], 0, 1, INF, 1, st));              // :190
+  RUN(lin(d.split, s.v2, H, d.M, H, p->weight[CNRF_L_FC_RGB], H + C, 3, raw, 4, t.br, 3, d.S, INF, 0, st));                       // :191-192
   RUN(copy_col(s.o, C + 1, raw + 3, 4, d.M, st));                                                                       // :194  [rgb | sigma]
   return CNRF_OK;
 }
@@ -337,31 +344,31 @@ int chain_bwd_f32(const Dims& d, const cnrf_codenerf_params* p, const cnrf_coden
                   float* g_x_xyz, cudaStream_t st) {
   const int H = d.H, C = d.C;
   // fc_rgb
-  RUN(wgrad(false, g_raw, 4, s.v2, H, d.M, 3, H, g->weight[CNRF_L_FC_RGB], H + C, st));
+  RUN(wgrad(d.split, g_raw, 4, s.v2, H, d.M, 3, H, g->weight[CNRF_L_FC_RGB], H + C, st));
   RUN(cnrf_strided_rowsum(g_raw, 4, d.N, d.S, d.S, 1, 3, dt.br, 3, st));
-  RUN(dgrad(false, g_raw, 4, d.M, 3, p->weight[CNRF_L_FC_RGB], H + C, H, ga, H, s.v2, H, 0, st));
+  RUN(dgrad(d.split, g_raw, 4, d.M, 3, p->weight[CNRF_L_FC_RGB], H + C, H, ga, H, s.v2, H, 0, st));
   // layer_dir2
-  RUN(wgrad(false, ga, H, s.v1, H, d.M, H, H, g->weight[CNRF_L_DIR2], H, st));
+  RUN(wgrad(d.split, ga, H, s.v1, H, d.M, H, H, g->weight[CNRF_L_DIR2], H, st));
   RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_DIR2], st));
-  RUN(dgrad(false, ga, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, gb, H, s.v1, H, 0, st));
+  RUN(dgrad(d.split, ga, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, gb, H, s.v1, H, 0, st));
   // layer_dir1 (feature half)
-  RUN(wgrad(false, gb, H, s.o + 1, C + 1, d.M, H, C, g->weight[CNRF_L_DIR1], C + d.dd, st));
+  RUN(wgrad(d.split, gb, H, s.o + 1, C + 1, d.M, H, C, g->weight[CNRF_L_DIR1], C + d.dd, st));
   if (d.pairing == CNRF_PAIRING_REFERENCE) RUN(cnrf_strided_rowsum(gb, H, d.N, 1, d.S, d.N, H, dt.bd, H, st));
   else RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.bd, H, st));
-  RUN(dgrad(false, gb, H, d.M, H, p->weight[CNRF_L_DIR1], C + d.dd, C, ga + 1, C + 1, nullptr, 0, 0, st));
+  RUN(dgrad(d.split, gb, H, d.M, H, p->weight[CNRF_L_DIR1], C + d.dd, C, ga + 1, C + 1, nullptr, 0, 0, st));
   RUN(copy_col(g_raw + 3, 4, ga, C + 1, d.M, st));                       // d sigma_raw -> column 0 of d o
   // fc_out
-  RUN(wgrad(false, ga, C + 1, s.h2, H, d.M, C + 1, H, g->weight[CNRF_L_FC_OUT], H + C, st));
+  RUN(wgrad(d.split, ga, C + 1, s.h2, H, d.M, C + 1, H, g->weight[CNRF_L_FC_OUT], H + C, st));
   RUN(cnrf_strided_rowsum(ga, C + 1, d.N, d.S, d.S, 1, C + 1, dt.bo, C + 1, st));
-  RUN(dgrad(false, ga, C + 1, d.M, C + 1, p->weight[CNRF_L_FC_OUT], H + C, H, gb, H, s.h2, H, 0, st));
+  RUN(dgrad(d.split, ga, C + 1, d.M, C + 1, p->weight[CNRF_L_FC_OUT], H + C, H, gb, H, s.h2, H, 0, st));
   // layer_xyz2
-  RUN(wgrad(false, gb, H, s.h1, H, d.M, H, H, g->weight[CNRF_L_XYZ2], H + C, st));
+  RUN(wgrad(d.split, gb, H, s.h1, H, d.M, H, H, g->weight[CNRF_L_XYZ2], H + C, st));
   RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.b2, H, st));
-  RUN(dgrad(false, gb, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, ga, H, s.h1, H, 0, st));
+  RUN(dgrad(d.split, gb, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, ga, H, s.h1, H, 0, st));
   // layer_xyz1
-  RUN(wgrad(false, ga, H, x_xyz, ld_xyz, d.M, H, d.dx, g->weight[CNRF_L_XYZ1], d.dx, st));
+  RUN(wgrad(d.split, ga, H, x_xyz, ld_xyz, d.M, H, d.dx, g->weight[CNRF_L_XYZ1], d.dx, st));
   RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_XYZ1], st));
-  if (g_x_xyz) RUN(dgrad(false, ga, H, d.M, H, p->weight[CNRF_L_XYZ1], d.dx, d.dx, g_x_xyz, d.dx, nullptr, 0, 0, st));
+  if (g_x_xyz) RUN(dgrad(d.split, ga, H, d.M, H, p->weight[CNRF_L_XYZ1], d.dx, d.dx, g_x_xyz, d.dx, nullptr, 0, 0, st));
   return CNRF_OK;
 }
 
@@ -392,7 +399,7 @@ size_t cnrf_tc_workspace_bytes(int64_t N, int64_t M, int backward);
 extern "C" size_t cnrf_codenerf_saved_bytes(const cnrf_field_shape* s) {
   if (check_shape(s) != CNRF_OK || !s->keep) return 0;
   Dims d = dims_of(s);
-  if (s->precision == CNRF_PRECISION_FP32) return saved_f32_bytes(d);
+  if (fp32_layout(s)) return saved_f32_bytes(d);
   // (+ shared-code mode: the code runs and one code row per run, found once in the forward and reused by the backward)
   return 4 * al(d.N * d.C) + cnrf_code_runs_bytes(d.N) + 256 + 2 * al(d.N * d.C) + cnrf_tc_saved_bytes(d.M) + 2048;
 }
@@ -401,7 +408,7 @@ extern "C" size_t cnrf_codenerf_workspace_bytes(const cnrf_field_shape* s, int32
   if (check_shape(s) != CNRF_OK) return 0;
   Dims d = dims_of(s);
   size_t b = tables_bytes(d);
-  if (s->precision == CNRF_PRECISION_FP32) {
+  if (fp32_layout(s)) {
     if (!backward) return b + (s->keep ? 0 : saved_f32_bytes(d));     // inference still needs the activation buffers
     return b + 2 * al(d.M * max_sz(d.H, d.C + 1)) + 3 * al(d.N * d.C) + al(d.N);
   }
@@ -463,7 +470,7 @@ int codenerf_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   carve_tables(d, w, t);
   if (!w.ok) return CNRF_E_WORKSPACE;
   if (in.ids && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
-  if (s->precision == CNRF_PRECISION_FP32) {
+  if (fp32_layout(s)) {
     SavedF32 sv;
     if (s->keep) {
       if (!saved || !carve_saved(d, saved, saved_bytes, sv)) return CNRF_E_WORKSPACE;
@@ -513,7 +520,7 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   if (!w.ok) return CNRF_E_WORKSPACE;
   if (in.ids && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
   RUN(zero_weight_grads(d, g, st));
-  if (s->precision == CNRF_PRECISION_FP32) {
+  if (fp32_layout(s)) {
     SavedF32 sv;
     if (!carve_saved(d, const_cast<void*>(saved), saved_bytes, sv)) return CNRF_E_WORKSPACE;
     size_t wide = max_sz(d.H, d.C + 1);
@@ -651,7 +658,7 @@ int check_field(const cnrf_field_shape* s, int Lx, int Ld, int& incx, int& incd)
 
 extern "C" size_t cnrf_field_workspace_bytes(const cnrf_field_shape* s, int32_t backward) {
   if (check_shape(s) != CNRF_OK) return 0;
-  return field_scratch_bytes(dims_of(s), s->precision, backward) + cnrf_codenerf_workspace_bytes(s, backward);
+  return field_scratch_bytes(dims_of(s), layout_of(s), backward) + cnrf_codenerf_workspace_bytes(s, backward);
 }
 
 int cnrf_field_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
@@ -665,9 +672,9 @@ int cnrf_field_fwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p
   Dims d = dims_of(s);
   Arena w(workspace, workspace_bytes);
   FieldScratch f;
-  carve_field(d, s->precision, 0, w, f);
+  carve_field(d, layout_of(s), 0, w, f);
   if (!w.ok) return CNRF_E_WORKSPACE;
-  RUN(field_encode(d, s->precision, pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
+  RUN(field_encode(d, layout_of(s), pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
   FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx, ids, num_codes};
   return codenerf_fwd_impl(s, p, in, raw, saved, saved_bytes, w.base + w.off, w.cap - w.off, st);
 }
@@ -687,9 +694,9 @@ int cnrf_field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p
   Dims d = dims_of(s);
   Arena w(workspace, workspace_bytes);
   FieldScratch f;
-  carve_field(d, s->precision, 1, w, f);
+  carve_field(d, layout_of(s), 1, w, f);
   if (!w.ok) return CNRF_E_WORKSPACE;
-  RUN(field_encode(d, s->precision, pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
+  RUN(field_encode(d, layout_of(s), pts, rd, freqs_xyz, L_xyz, incx, freqs_dir, L_dir, incd, f, st));
   FieldIn in{f.xemb, d.dx, f.demb, d.dd, z_s, ld_zs, z_t, ld_zt, pts, freqs_xyz, L_xyz, incx, ids, num_codes};
   RUN(codenerf_bwd_impl(s, p, in, g_raw, saved, saved_bytes, g, g_z_s, g_z_t, g_pts ? f.g_xemb : nullptr,
                         g_rd ? f.g_demb : nullptr, w.base + w.off, w.cap - w.off, st, accumulate_tables));

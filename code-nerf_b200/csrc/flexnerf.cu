@@ -45,10 +45,10 @@ inline int dims_of(const cnrf_flex_shape* s, FDims& d) {
       s->dim_xyz <= 0 || s->dim_dir <= 0 || s->num_rays <= 0 || s->num_samples <= 0)
     return CNRF_E_SHAPE;
   if (s->pairing != CNRF_PAIRING_REFERENCE && s->pairing != CNRF_PAIRING_CORRECT) return CNRF_E_SHAPE;
-  if (s->precision != CNRF_PRECISION_FP32 && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
+  if (s->precision != CNRF_PRECISION_FP32 && s->precision != CNRF_PRECISION_BF16 && s->precision != CNRF_PRECISION_SPLIT) return CNRF_E_UNSUPPORTED;
   d.L = s->num_layers - 1; d.H = s->hidden; d.dx = s->dim_xyz; d.dd = s->dim_dir; d.S = s->num_samples;
   d.pairing = s->pairing; d.skip = s->skip_mask; d.N = s->num_rays; d.M = s->num_rays * (int64_t)s->num_samples;
-  d.tc = s->precision == CNRF_PRECISION_BF16;
+  d.tc = s->precision != CNRF_PRECISION_FP32;      // BF16 and SPLIT: per-layer split-bf16 tensor-core GEMMs
   return CNRF_OK;
 }
 

@@ -3,6 +3,7 @@
 // the reference uses to build its (H,W,3) table, rotated by the pose, and written straight to the packed (B*n,3)
 // output -- the full-image bundle and the advanced-index gather of the reference never exist in HBM.
 #include "common.cuh"
+#include "internal.h"
 
 __device__ __forceinline__ void camera_dir(int64_t flat, int W, float focal, float cx, float cy, float d[3]) {
   int h = (int)(flat / W), w = (int)(flat % W);        // flat = h*W + w (flatten(1,2), ray_sampler.py:69)
@@ -20,7 +21,9 @@ __global__ void __launch_bounds__(256) ray_bundle_fwd_kernel(const float* __rest
   __shared__ __align__(16) float s_rd[768];
   __shared__ __align__(16) float s_ro[768];
   const int64_t total = B * n;
-  const int64_t i0 = (int64_t)blockIdx.x * 256;
+  // grid-stride over tiles of 256 rays: a few thousand resident blocks write the whole bundle (a block per tile spent
+  // a measurable share of a 50 us, write-only kernel on block scheduling)
+  for (int64_t i0 = (int64_t)blockIdx.x * 256; i0 < total; i0 += (int64_t)gridDim.x * 256) {
   const int64_t i = i0 + threadIdx.x;
   const bool full = vec_ok && i0 + 256 <= total;
   float v[3] = {0.f, 0.f, 0.f}, o[3] = {0.f, 0.f, 0.f};
@@ -49,14 +52,16 @@ __global__ void __launch_bounds__(256) ray_bundle_fwd_kernel(const float* __rest
         if (ro) ro[i * 3 + j] = o[j];
       }
     }
-    return;
+    continue;                                              // block-uniform: `full` depends on i0 only
   }
 #pragma unroll
   for (int j = 0; j < 3; ++j) { s_rd[threadIdx.x * 3 + j] = v[j]; s_ro[threadIdx.x * 3 + j] = o[j]; }
   __syncthreads();
   if (threadIdx.x < 192) {
-    reinterpret_cast<float4*>(rd + i0 * 3)[threadIdx.x] = reinterpret_cast<const float4*>(s_rd)[threadIdx.x];
-    if (ro) reinterpret_cast<float4*>(ro + i0 * 3)[threadIdx.x] = reinterpret_cast<const float4*>(s_ro)[threadIdx.x];
+    __stcs(reinterpret_cast<float4*>(rd + i0 * 3) + threadIdx.x, reinterpret_cast<const float4*>(s_rd)[threadIdx.x]);
+    if (ro) __stcs(reinterpret_cast<float4*>(ro + i0 * 3) + threadIdx.x, reinterpret_cast<const float4*>(s_ro)[threadIdx.x]);
+  }
+  __syncthreads();                                         // the staging rows are rewritten by the next tile
   }
 }
 
@@ -106,8 +111,9 @@ extern "C" int cnrf_ray_bundle_fwd(const float* pose, int64_t B, int32_t H, int3
   CNRF_REQUIRE(B > 0 && H > 0 && W > 0 && n > 0 && n <= (int64_t)H * W, CNRF_E_SHAPE);
   CNRF_REQUIRE(select || n == (int64_t)H * W, CNRF_E_SHAPE);
   const int vec_ok = ((reinterpret_cast<uintptr_t>(rd) | reinterpret_cast<uintptr_t>(ro)) & 15) == 0;
-  ray_bundle_fwd_kernel<<<grid_for(B * n, 256), 256, 0, as_stream(stream)>>>(pose, B, H, W, focal, cx, cy, select, n,
-                                                                             ro, rd, vec_ok);
+  const unsigned tiles = grid_for(B * n, 256), cap = (unsigned)cnrf_sm_count() * 8u;      // 8 resident blocks of 256 per SM
+  ray_bundle_fwd_kernel<<<tiles < cap ? tiles : cap, 256, 0, as_stream(stream)>>>(pose, B, H, W, focal, cx, cy, select, n,
+                                                                                  ro, rd, vec_ok);
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }

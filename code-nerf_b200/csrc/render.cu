@@ -30,7 +30,7 @@ struct Cut {     // carve 256-byte aligned pieces out of a caller buffer
 };
 
 struct Dims { int64_t N; int Sc, Sf; bool f32; };
-inline Dims dims_of(const cnrf_render_shape* s) { return {s->num_rays, s->num_coarse, s->num_coarse + s->num_fine, s->precision == CNRF_PRECISION_FP32}; }
+inline Dims dims_of(const cnrf_render_shape* s) { return {s->num_rays, s->num_coarse, s->num_coarse + s->num_fine, s->precision != CNRF_PRECISION_BF16}; }
 
 inline cnrf_field_shape field_shape(const cnrf_render_shape* s, int S, int keep) {
   cnrf_field_shape f;

@@ -13,14 +13,15 @@ from .volumetric_render import volume_render
 from codenerf_b200 import _lib
 
 # ---- knobs the reference does not have -----------------------------------------------------------------------
-_PRECISIONS = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}
+_PRECISIONS = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16, "split": _lib.PRECISION_SPLIT}
 _PAIRINGS = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}
 _state = {"precision": os.environ.get("CODENERF_PRECISION", "bf16"),
           "pairing": os.environ.get("CODENERF_PAIRING", "reference")}
 
 
 def set_precision(name: str) -> None:
-    """"bf16": fused tcgen05 MLP (throughput mode, default).  "fp32": CUDA-core fp32 MLP (1e-3 parity mode)."""
+    """"bf16": fused tcgen05 MLP (throughput mode, default).  "fp32": CUDA-core fp32 MLP (1e-3 parity mode).
+    "split": the fp32 path with its contractions on the tensor cores as split-bf16 (~16 mantissa bits)."""
     assert name in _PRECISIONS, f"precision must be one of {sorted(_PRECISIONS)}"
     _state["precision"] = name
 

@@ -130,6 +130,10 @@ int cnrf_composite_bwd(const float* raw, const float* z, const float* rd, int64_
 
 #define CNRF_PRECISION_FP32 0 /* fp32 FMA on CUDA cores: the 1e-3 parity mode                                     */
 #define CNRF_PRECISION_BF16 1 /* tcgen05.mma kind::f16, bf16 operands / fp32 TMEM accumulators: the throughput mode */
+#define CNRF_PRECISION_SPLIT 2 /* the fp32 path (fp32 activations, same saved layout) with every contraction on the tensor
+                                 * cores as split-bf16: operands carried as hi + lo bf16 images, hi*hi + hi*lo + lo*hi in fp32
+                                 * TMEM (~16 mantissa bits).  Used for camera-pose optimisation (eval.py:129-168), where the
+                                 * ray / point gradients need better than bf16 and the fp32 FMA path is 7x slower */
 
 #define CNRF_PAIRING_REFERENCE 0 /* flat row k=n*S+s gets the view direction of ray k mod N (nerf/__init__.py:127) */
 #define CNRF_PAIRING_CORRECT 1   /* ... of its own ray k / S                                                               */
@@ -289,6 +293,20 @@ typedef struct {
 } cnrf_adamw_tensor;
 int cnrf_adamw_step(const cnrf_adamw_tensor* tensors, int32_t count, float beta1, float beta2, float eps,
                     cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
+ * Device-resident dataset stage (reference: view_synthesis/datasets/dataset.py:70-74,90 decode a
+ * PNG and compute image / 255.0 in float64 -> float32 on the host for every sample; train.py:77-80 gather the selected
+ * target pixels).  The views live in HBM as the uint8 crops the PNGs hold:
+ *   cnrf_u8_to_unit        out[i] = (float)((double)in[i] / 255.0), i < n      (bit-identical to the loader's arithmetic)
+ *   cnrf_gather_pixels_u8  out[(b R + r) C_out + c] = views[view[b]][select[b R + r]][c] / 255.0, c < out_channels
+ *                          (views: [n_views][hw][channels] bytes; select values outside [0, hw) set *bad (may be NULL)
+ *                          and leave their rows untouched).
+ * ---------------------------------------------------------------------------------------------------- */
+int cnrf_u8_to_unit(const uint8_t* in, int64_t n, float* out, cnrf_stream_t stream);
+int cnrf_gather_pixels_u8(const uint8_t* views, int64_t n_views, int64_t hw, int32_t channels, const int64_t* view,
+                          const int64_t* select, int64_t B, int64_t R, int32_t out_channels, float* out, int32_t* bad,
+                          cnrf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
  * Photometric loss of the training loop (train.py:103-104): with a = rgb_coarse, b = rgb_fine and
