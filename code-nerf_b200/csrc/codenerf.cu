@@ -211,39 +211,50 @@ GemmArgs mk_mm(const float* A, int64_t a_rs, int64_t a_cs, const float* B, int64
   return g;
 }
 
+// The per-ray layers as dependency LEVELS of mutually independent GEMMs: a caller adds one level of one model (or of both
+// models of a render call: the pair path below) to a Batch and flushes it as one launch.
 // bof (folded mode): the fc_out feature bias table betao' [N,C]; betaf = betao' Wdf^T follows from it, and the backward's
 // d Wdf needs it again
+constexpr int PER_RAY_FWD_LEVELS = 3;
+int per_ray_fwd_add(int level, const Dims& d, const cnrf_codenerf_params* p, const float* x_dir, int64_t ld_dir, const float* z_s,
+                    int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
+                    bool split_bo, float* bof, Batch& b) {
+  const int H = d.H, C = d.C;
+  if (level == 0) {
+    if (split_bo) {   // the fold Wfh = Wdf Wout'h as four K-slices (Wdf = layer_dir1[:, :C], Wout'h = fc_out[1:, :H]): slice j goes to
+      if (!bof || C % 4) return CNRF_E_NULL;      // its own [H x H] buffer (plain stores; pack_weights_kernel adds them in order)
+      for (int j = 0; j < 4; ++j) {
+        GemmArgs g = mk_mm(p->weight[CNRF_L_DIR1] + j * (C / 4), C + d.dd, 1, p->weight[CNRF_L_FC_OUT] + (int64_t)(1 + j * (C / 4)) * (H + C),
+                           H + C, 1, t.wf + (size_t)j * H * H, H, H, H, C / 4);
+        g.accumulate = 0; g.k_slice = 0;
+        b.add_fixed(g);
+      }
+    }
+    b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 1));     // model.py:174
+    b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 1));     // :175
+    b.add(mk_lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 1));  // :177
+    // the tensor-core chain applies the view-direction half of layer_dir1 as 32 extra input columns instead of a bias table
+    if (!d.tc) b.add(mk_lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0));
+  } else if (level == 1) {
+    b.add(mk_lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0));
+    if (split_bo) {   // tensor-core chain: betao' and the sigma column here, the folded layer_dir1 bias rows one level later
+      b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0));
+      b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0));
+    } else {
+      b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0));
+    }
+    b.add(mk_lin(at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0));
+  } else if (split_bo) {   // betaf = betao' Wdf^T
+    b.add(mk_lin(bof, C, d.N, C, p->weight[CNRF_L_DIR1], C + d.dd, H, t.bf, H, nullptr, 0));
+  }
+  return CNRF_OK;
+}
 int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir, int64_t ld_dir, const float* z_s,
                 int64_t ld_zs, const float* z_t, int64_t ld_zt, float* as1, float* as2, float* at, const Tables& t,
                 bool split_bo, cudaStream_t st, float* bof = nullptr) {
-  const int H = d.H, C = d.C;
   Batch b(d.rows_dev);
-  if (split_bo) {   // the fold Wfh = Wdf Wout'h as four K-slices (Wdf = layer_dir1[:, :C], Wout'h = fc_out[1:, :H]): slice j goes to
-    if (!bof || C % 4) return CNRF_E_NULL;      // its own [H x H] buffer (plain stores; pack_weights_kernel adds them in order)
-    for (int j = 0; j < 4; ++j) {
-      GemmArgs g = mk_mm(p->weight[CNRF_L_DIR1] + j * (C / 4), C + d.dd, 1, p->weight[CNRF_L_FC_OUT] + (int64_t)(1 + j * (C / 4)) * (H + C),
-                         H + C, 1, t.wf + (size_t)j * H * H, H, H, H, C / 4);
-      g.accumulate = 0; g.k_slice = 0;
-      b.add_fixed(g);
-    }
-  }
-  b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, as1, C, p->bias[CNRF_L_SHAPE1], 1));     // model.py:174
-  b.add(mk_lin(z_s, ld_zs, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, as2, C, p->bias[CNRF_L_SHAPE2], 1));     // :175
-  b.add(mk_lin(z_t, ld_zt, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, at, C, p->bias[CNRF_L_TEXTURE1], 1));  // :177
-  // the tensor-core chain applies the view-direction half of layer_dir1 as 32 extra input columns instead of a bias table
-  if (!d.tc) b.add(mk_lin(x_dir, ld_dir, d.N, d.dd, p->weight[CNRF_L_DIR1] + C, C + d.dd, H, t.bd, H, p->bias[CNRF_L_DIR1], 0));
-  RUN(b.flush(d.tc, st));
-  b.add(mk_lin(as1, C, d.N, C, p->weight[CNRF_L_XYZ2] + H, H + C, H, t.b2, H, p->bias[CNRF_L_XYZ2], 0));
-  if (split_bo) {   // tensor-core chain: betao' and the sigma column here, the folded layer_dir1 bias rows one level later
-    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + (H + C) + H, H + C, C, bof, C, p->bias[CNRF_L_FC_OUT] + 1, 0));
-    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, 1, t.bos, 1, p->bias[CNRF_L_FC_OUT], 0));
-  } else {
-    b.add(mk_lin(as2, C, d.N, C, p->weight[CNRF_L_FC_OUT] + H, H + C, C + 1, t.bo, C + 1, p->bias[CNRF_L_FC_OUT], 0));
-  }
-  b.add(mk_lin(at, C, d.N, C, p->weight[CNRF_L_FC_RGB] + H, H + C, 3, t.br, 3, p->bias[CNRF_L_FC_RGB], 0));
-  RUN(b.flush(d.tc, st));
-  if (split_bo) {   // betaf = betao' Wdf^T
-    b.add(mk_lin(bof, C, d.N, C, p->weight[CNRF_L_DIR1], C + d.dd, H, t.bf, H, nullptr, 0));
+  for (int level = 0; level < PER_RAY_FWD_LEVELS; ++level) {
+    RUN(per_ray_fwd_add(level, d, p, x_dir, ld_dir, z_s, ld_zs, z_t, ld_zt, as1, as2, at, t, split_bo, bof, b));
     RUN(b.flush(d.tc, st));
   }
   return CNRF_OK;
@@ -252,70 +263,93 @@ int per_ray_fwd(const Dims& d, const cnrf_codenerf_params* p, const float* x_dir
 // gradients of the bias tables -> code-layer weights, code halves of the split layers, z_s / z_t / x_dir.
 // tmp: 3 x [N,C] scratch + [N] (a ones vector for the bias-gradient column sums of the tensor-core mode).
 // bof (tensor-core mode): the forward's betao' table [N,C]; dt.bf / dt.dwfh then hold d betaf and d Wfh (see the fold
-// note at the top of the file) and dt.bo only its sigma column
-int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codenerf_grads* g, const float* x_dir,
-                int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* as1,
-                const float* as2, const float* at, const Tables& dt, float* tmp, float* g_z_s, float* g_z_t,
-                float* g_x_dir, cudaStream_t st, const float* bof = nullptr) {
+// note at the top of the file) and dt.bo only its sigma column.
+// Levels: 0 (tensor-core mode only) the unfold products; 1 the bias tables' layers; 2 the three latent-code layers.
+// The tensor-core mode adds both shape branches into g_z_s atomically: the caller zero-fills g_z_s and sets the ones
+// vector (per_ray_bwd_fills) before level 0; the fp32 mode finishes with column-sum launches (per_ray_bwd_colsums).
+// acc_codes: g_z_s / g_z_t already hold another model's code gradients (pair path): add to them
+constexpr int PER_RAY_BWD_LEVELS = 3;
+inline float* per_ray_ones(const Dims& d, float* tmp) { return tmp + 3 * (al(d.N * d.C) / sizeof(float)); }
+int per_ray_bwd_add(int level, const Dims& d, const cnrf_codenerf_params* p, const cnrf_codenerf_grads* g, const float* x_dir,
+                    int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* as1,
+                    const float* as2, const float* at, const Tables& dt, float* tmp, float* g_z_s, float* g_z_t,
+                    float* g_x_dir, const float* bof, bool acc_codes, Batch& b) {
   const int H = d.H, C = d.C;
   const size_t nc = al(d.N * C) / sizeof(float);
   float *tmp_t = tmp, *tmp_s2 = tmp + nc, *tmp_s1 = tmp + 2 * nc, *ones = tmp + 3 * nc;
-  if (d.tc) {       // bias gradients were zero-filled with the weights (zero_weight_grads)
-    FillBatch f;
-    f.add(g_z_s, d.N * C);
-    f.add(ones, d.N, 1.0f);
-    RUN(cnrf_fill_batch(f, st));
+  if (level == 0) {
+    if (d.tc) {     // unfold:  d Wdf = d Wfh Wout'h^T (+ d betaf^T betao' below),  d Wout'h = Wdf^T d Wfh,  d betao' = d betaf Wdf
+      if (!bof) return CNRF_E_NULL;
+      b.add_fixed(mk_mm(dt.dwfh, H, 1, p->weight[CNRF_L_FC_OUT] + (H + C), 1, H + C, g->weight[CNRF_L_DIR1], C + d.dd, H, C, H));
+      b.add_fixed(mk_mm(p->weight[CNRF_L_DIR1], 1, C + d.dd, dt.dwfh, H, 1, g->weight[CNRF_L_FC_OUT] + (H + C), H + C, C, H, H));
+      b.add(mk_dgrad(dt.bf, H, d.N, H, p->weight[CNRF_L_DIR1], C + d.dd, C, dt.bo + 1, C + 1, nullptr, 0, 0));
+    }
+  } else if (level == 1) {
+    if (d.tc) b.add(mk_wgrad(dt.bf, H, bof, C, d.N, H, C, g->weight[CNRF_L_DIR1], C + d.dd));     // += onto the product above
+    // texture branch: betar = Wrt at + br;   shape branch 2: betao = Woc as2 + bo;   shape branch 1: beta2 = W2c as1 + b2;
+    // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
+    b.add(mk_wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C));
+    b.add(mk_dgrad(dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp_t, C, at, C, 0));
+    b.add(mk_wgrad(dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C));
+    b.add(mk_dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp_s2, C, as2, C, 0));
+    b.add(mk_wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C));
+    b.add(mk_dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp_s1, C, as1, C, 0));
+    if (d.rows_dev && g_x_dir) return CNRF_E_UNSUPPORTED;   // shared-code rays carry no pose gradient
+    if (!d.tc) b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
+    if (g_x_dir) b.add(mk_dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0));
+    if (d.tc) {
+      b.add(mk_colsum(ones, dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB]));
+      b.add(mk_colsum(ones, dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT]));
+      b.add(mk_colsum(ones, dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2]));
+    }
+  } else {
+    // the three latent-code layers
+    b.add(mk_wgrad(tmp_t, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C));
+    b.add(mk_dgrad(tmp_t, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, acc_codes ? 1 : 0));
+    b.add(mk_wgrad(tmp_s2, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C));
+    b.add(mk_wgrad(tmp_s1, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C));
+    // both shape branches land in g_z_s: added atomically onto the zero-filled buffer when they share a launch
+    b.add(mk_dgrad(tmp_s2, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, d.tc ? 1 : 0));
+    b.add(mk_dgrad(tmp_s1, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1));
+    if (d.tc) {
+      b.add(mk_colsum(ones, tmp_t, C, d.N, C, g->bias[CNRF_L_TEXTURE1]));
+      b.add(mk_colsum(ones, tmp_s2, C, d.N, C, g->bias[CNRF_L_SHAPE2]));
+      b.add(mk_colsum(ones, tmp_s1, C, d.N, C, g->bias[CNRF_L_SHAPE1]));
+    }
   }
-  Batch b(d.rows_dev);
-  if (d.tc) {       // unfold:  d Wdf = d Wfh Wout'h^T (+ d betaf^T betao' below),  d Wout'h = Wdf^T d Wfh,  d betao' = d betaf Wdf
-    if (!bof) return CNRF_E_NULL;
-    b.add_fixed(mk_mm(dt.dwfh, H, 1, p->weight[CNRF_L_FC_OUT] + (H + C), 1, H + C, g->weight[CNRF_L_DIR1], C + d.dd, H, C, H));
-    b.add_fixed(mk_mm(p->weight[CNRF_L_DIR1], 1, C + d.dd, dt.dwfh, H, 1, g->weight[CNRF_L_FC_OUT] + (H + C), H + C, C, H, H));
-    b.add(mk_dgrad(dt.bf, H, d.N, H, p->weight[CNRF_L_DIR1], C + d.dd, C, dt.bo + 1, C + 1, nullptr, 0, 0));
-    RUN(b.flush(true, st));
-    b.add(mk_wgrad(dt.bf, H, bof, C, d.N, H, C, g->weight[CNRF_L_DIR1], C + d.dd));     // += onto the product above
-  }
-  // texture branch: betar = Wrt at + br;   shape branch 2: betao = Woc as2 + bo;   shape branch 1: beta2 = W2c as1 + b2;
-  // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
-  b.add(mk_wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C));
-  b.add(mk_dgrad(dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp_t, C, at, C, 0));
-  b.add(mk_wgrad(dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C));
-  b.add(mk_dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp_s2, C, as2, C, 0));
-  b.add(mk_wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C));
-  b.add(mk_dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp_s1, C, as1, C, 0));
-  if (d.rows_dev && g_x_dir) return CNRF_E_UNSUPPORTED;   // shared-code rays carry no pose gradient
-  if (!d.tc) b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
-  if (g_x_dir) b.add(mk_dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0));
-  if (d.tc) {
-    b.add(mk_colsum(ones, dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB]));
-    b.add(mk_colsum(ones, dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT]));
-    b.add(mk_colsum(ones, dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2]));
-  }
-  RUN(b.flush(d.tc, st));
-  if (!d.tc) {
+  return CNRF_OK;
+}
+int per_ray_bwd_colsums(int level, const Dims& d, const cnrf_codenerf_grads* g, const Tables& dt, const float* tmp, cudaStream_t st) {
+  const int H = d.H, C = d.C;
+  const size_t nc = al(d.N * C) / sizeof(float);
+  if (level == 1) {
     RUN(cnrf_colsum(dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB], st));
     RUN(cnrf_colsum(dt.bo, C + 1, d.N, C + 1, g->bias[CNRF_L_FC_OUT], st));
     RUN(cnrf_colsum(dt.b2, H, d.N, H, g->bias[CNRF_L_XYZ2], st));
     RUN(cnrf_colsum(dt.bd, H, d.N, H, g->bias[CNRF_L_DIR1], st));
+  } else if (level == 2) {
+    RUN(cnrf_colsum(tmp, C, d.N, C, g->bias[CNRF_L_TEXTURE1], st));
+    RUN(cnrf_colsum(tmp + nc, C, d.N, C, g->bias[CNRF_L_SHAPE2], st));
+    RUN(cnrf_colsum(tmp + 2 * nc, C, d.N, C, g->bias[CNRF_L_SHAPE1], st));
   }
-  // the three latent-code layers
-  b.add(mk_wgrad(tmp_t, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C));
-  b.add(mk_dgrad(tmp_t, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, 0));
-  b.add(mk_wgrad(tmp_s2, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C));
-  b.add(mk_wgrad(tmp_s1, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C));
-  // both shape branches land in g_z_s: added atomically onto the zero-filled buffer when they share a launch
-  b.add(mk_dgrad(tmp_s2, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, d.tc ? 1 : 0));
-  b.add(mk_dgrad(tmp_s1, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1));
-  if (d.tc) {
-    b.add(mk_colsum(ones, tmp_t, C, d.N, C, g->bias[CNRF_L_TEXTURE1]));
-    b.add(mk_colsum(ones, tmp_s2, C, d.N, C, g->bias[CNRF_L_SHAPE2]));
-    b.add(mk_colsum(ones, tmp_s1, C, d.N, C, g->bias[CNRF_L_SHAPE1]));
+  return CNRF_OK;
+}
+int per_ray_bwd(const Dims& d, const cnrf_codenerf_params* p, const cnrf_codenerf_grads* g, const float* x_dir,
+                int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* as1,
+                const float* as2, const float* at, const Tables& dt, float* tmp, float* g_z_s, float* g_z_t,
+                float* g_x_dir, cudaStream_t st, const float* bof = nullptr) {
+  if (d.tc) {       // bias gradients were zero-filled with the weights (zero_weight_grads)
+    FillBatch f;
+    f.add(g_z_s, d.N * d.C);
+    f.add(per_ray_ones(d, tmp), d.N, 1.0f);
+    RUN(cnrf_fill_batch(f, st));
   }
-  RUN(b.flush(d.tc, st));
-  if (!d.tc) {
-    RUN(cnrf_colsum(tmp_t, C, d.N, C, g->bias[CNRF_L_TEXTURE1], st));
-    RUN(cnrf_colsum(tmp_s2, C, d.N, C, g->bias[CNRF_L_SHAPE2], st));
-    RUN(cnrf_colsum(tmp_s1, C, d.N, C, g->bias[CNRF_L_SHAPE1], st));
+  Batch b(d.rows_dev);
+  for (int level = 0; level < PER_RAY_BWD_LEVELS; ++level) {
+    RUN(per_ray_bwd_add(level, d, p, g, x_dir, ld_dir, z_s, ld_zs, z_t, ld_zt, as1, as2, at, dt, tmp, g_z_s, g_z_t, g_x_dir, bof,
+                        false, b));
+    RUN(b.flush(d.tc, st));
+    if (!d.tc) RUN(per_ray_bwd_colsums(level, d, g, dt, tmp, st));
   }
   return CNRF_OK;
 }
@@ -372,19 +406,23 @@ int chain_bwd_f32(const Dims& d, const cnrf_codenerf_params* p, const cnrf_coden
   return CNRF_OK;
 }
 
-int zero_weight_grads(const Dims& d, const cnrf_codenerf_grads* g, cudaStream_t st) {
+int add_weight_grad_fills(const Dims& d, const cnrf_codenerf_grads* g, FillBatch& f) {
   const int H = d.H, C = d.C;
   const size_t n[CNRF_NUM_LAYERS] = {(size_t)H * d.dx, (size_t)H * (H + C), (size_t)(C + 1) * (H + C), (size_t)C * C,
                                      (size_t)C * C, (size_t)C * C, (size_t)H * (C + d.dd), (size_t)H * H,
                                      (size_t)3 * (H + C)};
   const size_t nb[CNRF_NUM_LAYERS] = {(size_t)H, (size_t)H, (size_t)C + 1, (size_t)C, (size_t)C, (size_t)C, (size_t)H,
                                       (size_t)H, 3};
-  FillBatch f;
   for (int l = 0; l < CNRF_NUM_LAYERS; ++l) {
     if (!g->weight[l] || !g->bias[l]) return CNRF_E_NULL;
     f.add(g->weight[l], (int64_t)n[l]);
     f.add(g->bias[l], (int64_t)nb[l]);
   }
+  return CNRF_OK;
+}
+int zero_weight_grads(const Dims& d, const cnrf_codenerf_grads* g, cudaStream_t st) {
+  FillBatch f;
+  RUN(add_weight_grad_fills(d, g, f));
   return cnrf_fill_batch(f, st);
 }
 
@@ -426,7 +464,13 @@ struct TcChainArgs {
   const float* wf;                            // the four K-slices [4][256 x 256] of this call's fold Wfh = Wdf Wout'h
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
   const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
+  uint8_t* packed = nullptr;                  // != NULL: the weight images were packed there already (cnrf_tc_pack_pair)
+  bool prezeroed = false;                     // backward: the caller zero-filled every accumulation target
 };
+uint8_t* cnrf_tc_packed_in_saved(void* saved, int64_t M);
+size_t cnrf_tc_packed_bytes();
+int cnrf_tc_pack_pair(const cnrf_codenerf_params* p0, const float* wf0, uint8_t* at0, const cnrf_codenerf_params* p1,
+                      const float* wf1, uint8_t* at1, int dx, int dd, cudaStream_t st);
 int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t saved_bytes, void* ws, size_t ws_bytes,
                       cudaStream_t st);
 int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* saved, size_t saved_bytes,
@@ -752,4 +796,229 @@ extern "C" int cnrf_field_bwd_ids(const cnrf_field_shape* s, const cnrf_codenerf
   return cnrf_field_bwd_impl(s, p, pts, rd, freqs_xyz, L_xyz, freqs_dir, L_dir, ids, num_codes, tab_s, ld_s, tab_t, ld_t, g_raw,
                              saved, saved_bytes, g, g_tab_s, g_tab_t, nullptr, nullptr, workspace, workspace_bytes,
                              as_stream(stream), false);
+}
+
+
+// ---- both models of one render call (tensor-core mode): see internal.h --------------------------------------------------
+namespace {
+
+struct PairModel { float *as1, *as2, *at, *bof; char* tc_saved; size_t tc_saved_bytes; };
+struct PairCommon { CodeRuns runs; float *zc_s, *zc_t; };
+
+// the layout codenerf_fwd_impl gives a model's saved buffer (tensor-core mode): as1, as2, at, betao', [runs, one code row
+// per run x 2], then the chain's own saved images
+bool carve_pair_acts(const Dims& d, bool ids, Arena& a, PairModel& m, PairCommon* c) {
+  m.as1 = a.take(d.N * d.C); m.as2 = a.take(d.N * d.C); m.at = a.take(d.N * d.C); m.bof = a.take(d.N * d.C);
+  if (ids) {
+    float* rbase = a.take(cnrf_code_runs_bytes(d.N) / sizeof(float));
+    float* zs = a.take(d.N * d.C); float* zt = a.take(d.N * d.C);
+    if (a.ok && c) { c->runs = cnrf_code_runs_carve(rbase, d.N); c->zc_s = zs; c->zc_t = zt; }
+  }
+  m.tc_saved = a.base + a.off; m.tc_saved_bytes = a.cap - a.off;
+  return a.ok;
+}
+
+struct PairFwd {           // everything cnrf_pair_fwd_* derive from (in, side)
+  Dims d[2]; Tables t[2]; PairModel m[2]; PairCommon c; float *dirn, *demb; uint8_t* packed[2]; bool ids, keep;
+};
+inline size_t up1k_sz(size_t b) { return (b + 1023) & ~size_t(1023); }
+size_t pair_fwd_side_bytes(const Dims& d, bool keep) {
+  size_t b = al(d.N * 3) + al(d.N * d.dd) + 2 * tables_bytes(d);
+  if (!keep) b += 2 * 4 * al(d.N * d.C) + cnrf_code_runs_bytes(d.N) + 256 + 2 * al(d.N * d.C) + 2 * up1k_sz(cnrf_tc_packed_bytes()) + 2048;
+  return b + 1024;
+}
+int carve_pair_fwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairFwd& f) {
+  f.ids = in.ids != nullptr; f.keep = in.shape[0]->keep != 0;
+  for (int i = 0; i < 2; ++i) f.d[i] = dims_of(in.shape[i]);
+  Arena a(side, side_bytes);
+  f.dirn = a.take(f.d[0].N * 3); f.demb = a.take(f.d[0].N * f.d[0].dd);
+  for (int i = 0; i < 2; ++i) carve_tables(f.d[i], a, f.t[i]);
+  if (!a.ok) return CNRF_E_WORKSPACE;
+  if (f.keep) {
+    for (int i = 0; i < 2; ++i) {
+      if (!in.saved[i]) return CNRF_E_WORKSPACE;
+      Arena sa(in.saved[i], in.saved_bytes[i]);
+      if (!carve_pair_acts(f.d[i], f.ids, sa, f.m[i], i == 0 ? &f.c : nullptr)) return CNRF_E_WORKSPACE;   // the runs live with the coarse model
+      f.packed[i] = cnrf_tc_packed_in_saved(f.m[i].tc_saved, f.d[i].M);
+    }
+  } else {
+    for (int i = 0; i < 2; ++i) {
+      f.m[i].as1 = a.take(f.d[i].N * f.d[i].C); f.m[i].as2 = a.take(f.d[i].N * f.d[i].C);
+      f.m[i].at = a.take(f.d[i].N * f.d[i].C); f.m[i].bof = a.take(f.d[i].N * f.d[i].C);
+      f.m[i].tc_saved = nullptr; f.m[i].tc_saved_bytes = 0;
+    }
+    if (f.ids) {
+      float* rbase = a.take(cnrf_code_runs_bytes(f.d[0].N) / sizeof(float));
+      f.c.zc_s = a.take(f.d[0].N * f.d[0].C); f.c.zc_t = a.take(f.d[0].N * f.d[0].C);
+      if (!a.ok) return CNRF_E_WORKSPACE;
+      f.c.runs = cnrf_code_runs_carve(rbase, f.d[0].N);
+    }
+    for (int i = 0; i < 2; ++i) {
+      const size_t at = up1k_sz(reinterpret_cast<size_t>(a.base + a.off));
+      f.packed[i] = reinterpret_cast<uint8_t*>(at);
+      a.off = (at - reinterpret_cast<size_t>(a.base)) + up1k_sz(cnrf_tc_packed_bytes());
+      if (a.off > a.cap) return CNRF_E_WORKSPACE;
+    }
+  }
+  if (!a.ok) return CNRF_E_WORKSPACE;
+  if (f.ids) f.d[0].rows_dev = f.d[1].rows_dev = f.c.runs.count;
+  return CNRF_OK;
+}
+
+struct PairBwd { Dims d[2]; Tables dt[2]; float* tmp[2]; PairModel m[2]; PairCommon c; float *gz_s, *gz_t; bool ids; };
+size_t pair_bwd_side_bytes(const Dims& d) {
+  return 2 * (tables_bytes(d) + 3 * al(d.N * d.C) + al(d.N)) + 2 * al(d.N * d.C) + 1024;
+}
+int carve_pair_bwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairBwd& f) {
+  f.ids = in.ids != nullptr;
+  Arena a(side, side_bytes);
+  for (int i = 0; i < 2; ++i) {
+    f.d[i] = dims_of(in.shape[i]);
+    carve_tables(f.d[i], a, f.dt[i]);
+    f.tmp[i] = a.take(f.d[i].N * f.d[i].C); a.take(f.d[i].N * f.d[i].C); a.take(f.d[i].N * f.d[i].C); a.take(f.d[i].N);
+    if (!in.saved[i]) return CNRF_E_WORKSPACE;
+    Arena sa(in.saved[i], in.saved_bytes[i]);
+    if (!carve_pair_acts(f.d[i], f.ids, sa, f.m[i], i == 0 ? &f.c : nullptr)) return CNRF_E_WORKSPACE;
+  }
+  f.gz_s = a.take(f.d[0].N * f.d[0].C); f.gz_t = a.take(f.d[0].N * f.d[0].C);
+  if (!a.ok) return CNRF_E_WORKSPACE;
+  if (f.ids) f.d[0].rows_dev = f.d[1].rows_dev = f.c.runs.count;
+  return CNRF_OK;
+}
+
+int check_pair(const CnrfPairIn& in, int& incx, int& incd) {
+  for (int i = 0; i < 2; ++i) RUN(check_common(in.shape[i], in.params[i]));
+  if (!cnrf_pair_eligible(in.shape[0], in.shape[1])) return CNRF_E_UNSUPPORTED;
+  CNRF_REQUIRE(in.rd && in.freqs_xyz && in.freqs_dir && in.z_s && in.z_t, CNRF_E_NULL);
+  if (in.ids && in.num_codes <= 0) return CNRF_E_SHAPE;
+  return check_field(in.shape[0], in.L_xyz, in.L_dir, incx, incd);
+}
+
+}  // namespace
+
+bool cnrf_pair_eligible(const cnrf_field_shape* c, const cnrf_field_shape* f) {
+  if (check_shape(c) != CNRF_OK || check_shape(f) != CNRF_OK) return false;
+  if (c->precision != CNRF_PRECISION_BF16 || f->precision != CNRF_PRECISION_BF16) return false;
+  if (c->hidden != 256 || c->code != 256 || c->dim_xyz > 63 || c->dim_dir > 31) return false;
+  return c->hidden == f->hidden && c->code == f->code && c->dim_xyz == f->dim_xyz && c->dim_dir == f->dim_dir &&
+         c->num_rays == f->num_rays && c->pairing == f->pairing && c->keep == f->keep;
+}
+
+size_t cnrf_pair_side_bytes(const cnrf_field_shape* coarse, int32_t backward) {
+  if (check_shape(coarse) != CNRF_OK) return 0;
+  const Dims d = dims_of(coarse);
+  return backward ? pair_bwd_side_bytes(d) : pair_fwd_side_bytes(d, coarse->keep != 0);
+}
+
+int cnrf_pair_fwd_prepare(const CnrfPairIn& in, void* side, size_t side_bytes, cudaStream_t st) {
+  int incx, incd;
+  RUN(check_pair(in, incx, incd));
+  PairFwd f;
+  RUN(carve_pair_fwd(in, side, side_bytes, f));
+  const Dims& d = f.d[0];
+  // viewdirs = rd / ||rd|| and their encoding: the same rays serve both passes                nerf/__init__.py:126-129
+  normalize_dirs_kernel<<<grid_for(d.N, 256), 256, 0, st>>>(in.rd, d.N, f.dirn);
+  CNRF_LAUNCH_CHECK();
+  RUN(cnrf_pos_embed_fwd_ld(f.dirn, d.N, 3, in.freqs_dir, in.L_dir, incd, d.dd, f.demb, st));
+  const float *zs = in.z_s, *zt = in.z_t;
+  int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
+  if (f.ids) {     // both models read the same two embedding tables through the same ids: one run scan, one row per run
+    RUN(cnrf_code_runs(in.ids, d.N, in.num_codes, f.c.runs, st));
+    RUN(cnrf_gather_codes(in.ids, f.c.runs, d.N, d.C, in.z_s, in.ld_zs, f.c.zc_s, st));
+    RUN(cnrf_gather_codes(in.ids, f.c.runs, d.N, d.C, in.z_t, in.ld_zt, f.c.zc_t, st));
+    zs = f.c.zc_s; zt = f.c.zc_t; ld_zs = ld_zt = d.C;
+  }
+  Batch b(d.rows_dev);
+  for (int level = 0; level < PER_RAY_FWD_LEVELS; ++level) {
+    for (int i = 0; i < 2; ++i)
+      RUN(per_ray_fwd_add(level, f.d[i], in.params[i], f.demb, d.dd, zs, ld_zs, zt, ld_zt, f.m[i].as1, f.m[i].as2, f.m[i].at, f.t[i],
+                          true, f.m[i].bof, b));
+    RUN(b.flush(true, st));
+  }
+  return cnrf_tc_pack_pair(in.params[0], f.t[0].wf, f.packed[0], in.params[1], f.t[1].wf, f.packed[1], d.dx, d.dd, st);
+}
+
+int cnrf_pair_fwd_chain(const CnrfPairIn& in, int which, const float* pts, float* raw, void* side, size_t side_bytes, void* ws,
+                        size_t ws_bytes, cudaStream_t st) {
+  int incx, incd;
+  RUN(check_pair(in, incx, incd));
+  CNRF_REQUIRE(pts && raw && ws && (which == 0 || which == 1), CNRF_E_NULL);
+  PairFwd f;
+  RUN(carve_pair_fwd(in, side, side_bytes, f));
+  const Dims& d = f.d[which];
+  const Tables& t = f.t[which];
+  TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, in.params[which], nullptr, d.dx, pts, in.freqs_xyz, in.L_xyz, incx,
+                t.b2, t.bf, t.bos, t.br, t.wf, f.demb, d.dd, f.ids ? f.c.runs.gid : nullptr};
+  a.packed = f.packed[which];
+  return cnrf_tc_chain_fwd(a, raw, f.m[which].tc_saved, f.m[which].tc_saved_bytes, ws, ws_bytes, st);
+}
+
+int cnrf_pair_bwd_prepare(const CnrfPairIn& in, const cnrf_codenerf_grads* const g[2], void* side, size_t side_bytes, cudaStream_t st) {
+  int incx, incd;
+  RUN(check_pair(in, incx, incd));
+  CNRF_REQUIRE(g && g[0] && g[1], CNRF_E_NULL);
+  PairBwd f;
+  RUN(carve_pair_bwd(in, side, side_bytes, f));
+  // every accumulation target of the pass, both models, one launch: parameter gradients (the weight-gradient kernel and the
+  // split-K per-ray GEMMs add into them), the gradient tables the weight-gradient kernel's reducers add into, the ones vectors
+  FillBatch fb;
+  for (int i = 0; i < 2; ++i) {
+    const Dims& d = f.d[i];
+    RUN(add_weight_grad_fills(d, g[i], fb));
+    fb.add(f.dt[i].b2, d.N * d.H); fb.add(f.dt[i].bo, d.N * (d.C + 1)); fb.add(f.dt[i].br, d.N * 3);
+    fb.add(f.dt[i].bf, d.N * d.H); fb.add(f.dt[i].dwfh, (int64_t)d.H * d.H);
+    fb.add(per_ray_ones(d, f.tmp[i]), d.N, 1.0f);
+  }
+  fb.add(f.gz_s, f.d[0].N * f.d[0].C); fb.add(f.gz_t, f.d[0].N * f.d[0].C);
+  return cnrf_fill_batch(fb, st);
+}
+
+int cnrf_pair_bwd_chain(const CnrfPairIn& in, int which, const float* g_raw, const cnrf_codenerf_grads* g, void* side,
+                        size_t side_bytes, void* ws, size_t ws_bytes, cudaStream_t st) {
+  int incx, incd;
+  RUN(check_pair(in, incx, incd));
+  CNRF_REQUIRE(g_raw && g && ws && (which == 0 || which == 1), CNRF_E_NULL);
+  PairBwd f;
+  RUN(carve_pair_bwd(in, side, side_bytes, f));
+  const Dims& d = f.d[which];
+  const Tables& dt = f.dt[which];
+  TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, in.params[which], nullptr, d.dx, nullptr, in.freqs_xyz, in.L_xyz, incx,
+                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, d.dd, f.ids ? f.c.runs.gid : nullptr};
+  a.prezeroed = true;
+  return cnrf_tc_chain_bwd(a, g_raw, f.m[which].tc_saved, f.m[which].tc_saved_bytes, g, dt.b2, dt.bo, dt.br, nullptr, dt.bf, dt.dwfh,
+                           nullptr, ws, ws_bytes, st);
+}
+
+int cnrf_pair_bwd_finish(const CnrfPairIn& in, const cnrf_codenerf_grads* const g[2], float* g_z_s, float* g_z_t, void* side,
+                         size_t side_bytes, cudaStream_t st) {
+  int incx, incd;
+  RUN(check_pair(in, incx, incd));
+  CNRF_REQUIRE(g && g[0] && g[1] && g_z_s && g_z_t, CNRF_E_NULL);
+  PairBwd f;
+  RUN(carve_pair_bwd(in, side, side_bytes, f));
+  const Dims& d = f.d[0];
+  const float *zs = in.z_s, *zt = in.z_t;
+  int64_t ld_zs = in.ld_zs, ld_zt = in.ld_zt;
+  float *gz_s = g_z_s, *gz_t = g_z_t;      // per-ray codes: both models add straight into the caller's [N, C] gradients
+  FillBatch fb;
+  if (f.ids) {     // one gradient row per run (zero-filled by the prepare step), scattered into the dense tables at the end
+    zs = f.c.zc_s; zt = f.c.zc_t; ld_zs = ld_zt = d.C;
+    gz_s = f.gz_s; gz_t = f.gz_t;
+    fb.add(g_z_s, in.num_codes * d.C); fb.add(g_z_t, in.num_codes * d.C);
+  } else {
+    fb.add(g_z_s, d.N * d.C); fb.add(g_z_t, d.N * d.C);
+  }
+  RUN(cnrf_fill_batch(fb, st));
+  Batch b(d.rows_dev);
+  for (int level = 0; level < PER_RAY_BWD_LEVELS; ++level) {
+    for (int i = 0; i < 2; ++i)
+      RUN(per_ray_bwd_add(level, f.d[i], in.params[i], g[i], nullptr, d.dd, zs, ld_zs, zt, ld_zt, f.m[i].as1, f.m[i].as2, f.m[i].at,
+                          f.dt[i], f.tmp[i], gz_s, gz_t, nullptr, f.m[i].bof, true, b));
+    RUN(b.flush(true, st));
+  }
+  if (f.ids) {
+    RUN(cnrf_scatter_code_grads(in.ids, f.c.runs, d.N, d.C, gz_s, g_z_s, d.C, st));
+    RUN(cnrf_scatter_code_grads(in.ids, f.c.runs, d.N, d.C, gz_t, g_z_t, d.C, st));
+  }
+  return CNRF_OK;
 }

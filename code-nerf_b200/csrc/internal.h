@@ -70,10 +70,10 @@ int cnrf_sgemm(const GemmArgs& a, cudaStream_t st);
 // stride of an operand is 1 or K > 320 without split-K permission -- the caller then uses cnrf_sgemm.
 int cnrf_gemm_tc(const GemmArgs& a, cudaStream_t st);
 // up to CNRF_GEMM_BATCH_MAX mutually independent problems in one launch
-constexpr int CNRF_GEMM_BATCH_MAX = 16;
+constexpr int CNRF_GEMM_BATCH_MAX = 24;     // (a 4.9 KB kernel parameter: CUDA >= 12.1 passes up to 32 KB)
 int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st);
 // one launch: dst[i][0..n[i]) = value[i]  (zero-filling gradient buffers, ones vectors)
-constexpr int CNRF_FILL_BATCH_MAX = 24;
+constexpr int CNRF_FILL_BATCH_MAX = 64;
 struct FillBatch { float* dst[CNRF_FILL_BATCH_MAX]; int64_t n[CNRF_FILL_BATCH_MAX]; float value[CNRF_FILL_BATCH_MAX]; int count = 0;
   void add(float* p, int64_t cnt, float v = 0.f) { dst[count] = p; n[count] = cnt; value[count] = v; ++count; } };
 int cnrf_fill_batch(const FillBatch& b, cudaStream_t st);
@@ -96,6 +96,33 @@ int cnrf_field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p
                         const float* g_raw, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g, float* g_z_s,
                         float* g_z_t, float* g_pts, float* g_rd, void* workspace, size_t workspace_bytes, cudaStream_t st,
                         bool accumulate_tables);
+
+// ---- codenerf.cu: both models of one render call (tensor-core mode) -- the fused entry of render.cu ------------------------
+// The per-ray work of the coarse and the fine model (code runs, code rows, the three levels of code-layer GEMMs, the fc_out
+// folds, weight packing, direction encoding; in the backward the zero fills, the unfold / code-layer gradient GEMMs and
+// the scatter into the embedding tables) does not depend on the samples, so one set of launches serves both models:
+//   forward   cnrf_pair_fwd_prepare -> cnrf_pair_fwd_chain(0) ... cnrf_pair_fwd_chain(1)
+//   backward  cnrf_pair_bwd_prepare -> cnrf_pair_bwd_chain(1) -> cnrf_pair_bwd_chain(0) -> cnrf_pair_bwd_finish
+// `side` is caller scratch of cnrf_pair_side_bytes() that must stay untouched between the calls of one direction.
+struct CnrfPairIn {
+  const cnrf_field_shape* shape[2];            // [0] coarse, [1] fine: same rays, codes, widths; num_samples differ
+  const cnrf_codenerf_params* params[2];
+  const float* rd; const float* freqs_xyz; int32_t L_xyz; const float* freqs_dir; int32_t L_dir;
+  const int64_t* ids; int64_t num_codes;       // ids != NULL: z_s / z_t are the embedding tables (shared-code mode)
+  const float* z_s; int64_t ld_zs; const float* z_t; int64_t ld_zt;
+  void* saved[2]; size_t saved_bytes[2];       // cnrf_codenerf_saved_bytes(shape[i]) each when shape[i]->keep
+};
+bool cnrf_pair_eligible(const cnrf_field_shape* coarse, const cnrf_field_shape* fine);
+size_t cnrf_pair_side_bytes(const cnrf_field_shape* coarse, int32_t backward);
+int cnrf_pair_fwd_prepare(const CnrfPairIn& in, void* side, size_t side_bytes, cudaStream_t st);
+int cnrf_pair_fwd_chain(const CnrfPairIn& in, int which, const float* pts, float* raw, void* side, size_t side_bytes, void* ws,
+                        size_t ws_bytes, cudaStream_t st);
+int cnrf_pair_bwd_prepare(const CnrfPairIn& in, const cnrf_codenerf_grads* const g[2], void* side, size_t side_bytes, cudaStream_t st);
+int cnrf_pair_bwd_chain(const CnrfPairIn& in, int which, const float* g_raw, const cnrf_codenerf_grads* g, void* side,
+                        size_t side_bytes, void* ws, size_t ws_bytes, cudaStream_t st);
+// g_z_s / g_z_t: dense table gradients [num_codes, C] (ids mode, overwritten) or per-ray code gradients [N, C] (overwritten)
+int cnrf_pair_bwd_finish(const CnrfPairIn& in, const cnrf_codenerf_grads* const g[2], float* g_z_s, float* g_z_t, void* side,
+                         size_t side_bytes, cudaStream_t st);
 
 // ---- posembed.cu -------------------------------------------------------------------------------------------------
 int cnrf_pos_embed_fwd_ld(const float* x, int64_t M, int D, const float* freqs, int L, int inc, int64_t ld_out,

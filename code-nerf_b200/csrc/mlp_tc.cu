@@ -21,7 +21,8 @@
 __device__ __forceinline__ float wfh_at(const float* __restrict__ wf, int i) {
   return ((wf[i] + wf[65536 + i]) + wf[2 * 65536 + i]) + wf[3 * 65536 + i];
 }
-__global__ void pack_weights_kernel(cnrf_codenerf_params p, const float* __restrict__ wf, int dx, int dd, Packed pk) {
+__device__ __forceinline__ void pack_weights_body(const cnrf_codenerf_params& p, const float* __restrict__ wf, int dx, int dd,
+                                                  const Packed& pk) {
   const int ch = blockIdx.x;                  // 0 .. FWD_CHUNKS+BWD_CHUNKS-1
   for (int i = blockIdx.y * blockDim.x + threadIdx.x; i < 256 * 64; i += gridDim.y * blockDim.x) {
     int r = i >> 6, c = i & 63;
@@ -65,6 +66,14 @@ __global__ void pack_weights_kernel(cnrf_codenerf_params p, const float* __restr
     }
   }
 }
+__global__ void pack_weights_kernel(cnrf_codenerf_params p, const float* __restrict__ wf, int dx, int dd, Packed pk) {
+  pack_weights_body(p, wf, dx, dd, pk);
+}
+// both models of a render call in one launch (blockIdx.z = model)
+struct PackPair { cnrf_codenerf_params p[2]; const float* wf[2]; Packed pk[2]; };
+__global__ void pack_weights_pair_kernel(const __grid_constant__ PackPair a, int dx, int dd) {
+  pack_weights_body(a.p[blockIdx.z], a.wf[blockIdx.z], dx, dd, a.pk[blockIdx.z]);
+}
 
 // ---- host side --------------------------------------------------------------------------------------------------------
 __device__ int g_tc_error = 0;   // raised by a bounded barrier wait that timed out (read by cnrf_debug_tc_error)
@@ -78,6 +87,8 @@ struct TcChainArgs {   // mirrors the declaration in codenerf.cu
   const float* wf;                            // the four K-slices [4][256 x 256] of this call's fold Wfh = Wdf Wout'h
   const float* x_dir; int64_t ld_dir;         // gamma(d^) per ray [N, dd]
   const int32_t* gid;                         // shared-code mode: row of the bias tables that ray r uses (NULL: r)
+  uint8_t* packed = nullptr;                  // != NULL: the weight images were packed there already (cnrf_tc_pack_pair)
+  bool prezeroed = false;                     // backward: the caller zero-filled every accumulation target
 };
 
 static inline size_t up1k(size_t b) { return (b + 1023) & ~size_t(1023); }
@@ -101,6 +112,23 @@ static inline int64_t pairs_of(int64_t M) { return (tiles_of(M) + 1) / 2; }
 // per tile: the activation images; then per tile pair: the view-direction extension slab
 // ... then the packed weight images of this call (the backward runs on the same weights and reuses them)
 size_t cnrf_tc_saved_bytes(int64_t M) { return (size_t)tiles_of(M) * SAVED_PER_TILE + (size_t)pairs_of(M) * SLAB + PACKED_BYTES; }
+
+// where the packed weight images of a call live inside its saved buffer (what cnrf_tc_chain_fwd / _bwd use by default)
+uint8_t* cnrf_tc_packed_in_saved(void* saved, int64_t M) {
+  uint8_t* saved_al = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(saved)));
+  return saved_al + (size_t)tiles_of(M) * SAVED_PER_TILE + (size_t)pairs_of(M) * SLAB;
+}
+size_t cnrf_tc_packed_bytes() { return PACKED_BYTES + 1024; }
+// the weight images of two models in one launch; at0 / at1: 1024-byte aligned, cnrf_tc_packed_bytes() each
+int cnrf_tc_pack_pair(const cnrf_codenerf_params* p0, const float* wf0, uint8_t* at0, const cnrf_codenerf_params* p1,
+                      const float* wf1, uint8_t* at1, int dx, int dd, cudaStream_t st) {
+  if ((reinterpret_cast<uintptr_t>(at0) | reinterpret_cast<uintptr_t>(at1)) & 1023) return CNRF_E_WORKSPACE;
+  PackPair a;
+  a.p[0] = *p0; a.p[1] = *p1; a.wf[0] = wf0; a.wf[1] = wf1; a.pk[0] = carve_packed(at0); a.pk[1] = carve_packed(at1);
+  pack_weights_pair_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8, 2), 256, 0, st>>>(a, dx, dd);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
 
 // Extension slab of every tile pair (the K = 32 extra input columns of layer_dir1): row r, columns 32t .. 32t+31 =
 // [gamma(d^ of the ray paired with sample row r of tile t) | 1 | 0].  The pairing reproduces nerf/__init__.py:127
@@ -139,15 +167,18 @@ int cnrf_tc_chain_fwd(const TcChainArgs& a, float* raw, void* saved, size_t save
   if (saved && saved_bytes < cnrf_tc_saved_bytes(a.M) + 1024) return CNRF_E_WORKSPACE;
   if (a.dd > 31) return CNRF_E_UNSUPPORTED;
   uint8_t* saved_al = saved ? reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(saved))) : nullptr;
-  Packed pk = carve_packed(saved_al ? saved_al + (size_t)tiles_of(a.M) * SAVED_PER_TILE + (size_t)pairs_of(a.M) * SLAB : w);
+  Packed pk = carve_packed(a.packed ? a.packed
+                                    : saved_al ? saved_al + (size_t)tiles_of(a.M) * SAVED_PER_TILE + (size_t)pairs_of(a.M) * SLAB : w);
   // the extension slabs live with the saved images when a backward follows (the weight-gradient kernel reads them)
   uint8_t* ext = saved_al ? saved_al + (size_t)tiles_of(a.M) * SAVED_PER_TILE
                           : reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
   build_ext_kernel<<<grid_for(pairs_of(a.M) * 1024, 256), 256, 0, st>>>(a.x_dir, a.ld_dir, a.dd, a.N, a.M, a.S, a.pairing,
                                                                       ext, pairs_of(a.M));
   CNRF_LAUNCH_CHECK();
-  pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.wf, a.dx, a.dd, pk);
-  CNRF_LAUNCH_CHECK();
+  if (!a.packed) {
+    pack_weights_kernel<<<dim3(FWD_CHUNKS + BWD_CHUNKS, 8), 256, 0, st>>>(*a.p, a.wf, a.dx, a.dd, pk);
+    CNRF_LAUNCH_CHECK();
+  }
   FwdArgs f;
   f.N = a.N; f.M = a.M; f.S = a.S; f.pairing = a.pairing; f.dx = a.dx;
   f.pts = a.pts; f.x_xyz = a.x_xyz; f.ld_xyz = a.ld_xyz; f.freqs = a.freqs_xyz; f.L = a.L_xyz; f.inc = a.inc_xyz;
@@ -574,8 +605,10 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   Packed pk = carve_packed(const_cast<uint8_t*>(sv) + (size_t)tiles * SAVED_PER_TILE + (size_t)pairs_of(a.M) * SLAB);
   uint8_t* dy = reinterpret_cast<uint8_t*>(up1k(reinterpret_cast<size_t>(w + PACKED_BYTES)));
   int rc;
-  if ((rc = cnrf_fill_zero(g->bias[CNRF_L_XYZ1], 256 * sizeof(float), st))) return rc;
-  if ((rc = cnrf_fill_zero(g->bias[CNRF_L_DIR2], 256 * sizeof(float), st))) return rc;
+  if (!a.prezeroed) {
+    if ((rc = cnrf_fill_zero(g->bias[CNRF_L_XYZ1], 256 * sizeof(float), st))) return rc;
+    if ((rc = cnrf_fill_zero(g->bias[CNRF_L_DIR2], 256 * sizeof(float), st))) return rc;
+  }
   {
     static bool attr_set[CNRF_MAX_DEVICES] = {};
     const cudaError_t e = cnrf_once_per_device(attr_set, [] {
@@ -591,11 +624,13 @@ int cnrf_tc_chain_bwd(const TcChainArgs& a, const float* g_raw, const void* save
   d.M = a.M; d.S = a.S; d.saved = sv; d.dy = dy; d.g_raw = g_raw; d.gid = a.gid; d.d_br = d_br; d.d_bo = d_bo; d.err = tc_error_ptr();
   d.ext = sv + (size_t)tiles * SAVED_PER_TILE;
   // the per-ray tables are accumulated by the reducer warps
-  if ((rc = cnrf_fill_zero(d_b2, (size_t)a.N * 256 * sizeof(float), st))) return rc;
-  if ((rc = cnrf_fill_zero(d_bo, (size_t)a.N * 257 * sizeof(float), st))) return rc;
-  if ((rc = cnrf_fill_zero(d_br, (size_t)a.N * 3 * sizeof(float), st))) return rc;
-  if ((rc = cnrf_fill_zero(d_bf, (size_t)a.N * 256 * sizeof(float), st))) return rc;
-  if ((rc = cnrf_fill_zero(dwfh, (size_t)256 * 256 * sizeof(float), st))) return rc;
+  if (!a.prezeroed) {
+    if ((rc = cnrf_fill_zero(d_b2, (size_t)a.N * 256 * sizeof(float), st))) return rc;
+    if ((rc = cnrf_fill_zero(d_bo, (size_t)a.N * 257 * sizeof(float), st))) return rc;
+    if ((rc = cnrf_fill_zero(d_br, (size_t)a.N * 3 * sizeof(float), st))) return rc;
+    if ((rc = cnrf_fill_zero(d_bf, (size_t)a.N * 256 * sizeof(float), st))) return rc;
+    if ((rc = cnrf_fill_zero(dwfh, (size_t)256 * 256 * sizeof(float), st))) return rc;
+  }
   float* const nil = nullptr;
   // saved images: 0 h1, 1 h2, 2 v1, 3 v2;  gradient images: 0 d v2p, 1 d v1p, 2 d h2p, 3 d h1p
   d.job[0] = {0, 2, 256, g->weight[CNRF_L_DIR2], 256, 256, nil, -1, RED_COLSUM, g->bias[CNRF_L_DIR2], 0, nil};   // d v2p^T v1

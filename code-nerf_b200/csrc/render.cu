@@ -83,7 +83,8 @@ extern "C" size_t cnrf_render_workspace_bytes(const cnrf_render_shape* s, int32_
   const Dims d = dims_of(s);
   const cnrf_field_shape fc = field_shape(s, d.Sc, s->keep), ff = field_shape(s, d.Sf, s->keep);
   const size_t fw = cnrf_field_workspace_bytes(&fc, backward), fwf = cnrf_field_workspace_bytes(&ff, backward);
-  const size_t field = al256(fw > fwf ? fw : fwf) + 256;
+  size_t field = al256(fw > fwf ? fw : fwf) + 256;
+  if (cnrf_pair_eligible(&fc, &ff)) field += al256(cnrf_pair_side_bytes(&fc, backward)) + 256;     // the two-model per-ray state
   if (!backward) {
     size_t b = al256(d.N * d.Sc * 4) /*weights*/ + field + 512;
     if (!s->keep) b += kept_bytes(d, true);                       // inference: nothing is kept, everything is scratch
@@ -119,16 +120,30 @@ extern "C" int cnrf_render_fwd(const cnrf_render_shape* s, const cnrf_codenerf_p
   char* saved_f = s->keep ? saved_c + sb_c : nullptr;
   if (s->keep && sv.rest_bytes() < sb_c + sb_f) return CNRF_E_WORKSPACE;
 
+  // tensor-core mode: the per-ray work of BOTH models (code runs, code layers, folds, weight packing, direction encoding)
+  // in one set of launches ahead of the two per-sample chains (codenerf.cu, "both models of one render call")
+  const bool pair = cnrf_pair_eligible(&fc, &ff);
+  CnrfPairIn pin{{&fc, &ff}, {coarse, fine}, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
+                 in->z_s, in->ld_zs, in->z_t, in->ld_zt, {saved_c, saved_f}, {sb_c, sb_f}};
+  void* side = nullptr; size_t side_bytes = 0;
+  if (pair) {
+    side_bytes = al256(cnrf_pair_side_bytes(&fc, 0));
+    side = ws.take(side_bytes / sizeof(float));
+    if (!ws.ok) return CNRF_E_WORKSPACE;
+    RUN(cnrf_pair_fwd_prepare(pin, side, side_bytes, st));
+  }
   // coarse pass                                                                          nerf/__init__.py:82-84
   RUN(cnrf_sample_uniform_fwd(in->ro, in->rd, d.N, d.Sc, in->z_table, in->lower, in->upper, in->t_rand, k.pts_c, k.z_c, stream));
-  RUN(cnrf_field_fwd_impl(&fc, coarse, k.pts_c, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
-                          in->z_s, in->ld_zs, in->z_t, in->ld_zt, k.raw_c, saved_c, sb_c, ws.rest(), ws.rest_bytes(), st));
+  if (pair) RUN(cnrf_pair_fwd_chain(pin, 0, k.pts_c, k.raw_c, side, side_bytes, ws.rest(), ws.rest_bytes(), st));
+  else RUN(cnrf_field_fwd_impl(&fc, coarse, k.pts_c, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
+                               in->z_s, in->ld_zs, in->z_t, in->ld_zt, k.raw_c, saved_c, sb_c, ws.rest(), ws.rest_bytes(), st));
   RUN(cnrf_composite_fwd(k.raw_c, k.z_c, in->rd, d.N, d.Sc, rgb_coarse, nullptr, nullptr, weights, nullptr, stream));
   // fine pass: importance samples from weights[..., 1:-1]                                nerf/__init__.py:87-89
   RUN(cnrf_sample_pdf_fwd(in->ro, in->rd, weights + 1, d.Sc, k.z_c, d.N, d.Sc, s->num_fine, in->u, k.pts_f, k.z_f, nullptr, nullptr,
                           stream));
-  RUN(cnrf_field_fwd_impl(&ff, fine, k.pts_f, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
-                          in->z_s, in->ld_zs, in->z_t, in->ld_zt, k.raw_f, saved_f, sb_f, ws.rest(), ws.rest_bytes(), st));
+  if (pair) RUN(cnrf_pair_fwd_chain(pin, 1, k.pts_f, k.raw_f, side, side_bytes, ws.rest(), ws.rest_bytes(), st));
+  else RUN(cnrf_field_fwd_impl(&ff, fine, k.pts_f, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
+                               in->z_s, in->ld_zs, in->z_t, in->ld_zt, k.raw_f, saved_f, sb_f, ws.rest(), ws.rest_bytes(), st));
   float* disp = extras_fine, *acc = extras_fine ? extras_fine + d.N : nullptr, *depth = extras_fine ? extras_fine + 2 * d.N : nullptr;
   return cnrf_composite_fwd(k.raw_f, k.z_f, in->rd, d.N, d.Sf, rgb_fine, disp, acc, nullptr, depth, stream);
 }
@@ -160,6 +175,20 @@ extern "C" int cnrf_render_bwd(const cnrf_render_shape* s, const cnrf_codenerf_p
   // A missing upstream gradient is a zero gradient: the pass still runs so that every parameter gradient is written
   // (the caller's buffers are uninitialised) -- compositing treats a NULL g_rgb as zero.
   // fine pass first: its dW kernel is the long one, and a caller that overlaps a gradient exchange wants it early
+  if (cnrf_pair_eligible(&fc, &ff)) {     // tensor-core mode: zero fills, per-ray gradient GEMMs and table scatters once for both models
+    CnrfPairIn pin{{&fc, &ff}, {coarse, fine}, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
+                   in->z_s, in->ld_zs, in->z_t, in->ld_zt, {const_cast<char*>(saved_c), const_cast<char*>(saved_f)}, {sb_c, sb_f}};
+    const cnrf_codenerf_grads* const gs[2] = {g_coarse, g_fine};
+    const size_t side_bytes = al256(cnrf_pair_side_bytes(&fc, 1));
+    void* side = ws.take(side_bytes / sizeof(float));
+    if (!ws.ok) return CNRF_E_WORKSPACE;
+    RUN(cnrf_pair_bwd_prepare(pin, gs, side, side_bytes, st));
+    RUN(cnrf_composite_bwd(k.raw_f, k.z_f, in->rd, d.N, d.Sf, g_rgb_fine, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, stream));
+    RUN(cnrf_pair_bwd_chain(pin, 1, g_raw, g_fine, side, side_bytes, ws.rest(), ws.rest_bytes(), st));
+    RUN(cnrf_composite_bwd(k.raw_c, k.z_c, in->rd, d.N, d.Sc, g_rgb_coarse, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, stream));
+    RUN(cnrf_pair_bwd_chain(pin, 0, g_raw, g_coarse, side, side_bytes, ws.rest(), ws.rest_bytes(), st));
+    return cnrf_pair_bwd_finish(pin, gs, g_z_s, g_z_t, side, side_bytes, st);
+  }
   RUN(cnrf_composite_bwd(k.raw_f, k.z_f, in->rd, d.N, d.Sf, g_rgb_fine, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, stream));
   RUN(cnrf_field_bwd_impl(&ff, fine, k.pts_f, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
                           in->z_s, in->ld_zs, in->z_t, in->ld_zt, g_raw, saved_f, sb_f, g_fine, g_z_s, g_z_t, nullptr, nullptr,

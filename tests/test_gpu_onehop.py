@@ -285,10 +285,14 @@ def _reference_pose_spherical():
     return ns["pose_spherical"]
 
 
-def test_c3_config_shape_with_reference_pose_spherical(dev):
+@pytest.mark.parametrize("pose_precision,early_atol", [("fp32", 2e-3), ("split", 5e-3)])
+def test_c3_config_shape_with_reference_pose_spherical(dev, pose_precision, early_atol, monkeypatch):
     """config/srn-cars-code-3080-val.yml: 2048 rays of a 128 x 128 view, 64 + 64 samples, AdamW on (z_s, z_t) 1e-2,
     (theta, phi) 5e-2, rho 1e-1 (eval.py:126-138), regulariser 1e-6, 24 iterations of eval.py:140-168 -- through the
-    drop-in (pose gradients select the fp32 chain) and through the oracle, same pixel draws and sample offsets."""
+    drop-in and through the oracle, same pixel draws and sample offsets.  Pose gradients select the chain named by
+    CODENERF_POSE_GRAD_PRECISION: "fp32" (CUDA-core FMA, the golden parity mode) and "split" (the library default: the same
+    chain with split-bf16 tensor-core contractions; first-step gradients measured at <= 1.3e-3 of the oracle's)."""
+    monkeypatch.setenv("CODENERF_POSE_GRAD_PRECISION", pose_precision)
     import view_synthesis.nerf as nerf
     import view_synthesis.models as models
     pose_spherical = _reference_pose_spherical()
@@ -379,7 +383,7 @@ def test_c3_config_shape_with_reference_pose_spherical(dev):
         nerf.set_precision("fp32")
     g_err = {n: _errs(a, b) for a, b, n in zip(grads, grads_o, ("z_s", "z_t", "theta", "phi", "rho"))}
     traj, traj_o = np.array(traj), np.array(traj_o)
-    _record("c3_config_shape", {"first_step_gradients": g_err, "trajectory": traj.tolist(), "trajectory_oracle": traj_o.tolist()})
+    _record("c3_config_shape_" + pose_precision, {"first_step_gradients": g_err, "trajectory": traj.tolist(), "trajectory_oracle": traj_o.tolist()})
     print("\nC3 first-step gradients vs oracle:", {k: f"{v['max_norm']:.2e}" for k, v in g_err.items()})
     print("C3 (loss, theta, phi, rho) after 24 iterations:", traj[-1], "oracle:", traj_o[-1])
     np.testing.assert_allclose(traj[0, 0], traj_o[0, 0], rtol=1e-4)
@@ -390,7 +394,7 @@ def test_c3_config_shape_with_reference_pose_spherical(dev):
     # through zero an fp32-rounding difference becomes a full-rate step in the other direction -- the two runs agree to
     # 1e-3 for three iterations and then follow different, equally good, descent paths (measured |d phi| 0.23 after 24).
     np.testing.assert_allclose(traj[:, 0], traj_o[:, 0], rtol=5e-3)
-    np.testing.assert_allclose(traj[:3, 1:], traj_o[:3, 1:], atol=2e-3)
+    np.testing.assert_allclose(traj[:3, 1:], traj_o[:3, 1:], atol=early_atol)
     np.testing.assert_allclose(traj[:, 1:], traj_o[:, 1:], atol=0.5)
     codes_moved = float((lv[0].detach() - zs0.to(dev)).abs().max())
     assert 0.05 < codes_moved < 0.5, codes_moved                                         # ~24 steps of lr 1e-2
