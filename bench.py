@@ -63,6 +63,8 @@ def parse():
                     "utils/util.py:139-142 does, instead of codenerf_b200.parallel.GradAllReduce")
     ap.add_argument("--torch-loss", action="store_true", help="2 x torch.nn.functional.mse_loss + add (train.py:103-104 verbatim) "
                     "instead of codenerf_b200.ops.mse_pair")
+    ap.add_argument("--staged-loss", action="store_true", help="codenerf_b200.ops.mse_pair on the returned rgb tensors instead of "
+                    "the loss folded into the compositing epilogues (nerf.predict_radiance_render_and_loss)")
     ap.add_argument("--no-prefetch", action="store_true", help="e2e leg: draw each step's pixel permutations at the start "
                     "of the step (the reference's order of work) instead of under the previous step's kernels")
     ap.add_argument("--stock-caller", action="store_true", help="train.py:96-114 verbatim around the drop-in (see module docstring)")
@@ -368,12 +370,24 @@ def run_ours(args):
     poses_pin = torch.from_numpy(poses_np).pin_memory()
     ids_pin = torch.from_numpy(ids_np).pin_memory()
     n_rays = c["B"] * c["rays_per_image"]
+    fused_loss = not (stock or args.torch_loss or args.staged_loss)
 
     def chunks_step(ro, rd, tgt, oid, read_loss):
         total = None
         for i in range(0, n_rays, c["chunk"]):
             sl = slice(i, i + c["chunk"])
             codes = mods["embedding"](oid[sl])
+            if fused_loss:       # the loss rides in the compositing epilogues (cnrf_render_loss_fwd / _bwd)
+                lc, lf, loss, _rc, _rf = nerf.predict_radiance_render_and_loss(
+                    (ro[sl], rd[sl]), point_sampler, embedders, mods["nerf_coarse"], mods["nerf_fine"], codes, target_pixels=tgt[sl])
+                opt.zero_grad()
+                loss.backward()
+                if sync is not None:
+                    sync()
+                opt.step()
+                if read_loss:
+                    total = lf.detach() if total is None else total + lf.detach()
+                continue
             rgb_c, rgb_f = nerf.predict_radiance_and_render((ro[sl], rd[sl]), point_sampler, embedders,
                                                             mods["nerf_coarse"], mods["nerf_fine"], codes)
             if stock:                                                    # train.py:103-114 verbatim
@@ -494,7 +508,7 @@ def run_ours(args):
         cfgd.update({
             "caller": ("stock train.py loop body (train.py:96-114): 2 x mse_loss, .item() per chunk, get_params_tensor regulariser, "
                        "torch.optim.AdamW + LambdaLR, no prefetch" if stock else
-                       "codenerf_b200 extras: ops.mse_pair" + (" (off: --torch-loss)" if args.torch_loss else "") +
+                       "codenerf_b200 extras: " + ("loss folded into the compositing epilogues (predict_radiance_render_and_loss)" if not (args.torch_loss or args.staged_loss) else "ops.mse_pair" if not args.torch_loss else "2 x torch mse_loss (--torch-loss)") +
                        ", FusedAdamW (one launch), one loss read per step"),
             "gradient_exchange": ("none (1 GPU)" if world == 1 else "DistributedDataParallel x3 (utils/util.py:139-142)" if use_ddp
                                   else "codenerf_b200.parallel.GradAllReduce (one flat NCCL all-reduce per chunk step)"),

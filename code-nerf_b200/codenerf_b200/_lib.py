@@ -54,7 +54,16 @@ class RenderInputs(C.Structure):    # cnrf_render_inputs
                 ("z_s", C.c_void_p), ("ld_zs", c_i64), ("z_t", C.c_void_p), ("ld_zt", c_i64)]
 
 
+class LossTarget(C.Structure):      # cnrf_loss_target
+    _fields_ = [("rows", C.c_void_p), ("ld_rows", c_i64), ("views", C.c_void_p), ("pixel", C.c_void_p), ("channels", c_i32)]
+
+
 _SIGS = {
+    "cnrf_render_loss_fwd": (C.c_int, [C.POINTER(RenderShape), C.POINTER(PtrTable), C.POINTER(PtrTable), C.POINTER(RenderInputs),
+                                       C.POINTER(LossTarget), c_f32p, c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_render_loss_bwd": (C.c_int, [C.POINTER(RenderShape), C.POINTER(PtrTable), C.POINTER(PtrTable), C.POINTER(RenderInputs),
+                                       C.POINTER(LossTarget), c_f32p, c_f32p, c_f32p, c_f32p, c_f32p, C.c_void_p, c_sz,
+                                       C.POINTER(PtrTable), C.POINTER(PtrTable), c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
     "cnrf_render_saved_bytes": (c_sz, [C.POINTER(RenderShape)]),
     "cnrf_render_workspace_bytes": (c_sz, [C.POINTER(RenderShape), c_i32]),
     "cnrf_render_fwd": (C.c_int, [C.POINTER(RenderShape), C.POINTER(PtrTable), C.POINTER(PtrTable), C.POINTER(RenderInputs),

@@ -557,6 +557,109 @@ class _Render(torch.autograd.Function):
         return (None, None, None, None, None, g_codes[0], g_codes[1]) + grads
 
 
+class LossTargetSpec(object):
+    """Target pixels of a fused render + loss call: `rows` (N, >= 3) float32 rows already gathered (train.py:77-80), or
+    `views` (any shape ending in `channels` uint8, e.g. DeviceSRN.colors_u8) + `pixel` (N,) int64 flat pixel indices
+    (view index * H W + selected pixel): the gather and the loader's / 255.0 then happen inside the compositing epilogue."""
+    __slots__ = ("rows", "views", "pixel")
+
+    def __init__(self, rows=None, views=None, pixel=None):
+        assert (rows is None) != (views is None), "give target rows or uint8 views + pixel indices"
+        if views is not None:
+            assert pixel is not None and views.dtype == torch.uint8 and pixel.dtype == torch.int64 and views.shape[-1] in (3, 4)
+        self.rows, self.views, self.pixel = rows, views, pixel
+
+    def struct(self, N, keepalive):
+        t = _lib.LossTarget()
+        if self.views is not None:
+            v, px = self.views.contiguous(), self.pixel.contiguous()      # uint8 / int64: no dtype conversion
+            assert v.is_cuda and px.is_cuda, "views / pixel must be CUDA tensors (there is no CPU fallback)"
+            assert px.shape == (N,), "pixel must hold one index per ray"
+            keepalive += [v, px]
+            t.views, t.pixel, t.channels = v.data_ptr(), px.data_ptr(), v.shape[-1]
+        else:
+            r, ld = _rows(self.rows)
+            assert r.shape[0] == N and r.shape[-1] >= 3 and r.dtype == _f32
+            keepalive.append(r)
+            t.rows, t.ld_rows = r.data_ptr(), ld
+        return t
+
+
+class _RenderLoss(torch.autograd.Function):
+    """_Render + the photometric loss of train.py:103-104 folded into the compositing epilogues (cnrf_render_loss_fwd / _bwd):
+    -> coarse_loss, fine_loss, loss (0-dim), rgb_coarse, rgb_fine (not differentiable: their gradient is the loss's)."""
+
+    @staticmethod
+    def forward(ctx, spec, target, ro, rd, t_rand, u, code_a, code_b, *params):
+        _req_cuda(ro, rd, t_rand, u, code_a, code_b, *params)
+        lib = _lib.load()
+        ro, rd = _c(ro), _c(rd)
+        t_rand = _c(t_rand) if t_rand is not None else None
+        u = _c(u) if u is not None else None
+        code_a, ld_a = _rows(code_a)
+        code_b, ld_b = _rows(code_b)
+        params = tuple(_c(p) for p in params)
+        N = ro.shape[0]
+        dev = ro.device
+        if spec.ids is not None:
+            assert spec.ids.dtype == torch.int64 and spec.ids.shape == (N,) and spec.ids.is_contiguous(), "ids must be (N,) int64"
+            assert code_a.shape[0] == code_b.shape[0], "shape and texture tables must have the same number of rows"
+        keep = int(_OUTER_GRAD[0] and any(ctx.needs_input_grad))
+        shp = RenderShape(spec.hidden, spec.code, spec.dim_xyz, spec.dim_dir, N, spec.num_coarse, spec.num_fine, spec.pairing,
+                          spec.precision, keep)
+        saved = _bytes(lib.cnrf_render_saved_bytes(C.byref(shp)), dev) if keep else None
+        ws = _bytes(lib.cnrf_render_workspace_bytes(C.byref(shp), 0), dev)
+        rgb = torch.empty((2, N, 3), dtype=_f32, device=dev)
+        loss3 = torch.empty((3,), dtype=_f32, device=dev)
+        tc, tf = _ptr_table(params[:18]), _ptr_table(params[18:])
+        inp = _render_inputs(spec, ro, rd, t_rand, u, code_a, ld_a, code_b, ld_b)
+        alive = []
+        tgt = target.struct(N, alive)
+        check(lib.cnrf_render_loss_fwd(C.byref(shp), C.byref(tc), C.byref(tf), C.byref(inp), C.byref(tgt), _p(loss3), _p(rgb[0]),
+                                       _p(rgb[1]), _p(saved), saved.numel() if keep else 0, _p(ws), ws.numel(), _stream()),
+              "cnrf_render_loss_fwd")
+        if keep:
+            ctx.save_for_backward(rd, code_a, code_b, saved, rgb, *alive, *params)
+            ctx.spec, ctx.lds, ctx.N, ctx.n_alive, ctx.target = spec, (ld_a, ld_b), N, len(alive), target
+        ctx.set_materialize_grads(False)
+        ctx.mark_non_differentiable(rgb)
+        return loss3[0], loss3[1], loss3[2], rgb
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, g0, g1, g2, _g_rgb):
+        rd, code_a, code_b, saved, rgb, *rest = ctx.saved_tensors
+        alive, params = rest[:ctx.n_alive], rest[ctx.n_alive:]
+        spec, (ld_a, ld_b), N = ctx.spec, ctx.lds, ctx.N
+        lib = _lib.load()
+        dev = rd.device
+        if g0 is None and g1 is None and g2 is None:
+            return (None,) * (8 + len(params))
+        gs = [None if g is None else _c(g.to(_f32)) for g in (g0, g1, g2)]
+        shp = RenderShape(spec.hidden, spec.code, spec.dim_xyz, spec.dim_dir, N, spec.num_coarse, spec.num_fine, spec.pairing,
+                          spec.precision, 1)
+        sizes = [p.numel() for p in params]
+        flat = torch.empty((sum(sizes),), dtype=_f32, device=dev)          # all 36 parameter gradients: one allocation
+        grads = tuple(v.view_as(p) for v, p in zip(flat.split(sizes), params))
+        rows = code_a.shape[0] if spec.ids is not None else N
+        g_codes = torch.empty((2, rows, spec.code), dtype=_f32, device=dev)
+        ws = _bytes(lib.cnrf_render_workspace_bytes(C.byref(shp), 1), dev)
+        tc, tf = _ptr_table(params[:18]), _ptr_table(params[18:])
+        gc, gf = _ptr_table(grads[:18]), _ptr_table(grads[18:])
+        inp = _render_inputs(spec, None, rd, None, None, code_a, ld_a, code_b, ld_b)
+        tgt = ctx.target.struct(N, [])
+        check(lib.cnrf_render_loss_bwd(C.byref(shp), C.byref(tc), C.byref(tf), C.byref(inp), C.byref(tgt), _p(rgb[0]), _p(rgb[1]),
+                                       _p(gs[0]), _p(gs[1]), _p(gs[2]), _p(saved), saved.numel(), C.byref(gc), C.byref(gf),
+                                       _p(g_codes[0]), _p(g_codes[1]), _p(ws), ws.numel(), _stream()), "cnrf_render_loss_bwd")
+        return (None, None, None, None, None, None, g_codes[0], g_codes[1]) + grads
+
+
+def render_loss(spec, target, ro, rd, t_rand, u, code_a, code_b, params_coarse, params_fine):
+    """predict_radiance_and_render + train.py:103-104's photometric loss as one library call per direction:
+    -> (coarse_loss, fine_loss, loss, rgb (2, N, 3) [coarse, fine; detached])."""
+    return _apply(_RenderLoss, spec, target, ro, rd, t_rand, u, code_a, code_b, *params_coarse, *params_fine)
+
+
 def render(spec, ro, rd, t_rand, u, code_a, code_b, params_coarse, params_fine):
     """predict_radiance_and_render as one library call: -> (rgb_coarse, rgb_fine[, extras_fine])."""
     return _apply(_Render, spec, ro, rd, t_rand, u, code_a, code_b, *params_coarse, *params_fine)

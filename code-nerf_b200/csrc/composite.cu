@@ -14,8 +14,16 @@
 // < 2e-7; exp(raw-1) itself stays the accurate expf because the LAST sample multiplies sigma by 1e10, :43).  Parity with
 // the reference stays within 1e-6 absolute (tests/test_gpu_parity.py::test_volume_render_*: 2e-6 abs on every output).
 #include "common.cuh"
+#include "internal.h"
 
 constexpr int CWARPS = 8;  // warps per block
+
+// target pixel channel of ray n for the loss epilogue (internal.h: LossTarget); the uint8 form is the loader's own
+// (float)((double)v / 255.0) (datasets/dataset.py:72,90)
+__device__ __forceinline__ float loss_target(const LossTarget& t, int64_t n, int c) {
+  if (t.views) return (float)((double)__ldg(t.views + __ldg(t.pixel + n) * t.channels + c) / 255.0);
+  return __ldg(t.rows + n * t.ld + c);
+}
 
 // single-instruction SFU forms (flush-to-zero: a subnormal exp(-x) or alpha is 0 to every tolerance used here)
 __device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -97,7 +105,7 @@ template <int NCH, int R>
 __global__ void __launch_bounds__(CWARPS * 32)
 composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rd,
                      int64_t N, int S, float* __restrict__ rgb, float* __restrict__ disp, float* __restrict__ acc,
-                     float* __restrict__ weights, float* __restrict__ depth) {
+                     float* __restrict__ weights, float* __restrict__ depth, const CompositeLossFwd lf) {
   const int lane = threadIdx.x & 31;
   const int64_t n0 = ((int64_t)blockIdx.x * CWARPS + (threadIdx.x >> 5)) * R;
   if (n0 >= N) return;
@@ -160,6 +168,23 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
       if (disp) disp[n] = rcp_fast(fmaxf(1e-10f, tot * rcp_fast(other)));             // 1 / max(1e-10, depth / acc)  :64
     } else if (qn == 4) { if (acc) acc[n] = tot; }
   }
+  if (lf.sq_sum) {      // photometric loss folded into the epilogue (train.py:103-104): sum over rays and channels of (rgb - target)^2
+    float e = 0.f;
+    if (writer && n < N && qn < 3) { const float d = tot - loss_target(lf.t, n, qn); e = d * d; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) e += __shfl_xor_sync(FULL_MASK, e, o);
+    if (lane == 0) {
+      atomicAdd(lf.sq_sum, e);
+      if (lf.out3) {    // the last warp of the fine pass turns the two sums into (coarse_loss, fine_loss, loss)
+        __threadfence();
+        if (atomicAdd(lf.done, 1u) == lf.num_warps - 1u) {
+          __threadfence();
+          const float a = *(volatile float*)lf.other_sq * lf.inv, b = *(volatile float*)lf.sq_sum * lf.inv;
+          lf.out3[0] = a; lf.out3[1] = b; lf.out3[2] = a + b;
+        }
+      }
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -170,7 +195,7 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
                      int64_t N, int S, const float* __restrict__ g_rgb, const float* __restrict__ g_disp,
                      const float* __restrict__ g_acc, const float* __restrict__ g_weights,
                      const float* __restrict__ g_depth, float* __restrict__ g_raw, float* __restrict__ g_z,
-                     float* __restrict__ g_rd) {
+                     float* __restrict__ g_rd, const CompositeLossBwd lb) {
   const int lane = threadIdx.x & 31;
   const int64_t n0 = ((int64_t)blockIdx.x * CWARPS + (threadIdx.x >> 5)) * R;
   if (n0 >= N) return;
@@ -194,6 +219,12 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     const float norm = sqrtf(dx * dx + dy * dy + dz * dz);
     float gR = g_rgb ? __ldg(g_rgb + n * 3) : 0.f, gG = g_rgb ? __ldg(g_rgb + n * 3 + 1) : 0.f,
           gB = g_rgb ? __ldg(g_rgb + n * 3 + 2) : 0.f;
+    if (lb.rgb_out) {   // the loss lives in the forward epilogue: d loss / d rgb = (g_term + g_sum) * 2 (rgb - target) / (3 N)
+      const float k = ((lb.g_term ? __ldg(lb.g_term) : 0.f) + (lb.g_sum ? __ldg(lb.g_sum) : 0.f)) * lb.scale;
+      gR = k * (__ldg(lb.rgb_out + n * 3) - loss_target(lb.t, n, 0));
+      gG = k * (__ldg(lb.rgb_out + n * 3 + 1) - loss_target(lb.t, n, 1));
+      gB = k * (__ldg(lb.rgb_out + n * 3 + 2) - loss_target(lb.t, n, 2));
+    }
     float gD = g_depth ? __ldg(g_depth + n) : 0.f, gA = g_acc ? __ldg(g_acc + n) : 0.f;
 
     // ---- forward sweep: per-sample state stays in registers
@@ -286,21 +317,22 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 
 template <int NCH, int R>
 static void launch_fwd(const float* raw, const float* z, const float* rd, int64_t N, int S, float* rgb, float* disp,
-                       float* acc, float* weights, float* depth, cudaStream_t st) {
+                       float* acc, float* weights, float* depth, CompositeLossFwd lf, cudaStream_t st) {
+  lf.num_warps = (unsigned)((N + R - 1) / R);
   composite_fwd_kernel<NCH, R><<<grid_for(N, CWARPS * R), CWARPS * 32, 0, st>>>(raw, z, rd, N, S, rgb, disp, acc, weights,
-                                                                                 depth);
+                                                                                 depth, lf);
 }
 template <int NCH, int R>
 static void launch_bwd(const float* raw, const float* z, const float* rd, int64_t N, int S, const float* g_rgb,
                        const float* g_disp, const float* g_acc, const float* g_weights, const float* g_depth,
-                       float* g_raw, float* g_z, float* g_rd, cudaStream_t st) {
+                       float* g_raw, float* g_z, float* g_rd, const CompositeLossBwd& lb, cudaStream_t st) {
   const unsigned grid = grid_for(N, CWARPS * R);
   if (g_z || g_rd)
     composite_bwd_kernel<NCH, R, true><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
-                                                                      g_depth, g_raw, g_z, g_rd);
+                                                                      g_depth, g_raw, g_z, g_rd, lb);
   else
     composite_bwd_kernel<NCH, R, false><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
-                                                                       g_depth, g_raw, g_z, g_rd);
+                                                                       g_depth, g_raw, g_z, g_rd, lb);
 }
 
 // chunks of 32 samples per ray -> (NCH, rays per warp forward, rays per warp backward)
@@ -318,22 +350,31 @@ static void launch_bwd(const float* raw, const float* z, const float* rd, int64_
 #define CALL_FWD(NCH, RF, RB, ...) launch_fwd<NCH, RF>(__VA_ARGS__)
 #define CALL_BWD(NCH, RF, RB, ...) launch_bwd<NCH, RB>(__VA_ARGS__)
 
-extern "C" int cnrf_composite_fwd(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, float* rgb,
-                                  float* disp, float* acc, float* weights, float* depth, cnrf_stream_t stream) {
+int cnrf_composite_fwd_loss(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, float* rgb, float* disp,
+                            float* acc, float* weights, float* depth, const CompositeLossFwd& lf, cudaStream_t st) {
   CNRF_REQUIRE(raw && z && rd, CNRF_E_NULL);
   CNRF_REQUIRE(N > 0 && S > 0 && S <= 256, CNRF_E_SHAPE);
-  DISPATCH_NCH(S, CALL_FWD, raw, z, rd, N, S, rgb, disp, acc, weights, depth, as_stream(stream));
+  DISPATCH_NCH(S, CALL_FWD, raw, z, rd, N, S, rgb, disp, acc, weights, depth, lf, st);
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }
+extern "C" int cnrf_composite_fwd(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, float* rgb,
+                                  float* disp, float* acc, float* weights, float* depth, cnrf_stream_t stream) {
+  return cnrf_composite_fwd_loss(raw, z, rd, N, S, rgb, disp, acc, weights, depth, CompositeLossFwd(), as_stream(stream));
+}
 
+int cnrf_composite_bwd_loss(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, const float* g_rgb,
+                            const float* g_disp, const float* g_acc, const float* g_weights, const float* g_depth, float* g_raw,
+                            float* g_z, float* g_rd, const CompositeLossBwd& lb, cudaStream_t st) {
+  CNRF_REQUIRE(raw && z && rd && g_raw, CNRF_E_NULL);
+  CNRF_REQUIRE(N > 0 && S > 0 && S <= 256, CNRF_E_SHAPE);
+  DISPATCH_NCH(S, CALL_BWD, raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights, g_depth, g_raw, g_z, g_rd, lb, st);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
 extern "C" int cnrf_composite_bwd(const float* raw, const float* z, const float* rd, int64_t N, int32_t S,
                                   const float* g_rgb, const float* g_disp, const float* g_acc, const float* g_weights,
                                   const float* g_depth, float* g_raw, float* g_z, float* g_rd, cnrf_stream_t stream) {
-  CNRF_REQUIRE(raw && z && rd && g_raw, CNRF_E_NULL);
-  CNRF_REQUIRE(N > 0 && S > 0 && S <= 256, CNRF_E_SHAPE);
-  DISPATCH_NCH(S, CALL_BWD, raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights, g_depth, g_raw, g_z, g_rd,
-               as_stream(stream));
-  CNRF_LAUNCH_CHECK();
-  return CNRF_OK;
+  return cnrf_composite_bwd_loss(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights, g_depth, g_raw, g_z, g_rd, CompositeLossBwd(),
+                                 as_stream(stream));
 }

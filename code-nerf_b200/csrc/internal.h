@@ -124,6 +124,32 @@ int cnrf_pair_bwd_chain(const CnrfPairIn& in, int which, const float* g_raw, con
 int cnrf_pair_bwd_finish(const CnrfPairIn& in, const cnrf_codenerf_grads* const g[2], float* g_z_s, float* g_z_t, void* side,
                          size_t side_bytes, cudaStream_t st);
 
+// ---- composite.cu: the photometric loss of train.py:103-104 folded into the compositing epilogues --------
+// target of ray n, channel c: rows[n * ld + c] (already gathered float rows), or -- the gather of train.py:77-80 fused as
+// well -- views[pixel[n] * channels + c] / 255.0 from uint8 views resident in HBM (data.cu: the loader's own arithmetic)
+struct LossTarget { const float* rows = nullptr; int64_t ld = 0; const uint8_t* views = nullptr; const int64_t* pixel = nullptr; int channels = 0; };
+struct CompositeLossFwd {
+  LossTarget t;
+  float* sq_sum = nullptr;          // += sum (rgb - target)^2 of this pass (zero-filled by the caller); NULL: no loss
+  float* out3 = nullptr;            // fine pass only: (coarse_loss, fine_loss, loss) written by the last warp to finish
+  const float* other_sq = nullptr;  // ... the coarse pass's sum
+  unsigned* done = nullptr;         // ... warps finished (zero-filled by the caller)
+  unsigned num_warps = 0;           // set by the launcher
+  float inv = 0.f;                  // 1 / (3 N)
+};
+struct CompositeLossBwd {
+  LossTarget t;
+  const float* rgb_out = nullptr;   // the forward's rgb [N,3]; NULL: the upstream gradient is g_rgb
+  const float* g_term = nullptr;    // device scalars (NULL = 0): d / d (this pass's loss term), d / d (the sum)
+  const float* g_sum = nullptr;
+  float scale = 0.f;                // 2 / (3 N)
+};
+int cnrf_composite_fwd_loss(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, float* rgb, float* disp,
+                            float* acc, float* weights, float* depth, const CompositeLossFwd& lf, cudaStream_t st);
+int cnrf_composite_bwd_loss(const float* raw, const float* z, const float* rd, int64_t N, int32_t S, const float* g_rgb,
+                            const float* g_disp, const float* g_acc, const float* g_weights, const float* g_depth, float* g_raw,
+                            float* g_z, float* g_rd, const CompositeLossBwd& lb, cudaStream_t st);
+
 // ---- posembed.cu -------------------------------------------------------------------------------------------------
 int cnrf_pos_embed_fwd_ld(const float* x, int64_t M, int D, const float* freqs, int L, int inc, int64_t ld_out,
                           float* out, cudaStream_t st);

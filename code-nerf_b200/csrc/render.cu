@@ -86,7 +86,7 @@ extern "C" size_t cnrf_render_workspace_bytes(const cnrf_render_shape* s, int32_
   size_t field = al256(fw > fwf ? fw : fwf) + 256;
   if (cnrf_pair_eligible(&fc, &ff)) field += al256(cnrf_pair_side_bytes(&fc, backward)) + 256;     // the two-model per-ray state
   if (!backward) {
-    size_t b = al256(d.N * d.Sc * 4) /*weights*/ + field + 512;
+    size_t b = al256(d.N * d.Sc * 4) /*weights*/ + 256 /*loss sums*/ + field + 512;
     if (!s->keep) b += kept_bytes(d, true);                       // inference: nothing is kept, everything is scratch
     else if (!d.f32) b += al256(d.N * d.Sc * 12) + al256(d.N * d.Sf * 12);     // bf16 training: points are scratch
     return b;
@@ -94,9 +94,24 @@ extern "C" size_t cnrf_render_workspace_bytes(const cnrf_render_shape* s, int32_
   return al256(d.N * d.Sf * 16) /*g_raw*/ + 2 * al256(d.N * (size_t)s->code * 4) /*coarse per-ray code gradients*/ + field + 512;
 }
 
-extern "C" int cnrf_render_fwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
-                               const cnrf_render_inputs* in, float* rgb_coarse, float* rgb_fine, float* extras_fine,
-                               void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+namespace {
+inline int loss_target_of(const cnrf_loss_target* t, LossTarget& lt) {
+  if (!t) return CNRF_E_NULL;
+  if (t->views) {
+    CNRF_REQUIRE(t->pixel && t->channels >= 3 && t->channels <= 4, CNRF_E_SHAPE);
+    lt.views = t->views; lt.pixel = t->pixel; lt.channels = t->channels;
+  } else {
+    CNRF_REQUIRE(t->rows && t->ld_rows >= 3, CNRF_E_SHAPE);
+    lt.rows = t->rows; lt.ld = t->ld_rows;
+  }
+  return CNRF_OK;
+}
+
+// tgt != NULL: the photometric loss of train.py:103-104 rides in the two compositing epilogues and lands in loss3
+int render_fwd_impl(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                    const cnrf_render_inputs* in, const cnrf_loss_target* tgt, float* loss3, float* rgb_coarse, float* rgb_fine,
+                    float* extras_fine, void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes,
+                    cnrf_stream_t stream) {
   RUN(check(s));
   CNRF_REQUIRE(coarse && fine && in && rgb_coarse && rgb_fine && workspace, CNRF_E_NULL);
   CNRF_REQUIRE(in->ro && in->rd && in->z_table && in->lower && in->upper && in->freqs_xyz && in->freqs_dir && in->z_s && in->z_t,
@@ -113,7 +128,17 @@ extern "C" int cnrf_render_fwd(const cnrf_render_shape* s, const cnrf_codenerf_p
     carve_kept(d, ws, true, k);
   }
   float* weights = ws.take(d.N * d.Sc);
+  float* loss_acc = ws.take(64);           // [0] coarse sum of squares, [1] fine, [2] warps of the fine pass that finished
   if (!ws.ok || (s->keep && !sv.ok)) return CNRF_E_WORKSPACE;
+  CompositeLossFwd lc, lf;
+  if (tgt) {
+    CNRF_REQUIRE(loss3, CNRF_E_NULL);
+    RUN(loss_target_of(tgt, lc.t));
+    lf.t = lc.t;
+    lc.sq_sum = loss_acc; lf.sq_sum = loss_acc + 1; lf.other_sq = loss_acc; lf.done = reinterpret_cast<unsigned*>(loss_acc + 2);
+    lf.out3 = loss3; lf.inv = 1.0f / (3.0f * (float)d.N);
+    RUN(cnrf_fill_zero(loss_acc, 3 * sizeof(float), as_stream(stream)));
+  }
   const cnrf_field_shape fc = field_shape(s, d.Sc, s->keep), ff = field_shape(s, d.Sf, s->keep);
   const size_t sb_c = s->keep ? al256(cnrf_codenerf_saved_bytes(&fc)) : 0, sb_f = s->keep ? al256(cnrf_codenerf_saved_bytes(&ff)) : 0;
   char* saved_c = s->keep ? static_cast<char*>(sv.rest()) : nullptr;
@@ -137,7 +162,7 @@ extern "C" int cnrf_render_fwd(const cnrf_render_shape* s, const cnrf_codenerf_p
   if (pair) RUN(cnrf_pair_fwd_chain(pin, 0, k.pts_c, k.raw_c, side, side_bytes, ws.rest(), ws.rest_bytes(), st));
   else RUN(cnrf_field_fwd_impl(&fc, coarse, k.pts_c, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
                                in->z_s, in->ld_zs, in->z_t, in->ld_zt, k.raw_c, saved_c, sb_c, ws.rest(), ws.rest_bytes(), st));
-  RUN(cnrf_composite_fwd(k.raw_c, k.z_c, in->rd, d.N, d.Sc, rgb_coarse, nullptr, nullptr, weights, nullptr, stream));
+  RUN(cnrf_composite_fwd_loss(k.raw_c, k.z_c, in->rd, d.N, d.Sc, rgb_coarse, nullptr, nullptr, weights, nullptr, lc, st));
   // fine pass: importance samples from weights[..., 1:-1]                                nerf/__init__.py:87-89
   RUN(cnrf_sample_pdf_fwd(in->ro, in->rd, weights + 1, d.Sc, k.z_c, d.N, d.Sc, s->num_fine, in->u, k.pts_f, k.z_f, nullptr, nullptr,
                           stream));
@@ -145,16 +170,36 @@ extern "C" int cnrf_render_fwd(const cnrf_render_shape* s, const cnrf_codenerf_p
   else RUN(cnrf_field_fwd_impl(&ff, fine, k.pts_f, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
                                in->z_s, in->ld_zs, in->z_t, in->ld_zt, k.raw_f, saved_f, sb_f, ws.rest(), ws.rest_bytes(), st));
   float* disp = extras_fine, *acc = extras_fine ? extras_fine + d.N : nullptr, *depth = extras_fine ? extras_fine + 2 * d.N : nullptr;
-  return cnrf_composite_fwd(k.raw_f, k.z_f, in->rd, d.N, d.Sf, rgb_fine, disp, acc, nullptr, depth, stream);
+  return cnrf_composite_fwd_loss(k.raw_f, k.z_f, in->rd, d.N, d.Sf, rgb_fine, disp, acc, nullptr, depth, lf, st);
+}
+}  // namespace
+
+extern "C" int cnrf_render_fwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                               const cnrf_render_inputs* in, float* rgb_coarse, float* rgb_fine, float* extras_fine,
+                               void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+  return render_fwd_impl(s, coarse, fine, in, nullptr, nullptr, rgb_coarse, rgb_fine, extras_fine, saved, saved_bytes, workspace,
+                         workspace_bytes, stream);
 }
 
-extern "C" int cnrf_render_bwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
-                               const cnrf_render_inputs* in, const float* g_rgb_coarse, const float* g_rgb_fine, const void* saved,
-                               size_t saved_bytes, const cnrf_codenerf_grads* g_coarse, const cnrf_codenerf_grads* g_fine,
-                               float* g_z_s, float* g_z_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+extern "C" int cnrf_render_loss_fwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                                    const cnrf_render_inputs* in, const cnrf_loss_target* target, float* loss3, float* rgb_coarse,
+                                    float* rgb_fine, void* saved, size_t saved_bytes, void* workspace, size_t workspace_bytes,
+                                    cnrf_stream_t stream) {
+  CNRF_REQUIRE(target && loss3, CNRF_E_NULL);
+  return render_fwd_impl(s, coarse, fine, in, target, loss3, rgb_coarse, rgb_fine, nullptr, saved, saved_bytes, workspace,
+                         workspace_bytes, stream);
+}
+
+namespace {
+// lbc / lbf: the upstream gradients of the two compositing passes come from the loss folded into the forward epilogues
+int render_bwd_impl(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                    const cnrf_render_inputs* in, const float* g_rgb_coarse, const float* g_rgb_fine, const CompositeLossBwd& lbc,
+                    const CompositeLossBwd& lbf, const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g_coarse,
+                    const cnrf_codenerf_grads* g_fine, float* g_z_s, float* g_z_t, void* workspace, size_t workspace_bytes,
+                    cnrf_stream_t stream) {
   RUN(check(s));
   CNRF_REQUIRE(coarse && fine && in && saved && g_coarse && g_fine && g_z_s && g_z_t && workspace, CNRF_E_NULL);
-  CNRF_REQUIRE(g_rgb_coarse || g_rgb_fine, CNRF_E_NULL);
+  CNRF_REQUIRE(g_rgb_coarse || g_rgb_fine || lbc.rgb_out || lbf.rgb_out, CNRF_E_NULL);
   CNRF_REQUIRE(in->rd && in->freqs_xyz && in->freqs_dir && in->z_s && in->z_t, CNRF_E_NULL);
   if (!s->keep) return CNRF_E_WORKSPACE;
   const Dims d = dims_of(s);
@@ -183,17 +228,17 @@ extern "C" int cnrf_render_bwd(const cnrf_render_shape* s, const cnrf_codenerf_p
     void* side = ws.take(side_bytes / sizeof(float));
     if (!ws.ok) return CNRF_E_WORKSPACE;
     RUN(cnrf_pair_bwd_prepare(pin, gs, side, side_bytes, st));
-    RUN(cnrf_composite_bwd(k.raw_f, k.z_f, in->rd, d.N, d.Sf, g_rgb_fine, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, stream));
+    RUN(cnrf_composite_bwd_loss(k.raw_f, k.z_f, in->rd, d.N, d.Sf, g_rgb_fine, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, lbf, st));
     RUN(cnrf_pair_bwd_chain(pin, 1, g_raw, g_fine, side, side_bytes, ws.rest(), ws.rest_bytes(), st));
-    RUN(cnrf_composite_bwd(k.raw_c, k.z_c, in->rd, d.N, d.Sc, g_rgb_coarse, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, stream));
+    RUN(cnrf_composite_bwd_loss(k.raw_c, k.z_c, in->rd, d.N, d.Sc, g_rgb_coarse, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, lbc, st));
     RUN(cnrf_pair_bwd_chain(pin, 0, g_raw, g_coarse, side, side_bytes, ws.rest(), ws.rest_bytes(), st));
     return cnrf_pair_bwd_finish(pin, gs, g_z_s, g_z_t, side, side_bytes, st);
   }
-  RUN(cnrf_composite_bwd(k.raw_f, k.z_f, in->rd, d.N, d.Sf, g_rgb_fine, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, stream));
+  RUN(cnrf_composite_bwd_loss(k.raw_f, k.z_f, in->rd, d.N, d.Sf, g_rgb_fine, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, lbf, st));
   RUN(cnrf_field_bwd_impl(&ff, fine, k.pts_f, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
                           in->z_s, in->ld_zs, in->z_t, in->ld_zt, g_raw, saved_f, sb_f, g_fine, g_z_s, g_z_t, nullptr, nullptr,
                           ws.rest(), ws.rest_bytes(), st, false));
-  RUN(cnrf_composite_bwd(k.raw_c, k.z_c, in->rd, d.N, d.Sc, g_rgb_coarse, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, stream));
+  RUN(cnrf_composite_bwd_loss(k.raw_c, k.z_c, in->rd, d.N, d.Sc, g_rgb_coarse, nullptr, nullptr, nullptr, nullptr, g_raw, nullptr, nullptr, lbc, st));
   // coarse model: table gradients are scatter-added onto the fine model's (shared-code mode); per-ray code gradients go
   // through a scratch pair and one add
   RUN(cnrf_field_bwd_impl(&fc, coarse, k.pts_c, in->rd, in->freqs_xyz, in->L_xyz, in->freqs_dir, in->L_dir, in->ids, in->num_codes,
@@ -208,4 +253,31 @@ extern "C" int cnrf_render_bwd(const cnrf_render_shape* s, const cnrf_codenerf_p
     CNRF_LAUNCH_CHECK();
   }
   return CNRF_OK;
+}
+}  // namespace
+
+extern "C" int cnrf_render_bwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                               const cnrf_render_inputs* in, const float* g_rgb_coarse, const float* g_rgb_fine, const void* saved,
+                               size_t saved_bytes, const cnrf_codenerf_grads* g_coarse, const cnrf_codenerf_grads* g_fine,
+                               float* g_z_s, float* g_z_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+  return render_bwd_impl(s, coarse, fine, in, g_rgb_coarse, g_rgb_fine, CompositeLossBwd(), CompositeLossBwd(), saved, saved_bytes,
+                         g_coarse, g_fine, g_z_s, g_z_t, workspace, workspace_bytes, stream);
+}
+
+extern "C" int cnrf_render_loss_bwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                                    const cnrf_render_inputs* in, const cnrf_loss_target* target, const float* rgb_coarse,
+                                    const float* rgb_fine, const float* g_loss_coarse, const float* g_loss_fine,
+                                    const float* g_loss_sum, const void* saved, size_t saved_bytes,
+                                    const cnrf_codenerf_grads* g_coarse, const cnrf_codenerf_grads* g_fine, float* g_z_s,
+                                    float* g_z_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
+  CNRF_REQUIRE(s && target && rgb_coarse && rgb_fine, CNRF_E_NULL);
+  CNRF_REQUIRE(g_loss_coarse || g_loss_fine || g_loss_sum, CNRF_E_NULL);
+  CompositeLossBwd lbc, lbf;
+  RUN(loss_target_of(target, lbc.t));
+  lbf.t = lbc.t;
+  lbc.rgb_out = rgb_coarse; lbc.g_term = g_loss_coarse; lbc.g_sum = g_loss_sum;
+  lbf.rgb_out = rgb_fine; lbf.g_term = g_loss_fine; lbf.g_sum = g_loss_sum;
+  lbc.scale = lbf.scale = 2.0f / (3.0f * (float)s->num_rays);
+  return render_bwd_impl(s, coarse, fine, in, nullptr, nullptr, lbc, lbf, saved, saved_bytes, g_coarse, g_fine, g_z_s, g_z_t,
+                         workspace, workspace_bytes, stream);
 }

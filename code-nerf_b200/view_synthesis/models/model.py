@@ -7,6 +7,8 @@ import torch
 
 from codenerf_b200 import _lib, ops
 
+_PRECISION_IDS = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16, "split": _lib.PRECISION_SPLIT}
+
 __all__ = ["FlexibleNeRFModel", "CodeNeRFModel", "ShapeTextureEmbedding", "get_params_tensor"]
 
 
@@ -69,7 +71,7 @@ class FlexibleNeRFModel(torch.nn.Module):
             x_xyz = ex.embed(x.pts.reshape(-1, x.pts.shape[-1]))
             viewdirs = x.rd / x.rd.norm(p=2, dim=-1).unsqueeze(-1)                       # nerf/__init__.py:126
             x_dir = ed.embed(viewdirs)
-            precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[x.precision]
+            precision = _PRECISION_IDS[x.precision]
             pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
             raw = ops.flexnerf(params, x_xyz, x_dir, self.num_layers, self.hidden_size, self.dim_xyz, self.dim_dir,
                                self._skip_mask(), S, pairing=pairing, precision=precision)
@@ -213,7 +215,7 @@ class CodeNeRFModel(torch.nn.Module):
             ex, ed = x.embedder_xyz, x.embedder_dir
             assert 3 * ex.out_dim_per_channel == self.dim_xyz and 3 * ed.out_dim_per_channel == self.dim_dir, \
                 "embedder widths do not match the model's dim_xyz / dim_dir"
-            precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[x.precision]
+            precision = _PRECISION_IDS[x.precision]
             pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
             src = _code_source(z_s, z_t)
             return ops.codenerf_field(params, x.pts, x.rd, z_s, z_t, ex.frequency_bands, ed.frequency_bands,
@@ -230,7 +232,7 @@ class CodeNeRFModel(torch.nn.Module):
         ex, ed, ps = q.embedder_xyz, q.embedder_dir, q.point_sampler
         assert 3 * ex.out_dim_per_channel == self.dim_xyz and 3 * ed.out_dim_per_channel == self.dim_dir, \
             "embedder widths do not match the model's dim_xyz / dim_dir"
-        precision = {"fp32": _lib.PRECISION_FP32, "bf16": _lib.PRECISION_BF16}[q.precision]
+        precision = _PRECISION_IDS[q.precision]
         pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[q.pairing]
         src = _code_source(z_s, z_t) if precision == _lib.PRECISION_BF16 else None
         ids = None
@@ -239,6 +241,8 @@ class CodeNeRFModel(torch.nn.Module):
         spec = ops.RenderSpec(self.hidden_size, self.shape_code_size, self.dim_xyz, self.dim_dir, ps.num_samples_coarse,
                               ps.num_samples_fine, pairing, precision, ps.z_vals, ps.lower, ps.upper, ex.frequency_bands,
                               ed.frequency_bands, ids=ids)
+        if q.loss_target is not None:
+            return ops.render_loss(spec, q.loss_target, q.ro, q.rd, q.t_rand, q.u, z_s, z_t, q.coarse.params, params)
         return ops.render(spec, q.ro, q.rd, q.t_rand, q.u, z_s, z_t, q.coarse.params, params)
 
     def _as_written(self, params, z_s, z_t, x, lead):

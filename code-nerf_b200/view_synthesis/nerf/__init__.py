@@ -57,12 +57,14 @@ class RenderQuery(object):
     through `coarse_model(z_s, z_t, query)` first (query.coarse is None -> the model returns its parameter token), then
     through `fine_model(z_s, z_t, query)` with the token attached -> (rgb_coarse, rgb_fine).  Both calls go through the
     modules' __call__, hence through DistributedDataParallel.forward when the caller wrapped them."""
-    __slots__ = ("ro", "rd", "point_sampler", "embedder_xyz", "embedder_dir", "precision", "pairing", "t_rand", "u", "coarse")
+    __slots__ = ("ro", "rd", "point_sampler", "embedder_xyz", "embedder_dir", "precision", "pairing", "t_rand", "u", "coarse",
+                 "loss_target")
 
-    def __init__(self, ro, rd, point_sampler, embedder_xyz, embedder_dir, precision, pairing, t_rand, u):
+    def __init__(self, ro, rd, point_sampler, embedder_xyz, embedder_dir, precision, pairing, t_rand, u, loss_target=None):
         self.ro, self.rd, self.point_sampler = ro, rd, point_sampler
         self.embedder_xyz, self.embedder_dir, self.precision, self.pairing = embedder_xyz, embedder_dir, precision, pairing
         self.t_rand, self.u, self.coarse = t_rand, u, None
+        self.loss_target = loss_target      # codenerf_b200.ops.LossTargetSpec: fold train.py:103-104's loss into the call
 
 
 def _fused_render_ok(rays, point_sampler, embedders, coarse_model, fine_model) -> bool:
@@ -143,6 +145,34 @@ def predict_radiance_and_render(rays, point_sampler: PointSampler, embedders, co
     radiance_field_fine = forward_pass(fine_model, embedders, rd, pts_fine, latent_embedding)
     (rgb_fine, _, _, _, _) = volume_render(radiance_field_fine, z_vals_fine, rd)
     return rgb_coarse, rgb_fine
+
+
+def predict_radiance_render_and_loss(rays, point_sampler: PointSampler, embedders, coarse_model: torch.nn.Module,
+                                     fine_model: torch.nn.Module, latent_embedding, target_pixels=None, views_u8=None,
+                                     pixel_index=None):
+    """Not in the reference: predict_radiance_and_render plus the photometric loss of
+    train.py:103-104 with the loss -- and, given `views_u8` / `pixel_index`, the target-pixel gather of train.py:77-80 --
+    folded into the compositing epilogues.  -> (coarse_loss, fine_loss, loss, rgb_coarse, rgb_fine); the rgb tensors are
+    detached (their gradient is the loss's).  Targets: `target_pixels` (N, >= 3) float rows, or uint8 views (..., C) resident
+    on the device (codenerf_b200.data.DeviceSRN.colors_u8) with `pixel_index` (N,) int64 = view * H W + selected pixel.
+    Callers the fused entry does not serve (pose gradients, other model classes) get the staged composition."""
+    from codenerf_b200 import ops
+    (ro, rd) = rays
+    if _fused_render_ok(rays, point_sampler, embedders, coarse_model, fine_model):
+        t_rand, u = point_sampler.draw_offsets(ro.shape[0], ro.dtype, ro.device)
+        target = ops.LossTargetSpec(rows=target_pixels, views=views_u8, pixel=pixel_index)
+        query = RenderQuery(ro, rd, point_sampler, embedders[0], embedders[1], _state["precision"], _state["pairing"], t_rand, u,
+                            loss_target=target)
+        z_s, z_t = latent_embedding
+        query.coarse = coarse_model(z_s, z_t, query)
+        coarse_loss, fine_loss, loss, rgb = fine_model(z_s, z_t, query)
+        return coarse_loss, fine_loss, loss, rgb[0], rgb[1]
+    rgb_coarse, rgb_fine = predict_radiance_and_render(rays, point_sampler, embedders, coarse_model, fine_model, latent_embedding)
+    if target_pixels is None:
+        flat = views_u8.reshape(-1, views_u8.shape[-1])
+        target_pixels = flat[pixel_index].to(torch.float64).div(255.0).to(torch.float32)
+    coarse_loss, fine_loss, loss = ops.mse_pair(rgb_coarse, rgb_fine, target_pixels)
+    return coarse_loss, fine_loss, loss, rgb_coarse.detach(), rgb_fine.detach()
 
 
 def forward_pass(model: torch.nn.Module, embedders, rd, pts: torch.Tensor, object_embedding) -> torch.Tensor:

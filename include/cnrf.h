@@ -373,6 +373,36 @@ int cnrf_render_bwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coar
                     float* g_z_s, float* g_z_t, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
+ * predict_radiance_and_render + the photometric loss of the training loop in one call per direction (SURVEY section 8
+ * row f2; reference: train.py:77-80 gathers the selected target pixels, train.py:103-104 computes
+ * mse_loss(rgb_coarse[..., :3], target[..., :3]) + mse_loss(rgb_fine[..., :3], target[..., :3])).  The squared errors are
+ * accumulated in the epilogues of the two compositing kernels (warp sums added atomically: the last bits of the loss
+ * depend on the summation order) and the last warp of the fine pass writes
+ *   loss3 = (coarse_loss, fine_loss, coarse_loss + fine_loss);
+ * the backward forms d loss / d rgb = (g_loss_term + g_loss_sum) * 2 (rgb - target) / (3 N) inside the compositing
+ * backward from the forward's rgb outputs, so neither the [N,3] gradients nor (uint8 form) the gathered float targets exist.
+ * Target of ray n: rows[n * ld_rows + c], c < 3 (rows already gathered; RGBA rows: ld_rows = 4), or, when views != NULL,
+ * views[pixel[n] * channels + c] / 255.0 computed as the loader does (float64 division, float32 cast:
+ * datasets/dataset.py:72,90) from uint8 views resident in device memory; pixel[n] = view index * H W + selected pixel.
+ * Workspace / saved sizes are those of cnrf_render_fwd / _bwd.
+ * ---------------------------------------------------------------------------------------------------- */
+typedef struct {
+  const float* rows; int64_t ld_rows;
+  const uint8_t* views; const int64_t* pixel; int32_t channels;
+} cnrf_loss_target;
+int cnrf_render_loss_fwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                         const cnrf_render_inputs* in, const cnrf_loss_target* target, float* loss3 /*[3]*/,
+                         float* rgb_coarse /*[N,3]*/, float* rgb_fine /*[N,3]*/, void* saved, size_t saved_bytes, void* workspace,
+                         size_t workspace_bytes, cnrf_stream_t stream);
+/* g_loss_*: device scalars, the gradients of the three numbers of loss3 (any may be NULL = 0, not all) */
+int cnrf_render_loss_bwd(const cnrf_render_shape* s, const cnrf_codenerf_params* coarse, const cnrf_codenerf_params* fine,
+                         const cnrf_render_inputs* in, const cnrf_loss_target* target, const float* rgb_coarse,
+                         const float* rgb_fine, const float* g_loss_coarse, const float* g_loss_fine, const float* g_loss_sum,
+                         const void* saved, size_t saved_bytes, const cnrf_codenerf_grads* g_coarse,
+                         const cnrf_codenerf_grads* g_fine, float* g_z_s, float* g_z_t, void* workspace, size_t workspace_bytes,
+                         cnrf_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------------
  * Diagnostics (used by tests only).  One-CTA tcgen05 GEMM over the 128-byte-swizzled shared-memory image the fused
  * MLP kernels use.  mode 0: D[128,N] = A[128,K] B[N,K]^T (K-major operands); mode 1: D[128,N] = A[K,128]^T B[K,N]
  * (MN-major operands, the dW = dY^T X form).  *err is set to 1 if the kernel's bounded barrier wait timed out.
