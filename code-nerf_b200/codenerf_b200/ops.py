@@ -362,16 +362,19 @@ class _Field(torch.autograd.Function):
         shp = _shape(hidden, code, dim_xyz, dim_dir, N, S, pairing, precision, 1)
         g_raw = _c(g_raw)
         dev = pts.device
-        grads = tuple(torch.empty_like(p) for p in params)
+        # a frozen network (eval.py:121-124) needs no weight gradients: the fp32-layout chains then skip those GEMMs
+        frozen = precision != _lib.PRECISION_BF16 and not any(ctx.needs_input_grad[7:])
+        grads = (None,) * len(params) if frozen else tuple(torch.empty_like(p) for p in params)
         g_zs = torch.empty((N, code), dtype=_f32, device=dev)
         g_zt = torch.empty((N, code), dtype=_f32, device=dev)
         g_pts = torch.empty_like(pts) if ctx.needs_input_grad[1] else None
         g_rd = torch.empty_like(rd) if ctx.needs_input_grad[2] else None
         ws = _bytes(lib.cnrf_field_workspace_bytes(C.byref(shp), 1), dev)
-        tab, gtab = _ptr_table(params), _ptr_table(grads)
+        tab = _ptr_table(params)
+        gtab = None if frozen else C.byref(_ptr_table(grads))
         check(lib.cnrf_field_bwd(C.byref(shp), C.byref(tab), _p(pts), _p(rd), _p(freqs_xyz), freqs_xyz.shape[0],
                                  _p(freqs_dir), freqs_dir.shape[0], _p(z_s), ld_zs, _p(z_t), ld_zt, _p(g_raw), _p(saved),
-                                 saved.numel(), C.byref(gtab), _p(g_zs), _p(g_zt), _p(g_pts), _p(g_rd), _p(ws),
+                                 saved.numel(), gtab, _p(g_zs), _p(g_zt), _p(g_pts), _p(g_rd), _p(ws),
                                  ws.numel(), _stream()), "cnrf_field_bwd")
         return (None, g_pts, g_rd, g_zs, g_zt, None, None) + grads
 

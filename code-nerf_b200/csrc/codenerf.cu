@@ -277,6 +277,7 @@ int per_ray_bwd_add(int level, const Dims& d, const cnrf_codenerf_params* p, con
   const int H = d.H, C = d.C;
   const size_t nc = al(d.N * C) / sizeof(float);
   float *tmp_t = tmp, *tmp_s2 = tmp + nc, *tmp_s1 = tmp + 2 * nc, *ones = tmp + 3 * nc;
+  if (d.tc && !g) return CNRF_E_NULL;
   if (level == 0) {
     if (d.tc) {     // unfold:  d Wdf = d Wfh Wout'h^T (+ d betaf^T betao' below),  d Wout'h = Wdf^T d Wfh,  d betao' = d betaf Wdf
       if (!bof) return CNRF_E_NULL;
@@ -288,14 +289,14 @@ int per_ray_bwd_add(int level, const Dims& d, const cnrf_codenerf_params* p, con
     if (d.tc) b.add(mk_wgrad(dt.bf, H, bof, C, d.N, H, C, g->weight[CNRF_L_DIR1], C + d.dd));     // += onto the product above
     // texture branch: betar = Wrt at + br;   shape branch 2: betao = Woc as2 + bo;   shape branch 1: beta2 = W2c as1 + b2;
     // view-direction half of layer_dir1: betad = Wdv gamma(d) + bd1
-    b.add(mk_wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C));
+    if (g) b.add(mk_wgrad(dt.br, 3, at, C, d.N, 3, C, g->weight[CNRF_L_FC_RGB] + H, H + C));
     b.add(mk_dgrad(dt.br, 3, d.N, 3, p->weight[CNRF_L_FC_RGB] + H, H + C, C, tmp_t, C, at, C, 0));
-    b.add(mk_wgrad(dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C));
+    if (g) b.add(mk_wgrad(dt.bo, C + 1, as2, C, d.N, C + 1, C, g->weight[CNRF_L_FC_OUT] + H, H + C));
     b.add(mk_dgrad(dt.bo, C + 1, d.N, C + 1, p->weight[CNRF_L_FC_OUT] + H, H + C, C, tmp_s2, C, as2, C, 0));
-    b.add(mk_wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C));
+    if (g) b.add(mk_wgrad(dt.b2, H, as1, C, d.N, H, C, g->weight[CNRF_L_XYZ2] + H, H + C));
     b.add(mk_dgrad(dt.b2, H, d.N, H, p->weight[CNRF_L_XYZ2] + H, H + C, C, tmp_s1, C, as1, C, 0));
     if (d.rows_dev && g_x_dir) return CNRF_E_UNSUPPORTED;   // shared-code rays carry no pose gradient
-    if (!d.tc) b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
+    if (!d.tc && g) b.add(mk_wgrad(dt.bd, H, x_dir, ld_dir, d.N, H, d.dd, g->weight[CNRF_L_DIR1] + C, C + d.dd));
     if (g_x_dir) b.add(mk_dgrad(dt.bd, H, d.N, H, p->weight[CNRF_L_DIR1] + C, C + d.dd, d.dd, g_x_dir, d.dd, nullptr, 0, 0));
     if (d.tc) {
       b.add(mk_colsum(ones, dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB]));
@@ -304,10 +305,10 @@ int per_ray_bwd_add(int level, const Dims& d, const cnrf_codenerf_params* p, con
     }
   } else {
     // the three latent-code layers
-    b.add(mk_wgrad(tmp_t, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C));
+    if (g) b.add(mk_wgrad(tmp_t, C, z_t, ld_zt, d.N, C, C, g->weight[CNRF_L_TEXTURE1], C));
     b.add(mk_dgrad(tmp_t, C, d.N, C, p->weight[CNRF_L_TEXTURE1], C, C, g_z_t, C, nullptr, 0, acc_codes ? 1 : 0));
-    b.add(mk_wgrad(tmp_s2, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C));
-    b.add(mk_wgrad(tmp_s1, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C));
+    if (g) b.add(mk_wgrad(tmp_s2, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE2], C));
+    if (g) b.add(mk_wgrad(tmp_s1, C, z_s, ld_zs, d.N, C, C, g->weight[CNRF_L_SHAPE1], C));
     // both shape branches land in g_z_s: added atomically onto the zero-filled buffer when they share a launch
     b.add(mk_dgrad(tmp_s2, C, d.N, C, p->weight[CNRF_L_SHAPE2], C, C, g_z_s, C, nullptr, 0, d.tc ? 1 : 0));
     b.add(mk_dgrad(tmp_s1, C, d.N, C, p->weight[CNRF_L_SHAPE1], C, C, g_z_s, C, nullptr, 0, 1));
@@ -321,6 +322,7 @@ int per_ray_bwd_add(int level, const Dims& d, const cnrf_codenerf_params* p, con
 }
 int per_ray_bwd_colsums(int level, const Dims& d, const cnrf_codenerf_grads* g, const Tables& dt, const float* tmp, cudaStream_t st) {
   const int H = d.H, C = d.C;
+  if (!g) return CNRF_OK;
   const size_t nc = al(d.N * C) / sizeof(float);
   if (level == 1) {
     RUN(cnrf_colsum(dt.br, 3, d.N, 3, g->bias[CNRF_L_FC_RGB], st));
@@ -378,30 +380,30 @@ int chain_bwd_f32(const Dims& d, const cnrf_codenerf_params* p, const cnrf_coden
                   float* g_x_xyz, cudaStream_t st) {
   const int H = d.H, C = d.C;
   // fc_rgb
-  RUN(wgrad(d.split, g_raw, 4, s.v2, H, d.M, 3, H, g->weight[CNRF_L_FC_RGB], H + C, st));
+  if (g) RUN(wgrad(d.split, g_raw, 4, s.v2, H, d.M, 3, H, g->weight[CNRF_L_FC_RGB], H + C, st));
   RUN(cnrf_strided_rowsum(g_raw, 4, d.N, d.S, d.S, 1, 3, dt.br, 3, st));
   RUN(dgrad(d.split, g_raw, 4, d.M, 3, p->weight[CNRF_L_FC_RGB], H + C, H, ga, H, s.v2, H, 0, st));
   // layer_dir2
-  RUN(wgrad(d.split, ga, H, s.v1, H, d.M, H, H, g->weight[CNRF_L_DIR2], H, st));
-  RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_DIR2], st));
+  if (g) RUN(wgrad(d.split, ga, H, s.v1, H, d.M, H, H, g->weight[CNRF_L_DIR2], H, st));
+  if (g) RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_DIR2], st));
   RUN(dgrad(d.split, ga, H, d.M, H, p->weight[CNRF_L_DIR2], H, H, gb, H, s.v1, H, 0, st));
   // layer_dir1 (feature half)
-  RUN(wgrad(d.split, gb, H, s.o + 1, C + 1, d.M, H, C, g->weight[CNRF_L_DIR1], C + d.dd, st));
+  if (g) RUN(wgrad(d.split, gb, H, s.o + 1, C + 1, d.M, H, C, g->weight[CNRF_L_DIR1], C + d.dd, st));
   if (d.pairing == CNRF_PAIRING_REFERENCE) RUN(cnrf_strided_rowsum(gb, H, d.N, 1, d.S, d.N, H, dt.bd, H, st));
   else RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.bd, H, st));
   RUN(dgrad(d.split, gb, H, d.M, H, p->weight[CNRF_L_DIR1], C + d.dd, C, ga + 1, C + 1, nullptr, 0, 0, st));
   RUN(copy_col(g_raw + 3, 4, ga, C + 1, d.M, st));                       // d sigma_raw -> column 0 of d o
   // fc_out
-  RUN(wgrad(d.split, ga, C + 1, s.h2, H, d.M, C + 1, H, g->weight[CNRF_L_FC_OUT], H + C, st));
+  if (g) RUN(wgrad(d.split, ga, C + 1, s.h2, H, d.M, C + 1, H, g->weight[CNRF_L_FC_OUT], H + C, st));
   RUN(cnrf_strided_rowsum(ga, C + 1, d.N, d.S, d.S, 1, C + 1, dt.bo, C + 1, st));
   RUN(dgrad(d.split, ga, C + 1, d.M, C + 1, p->weight[CNRF_L_FC_OUT], H + C, H, gb, H, s.h2, H, 0, st));
   // layer_xyz2
-  RUN(wgrad(d.split, gb, H, s.h1, H, d.M, H, H, g->weight[CNRF_L_XYZ2], H + C, st));
+  if (g) RUN(wgrad(d.split, gb, H, s.h1, H, d.M, H, H, g->weight[CNRF_L_XYZ2], H + C, st));
   RUN(cnrf_strided_rowsum(gb, H, d.N, d.S, d.S, 1, H, dt.b2, H, st));
   RUN(dgrad(d.split, gb, H, d.M, H, p->weight[CNRF_L_XYZ2], H + C, H, ga, H, s.h1, H, 0, st));
   // layer_xyz1
-  RUN(wgrad(d.split, ga, H, x_xyz, ld_xyz, d.M, H, d.dx, g->weight[CNRF_L_XYZ1], d.dx, st));
-  RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_XYZ1], st));
+  if (g) RUN(wgrad(d.split, ga, H, x_xyz, ld_xyz, d.M, H, d.dx, g->weight[CNRF_L_XYZ1], d.dx, st));
+  if (g) RUN(cnrf_colsum(ga, H, d.M, H, g->bias[CNRF_L_XYZ1], st));
   if (g_x_xyz) RUN(dgrad(d.split, ga, H, d.M, H, p->weight[CNRF_L_XYZ1], d.dx, d.dx, g_x_xyz, d.dx, nullptr, 0, 0, st));
   return CNRF_OK;
 }
@@ -563,7 +565,8 @@ int codenerf_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
   w.take(d.N * d.C); w.take(d.N * d.C); w.take(d.N);
   if (!w.ok) return CNRF_E_WORKSPACE;
   if (in.ids && s->precision != CNRF_PRECISION_BF16) return CNRF_E_UNSUPPORTED;
-  RUN(zero_weight_grads(d, g, st));
+  if (!g && !fp32_layout(s)) return CNRF_E_NULL;       // only the fp32-layout chains skip the weight gradients of a frozen network
+  if (g) RUN(zero_weight_grads(d, g, st));
   if (fp32_layout(s)) {
     SavedF32 sv;
     if (!carve_saved(d, const_cast<void*>(saved), saved_bytes, sv)) return CNRF_E_WORKSPACE;
@@ -637,7 +640,7 @@ extern "C" int cnrf_codenerf_bwd(const cnrf_field_shape* s, const cnrf_codenerf_
                                  float* g_x_xyz, float* g_x_dir, void* workspace, size_t workspace_bytes,
                                  cnrf_stream_t stream) {
   RUN(check_common(s, p));
-  CNRF_REQUIRE(x_xyz && x_dir && z_s && z_t && g_raw && g && g_z_s && g_z_t && workspace, CNRF_E_NULL);
+  CNRF_REQUIRE(x_xyz && x_dir && z_s && z_t && g_raw && g_z_s && g_z_t && workspace, CNRF_E_NULL);
   FieldIn in{x_xyz, ld_xyz, x_dir, ld_dir, z_s, ld_zs, z_t, ld_zt, nullptr, nullptr, 0, 0};
   return codenerf_bwd_impl(s, p, in, g_raw, saved, saved_bytes, g, g_z_s, g_z_t, g_x_xyz, g_x_dir, workspace,
                            workspace_bytes, as_stream(stream));
@@ -732,7 +735,7 @@ int cnrf_field_bwd_impl(const cnrf_field_shape* s, const cnrf_codenerf_params* p
   RUN(check_common(s, p));
   // the bf16 chain saved its own encoded inputs: the points are only read again in the fp32 mode or for point gradients
   CNRF_REQUIRE((pts || (s->precision == CNRF_PRECISION_BF16 && !g_pts)) && rd && freqs_xyz && freqs_dir && z_s && z_t && g_raw &&
-               g && g_z_s && g_z_t && workspace, CNRF_E_NULL);
+               g_z_s && g_z_t && workspace, CNRF_E_NULL);
   int incx, incd;
   RUN(check_field(s, L_xyz, L_dir, incx, incd));
   Dims d = dims_of(s);

@@ -174,7 +174,9 @@ int cnrf_codenerf_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, 
                       const float* x_dir, int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t,
                       int64_t ld_zt, float* raw /*[M,4]*/, void* saved, size_t saved_bytes, void* workspace,
                       size_t workspace_bytes, cnrf_stream_t stream);
-/* g_z_s, g_z_t: dense [N, C].  g_x_xyz [M, dim_xyz] / g_x_dir [N, dim_dir] may be NULL when not needed. */
+/* g_z_s, g_z_t: dense [N, C].  g_x_xyz [M, dim_xyz] / g_x_dir [N, dim_dir] may be NULL when not needed.
+ * g may be NULL in CNRF_PRECISION_FP32 / _SPLIT: a frozen network (eval.py:121-124 sets requires_grad_(False) on both models
+ * before the test-time optimisation) -- no weight-gradient GEMM or reduction is launched; CNRF_PRECISION_BF16 returns CNRF_E_NULL. */
 int cnrf_codenerf_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* x_xyz, int64_t ld_xyz,
                       const float* x_dir, int64_t ld_dir, const float* z_s, int64_t ld_zs, const float* z_t,
                       int64_t ld_zt, const float* g_raw /*[M,4]*/, const void* saved, size_t saved_bytes,
@@ -189,7 +191,8 @@ int cnrf_field_fwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, con
                    const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const float* z_s,
                    int64_t ld_zs, const float* z_t, int64_t ld_zt, float* raw /*[N,S,4]*/, void* saved,
                    size_t saved_bytes, void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
-/* g_pts [N,S,3] / g_rd [N,3] may be NULL (training: rays carry no gradient; test-time pose optimisation needs them). */
+/* g_pts [N,S,3] / g_rd [N,3] may be NULL (training: rays carry no gradient; test-time pose optimisation needs them).
+ * g may be NULL for a frozen network in CNRF_PRECISION_FP32 / _SPLIT (see cnrf_codenerf_bwd). */
 int cnrf_field_bwd(const cnrf_field_shape* s, const cnrf_codenerf_params* p, const float* pts, const float* rd,
                    const float* freqs_xyz, int32_t L_xyz, const float* freqs_dir, int32_t L_dir, const float* z_s,
                    int64_t ld_zs, const float* z_t, int64_t ld_zt, const float* g_raw, const void* saved,

@@ -119,6 +119,13 @@ def measure(N=524288, reps=20, dev=None, verbose=True):
     ro_b, rd_b = torch.empty(B * H * W, 3, **f32), torch.empty(B * H * W, 3, **f32)
     ms = timed(lambda: lib.cnrf_ray_bundle_fwd(_p(pose), B, H, W, 131.25, 64.0, 64.0, None, H * W, _p(ro_b), _p(rd_b), _stream()))
     report("ray_bundle 128x128 images", 24, ms, n=B * H * W)
+    # what a write-only stream of that size reaches on this GPU (the peak in the last column is a COPY figure: read + write):
+    # cudaMemsetAsync over the same two buffers (24 B/ray as well)
+    def _memset():
+        ro_b.zero_(); rd_b.zero_()
+        return 0
+    ms = timed(_memset)
+    report("reference: memset of the same 24 B/ray (write-only ceiling)", 24, ms, n=B * H * W)
 
     return rows
 

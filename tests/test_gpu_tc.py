@@ -371,3 +371,43 @@ def test_tc_pose_gradients_match_fp32(dev, N, S, pairing, monkeypatch):
     finally:
         nerf.set_pairing("reference")
         nerf.set_precision("fp32")
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pose_precision", ["fp32", "split"])
+def test_frozen_network_skips_weight_gradients(dev, pose_precision, monkeypatch):
+    """eval.py:121-124 freezes both networks before the test-time optimisation of codes and pose.  The fp32-layout chains
+    then launch no weight-gradient GEMM (cnrf_field_bwd with g = NULL): the ray / point / code gradients are the same
+    launches on the same operands as with trainable networks -- bit-identical -- and the parameters get no .grad."""
+    import view_synthesis.nerf as nerf
+    from codenerf_b200 import _lib
+    monkeypatch.setenv("CODENERF_POSE_GRAD_PRECISION", pose_precision)
+    N, S = 200, 64
+    g = torch.Generator().manual_seed(77)
+    ro0, rd0 = torch.randn(N, 3, generator=g) * 0.1, torch.randn(N, 3, generator=g)
+    z = (torch.rand(N, S, generator=g) + 0.3).to(dev)
+    codes0 = [torch.randn(1, 256, generator=g), torch.randn(1, 256, generator=g)]
+    graw = (torch.rand(N, S, 4, generator=g) + 0.5).to(dev)
+    nerf.set_precision("bf16")
+    res = {}
+    try:
+        for frozen in (False, True):
+            m = _models(dev)
+            if frozen:
+                m.requires_grad_(False)
+            ro, rd = ro0.clone().to(dev).requires_grad_(True), rd0.clone().to(dev).requires_grad_(True)
+            codes = [c.clone().to(dev).requires_grad_(True) for c in codes0]
+            pts = ro[:, None, :] + rd[:, None, :] * z[..., None]
+            n0 = _lib.load().cnrf_launch_count()
+            raw = nerf.forward_pass(m, _embedders(dev), rd, pts, tuple(c.expand(N, -1) for c in codes))
+            raw.backward(graw)
+            torch.cuda.synchronize()
+            res[frozen] = (raw.detach(), ro.grad, rd.grad, codes[0].grad, codes[1].grad, _lib.load().cnrf_launch_count() - n0,
+                           [p.grad for p in m.parameters()])
+        for a, b in zip(res[True][:5], res[False][:5]):
+            assert torch.equal(a, b)
+        assert all(gp is None for gp in res[True][6]) and all(gp is not None for gp in res[False][6])
+        assert res[True][5] < res[False][5], (res[True][5], res[False][5])
+        print(f"\nlaunches with trainable / frozen networks ({pose_precision}): {res[False][5]} / {res[True][5]}")
+    finally:
+        nerf.set_precision("fp32")
