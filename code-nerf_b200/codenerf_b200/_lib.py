@@ -122,6 +122,7 @@ _SIGS = {
     "cnrf_flexnerf_bwd": (C.c_int, [C.POINTER(FlexShape), C.POINTER(FlexPtrs), c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p,
                                     c_sz, C.POINTER(FlexPtrs), c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
     "cnrf_adamw_step": (C.c_int, [C.c_void_p, c_i32, c_f, c_f, c_f, C.c_void_p]),
+    "cnrf_adamw_step_dev": (C.c_int, [C.c_void_p, c_i32, c_f, c_f, c_f, C.c_void_p, C.c_void_p]),
     "cnrf_mse_pair_fwd": (C.c_int, [c_f32p, c_i64, c_f32p, c_i64, c_f32p, c_i64, c_i64, c_f32p, C.c_void_p]),
     "cnrf_mse_pair_bwd": (C.c_int, [c_f32p, c_i64, c_f32p, c_i64, c_f32p, c_i64, c_i64, c_f32p, c_f32p, c_f32p, c_f32p, c_f32p,
                                     C.c_void_p]),

@@ -296,6 +296,11 @@ typedef struct {
 } cnrf_adamw_tensor;
 int cnrf_adamw_step(const cnrf_adamw_tensor* tensors, int32_t count, float beta1, float beta2, float eps,
                     cnrf_stream_t stream);
+/* The same step with the step count on the DEVICE (what torch.optim.AdamW(capturable=True) does): *step_dev is
+ * incremented by a one-thread launch and the bias corrections are computed from it inside the kernel, so the launch
+ * sequence can be captured in a CUDA graph and replayed (tensors[i].step is ignored; every tensor shares the count). */
+int cnrf_adamw_step_dev(const cnrf_adamw_tensor* tensors, int32_t count, float beta1, float beta2, float eps,
+                        int64_t* step_dev, cnrf_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------------
  * Device-resident dataset stage (reference: view_synthesis/datasets/dataset.py:70-74,90 decode a
