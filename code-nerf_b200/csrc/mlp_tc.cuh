@@ -26,13 +26,24 @@ constexpr int NTHREADS = 384;
 constexpr int STORE_WARP = 11;
 __device__ __forceinline__ int producer_index(int warp) { return warp == 0 ? 0 : warp == 10 ? 1 : -1; }
 // one warp copies `bytes` (a multiple of 4 KB) of a shared-memory image to global memory
+// (-DCNRF_EXP_NO_STG / -DCNRF_EXP_NO_COPY: attribution builds of scripts/exp_fwd_store_attribution.sh -- wrong results, right timing)
 __device__ __forceinline__ void warp_copy_image(uint8_t* __restrict__ dst, const uint8_t* src_smem, int bytes, int lane) {
+#ifdef CNRF_EXP_NO_COPY
+  return;
+#endif
   for (int off = lane * 16; off < bytes; off += 8 * 512) {
     uint4 v[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) v[j] = *reinterpret_cast<const uint4*>(src_smem + off + j * 512);
+#ifdef CNRF_EXP_NO_STG
+    uint32_t acc = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc |= v[j].x ^ v[j].y ^ v[j].z ^ v[j].w;
+    if (acc == 0x12345u) __stcs(reinterpret_cast<uint4*>(dst + off), v[0]);
+#else
 #pragma unroll
     for (int j = 0; j < 8; ++j) __stcs(reinterpret_cast<uint4*>(dst + off + j * 512), v[j]);
+#endif
   }
 }
 // fc_out is FOLDED into layer_dir1 (models/model.py:182-189 apply no activation between them): the per-sample chain has four
