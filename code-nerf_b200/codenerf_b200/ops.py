@@ -465,6 +465,18 @@ def codenerf_field(params, pts, rd, z_s, z_t, freqs_xyz, freqs_dir, hidden, code
 # ----------------------------------------------------------------------------------------------------------
 # The whole pipeline of predict_radiance_and_render (nerf/__init__.py:74-91) as one library call per direction
 # ----------------------------------------------------------------------------------------------------------
+def _flat_grads(params, dev):
+    """One allocation for all parameter gradients, every gradient 16-byte aligned inside it (fc_out's 257-element bias would
+    otherwise leave everything behind it on 4-byte boundaries: the weight-gradient kernel's vector reductions and FusedAdamW's
+    float4 path both want aligned rows)."""
+    offs, total = [], 0
+    for p in params:
+        offs.append(total)
+        total += (p.numel() + 3) & ~3
+    flat = torch.empty((total,), dtype=_f32, device=dev)
+    return flat, tuple(flat[o:o + p.numel()].view_as(p) for o, p in zip(offs, params))
+
+
 class RenderSpec(object):
     """Everything about one fused render call that is not a differentiable tensor."""
     __slots__ = ("hidden", "code", "dim_xyz", "dim_dir", "num_coarse", "num_fine", "pairing", "precision", "z_table", "lower",
@@ -545,9 +557,7 @@ class _Render(torch.autograd.Function):
         g_f = _c(g_f) if g_f is not None else None
         shp = RenderShape(spec.hidden, spec.code, spec.dim_xyz, spec.dim_dir, N, spec.num_coarse, spec.num_fine, spec.pairing,
                           spec.precision, 1)
-        sizes = [p.numel() for p in params]
-        flat = torch.empty((sum(sizes),), dtype=_f32, device=dev)          # all 36 parameter gradients: one allocation
-        grads = tuple(v.view_as(p) for v, p in zip(flat.split(sizes), params))
+        flat, grads = _flat_grads(params, dev)                             # all 36 parameter gradients: one allocation
         rows = code_a.shape[0] if spec.ids is not None else N
         g_codes = torch.empty((2, rows, spec.code), dtype=_f32, device=dev)
         ws = _bytes(lib.cnrf_render_workspace_bytes(C.byref(shp), 1), dev)
@@ -641,9 +651,7 @@ class _RenderLoss(torch.autograd.Function):
         gs = [None if g is None else _c(g.to(_f32)) for g in (g0, g1, g2)]
         shp = RenderShape(spec.hidden, spec.code, spec.dim_xyz, spec.dim_dir, N, spec.num_coarse, spec.num_fine, spec.pairing,
                           spec.precision, 1)
-        sizes = [p.numel() for p in params]
-        flat = torch.empty((sum(sizes),), dtype=_f32, device=dev)          # all 36 parameter gradients: one allocation
-        grads = tuple(v.view_as(p) for v, p in zip(flat.split(sizes), params))
+        flat, grads = _flat_grads(params, dev)                             # all 36 parameter gradients: one allocation
         rows = code_a.shape[0] if spec.ids is not None else N
         g_codes = torch.empty((2, rows, spec.code), dtype=_f32, device=dev)
         ws = _bytes(lib.cnrf_render_workspace_bytes(C.byref(shp), 1), dev)

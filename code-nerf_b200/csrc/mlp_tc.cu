@@ -543,6 +543,17 @@ __global__ void __launch_bounds__(DW_THREADS, 1) mlp_dw_tc_kernel(const DwArgs a
           uint32_t v[32];
           tmem_ld32(tmem + mh * 256 + ((uint32_t)(q * 32) << 16) + c0, v);
           tmem_ld_wait();
+          float* orow = job.out + (size_t)n * job.ld + c0;
+          // 16-byte vector reductions (red.global.add.v4.f32) wherever the 32 columns are all real and the row is aligned:
+          // a quarter of the L2 atomic operations of this epilogue, which is most of the launch's fixed cost (~65 us of a
+          // 160 us coarse launch before; every CTA of a job adds a full [256 x N] partial into the same gradient)
+          if (c0 + 32 <= job.k_valid && (reinterpret_cast<uintptr_t>(orow) & 15) == 0) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              atomicAdd(reinterpret_cast<float4*>(orow + j), make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                                         __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+            continue;
+          }
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const int k = c0 + j;
