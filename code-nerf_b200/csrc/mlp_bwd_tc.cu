@@ -50,6 +50,7 @@ struct BEpi {
   bool elected, tile_ok;
   const uint8_t* masks;    // this tile's sign words: [4 layers][8 column blocks][128 rows]
   float4 g;                // upstream gradient of this row's (r, g, b, sigma)
+  int64_t exp_tile;        // (attribution builds)
 };
 
 // warp-wide wait whose result the compiler can prove uniform (keeps the MMA issuer's state in uniform registers)
@@ -111,6 +112,14 @@ __device__ __forceinline__ bool bwd_stage(const BwdArgs& a, BEpi& c, int t, uint
 #pragma unroll
     for (int j = 0; j < 16; ++j) pk[j] = pack_bf16(f[2 * j], f[2 * j + 1]);
     store_row_block(c.tile, c.r, cb, pk);
+#ifdef CNRF_EXP_COALESCED_DIRECT
+    if (c.tile_ok) {
+      uint8_t* img = a.dy + (size_t)c.exp_tile * DY_PER_TILE + (size_t)(S + 1) * TILE_BYTES;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        __stcs(reinterpret_cast<uint4*>(img + (size_t)((cb * 4 + j) * 128 + c.r) * 16), make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]));
+    }
+#endif
   };
   uint32_t va[32], vb[32];
   if (S >= 0) tmem_ld32(c.tacc, va);
@@ -323,6 +332,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) mlp_bwd_tc_kernel(const BwdArgs a
     for (int64_t pr = blockIdx.x; pr < num_pairs; pr += gridDim.x) {
       const int64_t tile_idx = pr * 2 + t;
       c.tile_ok = tile_idx < num_tiles;
+      c.exp_tile = tile_idx;
       const int64_t m = tile_idx * TILE + c.r;
       c.masks = a.saved + (size_t)(c.tile_ok ? tile_idx : 0) * SAVED_PER_TILE + SAVED_MASKS;
       c.g = m < a.M ? __ldg(reinterpret_cast<const float4*>(a.g_raw) + m) : make_float4(0.f, 0.f, 0.f, 0.f);

@@ -212,6 +212,14 @@ __device__ __forceinline__ bool epi_layer(const FwdArgs& a, Epi& c, int t, uint3
 #pragma unroll
       for (int j = 0; j < 16; ++j) pk[j] = cvt_relu_bf16x2(f[2 * j], f[2 * j + 1]);
       store_row_block(c.tile, c.r, cb, pk);
+#ifdef CNRF_EXP_COALESCED_DIRECT
+      if (SV && c.sv) {
+        uint8_t* img = c.sv + SAVED_GAMMA + (size_t)E * TILE_BYTES;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          __stcs(reinterpret_cast<uint4*>(img + (size_t)((cb * 4 + j) * 128 + c.r) * 16), make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]));
+      }
+#endif
     }
   };
   uint32_t va[32], vb[32];

@@ -28,7 +28,7 @@ __device__ __forceinline__ int producer_index(int warp) { return warp == 0 ? 0 :
 // one warp copies `bytes` (a multiple of 4 KB) of a shared-memory image to global memory
 // (-DCNRF_EXP_NO_STG / -DCNRF_EXP_NO_COPY: attribution builds of scripts/exp_fwd_store_attribution.sh -- wrong results, right timing)
 __device__ __forceinline__ void warp_copy_image(uint8_t* __restrict__ dst, const uint8_t* src_smem, int bytes, int lane) {
-#ifdef CNRF_EXP_NO_COPY
+#if defined(CNRF_EXP_NO_COPY) || defined(CNRF_EXP_COALESCED_DIRECT)
   return;
 #endif
   for (int off = lane * 16; off < bytes; off += 8 * 512) {
