@@ -103,6 +103,18 @@ int cnrf_code_runs(const int64_t* ids, int64_t N, int64_t num_codes, const CodeR
   return CNRF_OK;
 }
 
+// every ray carries the SAME code row (a stride-0 expand: eval.py:149, nerf/__init__.py:176-177): one run
+__global__ void broadcast_runs_kernel(int64_t N, int32_t* __restrict__ gid, int32_t* __restrict__ rep, int32_t* __restrict__ count) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < N) gid[i] = 0;
+  if (i == 0) { rep[0] = 0; *count = 1; }
+}
+int cnrf_code_runs_broadcast(int64_t N, const CodeRuns& r, cudaStream_t st) {
+  broadcast_runs_kernel<<<grid_for(N, 256), 256, 0, st>>>(N, r.gid, r.rep, r.count);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
 int cnrf_gather_codes(const int64_t* ids, const CodeRuns& r, int64_t N, int C, const float* tab, int64_t ld, float* out,
                       cudaStream_t st) {
   if (C % 4 || ld % 4 || (reinterpret_cast<uintptr_t>(tab) & 15) || (reinterpret_cast<uintptr_t>(out) & 15)) return CNRF_E_SHAPE;

@@ -823,6 +823,8 @@ bool carve_pair_acts(const Dims& d, bool ids, Arena& a, PairModel& m, PairCommon
 
 struct PairFwd {           // everything cnrf_pair_fwd_* derive from (in, side)
   Dims d[2]; Tables t[2]; PairModel m[2]; PairCommon c; float *dirn, *demb; uint8_t* packed[2]; bool ids, keep;
+  bool bcast;      // every ray carries the same code row (stride-0 expand, eval.py:149): treated as ONE run, no ids needed
+  bool shared() const { return ids || bcast; }
 };
 inline size_t up1k_sz(size_t b) { return (b + 1023) & ~size_t(1023); }
 size_t pair_fwd_side_bytes(const Dims& d, bool keep) {
@@ -832,6 +834,7 @@ size_t pair_fwd_side_bytes(const Dims& d, bool keep) {
 }
 int carve_pair_fwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairFwd& f) {
   f.ids = in.ids != nullptr; f.keep = in.shape[0]->keep != 0;
+  f.bcast = !f.ids && in.ld_zs == 0 && in.ld_zt == 0;
   for (int i = 0; i < 2; ++i) f.d[i] = dims_of(in.shape[i]);
   Arena a(side, side_bytes);
   f.dirn = a.take(f.d[0].N * 3); f.demb = a.take(f.d[0].N * f.d[0].dd);
@@ -841,7 +844,7 @@ int carve_pair_fwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairFwd&
     for (int i = 0; i < 2; ++i) {
       if (!in.saved[i]) return CNRF_E_WORKSPACE;
       Arena sa(in.saved[i], in.saved_bytes[i]);
-      if (!carve_pair_acts(f.d[i], f.ids, sa, f.m[i], i == 0 ? &f.c : nullptr)) return CNRF_E_WORKSPACE;   // the runs live with the coarse model
+      if (!carve_pair_acts(f.d[i], f.shared(), sa, f.m[i], i == 0 ? &f.c : nullptr)) return CNRF_E_WORKSPACE;   // the runs live with the coarse model
       f.packed[i] = cnrf_tc_packed_in_saved(f.m[i].tc_saved, f.d[i].M);
     }
   } else {
@@ -850,7 +853,7 @@ int carve_pair_fwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairFwd&
       f.m[i].at = a.take(f.d[i].N * f.d[i].C); f.m[i].bof = a.take(f.d[i].N * f.d[i].C);
       f.m[i].tc_saved = nullptr; f.m[i].tc_saved_bytes = 0;
     }
-    if (f.ids) {
+    if (f.shared()) {
       float* rbase = a.take(cnrf_code_runs_bytes(f.d[0].N) / sizeof(float));
       f.c.zc_s = a.take(f.d[0].N * f.d[0].C); f.c.zc_t = a.take(f.d[0].N * f.d[0].C);
       if (!a.ok) return CNRF_E_WORKSPACE;
@@ -864,16 +867,18 @@ int carve_pair_fwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairFwd&
     }
   }
   if (!a.ok) return CNRF_E_WORKSPACE;
-  if (f.ids) f.d[0].rows_dev = f.d[1].rows_dev = f.c.runs.count;
+  if (f.shared()) f.d[0].rows_dev = f.d[1].rows_dev = f.c.runs.count;
   return CNRF_OK;
 }
 
-struct PairBwd { Dims d[2]; Tables dt[2]; float* tmp[2]; PairModel m[2]; PairCommon c; float *gz_s, *gz_t; bool ids; };
+struct PairBwd { Dims d[2]; Tables dt[2]; float* tmp[2]; PairModel m[2]; PairCommon c; float *gz_s, *gz_t; bool ids, bcast;
+                 bool shared() const { return ids || bcast; } };
 size_t pair_bwd_side_bytes(const Dims& d) {
   return 2 * (tables_bytes(d) + 3 * al(d.N * d.C) + al(d.N)) + 2 * al(d.N * d.C) + 1024;
 }
 int carve_pair_bwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairBwd& f) {
   f.ids = in.ids != nullptr;
+  f.bcast = !f.ids && in.ld_zs == 0 && in.ld_zt == 0;
   Arena a(side, side_bytes);
   for (int i = 0; i < 2; ++i) {
     f.d[i] = dims_of(in.shape[i]);
@@ -881,11 +886,11 @@ int carve_pair_bwd(const CnrfPairIn& in, void* side, size_t side_bytes, PairBwd&
     f.tmp[i] = a.take(f.d[i].N * f.d[i].C); a.take(f.d[i].N * f.d[i].C); a.take(f.d[i].N * f.d[i].C); a.take(f.d[i].N);
     if (!in.saved[i]) return CNRF_E_WORKSPACE;
     Arena sa(in.saved[i], in.saved_bytes[i]);
-    if (!carve_pair_acts(f.d[i], f.ids, sa, f.m[i], i == 0 ? &f.c : nullptr)) return CNRF_E_WORKSPACE;
+    if (!carve_pair_acts(f.d[i], f.shared(), sa, f.m[i], i == 0 ? &f.c : nullptr)) return CNRF_E_WORKSPACE;
   }
   f.gz_s = a.take(f.d[0].N * f.d[0].C); f.gz_t = a.take(f.d[0].N * f.d[0].C);
   if (!a.ok) return CNRF_E_WORKSPACE;
-  if (f.ids) f.d[0].rows_dev = f.d[1].rows_dev = f.c.runs.count;
+  if (f.shared()) f.d[0].rows_dev = f.d[1].rows_dev = f.c.runs.count;
   return CNRF_OK;
 }
 
@@ -930,6 +935,9 @@ int cnrf_pair_fwd_prepare(const CnrfPairIn& in, void* side, size_t side_bytes, c
     RUN(cnrf_gather_codes(in.ids, f.c.runs, d.N, d.C, in.z_s, in.ld_zs, f.c.zc_s, st));
     RUN(cnrf_gather_codes(in.ids, f.c.runs, d.N, d.C, in.z_t, in.ld_zt, f.c.zc_t, st));
     zs = f.c.zc_s; zt = f.c.zc_t; ld_zs = ld_zt = d.C;
+  } else if (f.bcast) {   // one code row for every ray: one run, its row is row 0 of the caller's tensors
+    RUN(cnrf_code_runs_broadcast(d.N, f.c.runs, st));
+    ld_zs = ld_zt = d.C;
   }
   Batch b(d.rows_dev);
   for (int level = 0; level < PER_RAY_FWD_LEVELS; ++level) {
@@ -951,7 +959,7 @@ int cnrf_pair_fwd_chain(const CnrfPairIn& in, int which, const float* pts, float
   const Dims& d = f.d[which];
   const Tables& t = f.t[which];
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, in.params[which], nullptr, d.dx, pts, in.freqs_xyz, in.L_xyz, incx,
-                t.b2, t.bf, t.bos, t.br, t.wf, f.demb, d.dd, f.ids ? f.c.runs.gid : nullptr};
+                t.b2, t.bf, t.bos, t.br, t.wf, f.demb, d.dd, f.shared() ? f.c.runs.gid : nullptr};
   a.packed = f.packed[which];
   return cnrf_tc_chain_fwd(a, raw, f.m[which].tc_saved, f.m[which].tc_saved_bytes, ws, ws_bytes, st);
 }
@@ -986,7 +994,7 @@ int cnrf_pair_bwd_chain(const CnrfPairIn& in, int which, const float* g_raw, con
   const Dims& d = f.d[which];
   const Tables& dt = f.dt[which];
   TcChainArgs a{d.N, d.M, d.S, d.pairing, d.dx, d.dd, in.params[which], nullptr, d.dx, nullptr, in.freqs_xyz, in.L_xyz, incx,
-                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, d.dd, f.ids ? f.c.runs.gid : nullptr};
+                nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, d.dd, f.shared() ? f.c.runs.gid : nullptr};
   a.prezeroed = true;
   return cnrf_tc_chain_bwd(a, g_raw, f.m[which].tc_saved, f.m[which].tc_saved_bytes, g, dt.b2, dt.bo, dt.br, nullptr, dt.bf, dt.dwfh,
                            nullptr, ws, ws_bytes, st);
@@ -1008,8 +1016,9 @@ int cnrf_pair_bwd_finish(const CnrfPairIn& in, const cnrf_codenerf_grads* const 
     zs = f.c.zc_s; zt = f.c.zc_t; ld_zs = ld_zt = d.C;
     gz_s = f.gz_s; gz_t = f.gz_t;
     fb.add(g_z_s, in.num_codes * d.C); fb.add(g_z_t, in.num_codes * d.C);
-  } else {
-    fb.add(g_z_s, d.N * d.C); fb.add(g_z_t, d.N * d.C);
+  } else {                // (broadcast codes: the single run's gradient lands in row 0, the other rows stay zero -- the sum over
+    fb.add(g_z_s, d.N * d.C); fb.add(g_z_t, d.N * d.C);      //  rows that the caller's expand() backward takes is the same)
+    if (f.bcast) ld_zs = ld_zt = d.C;
   }
   RUN(cnrf_fill_batch(fb, st));
   Batch b(d.rows_dev);

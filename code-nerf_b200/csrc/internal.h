@@ -166,6 +166,7 @@ struct CodeRuns { int32_t* gid = nullptr; int32_t* rep = nullptr; int32_t* count
 size_t cnrf_code_runs_bytes(int64_t N);
 CodeRuns cnrf_code_runs_carve(void* base /*256-byte aligned*/, int64_t N);
 int cnrf_code_runs(const int64_t* ids, int64_t N, int64_t num_codes, const CodeRuns& r, cudaStream_t st);
+int cnrf_code_runs_broadcast(int64_t N, const CodeRuns& r, cudaStream_t st);     // all rays share one code row: a single run
 int cnrf_gather_codes(const int64_t* ids, const CodeRuns& r, int64_t N, int C, const float* tab, int64_t ld, float* out,
                       cudaStream_t st);
 int cnrf_scatter_code_grads(const int64_t* ids, const CodeRuns& r, int64_t N, int C, const float* g_codes, float* g_tab,
