@@ -216,3 +216,40 @@ def test_grad_allreduce_two_ranks_gloo(tmp_path):
     for r in (r0, r1):
         assert torch.equal(r["gw"], want_w) and torch.equal(r["gb"], want_b)
         assert torch.equal(r["ge"], torch.zeros(4, 2)) and r["flat_views"]
+
+
+def test_flat_gradient_allocation_is_16_byte_aligned_per_parameter():
+    """ops._flat_grads: one allocation for all parameter gradients of a fused backward, every gradient on a 16-byte boundary
+    (fc_out's 257-element bias would otherwise shift everything behind it: the weight-gradient kernel's vector reductions
+    and FusedAdamW's float4 path need aligned rows)."""
+    import torch
+    from codenerf_b200 import ops
+    import view_synthesis.models as models
+    m = models.CodeNeRFModel(256, 3, 256, 256, 10, 4)
+    params = list(m.parameters()) + list(m.parameters())
+    flat, grads = ops._flat_grads(params, torch.device("cpu"))
+    assert len(grads) == len(params) and flat.dim() == 1
+    end = 0
+    for g, p in zip(grads, params):
+        assert g.shape == p.shape and g.is_contiguous()
+        assert g.storage_offset() % 4 == 0 and g.storage_offset() >= end          # aligned, in order, no overlap
+        assert g.untyped_storage().data_ptr() == flat.untyped_storage().data_ptr()
+        end = g.storage_offset() + g.numel()
+    assert end <= flat.numel() < end + 4
+
+
+def test_loss_target_spec_argument_checks():
+    """ops.LossTargetSpec: exactly one of (rows) / (uint8 views + int64 pixel indices); CPU tensors are refused when the
+    struct is built (there is no CPU fallback)."""
+    import pytest
+    import torch
+    from codenerf_b200 import ops
+    with pytest.raises(AssertionError):
+        ops.LossTargetSpec()
+    with pytest.raises(AssertionError):
+        ops.LossTargetSpec(rows=torch.zeros(4, 3), views=torch.zeros(1, 2, 2, 4, dtype=torch.uint8), pixel=torch.zeros(4, dtype=torch.int64))
+    with pytest.raises(AssertionError):
+        ops.LossTargetSpec(views=torch.zeros(1, 2, 2, 4), pixel=torch.zeros(4, dtype=torch.int64))       # float views
+    spec = ops.LossTargetSpec(views=torch.zeros(1, 2, 2, 4, dtype=torch.uint8), pixel=torch.zeros(4, dtype=torch.int64))
+    with pytest.raises(AssertionError):
+        spec.struct(4, [])                                                                             # CPU tensors
