@@ -515,6 +515,21 @@ def run_ours(args):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
+    # standalone rooflines of the HBM-bound stages (north_star: compositing / sampling vs the HBM peak): one launch per
+    # repetition over 524,288 rays (working sets > L2), CUDA events, algorithmic bytes of SURVEY section 8(d).  Measured BEFORE
+    # the training steps: these kernels are issue-bound, and after a minute of graph-replayed tensor work the box sits at its
+    # power cap (SM clock ~1.82 GHz instead of 1.965), which costs them 7-8 % that have nothing to do with the kernels.
+    hbm_rows, hbm_peak = None, None
+    if world == 1 and rank == 0 and not args.no_hbm_kernels:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("time_hbm_kernels", os.path.join(ROOT, "scripts", "time_hbm_kernels.py"))
+        thk = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(thk)
+        hbm_rows = [{k: (round(r[k], 4) if isinstance(r[k], float) else r[k]) for k in
+                     ("kernel", "rays", "bytes_per_ray", "ms", "GBps", "frac")}
+                    for r in thk.measure(524288, 10, dev, verbose=False)]
+        hbm_peak = {"GBps": thk.hbm_peak()[0], "source": thk.hbm_peak()[1]}
+        torch.cuda.empty_cache()
     lib = _lib.load()
     step_resident(); torch.cuda.synchronize()
     n0 = lib.cnrf_launch_count(); step_resident(); torch.cuda.synchronize()
@@ -595,17 +610,9 @@ def run_ours(args):
                 "chain_kernels_dram_bytes_per_chunk": chunk_traffic,
                 "model_flops_per_ray": FLOP_PER_RAY_TRAIN,
                 "achieved_tflops_whole_step": value * FLOP_PER_RAY_TRAIN / 1e12 / world}
-        if world == 1 and not args.no_hbm_kernels:
-            # standalone rooflines of the HBM-bound stages (north_star: compositing / sampling vs the HBM peak): one launch
-            # per repetition over 524,288 rays (working sets > L2), CUDA events, algorithmic bytes of SURVEY section 8(d)
-            import importlib.util
-            spec = importlib.util.spec_from_file_location("time_hbm_kernels", os.path.join(ROOT, "scripts", "time_hbm_kernels.py"))
-            thk = importlib.util.module_from_spec(spec)
-            spec.loader.exec_module(thk)
-            line["hbm_kernels"] = [{k: (round(r[k], 4) if isinstance(r[k], float) else r[k]) for k in
-                                    ("kernel", "rays", "bytes_per_ray", "ms", "GBps", "frac")}
-                                   for r in thk.measure(524288, 10, dev, verbose=False)]
-            line["hbm_kernels_peak"] = {"GBps": thk.hbm_peak()[0], "source": thk.hbm_peak()[1]}
+        if hbm_rows is not None:
+            line["hbm_kernels"] = hbm_rows
+            line["hbm_kernels_peak"] = hbm_peak
         torch.cuda.empty_cache()
         if world == 1 and not args.no_eager_baseline:
             # the unmodified reference through stock eager torch on this B200, >= 10 full C2 steps

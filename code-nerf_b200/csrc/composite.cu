@@ -101,7 +101,9 @@ __device__ __forceinline__ float next_dist(const RayRegs<NCH>& q, int c, int S, 
 struct Sums { float R, G, B, D, A; };
 
 // ---------------------------------------------------------------------------------------------------------------
-template <int NCH, int R>
+// LOSS: the photometric loss rides in the epilogue (CompositeLossFwd); a separate instantiation, so that the plain kernels
+// stay exactly the code they were (the loss arguments cost the non-loss launches 3-16 % when they shared one body)
+template <int NCH, int R, bool LOSS>
 __global__ void __launch_bounds__(CWARPS * 32)
 composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rd,
                      int64_t N, int S, float* __restrict__ rgb, float* __restrict__ disp, float* __restrict__ acc,
@@ -168,7 +170,7 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
       if (disp) disp[n] = rcp_fast(fmaxf(1e-10f, tot * rcp_fast(other)));             // 1 / max(1e-10, depth / acc)  :64
     } else if (qn == 4) { if (acc) acc[n] = tot; }
   }
-  if (lf.sq_sum) {      // photometric loss folded into the epilogue (train.py:103-104): sum over rays and channels of (rgb - target)^2
+  if (LOSS) {           // photometric loss folded into the epilogue (train.py:103-104): sum over rays and channels of (rgb - target)^2
     float e = 0.f;
     if (writer && n < N && qn < 3) { const float d = tot - loss_target(lf.t, n, qn); e = d * d; }
 #pragma unroll
@@ -189,7 +191,7 @@ composite_fwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
 
 // ---------------------------------------------------------------------------------------------------------------
 // GEO: the caller wants g_z and / or g_rd (camera-pose optimisation); training needs neither.
-template <int NCH, int R, bool GEO>
+template <int NCH, int R, bool GEO, bool LOSS>
 __global__ void __launch_bounds__(CWARPS * 32)
 composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z, const float* __restrict__ rd,
                      int64_t N, int S, const float* __restrict__ g_rgb, const float* __restrict__ g_disp,
@@ -219,7 +221,7 @@ composite_bwd_kernel(const float* __restrict__ raw, const float* __restrict__ z,
     const float norm = sqrtf(dx * dx + dy * dy + dz * dz);
     float gR = g_rgb ? __ldg(g_rgb + n * 3) : 0.f, gG = g_rgb ? __ldg(g_rgb + n * 3 + 1) : 0.f,
           gB = g_rgb ? __ldg(g_rgb + n * 3 + 2) : 0.f;
-    if (lb.rgb_out) {   // the loss lives in the forward epilogue: d loss / d rgb = (g_term + g_sum) * 2 (rgb - target) / (3 N)
+    if (LOSS) {         // the loss lives in the forward epilogue: d loss / d rgb = (g_term + g_sum) * 2 (rgb - target) / (3 N)
       const float k = ((lb.g_term ? __ldg(lb.g_term) : 0.f) + (lb.g_sum ? __ldg(lb.g_sum) : 0.f)) * lb.scale;
       gR = k * (__ldg(lb.rgb_out + n * 3) - loss_target(lb.t, n, 0));
       gG = k * (__ldg(lb.rgb_out + n * 3 + 1) - loss_target(lb.t, n, 1));
@@ -319,20 +321,27 @@ template <int NCH, int R>
 static void launch_fwd(const float* raw, const float* z, const float* rd, int64_t N, int S, float* rgb, float* disp,
                        float* acc, float* weights, float* depth, CompositeLossFwd lf, cudaStream_t st) {
   lf.num_warps = (unsigned)((N + R - 1) / R);
-  composite_fwd_kernel<NCH, R><<<grid_for(N, CWARPS * R), CWARPS * 32, 0, st>>>(raw, z, rd, N, S, rgb, disp, acc, weights,
-                                                                                 depth, lf);
+  if (lf.sq_sum)
+    composite_fwd_kernel<NCH, R, true><<<grid_for(N, CWARPS * R), CWARPS * 32, 0, st>>>(raw, z, rd, N, S, rgb, disp, acc, weights,
+                                                                                         depth, lf);
+  else
+    composite_fwd_kernel<NCH, R, false><<<grid_for(N, CWARPS * R), CWARPS * 32, 0, st>>>(raw, z, rd, N, S, rgb, disp, acc, weights,
+                                                                                          depth, lf);
 }
 template <int NCH, int R>
 static void launch_bwd(const float* raw, const float* z, const float* rd, int64_t N, int S, const float* g_rgb,
                        const float* g_disp, const float* g_acc, const float* g_weights, const float* g_depth,
                        float* g_raw, float* g_z, float* g_rd, const CompositeLossBwd& lb, cudaStream_t st) {
   const unsigned grid = grid_for(N, CWARPS * R);
-  if (g_z || g_rd)
-    composite_bwd_kernel<NCH, R, true><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
-                                                                      g_depth, g_raw, g_z, g_rd, lb);
+  if (lb.rgb_out)      // (the loss variant serves the fused training entry: rays carry no gradient there)
+    composite_bwd_kernel<NCH, R, false, true><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
+                                                                             g_depth, g_raw, nullptr, nullptr, lb);
+  else if (g_z || g_rd)
+    composite_bwd_kernel<NCH, R, true, false><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
+                                                                             g_depth, g_raw, g_z, g_rd, lb);
   else
-    composite_bwd_kernel<NCH, R, false><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
-                                                                       g_depth, g_raw, g_z, g_rd, lb);
+    composite_bwd_kernel<NCH, R, false, false><<<grid, CWARPS * 32, 0, st>>>(raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights,
+                                                                              g_depth, g_raw, g_z, g_rd, lb);
 }
 
 // chunks of 32 samples per ray -> (NCH, rays per warp forward, rays per warp backward)
@@ -367,6 +376,7 @@ int cnrf_composite_bwd_loss(const float* raw, const float* z, const float* rd, i
                             const float* g_disp, const float* g_acc, const float* g_weights, const float* g_depth, float* g_raw,
                             float* g_z, float* g_rd, const CompositeLossBwd& lb, cudaStream_t st) {
   CNRF_REQUIRE(raw && z && rd && g_raw, CNRF_E_NULL);
+  CNRF_REQUIRE(!(lb.rgb_out && (g_z || g_rd)), CNRF_E_UNSUPPORTED);
   CNRF_REQUIRE(N > 0 && S > 0 && S <= 256, CNRF_E_SHAPE);
   DISPATCH_NCH(S, CALL_BWD, raw, z, rd, N, S, g_rgb, g_disp, g_acc, g_weights, g_depth, g_raw, g_z, g_rd, lb, st);
   CNRF_LAUNCH_CHECK();
