@@ -7,9 +7,13 @@
 //           slabs instead of four -- cat(h, xyz) (models/model.py:63) never exists.  A ring of three 32 KB weight slabs
 //           ([256 out x 64 in] bf16, pre-swizzled in global memory by pack_flex_weights_kernel, so one slab is ONE 1-D TMA
 //           bulk copy) runs ahead of the MMAs across layers and tiles.
-//   TMEM  : one [128 x 256] fp32 accumulator.
+//   TMEM  : two [128 x 256] fp32 accumulators, used by alternate layers.
 //   warps : 0-7 epilogue (tcgen05.ld -> + bias -> ReLU -> bf16 -> swizzled smem = next layer's A operand), 8 = TMA
 //           producer, 9 = MMA issuer (elect.sync lane, M128 N256 K16).
+// Layer-to-layer overlap inside a tile: the eight epilogue warps finish the next layer's A operand one 64-column slab at a
+// time (slab s = columns 64 s .. 64 s + 63: warp half h converts its 32 of them) and arrive on that slab's barrier; the MMA
+// warp starts the next layer's K slab s as soon as slab s is there, accumulating into the OTHER TMEM buffer, so only the last
+// K slab's MMAs remain when the epilogue ends (before: MMA ~2.0 k clk, then epilogue ~3.9 k clk, nothing overlapped).
 // Heads: fc_alpha rides in the layers_dir[0] GEMM as output row 128 (N = 144), so sigma costs nothing; the view-direction
 // half of layers_dir[0] arrives as a per-ray fp32 bias row (pairing as nerf/__init__.py:127); fc_rgb (128 -> 3) is a
 // CUDA-core dot product in that layer's epilogue.  bf16 operands / fp32 accumulation, like the CodeNeRF chain.
@@ -94,13 +98,15 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   float* part_sm = wrgb_sm + 3 * 128;                      // [128][4]
   uint64_t* bars = reinterpret_cast<uint64_t*>(part_sm + 128 * 4);
   uint64_t *full = bars, *empty = bars + RING, *acc_bar = bars + 2 * RING, *act_bar = bars + 2 * RING + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RING + 2);
+  uint64_t* slab_bar = bars + 2 * RING + 2;            // [4]: the next layer's A slab s is written (8 arrivals: every epilogue warp)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RING + 6);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
     for (int i = 0; i < RING; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
     mbar_init(acc_bar, 1);
-    mbar_init(act_bar, FT_EPI_WARPS);
+    mbar_init(act_bar, FT_EPI_WARPS);                  // gamma(x) of the tile is written (layer1's A operand)
+    for (int i = 0; i < 4; ++i) mbar_init(&slab_bar[i], FT_EPI_WARPS);
     mbar_fence_init();
   }
   for (int i = tid; i < a.nlayers * 256; i += FT_THREADS) {
@@ -108,7 +114,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     bias_sm[i] = a.bias[l] ? __ldg(a.bias[l] + (i & 255)) : 0.f;
   }
   for (int i = tid; i < 3 * 128; i += FT_THREADS) wrgb_sm[i] = __ldg(a.w_rgb + i);
-  if (warp == 9) tmem_alloc(tmem_slot, 256);
+  if (warp == 9) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -123,7 +129,8 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
       for (int l = 0; l < a.nlayers && ok; ++l) {
         const FlexLayer L = a.layer[l];
         const uint32_t bytes = L.n_out == 256 ? SLAB_W : SLAB_WD;
-        for (int j = 0; j < L.kslabs && ok; ++j, ++s) {
+        for (int i = 0; i < L.kslabs && ok; ++i, ++s) {
+          const int j = L.skip ? (i == 0 ? L.kslabs - 1 : i - 1) : i;      // K-slab order of the MMA warp (gamma(x) first)
           const uint32_t slot = s % RING, ph = (s / RING) & 1;
           ok = mbar_wait(&empty[slot], ph ^ 1, a.err);
           if (ok && elect_one()) {
@@ -136,29 +143,39 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     }
   } else if (warp == 9) {
     // ---- MMA issuer
-    uint32_t s = 0, act_ph = 0;
+    uint32_t s = 0, act_ph = 0, slab_ph = 0;
     for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
       for (int l = 0; l < a.nlayers && ok; ++l) {
         const FlexLayer L = a.layer[l];
         const uint32_t idesc = idesc_bf16(FT_ROWS, L.n_out, 0, 0);
-        ok = mbar_wait(act_bar, act_ph, a.err);            // this layer's A operand is in shared memory
-        act_ph ^= 1;
-        tc_fence_after();
-        for (int j = 0; j < L.kslabs && ok; ++j, ++s) {
+        const uint32_t acc = tmem + (uint32_t)(l & 1) * 256u;     // alternate layers, alternate accumulators
+        if (l == 0) {                                       // layer1 reads gamma(x): written once per tile
+          ok = mbar_wait(act_bar, act_ph, a.err);
+          act_ph ^= 1;
+          tc_fence_after();
+        }
+        for (int i = 0; i < L.kslabs && ok; ++i, ++s) {
+          const int j = L.skip ? (i == 0 ? L.kslabs - 1 : i - 1) : i;      // K slab (the skip layer starts with gamma(x), always there)
+          const int aslab = (L.skip && j == L.kslabs - 1) ? 4 : L.a_first + j;
+          if (l > 0 && aslab < 4) {                         // a hidden slab: the previous layer's epilogue has finished it
+            ok = mbar_wait(&slab_bar[aslab], slab_ph, a.err);
+            tc_fence_after();
+            if (!ok) break;
+          }
           const uint32_t slot = s % RING, ph = (s / RING) & 1;
           ok = mbar_wait(&full[slot], ph, a.err);
           tc_fence_after();
-          const int aslab = (L.skip && j == L.kslabs - 1) ? 4 : L.a_first + j;
           const uint32_t pa = smem_u32(act + aslab * SLAB_A), pb = smem_u32(ring + slot * SLAB_W);
           if (ok && elect_one()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              umma_bf16(tmem, smem_desc(pa + k * 32, 16, 1024, SWIZZLE_128B), smem_desc(pb + k * 32, 16, 1024, SWIZZLE_128B),
-                        idesc, (j > 0 || k > 0) ? 1u : 0u);
+              umma_bf16(acc, smem_desc(pa + k * 32, 16, 1024, SWIZZLE_128B), smem_desc(pb + k * 32, 16, 1024, SWIZZLE_128B),
+                        idesc, (i > 0 || k > 0) ? 1u : 0u);
             umma_commit(&empty[slot]);                      // the slot is free once these MMAs have read it
           }
           __syncwarp();
         }
+        if (l > 0) slab_ph ^= 1;                            // every slab barrier completes once per hidden-layer epilogue
         if (ok && elect_one()) umma_commit(acc_bar);
         __syncwarp();
       }
@@ -191,32 +208,34 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
         acc_ph ^= 1;
         tc_fence_after();
         if (!ok) break;
+        const uint32_t acc = tmem + (uint32_t)(l & 1) * 256u;
         if (l + 1 < a.nlayers) {
-          // hidden layer: 128 columns of this warp's half, 32 at a time -> bias, ReLU, bf16, slab (col >> 6)
-          const float* b = bias_sm + l * 256 + h * 128;
-          const uint32_t t0 = tmem + ((uint32_t)(q * 32) << 16) + h * 128;
+          // hidden layer: slab s = columns 64 s .. 64 s + 63 of the next A operand; this warp converts the 32 columns of its
+          // half h, then arrives on the slab's barrier -- the MMA warp starts the next layer's K slab s right away
+          const float* b = bias_sm + l * 256;
+          const uint32_t t0 = acc + ((uint32_t)(q * 32) << 16) + h * 32;
           uint32_t v[2][32];
           tmem_ld32(t0, v[0]);
 #pragma unroll
-          for (int cb = 0; cb < 4; ++cb) {
+          for (int sl = 0; sl < 4; ++sl) {
             tmem_ld_wait();
-            if (cb + 1 < 4) tmem_ld32(t0 + (cb + 1) * 32, v[(cb + 1) & 1]);      // next block in flight under this one
+            if (sl + 1 < 4) tmem_ld32(t0 + (sl + 1) * 64, v[(sl + 1) & 1]);      // next slab's block in flight under this one
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-              const float4 b0 = *reinterpret_cast<const float4*>(b + cb * 32 + c * 8);       // warp-uniform: LDS broadcast
-              const float4 b1 = *reinterpret_cast<const float4*>(b + cb * 32 + c * 8 + 4);
+              const int col = sl * 64 + h * 32 + c * 8;
+              const float4 b0 = *reinterpret_cast<const float4*>(b + col);       // warp-uniform: LDS broadcast
+              const float4 b1 = *reinterpret_cast<const float4*>(b + col + 4);
               const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
               float x[8];
 #pragma unroll
-              for (int e = 0; e < 8; ++e) x[e] = __uint_as_float(v[cb & 1][c * 8 + e]) + bb[e];
+              for (int e = 0; e < 8; ++e) x[e] = __uint_as_float(v[sl & 1][c * 8 + e]) + bb[e];
               // ReLU rides in the conversion (cvt.rn.relu.bf16x2.f32): no FMNMX per element
               const uint4 p = make_uint4(pack_bf16_relu(x[0], x[1]), pack_bf16_relu(x[2], x[3]), pack_bf16_relu(x[4], x[5]),
                                          pack_bf16_relu(x[6], x[7]));
-              const int col = h * 128 + cb * 32 + c * 8;
-              *reinterpret_cast<uint4*>(act + (col >> 6) * SLAB_A + row * 128 + ((((col & 63) >> 3) ^ (row & 7)) << 4)) = p;
+              *reinterpret_cast<uint4*>(act + sl * SLAB_A + row * 128 + (((h * 4 + c) ^ (row & 7)) << 4)) = p;
             }
+            epi_arrive(&slab_bar[sl], lane);
           }
-          epi_arrive(act_bar, lane);
         } else {
           // direction layer: columns [64 h, 64 h + 64) -> + betad[ray] -> ReLU -> fc_rgb partial sums; column 128 = sigma
           const int64_t ray = a.pairing == CNRF_PAIRING_REFERENCE ? (m % a.N) : (m / a.S);
@@ -225,7 +244,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
 #pragma unroll 1
           for (int cb = 0; cb < 2; ++cb) {
             uint32_t v[32];
-            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + h * 64 + cb * 32, v);
+            tmem_ld32(acc + ((uint32_t)(q * 32) << 16) + h * 64 + cb * 32, v);
             tmem_ld_wait();
 #pragma unroll
             for (int e = 0; e < 32; e += 4) {
@@ -242,7 +261,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
           float sigma = 0.f;
           if (h == 0) {
             uint32_t v[32];
-            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + 128, v);
+            tmem_ld32(acc + ((uint32_t)(q * 32) << 16) + 128, v);
             tmem_ld_wait();
             sigma = __uint_as_float(v[0]) + __ldg(a.b_alpha);
           } else {
@@ -262,7 +281,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem, 256);
+  if (warp == 9) tmem_dealloc(tmem, 512);
 }
 
 __device__ int g_flex_tc_error = 0;
