@@ -36,35 +36,29 @@ class SRNDataset(torch.utils.data.Dataset):
     Dataset from Scene Representation Networks (V. Sitzmann et al 2020)
     """
 
-    def __init__(
-        self, path: str,
-        stage: Literal["train", "val", "test"] = "train",
-    ):
-        super(SRNDataset, self).__init__()
-        self.base_path = Path(path)
-        self.dataset_name = self.base_path.stem.split("_")[-1]
-        self.base_path = self.base_path / f"{self.dataset_name}_{stage}"
-
-        print("Loading SRN dataset", self.base_path, "name:", self.dataset_name)
+    def __init__(self, path: str, stage: Literal["train", "val", "test"] = "train"):
+        """Same attributes and printed lines as the reference constructor (dataset.py:15-57): base_path, dataset_name, stage,
+        intrinsic (sorted intrinsics files = one per object), num_objects, rgb_all_filenames / pose_all_filenames (lists of
+        (object index, path), sorted per object), num_views."""
+        super().__init__()
+        root = Path(path)
+        self.dataset_name = root.stem.split("_")[-1]                       # ".../srn_cars" -> "cars"
         self.stage = stage
+        self.base_path = root / f"{self.dataset_name}_{stage}"
+        print("Loading SRN dataset", self.base_path, "name:", self.dataset_name)
         assert self.base_path.exists(), f"{self.base_path} does not exist"
-
-        is_chair = "chair" in self.dataset_name
-        if is_chair and stage == "train":
-            tmp = self.base_path / "chairs_2.0_train"
-            if tmp.exists():
-                self.base_path = tmp
+        if stage == "train" and "chair" in self.dataset_name:               # the chairs training split sits one level deeper
+            nested = self.base_path / "chairs_2.0_train"
+            self.base_path = nested if nested.exists() else self.base_path
 
         self.intrinsic = sorted(self.base_path.glob("*/intrinsics.txt"))
         self.num_objects = len(self.intrinsic)
 
-        self.rgb_all_filenames, self.pose_all_filenames = [], []
-        for index, intrinsic_path in enumerate(self.intrinsic):
-            rgb_files = sorted([(index, p) for p in (intrinsic_path.parent / "rgb").iterdir()])
-            pose_files = sorted([(index, p) for p in (intrinsic_path.parent / "pose").iterdir()])
-            self.rgb_all_filenames.extend(rgb_files)
-            self.pose_all_filenames.extend(pose_files)
+        def views(object_index, sub):
+            return sorted((object_index, f) for f in (self.intrinsic[object_index].parent / sub).iterdir())
 
+        self.rgb_all_filenames = [v for k in range(self.num_objects) for v in views(k, "rgb")]
+        self.pose_all_filenames = [v for k in range(self.num_objects) for v in views(k, "pose")]
         assert len(self.rgb_all_filenames) == len(self.pose_all_filenames)
         self.num_views = len(self.rgb_all_filenames) // self.num_objects
         print(f"Total number of objects in the set: {self.num_objects}")
