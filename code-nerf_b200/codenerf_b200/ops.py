@@ -740,13 +740,17 @@ def codenerf_model(params, z_s, z_t, x, hidden, code, dim_xyz, dim_dir, precisio
 # ----------------------------------------------------------------------------------------------------------
 # Vanilla NeRF field (FlexibleNeRFModel, models/model.py:5-76)
 # ----------------------------------------------------------------------------------------------------------
-def _flex_ptrs(tensors, num_xyz):
-    """tensors: (w,b) pairs in state_dict order -- layer1, layers_xyz[0..], fc_feat, layers_dir[0], fc_alpha, fc_rgb."""
+def _flex_ptrs(tensors, num_xyz, viewdirs=True):
+    """tensors: (w,b) pairs in state_dict order -- layer1, layers_xyz[0..], fc_feat, layers_dir[0], fc_alpha, fc_rgb; or, for
+    the use_viewdirs=False network (dim_dir == 0 at the C boundary), layer1, layers_xyz[0..], fc_out (in the w_rgb slot)."""
     t = FlexPtrs()
     it = iter(tensors)
     t.w_layer1, t.b_layer1 = next(it).data_ptr(), next(it).data_ptr()
     for i in range(num_xyz):
         t.w_xyz[i], t.b_xyz[i] = next(it).data_ptr(), next(it).data_ptr()
+    if not viewdirs:
+        t.w_rgb, t.b_rgb = next(it).data_ptr(), next(it).data_ptr()
+        return t
     t.w_feat, t.b_feat = next(it).data_ptr(), next(it).data_ptr()
     t.w_dir, t.b_dir = next(it).data_ptr(), next(it).data_ptr()
     t.w_alpha, t.b_alpha = next(it).data_ptr(), next(it).data_ptr()
@@ -763,22 +767,26 @@ class _FlexNerf(torch.autograd.Function):
         lib = _lib.load()
         num_layers, hidden, dim_xyz, dim_dir, skip_mask, S, pairing, precision = cfg
         x_xyz, ld_xyz = _rows(x_xyz)
-        x_dir, ld_dir = _rows(x_dir)
         if ld_xyz == 0:
             x_xyz, ld_xyz = x_xyz.contiguous(), x_xyz.shape[1]
-        if ld_dir == 0:
-            x_dir, ld_dir = x_dir.contiguous(), x_dir.shape[1]
+        if dim_dir == 0:         # use_viewdirs=False: x_dir only carries the ray count, (N, 0)
+            x_dir, ld_dir = x_dir.new_empty((x_dir.shape[0], 0)), 0
+        else:
+            x_dir, ld_dir = _rows(x_dir)
+            if ld_dir == 0:
+                x_dir, ld_dir = x_dir.contiguous(), x_dir.shape[1]
         params = tuple(_c(p) for p in params)
         M, N = x_xyz.shape[0], x_dir.shape[0]
         assert M == N * S, "FlexibleNeRF field: rows of x_xyz must be rays x samples"
+        assert len(params) == 2 * (num_layers + (4 if dim_dir else 1)), "FlexibleNeRF field: parameter count"
         keep = int(_OUTER_GRAD[0] and any(ctx.needs_input_grad))   # under no_grad (rendering) nothing is saved
         shp = FlexShape(num_layers, hidden, dim_xyz, dim_dir, skip_mask, N, S, pairing, precision, keep)
         dev = x_xyz.device
         saved = _bytes(lib.cnrf_flexnerf_saved_bytes(C.byref(shp)), dev)
         ws = _bytes(lib.cnrf_flexnerf_workspace_bytes(C.byref(shp), 0), dev)
         raw = torch.empty((M, 4), dtype=_f32, device=dev)
-        tab = _flex_ptrs(params, num_layers - 1)
-        check(lib.cnrf_flexnerf_fwd(C.byref(shp), C.byref(tab), _p(x_xyz), ld_xyz, _p(x_dir), ld_dir, _p(raw),
+        tab = _flex_ptrs(params, num_layers - 1, dim_dir > 0)
+        check(lib.cnrf_flexnerf_fwd(C.byref(shp), C.byref(tab), _p(x_xyz), ld_xyz, _p(x_dir) if dim_dir else None, ld_dir, _p(raw),
                                     _p(saved) if keep else None, saved.numel() if keep else 0, _p(ws), ws.numel(), _stream()),
               "cnrf_flexnerf_fwd")
         if keep:
@@ -799,10 +807,10 @@ class _FlexNerf(torch.autograd.Function):
         g_raw = _c(g_raw)
         grads = tuple(torch.empty_like(p) for p in params)
         g_xyz = torch.empty((M, dim_xyz), dtype=_f32, device=dev) if ctx.needs_input_grad[1] else None
-        g_dir = torch.empty((N, dim_dir), dtype=_f32, device=dev) if ctx.needs_input_grad[2] else None
+        g_dir = torch.empty((N, dim_dir), dtype=_f32, device=dev) if ctx.needs_input_grad[2] and dim_dir else None
         ws = _bytes(lib.cnrf_flexnerf_workspace_bytes(C.byref(shp), 1), dev)
-        tab, gtab = _flex_ptrs(params, num_layers - 1), _flex_ptrs(grads, num_layers - 1)
-        check(lib.cnrf_flexnerf_bwd(C.byref(shp), C.byref(tab), _p(x_xyz), ld_xyz, _p(x_dir), ld_dir, _p(g_raw), _p(saved),
+        tab, gtab = _flex_ptrs(params, num_layers - 1, dim_dir > 0), _flex_ptrs(grads, num_layers - 1, dim_dir > 0)
+        check(lib.cnrf_flexnerf_bwd(C.byref(shp), C.byref(tab), _p(x_xyz), ld_xyz, _p(x_dir) if dim_dir else None, ld_dir, _p(g_raw), _p(saved),
                                     saved.numel(), C.byref(gtab), _p(g_xyz), _p(g_dir), _p(ws), ws.numel(), _stream()),
               "cnrf_flexnerf_bwd")
         return (None, g_xyz, g_dir) + grads

@@ -299,7 +299,7 @@ size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers) {
 }
 
 bool cnrf_flex_fused_eligible(const cnrf_flex_shape* s) {
-  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->hidden == 256 && s->dim_xyz <= 64 && s->num_layers + 1 <= FT_MAX_LAYERS;
+  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->dim_dir > 0 && s->hidden == 256 && s->dim_xyz <= 64 && s->num_layers + 1 <= FT_MAX_LAYERS;
 }
 
 // betad: [N,128] fp32 already computed; packed: cnrf_flex_fused_packed_bytes() of 1024-byte aligned workspace

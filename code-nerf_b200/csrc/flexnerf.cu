@@ -34,6 +34,7 @@ struct FDims {
   uint32_t skip;
   int64_t N, M;
   bool tc;
+  bool viewdirs() const { return dd > 0; }      // dim_dir == 0: the use_viewdirs=False network (fc_out head, model.py:47,76)
   bool is_skip(int i) const { return (skip >> i) & 1u; }
   // activation a (0 = output of layer1, i+1 = output of layers_xyz[i]) feeds layers_xyz[a] (or fc_feat when a == L)
   int64_t ld_act(int a) const { return (a < L && is_skip(a)) ? H + dx : H; }
@@ -42,7 +43,7 @@ struct FDims {
 inline int dims_of(const cnrf_flex_shape* s, FDims& d) {
   if (!s) return CNRF_E_NULL;
   if (s->num_layers < 1 || s->num_layers - 1 > CNRF_FLEX_MAX_XYZ_LAYERS || s->hidden < 2 || (s->hidden & 1) ||
-      s->dim_xyz <= 0 || s->dim_dir <= 0 || s->num_rays <= 0 || s->num_samples <= 0)
+      s->dim_xyz <= 0 || s->dim_dir < 0 || s->num_rays <= 0 || s->num_samples <= 0)
     return CNRF_E_SHAPE;
   if (s->pairing != CNRF_PAIRING_REFERENCE && s->pairing != CNRF_PAIRING_CORRECT) return CNRF_E_SHAPE;
   if (s->precision != CNRF_PRECISION_FP32 && s->precision != CNRF_PRECISION_BF16 && s->precision != CNRF_PRECISION_SPLIT) return CNRF_E_UNSUPPORTED;
@@ -162,7 +163,7 @@ extern "C" int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_param
                                  void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
   FDims d;
   RUN(dims_of(s, d));
-  CNRF_REQUIRE(p && x_xyz && x_dir && raw && workspace, CNRF_E_NULL);
+  CNRF_REQUIRE(p && x_xyz && (x_dir || !d.viewdirs()) && raw && workspace, CNRF_E_NULL);
   CNRF_REQUIRE(ld_xyz >= d.dx && ld_dir >= d.dd, CNRF_E_SHAPE);
   cudaStream_t st = as_stream(stream);
   const int H = d.H, H2 = d.H / 2;
@@ -187,7 +188,7 @@ extern "C" int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_param
   CNRF_REQUIRE(ws.ok, CNRF_E_WORKSPACE);
 
   // per ray: betad = Wdir[:, H:] gamma(d) + bdir                                      models/model.py:69-71
-  RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->w_dir + H, H + d.dd, H2, betad, H2, p->b_dir, 0, 1, INT64_MAX, 0, st));
+  if (d.viewdirs()) RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->w_dir + H, H + d.dd, H2, betad, H2, p->b_dir, 0, 1, INT64_MAX, 0, st));
   // h = relu(layer1 xyz)                                                              :59
   RUN(lin(d.tc, x_xyz, ld_xyz, d.M, d.dx, p->w_layer1, d.dx, H, sv.act[0], d.ld_act(0), p->b_layer1, 0, 1, INT64_MAX, 1, st));
   for (int i = 0; i < d.L; ++i) {                                                      // :60-64
@@ -196,6 +197,8 @@ extern "C" int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_param
     RUN(lin(d.tc, sv.act[i], d.ld_act(i), d.M, K, p->w_xyz[i], K, H, sv.act[i + 1], d.ld_act(i + 1), p->b_xyz[i], 0, 1,
             INT64_MAX, 1, st));
   }
+  if (!d.viewdirs())   // raw = fc_out h_L  (fc_out [4,H] rides in w_rgb / b_rgb)                                  :76
+    return lin(d.tc, sv.act[d.L], d.ld_act(d.L), d.M, H, p->w_rgb, H, 4, raw, 4, p->b_rgb, 0, 1, INT64_MAX, 0, st);
   RUN(lin(d.tc, sv.act[d.L], H, d.M, H, p->w_feat, H, H, sv.feat, H, p->b_feat, 0, 1, INT64_MAX, 1, st));      // :67
   RUN(lin(d.tc, sv.feat, H, d.M, H, p->w_alpha, H, 1, raw + 3, 4, p->b_alpha, 0, 1, INT64_MAX, 0, st));         // :68
   int64_t div, mod;
@@ -211,7 +214,7 @@ extern "C" int cnrf_flexnerf_bwd(const cnrf_flex_shape* s, const cnrf_flex_param
                                  void* workspace, size_t workspace_bytes, cnrf_stream_t stream) {
   FDims d;
   RUN(dims_of(s, d));
-  CNRF_REQUIRE(p && x_xyz && x_dir && g_raw && saved && g && workspace, CNRF_E_NULL);
+  CNRF_REQUIRE(p && x_xyz && (x_dir || !d.viewdirs()) && g_raw && saved && g && workspace, CNRF_E_NULL);
   cudaStream_t st = as_stream(stream);
   const int H = d.H, H2 = d.H / 2;
   Saved sv;
@@ -232,16 +235,27 @@ extern "C" int cnrf_flexnerf_bwd(const cnrf_flex_shape* s, const cnrf_flex_param
     RUN(add(ones, d.M, 1.0f));
     RUN(add(g->w_layer1, (int64_t)H * d.dx)); RUN(add(g->b_layer1, H));
     for (int i = 0; i < d.L; ++i) { RUN(add(g->w_xyz[i], (int64_t)H * (d.is_skip(i) ? H + d.dx : H))); RUN(add(g->b_xyz[i], H)); }
-    RUN(add(g->w_feat, (int64_t)H * H)); RUN(add(g->b_feat, H));
-    RUN(add(g->w_dir, (int64_t)H2 * (H + d.dd))); RUN(add(g->b_dir, H2));
-    RUN(add(g->w_alpha, H)); RUN(add(g->b_alpha, 1));
-    RUN(add(g->w_rgb, (int64_t)3 * H2)); RUN(add(g->b_rgb, 3));
+    if (d.viewdirs()) {
+      RUN(add(g->w_feat, (int64_t)H * H)); RUN(add(g->b_feat, H));
+      RUN(add(g->w_dir, (int64_t)H2 * (H + d.dd))); RUN(add(g->b_dir, H2));
+      RUN(add(g->w_alpha, H)); RUN(add(g->b_alpha, 1));
+      RUN(add(g->w_rgb, (int64_t)3 * H2)); RUN(add(g->b_rgb, 3));
+    } else {
+      RUN(add(g->w_rgb, (int64_t)4 * H)); RUN(add(g->b_rgb, 4));
+    }
     if (g_x_xyz) RUN(add(g_x_xyz, d.M * d.dx));
     RUN(cnrf_fill_batch(f, st));
   }
   auto bias_grad = [&](const float* dY, int64_t ldy, int64_t rows, int Nout, float* db) {
     return wgrad(d.tc, ones, 1, dY, ldy, rows, 1, Nout, db, Nout, st);                 // db = ones^T dY
   };
+  float *cur = gb, *nxt = ga;   // cur receives d h_L
+  if (!d.viewdirs()) {
+    // raw = fc_out h_L                                                                  models/model.py:76
+    RUN(wgrad(d.tc, g_raw, 4, sv.act[d.L], d.ld_act(d.L), d.M, 4, H, g->w_rgb, H, st));
+    RUN(bias_grad(g_raw, 4, d.M, 4, g->b_rgb));
+    RUN(dgrad(d.tc, g_raw, 4, d.M, 4, p->w_rgb, H, H, cur, H, sv.act[d.L], d.ld_act(d.L), 0, st));
+  } else {
   // rgb = fc_rgb v                                                                      models/model.py:72
   RUN(wgrad(d.tc, g_raw, 4, sv.v, H2, d.M, 3, H2, g->w_rgb, H2, st));
   RUN(bias_grad(g_raw, 4, d.M, 3, g->b_rgb));
@@ -263,8 +277,8 @@ extern "C" int cnrf_flexnerf_bwd(const cnrf_flex_shape* s, const cnrf_flex_param
   // feat = relu(fc_feat h_L)                                                            :67
   RUN(wgrad(d.tc, ga, H, sv.act[d.L], d.ld_act(d.L), d.M, H, H, g->w_feat, H, st));
   RUN(bias_grad(ga, H, d.M, H, g->b_feat));
-  float *cur = gb, *nxt = ga;   // cur receives d h_L
   RUN(dgrad(d.tc, ga, H, d.M, H, p->w_feat, H, H, cur, H, sv.act[d.L], d.ld_act(d.L), 0, st));
+  }
   for (int i = d.L - 1; i >= 0; --i) {                                                   // :60-64
     const int K = d.is_skip(i) ? H + d.dx : H;
     RUN(wgrad(d.tc, cur, H, sv.act[i], d.ld_act(i), d.M, H, K, g->w_xyz[i], K, st));

@@ -20,13 +20,12 @@ class FlexibleNeRFModel(torch.nn.Module):
       * x: a tensor (..., dim_xyz + dim_dir) of embedded inputs -- the reference's literal signature -> (..., 4);
       * x: a view_synthesis.nerf.FieldQuery (what our forward_pass passes): points and ray directions are embedded by the
         CUDA operator and the view-direction half of layers_dir[0] is evaluated once per ray -> (N, S, 4).
-    The use_viewdirs=False variant (fc_out head, :47-48,75-76) is not on the hot path of any config and raises."""
+    use_viewdirs=False (:47-48,75-76) keeps layer1 / layers_xyz and ends in fc_out (hidden -> 4); the direction columns of x,
+    if any, are ignored as in the reference.  It runs on the per-layer toolkit GEMMs (cnrf_flexnerf_* with dim_dir = 0)."""
 
     def __init__(self, num_layers=4, hidden_size=128, skip_connect_ids=[4], num_encoding_fn_xyz=6, num_encoding_fn_dir=4,
                  include_input_xyz=True, include_input_dir=True, use_viewdirs=True):
         super(FlexibleNeRFModel, self).__init__()
-        if not use_viewdirs:
-            raise NotImplementedError("FlexibleNeRFModel(use_viewdirs=False) has no libcnrf kernel path")
         self.num_layers = num_layers
         self.hidden_size = hidden_size
         self.skip_connect_ids = skip_connect_ids
@@ -43,15 +42,19 @@ class FlexibleNeRFModel(torch.nn.Module):
                 self.layers_xyz.append(torch.nn.Linear(self.dim_xyz + hidden_size, hidden_size))
             else:
                 self.layers_xyz.append(torch.nn.Linear(hidden_size, hidden_size))
-        self.fc_feat = torch.nn.Linear(hidden_size, hidden_size)
-        self.layers_dir = torch.nn.ModuleList()
-        self.layers_dir.append(torch.nn.Linear(self.dim_dir + hidden_size, hidden_size // 2))
-        self.fc_alpha = torch.nn.Linear(hidden_size, 1)
-        self.fc_rgb = torch.nn.Linear(hidden_size // 2, 3)
+        if use_viewdirs:
+            self.fc_feat = torch.nn.Linear(hidden_size, hidden_size)
+            self.layers_dir = torch.nn.ModuleList()
+            self.layers_dir.append(torch.nn.Linear(self.dim_dir + hidden_size, hidden_size // 2))
+            self.fc_alpha = torch.nn.Linear(hidden_size, 1)
+            self.fc_rgb = torch.nn.Linear(hidden_size // 2, 3)
+        else:
+            self.fc_out = torch.nn.Linear(hidden_size, 4)
         self.relu = torch.nn.functional.relu
 
     def _param_list(self):
-        layers = [self.layer1] + list(self.layers_xyz) + [self.fc_feat, self.layers_dir[0], self.fc_alpha, self.fc_rgb]
+        head = [self.fc_feat, self.layers_dir[0], self.fc_alpha, self.fc_rgb] if self.use_viewdirs else [self.fc_out]
+        layers = [self.layer1] + list(self.layers_xyz) + head
         out = []
         for layer in layers:
             out += [layer.weight, layer.bias]
@@ -65,21 +68,26 @@ class FlexibleNeRFModel(torch.nn.Module):
         params = self._param_list()
         if isinstance(x, FieldQuery):
             ex, ed = x.embedder_xyz, x.embedder_dir
-            assert 3 * ex.out_dim_per_channel == self.dim_xyz and 3 * ed.out_dim_per_channel == self.dim_dir, \
-                "embedder widths do not match the model's dim_xyz / dim_dir"
+            assert 3 * ex.out_dim_per_channel == self.dim_xyz, "embedder width does not match the model's dim_xyz"
             N, S = x.pts.shape[0], x.pts.shape[1]
             x_xyz = ex.embed(x.pts.reshape(-1, x.pts.shape[-1]))
-            viewdirs = x.rd / x.rd.norm(p=2, dim=-1).unsqueeze(-1)                       # nerf/__init__.py:126
-            x_dir = ed.embed(viewdirs)
+            if self.use_viewdirs:
+                assert 3 * ed.out_dim_per_channel == self.dim_dir, "embedder width does not match the model's dim_dir"
+                viewdirs = x.rd / x.rd.norm(p=2, dim=-1).unsqueeze(-1)                   # nerf/__init__.py:126
+                x_dir = ed.embed(viewdirs)
+            else:
+                x_dir = x_xyz.new_empty((N, 0))
             precision = _PRECISION_IDS[x.precision]
             pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
-            raw = ops.flexnerf(params, x_xyz, x_dir, self.num_layers, self.hidden_size, self.dim_xyz, self.dim_dir,
-                               self._skip_mask(), S, pairing=pairing, precision=precision)
+            raw = ops.flexnerf(params, x_xyz, x_dir, self.num_layers, self.hidden_size, self.dim_xyz,
+                               self.dim_dir if self.use_viewdirs else 0, self._skip_mask(), S, pairing=pairing,
+                               precision=precision)
             return raw.reshape(N, S, 4)
         lead = x.shape[:-1]
         x2 = x.reshape(-1, x.shape[-1])
-        raw = ops.flexnerf(params, x2[:, : self.dim_xyz], x2[:, self.dim_xyz:], self.num_layers, self.hidden_size,
-                           self.dim_xyz, self.dim_dir, self._skip_mask(), 1, pairing=_lib.PAIRING_CORRECT,
+        x_dir = x2[:, self.dim_xyz:] if self.use_viewdirs else x2.new_empty((x2.shape[0], 0))
+        raw = ops.flexnerf(params, x2[:, : self.dim_xyz], x_dir, self.num_layers, self.hidden_size, self.dim_xyz,
+                           self.dim_dir if self.use_viewdirs else 0, self._skip_mask(), 1, pairing=_lib.PAIRING_CORRECT,
                            precision=_lib.PRECISION_FP32)
         return raw.reshape(*lead, 4)
 

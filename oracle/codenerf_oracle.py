@@ -359,13 +359,15 @@ def render_split_np(num_rays: int, n_gpus: int) -> Tuple[np.ndarray, np.ndarray]
 # ----------------------------------------------------------------------------------------
 def flexible_nerf_mlp(p: Dict[str, Tensor], x: Tensor, dim_xyz: int, num_layers: int,
                       skip_connect_ids: Sequence[int]) -> Tensor:
-    """models/model.py:58-74 (use_viewdirs=True branch)."""
+    """models/model.py:58-76; the use_viewdirs=False network is recognised by its fc_out head (:47-48,75-76)."""
     xyz, view = x[..., :dim_xyz], x[..., dim_xyz:]
     out = torch.relu(_lin(p, "layer1", xyz))
     for i in range(num_layers - 1):
         if i in skip_connect_ids:
             out = torch.cat((out, xyz), dim=-1)
         out = torch.relu(_lin(p, f"layers_xyz.{i}", out))
+    if "fc_out.weight" in p:
+        return _lin(p, "fc_out", out)
     feat = torch.relu(_lin(p, "fc_feat", out))
     sigma = _lin(p, "fc_alpha", feat)
     out = torch.relu(_lin(p, "layers_dir.0", torch.cat((feat, view), dim=-1)))
@@ -374,11 +376,14 @@ def flexible_nerf_mlp(p: Dict[str, Tensor], x: Tensor, dim_xyz: int, num_layers:
 
 
 def flexible_nerf_shapes(num_layers: int, hidden: int, skip_connect_ids: Sequence[int], dim_xyz: int,
-                         dim_dir: int) -> Dict[str, Tuple[int, int]]:
-    """(out, in) of every Linear of FlexibleNeRFModel(use_viewdirs=True), in state_dict order.  models/model.py:31-46."""
+                         dim_dir: int, use_viewdirs: bool = True) -> Dict[str, Tuple[int, int]]:
+    """(out, in) of every Linear of FlexibleNeRFModel, in state_dict order.  models/model.py:31-48."""
     shapes = {"layer1": (hidden, dim_xyz)}
     for i in range(num_layers - 1):
         shapes[f"layers_xyz.{i}"] = (hidden, hidden + dim_xyz) if i in skip_connect_ids else (hidden, hidden)
+    if not use_viewdirs:
+        shapes["fc_out"] = (4, hidden)
+        return shapes
     shapes["fc_feat"] = (hidden, hidden)
     shapes["layers_dir.0"] = (hidden // 2, dim_dir + hidden)
     shapes["fc_alpha"] = (1, hidden)
@@ -387,11 +392,11 @@ def flexible_nerf_shapes(num_layers: int, hidden: int, skip_connect_ids: Sequenc
 
 
 def make_flexible_nerf_params(seed: int, num_layers: int = 8, hidden: int = 256, skip_connect_ids: Sequence[int] = (4,),
-                              dim_xyz: int = 63, dim_dir: int = 27) -> Dict[str, Tensor]:
+                              dim_xyz: int = 63, dim_dir: int = 27, use_viewdirs: bool = True) -> Dict[str, Tensor]:
     """Deterministic FlexibleNeRFModel parameters (numpy PCG64, torch.nn.Linear's default init range)."""
     rng = np.random.default_rng(seed)
     out: Dict[str, Tensor] = {}
-    for name, (o, i) in flexible_nerf_shapes(num_layers, hidden, skip_connect_ids, dim_xyz, dim_dir).items():
+    for name, (o, i) in flexible_nerf_shapes(num_layers, hidden, skip_connect_ids, dim_xyz, dim_dir, use_viewdirs).items():
         bound = 1.0 / math.sqrt(i)
         out[name + ".weight"] = torch.from_numpy(rng.uniform(-bound, bound, size=(o, i)).astype(np.float32))
         out[name + ".bias"] = torch.from_numpy(rng.uniform(-bound, bound, size=(o,)).astype(np.float32))

@@ -52,6 +52,21 @@ def main():
         with torch.no_grad():
             raw = nerf.forward_pass(Adapter(model), (pe_x, pe_d), rd, pts, (torch.zeros(N, 1), torch.zeros(N, 1)))
         out.update({f"{tag}_fp_rd": rd.numpy(), f"{tag}_fp_pts": pts.numpy(), f"{tag}_fp_raw": raw.numpy()})
+    # use_viewdirs=False (fc_out head, models/model.py:47-48,75-76): own generator, so the fixtures above keep their values
+    rng = np.random.default_rng(8765)
+    for tag, (L, H, skips, M) in {"small_nv": (4, 64, (2,), 37), "lego_nv": (8, 256, (4,), 19)}.items():
+        p = orc.make_flexible_nerf_params(32, L, H, skips, use_viewdirs=False)
+        model = models.FlexibleNeRFModel(L, H, list(skips), 10, 4, True, True, False)
+        model.load_state_dict({k: v.clone() for k, v in p.items()})
+        x = torch.from_numpy(rng.normal(size=(M, 90)).astype(np.float32)).requires_grad_(True)   # direction columns ignored
+        y = model(x)
+        g = torch.from_numpy(rng.normal(size=(M, 4)).astype(np.float32))
+        (y * g).sum().backward()
+        out.update({f"{tag}_L": L, f"{tag}_H": H, f"{tag}_skips": np.array(skips), f"{tag}_x": x.detach().numpy(),
+                    f"{tag}_y": y.detach().numpy(), f"{tag}_gy": g.numpy(), f"{tag}_gx": x.grad.numpy()})
+        for name, prm in model.named_parameters():
+            out[f"{tag}_g_{name}"] = prm.grad.numpy().reshape(-1)[::97].copy()
+            out[f"{tag}_gsum_{name}"] = np.float64(prm.grad.numpy().astype(np.float64).sum())
     np.savez(os.path.join(OUT, "flexnerf.npz"), **out)
     print("wrote flexnerf.npz", {k: v.shape for k, v in out.items() if hasattr(v, "shape") and v.ndim > 1})
 

@@ -45,6 +45,47 @@ def test_flexible_model_golden(golden_dir, dev, tag):
         assert abs(float(prm.grad.double().sum()) - float(g[f"{tag}_gsum_{name}"])) < 1e-3 * max(1.0, float(prm.grad.abs().sum()))
 
 
+@pytest.mark.parametrize("tag", ["small_nv", "lego_nv"])
+def test_flexible_model_without_viewdirs_golden(golden_dir, dev, tag):
+    """use_viewdirs=False (fc_out head, models/model.py:47-48,75-76): same state_dict names as the reference, outputs and all
+    gradients vs the live reference's; forward_pass around it (FieldQuery path) gives the same values in fp32 and bf16."""
+    import view_synthesis.models as models
+    import view_synthesis.nerf as nerf
+    g = np.load(os.path.join(golden_dir, "flexnerf.npz"))
+    L, H, skips = int(g[f"{tag}_L"]), int(g[f"{tag}_H"]), tuple(int(v) for v in g[f"{tag}_skips"])
+    p = orc.make_flexible_nerf_params(32, L, H, skips, use_viewdirs=False)
+    m = models.FlexibleNeRFModel(L, H, list(skips), 10, 4, True, True, False)
+    assert list(p) == list(m.state_dict())
+    m.load_state_dict({k: v.detach().clone() for k, v in p.items()})
+    m = m.to(dev)
+    x = T(g[f"{tag}_x"]).to(dev).requires_grad_(True)
+    y = m(x)
+    np.testing.assert_allclose(y.detach().cpu().numpy(), g[f"{tag}_y"], rtol=1e-4, atol=1e-4)
+    (y * T(g[f"{tag}_gy"]).to(dev)).sum().backward()
+    np.testing.assert_allclose(x.grad.cpu().numpy(), g[f"{tag}_gx"], rtol=1e-3, atol=1e-4)
+    for name, prm in m.named_parameters():
+        want = g[f"{tag}_g_{name}"]
+        np.testing.assert_allclose(prm.grad.cpu().numpy().reshape(-1)[::97], want, rtol=1e-3,
+                                   atol=1e-4 * max(1.0, float(np.abs(want).max())))
+        assert abs(float(prm.grad.double().sum()) - float(g[f"{tag}_gsum_{name}"])) < 1e-3 * max(1.0, float(prm.grad.abs().sum()))
+    # forward_pass: points embedded by the CUDA operator, ray directions unused; oracle on the same points
+    N, S = 64, 24
+    gen = torch.Generator().manual_seed(5)
+    rd, pts = torch.randn(N, 3, generator=gen), torch.randn(N, S, 3, generator=gen)
+    want = orc.flexible_forward_pass(p, rd, pts, orc.frequency_bands(10, True), orc.frequency_bands(4, True), L, skips)
+    emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev), nerf.PositionalEmbedder(4, True, True, torch.float32, dev))
+    zero = (torch.zeros(N, 1, device=dev), torch.zeros(N, 1, device=dev))
+    old = nerf.get_precision()
+    try:
+        for precision, tol in (("fp32", 1e-4), ("bf16", 3e-2)):
+            nerf.set_precision(precision)
+            with torch.no_grad():
+                raw = nerf.forward_pass(m, emb, rd.to(dev), pts.to(dev), zero)
+            np.testing.assert_allclose(raw.cpu().numpy(), want.detach().numpy(), rtol=tol, atol=tol)
+    finally:
+        nerf.set_precision(old)
+
+
 @pytest.mark.parametrize("tag", ["small", "lego"])
 def test_flexible_forward_pass_golden_pairing(golden_dir, dev, tag):
     """forward_pass around the class reproduces the reference's view-direction tiling (F6) in both precisions."""

@@ -162,3 +162,20 @@ def test_flexible_nerf_model(golden_dir):
         raw = orc.flexible_forward_pass({k: v.detach() for k, v in p.items()}, T(g[f"{tag}_fp_rd"]), T(g[f"{tag}_fp_pts"]),
                                         orc.frequency_bands(10, True), orc.frequency_bands(4, True), L, skips)
         close(raw, g[f"{tag}_fp_raw"], 2e-5)
+
+
+def test_flexible_nerf_model_without_viewdirs(golden_dir):
+    """a15, use_viewdirs=False (fc_out head, models/model.py:47-48,75-76): the direction columns of x carry no gradient."""
+    g = load(golden_dir, "flexnerf.npz")
+    for tag in ("small_nv", "lego_nv"):
+        L, H, skips = int(g[f"{tag}_L"]), int(g[f"{tag}_H"]), tuple(int(v) for v in g[f"{tag}_skips"])
+        p = {k: v.requires_grad_(True) for k, v in orc.make_flexible_nerf_params(32, L, H, skips, use_viewdirs=False).items()}
+        assert list(p)[-2:] == ["fc_out.weight", "fc_out.bias"] and len(p) == 2 * (L + 1)
+        x = T(g[f"{tag}_x"]).requires_grad_(True)
+        y = orc.flexible_nerf_mlp(p, x, 63, L, skips)
+        close(y, g[f"{tag}_y"], 2e-5)
+        (y * T(g[f"{tag}_gy"])).sum().backward()
+        close(x.grad, g[f"{tag}_gx"], 2e-5)
+        assert float(T(g[f"{tag}_gx"])[:, 63:].abs().max()) == 0.0
+        for name, prm in p.items():
+            np.testing.assert_allclose(prm.grad.numpy().reshape(-1)[::97], g[f"{tag}_g_{name}"], rtol=1e-4, atol=2e-5)
