@@ -119,6 +119,9 @@ _SIGS = {
     "cnrf_flexnerf_workspace_bytes": (c_sz, [C.POINTER(FlexShape), c_i32]),
     "cnrf_flexnerf_fwd": (C.c_int, [C.POINTER(FlexShape), C.POINTER(FlexPtrs), c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p,
                                     c_sz, C.c_void_p, c_sz, C.c_void_p]),
+    "cnrf_flexnerf_fused_inference": (c_i32, [C.POINTER(FlexShape)]),
+    "cnrf_flexnerf_fwd_pts": (C.c_int, [C.POINTER(FlexShape), C.POINTER(FlexPtrs), c_f32p, c_i64, c_f32p, c_i32, c_i32, c_f32p,
+                                        c_i64, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
     "cnrf_flexnerf_bwd": (C.c_int, [C.POINTER(FlexShape), C.POINTER(FlexPtrs), c_f32p, c_i64, c_f32p, c_i64, c_f32p, C.c_void_p,
                                     c_sz, C.POINTER(FlexPtrs), c_f32p, c_f32p, C.c_void_p, c_sz, C.c_void_p]),
     "cnrf_adamw_step": (C.c_int, [C.c_void_p, c_i32, c_f, c_f, c_f, C.c_void_p]),

@@ -816,6 +816,44 @@ class _FlexNerf(torch.autograd.Function):
         return (None, g_xyz, g_dir) + grads
 
 
+def flexnerf_fused_inference(num_layers, hidden, dim_xyz, dim_dir, skip_mask, precision):
+    """True where cnrf_flexnerf_fwd_pts applies: no gradients wanted and the fused bf16 chain takes this network."""
+    if torch.is_grad_enabled() or dim_dir <= 0:
+        return False
+    shp = FlexShape(int(num_layers), int(hidden), int(dim_xyz), int(dim_dir), int(skip_mask), 1, 1, _lib.PAIRING_REFERENCE,
+                    int(precision), 0)
+    return bool(_lib.load().cnrf_flexnerf_fused_inference(C.byref(shp)))
+
+
+def flexnerf_pts(params, pts, freqs_xyz, include_input, x_dir, num_layers, hidden, dim_xyz, dim_dir, skip_mask, num_samples,
+                 pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_BF16):
+    """Inference from sample positions pts (M, 3): gamma(x) is produced inside the fused chain (cnrf_flexnerf_fwd_pts).
+    Call only where flexnerf_fused_inference(...) is True."""
+    _req_cuda(pts, x_dir, freqs_xyz, *params)
+    assert not torch.is_grad_enabled(), "flexnerf_pts is the no-grad inference path"
+    lib = _lib.load()
+    pts, ld_pts = _rows(pts)
+    if ld_pts == 0:
+        pts, ld_pts = pts.contiguous(), pts.shape[1]
+    x_dir, ld_dir = _rows(x_dir)
+    if ld_dir == 0:
+        x_dir, ld_dir = x_dir.contiguous(), x_dir.shape[1]
+    params = tuple(_c(p.detach()) for p in params)
+    freqs_xyz = _c(freqs_xyz)
+    M, N = pts.shape[0], x_dir.shape[0]
+    assert M == N * num_samples and pts.shape[1] == 3, "FlexibleNeRF field: pts must be (rays x samples, 3)"
+    shp = FlexShape(int(num_layers), int(hidden), int(dim_xyz), int(dim_dir), int(skip_mask), N, int(num_samples), int(pairing),
+                    int(precision), 0)
+    dev = pts.device
+    ws = _bytes(lib.cnrf_flexnerf_workspace_bytes(C.byref(shp), 0), dev)
+    raw = torch.empty((M, 4), dtype=_f32, device=dev)
+    tab = _flex_ptrs(params, num_layers - 1, True)
+    check(lib.cnrf_flexnerf_fwd_pts(C.byref(shp), C.byref(tab), _p(pts), ld_pts, _p(freqs_xyz), freqs_xyz.numel(),
+                                    int(bool(include_input)), _p(x_dir), ld_dir, _p(raw), _p(ws), ws.numel(), _stream()),
+          "cnrf_flexnerf_fwd_pts")
+    return raw
+
+
 def flexnerf(params, x_xyz, x_dir, num_layers, hidden, dim_xyz, dim_dir, skip_mask, num_samples,
              pairing=_lib.PAIRING_REFERENCE, precision=_lib.PRECISION_FP32):
     cfg = (int(num_layers), int(hidden), int(dim_xyz), int(dim_dir), int(skip_mask), int(num_samples), int(pairing),

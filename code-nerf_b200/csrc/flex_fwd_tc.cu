@@ -31,8 +31,9 @@ constexpr int SLAB_W = 256 * 128;              // 32 KB weight slab (N = 256)
 constexpr int SLAB_WD = 144 * 128;             // 18 KB weight slab of the direction layer (N = 128 + sigma row, padded to 144)
 constexpr int RING = 3;
 constexpr int FT_MAX_LAYERS = 18;
+constexpr int FT_MAX_FREQS = 16;
 constexpr int FT_SMEM = 5 * SLAB_A + RING * SLAB_W + FT_MAX_LAYERS * 256 * 4 /*biases*/ + 3 * 128 * 4 /*w_rgb*/ +
-                        128 * 4 * 4 /*rgb partials*/ + 256 /*barriers*/ + 1024 /*alignment*/;
+                        128 * 4 * 4 /*rgb partials*/ + FT_MAX_FREQS * 4 + 256 /*barriers*/ + 1024 /*alignment*/;
 
 struct FlexLayer {
   uint32_t wofs;      // byte offset of the layer's first weight slab in the packed image
@@ -47,6 +48,8 @@ struct FlexFwdArgs {
   const uint8_t* packed;
   const float* bias[FT_MAX_LAYERS];  // fp32 [256] (unused for the direction layer: its bias is inside betad)
   const float* x_xyz; int64_t ld_xyz; int dx;
+  // pts != NULL: gamma(x) is computed here from the sample positions [M,3] (position_embed.py:44-53), x_xyz is not read
+  const float* pts; int64_t ld_pts; const float* freqs; int nfreq; int inc;
   const float* betad;                // [N, 128] per-ray: Wdir[:, H:] gamma(d) + b_dir
   const float* w_rgb; const float* b_rgb; const float* b_alpha;
   float* raw;                        // [M, 4]
@@ -81,6 +84,32 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
   return d;
 }
 
+// gamma(x) columns [32 H, 32 H + 32) of one sample: column 3 (INC + 2 k) + d = sin(f_k x_d), three columns on = cos(f_k x_d)
+// (position_embed.py:44-53).  One sincosf per (band, channel) the column range touches; every index is static once unrolled.
+template <int H, int INC>
+__device__ __forceinline__ void gamma_cols(const float (&x)[3], const float* fr, int nfreq, float (&v)[32]) {
+  constexpr int J0 = 32 * H, J1 = J0 + 32;
+  constexpr int B0 = J0 / 3 - INC, B1 = (J1 - 1) / 3 - INC;
+  constexpr int K0 = B0 < 0 ? 0 : B0 >> 1, K1 = B1 >> 1;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = 0.f;
+  if (INC && H == 0) { v[0] = x[0]; v[1] = x[1]; v[2] = x[2]; }
+#pragma unroll
+  for (int k = K0; k <= K1; ++k) {
+    if (k < nfreq) {
+      const float f = fr[k];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        float sn, cs;
+        sincosf(__fmul_rn(x[d], f), &sn, &cs);
+        const int js = 3 * (INC + 2 * k) + d - J0, jc = js + 3;
+        if (js >= 0 && js < 32) v[js] = sn;
+        if (jc >= 0 && jc < 32) v[jc] = cs;
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ void epi_arrive(uint64_t* bar, int lane) {
   fence_proxy_async();            // generic-proxy smem writes -> visible to the tensor core's async proxy
   tc_fence_before();
@@ -96,7 +125,8 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   float* bias_sm = reinterpret_cast<float*>(ring + RING * SLAB_W);
   float* wrgb_sm = bias_sm + FT_MAX_LAYERS * 256;
   float* part_sm = wrgb_sm + 3 * 128;                      // [128][4]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(part_sm + 128 * 4);
+  float* freq_sm = part_sm + 128 * 4;                      // [FT_MAX_FREQS]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(freq_sm + FT_MAX_FREQS);
   uint64_t *full = bars, *empty = bars + RING, *acc_bar = bars + 2 * RING, *act_bar = bars + 2 * RING + 1;
   uint64_t* slab_bar = bars + 2 * RING + 2;            // [4]: the next layer's A slab s is written (8 arrivals: every epilogue warp)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RING + 6);
@@ -114,6 +144,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     bias_sm[i] = a.bias[l] ? __ldg(a.bias[l] + (i & 255)) : 0.f;
   }
   for (int i = tid; i < 3 * 128; i += FT_THREADS) wrgb_sm[i] = __ldg(a.w_rgb + i);
+  if (a.pts && tid < a.nfreq) freq_sm[tid] = __ldg(a.freqs + tid);
   if (warp == 9) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
@@ -188,7 +219,19 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
       const int64_t m = t * FT_ROWS + row;
       // gamma(x) -> slab 4: this thread converts columns [32 h, 32 h + 32) of its row
-      {
+      if (a.pts) {
+        const float* pr = a.pts + (m < a.M ? m : 0) * a.ld_pts;
+        const float x[3] = {__ldg(pr), __ldg(pr + 1), __ldg(pr + 2)};
+        float v[32];
+        if (h == 0) { if (a.inc) gamma_cols<0, 1>(x, freq_sm, a.nfreq, v); else gamma_cols<0, 0>(x, freq_sm, a.nfreq, v); }
+        else        { if (a.inc) gamma_cols<1, 1>(x, freq_sm, a.nfreq, v); else gamma_cols<1, 0>(x, freq_sm, a.nfreq, v); }
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const uint4 p = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
+                                     pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
+          *reinterpret_cast<uint4*>(act + 4 * SLAB_A + row * 128 + (((h * 4 + c) ^ (row & 7)) << 4)) = p;
+        }
+      } else {
         const float* xr = a.x_xyz + (m < a.M ? m : 0) * a.ld_xyz;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
@@ -304,7 +347,8 @@ bool cnrf_flex_fused_eligible(const cnrf_flex_shape* s) {
 
 // betad: [N,128] fp32 already computed; packed: cnrf_flex_fused_packed_bytes() of 1024-byte aligned workspace
 int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
-                        const float* betad, float* raw, uint8_t* packed, cudaStream_t st) {
+                        const float* betad, float* raw, uint8_t* packed, cudaStream_t st, const FlexPts* gp) {
+  if (gp && (gp->nfreq < 1 || gp->nfreq > FT_MAX_FREQS || 3 * (gp->inc + 2 * gp->nfreq) != s->dim_xyz)) return CNRF_E_SHAPE;
   const int H = 256, L = s->num_layers - 1, dx = s->dim_xyz, dd = s->dim_dir;
   FlexFwdArgs a = {};
   PackArgs pk = {};
@@ -346,6 +390,7 @@ int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, con
   }
   a.packed = packed;
   a.x_xyz = x_xyz; a.ld_xyz = ld_xyz; a.dx = dx;
+  if (gp) { a.pts = gp->pts; a.ld_pts = gp->ld; a.freqs = gp->freqs; a.nfreq = gp->nfreq; a.inc = gp->inc; }
   a.betad = betad; a.w_rgb = p->w_rgb; a.b_rgb = p->b_rgb; a.b_alpha = p->b_alpha;
   a.raw = raw; a.M = s->num_rays * (int64_t)s->num_samples; a.N = s->num_rays; a.S = s->num_samples; a.pairing = s->pairing;
   cudaGetSymbolAddress(reinterpret_cast<void**>(&a.err), g_flex_tc_error);

@@ -208,6 +208,33 @@ extern "C" int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_param
   return CNRF_OK;
 }
 
+extern "C" int32_t cnrf_flexnerf_fused_inference(const cnrf_flex_shape* s) {
+  FDims d;
+  static const bool no_fused = getenv("CNRF_FLEX_NO_FUSED") != nullptr;
+  return dims_of(s, d) == CNRF_OK && cnrf_flex_fused_eligible(s) && !no_fused ? 1 : 0;
+}
+
+extern "C" int cnrf_flexnerf_fwd_pts(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* pts, int64_t ld_pts,
+                                     const float* freqs_xyz, int32_t num_freqs, int32_t include_input, const float* x_dir,
+                                     int64_t ld_dir, float* raw, void* workspace, size_t workspace_bytes,
+                                     cnrf_stream_t stream) {
+  FDims d;
+  RUN(dims_of(s, d));
+  CNRF_REQUIRE(p && pts && freqs_xyz && x_dir && raw && workspace, CNRF_E_NULL);
+  CNRF_REQUIRE(ld_pts >= 3 && ld_dir >= d.dd, CNRF_E_SHAPE);
+  if (!cnrf_flexnerf_fused_inference(s)) return CNRF_E_UNSUPPORTED;
+  cudaStream_t st = as_stream(stream);
+  const int H = d.H, H2 = d.H / 2;
+  Arena ws(workspace, workspace_bytes);
+  float* betad = ws.take(d.N * H2);
+  float* pk = ws.take((cnrf_flex_fused_packed_bytes(d.L) + 1024) / sizeof(float));
+  CNRF_REQUIRE(ws.ok, CNRF_E_WORKSPACE);
+  uint8_t* packed = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(pk) + 1023) & ~uintptr_t(1023));
+  RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->w_dir + H, H + d.dd, H2, betad, H2, p->b_dir, 0, 1, INT64_MAX, 0, st));
+  const FlexPts gp = {pts, ld_pts, freqs_xyz, num_freqs, include_input ? 1 : 0};
+  return cnrf_flex_fused_fwd(s, p, nullptr, 0, betad, raw, packed, st, &gp);
+}
+
 extern "C" int cnrf_flexnerf_bwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
                                  const float* x_dir, int64_t ld_dir, const float* g_raw, const void* saved,
                                  size_t saved_bytes, const cnrf_flex_grads* g, float* g_x_xyz, float* g_x_dir,

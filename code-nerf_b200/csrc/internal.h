@@ -175,6 +175,9 @@ int cnrf_scatter_code_grads(const int64_t* ids, const CodeRuns& r, int64_t N, in
 // ---- flex_fwd_tc.cu: fused tcgen05 forward chain of the vanilla NeRF field (inference, bf16, hidden 256) -----------------
 bool cnrf_flex_fused_eligible(const cnrf_flex_shape* s);
 size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers);
+// gp != NULL: the kernel encodes the sample positions itself (x_xyz unused)
+struct FlexPts { const float* pts; int64_t ld; const float* freqs; int nfreq; int inc; };
 int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
-                        const float* betad /*[N,128]*/, float* raw, uint8_t* packed /*1024-byte aligned*/, cudaStream_t st);
+                        const float* betad /*[N,128]*/, float* raw, uint8_t* packed /*1024-byte aligned*/, cudaStream_t st,
+                        const FlexPts* gp = nullptr);
 int cnrf_flex_fused_error();

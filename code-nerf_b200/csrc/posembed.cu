@@ -4,21 +4,30 @@
 // 2^9 * |x|, so no fast-math intrinsics.
 #include "common.cuh"
 
+// One thread per (row m, band k, channel d): ONE sincosf serves the sin and the cos column of the band (k == 0 of an
+// include_input encoding copies x instead).  Row-major thread order, so a warp writes a contiguous run of each row.
 __global__ void pos_embed_fwd_kernel(const float* __restrict__ x, int64_t M, int D, const float* __restrict__ freqs,
                                      int L, int inc, int64_t ld_out, float* __restrict__ out) {
-  const int width = D * (inc + 2 * L);
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= M * width) return;
-  int64_t m = i / width;
-  int j = (int)(i - m * width);
-  int blk = j / D, d = j - blk * D;
-  float v = x[m * D + d];
-  if (!(inc && blk == 0)) {
-    int b = blk - inc;
-    float a = __fmul_rn(v, freqs[b >> 1]);                 // tensor * freq       position_embed.py:48
-    v = (b & 1) ? cosf(a) : sinf(a);                       // [sin, cos] per band position_embed.py:47
+  const int per_row = D * (L + inc);
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= M * per_row) return;
+  int64_t m;
+  int j;
+  if (M * per_row < (int64_t)1 << 32) {                    // 32-bit division when the index fits
+    const uint32_t mi = (uint32_t)i / (uint32_t)per_row;
+    m = mi; j = (int)((uint32_t)i - mi * (uint32_t)per_row);
+  } else {
+    m = i / per_row; j = (int)(i - m * per_row);
   }
-  out[m * ld_out + j] = v;
+  const int k = j / D, d = j - k * D;
+  const float v = __ldg(x + m * D + d);
+  float* o = out + m * ld_out;
+  if (inc && k == 0) { o[d] = v; return; }
+  const int b = k - inc;
+  float sn, cs;
+  sincosf(__fmul_rn(v, __ldg(freqs + b)), &sn, &cs);        // tensor * freq       position_embed.py:48
+  o[(inc + 2 * b) * D + d] = sn;                            // [sin, cos] per band position_embed.py:47
+  o[(inc + 2 * b + 1) * D + d] = cs;
 }
 
 __global__ void pos_embed_bwd_kernel(const float* __restrict__ x, const float* __restrict__ g_out, int64_t M, int D,
@@ -44,7 +53,7 @@ __global__ void pos_embed_bwd_kernel(const float* __restrict__ x, const float* _
 // internal entry points with a row stride (used by the fp32 field path to write into padded buffers)
 int cnrf_pos_embed_fwd_ld(const float* x, int64_t M, int D, const float* freqs, int L, int inc, int64_t ld_out,
                           float* out, cudaStream_t st) {
-  pos_embed_fwd_kernel<<<grid_for(M * D * (inc + 2 * L), 256), 256, 0, st>>>(x, M, D, freqs, L, inc, ld_out, out);
+  pos_embed_fwd_kernel<<<grid_for(M * D * (inc + L), 256), 256, 0, st>>>(x, M, D, freqs, L, inc, ld_out, out);
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }

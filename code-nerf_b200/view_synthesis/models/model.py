@@ -70,6 +70,17 @@ class FlexibleNeRFModel(torch.nn.Module):
             ex, ed = x.embedder_xyz, x.embedder_dir
             assert 3 * ex.out_dim_per_channel == self.dim_xyz, "embedder width does not match the model's dim_xyz"
             N, S = x.pts.shape[0], x.pts.shape[1]
+            precision = _PRECISION_IDS[x.precision]
+            pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
+            if self.use_viewdirs and x.pts.shape[-1] == 3 and ops.flexnerf_fused_inference(
+                    self.num_layers, self.hidden_size, self.dim_xyz, self.dim_dir, self._skip_mask(), precision):
+                # rendering: the fused chain encodes the sample positions itself, gamma(x) never exists in HBM
+                assert 3 * ed.out_dim_per_channel == self.dim_dir, "embedder width does not match the model's dim_dir"
+                viewdirs = x.rd / x.rd.norm(p=2, dim=-1).unsqueeze(-1)                   # nerf/__init__.py:126
+                raw = ops.flexnerf_pts(params, x.pts.reshape(-1, 3), ex.frequency_bands, ex.include_input, ed.embed(viewdirs),
+                                       self.num_layers, self.hidden_size, self.dim_xyz, self.dim_dir, self._skip_mask(), S,
+                                       pairing=pairing, precision=precision)
+                return raw.reshape(N, S, 4)
             x_xyz = ex.embed(x.pts.reshape(-1, x.pts.shape[-1]))
             if self.use_viewdirs:
                 assert 3 * ed.out_dim_per_channel == self.dim_dir, "embedder width does not match the model's dim_dir"
@@ -77,8 +88,6 @@ class FlexibleNeRFModel(torch.nn.Module):
                 x_dir = ed.embed(viewdirs)
             else:
                 x_dir = x_xyz.new_empty((N, 0))
-            precision = _PRECISION_IDS[x.precision]
-            pairing = {"reference": _lib.PAIRING_REFERENCE, "correct": _lib.PAIRING_CORRECT}[x.pairing]
             raw = ops.flexnerf(params, x_xyz, x_dir, self.num_layers, self.hidden_size, self.dim_xyz,
                                self.dim_dir if self.use_viewdirs else 0, self._skip_mask(), S, pairing=pairing,
                                precision=precision)

@@ -279,6 +279,17 @@ size_t cnrf_flexnerf_workspace_bytes(const cnrf_flex_shape* s, int32_t backward)
 int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
                       const float* x_dir, int64_t ld_dir, float* raw /*[M,4]*/, void* saved, size_t saved_bytes,
                       void* workspace, size_t workspace_bytes, cnrf_stream_t stream);
+/* Inference straight from the sample positions: forward_pass (nerf/__init__.py:116-134) embeds pts [M,3] (row stride
+ * ld_pts) with PositionalEmbedder (position_embed.py:44-53: freqs_xyz [num_freqs], include_input) and feeds the result to
+ * the model; here gamma(x) is produced inside the fused tcgen05 chain and never exists in HBM.  dim_xyz must equal
+ * 3 * (include_input + 2 * num_freqs).  Only where cnrf_flexnerf_fused_inference(s) is 1 (CNRF_PRECISION_BF16, keep = 0,
+ * hidden 256, dim_xyz <= 64, dim_dir > 0); CNRF_E_UNSUPPORTED otherwise -- embed and call cnrf_flexnerf_fwd then.
+ * Workspace: cnrf_flexnerf_workspace_bytes(s, 0). */
+int32_t cnrf_flexnerf_fused_inference(const cnrf_flex_shape* s);
+int cnrf_flexnerf_fwd_pts(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* pts, int64_t ld_pts,
+                          const float* freqs_xyz, int32_t num_freqs, int32_t include_input, const float* x_dir,
+                          int64_t ld_dir, float* raw /*[M,4]*/, void* workspace, size_t workspace_bytes,
+                          cnrf_stream_t stream);
 /* g_x_xyz [M, dim_xyz] / g_x_dir [N, dim_dir] (dense) may be NULL when the inputs carry no gradient. */
 int cnrf_flexnerf_bwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
                       const float* x_dir, int64_t ld_dir, const float* g_raw /*[M,4]*/, const void* saved,

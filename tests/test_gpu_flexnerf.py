@@ -184,3 +184,33 @@ def test_flexible_fused_inference_chain(dev, N, S, pairing, L, skips):
                                           L, skips, pairing=pairing)
     err = (raw.cpu() - raw_o).abs()
     assert float(err.max()) < 3e-2 and float(err.mean()) < 3e-3, (float(err.max()), float(err.mean()))
+
+
+@pytest.mark.parametrize("nf,logs,inc", [(10, True, True), (10, False, True), (10, True, False), (7, True, True)])
+def test_flexible_fused_chain_encodes_positions_itself(dev, nf, logs, inc):
+    """cnrf_flexnerf_fwd_pts (gamma(x) computed inside the fused chain from the sample positions, position_embed.py:44-53)
+    against cnrf_flexnerf_fwd on the embedded tensor: same bf16 operands up to the last bit of a sine, so 2e-3 on the raw
+    field; linear / log bands, with and without the input columns, a width that leaves slab columns unused."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    from codenerf_b200 import ops, _lib
+    L, H, skips, N, S = 8, 256, (4,), 257, 33
+    torch.manual_seed(nf + inc)
+    m = models.FlexibleNeRFModel(L, H, list(skips), nf, 4, inc, True, True).to(dev)
+    ex = nerf.PositionalEmbedder(nf, logs, inc, torch.float32, dev)
+    ed = nerf.PositionalEmbedder(4, True, True, torch.float32, dev)
+    pts = (torch.rand(N, S, 3, device=dev) * 6 - 3)
+    rd = torch.randn(N, 3, device=dev)
+    x_dir = ed.embed(rd / rd.norm(dim=-1, keepdim=True))
+    args = (L, H, m.dim_xyz, m.dim_dir, m._skip_mask(), S)
+    with torch.no_grad():
+        assert ops.flexnerf_fused_inference(L, H, m.dim_xyz, m.dim_dir, m._skip_mask(), _lib.PRECISION_BF16)
+        a = ops.flexnerf_pts(m._param_list(), pts.reshape(-1, 3), ex.frequency_bands, inc, x_dir, *args,
+                             precision=_lib.PRECISION_BF16)
+        b = ops.flexnerf(m._param_list(), ex.embed(pts.reshape(-1, 3)), x_dir, *args, precision=_lib.PRECISION_BF16)
+    assert _lib.load().cnrf_debug_tc_error() == 0
+    assert torch.isfinite(a).all()
+    err = (a - b).abs()
+    assert float(err.max()) < 2e-3 and float(err.mean()) < 1e-5, (float(err.max()), float(err.mean()))
+    assert not ops.flexnerf_fused_inference(L, 128, m.dim_xyz, m.dim_dir, m._skip_mask(), _lib.PRECISION_BF16)
+    assert not ops.flexnerf_fused_inference(L, H, m.dim_xyz, m.dim_dir, m._skip_mask(), _lib.PRECISION_FP32)
