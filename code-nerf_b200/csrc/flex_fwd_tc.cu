@@ -9,7 +9,9 @@
 //           bulk copy) runs ahead of the MMAs across layers and tiles.
 //   TMEM  : two [128 x 256] fp32 accumulators, used by alternate layers.
 //   warps : 0-7 epilogue (tcgen05.ld -> + bias -> ReLU -> bf16 -> swizzled smem = next layer's A operand), 8 = TMA
-//           producer, 9 = MMA issuer (elect.sync lane, M128 N256 K16).
+//           producer, 9 = MMA issuer (elect.sync lane, M128 N256 K16).  -DFT_EPI_WARPS_N=16 gives every sample row four
+//           epilogue threads instead of two: measured 2.5 % SLOWER on a lego frame (226 vs 221 ms) -- the epilogue is bound
+//           by the shared-memory pipe it shares with the MMAs' operand reads, not by latency.
 // Layer-to-layer overlap inside a tile: the eight epilogue warps finish the next layer's A operand one 64-column slab at a
 // time (slab s = columns 64 s .. 64 s + 63: warp half h converts its 32 of them) and arrive on that slab's barrier; the MMA
 // warp starts the next layer's K slab s as soon as slab s is there, accumulating into the OTHER TMEM buffer, so only the last
@@ -24,8 +26,26 @@
 
 using namespace tc;
 
+// Timer builds only (-DCNRF_FLEX_TIMERS, scripts/trace_flex.py): clock64 stamps of block 0's 4th tile, [layer][event]:
+//   0 epilogue sees the accumulator, 1-4 epilogue warp 0 has arrived on slab 0-3 (last layer: 1 = raw written), 5 gamma(x) built,
+//   8 + 3 i + {0 A slab seen, 1 weight slab seen, 2 MMAs issued} for K slab i of the MMA warp, 23 accumulator committed,
+//   24 + 2 i + {0 ring slot seen empty, 1 copy issued} for K slab i of the producer warp.
+__device__ long long g_flex_trace[18 * 40];
+#ifdef CNRF_FLEX_TIMERS
+#define XTRACE(it, l, ev) do { if (blockIdx.x == 0 && (it) == 3 && (threadIdx.x & 31) == 0) g_flex_trace[(l) * 40 + (ev)] = clock64(); } while (0)
+#else
+#define XTRACE(it, l, ev) do { } while (0)
+#endif
+
 namespace {
-constexpr int FT_ROWS = 128, FT_THREADS = 320, FT_EPI_WARPS = 8;
+#ifndef FT_EPI_WARPS_N
+#define FT_EPI_WARPS_N 8
+#endif
+constexpr int FT_ROWS = 128, FT_EPI_WARPS = FT_EPI_WARPS_N, FT_THREADS = 32 * (FT_EPI_WARPS + 2);
+constexpr int EH = FT_EPI_WARPS / 4;           // epilogue threads per sample row (TMEM lane quarter = warp_id % 4)
+constexpr int CW = 64 / EH;                    // columns of every 64-column slab one thread converts
+constexpr int DW = 128 / EH;                   // columns of the direction layer one thread reduces
+static_assert(EH == 2 || EH == 4, "8 or 16 epilogue warps");
 constexpr int SLAB_A = FT_ROWS * 128;          // 16 KB activation slab
 constexpr int SLAB_W = 256 * 128;              // 32 KB weight slab (N = 256)
 constexpr int SLAB_WD = 144 * 128;             // 18 KB weight slab of the direction layer (N = 128 + sigma row, padded to 144)
@@ -33,7 +53,7 @@ constexpr int RING = 3;
 constexpr int FT_MAX_LAYERS = 18;
 constexpr int FT_MAX_FREQS = 16;
 constexpr int FT_SMEM = 5 * SLAB_A + RING * SLAB_W + FT_MAX_LAYERS * 256 * 4 /*biases*/ + 3 * 128 * 4 /*w_rgb*/ +
-                        128 * 4 * 4 /*rgb partials*/ + FT_MAX_FREQS * 4 + 256 /*barriers*/ + 1024 /*alignment*/;
+                        (EH - 1) * 128 * 4 * 4 /*rgb partials*/ + FT_MAX_FREQS * 4 + 256 /*barriers*/ + 1024 /*alignment*/;
 
 struct FlexLayer {
   uint32_t wofs;      // byte offset of the layer's first weight slab in the packed image
@@ -84,15 +104,15 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
   return d;
 }
 
-// gamma(x) columns [32 H, 32 H + 32) of one sample: column 3 (INC + 2 k) + d = sin(f_k x_d), three columns on = cos(f_k x_d)
+// gamma(x) columns [CW H, CW H + CW) of one sample: column 3 (INC + 2 k) + d = sin(f_k x_d), three columns on = cos(f_k x_d)
 // (position_embed.py:44-53).  One sincosf per (band, channel) the column range touches; every index is static once unrolled.
 template <int H, int INC>
-__device__ __forceinline__ void gamma_cols(const float (&x)[3], const float* fr, int nfreq, float (&v)[32]) {
-  constexpr int J0 = 32 * H, J1 = J0 + 32;
+__device__ __forceinline__ void gamma_cols(const float (&x)[3], const float* fr, int nfreq, float (&v)[CW]) {
+  constexpr int J0 = CW * H, J1 = J0 + CW;
   constexpr int B0 = J0 / 3 - INC, B1 = (J1 - 1) / 3 - INC;
   constexpr int K0 = B0 < 0 ? 0 : B0 >> 1, K1 = B1 >> 1;
 #pragma unroll
-  for (int j = 0; j < 32; ++j) v[j] = 0.f;
+  for (int j = 0; j < CW; ++j) v[j] = 0.f;
   if (INC && H == 0) { v[0] = x[0]; v[1] = x[1]; v[2] = x[2]; }
 #pragma unroll
   for (int k = K0; k <= K1; ++k) {
@@ -103,12 +123,22 @@ __device__ __forceinline__ void gamma_cols(const float (&x)[3], const float* fr,
         float sn, cs;
         sincosf(__fmul_rn(x[d], f), &sn, &cs);
         const int js = 3 * (INC + 2 * k) + d - J0, jc = js + 3;
-        if (js >= 0 && js < 32) v[js] = sn;
-        if (jc >= 0 && jc < 32) v[jc] = cs;
+        if (js >= 0 && js < CW) v[js] = sn;
+        if (jc >= 0 && jc < CW) v[jc] = cs;
       }
     }
   }
 }
+template <int INC>
+__device__ __forceinline__ void gamma_row_part(int h, const float (&x)[3], const float* fr, int nfreq, float (&v)[CW]) {
+  if (h == 0) gamma_cols<0, INC>(x, fr, nfreq, v);
+  else if (h == 1) gamma_cols<1, INC>(x, fr, nfreq, v);
+  else if (EH == 4 && h == 2) gamma_cols<2 % EH, INC>(x, fr, nfreq, v);
+  else gamma_cols<3 % EH, INC>(x, fr, nfreq, v);
+}
+template <int W> struct TmemLd;
+template <> struct TmemLd<32> { static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[32]) { tmem_ld32(t, r); } };
+template <> struct TmemLd<16> { static __device__ __forceinline__ void ld(uint32_t t, uint32_t (&r)[16]) { tmem_ld16(t, r); } };
 
 __device__ __forceinline__ void epi_arrive(uint64_t* bar, int lane) {
   fence_proxy_async();            // generic-proxy smem writes -> visible to the tensor core's async proxy
@@ -125,7 +155,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   float* bias_sm = reinterpret_cast<float*>(ring + RING * SLAB_W);
   float* wrgb_sm = bias_sm + FT_MAX_LAYERS * 256;
   float* part_sm = wrgb_sm + 3 * 128;                      // [128][4]
-  float* freq_sm = part_sm + 128 * 4;                      // [FT_MAX_FREQS]
+  float* freq_sm = part_sm + (EH - 1) * 128 * 4;                      // [FT_MAX_FREQS]
   uint64_t* bars = reinterpret_cast<uint64_t*>(freq_sm + FT_MAX_FREQS);
   uint64_t *full = bars, *empty = bars + RING, *acc_bar = bars + 2 * RING, *act_bar = bars + 2 * RING + 1;
   uint64_t* slab_bar = bars + 2 * RING + 2;            // [4]: the next layer's A slab s is written (8 arrivals: every epilogue warp)
@@ -145,7 +175,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   }
   for (int i = tid; i < 3 * 128; i += FT_THREADS) wrgb_sm[i] = __ldg(a.w_rgb + i);
   if (a.pts && tid < a.nfreq) freq_sm[tid] = __ldg(a.freqs + tid);
-  if (warp == 9) tmem_alloc(tmem_slot, 512);
+  if (warp == FT_EPI_WARPS + 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -153,119 +183,131 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   const int64_t ntiles = (a.M + FT_ROWS - 1) / FT_ROWS;
   bool ok = true;
 
-  if (warp == 8) {
+  if (warp == FT_EPI_WARPS) {
     // ---- TMA producer: the global sequence of weight slabs (tile-major, layer, K slab) through the ring
-    uint32_t s = 0;
-    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+    uint32_t slot = 0, par = 1;
+    int it = 0;
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
       for (int l = 0; l < a.nlayers && ok; ++l) {
         const FlexLayer L = a.layer[l];
         const uint32_t bytes = L.n_out == 256 ? SLAB_W : SLAB_WD;
-        for (int i = 0; i < L.kslabs && ok; ++i, ++s) {
+        for (int i = 0; i < L.kslabs && ok; ++i) {
           const int j = L.skip ? (i == 0 ? L.kslabs - 1 : i - 1) : i;      // K-slab order of the MMA warp (gamma(x) first)
-          const uint32_t slot = s % RING, ph = (s / RING) & 1;
-          ok = mbar_wait(&empty[slot], ph ^ 1, a.err);
+          ok = mbar_wait(&empty[slot], par, a.err);
+          XTRACE(it, l, 24 + 2 * i);
           if (ok && elect_one()) {
             mbar_arrive_expect_tx(&full[slot], bytes);
             bulk_g2s(ring + slot * SLAB_W, a.packed + L.wofs + (size_t)j * bytes, bytes, &full[slot]);
           }
           __syncwarp();
+          XTRACE(it, l, 25 + 2 * i);
+          if (++slot == RING) { slot = 0; par ^= 1u; }
         }
       }
     }
-  } else if (warp == 9) {
-    // ---- MMA issuer
-    uint32_t s = 0, act_ph = 0, slab_ph = 0;
-    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+  } else if (warp == FT_EPI_WARPS + 1) {
+    // ---- MMA issuer.  The 64-bit operand descriptors differ only in their start-address field (bytes >> 4): the two
+    // bases are built once and every MMA adds an offset, which keeps the issue sequence of a K slab short.
+    const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);          // provably warp-uniform copy
+    const uint64_t a_desc0 = smem_desc(smem_u32(act), 16, 1024, SWIZZLE_128B);
+    const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
+    uint32_t slot = 0, par = 0, act_ph = 0, slab_ph = 0;
+    int it = 0;
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
+#pragma unroll 1
       for (int l = 0; l < a.nlayers && ok; ++l) {
         const FlexLayer L = a.layer[l];
         const uint32_t idesc = idesc_bf16(FT_ROWS, L.n_out, 0, 0);
-        const uint32_t acc = tmem + (uint32_t)(l & 1) * 256u;     // alternate layers, alternate accumulators
+        const uint32_t acc = tmem_u + (uint32_t)(l & 1) * 256u;   // alternate layers, alternate accumulators
         if (l == 0) {                                       // layer1 reads gamma(x): written once per tile
-          ok = mbar_wait(act_bar, act_ph, a.err);
+          ok = __all_sync(0xFFFFFFFFu, mbar_wait(act_bar, act_ph, a.err));
           act_ph ^= 1;
           tc_fence_after();
         }
-        for (int i = 0; i < L.kslabs && ok; ++i, ++s) {
+#pragma unroll 1
+        for (int i = 0; i < L.kslabs && ok; ++i) {
           const int j = L.skip ? (i == 0 ? L.kslabs - 1 : i - 1) : i;      // K slab (the skip layer starts with gamma(x), always there)
           const int aslab = (L.skip && j == L.kslabs - 1) ? 4 : L.a_first + j;
           if (l > 0 && aslab < 4) {                         // a hidden slab: the previous layer's epilogue has finished it
-            ok = mbar_wait(&slab_bar[aslab], slab_ph, a.err);
-            tc_fence_after();
+            ok = __all_sync(0xFFFFFFFFu, mbar_wait(&slab_bar[aslab], slab_ph, a.err));
             if (!ok) break;
           }
-          const uint32_t slot = s % RING, ph = (s / RING) & 1;
-          ok = mbar_wait(&full[slot], ph, a.err);
+          XTRACE(it, l, 8 + 3 * i);
+          ok = __all_sync(0xFFFFFFFFu, mbar_wait(&full[slot], par, a.err));
           tc_fence_after();
-          const uint32_t pa = smem_u32(act + aslab * SLAB_A), pb = smem_u32(ring + slot * SLAB_W);
+          XTRACE(it, l, 9 + 3 * i);
+          const uint64_t ad = a_desc0 + (uint64_t)((uint32_t)(aslab * SLAB_A) >> 4);
+          const uint64_t bd = b_desc0 + (uint64_t)((slot * (uint32_t)SLAB_W) >> 4);
           if (ok && elect_one()) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              umma_bf16(acc, smem_desc(pa + k * 32, 16, 1024, SWIZZLE_128B), smem_desc(pb + k * 32, 16, 1024, SWIZZLE_128B),
-                        idesc, (i > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < 4; ++k) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, (i | k) != 0);
             umma_commit(&empty[slot]);                      // the slot is free once these MMAs have read it
           }
           __syncwarp();
+          XTRACE(it, l, 10 + 3 * i);
+          if (++slot == RING) { slot = 0; par ^= 1u; }
         }
         if (l > 0) slab_ph ^= 1;                            // every slab barrier completes once per hidden-layer epilogue
         if (ok && elect_one()) umma_commit(acc_bar);
         __syncwarp();
+        XTRACE(it, l, 23);
       }
     }
   } else {
-    // ---- epilogue warps: warp w owns TMEM lanes / rows 32 (w & 3) .. +31 and column half w >> 2
+    // ---- epilogue warps: warp w owns TMEM lanes / rows 32 (w & 3) .. +31 and column part h = w >> 2 of EH
     const int q = warp & 3, h = warp >> 2;
     const int row = q * 32 + lane;
     uint32_t acc_ph = 0;
-    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+    int it = 0;
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
       const int64_t m = t * FT_ROWS + row;
-      // gamma(x) -> slab 4: this thread converts columns [32 h, 32 h + 32) of its row
-      if (a.pts) {
-        const float* pr = a.pts + (m < a.M ? m : 0) * a.ld_pts;
-        const float x[3] = {__ldg(pr), __ldg(pr + 1), __ldg(pr + 2)};
-        float v[32];
-        if (h == 0) { if (a.inc) gamma_cols<0, 1>(x, freq_sm, a.nfreq, v); else gamma_cols<0, 0>(x, freq_sm, a.nfreq, v); }
-        else        { if (a.inc) gamma_cols<1, 1>(x, freq_sm, a.nfreq, v); else gamma_cols<1, 0>(x, freq_sm, a.nfreq, v); }
+      // gamma(x) -> slab 4: this thread converts columns [CW h, CW h + CW) of its row
+      {
+        float v[CW];
+        if (a.pts) {
+          const float* pr = a.pts + (m < a.M ? m : 0) * a.ld_pts;
+          const float x[3] = {__ldg(pr), __ldg(pr + 1), __ldg(pr + 2)};
+          if (a.inc) gamma_row_part<1>(h, x, freq_sm, a.nfreq, v); else gamma_row_part<0>(h, x, freq_sm, a.nfreq, v);
+        } else {
+          const float* xr = a.x_xyz + (m < a.M ? m : 0) * a.ld_xyz;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const uint4 p = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
-                                     pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
-          *reinterpret_cast<uint4*>(act + 4 * SLAB_A + row * 128 + (((h * 4 + c) ^ (row & 7)) << 4)) = p;
-        }
-      } else {
-        const float* xr = a.x_xyz + (m < a.M ? m : 0) * a.ld_xyz;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          float v[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int col = h * 32 + c * 8 + e;
+          for (int e = 0; e < CW; ++e) {
+            const int col = h * CW + e;
             v[e] = (m < a.M && col < a.dx) ? __ldg(xr + col) : 0.f;
           }
-          const uint4 p = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
-          *reinterpret_cast<uint4*>(act + 4 * SLAB_A + row * 128 + (((h * 4 + c) ^ (row & 7)) << 4)) = p;
+        }
+#pragma unroll
+        for (int c = 0; c < CW / 8; ++c) {
+          const uint4 p = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
+                                     pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
+          *reinterpret_cast<uint4*>(act + 4 * SLAB_A + row * 128 + (((h * (CW / 8) + c) ^ (row & 7)) << 4)) = p;
         }
       }
       epi_arrive(act_bar, lane);
+      if (warp == 0) XTRACE(it, 0, 5);
       for (int l = 0; l < a.nlayers && ok; ++l) {
         ok = mbar_wait(acc_bar, acc_ph, a.err);
         acc_ph ^= 1;
         tc_fence_after();
         if (!ok) break;
+        if (warp == 0) XTRACE(it, l, 0);
         const uint32_t acc = tmem + (uint32_t)(l & 1) * 256u;
         if (l + 1 < a.nlayers) {
-          // hidden layer: slab s = columns 64 s .. 64 s + 63 of the next A operand; this warp converts the 32 columns of its
-          // half h, then arrives on the slab's barrier -- the MMA warp starts the next layer's K slab s right away
+          // hidden layer: slab s = columns 64 s .. 64 s + 63 of the next A operand; this thread converts CW of them, then the
+          // warp arrives on the slab's barrier -- the MMA warp starts the next layer's K slab s right away
           const float* b = bias_sm + l * 256;
-          const uint32_t t0 = acc + ((uint32_t)(q * 32) << 16) + h * 32;
-          uint32_t v[2][32];
-          tmem_ld32(t0, v[0]);
+          const uint32_t t0 = acc + ((uint32_t)(q * 32) << 16) + h * CW;
+          uint32_t v[2][CW];
+          TmemLd<CW>::ld(t0, v[0]);
 #pragma unroll
           for (int sl = 0; sl < 4; ++sl) {
+            if (warp == 0 && sl == 1) XTRACE(it, l, 30);
             tmem_ld_wait();
-            if (sl + 1 < 4) tmem_ld32(t0 + (sl + 1) * 64, v[(sl + 1) & 1]);      // next slab's block in flight under this one
+            if (warp == 0 && sl == 1) XTRACE(it, l, 31);
+            if (sl + 1 < 4) TmemLd<CW>::ld(t0 + (sl + 1) * 64, v[(sl + 1) & 1]);      // next slab's block in flight under this one
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              const int col = sl * 64 + h * 32 + c * 8;
+            for (int c = 0; c < CW / 8; ++c) {
+              const int col = sl * 64 + h * CW + c * 8;
               const float4 b0 = *reinterpret_cast<const float4*>(b + col);       // warp-uniform: LDS broadcast
               const float4 b1 = *reinterpret_cast<const float4*>(b + col + 4);
               const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
@@ -275,19 +317,25 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
               // ReLU rides in the conversion (cvt.rn.relu.bf16x2.f32): no FMNMX per element
               const uint4 p = make_uint4(pack_bf16_relu(x[0], x[1]), pack_bf16_relu(x[2], x[3]), pack_bf16_relu(x[4], x[5]),
                                          pack_bf16_relu(x[6], x[7]));
-              *reinterpret_cast<uint4*>(act + sl * SLAB_A + row * 128 + (((h * 4 + c) ^ (row & 7)) << 4)) = p;
+              *reinterpret_cast<uint4*>(act + sl * SLAB_A + row * 128 + (((h * (CW / 8) + c) ^ (row & 7)) << 4)) = p;
             }
+            if (warp == 0 && sl == 1) XTRACE(it, l, 32);
+#ifdef CNRF_FLEX_TIMERS
+            fence_proxy_async();
+            if (warp == 0 && sl == 1) XTRACE(it, l, 33);
+#endif
             epi_arrive(&slab_bar[sl], lane);
+            if (warp == 0) XTRACE(it, l, 1 + sl);
           }
         } else {
-          // direction layer: columns [64 h, 64 h + 64) -> + betad[ray] -> ReLU -> fc_rgb partial sums; column 128 = sigma
+          // direction layer: columns [DW h, DW h + DW) -> + betad[ray] -> ReLU -> fc_rgb partial sums; column 128 = sigma
           const int64_t ray = a.pairing == CNRF_PAIRING_REFERENCE ? (m % a.N) : (m / a.S);
-          const float* bd = a.betad + (m < a.M ? ray : 0) * 128 + h * 64;
+          const float* bd = a.betad + (m < a.M ? ray : 0) * 128 + h * DW;
           float r = 0.f, g = 0.f, bl = 0.f;
 #pragma unroll 1
-          for (int cb = 0; cb < 2; ++cb) {
+          for (int cb = 0; cb < DW / 32; ++cb) {
             uint32_t v[32];
-            tmem_ld32(acc + ((uint32_t)(q * 32) << 16) + h * 64 + cb * 32, v);
+            tmem_ld32(acc + ((uint32_t)(q * 32) << 16) + h * DW + cb * 32, v);
             tmem_ld_wait();
 #pragma unroll
             for (int e = 0; e < 32; e += 4) {
@@ -295,7 +343,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
               const float add[4] = {bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
               for (int i = 0; i < 4; ++i) {
-                const int n = h * 64 + cb * 32 + e + i;
+                const int n = h * DW + cb * 32 + e + i;
                 const float x = fmaxf(__uint_as_float(v[e + i]) + add[i], 0.f);
                 r = fmaf(x, wrgb_sm[n], r); g = fmaf(x, wrgb_sm[128 + n], g); bl = fmaf(x, wrgb_sm[256 + n], bl);
               }
@@ -303,28 +351,34 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
           }
           float sigma = 0.f;
           if (h == 0) {
-            uint32_t v[32];
-            tmem_ld32(acc + ((uint32_t)(q * 32) << 16) + 128, v);
+            uint32_t v[16];
+            tmem_ld16(acc + ((uint32_t)(q * 32) << 16) + 128, v);
             tmem_ld_wait();
             sigma = __uint_as_float(v[0]) + __ldg(a.b_alpha);
           } else {
-            part_sm[row * 4 + 0] = r; part_sm[row * 4 + 1] = g; part_sm[row * 4 + 2] = bl;
+            float* ps = part_sm + ((h - 1) * 128 + row) * 4;
+            ps[0] = r; ps[1] = g; ps[2] = bl;
           }
           tc_fence_before();
-          asm volatile("bar.sync 1, 256;" ::: "memory");     // the eight epilogue warps only
+          asm volatile("bar.sync 1, %0;" ::"n"(FT_EPI_WARPS * 32) : "memory");     // the epilogue warps only
           if (h == 0 && m < a.M) {
-            const float4 o = make_float4(r + part_sm[row * 4 + 0] + __ldg(a.b_rgb), g + part_sm[row * 4 + 1] + __ldg(a.b_rgb + 1),
-                                         bl + part_sm[row * 4 + 2] + __ldg(a.b_rgb + 2), sigma);
+#pragma unroll
+            for (int hh = 1; hh < EH; ++hh) {
+              const float4 ps = *reinterpret_cast<const float4*>(part_sm + ((hh - 1) * 128 + row) * 4);
+              r += ps.x; g += ps.y; bl += ps.z;
+            }
+            const float4 o = make_float4(r + __ldg(a.b_rgb), g + __ldg(a.b_rgb + 1), bl + __ldg(a.b_rgb + 2), sigma);
             *reinterpret_cast<float4*>(a.raw + m * 4) = o;     // raw = [rgb | sigma]  (models/model.py:73)
           }
-          asm volatile("bar.sync 1, 256;" ::: "memory");
+          asm volatile("bar.sync 1, %0;" ::"n"(FT_EPI_WARPS * 32) : "memory");
+          if (warp == 0) XTRACE(it, l, 1);
         }
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 9) tmem_dealloc(tmem, 512);
+  if (warp == FT_EPI_WARPS + 1) tmem_dealloc(tmem, 512);
 }
 
 __device__ int g_flex_tc_error = 0;
@@ -335,6 +389,12 @@ int cnrf_flex_fused_error() {
   int v = 0;
   cudaMemcpyFromSymbol(&v, g_flex_tc_error, sizeof(int));
   return v;
+}
+
+extern "C" int cnrf_debug_flex_trace(long long* host_out720) {
+  if (!host_out720) return CNRF_E_NULL;
+  const cudaError_t e = cudaMemcpyFromSymbol(host_out720, g_flex_trace, sizeof(long long) * 18 * 40);
+  return e == cudaSuccess ? CNRF_OK : (int)e;
 }
 
 size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers) {

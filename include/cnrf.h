@@ -438,6 +438,8 @@ int cnrf_debug_fwd_times(long long* host_out16, int reset);
 /* Timer builds (-DCNRF_FWD_TIMERS) only: clock64 stamps [tile 2][layer 4][event 8] of one steady-state tile pair of block 0
  * (events: mlp_fwd_tc.cu, g_fwd_trace); all zero in ordinary builds. */
 int cnrf_debug_fwd_trace(long long* host_out128);  /* [64] pair trace, then [16 images][4 events] of its layer 1 */
+/* The same for the vanilla-NeRF chain (flex_fwd_tc.cu, -DCNRF_FLEX_TIMERS): [18 layers][40 events] of block 0's 4th tile. */
+int cnrf_debug_flex_trace(long long* host_out720);
 double cnrf_debug_fwd_kernel_ms(int64_t min_rows, int64_t* launches, int64_t* rows);
 /* The same for any of the three tensor-core kernels: which = 0 forward chain, 1 backward-data chain, 2 weight gradients;
  * min_rows < 0 only queries. */
