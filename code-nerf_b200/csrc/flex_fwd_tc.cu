@@ -4,11 +4,16 @@
 // One persistent CTA per SM takes 128-sample tiles through ALL layers without leaving the SM:
 //   smem  : five activation slabs [128 x 64] bf16 (128-byte swizzle): slabs 0-3 = the 256 hidden features, overwritten in
 //           place layer by layer; slab 4 = gamma(x) (63 columns + a zero), kept for the skip layer, whose K is simply five
-//           slabs instead of four -- cat(h, xyz) (models/model.py:63) never exists.  A ring of three 32 KB weight slabs
+//           slabs instead of four -- cat(h, xyz) (models/model.py:63) never exists.  A ring of three 40 KB slots, each a 32 KB weight slab
 //           ([256 out x 64 in] bf16, pre-swizzled in global memory by pack_flex_weights_kernel, so one slab is ONE 1-D TMA
 //           bulk copy) runs ahead of the MMAs across layers and tiles.
 //   TMEM  : two [128 x 256] fp32 accumulators, used by alternate layers.
-//   warps : 0-7 epilogue (tcgen05.ld -> + bias -> ReLU -> bf16 -> swizzled smem = next layer's A operand), 8 = TMA
+//   bias  : comes through the tensor core.  Column 63 of the gamma(x) slab is 1 (dim_xyz <= 63): layer1 and the skip layer
+//           carry their bias (bf16) in column 63 of that slab's weights; every other hidden layer issues ONE more K16 MMA of
+//           gamma(x)'s last K chunk against an 8 KB image [256 x 16] that is zero but for k = 15 (it travels behind the layer's
+//           last weight slab in the same bulk copy).  The epilogue no longer reads a bias vector from shared memory (a third of
+//           its shared-memory wavefronts, on the pipe the MMAs' operand reads already load to 75 %) nor adds it.
+//   warps : 0-7 epilogue (tcgen05.ld -> ReLU -> bf16 -> swizzled smem = next layer's A operand), 8 = TMA
 //           producer, 9 = MMA issuer (elect.sync lane, M128 N256 K16).  -DFT_EPI_WARPS_N=16 gives every sample row four
 //           epilogue threads instead of two: measured 2.5 % SLOWER on a lego frame (226 vs 221 ms) -- the epilogue is bound
 //           by the shared-memory pipe it shares with the MMAs' operand reads, not by latency.
@@ -49,10 +54,12 @@ static_assert(EH == 2 || EH == 4, "8 or 16 epilogue warps");
 constexpr int SLAB_A = FT_ROWS * 128;          // 16 KB activation slab
 constexpr int SLAB_W = 256 * 128;              // 32 KB weight slab (N = 256)
 constexpr int SLAB_WD = 144 * 128;             // 18 KB weight slab of the direction layer (N = 128 + sigma row, padded to 144)
+constexpr int BIAS_IMG = 256 * 32;             // 8 KB: [256 out x 16 in] bf16, no swizzle (core matrices of 8 rows x 16 B)
+constexpr int SLOT = SLAB_W + BIAS_IMG;        // a ring slot: a weight slab, + the layer's bias image behind its last one
 constexpr int RING = 3;
 constexpr int FT_MAX_LAYERS = 18;
 constexpr int FT_MAX_FREQS = 16;
-constexpr int FT_SMEM = 5 * SLAB_A + RING * SLAB_W + FT_MAX_LAYERS * 256 * 4 /*biases*/ + 3 * 128 * 4 /*w_rgb*/ +
+constexpr int FT_SMEM = 5 * SLAB_A + RING * SLOT + 3 * 128 * 4 /*w_rgb*/ +
                         (EH - 1) * 128 * 4 * 4 /*rgb partials*/ + FT_MAX_FREQS * 4 + 256 /*barriers*/ + 1024 /*alignment*/;
 
 struct FlexLayer {
@@ -61,12 +68,13 @@ struct FlexLayer {
   int16_t a_first;    // first activation slab: 0 (hidden) or 4 (layer1 reads gamma(x))
   int16_t skip;       // 1: the last K slab is gamma(x) (slab 4)
   int16_t n_out;      // 256, or 144 for the direction layer
+  int16_t bias_img;   // 1: an 8 KB bias image follows the last K slab (one more K16 MMA against gamma(x)'s ones column)
+  int16_t pad;
 };
 struct FlexFwdArgs {
   FlexLayer layer[FT_MAX_LAYERS];
   int nlayers;                       // layer1, layers_xyz..., fc_feat, layers_dir[0]
   const uint8_t* packed;
-  const float* bias[FT_MAX_LAYERS];  // fp32 [256] (unused for the direction layer: its bias is inside betad)
   const float* x_xyz; int64_t ld_xyz; int dx;
   // pts != NULL: gamma(x) is computed here from the sample positions [M,3] (position_embed.py:44-53), x_xyz is not read
   const float* pts; int64_t ld_pts; const float* freqs; int nfreq; int inc;
@@ -77,13 +85,25 @@ struct FlexFwdArgs {
   int* err;
 };
 
-struct PackJob { const float* w; int ldw; int rows; int k0; int kcols; uint32_t ofs; int nrows_slab; };
+// bias != NULL: column `bias_col` of the slab holds the layer's bias (multiplied by the ones column of gamma(x));
+// kcols < 0: the job is a bias image instead -- [256 x 16] without swizzle, zero but for k = 15
+struct PackJob { const float* w; const float* bias; uint32_t ofs; int ldw; int k0; int16_t rows, kcols, nrows_slab, bias_col; };
+static_assert(sizeof(PackJob) == 40, "PackArgs must stay under the 4 KB kernel-parameter limit");
 struct PackArgs { PackJob job[FT_MAX_LAYERS * 5 + 4]; int count; uint8_t* out; };
 
 // one block per slab: element (n, kk) of the slab <- W[n][k0 + kk] (0 outside), bf16, 128-byte swizzled
 __global__ void pack_flex_weights_kernel(const __grid_constant__ PackArgs a) {
   const PackJob& j = a.job[blockIdx.x];
   uint8_t* dst = a.out + j.ofs;
+  if (j.kcols < 0) {      // bias image: element (n, k) at (n / 8) * 256 + (k / 8) * 128 + (n % 8) * 16 + (k % 8) * 2
+    for (int i = threadIdx.x; i < 256 * 2; i += blockDim.x) {
+      const int n = i >> 1, kc = i & 1;
+      uint4 p = make_uint4(0u, 0u, 0u, 0u);
+      if (kc == 1) p.w = pack_bf16(0.f, __ldg(j.bias + n));                 // k = 15: the high half of the last word
+      *reinterpret_cast<uint4*>(dst + (n >> 3) * 256 + kc * 128 + (n & 7) * 16) = p;
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < j.nrows_slab * 8; i += blockDim.x) {       // 16-byte chunks
     const int n = i >> 3, c = i & 7;
     float v[8];
@@ -91,6 +111,7 @@ __global__ void pack_flex_weights_kernel(const __grid_constant__ PackArgs a) {
     for (int e = 0; e < 8; ++e) {
       const int kk = c * 8 + e;
       v[e] = (n < j.rows && kk < j.kcols) ? __ldg(j.w + (int64_t)n * j.ldw + j.k0 + kk) : 0.f;
+      if (j.bias && kk == j.bias_col && n < j.rows) v[e] = __ldg(j.bias + n);
     }
     const uint4 p = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]), pack_bf16(v[6], v[7]));
     *reinterpret_cast<uint4*>(dst + n * 128 + ((c ^ (n & 7)) << 4)) = p;
@@ -151,9 +172,8 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* act = smem;                                     // 5 slabs
-  uint8_t* ring = smem + 5 * SLAB_A;                       // RING x 32 KB
-  float* bias_sm = reinterpret_cast<float*>(ring + RING * SLAB_W);
-  float* wrgb_sm = bias_sm + FT_MAX_LAYERS * 256;
+  uint8_t* ring = smem + 5 * SLAB_A;                       // RING x 40 KB
+  float* wrgb_sm = reinterpret_cast<float*>(ring + RING * SLOT);
   float* part_sm = wrgb_sm + 3 * 128;                      // [128][4]
   float* freq_sm = part_sm + (EH - 1) * 128 * 4;                      // [FT_MAX_FREQS]
   uint64_t* bars = reinterpret_cast<uint64_t*>(freq_sm + FT_MAX_FREQS);
@@ -168,10 +188,6 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     mbar_init(act_bar, FT_EPI_WARPS);                  // gamma(x) of the tile is written (layer1's A operand)
     for (int i = 0; i < 4; ++i) mbar_init(&slab_bar[i], FT_EPI_WARPS);
     mbar_fence_init();
-  }
-  for (int i = tid; i < a.nlayers * 256; i += FT_THREADS) {
-    const int l = i >> 8;
-    bias_sm[i] = a.bias[l] ? __ldg(a.bias[l] + (i & 255)) : 0.f;
   }
   for (int i = tid; i < 3 * 128; i += FT_THREADS) wrgb_sm[i] = __ldg(a.w_rgb + i);
   if (a.pts && tid < a.nfreq) freq_sm[tid] = __ldg(a.freqs + tid);
@@ -195,9 +211,11 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
           const int j = L.skip ? (i == 0 ? L.kslabs - 1 : i - 1) : i;      // K-slab order of the MMA warp (gamma(x) first)
           ok = mbar_wait(&empty[slot], par, a.err);
           XTRACE(it, l, 24 + 2 * i);
+          // the bias image lies behind the layer's last slab in the packed stream and travels with the last copy
+          const uint32_t nb = bytes + ((L.bias_img && i == L.kslabs - 1) ? (uint32_t)BIAS_IMG : 0u);
           if (ok && elect_one()) {
-            mbar_arrive_expect_tx(&full[slot], bytes);
-            bulk_g2s(ring + slot * SLAB_W, a.packed + L.wofs + (size_t)j * bytes, bytes, &full[slot]);
+            mbar_arrive_expect_tx(&full[slot], nb);
+            bulk_g2s(ring + slot * SLOT, a.packed + L.wofs + (size_t)j * bytes, nb, &full[slot]);
           }
           __syncwarp();
           XTRACE(it, l, 25 + 2 * i);
@@ -211,6 +229,9 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);          // provably warp-uniform copy
     const uint64_t a_desc0 = smem_desc(smem_u32(act), 16, 1024, SWIZZLE_128B);
     const uint64_t b_desc0 = smem_desc(smem_u32(ring), 16, 1024, SWIZZLE_128B);
+    // bias: K chunk 3 of gamma(x) (columns 48-63, column 63 == 1) against the image [256 x 16], zero but for k = 15
+    const uint64_t ones_desc = a_desc0 + (uint64_t)((uint32_t)(4 * SLAB_A + 96) >> 4);
+    const uint64_t bias_desc0 = smem_desc(smem_u32(ring) + SLAB_W, 128, 256, 0u /*no swizzle*/);
     uint32_t slot = 0, par = 0, act_ph = 0, slab_ph = 0;
     int it = 0;
     for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
@@ -237,10 +258,12 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
           tc_fence_after();
           XTRACE(it, l, 9 + 3 * i);
           const uint64_t ad = a_desc0 + (uint64_t)((uint32_t)(aslab * SLAB_A) >> 4);
-          const uint64_t bd = b_desc0 + (uint64_t)((slot * (uint32_t)SLAB_W) >> 4);
+          const uint64_t bd = b_desc0 + (uint64_t)((slot * (uint32_t)SLOT) >> 4);
+          const bool with_bias = L.bias_img && i == L.kslabs - 1;
           if (ok && elect_one()) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, (i | k) != 0);
+            if (with_bias) umma_bf16(acc, ones_desc, bias_desc0 + (uint64_t)((slot * (uint32_t)SLOT) >> 4), idesc, 1u);
             umma_commit(&empty[slot]);                      // the slot is free once these MMAs have read it
           }
           __syncwarp();
@@ -276,6 +299,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
             v[e] = (m < a.M && col < a.dx) ? __ldg(xr + col) : 0.f;
           }
         }
+        if (h == EH - 1) v[CW - 1] = 1.f;         // column 63: the ones column every layer's bias is multiplied by (dx <= 63)
 #pragma unroll
         for (int c = 0; c < CW / 8; ++c) {
           const uint4 p = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
@@ -295,7 +319,6 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
         if (l + 1 < a.nlayers) {
           // hidden layer: slab s = columns 64 s .. 64 s + 63 of the next A operand; this thread converts CW of them, then the
           // warp arrives on the slab's barrier -- the MMA warp starts the next layer's K slab s right away
-          const float* b = bias_sm + l * 256;
           const uint32_t t0 = acc + ((uint32_t)(q * 32) << 16) + h * CW;
           uint32_t v[2][CW];
           TmemLd<CW>::ld(t0, v[0]);
@@ -307,13 +330,9 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
             if (sl + 1 < 4) TmemLd<CW>::ld(t0 + (sl + 1) * 64, v[(sl + 1) & 1]);      // next slab's block in flight under this one
 #pragma unroll
             for (int c = 0; c < CW / 8; ++c) {
-              const int col = sl * 64 + h * CW + c * 8;
-              const float4 b0 = *reinterpret_cast<const float4*>(b + col);       // warp-uniform: LDS broadcast
-              const float4 b1 = *reinterpret_cast<const float4*>(b + col + 4);
-              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-              float x[8];
+              float x[8];         // the bias is already in the accumulator (it came through the tensor core)
 #pragma unroll
-              for (int e = 0; e < 8; ++e) x[e] = __uint_as_float(v[sl & 1][c * 8 + e]) + bb[e];
+              for (int e = 0; e < 8; ++e) x[e] = __uint_as_float(v[sl & 1][c * 8 + e]);
               // ReLU rides in the conversion (cvt.rn.relu.bf16x2.f32): no FMNMX per element
               const uint4 p = make_uint4(pack_bf16_relu(x[0], x[1]), pack_bf16_relu(x[2], x[3]), pack_bf16_relu(x[4], x[5]),
                                          pack_bf16_relu(x[6], x[7]));
@@ -398,11 +417,12 @@ extern "C" int cnrf_debug_flex_trace(long long* host_out720) {
 }
 
 size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers) {
-  return (size_t)SLAB_W * (1 + 5 * (size_t)num_xyz_layers + 4) + (size_t)SLAB_WD * 4 + 1024;
+  return (size_t)SLAB_W * (1 + 5 * (size_t)num_xyz_layers + 4) + (size_t)BIAS_IMG * ((size_t)num_xyz_layers + 1) +
+         (size_t)SLAB_WD * 4 + 1024;
 }
 
 bool cnrf_flex_fused_eligible(const cnrf_flex_shape* s) {
-  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->dim_dir > 0 && s->hidden == 256 && s->dim_xyz <= 64 && s->num_layers + 1 <= FT_MAX_LAYERS;
+  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->dim_dir > 0 && s->hidden == 256 && s->dim_xyz <= 63 && s->num_layers + 1 <= FT_MAX_LAYERS;
 }
 
 // betad: [N,128] fp32 already computed; packed: cnrf_flex_fused_packed_bytes() of 1024-byte aligned workspace
@@ -414,24 +434,33 @@ int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, con
   PackArgs pk = {};
   pk.out = packed;
   uint32_t ofs = 0;
-  auto add_job = [&](const float* w, int ldw, int rows, int k0, int kcols, int nrows_slab) {
+  auto add_job = [&](const float* w, int ldw, int rows, int k0, int kcols, int nrows_slab, const float* bias = nullptr) {
     PackJob& j = pk.job[pk.count++];
-    j.w = w; j.ldw = ldw; j.rows = rows; j.k0 = k0; j.kcols = kcols; j.ofs = ofs; j.nrows_slab = nrows_slab;
+    j.w = w; j.ldw = ldw; j.rows = (int16_t)rows; j.k0 = k0; j.kcols = (int16_t)kcols; j.ofs = ofs; j.nrows_slab = (int16_t)nrows_slab;
+    j.bias = bias; j.bias_col = 63;                   // a gamma(x) slab: its bias rides in column 63
     ofs += (uint32_t)nrows_slab * 128;
   };
+  auto add_bias_image = [&](const float* bias) {
+    PackJob& j = pk.job[pk.count++];
+    j = {};
+    j.kcols = -1; j.ofs = ofs; j.bias = bias;
+    ofs += (uint32_t)BIAS_IMG;
+  };
   int nl = 0;
-  a.layer[nl] = {ofs, 1, 4, 0, 256}; a.bias[nl] = p->b_layer1; ++nl;                       // layer1: A = gamma(x)
-  add_job(p->w_layer1, dx, H, 0, dx, 256);
+  a.layer[nl] = {ofs, 1, 4, 0, 256, 0, 0}; ++nl;                                           // layer1: A = gamma(x)
+  add_job(p->w_layer1, dx, H, 0, dx, 256, p->b_layer1);
   for (int i = 0; i < L; ++i) {
     const bool skip = (s->skip_mask >> i) & 1u;
     const int K = skip ? H + dx : H;
-    a.layer[nl] = {ofs, (int16_t)(skip ? 5 : 4), 0, (int16_t)skip, 256}; a.bias[nl] = p->b_xyz[i]; ++nl;
+    a.layer[nl] = {ofs, (int16_t)(skip ? 5 : 4), 0, (int16_t)skip, 256, (int16_t)(skip ? 0 : 1), 0}; ++nl;
     for (int j = 0; j < 4; ++j) add_job(p->w_xyz[i], K, H, 64 * j, 64, 256);
-    if (skip) add_job(p->w_xyz[i], K, H, H, dx, 256);
+    if (skip) add_job(p->w_xyz[i], K, H, H, dx, 256, p->b_xyz[i]);
+    else add_bias_image(p->b_xyz[i]);
   }
-  a.layer[nl] = {ofs, 4, 0, 0, 256}; a.bias[nl] = p->b_feat; ++nl;
+  a.layer[nl] = {ofs, 4, 0, 0, 256, 1, 0}; ++nl;
   for (int j = 0; j < 4; ++j) add_job(p->w_feat, H, H, 64 * j, 64, 256);
-  a.layer[nl] = {ofs, 4, 0, 0, 144}; a.bias[nl] = nullptr; ++nl;                            // layers_dir[0] (+ fc_alpha row)
+  add_bias_image(p->b_feat);
+  a.layer[nl] = {ofs, 4, 0, 0, 144, 0, 0}; ++nl;                            // layers_dir[0] (+ fc_alpha row)
   const uint32_t dir_ofs = ofs;
   for (int j = 0; j < 4; ++j) add_job(p->w_dir, H + dd, 128, 64 * j, 64, 144);
   a.nlayers = nl;
