@@ -59,17 +59,18 @@ constexpr int SLOT = SLAB_W + BIAS_IMG;        // a ring slot: a weight slab, + 
 constexpr int RING = 3;
 constexpr int FT_MAX_LAYERS = 18;
 constexpr int FT_MAX_FREQS = 16;
-constexpr int FT_SMEM = 5 * SLAB_A + RING * SLOT + 3 * 128 * 4 /*w_rgb*/ +
+constexpr int NSLAB_A = 6;                     // 0-3 hidden features, 4 gamma(x) | 1, 5 gamma(d) | 1
+constexpr int FT_SMEM = NSLAB_A * SLAB_A + RING * SLOT + 3 * 128 * 4 /*w_rgb*/ +
                         (EH - 1) * 128 * 4 * 4 /*rgb partials*/ + FT_MAX_FREQS * 4 + 256 /*barriers*/ + 1024 /*alignment*/;
 
 struct FlexLayer {
   uint32_t wofs;      // byte offset of the layer's first weight slab in the packed image
   int16_t kslabs;     // K slabs of 64
   int16_t a_first;    // first activation slab: 0 (hidden) or 4 (layer1 reads gamma(x))
-  int16_t skip;       // 1: the last K slab is gamma(x) (slab 4)
+  int16_t skip;       // 1: the layer's last K slab is activation slab `pad` (4: gamma(x), 5: gamma(d)), issued first
   int16_t n_out;      // 256, or 144 for the direction layer
   int16_t bias_img;   // 1: an 8 KB bias image follows the last K slab (one more K16 MMA against gamma(x)'s ones column)
-  int16_t pad;
+  int16_t pad;        // the extra slab of a skip layer
 };
 struct FlexFwdArgs {
   FlexLayer layer[FT_MAX_LAYERS];
@@ -78,8 +79,8 @@ struct FlexFwdArgs {
   const float* x_xyz; int64_t ld_xyz; int dx;
   // pts != NULL: gamma(x) is computed here from the sample positions [M,3] (position_embed.py:44-53), x_xyz is not read
   const float* pts; int64_t ld_pts; const float* freqs; int nfreq; int inc;
-  const float* betad;                // [N, 128] per-ray: Wdir[:, H:] gamma(d) + b_dir
-  const float* w_rgb; const float* b_rgb; const float* b_alpha;
+  const float* x_dir; int64_t ld_dir; int dd;   // [N, dd] embedded view directions, one row per RAY (pairing below)
+  const float* w_rgb; const float* b_rgb;
   float* raw;                        // [M, 4]
   int64_t M, N; int S, pairing;
   int* err;
@@ -172,14 +173,15 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* act = smem;                                     // 5 slabs
-  uint8_t* ring = smem + 5 * SLAB_A;                       // RING x 40 KB
+  uint8_t* ring = smem + NSLAB_A * SLAB_A;                       // RING x 40 KB
   float* wrgb_sm = reinterpret_cast<float*>(ring + RING * SLOT);
   float* part_sm = wrgb_sm + 3 * 128;                      // [128][4]
   float* freq_sm = part_sm + (EH - 1) * 128 * 4;                      // [FT_MAX_FREQS]
   uint64_t* bars = reinterpret_cast<uint64_t*>(freq_sm + FT_MAX_FREQS);
   uint64_t *full = bars, *empty = bars + RING, *acc_bar = bars + 2 * RING, *act_bar = bars + 2 * RING + 1;
   uint64_t* slab_bar = bars + 2 * RING + 2;            // [4]: the next layer's A slab s is written (8 arrivals: every epilogue warp)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RING + 6);
+  uint64_t* dir_bar = bars + 2 * RING + 6;             // gamma(d) of the tile is written (the direction layer's extra K slab)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * RING + 7);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
@@ -187,10 +189,13 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     mbar_init(acc_bar, 1);
     mbar_init(act_bar, FT_EPI_WARPS);                  // gamma(x) of the tile is written (layer1's A operand)
     for (int i = 0; i < 4; ++i) mbar_init(&slab_bar[i], FT_EPI_WARPS);
+    mbar_init(dir_bar, FT_EPI_WARPS);
     mbar_fence_init();
   }
   for (int i = tid; i < 3 * 128; i += FT_THREADS) wrgb_sm[i] = __ldg(a.w_rgb + i);
   if (a.pts && tid < a.nfreq) freq_sm[tid] = __ldg(a.freqs + tid);
+  for (int i = tid; i < SLAB_A / 16; i += FT_THREADS)          // gamma(d) slab: the columns past dd stay zero for good
+    reinterpret_cast<uint4*>(act + 5 * SLAB_A)[i] = make_uint4(0u, 0u, 0u, 0u);
   if (warp == FT_EPI_WARPS + 1) tmem_alloc(tmem_slot, 512);
   tc_fence_before();
   __syncthreads();
@@ -232,7 +237,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     // bias: K chunk 3 of gamma(x) (columns 48-63, column 63 == 1) against the image [256 x 16], zero but for k = 15
     const uint64_t ones_desc = a_desc0 + (uint64_t)((uint32_t)(4 * SLAB_A + 96) >> 4);
     const uint64_t bias_desc0 = smem_desc(smem_u32(ring) + SLAB_W, 128, 256, 0u /*no swizzle*/);
-    uint32_t slot = 0, par = 0, act_ph = 0, slab_ph = 0;
+    uint32_t slot = 0, par = 0, act_ph = 0, slab_ph = 0, dir_ph = 0;
     int it = 0;
     for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
 #pragma unroll 1
@@ -248,9 +253,13 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
 #pragma unroll 1
         for (int i = 0; i < L.kslabs && ok; ++i) {
           const int j = L.skip ? (i == 0 ? L.kslabs - 1 : i - 1) : i;      // K slab (the skip layer starts with gamma(x), always there)
-          const int aslab = (L.skip && j == L.kslabs - 1) ? 4 : L.a_first + j;
+          const int aslab = (L.skip && j == L.kslabs - 1) ? L.pad : L.a_first + j;
           if (l > 0 && aslab < 4) {                         // a hidden slab: the previous layer's epilogue has finished it
             ok = __all_sync(0xFFFFFFFFu, mbar_wait(&slab_bar[aslab], slab_ph, a.err));
+            if (!ok) break;
+          } else if (aslab == 5) {                          // gamma(d): written once per tile, early
+            ok = __all_sync(0xFFFFFFFFu, mbar_wait(dir_bar, dir_ph, a.err));
+            dir_ph ^= 1;
             if (!ok) break;
           }
           XTRACE(it, l, 8 + 3 * i);
@@ -282,32 +291,77 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     const int row = q * 32 + lane;
     uint32_t acc_ph = 0;
     int it = 0;
-    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
+    // gamma(x) | 1 of tile t -> slab 4: this thread converts columns [CW h, CW h + CW) of its row.  Runs for the FIRST tile
+    // before the loop and for every later tile while the MMA warp works on the previous tile's direction layer (the
+    // epilogue warps would idle there; slab 4's last reader, fc_feat's bias MMA, has completed by then).
+    auto build_gamma_x = [&](int64_t t) {
       const int64_t m = t * FT_ROWS + row;
-      // gamma(x) -> slab 4: this thread converts columns [CW h, CW h + CW) of its row
-      {
-        float v[CW];
-        if (a.pts) {
-          const float* pr = a.pts + (m < a.M ? m : 0) * a.ld_pts;
-          const float x[3] = {__ldg(pr), __ldg(pr + 1), __ldg(pr + 2)};
-          if (a.inc) gamma_row_part<1>(h, x, freq_sm, a.nfreq, v); else gamma_row_part<0>(h, x, freq_sm, a.nfreq, v);
-        } else {
-          const float* xr = a.x_xyz + (m < a.M ? m : 0) * a.ld_xyz;
+      float v[CW];
+      if (a.pts) {
+        const float* pr = a.pts + (m < a.M ? m : 0) * a.ld_pts;
+        const float x[3] = {__ldg(pr), __ldg(pr + 1), __ldg(pr + 2)};
+        if (a.inc) gamma_row_part<1>(h, x, freq_sm, a.nfreq, v); else gamma_row_part<0>(h, x, freq_sm, a.nfreq, v);
+      } else {
+        const float* xr = a.x_xyz + (m < a.M ? m : 0) * a.ld_xyz;
 #pragma unroll
-          for (int e = 0; e < CW; ++e) {
-            const int col = h * CW + e;
-            v[e] = (m < a.M && col < a.dx) ? __ldg(xr + col) : 0.f;
-          }
-        }
-        if (h == EH - 1) v[CW - 1] = 1.f;         // column 63: the ones column every layer's bias is multiplied by (dx <= 63)
-#pragma unroll
-        for (int c = 0; c < CW / 8; ++c) {
-          const uint4 p = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
-                                     pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
-          *reinterpret_cast<uint4*>(act + 4 * SLAB_A + row * 128 + (((h * (CW / 8) + c) ^ (row & 7)) << 4)) = p;
+        for (int e = 0; e < CW; ++e) {
+          const int col = h * CW + e;
+          v[e] = (m < a.M && col < a.dx) ? __ldg(xr + col) : 0.f;
         }
       }
+      if (h == EH - 1) v[CW - 1] = 1.f;         // column 63: the ones column every layer's bias is multiplied by (dx <= 63)
+#pragma unroll
+      for (int c = 0; c < CW / 8; ++c) {
+        const uint4 p = make_uint4(pack_bf16(v[c * 8], v[c * 8 + 1]), pack_bf16(v[c * 8 + 2], v[c * 8 + 3]),
+                                   pack_bf16(v[c * 8 + 4], v[c * 8 + 5]), pack_bf16(v[c * 8 + 6], v[c * 8 + 7]));
+        *reinterpret_cast<uint4*>(act + 4 * SLAB_A + row * 128 + (((h * (CW / 8) + c) ^ (row & 7)) << 4)) = p;
+      }
       epi_arrive(act_bar, lane);
+    };
+    // gamma(d) | 1 of tile t -> slab 5: row r gets the embedded direction of ITS ray (reference pairing: sample m belongs
+    // to ray m % N, nerf/__init__.py:127; correct pairing: m / S) and a one in column dd, which the direction layer's bias
+    // and fc_alpha's are multiplied by.  The threads walk the [128 x (dd + 1)] block element-wise, four loads in flight, so
+    // consecutive threads read consecutive floats (consecutive rows are consecutive rays in the reference pairing).  Runs
+    // after the tile's first epilogue, while the MMA warp is busy with layer 2: only the tile's last layer reads the slab.
+    const int wd = a.dd + 1;
+    const int tid_e = warp * 32 + lane;
+    const int step_r = (FT_EPI_WARPS * 32) / wd, step_c = (FT_EPI_WARPS * 32) % wd;
+    const int r_first = tid_e / wd, c_first = tid_e % wd;
+    auto build_gamma_d = [&](int64_t t) {
+      const int64_t m0 = t * FT_ROWS;
+      const int64_t ray0 = a.pairing == CNRF_PAIRING_REFERENCE ? m0 % a.N : 0;
+      int r = r_first, c = c_first;
+      while (r < FT_ROWS) {
+        float v[4];
+        int rr[4], cc[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          rr[k] = r; cc[k] = c;
+          if (r < FT_ROWS) {
+            const int64_t mm = m0 + r < a.M ? m0 + r : a.M - 1;
+            int64_t ray;
+            if (a.pairing == CNRF_PAIRING_REFERENCE) {
+              ray = ray0 + (mm - m0);
+              while (ray >= a.N) ray -= a.N;
+            } else {
+              ray = mm / a.S;
+            }
+            v[k] = c < a.dd ? __ldg(a.x_dir + ray * a.ld_dir + c) : 1.f;
+          }
+          r += step_r; c += step_c;
+          if (c >= wd) { c -= wd; ++r; }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (rr[k] < FT_ROWS)
+            *reinterpret_cast<__nv_bfloat16*>(act + 5 * SLAB_A + rr[k] * 128 + (((cc[k] >> 3) ^ (rr[k] & 7)) << 4) + (cc[k] & 7) * 2) =
+                __float2bfloat16_rn(v[k]);
+      }
+      epi_arrive(dir_bar, lane);
+    };
+    if ((int64_t)blockIdx.x < ntiles) build_gamma_x(blockIdx.x);
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
+      const int64_t m = t * FT_ROWS + row;
       if (warp == 0) XTRACE(it, 0, 5);
       for (int l = 0; l < a.nlayers && ok; ++l) {
         ok = mbar_wait(acc_bar, acc_ph, a.err);
@@ -346,26 +400,29 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
             epi_arrive(&slab_bar[sl], lane);
             if (warp == 0) XTRACE(it, l, 1 + sl);
           }
+          if (l == 0) build_gamma_d(t);
+          if (l == a.nlayers - 2 && t + gridDim.x < ntiles) build_gamma_x(t + gridDim.x);
         } else {
-          // direction layer: columns [DW h, DW h + DW) -> + betad[ray] -> ReLU -> fc_rgb partial sums; column 128 = sigma
-          const int64_t ray = a.pairing == CNRF_PAIRING_REFERENCE ? (m % a.N) : (m / a.S);
-          const float* bd = a.betad + (m < a.M ? ray : 0) * 128 + h * DW;
+          // direction layer: columns [DW h, DW h + DW) -> ReLU -> fc_rgb partial sums; column 128 = sigma (the per-ray
+          // direction term and both biases are already in the accumulator: they came in as the gamma(d) | 1 K slab)
           float r = 0.f, g = 0.f, bl = 0.f;
-#pragma unroll 1
+          uint32_t v[DW / 32][32];
+#pragma unroll
+          for (int cb = 0; cb < DW / 32; ++cb) tmem_ld32(acc + ((uint32_t)(q * 32) << 16) + h * DW + cb * 32, v[cb]);
+          tmem_ld_wait();
+#pragma unroll
           for (int cb = 0; cb < DW / 32; ++cb) {
-            uint32_t v[32];
-            tmem_ld32(acc + ((uint32_t)(q * 32) << 16) + h * DW + cb * 32, v);
-            tmem_ld_wait();
 #pragma unroll
             for (int e = 0; e < 32; e += 4) {
-              const float4 bb = __ldg(reinterpret_cast<const float4*>(bd + cb * 32 + e));
-              const float add[4] = {bb.x, bb.y, bb.z, bb.w};
-#pragma unroll
-              for (int i = 0; i < 4; ++i) {
-                const int n = h * DW + cb * 32 + e + i;
-                const float x = fmaxf(__uint_as_float(v[e + i]) + add[i], 0.f);
-                r = fmaf(x, wrgb_sm[n], r); g = fmaf(x, wrgb_sm[128 + n], g); bl = fmaf(x, wrgb_sm[256 + n], bl);
-              }
+              const int n = h * DW + cb * 32 + e;
+              const float4 wr = *reinterpret_cast<const float4*>(wrgb_sm + n);
+              const float4 wg = *reinterpret_cast<const float4*>(wrgb_sm + 128 + n);
+              const float4 wb = *reinterpret_cast<const float4*>(wrgb_sm + 256 + n);
+              const float x0 = fmaxf(__uint_as_float(v[cb][e]), 0.f), x1 = fmaxf(__uint_as_float(v[cb][e + 1]), 0.f);
+              const float x2 = fmaxf(__uint_as_float(v[cb][e + 2]), 0.f), x3 = fmaxf(__uint_as_float(v[cb][e + 3]), 0.f);
+              r = fmaf(x3, wr.w, fmaf(x2, wr.z, fmaf(x1, wr.y, fmaf(x0, wr.x, r))));
+              g = fmaf(x3, wg.w, fmaf(x2, wg.z, fmaf(x1, wg.y, fmaf(x0, wg.x, g))));
+              bl = fmaf(x3, wb.w, fmaf(x2, wb.z, fmaf(x1, wb.y, fmaf(x0, wb.x, bl))));
             }
           }
           float sigma = 0.f;
@@ -373,7 +430,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
             uint32_t v[16];
             tmem_ld16(acc + ((uint32_t)(q * 32) << 16) + 128, v);
             tmem_ld_wait();
-            sigma = __uint_as_float(v[0]) + __ldg(a.b_alpha);
+            sigma = __uint_as_float(v[0]);
           } else {
             float* ps = part_sm + ((h - 1) * 128 + row) * 4;
             ps[0] = r; ps[1] = g; ps[2] = bl;
@@ -418,26 +475,27 @@ extern "C" int cnrf_debug_flex_trace(long long* host_out720) {
 
 size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers) {
   return (size_t)SLAB_W * (1 + 5 * (size_t)num_xyz_layers + 4) + (size_t)BIAS_IMG * ((size_t)num_xyz_layers + 1) +
-         (size_t)SLAB_WD * 4 + 1024;
+         (size_t)SLAB_WD * 5 + 1024;
 }
 
 bool cnrf_flex_fused_eligible(const cnrf_flex_shape* s) {
-  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->dim_dir > 0 && s->hidden == 256 && s->dim_xyz <= 63 && s->num_layers + 1 <= FT_MAX_LAYERS;
+  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->dim_dir > 0 && s->dim_dir <= 63 && s->hidden == 256 && s->dim_xyz <= 63 && s->num_layers + 1 <= FT_MAX_LAYERS;
 }
 
-// betad: [N,128] fp32 already computed; packed: cnrf_flex_fused_packed_bytes() of 1024-byte aligned workspace
+// x_dir: [N, dim_dir] embedded view directions; packed: cnrf_flex_fused_packed_bytes() of 1024-byte aligned workspace
 int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
-                        const float* betad, float* raw, uint8_t* packed, cudaStream_t st, const FlexPts* gp) {
+                        const float* x_dir, int64_t ld_dir, float* raw, uint8_t* packed, cudaStream_t st, const FlexPts* gp) {
   if (gp && (gp->nfreq < 1 || gp->nfreq > FT_MAX_FREQS || 3 * (gp->inc + 2 * gp->nfreq) != s->dim_xyz)) return CNRF_E_SHAPE;
   const int H = 256, L = s->num_layers - 1, dx = s->dim_xyz, dd = s->dim_dir;
   FlexFwdArgs a = {};
   PackArgs pk = {};
   pk.out = packed;
   uint32_t ofs = 0;
-  auto add_job = [&](const float* w, int ldw, int rows, int k0, int kcols, int nrows_slab, const float* bias = nullptr) {
+  auto add_job = [&](const float* w, int ldw, int rows, int k0, int kcols, int nrows_slab, const float* bias = nullptr,
+                     int bias_col = 63) {
     PackJob& j = pk.job[pk.count++];
     j.w = w; j.ldw = ldw; j.rows = (int16_t)rows; j.k0 = k0; j.kcols = (int16_t)kcols; j.ofs = ofs; j.nrows_slab = (int16_t)nrows_slab;
-    j.bias = bias; j.bias_col = 63;                   // a gamma(x) slab: its bias rides in column 63
+    j.bias = bias; j.bias_col = (int16_t)bias_col;    // a gamma(x) slab: its bias rides in column 63 (gamma(d): column dd)
     ofs += (uint32_t)nrows_slab * 128;
   };
   auto add_bias_image = [&](const float* bias) {
@@ -452,7 +510,7 @@ int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, con
   for (int i = 0; i < L; ++i) {
     const bool skip = (s->skip_mask >> i) & 1u;
     const int K = skip ? H + dx : H;
-    a.layer[nl] = {ofs, (int16_t)(skip ? 5 : 4), 0, (int16_t)skip, 256, (int16_t)(skip ? 0 : 1), 0}; ++nl;
+    a.layer[nl] = {ofs, (int16_t)(skip ? 5 : 4), 0, (int16_t)skip, 256, (int16_t)(skip ? 0 : 1), 4}; ++nl;
     for (int j = 0; j < 4; ++j) add_job(p->w_xyz[i], K, H, 64 * j, 64, 256);
     if (skip) add_job(p->w_xyz[i], K, H, H, dx, 256, p->b_xyz[i]);
     else add_bias_image(p->b_xyz[i]);
@@ -460,9 +518,11 @@ int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, con
   a.layer[nl] = {ofs, 4, 0, 0, 256, 1, 0}; ++nl;
   for (int j = 0; j < 4; ++j) add_job(p->w_feat, H, H, 64 * j, 64, 256);
   add_bias_image(p->b_feat);
-  a.layer[nl] = {ofs, 4, 0, 0, 144, 0, 0}; ++nl;                            // layers_dir[0] (+ fc_alpha row)
+  // layers_dir[0] (+ fc_alpha as output row 128): K slabs 0-3 = feat, K slab 4 = gamma(d) | 1 against [Wdir[:, H:] | b_dir]
+  a.layer[nl] = {ofs, 5, 0, 1, 144, 0, 5}; ++nl;
   const uint32_t dir_ofs = ofs;
   for (int j = 0; j < 4; ++j) add_job(p->w_dir, H + dd, 128, 64 * j, 64, 144);
+  add_job(p->w_dir, H + dd, 128, H, dd, 144, p->b_dir, dd);
   a.nlayers = nl;
   pack_flex_weights_kernel<<<pk.count, 256, 0, st>>>(pk);
   CNRF_LAUNCH_CHECK();
@@ -474,13 +534,18 @@ int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, con
       jb.w = p->w_alpha; jb.ldw = H; jb.rows = 1; jb.k0 = 64 * j; jb.kcols = 64; jb.ofs = dir_ofs + j * SLAB_WD + 128 * 128;
       jb.nrows_slab = 1;
     }
+    {   // ... and its bias in column dd of the gamma(d) slab's row 128
+      PackJob& jb = pa.job[pa.count++];
+      jb.rows = 1; jb.kcols = 0; jb.ofs = dir_ofs + 4 * SLAB_WD + 128 * 128; jb.nrows_slab = 1;
+      jb.bias = p->b_alpha; jb.bias_col = (int16_t)dd;
+    }
     pack_flex_weights_kernel<<<pa.count, 32, 0, st>>>(pa);
     CNRF_LAUNCH_CHECK();
   }
   a.packed = packed;
   a.x_xyz = x_xyz; a.ld_xyz = ld_xyz; a.dx = dx;
   if (gp) { a.pts = gp->pts; a.ld_pts = gp->ld; a.freqs = gp->freqs; a.nfreq = gp->nfreq; a.inc = gp->inc; }
-  a.betad = betad; a.w_rgb = p->w_rgb; a.b_rgb = p->b_rgb; a.b_alpha = p->b_alpha;
+  a.x_dir = x_dir; a.ld_dir = ld_dir; a.dd = dd; a.w_rgb = p->w_rgb; a.b_rgb = p->b_rgb;
   a.raw = raw; a.M = s->num_rays * (int64_t)s->num_samples; a.N = s->num_rays; a.S = s->num_samples; a.pairing = s->pairing;
   cudaGetSymbolAddress(reinterpret_cast<void**>(&a.err), g_flex_tc_error);
   {

@@ -175,8 +175,7 @@ extern "C" int cnrf_flexnerf_fwd(const cnrf_flex_shape* s, const cnrf_flex_param
     float* pk = ws.take((cnrf_flex_fused_packed_bytes(d.L) + 1024) / sizeof(float));
     CNRF_REQUIRE(ws.ok, CNRF_E_WORKSPACE);
     uint8_t* packed = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(pk) + 1023) & ~uintptr_t(1023));
-    RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->w_dir + H, H + d.dd, H2, betad, H2, p->b_dir, 0, 1, INT64_MAX, 0, st));
-    return cnrf_flex_fused_fwd(s, p, x_xyz, ld_xyz, betad, raw, packed, st);
+    return cnrf_flex_fused_fwd(s, p, x_xyz, ld_xyz, x_dir, ld_dir, raw, packed, st);
   }
   Saved sv;
   if (s->keep) {
@@ -230,9 +229,8 @@ extern "C" int cnrf_flexnerf_fwd_pts(const cnrf_flex_shape* s, const cnrf_flex_p
   float* pk = ws.take((cnrf_flex_fused_packed_bytes(d.L) + 1024) / sizeof(float));
   CNRF_REQUIRE(ws.ok, CNRF_E_WORKSPACE);
   uint8_t* packed = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(pk) + 1023) & ~uintptr_t(1023));
-  RUN(lin(d.tc, x_dir, ld_dir, d.N, d.dd, p->w_dir + H, H + d.dd, H2, betad, H2, p->b_dir, 0, 1, INT64_MAX, 0, st));
   const FlexPts gp = {pts, ld_pts, freqs_xyz, num_freqs, include_input ? 1 : 0};
-  return cnrf_flex_fused_fwd(s, p, nullptr, 0, betad, raw, packed, st, &gp);
+  return cnrf_flex_fused_fwd(s, p, nullptr, 0, x_dir, ld_dir, raw, packed, st, &gp);
 }
 
 extern "C" int cnrf_flexnerf_bwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,

@@ -178,6 +178,7 @@ size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers);
 // gp != NULL: the kernel encodes the sample positions itself (x_xyz unused)
 struct FlexPts { const float* pts; int64_t ld; const float* freqs; int nfreq; int inc; };
 int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, const float* x_xyz, int64_t ld_xyz,
-                        const float* betad /*[N,128]*/, float* raw, uint8_t* packed /*1024-byte aligned*/, cudaStream_t st,
+                        const float* x_dir /*[N,dim_dir]*/, int64_t ld_dir, float* raw, uint8_t* packed /*1024-byte aligned*/,
+                        cudaStream_t st,
                         const FlexPts* gp = nullptr);
 int cnrf_flex_fused_error();
