@@ -128,6 +128,17 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
 
 // gamma(x) columns [CW H, CW H + CW) of one sample: column 3 (INC + 2 k) + d = sin(f_k x_d), three columns on = cos(f_k x_d)
 // (position_embed.py:44-53).  One sincosf per (band, channel) the column range touches; every index is static once unrolled.
+// sin / cos of t for the bf16 operand: two-constant Cody-Waite reduction to [-pi, pi] (|t| reaches 2^9 |x|, a few thousand
+// radians), then the SFU approximations (2^-21.4 absolute there): ~5e-7 absolute, four orders below a bf16 ulp, for about
+// 8 instructions instead of the ~45 of sincosf.
+__device__ __forceinline__ void sincos_bf16_operand(float t, float* sn, float* cs) {
+  const float n = rintf(t * 0.15915494309189535f);
+  float y = fmaf(n, -6.2831854820251465f, t);
+  y = fmaf(n, 1.7484555e-7f, y);                     // 2 pi = 6.2831854820251465 - 1.7484555e-7
+  *sn = __sinf(y);
+  *cs = __cosf(y);
+}
+
 template <int H, int INC>
 __device__ __forceinline__ void gamma_cols(const float (&x)[3], const float* fr, int nfreq, float (&v)[CW]) {
   constexpr int J0 = CW * H, J1 = J0 + CW;
@@ -143,7 +154,7 @@ __device__ __forceinline__ void gamma_cols(const float (&x)[3], const float* fr,
 #pragma unroll
       for (int d = 0; d < 3; ++d) {
         float sn, cs;
-        sincosf(__fmul_rn(x[d], f), &sn, &cs);
+        sincos_bf16_operand(__fmul_rn(x[d], f), &sn, &cs);
         const int js = 3 * (INC + 2 * k) + d - J0, jc = js + 3;
         if (js >= 0 && js < CW) v[js] = sn;
         if (jc >= 0 && jc < CW) v[jc] = cs;
@@ -320,44 +331,45 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
     };
     // gamma(d) | 1 of tile t -> slab 5: row r gets the embedded direction of ITS ray (reference pairing: sample m belongs
     // to ray m % N, nerf/__init__.py:127; correct pairing: m / S) and a one in column dd, which the direction layer's bias
-    // and fc_alpha's are multiplied by.  The threads walk the [128 x (dd + 1)] block element-wise, four loads in flight, so
-    // consecutive threads read consecutive floats (consecutive rows are consecutive rays in the reference pairing).  Runs
-    // after the tile's first epilogue, while the MMA warp is busy with layer 2: only the tile's last layer reads the slab.
+    // and fc_alpha's are multiplied by.  Runs after the tile's first epilogue, while the MMA warp is busy with layer 2: only
+    // the tile's last layer reads the slab.
+    // (warp w takes rows w, w + W, ...: one 108-byte row per load instruction, lane = column; the ray of each row is
+    // computed by one lane -- a single division -- and handed round by shuffles)
     const int wd = a.dd + 1;
-    const int tid_e = warp * 32 + lane;
-    const int step_r = (FT_EPI_WARPS * 32) / wd, step_c = (FT_EPI_WARPS * 32) % wd;
-    const int r_first = tid_e / wd, c_first = tid_e % wd;
     auto build_gamma_d = [&](int64_t t) {
+      if (warp == 0) XTRACE(it, 1, 34);
+      constexpr int RPW = FT_ROWS / FT_EPI_WARPS;          // rows per warp
       const int64_t m0 = t * FT_ROWS;
-      const int64_t ray0 = a.pairing == CNRF_PAIRING_REFERENCE ? m0 % a.N : 0;
-      int r = r_first, c = c_first;
-      while (r < FT_ROWS) {
-        float v[4];
-        int rr[4], cc[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          rr[k] = r; cc[k] = c;
-          if (r < FT_ROWS) {
-            const int64_t mm = m0 + r < a.M ? m0 + r : a.M - 1;
-            int64_t ray;
-            if (a.pairing == CNRF_PAIRING_REFERENCE) {
-              ray = ray0 + (mm - m0);
-              while (ray >= a.N) ray -= a.N;
-            } else {
-              ray = mm / a.S;
-            }
-            v[k] = c < a.dd ? __ldg(a.x_dir + ray * a.ld_dir + c) : 1.f;
-          }
-          r += step_r; c += step_c;
-          if (c >= wd) { c -= wd; ++r; }
-        }
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (rr[k] < FT_ROWS)
-            *reinterpret_cast<__nv_bfloat16*>(act + 5 * SLAB_A + rr[k] * 128 + (((cc[k] >> 3) ^ (rr[k] & 7)) << 4) + (cc[k] & 7) * 2) =
-                __float2bfloat16_rn(v[k]);
+      int my_ray = 0;
+      if (lane < RPW) {
+        const int64_t mr = m0 + warp + FT_EPI_WARPS * lane;
+        const int64_t mm = mr < a.M ? mr : a.M - 1;
+        if (a.M < ((int64_t)1 << 31))
+          my_ray = a.pairing == CNRF_PAIRING_REFERENCE ? (int)((uint32_t)mm % (uint32_t)a.N) : (int)((uint32_t)mm / (uint32_t)a.S);
+        else
+          my_ray = a.pairing == CNRF_PAIRING_REFERENCE ? (int)(mm % a.N) : (int)(mm / a.S);
       }
+      for (int c0 = 0; c0 < wd; c0 += 32) {
+        const int c = c0 + lane;
+        float v[RPW];
+#pragma unroll
+        for (int i = 0; i < RPW; ++i) {
+          const int ray = __shfl_sync(0xFFFFFFFFu, my_ray, i);
+          v[i] = c < a.dd ? __ldg(a.x_dir + (int64_t)ray * a.ld_dir + c) : 1.f;
+        }
+        if (warp == 0) XTRACE(it, 1, 35);
+        if (c < wd) {
+#pragma unroll
+          for (int i = 0; i < RPW; ++i) {
+            const int r = warp + FT_EPI_WARPS * i;
+            *reinterpret_cast<__nv_bfloat16*>(act + 5 * SLAB_A + r * 128 + (((c >> 3) ^ (r & 7)) << 4) + (c & 7) * 2) =
+                __float2bfloat16_rn(v[i]);
+          }
+        }
+      }
+      if (warp == 0) XTRACE(it, 1, 36);
       epi_arrive(dir_bar, lane);
+      if (warp == 0) XTRACE(it, 1, 37);
     };
     if ((int64_t)blockIdx.x < ntiles) build_gamma_x(blockIdx.x);
     for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
@@ -479,7 +491,7 @@ size_t cnrf_flex_fused_packed_bytes(int num_xyz_layers) {
 }
 
 bool cnrf_flex_fused_eligible(const cnrf_flex_shape* s) {
-  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->dim_dir > 0 && s->dim_dir <= 63 && s->hidden == 256 && s->dim_xyz <= 63 && s->num_layers + 1 <= FT_MAX_LAYERS;
+  return s->precision == CNRF_PRECISION_BF16 && !s->keep && s->dim_dir > 0 && s->dim_dir <= 63 && s->num_rays < ((int64_t)1 << 31) && s->hidden == 256 && s->dim_xyz <= 63 && s->num_layers + 1 <= FT_MAX_LAYERS;
 }
 
 // x_dir: [N, dim_dir] embedded view directions; packed: cnrf_flex_fused_packed_bytes() of 1024-byte aligned workspace

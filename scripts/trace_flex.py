@@ -42,6 +42,8 @@ for l in range(10):
     lines.append("         mma " + " | ".join(f"A{rel(r[8 + 3 * i])} W{rel(r[9 + 3 * i])} iss{rel(r[10 + 3 * i])}" for i in range(5) if r[10 + 3 * i] > 0) + f" commit {rel(r[23])}")
     if r[30] > 0:
         lines.append(f"         epi slab 1 of warp 0: wait_ld {r[31] - r[30]} convert+store {r[32] - r[31]} fence.proxy.async {r[33] - r[32]} arrive {r[2] - r[33]}")
+    if l == 1 and r[34] > 0:
+        lines.append(f"         gamma(d) build of warp 0: start {rel(r[34])} loads issued {rel(r[35])} stored {rel(r[36])} arrived {rel(r[37])}")
     lines.append("         tma " + " | ".join(f"empty{rel(r[24 + 2 * i])} iss{rel(r[25 + 2 * i])}" for i in range(5) if r[25 + 2 * i] > 0))
 txt = "\n".join(lines)
 print(txt)
