@@ -214,3 +214,37 @@ def test_flexible_fused_chain_encodes_positions_itself(dev, nf, logs, inc):
     assert float(err.max()) < 2e-3 and float(err.mean()) < 1e-5, (float(err.max()), float(err.mean()))
     assert not ops.flexnerf_fused_inference(L, 128, m.dim_xyz, m.dim_dir, m._skip_mask(), _lib.PRECISION_BF16)
     assert not ops.flexnerf_fused_inference(L, H, m.dim_xyz, m.dim_dir, m._skip_mask(), _lib.PRECISION_FP32)
+
+
+@pytest.mark.parametrize("nf_dir,inc_dir,N,S,pairing", [(10, True, 100, 40, "reference"), (1, True, 100, 40, "correct"),
+                                                        (4, False, 3, 5, "reference"), (10, True, 1, 130, "correct")])
+def test_flexible_fused_chain_direction_widths(dev, nf_dir, inc_dir, N, S, pairing):
+    """The gamma(d) | 1 K slab of the fused chain at other view-direction widths (63 columns = two passes of its builder, 9,
+    24), fewer rows than one tile, fewer rays than rows: against the fp32 per-layer path of the same model (independent
+    code: embedded tensor, toolkit GEMMs), 3e-2 abs on the raw field as for every bf16 chain."""
+    import view_synthesis.nerf as nerf
+    import view_synthesis.models as models
+    from codenerf_b200 import _lib
+    torch.manual_seed(nf_dir * 7 + N)
+    m = models.FlexibleNeRFModel(3, 256, [1], 10, nf_dir, True, inc_dir, True).to(dev)
+    with torch.no_grad():
+        for p in m.parameters():
+            if p.dim() == 1:
+                p.uniform_(-0.5, 0.5)            # biases large enough to matter: they travel through the tensor core in bf16
+    emb = (nerf.PositionalEmbedder(10, True, True, torch.float32, dev),
+           nerf.PositionalEmbedder(nf_dir, True, inc_dir, torch.float32, dev))
+    rd, pts = torch.randn(N, 3, device=dev), torch.rand(N, S, 3, device=dev) * 3 - 1.5
+    old_p, old_q = nerf.get_precision(), nerf.get_pairing()
+    out = {}
+    try:
+        nerf.set_pairing(pairing)
+        for precision in ("fp32", "bf16"):
+            nerf.set_precision(precision)
+            with torch.no_grad():
+                out[precision] = nerf.forward_pass(m, emb, rd, pts, (None, None))
+        assert _lib.load().cnrf_debug_tc_error() == 0
+    finally:
+        nerf.set_precision(old_p); nerf.set_pairing(old_q)
+    err = (out["bf16"] - out["fp32"]).abs()
+    scale = float(out["fp32"].abs().max())
+    assert float(err.max()) < 3e-2 * max(1.0, scale) and float(err.mean()) < 4e-3 * max(1.0, scale), (float(err.max()), float(err.mean()), scale)
