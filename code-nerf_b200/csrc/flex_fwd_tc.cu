@@ -11,7 +11,8 @@
 //   bias  : comes through the tensor core.  Column 63 of the gamma(x) slab is 1 (dim_xyz <= 63): layer1 and the skip layer
 //           carry their bias (bf16) in column 63 of that slab's weights; every other hidden layer issues ONE more K16 MMA of
 //           gamma(x)'s last K chunk against an 8 KB image [256 x 16] that is zero but for k = 15 (it travels behind the layer's
-//           last weight slab in the same bulk copy).  The epilogue no longer reads a bias vector from shared memory (a third of
+//           first weight slab in the same bulk copy and opens the layer's accumulation; handing slab 0 over in two halves
+//           of 16 columns per thread was measured too: 171.5 against 168.7 ms per lego frame, not kept).  The epilogue no longer reads a bias vector from shared memory (a third of
 //           its shared-memory wavefronts, on the pipe the MMAs' operand reads already load to 75 %) nor adds it.
 //   warps : 0-7 epilogue (tcgen05.ld -> ReLU -> bf16 -> swizzled smem = next layer's A operand), 8 = TMA
 //           producer, 9 = MMA issuer (elect.sync lane, M128 N256 K16).  -DFT_EPI_WARPS_N=16 gives every sample row four
@@ -55,7 +56,7 @@ constexpr int SLAB_A = FT_ROWS * 128;          // 16 KB activation slab
 constexpr int SLAB_W = 256 * 128;              // 32 KB weight slab (N = 256)
 constexpr int SLAB_WD = 144 * 128;             // 18 KB weight slab of the direction layer (N = 128 + sigma row, padded to 144)
 constexpr int BIAS_IMG = 256 * 32;             // 8 KB: [256 out x 16 in] bf16, no swizzle (core matrices of 8 rows x 16 B)
-constexpr int SLOT = SLAB_W + BIAS_IMG;        // a ring slot: a weight slab, + the layer's bias image behind its last one
+constexpr int SLOT = SLAB_W + BIAS_IMG;        // a ring slot: a weight slab, + the layer's bias image behind its first one
 constexpr int RING = 3;
 constexpr int FT_MAX_LAYERS = 18;
 constexpr int FT_MAX_FREQS = 16;
@@ -69,7 +70,7 @@ struct FlexLayer {
   int16_t a_first;    // first activation slab: 0 (hidden) or 4 (layer1 reads gamma(x))
   int16_t skip;       // 1: the layer's last K slab is activation slab `pad` (4: gamma(x), 5: gamma(d)), issued first
   int16_t n_out;      // 256, or 144 for the direction layer
-  int16_t bias_img;   // 1: an 8 KB bias image follows the last K slab (one more K16 MMA against gamma(x)'s ones column)
+  int16_t bias_img;   // 1: an 8 KB bias image follows the first K slab (one more K16 MMA against gamma(x)'s ones column)
   int16_t pad;        // the extra slab of a skip layer
 };
 struct FlexFwdArgs {
@@ -227,11 +228,12 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
           const int j = L.skip ? (i == 0 ? L.kslabs - 1 : i - 1) : i;      // K-slab order of the MMA warp (gamma(x) first)
           ok = mbar_wait(&empty[slot], par, a.err);
           XTRACE(it, l, 24 + 2 * i);
-          // the bias image lies behind the layer's last slab in the packed stream and travels with the last copy
-          const uint32_t nb = bytes + ((L.bias_img && i == L.kslabs - 1) ? (uint32_t)BIAS_IMG : 0u);
+          // the bias image lies behind the layer's FIRST slab in the packed stream and travels with the first copy
+          const uint32_t nb = bytes + ((L.bias_img && i == 0) ? (uint32_t)BIAS_IMG : 0u);
+          const size_t src = L.wofs + (size_t)j * bytes + ((L.bias_img && i > 0) ? (size_t)BIAS_IMG : 0);
           if (ok && elect_one()) {
             mbar_arrive_expect_tx(&full[slot], nb);
-            bulk_g2s(ring + slot * SLOT, a.packed + L.wofs + (size_t)j * bytes, nb, &full[slot]);
+            bulk_g2s(ring + slot * SLOT, a.packed + src, nb, &full[slot]);
           }
           __syncwarp();
           XTRACE(it, l, 25 + 2 * i);
@@ -279,11 +281,13 @@ __global__ void __launch_bounds__(FT_THREADS, 1) flex_fwd_tc_kernel(const __grid
           XTRACE(it, l, 9 + 3 * i);
           const uint64_t ad = a_desc0 + (uint64_t)((uint32_t)(aslab * SLAB_A) >> 4);
           const uint64_t bd = b_desc0 + (uint64_t)((slot * (uint32_t)SLOT) >> 4);
-          const bool with_bias = L.bias_img && i == L.kslabs - 1;
+          // the bias MMA opens the layer (gamma(x) is always there): nothing but the last slab's four MMAs is left when
+          // the previous epilogue ends
+          const bool with_bias = L.bias_img && i == 0;
           if (ok && elect_one()) {
+            if (with_bias) umma_bf16(acc, ones_desc, bias_desc0 + (uint64_t)((slot * (uint32_t)SLOT) >> 4), idesc, 0u);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, (i | k) != 0);
-            if (with_bias) umma_bf16(acc, ones_desc, bias_desc0 + (uint64_t)((slot * (uint32_t)SLOT) >> 4), idesc, 1u);
+            for (int k = 0; k < 4; ++k) umma_bf16(acc, ad + 2 * k, bd + 2 * k, idesc, (i | k) != 0 || with_bias);
             umma_commit(&empty[slot]);                      // the slot is free once these MMAs have read it
           }
           __syncwarp();
@@ -523,13 +527,17 @@ int cnrf_flex_fused_fwd(const cnrf_flex_shape* s, const cnrf_flex_params* p, con
     const bool skip = (s->skip_mask >> i) & 1u;
     const int K = skip ? H + dx : H;
     a.layer[nl] = {ofs, (int16_t)(skip ? 5 : 4), 0, (int16_t)skip, 256, (int16_t)(skip ? 0 : 1), 4}; ++nl;
-    for (int j = 0; j < 4; ++j) add_job(p->w_xyz[i], K, H, 64 * j, 64, 256);
+    for (int j = 0; j < 4; ++j) {
+      add_job(p->w_xyz[i], K, H, 64 * j, 64, 256);
+      if (j == 0 && !skip) add_bias_image(p->b_xyz[i]);     // behind the first slab: the bias MMA opens the layer
+    }
     if (skip) add_job(p->w_xyz[i], K, H, H, dx, 256, p->b_xyz[i]);
-    else add_bias_image(p->b_xyz[i]);
   }
   a.layer[nl] = {ofs, 4, 0, 0, 256, 1, 0}; ++nl;
-  for (int j = 0; j < 4; ++j) add_job(p->w_feat, H, H, 64 * j, 64, 256);
-  add_bias_image(p->b_feat);
+  for (int j = 0; j < 4; ++j) {
+    add_job(p->w_feat, H, H, 64 * j, 64, 256);
+    if (j == 0) add_bias_image(p->b_feat);
+  }
   // layers_dir[0] (+ fc_alpha as output row 128): K slabs 0-3 = feat, K slab 4 = gamma(d) | 1 against [Wdir[:, H:] | b_dir]
   a.layer[nl] = {ofs, 5, 0, 1, 144, 0, 5}; ++nl;
   const uint32_t dir_ofs = ofs;
