@@ -12,6 +12,7 @@
 // shared-memory image (rows = the strided index, columns = the contiguous index), ONE thread issues the MMAs, the
 // operand majorness is chosen by the descriptor (K-major when k is the contiguous index, MN-major otherwise -- no
 // transposed copies), 8 warps run the epilogue with 16-byte stores / vector reductions.
+#include <cstdlib>
 #include "common.cuh"
 #include "internal.h"
 #include "tc_common.cuh"
@@ -22,6 +23,7 @@ namespace {
 constexpr int GBM = 128, GBN = 64, GKC = 64, GKSLICE = 256, GTHREADS = 256, GOCC = 4;
 constexpr int A_BYTES = GBM * GKC * 2;      // one bf16 image of the A tile for a 64-wide K chunk (16 KB)
 constexpr int B_BYTES = GBN * GKC * 2;      // ... of the B tile (8 KB)
+constexpr int G_SMEM_WIDE = 2 * (A_BYTES + 256 * GKC * 2) + 1024;          // 128 x 256 tile: 97 KB -> two CTAs per SM
 constexpr int G_SMEM = 2 * (A_BYTES + B_BYTES) + 1024 /*alignment slack*/;   // hi and lo images: 49 KB -> four CTAs per SM
                                                                           // hide each other's load round trips
 
@@ -37,6 +39,7 @@ struct GemmBatch {
 // image(r, c) = src[(r0 + r) * row_stride + c0 + c] (0 outside rows_valid x cols_valid); columns are the contiguous index.
 // Slab s holds columns [64 s, 64 s + 64) of every row, rows 128 bytes apart, 128-byte swizzle (tc_common.cuh).
 // hi = bf16(x), lo = bf16(x - hi).
+template <int U>                                       // independent global loads in flight per thread (see below)
 __device__ __noinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int rows_tile, int cols_tile,
                                         uint32_t slab_stride, const float* __restrict__ src, int64_t row_stride,
                                         int64_t r0, int64_t c0, int64_t rows_valid, int64_t cols_valid, int tid) {
@@ -45,8 +48,7 @@ __device__ __noinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int ro
   const bool pow2 = (groups & (groups - 1)) == 0;
   const int total = rows_tile * groups;
   const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((row_stride & 3) == 0) && ((c0 & 3) == 0);
-  constexpr int U = 8;                                 // independent global loads in flight per thread: a whole
-                                                       // 128 x 64 chunk is ONE round trip (cold misses cost ~2.5 us each)
+  // U = 8: a whole 128 x 64 chunk is ONE round trip (cold misses cost ~2.5 us each); U = 16: the 256 x 64 chunk of a wide tile
 #pragma unroll 1
   for (int base = tid; base < total; base += GTHREADS * U) {
     float4 v[U];
@@ -179,7 +181,17 @@ __device__ void small_k_tile(const GemmArgs& g, bool add, int64_t m0, int64_t n0
   }
 }
 
-__global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __grid_constant__ GemmBatch b, int* err) {
+// BN = 64: the batched per-ray kernel described above.  BN = 256 (one problem per launch, no device-side row counts): the
+// per-SAMPLE layers of the vanilla field in training and of the `split` pose chain -- hundreds of thousands of rows against
+// a 256-wide weight matrix.  There a 128 x 64 tile converts its 128-row operand tile to bf16 once per 64 output columns and
+// issues N = 64 MMAs; the wide tile converts it once and issues N = 256 MMAs (2 CTAs per SM instead of 4: TMEM).  Measured:
+// lego.yml's training step 298 -> 234 ms, the C3 pose-optimisation iteration 11.9 -> 10.5 ms.  Both kernels walk a CTA's K
+// chunks serially (load round trip -> convert -> MMA -> wait); the wide one is bound by its three load round trips per
+// chunk (an L2 prefetch of the whole tile changed nothing: the latency is the dependent chain, not HBM).
+template <int BN>
+__global__ void __launch_bounds__(GTHREADS, BN == 64 ? GOCC : 2) gemm_tc_batch_kernel(const __grid_constant__ GemmBatch b, int* err) {
+  constexpr int GBN = BN;
+  constexpr int B_BYTES = BN * GKC * 2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t bar;
@@ -207,7 +219,7 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   const int64_t n0 = (int64_t)ny * GBN;
   const int64_t kbeg = (int64_t)kz * b.kslice[p];
   const int64_t kend = min(g.K, kbeg + b.kslice[p]);
-  if (g.rows_dev) {
+  if (BN == 64 && g.rows_dev) {
     const bool add = g.split_k > 1 || g.accumulate || multi_k;
     // the staging buffers of the few-row path must fit the operand-image area: 8 x K + 16 x 8 x 16 floats
     if (g.rows_dim == 1 && g.M <= SMALL_ROWS && kbeg < g.K &&
@@ -223,7 +235,7 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   if (m0 >= g.M || kbeg >= g.K) return;
 
   if (tid == 0) { mbar_init(&bar, 1); mbar_fence_init(); }
-  if (warp == 1) tmem_alloc(&tmem_slot, 64);
+  if (warp == 1) tmem_alloc(&tmem_slot, BN);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -243,10 +255,11 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
     // K-major image: [tile rows x kpad cols(k)];  MN-major image: [kpad rows(k) x tile cols]
     const uint32_t a_slab = a_mn ? (uint32_t)kpad * 128u : (uint32_t)GBM * 128u;
     const uint32_t b_slab = b_mn ? (uint32_t)kpad * 128u : (uint32_t)GBN * 128u;
-    if (!a_mn) fill_image(a_hi, a_lo, GBM, (kpad + 63) & ~63, a_slab, g.A, g.a_rs, m0, k0, g.M, k0 + kc, tid);
-    else       fill_image(a_hi, a_lo, kpad, GBM, a_slab, g.A, g.a_cs, k0, m0, k0 + kc, g.M, tid);
-    if (!b_mn) fill_image(b_hi, b_lo, GBN, (kpad + 63) & ~63, b_slab, g.B, g.b_cs, n0, k0, g.N, k0 + kc, tid);
-    else       fill_image(b_hi, b_lo, kpad, GBN, b_slab, g.B, g.b_rs, k0, n0, k0 + kc, g.N, tid);
+    constexpr int UB = 8;      // 16 loads in flight for the wide B tile were measured: no gain (242 vs 234 ms per lego step)
+    if (!a_mn) fill_image<8>(a_hi, a_lo, GBM, (kpad + 63) & ~63, a_slab, g.A, g.a_rs, m0, k0, g.M, k0 + kc, tid);
+    else       fill_image<8>(a_hi, a_lo, kpad, GBM, a_slab, g.A, g.a_cs, k0, m0, k0 + kc, g.M, tid);
+    if (!b_mn) fill_image<UB>(b_hi, b_lo, GBN, (kpad + 63) & ~63, b_slab, g.B, g.b_cs, n0, k0, g.N, k0 + kc, tid);
+    else       fill_image<UB>(b_hi, b_lo, kpad, GBN, b_slab, g.B, g.b_rs, k0, n0, k0 + kc, g.N, tid);
     fence_proxy_async();
     tc_fence_before();
     __syncthreads();
@@ -271,43 +284,47 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   ok = ok && mbar_wait(&bar, phase, err);
   tc_fence_after();
   if (ok) {
-    const int q = warp & 3, half = warp >> 2;          // TMEM lane quarter, column half of the 64-wide tile
+    const int q = warp & 3, half = warp >> 2;          // TMEM lane quarter, column half of every 64-wide column group
     const int64_t m = m0 + q * 32 + lane;
-    uint32_t v[32];
-    tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + half * 32, v);
-    tmem_ld_wait();
-    if (m < g.M) {
-      const bool add = g.split_k > 1 || g.accumulate || multi_k;
-      const float* brow = g.bias ? g.bias + ((m / g.bias_div) % g.bias_mod) * g.ld_bias : nullptr;
-      float* crow = g.C + m * g.ldc;
-      const float* mrow = g.mask ? g.mask + m * g.ld_mask : nullptr;
-      const bool al16 = ((reinterpret_cast<uintptr_t>(crow) & 15) == 0) &&
-                        (!brow || (reinterpret_cast<uintptr_t>(brow) & 15) == 0) &&
-                        (!mrow || (reinterpret_cast<uintptr_t>(mrow) & 15) == 0);
+    const bool add = g.split_k > 1 || g.accumulate || multi_k;
+    const float* brow = (g.bias && m < g.M) ? g.bias + ((m / g.bias_div) % g.bias_mod) * g.ld_bias : nullptr;
+    float* crow = g.C + m * g.ldc;
+    const float* mrow = g.mask ? g.mask + m * g.ld_mask : nullptr;
+    const bool al16 = ((reinterpret_cast<uintptr_t>(crow) & 15) == 0) &&
+                      (!brow || (reinterpret_cast<uintptr_t>(brow) & 15) == 0) &&
+                      (!mrow || (reinterpret_cast<uintptr_t>(mrow) & 15) == 0);
+#pragma unroll 1
+    for (int cg = 0; cg < BN / 64; ++cg) {
+      if (n0 + cg * 64 >= g.N) break;                  // warp-uniform
+      uint32_t v[32];
+      tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + cg * 64 + half * 32, v);
+      tmem_ld_wait();
+      if (m < g.M) {
 #pragma unroll
-      for (int j = 0; j < 32; j += 4) {
-        const int64_t n = n0 + half * 32 + j;
-        if (n >= g.N) break;
-        float x[4] = {__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])};
-        if (al16 && n + 3 < g.N) {
-          if (add) { atomicAdd(reinterpret_cast<float4*>(crow + n), make_float4(x[0], x[1], x[2], x[3])); continue; }
-          if (brow) { const float4 t = __ldg(reinterpret_cast<const float4*>(brow + n)); x[0] += t.x; x[1] += t.y; x[2] += t.z; x[3] += t.w; }
-          if (g.relu) { x[0] = fmaxf(x[0], 0.f); x[1] = fmaxf(x[1], 0.f); x[2] = fmaxf(x[2], 0.f); x[3] = fmaxf(x[3], 0.f); }
-          if (mrow) {
-            const float4 t = __ldg(reinterpret_cast<const float4*>(mrow + n));
-            x[0] = t.x > 0.f ? x[0] : 0.f; x[1] = t.y > 0.f ? x[1] : 0.f; x[2] = t.z > 0.f ? x[2] : 0.f; x[3] = t.w > 0.f ? x[3] : 0.f;
-          }
-          *reinterpret_cast<float4*>(crow + n) = make_float4(x[0], x[1], x[2], x[3]);
-        } else {
+        for (int j = 0; j < 32; j += 4) {
+          const int64_t n = n0 + cg * 64 + half * 32 + j;
+          if (n >= g.N) break;
+          float x[4] = {__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])};
+          if (al16 && n + 3 < g.N) {
+            if (add) { atomicAdd(reinterpret_cast<float4*>(crow + n), make_float4(x[0], x[1], x[2], x[3])); continue; }
+            if (brow) { const float4 t = __ldg(reinterpret_cast<const float4*>(brow + n)); x[0] += t.x; x[1] += t.y; x[2] += t.z; x[3] += t.w; }
+            if (g.relu) { x[0] = fmaxf(x[0], 0.f); x[1] = fmaxf(x[1], 0.f); x[2] = fmaxf(x[2], 0.f); x[3] = fmaxf(x[3], 0.f); }
+            if (mrow) {
+              const float4 t = __ldg(reinterpret_cast<const float4*>(mrow + n));
+              x[0] = t.x > 0.f ? x[0] : 0.f; x[1] = t.y > 0.f ? x[1] : 0.f; x[2] = t.z > 0.f ? x[2] : 0.f; x[3] = t.w > 0.f ? x[3] : 0.f;
+            }
+            *reinterpret_cast<float4*>(crow + n) = make_float4(x[0], x[1], x[2], x[3]);
+          } else {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            if (n + i >= g.N) break;
-            float y = x[i];
-            if (add) { atomicAdd(crow + n + i, y); continue; }
-            if (brow) y += brow[n + i];
-            if (g.relu) y = fmaxf(y, 0.f);
-            if (mrow) y = mrow[n + i] > 0.f ? y : 0.f;
-            crow[n + i] = y;
+            for (int i = 0; i < 4; ++i) {
+              if (n + i >= g.N) break;
+              float y = x[i];
+              if (add) { atomicAdd(crow + n + i, y); continue; }
+              if (brow) y += brow[n + i];
+              if (g.relu) y = fmaxf(y, 0.f);
+              if (mrow) y = mrow[n + i] > 0.f ? y : 0.f;
+              crow[n + i] = y;
+            }
           }
         }
       }
@@ -315,7 +332,7 @@ __global__ void __launch_bounds__(GTHREADS, GOCC) gemm_tc_batch_kernel(const __g
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 64);
+  if (warp == 1) tmem_dealloc(tmem, BN);
 }
 }  // namespace
 
@@ -333,6 +350,15 @@ int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
   GemmBatch b;
   b.count = count;
   int total = 0;
+  // one big problem with a wide output (>= 296 row tiles or K slices: two CTAs on every SM): the 128 x 256 tile
+  int bn = GBN;
+  if (count == 1 && !list[0].rows_dev && list[0].N >= 192 && list[0].K > 0 && list[0].split_k >= 1) {
+    static const bool no_wide = getenv("CNRF_GEMM_NO_WIDE") != nullptr;      // A/B switch
+    const GemmArgs& a = list[0];
+    const bool may_split = a.split_k > 1 || a.accumulate;
+    const int64_t ks = a.k_slice > 0 ? a.k_slice : (may_split && a.K > 2 * GKSLICE) ? GKSLICE : a.K;
+    if (!no_wide && ((a.M + GBM - 1) / GBM) * ((a.K + ks - 1) / ks) >= 296) bn = 256;
+  }
   for (int i = 0; i < count; ++i) {
     const GemmArgs& a = list[i];
     if (!a.A || !a.B || !a.C) return CNRF_E_NULL;
@@ -345,7 +371,7 @@ int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
     b.kslice[i] = a.k_slice > 0 ? a.k_slice : (may_split && a.K > 2 * GKSLICE) ? GKSLICE : a.K;
     b.g[i] = a;
     b.mt[i] = (int)((a.M + GBM - 1) / GBM);
-    b.nt[i] = (a.N + GBN - 1) / GBN;
+    b.nt[i] = (a.N + bn - 1) / bn;
     b.first[i] = total;
     total += b.mt[i] * b.nt[i] * (int)((a.K + b.kslice[i] - 1) / b.kslice[i]);
   }
@@ -353,10 +379,13 @@ int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
   {
     static bool attr_set[CNRF_MAX_DEVICES] = {};
     const cudaError_t e = cnrf_once_per_device(attr_set, [] {
-      return cudaFuncSetAttribute(gemm_tc_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM); });
+      cudaError_t e1 = cudaFuncSetAttribute(gemm_tc_batch_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+      if (e1 == cudaSuccess) e1 = cudaFuncSetAttribute(gemm_tc_batch_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM_WIDE);
+      return e1; });
     if (e != cudaSuccess) return (int)e;
   }
-  gemm_tc_batch_kernel<<<total, GTHREADS, G_SMEM, st>>>(b, gemm_err_ptr());
+  if (bn == 256) gemm_tc_batch_kernel<256><<<total, GTHREADS, G_SMEM_WIDE, st>>>(b, gemm_err_ptr());
+  else gemm_tc_batch_kernel<64><<<total, GTHREADS, G_SMEM, st>>>(b, gemm_err_ptr());
   CNRF_LAUNCH_CHECK();
   return CNRF_OK;
 }
