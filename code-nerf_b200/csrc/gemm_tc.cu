@@ -48,6 +48,38 @@ __device__ __noinline__ void fill_image(uint8_t* img_hi, uint8_t* img_lo, int ro
   const bool pow2 = (groups & (groups - 1)) == 0;
   const int total = rows_tile * groups;
   const bool vec = ((reinterpret_cast<uintptr_t>(src) & 15) == 0) && ((row_stride & 3) == 0) && ((c0 & 3) == 0);
+  // Interior tiles of aligned operands (every chunk of a K = 256 layer): a thread keeps ONE column group and walks rows, so
+  // a float4 costs a pointer add, the load, the conversion and a store -- the general loop below spends ~50 integer
+  // instructions per float4 on index arithmetic and bounds, which is what bound the big per-sample GEMMs.
+  if (vec && pow2 && groups <= GTHREADS && r0 + rows_tile <= rows_valid && c0 + cols_tile <= cols_valid) {
+    const int rstep = GTHREADS >> gshift;                // rows covered by one pass of the 256 threads
+    const int c = (tid & (groups - 1)) << 2;
+    int r = tid >> gshift;
+    const float* p = src + (r0 + r) * row_stride + c0 + c;
+    const int64_t pstep = (int64_t)rstep * row_stride;
+    const uint32_t cpart = (uint32_t)(c >> 6) * slab_stride + (uint32_t)((c & 7) << 1);
+    const int chunk = (c & 63) >> 3;
+#pragma unroll 1
+    for (; r < rows_tile; r += rstep * U, p += (int64_t)U * pstep) {
+      float4 v[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (r + u * rstep < rows_tile) v[u] = __ldg(reinterpret_cast<const float4*>(p + (int64_t)u * pstep));
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int rr = r + u * rstep;
+        if (rr < rows_tile) {
+          const float hx = __bfloat162float(__float2bfloat16(v[u].x)), hy = __bfloat162float(__float2bfloat16(v[u].y));
+          const float hz = __bfloat162float(__float2bfloat16(v[u].z)), hw = __bfloat162float(__float2bfloat16(v[u].w));
+          const uint32_t off = cpart + (uint32_t)(rr * 128 + ((chunk ^ (rr & 7)) << 4));
+          *reinterpret_cast<uint2*>(img_hi + off) = make_uint2(pack_bf16(hx, hy), pack_bf16(hz, hw));
+          *reinterpret_cast<uint2*>(img_lo + off) =
+              make_uint2(pack_bf16(v[u].x - hx, v[u].y - hy), pack_bf16(v[u].z - hz, v[u].w - hw));
+        }
+      }
+    }
+    return;
+  }
   // U = 8: a whole 128 x 64 chunk is ONE round trip (cold misses cost ~2.5 us each); U = 16: the 256 x 64 chunk of a wide tile
 #pragma unroll 1
   for (int base = tid; base < total; base += GTHREADS * U) {
