@@ -379,6 +379,10 @@ static int* gemm_err_ptr() {
 int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st) {
   if (count <= 0) return CNRF_OK;
   if (!list || count > CNRF_GEMM_BATCH_MAX) return CNRF_E_SHAPE;
+  if (count == 1) {                                    // one big per-sample problem: the streaming kernel (gemm_stream.cu)
+    const int rc = cnrf_gemm_stream(list[0], st);
+    if (rc != CNRF_E_UNSUPPORTED) return rc;
+  }
   GemmBatch b;
   b.count = count;
   int total = 0;

@@ -195,7 +195,7 @@ extern "C" int cnrf_debug_tc_error(void) {
   int v = 0;
   cudaDeviceSynchronize();
   cudaMemcpyFromSymbol(&v, g_tc_error, sizeof(int));
-  return v | cnrf_flex_fused_error();
+  return v | cnrf_flex_fused_error() | cnrf_gemm_stream_error();
 }
 
 // =====================================================================================================================

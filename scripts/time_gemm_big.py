@@ -1,0 +1,25 @@
+"""Timing of ONE big per-sample GEMM of the toolkit (the shapes of vanilla-NeRF training / the split pose chain):
+    python scripts/time_gemm_big.py [M=786432]          CNRF_GEMM_NO_STREAM=1 selects the batched kernel's wide tiles"""
+import ctypes as C, os, sys, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "code-nerf_b200"))
+from codenerf_b200 import _lib
+lib = _lib.load(); dev = torch.device("cuda", 0)
+M = int(sys.argv[1]) if len(sys.argv) > 1 else 786432
+def run(N, K, form, reps=10):
+    X, W, dY = torch.randn(M, K, device=dev), torch.randn(N, K, device=dev), torch.randn(M, N, device=dev)
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream); p = lambda t: C.c_void_p(t.data_ptr())
+    if form == "lin":   out = torch.zeros(M, N, device=dev); f = lambda: lib.cnrf_debug_gemm(1, p(X), K, 1, p(W), 1, K, p(out), N, M, N, K, 0, st)
+    if form == "dgrad": out = torch.zeros(M, K, device=dev); f = lambda: lib.cnrf_debug_gemm(1, p(dY), N, 1, p(W), K, 1, p(out), K, M, K, N, 0, st)
+    for _ in range(2): f()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps): f()
+    e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / reps * 1e3
+    ref = (X @ W.t()) if form == "lin" else (dY @ W)
+    err = float((out - ref).abs().max() / ref.abs().max())
+    gb = (M * K + M * N) * 4 / 1e9 if form == "lin" else (M * N + M * K) * 4 / 1e9
+    print(f"{form:6s} M={M} N={N} K={K}: {us:.1f} us  {2 * M * N * K / us / 1e6:.0f} TFLOP/s  {gb / us * 1e6:.0f} GB/s  max rel err {err:.1e}")
+run(256, 256, "lin"); run(256, 256, "dgrad"); run(128, 256, "lin"); run(256, 64, "lin")
