@@ -86,6 +86,7 @@ _SIGS = {
     "cnrf_debug_tmem_ld": (C.c_int, [c_i32, c_i32, c_i32, c_i32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "cnrf_debug_fwd_trace": (C.c_int, [C.c_void_p]),
     "cnrf_debug_flex_trace": (C.c_int, [C.c_void_p]),
+    "cnrf_debug_stream_trace": (C.c_int, [C.c_void_p]),
     "cnrf_debug_fwd_times": (C.c_int, [C.c_void_p, C.c_int]),
     "cnrf_debug_fwd_kernel_ms": (C.c_double, [c_i64, C.c_void_p, C.c_void_p]),
     "cnrf_debug_kernel_ms": (C.c_double, [c_i32, c_i64, C.c_void_p, C.c_void_p]),

@@ -32,6 +32,15 @@ constexpr int ST_SMEM = NA * A_SLOT + NB * B_SLOT + 256 + ST_EPI * 32 * ST_STG_L
 
 __device__ uint8_t g_stream_b[ST_MAXCH * B_SLOT];                 // packed weights of the running call (320 KB)
 __device__ int g_stream_error = 0;
+// Timer builds only (-DCNRF_STREAM_TIMERS): clock64 stamps of block 0's 6th tile: [0..] converter per chunk {loads issued, slot
+// free, arrived} at 0 + 3 ch; MMA per chunk {A seen, B seen, issued} at 16 + 3 ch, 31 accumulator free, 32 committed; TMA per
+// chunk {slot free, issued} at 36 + 2 ch; epilogue warp 0 {48 accumulator seen, 49 done}, epilogue warp 4 {50, 51}.
+__device__ long long g_stream_trace[64];
+#ifdef CNRF_STREAM_TIMERS
+#define STRACE(it, ev) do { if (blockIdx.x == 0 && (it) == 5 && (threadIdx.x & 31) == 0) g_stream_trace[ev] = clock64(); } while (0)
+#else
+#define STRACE(it, ev) do { } while (0)
+#endif
 
 struct StreamArgs {
   GemmArgs g;
@@ -98,6 +107,13 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
     const uint32_t cpart = (uint32_t)((((cg >> 1)) << 4) | ((cg & 1) << 3));     // chunk bits are XOR-ed with the row below
     auto load = [&](int64_t m0, int ch, float4 (&v)[8]) {
       const int64_t k = (int64_t)ch * ST_KC + cg * 4;
+      if (a.a_vec && m0 + ST_ROWS <= g.M && (int64_t)(ch + 1) * ST_KC <= g.K) {      // interior chunk: pointer walk, no checks
+        const float* p = g.A + (m0 + r1) * g.a_rs + k;
+        const int64_t step = 16 * g.a_rs;
+#pragma unroll
+        for (int u = 0; u < 8; ++u, p += step) v[u] = __ldg(reinterpret_cast<const float4*>(p));
+        return;
+      }
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         const int64_t m = m0 + r1 + 16 * u;
@@ -126,8 +142,11 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
       int64_t tn = t; int chn = ch + 1;
       if (chn == a.nch) { chn = 0; tn = t + gridDim.x; }
       if (tn < ntiles) load(tn * ST_ROWS, chn, nxt);
+      const int itc = (int)((t - blockIdx.x) / gridDim.x);
+      if (warp == ST_EPI) STRACE(itc, 3 * ch);
       const uint32_t slot = s % NA, par = ((s / NA) & 1) ^ 1;
       ok = mbar_wait(&a_empty[slot], par, a.err);
+      if (warp == ST_EPI) STRACE(itc, 3 * ch + 1);
       uint8_t* hi = a_ring + slot * A_SLOT;
       uint8_t* lo = hi + A_IMG;
 #pragma unroll
@@ -140,6 +159,7 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&a_full[slot]);
+      if (warp == ST_EPI) STRACE(itc, 3 * ch + 2);
 #pragma unroll
       for (int u = 0; u < 8; ++u) cur[u] = nxt[u];
       ++s; t = tn; ch = chn;
@@ -147,15 +167,18 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
   } else if (warp == ST_EPI + ST_CONV) {
     // ---- TMA producer: the packed B chunks, once per tile
     uint32_t s = 0;
-    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x) {
+    int itt = 0;
+    for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++itt) {
       for (int ch = 0; ch < a.nch && ok; ++ch, ++s) {
         const uint32_t slot = s % NB, par = ((s / NB) & 1) ^ 1;
         ok = mbar_wait(&b_empty[slot], par, a.err);
+        STRACE(itt, 36 + 2 * ch);
         if (ok && elect_one()) {
           mbar_arrive_expect_tx(&b_full[slot], B_SLOT);
           bulk_g2s(b_ring + slot * B_SLOT, g_stream_b + (size_t)ch * B_SLOT, B_SLOT, &b_full[slot]);
         }
         __syncwarp();
+        STRACE(itt, 37 + 2 * ch);
       }
     }
   } else if (warp == ST_EPI + ST_CONV + 1) {
@@ -169,13 +192,16 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
       const uint32_t buf = it & 1;
       ok = __all_sync(0xFFFFFFFFu, mbar_wait(&acc_empty[buf], ((it >> 1) & 1) ^ 1, a.err));    // the epilogue has drained it
       tc_fence_after();
+      STRACE(it, 31);
       const uint32_t acc = tmem_u + buf * 256u;
 #pragma unroll 1
       for (int ch = 0; ch < a.nch && ok; ++ch, ++sa, ++sb) {
         const uint32_t slot_a = sa % NA, slot_b = sb % NB;
         ok = __all_sync(0xFFFFFFFFu, mbar_wait(&a_full[slot_a], (sa / NA) & 1, a.err));
+        STRACE(it, 16 + 3 * ch);
         ok = ok && __all_sync(0xFFFFFFFFu, mbar_wait(&b_full[slot_b], (sb / NB) & 1, a.err));
         tc_fence_after();
+        STRACE(it, 17 + 3 * ch);
         const uint64_t ah = a_desc0 + (uint64_t)((slot_a * (uint32_t)A_SLOT) >> 4), al = ah + (uint64_t)(A_IMG >> 4);
         const uint64_t bh = b_desc0 + (uint64_t)((slot_b * (uint32_t)B_SLOT) >> 4), bl = bh + (uint64_t)(B_IMG >> 4);
         if (ok && elect_one()) {
@@ -189,9 +215,11 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
           umma_commit(&b_empty[slot_b]);
         }
         __syncwarp();
+        STRACE(it, 18 + 3 * ch);
       }
       if (ok && elect_one()) umma_commit(&acc_full[buf]);
       __syncwarp();
+      STRACE(it, 32);
     }
   } else {
     // ---- epilogue warps: TMEM lane quarter = warp.  tcgen05.ld hands a thread 32 columns of ONE row; stored like that, a
@@ -202,12 +230,19 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
     const int q = warp & 3, hf = warp >> 2;                       // TMEM lane quarter, column half [128 hf, 128 hf + 128)
     const int sub_r = lane >> 2, c4 = (lane & 3) * 4;             // after the turn: 4 lanes cover 64 contiguous bytes of a row
     const bool one_bias_row = g.ld_bias == 0;
+    // every row pointer of C / mask / bias is 16-byte aligned at every column this lane touches, and there is at most one bias row
+    const bool fast_ptrs = ((reinterpret_cast<uintptr_t>(g.C) & 15) == 0) && ((g.ldc & 3) == 0) &&
+                           (!g.mask || (((reinterpret_cast<uintptr_t>(g.mask) & 15) == 0) && ((g.ld_mask & 3) == 0))) &&
+                           (!g.bias || (one_bias_row && (reinterpret_cast<uintptr_t>(g.bias) & 15) == 0));
+    const bool relu = g.relu != 0;
     uint32_t it = 0;
     for (int64_t t = blockIdx.x; t < ntiles && ok; t += gridDim.x, ++it) {
       const uint32_t buf = it & 1;
       ok = mbar_wait(&acc_full[buf], (it >> 1) & 1, a.err);
       tc_fence_after();
       if (!ok) break;
+      if (warp == 0) STRACE(it, 48);
+      if (warp == 4) STRACE(it, 50);
       const int64_t mw = t * ST_ROWS + q * 32 + sub_r;            // this lane's first row after the turn (then + 8 j)
       const uint32_t t0 = tmem + buf * 256u + ((uint32_t)(q * 32) << 16) + hf * 128;
       const int nb = min(8, max(0, (a.nmma - hf * 128 + 15) / 16));
@@ -226,6 +261,24 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
         if (g.bias && one_bias_row && n_ok) bv = __ldg(reinterpret_cast<const float4*>(g.bias + n));
         float* cp = g.C + mw * g.ldc + n;
         const float* mp = g.mask ? g.mask + mw * g.ld_mask + n : nullptr;
+        // interior block of aligned operands with one bias row (every block of a 256-wide layer): no per-element checks
+        if (fast_ptrs && n_ok && mw - sub_r + 32 <= g.M && !g.accumulate) {
+          const int64_t cstep = 8 * g.ldc, mstep = 8 * g.ld_mask;
+#pragma unroll
+          for (int j = 0; j < 4; ++j, cp += cstep) {
+            const float4 acc = *reinterpret_cast<const float4*>(stg + (sub_r + 8 * j) * ST_STG_LD + c4);
+            float4 x = make_float4(acc.x + bv.x, acc.y + bv.y, acc.z + bv.z, acc.w + bv.w);
+            if (relu) { x.x = fmaxf(x.x, 0.f); x.y = fmaxf(x.y, 0.f); x.z = fmaxf(x.z, 0.f); x.w = fmaxf(x.w, 0.f); }
+            if (mp) {
+              const float4 k = __ldg(reinterpret_cast<const float4*>(mp));
+              x.x = k.x > 0.f ? x.x : 0.f; x.y = k.y > 0.f ? x.y : 0.f; x.z = k.z > 0.f ? x.z : 0.f; x.w = k.w > 0.f ? x.w : 0.f;
+              mp += mstep;
+            }
+            *reinterpret_cast<float4*>(cp) = x;
+          }
+          __syncwarp();
+          return;
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j, cp += 8 * g.ldc, mp = mp ? mp + 8 * g.ld_mask : nullptr) {
           const int64_t m = mw + 8 * j;
@@ -274,6 +327,8 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
+      if (warp == 0) STRACE(it, 49);
+      if (warp == 4) STRACE(it, 51);
     }
   }
   tc_fence_before();
@@ -281,6 +336,12 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
   if (warp == ST_EPI + ST_CONV + 1) tmem_dealloc(tmem, 512);
 }
 }  // namespace
+
+extern "C" int cnrf_debug_stream_trace(long long* host_out64) {
+  if (!host_out64) return CNRF_E_NULL;
+  const cudaError_t e = cudaMemcpyFromSymbol(host_out64, g_stream_trace, sizeof(long long) * 64);
+  return e == cudaSuccess ? CNRF_OK : (int)e;
+}
 
 int cnrf_gemm_stream_error() {
   int v = 0;

@@ -440,6 +440,8 @@ int cnrf_debug_fwd_times(long long* host_out16, int reset);
 int cnrf_debug_fwd_trace(long long* host_out128);  /* [64] pair trace, then [16 images][4 events] of its layer 1 */
 /* The same for the vanilla-NeRF chain (flex_fwd_tc.cu, -DCNRF_FLEX_TIMERS): [18 layers][40 events] of block 0's 4th tile. */
 int cnrf_debug_flex_trace(long long* host_out720);
+/* ... and of the streaming GEMM (gemm_stream.cu, -DCNRF_STREAM_TIMERS): 64 stamps of block 0's 6th tile. */
+int cnrf_debug_stream_trace(long long* host_out64);
 double cnrf_debug_fwd_kernel_ms(int64_t min_rows, int64_t* launches, int64_t* rows);
 /* The same for any of the three tensor-core kernels: which = 0 forward chain, 1 backward-data chain, 2 weight gradients;
  * min_rows < 0 only queries. */
