@@ -68,10 +68,13 @@ __global__ void pack_b_kernel(const float* __restrict__ B, int64_t b_rs, int64_t
   }
 }
 
+// hi = bf16(v) (round to nearest), lo = bf16(v - hi): packed conversions (one F2FP per pair; the scalar F2F.BF16 is a
+// quarter-rate instruction and was the converters' hottest line in ncu), hi read back as a float by shifting
 __device__ __forceinline__ void store_hi_lo(uint8_t* hi, uint8_t* lo, uint32_t off, const float4 v) {
-  const float hx = __bfloat162float(__float2bfloat16(v.x)), hy = __bfloat162float(__float2bfloat16(v.y));
-  const float hz = __bfloat162float(__float2bfloat16(v.z)), hw = __bfloat162float(__float2bfloat16(v.w));
-  *reinterpret_cast<uint2*>(hi + off) = make_uint2(pack_bf16(hx, hy), pack_bf16(hz, hw));
+  const uint32_t h01 = pack_bf16(v.x, v.y), h23 = pack_bf16(v.z, v.w);
+  const float hx = __uint_as_float(h01 << 16), hy = __uint_as_float(h01 & 0xFFFF0000u);
+  const float hz = __uint_as_float(h23 << 16), hw = __uint_as_float(h23 & 0xFFFF0000u);
+  *reinterpret_cast<uint2*>(hi + off) = make_uint2(h01, h23);
   *reinterpret_cast<uint2*>(lo + off) = make_uint2(pack_bf16(v.x - hx, v.y - hy), pack_bf16(v.z - hz, v.w - hw));
 }
 
@@ -225,7 +228,9 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
     // ---- epilogue warps: TMEM lane quarter = warp.  tcgen05.ld hands a thread 32 columns of ONE row; stored like that, a
     // warp's 16-byte stores hit 32 different rows (32 half-used sectors per instruction: the kernel sat at 2 TB/s of output).
     // Eight warps (two per lane quarter, 128 columns each) turn [32 rows x 16 columns] blocks through private staging areas:
-    // four lanes then cover 64 contiguous bytes of a row, and bias / mask / C are read and written as whole sectors.
+    // four lanes then cover 64 contiguous bytes of a row, and bias / mask / C are read and written as whole sectors.  (Measured
+    // and not kept: four warps turning [32 x 32] blocks, i.e. whole 128-byte lines -- 445 against 415 us for a 786k x 256 x 256
+    // layer; the bias row preloaded into registers with the block loop unrolled -- 443 us.)
     float* stg = reinterpret_cast<float*>(smem + NA * A_SLOT + NB * B_SLOT + 256) + warp * (32 * ST_STG_LD);
     const int q = warp & 3, hf = warp >> 2;                       // TMEM lane quarter, column half [128 hf, 128 hf + 128)
     const int sub_r = lane >> 2, c4 = (lane & 3) * 4;             // after the turn: 4 lanes cover 64 contiguous bytes of a row
@@ -258,7 +263,8 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
         const int n = hf * 128 + cb * 16 + c4;
         float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool n_ok = n + 3 < g.N;
-        if (g.bias && one_bias_row && n_ok) bv = __ldg(reinterpret_cast<const float4*>(g.bias + n));
+        if (g.bias && one_bias_row && n_ok && (reinterpret_cast<uintptr_t>(g.bias) & 15) == 0)
+          bv = __ldg(reinterpret_cast<const float4*>(g.bias + n));
         float* cp = g.C + mw * g.ldc + n;
         const float* mp = g.mask ? g.mask + mw * g.ld_mask + n : nullptr;
         // interior block of aligned operands with one bias row (every block of a 256-wide layer): no per-element checks

@@ -22,7 +22,7 @@ def run(N, K, form, reps=10):
     err = float((out - ref).abs().max() / ref.abs().max())
     gb = (M * K + M * N) * 4 / 1e9 if form == "lin" else (M * N + M * K) * 4 / 1e9
     print(f"{form:6s} M={M} N={N} K={K}: {us:.1f} us  {2 * M * N * K / us / 1e6:.0f} TFLOP/s  {gb / us * 1e6:.0f} GB/s  max rel err {err:.1e}")
-run(256, 256, "lin"); run(256, 256, "dgrad"); run(128, 256, "lin"); run(256, 64, "lin")
+run(256, 64, "lin"); run(128, 256, "lin"); run(256, 256, "dgrad"); run(256, 256, "lin")
 buf = (C.c_longlong * 64)()
 lib.cnrf_debug_stream_trace(C.cast(buf, C.c_void_p))
 tr = list(buf)
