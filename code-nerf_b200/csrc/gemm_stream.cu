@@ -343,6 +343,190 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
 }
 }  // namespace
 
+// ---- the same idea for weight gradients: C[m, n] += sum over ROWS r of A(m, r) B(r, n), A(m, r) = dY[r][m], B(r, n) = X[r][n] ------
+// Both operands stream (hundreds of thousands of rows, <= 256 columns each); the accumulators never leave TMEM: two
+// [128 x N] halves of dW, added to C once per CTA at the end (C is zero-filled by the caller, as for every split-K GEMM here).
+// Chunks of 32 rows; an operand chunk [32 x 256] is stored as an MN-major image (rows = the contraction index, four slabs of 64
+// columns, 128-byte swizzle -- the layout gemm_tc.cu uses for its MN-major operands), hi and lo.
+namespace {
+constexpr int WG_KC = 32;
+constexpr int WG_SLAB = WG_KC * 128;             // [32 rows x 64 columns] bf16
+constexpr int WG_IMG = 4 * WG_SLAB;              // 256 columns: 16 KB
+constexpr int WG_SLOT = 4 * WG_IMG;              // A hi | A lo | B hi | B lo
+constexpr int WG_NS = 3;
+constexpr int WG_CONV = 8;
+constexpr int WG_THREADS = 32 * (WG_CONV + 1);   // 0-7 converters (and the final reduction), 8 = MMA
+constexpr int WG_SMEM = WG_NS * WG_SLOT + 256 + 1024;
+
+struct WgradArgs {
+  GemmArgs g;
+  int nmma;              // N rounded up to 16
+  int a_vec, b_vec;      // operand rows are 16-byte aligned
+  int* err;
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1) gemm_stream_wgrad_kernel(const __grid_constant__ WgradArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + WG_NS * WG_SLOT);
+  uint64_t *full = bars, *empty = bars + WG_NS, *done = bars + 2 * WG_NS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const GemmArgs& g = a.g;
+  if (tid == 0) {
+    for (int i = 0; i < WG_NS; ++i) { mbar_init(&full[i], WG_CONV); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    mbar_fence_init();
+  }
+  if (warp == WG_CONV) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const int64_t nchunks = (g.K + WG_KC - 1) / WG_KC;
+  const int64_t mine = blockIdx.x < nchunks ? (nchunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;   // chunks of this CTA
+  const int mhalves = g.M > 128 ? 2 : 1;
+  bool ok = true;
+
+  if (warp < WG_CONV) {
+    // ---- converters: thread = (row rr + 4 u of the chunk, float4 column group c)
+    const int rr = tid >> 6, c = (tid & 63) * 4;
+    const uint32_t cofs = (uint32_t)(c >> 6) * WG_SLAB;
+    auto load = [&](int64_t q, float4 (&va)[8], float4 (&vb)[8]) {
+      const int64_t r0 = (blockIdx.x + q * gridDim.x) * WG_KC + rr;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int64_t r = r0 + 4 * u;
+        va[u] = vb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < g.K) {
+          if (c < g.M) {
+            const float* p = g.A + r * g.a_cs + c;
+            if (a.a_vec && c + 3 < g.M) va[u] = __ldg(reinterpret_cast<const float4*>(p));
+            else { va[u].x = __ldg(p); if (c + 1 < g.M) va[u].y = __ldg(p + 1); if (c + 2 < g.M) va[u].z = __ldg(p + 2); if (c + 3 < g.M) va[u].w = __ldg(p + 3); }
+          }
+          if (c < g.N) {
+            const float* p = g.B + r * g.b_rs + c;
+            if (a.b_vec && c + 3 < g.N) vb[u] = __ldg(reinterpret_cast<const float4*>(p));
+            else { vb[u].x = __ldg(p); if (c + 1 < g.N) vb[u].y = __ldg(p + 1); if (c + 2 < g.N) vb[u].z = __ldg(p + 2); if (c + 3 < g.N) vb[u].w = __ldg(p + 3); }
+          }
+        }
+      }
+    };
+    float4 ca[8], cb[8], na[8], nb[8];
+    if (mine > 0) load(0, ca, cb);
+    for (int64_t q = 0; q < mine && ok; ++q) {
+      if (q + 1 < mine) load(q + 1, na, nb);                     // next chunk's loads under this one's conversion
+      const uint32_t slot = (uint32_t)(q % WG_NS), par = (uint32_t)((q / WG_NS) & 1) ^ 1;
+      ok = mbar_wait(&empty[slot], par, a.err);
+      uint8_t* base = smem + slot * WG_SLOT;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const uint32_t off = cofs + slab_offset(rr + 4 * u, c & 63);
+        store_hi_lo(base, base + WG_IMG, off, ca[u]);
+        store_hi_lo(base + 2 * WG_IMG, base + 3 * WG_IMG, off, cb[u]);
+      }
+      fence_proxy_async();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[slot]);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { ca[u] = na[u]; cb[u] = nb[u]; }
+    }
+    // ---- final reduction: warp = (TMEM lane quarter, M half); a thread adds one row of its half into C
+    if (mine > 0 && ok) {
+      ok = mbar_wait(done, 0, a.err);
+      tc_fence_after();
+      const int q4 = warp & 3, hf = warp >> 2;
+      const int64_t m = hf * 128 + q4 * 32 + lane;
+      if (ok && hf < mhalves) {
+        float* crow = g.C + m * g.ldc;
+        const bool al16 = (reinterpret_cast<uintptr_t>(crow) & 15) == 0;
+        const uint32_t t0 = tmem + hf * 256u + ((uint32_t)(q4 * 32) << 16);
+#pragma unroll 1
+        for (int cbk = 0; cbk < (a.nmma + 31) / 32; ++cbk) {
+          uint32_t v[32];
+          tmem_ld32(t0 + cbk * 32, v);
+          tmem_ld_wait();
+          if (m < g.M) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const int n = cbk * 32 + j;
+              if (n >= g.N) break;
+              if (al16 && n + 3 < g.N) {
+                atomicAdd(reinterpret_cast<float4*>(crow + n), make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                                         __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+              } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (n + i < g.N) atomicAdd(crow + n + i, __uint_as_float(v[j + i]));
+              }
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ---- MMA issuer
+    const uint32_t tmem_u = __shfl_sync(0xFFFFFFFFu, tmem, 0);
+    const uint64_t desc0 = smem_desc(smem_u32(smem), WG_SLAB, 1024, SWIZZLE_128B);       // MN-major: LBO = slab stride
+    const uint32_t idesc = idesc_bf16(128, a.nmma, 1, 1);
+#pragma unroll 1
+    for (int64_t q = 0; q < mine && ok; ++q) {
+      const uint32_t slot = (uint32_t)(q % WG_NS);
+      ok = __all_sync(0xFFFFFFFFu, mbar_wait(&full[slot], (uint32_t)((q / WG_NS) & 1), a.err));
+      tc_fence_after();
+      const uint64_t ah = desc0 + (uint64_t)((slot * (uint32_t)WG_SLOT) >> 4), al = ah + (uint64_t)(WG_IMG >> 4);
+      const uint64_t bh = ah + (uint64_t)((2 * WG_IMG) >> 4), bl = ah + (uint64_t)((3 * WG_IMG) >> 4);
+      if (ok && elect_one()) {
+        for (int mh = 0; mh < mhalves; ++mh) {
+          const uint32_t acc = tmem_u + mh * 256u;
+          const uint64_t mo = (uint64_t)((mh * 2 * WG_SLAB) >> 4);                       // columns 128 mh ..: two slabs on
+          const uint32_t first = q == 0 ? 0u : 1u;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) umma_bf16(acc, ah + mo + 128 * j, bh + 128 * j, idesc, j == 0 ? first : 1u);   // hi * hi
+#pragma unroll
+          for (int j = 0; j < 2; ++j) umma_bf16(acc, ah + mo + 128 * j, bl + 128 * j, idesc, 1u);                   // hi * lo
+#pragma unroll
+          for (int j = 0; j < 2; ++j) umma_bf16(acc, al + mo + 128 * j, bh + 128 * j, idesc, 1u);                   // lo * hi
+        }
+        umma_commit(&empty[slot]);
+      }
+      __syncwarp();
+    }
+    if (ok && mine > 0 && elect_one()) umma_commit(done);
+    __syncwarp();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WG_CONV) tmem_dealloc(tmem, 512);
+}
+}  // namespace
+
+// dW-shaped problems: A(m, k) = A[m + k * a_cs], B(k, n) = B[k * b_rs + n], partial sums added atomically into C
+int cnrf_gemm_stream_wgrad(const GemmArgs& g, cudaStream_t st) {
+  static const bool off = getenv("CNRF_GEMM_NO_STREAM") != nullptr;
+  if (off || !g.A || !g.B || !g.C) return CNRF_E_UNSUPPORTED;
+  if (g.rows_dev || g.k_slice > 0 || g.a_rs != 1 || g.b_cs != 1 || !(g.split_k > 1 || g.accumulate)) return CNRF_E_UNSUPPORTED;
+  if (g.bias || g.relu || g.mask) return CNRF_E_UNSUPPORTED;
+  if (g.M < 16 || g.M > 256 || g.N < 16 || g.N > 256 || g.K < (int64_t)296 * 128) return CNRF_E_UNSUPPORTED;
+  WgradArgs a = {};
+  a.g = g;
+  a.nmma = (g.N + 15) & ~15;
+  a.a_vec = ((reinterpret_cast<uintptr_t>(g.A) & 15) == 0) && ((g.a_cs & 3) == 0);
+  a.b_vec = ((reinterpret_cast<uintptr_t>(g.B) & 15) == 0) && ((g.b_rs & 3) == 0);
+  cudaGetSymbolAddress(reinterpret_cast<void**>(&a.err), g_stream_error);
+  {
+    static bool attr_set[CNRF_MAX_DEVICES] = {};
+    const cudaError_t e = cnrf_once_per_device(attr_set, [] {
+      return cudaFuncSetAttribute(gemm_stream_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM); });
+    if (e != cudaSuccess) return (int)e;
+  }
+  const int64_t nchunks = (g.K + WG_KC - 1) / WG_KC;
+  const int grid = (int)std::min<int64_t>(nchunks, cnrf_sm_count());
+  gemm_stream_wgrad_kernel<<<grid, WG_THREADS, WG_SMEM, st>>>(a);
+  CNRF_LAUNCH_CHECK();
+  return CNRF_OK;
+}
+
 extern "C" int cnrf_debug_stream_trace(long long* host_out64) {
   if (!host_out64) return CNRF_E_NULL;
   const cudaError_t e = cudaMemcpyFromSymbol(host_out64, g_stream_trace, sizeof(long long) * 64);
@@ -359,6 +543,7 @@ int cnrf_gemm_stream_error() {
 int cnrf_gemm_stream(const GemmArgs& g, cudaStream_t st) {
   static const bool off = getenv("CNRF_GEMM_NO_STREAM") != nullptr;         // A/B switch
   if (off || !g.A || !g.B || !g.C) return CNRF_E_UNSUPPORTED;
+  if (g.a_rs == 1 && g.a_cs != 1) return cnrf_gemm_stream_wgrad(g, st);                 // contraction over rows: weight gradients
   if (g.rows_dev || g.split_k > 1 || g.k_slice > 0 || g.a_cs != 1) return CNRF_E_UNSUPPORTED;
   if (g.N < 64 || g.N > 256 || g.K < 16 || g.K > ST_MAXCH * ST_KC || g.M < 296 * 128) return CNRF_E_UNSUPPORTED;
   if (g.b_rs != 1 && g.b_cs != 1) return CNRF_E_UNSUPPORTED;

@@ -11,6 +11,7 @@ def run(N, K, form, reps=10):
     st = C.c_void_p(torch.cuda.current_stream().cuda_stream); p = lambda t: C.c_void_p(t.data_ptr())
     if form == "lin":   out = torch.zeros(M, N, device=dev); f = lambda: lib.cnrf_debug_gemm(1, p(X), K, 1, p(W), 1, K, p(out), N, M, N, K, 0, st)
     if form == "dgrad": out = torch.zeros(M, K, device=dev); f = lambda: lib.cnrf_debug_gemm(1, p(dY), N, 1, p(W), K, 1, p(out), K, M, K, N, 0, st)
+    if form == "wgrad": out = torch.zeros(N, K, device=dev); f = lambda: lib.cnrf_debug_gemm(1, p(dY), 1, N, p(X), K, 1, p(out), K, N, K, M, 1, st)
     for _ in range(2): f()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -18,11 +19,17 @@ def run(N, K, form, reps=10):
     for _ in range(reps): f()
     e1.record(); torch.cuda.synchronize()
     us = e0.elapsed_time(e1) / reps * 1e3
+    if form == "wgrad":
+        out.zero_(); f(); torch.cuda.synchronize()
+        ref = dY.double().t() @ X.double()
+        err = float((out.double() - ref).abs().max() / ref.abs().max())
+        print(f"{form:6s} M={M} N={N} K={K}: {us:.1f} us  {2 * M * N * K / us / 1e6:.0f} TFLOP/s  {(M * K + M * N) * 4 / 1e9 / us * 1e6:.0f} GB/s  max rel err {err:.1e}")
+        return
     ref = (X @ W.t()) if form == "lin" else (dY @ W)
     err = float((out - ref).abs().max() / ref.abs().max())
     gb = (M * K + M * N) * 4 / 1e9 if form == "lin" else (M * N + M * K) * 4 / 1e9
     print(f"{form:6s} M={M} N={N} K={K}: {us:.1f} us  {2 * M * N * K / us / 1e6:.0f} TFLOP/s  {gb / us * 1e6:.0f} GB/s  max rel err {err:.1e}")
-run(256, 64, "lin"); run(128, 256, "lin"); run(256, 256, "dgrad"); run(256, 256, "lin")
+run(256, 64, "lin"); run(128, 256, "lin"); run(256, 256, "dgrad"); run(256, 256, "lin"); run(256, 256, "wgrad"); run(128, 256, "wgrad"); run(256, 64, "wgrad")
 buf = (C.c_longlong * 64)()
 lib.cnrf_debug_stream_trace(C.cast(buf, C.c_void_p))
 tr = list(buf)
