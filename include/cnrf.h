@@ -244,8 +244,9 @@ int cnrf_field_bwd_ids(const cnrf_field_shape* s, const cnrf_codenerf_params* p,
  * pairing assigns rows to samples -- the view-direction half of layers_dir[0] is evaluated once per ray and enters the
  * per-sample layer as a bias row), M = num_rays * num_samples.  FlexibleNeRFModel.forward(x) on an already-embedded
  * [M, dim_xyz+dim_dir] tensor is the case num_rays = M, num_samples = 1.  Every layer is one GEMM of the per-ray toolkit
- * (sgemm.cu in CNRF_PRECISION_FP32, gemm_tc.cu split-bf16 tcgen05 in CNRF_PRECISION_BF16); bf16 inference at hidden 256
- * runs as one fused tcgen05 chain (flex_fwd_tc.cu).
+ * (sgemm.cu in CNRF_PRECISION_FP32; split-bf16 tcgen05 in CNRF_PRECISION_BF16: gemm_stream.cu for the big per-sample
+ * layers and their gradients, gemm_tc.cu for the rest); bf16 inference at hidden 256 runs as one fused tcgen05 chain
+ * (flex_fwd_tc.cu).
  * dim_dir == 0 selects the use_viewdirs=False network (models/model.py:47-48,75-76): raw = fc_out h, fc_out [4,H] / [4]
  * passed (and its gradient returned) in w_rgb / b_rgb; x_dir may be NULL and fc_feat / layers_dir / fc_alpha are not read.
  * ---------------------------------------------------------------------------------------------------- */
