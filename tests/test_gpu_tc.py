@@ -185,6 +185,31 @@ def test_gemm_tc_forms(dev, M, N, K):
     assert _lib.load().cnrf_debug_tc_error() == 0
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K", [(40001, 256, 256), (37888, 128, 319), (50000, 256, 63), (65536, 64, 128), (39000, 256, 100)])
+def test_gemm_stream_forms(dev, M, N, K, monkeypatch):
+    """The persistent streaming kernels of the big per-sample layers (gemm_stream.cu: >= 296 row tiles): X W^T, dY W and
+    dY^T X at a ragged last tile, a K tail (319 = five chunks, 63 and 100 = one and two partial chunks), rows that are not
+    16-byte aligned (leading dimension 319 / 63), 64- and 128-wide outputs, C += ...; against fp64 products.  Split-bf16:
+    ~16 mantissa bits per product; the weight-gradient form accumulates a CTA's whole row range in fp32 TMEM."""
+    g = torch.Generator(device="cpu").manual_seed(M + N * 3 + K)
+    X, W = torch.randn(M, K, generator=g).to(dev), torch.randn(N, K, generator=g).to(dev)
+    dY = torch.randn(M, N, generator=g).to(dev)
+    rel = lambda got, ref: float((got.double() - ref).abs().max() / ref.abs().max())
+    lin = _gemm(dev, 1, X, K, 1, W, 1, K, M, N, K)
+    assert rel(lin, X.double() @ W.double().t()) < 3e-5
+    dx = _gemm(dev, 1, dY, N, 1, W, K, 1, M, K, N) if K >= 64 else None            # N (here K columns) >= 64 for the stream
+    if dx is not None:
+        assert rel(dx, dY.double() @ W.double()) < 3e-5
+    acc = torch.full((M, N), 0.5, device=dev)
+    lin2 = _gemm(dev, 1, X, K, 1, W, 1, K, M, N, K, C=acc, accumulate=1)             # C += X W^T
+    assert rel(lin2, 0.5 + X.double() @ W.double().t()) < 3e-5
+    dw = _gemm(dev, 1, dY, 1, N, X, K, 1, N, K, M, C=torch.ones(N, K, device=dev), accumulate=1)
+    assert rel(dw, 1.0 + dY.double().t() @ X.double()) < 1e-4
+    from codenerf_b200 import _lib
+    assert _lib.load().cnrf_debug_tc_error() == 0
+
+
 # ---- shared latent codes (code_runs.cu, cnrf_field_*_ids) against the per-ray code path -------------------------------
 def _id_patterns(N, num_codes, g):
     runs = torch.randint(0, num_codes, (N,), generator=g)
