@@ -254,12 +254,15 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
       uint32_t va[16], vb[16];
       if (nb > 0) tmem_ld16(t0, va);
       auto block = [&](int cb, const uint32_t (&w)[16], uint32_t (&next)[16]) {
+        if (warp == 0 && cb == 2) STRACE(it, 52);
         tmem_ld_wait();
+        if (warp == 0 && cb == 2) STRACE(it, 53);
 #pragma unroll
         for (int j = 0; j < 4; ++j)
           *reinterpret_cast<uint4*>(stg + lane * ST_STG_LD + 4 * j) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
         if (cb + 1 < nb) tmem_ld16(t0 + (cb + 1) * 16, next);                  // next block's load under this one's stores
         __syncwarp();
+        if (warp == 0 && cb == 2) STRACE(it, 54);
         const int n = hf * 128 + cb * 16 + c4;
         float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
         const bool n_ok = n + 3 < g.N;
@@ -282,7 +285,9 @@ __global__ void __launch_bounds__(ST_THREADS, 1) gemm_stream_kernel(const __grid
             }
             *reinterpret_cast<float4*>(cp) = x;
           }
+          if (warp == 0 && cb == 2) STRACE(it, 55);
           __syncwarp();
+          if (warp == 0 && cb == 2) STRACE(it, 56);
           return;
         }
 #pragma unroll

@@ -29,7 +29,7 @@ def run(N, K, form, reps=10):
     err = float((out - ref).abs().max() / ref.abs().max())
     gb = (M * K + M * N) * 4 / 1e9 if form == "lin" else (M * N + M * K) * 4 / 1e9
     print(f"{form:6s} M={M} N={N} K={K}: {us:.1f} us  {2 * M * N * K / us / 1e6:.0f} TFLOP/s  {gb / us * 1e6:.0f} GB/s  max rel err {err:.1e}")
-run(256, 64, "lin"); run(128, 256, "lin"); run(256, 256, "dgrad"); run(256, 256, "lin"); run(256, 256, "wgrad"); run(128, 256, "wgrad"); run(256, 64, "wgrad")
+run(256, 64, "lin"); run(128, 256, "lin"); run(256, 256, "dgrad"); run(256, 256, "wgrad"); run(256, 256, "lin")
 buf = (C.c_longlong * 64)()
 lib.cnrf_debug_stream_trace(C.cast(buf, C.c_void_p))
 tr = list(buf)
@@ -41,3 +41,5 @@ if any(tr):
         if tr[3 * ch] > 0:
             print(f"  chunk {ch}: conv loads_issued {r(3*ch)} slot_free {r(3*ch+1)} arrived {r(3*ch+2)} | mma A {r(16+3*ch)} B {r(17+3*ch)} issued {r(18+3*ch)} | tma free {r(36+2*ch)} issued {r(37+2*ch)}")
     print(f"  mma acc_free {r(31)} committed {r(32)} | epi w0 seen {r(48)} done {r(49)} | epi w4 seen {r(50)} done {r(51)}")
+    if tr[52] > 0:
+        print(f"  epi w0 block 2: start {r(52)} tmem_wait {tr[53]-tr[52]} stage+sync {tr[54]-tr[53]} turn+store {tr[55]-tr[54]} sync {tr[56]-tr[55]}")
