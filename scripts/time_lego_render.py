@@ -32,9 +32,10 @@ _, rd = ops.ray_bundle(pose, Hh, Ww, 1111.0, Ww / 2, Hh / 2, want_ro=False)
 rd = rd[:n_rays].contiguous()
 ro = pose[0, :3, 3].expand(rd.shape[0], 3).contiguous()
 res = {"workload": "lego.yml render: FlexibleNeRFModel 8x256 skip[4], 64+128 samples, chunks of 8192 rays", "rays": int(rd.shape[0])}
-for precision in ("bf16", "fp32"):
+for precision in ("bf16", "split", "fp32"):
     nerf.set_precision(precision)
-    rays = rd.shape[0] if precision == "bf16" else min(rd.shape[0], 8 * chunk)      # the fp32 SIMT chain is the parity mode
+    # fp32 = the CUDA-core parity mode; split = the same per-layer path on split-bf16 tensor-core GEMMs (fp32-grade accuracy)
+    rays = rd.shape[0] if precision == "bf16" else min(rd.shape[0], (32 if precision == "split" else 8) * chunk)
 
     def render():
         outs = []
