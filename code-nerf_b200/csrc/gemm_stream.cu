@@ -1,7 +1,7 @@
 // Streaming tcgen05 GEMM for the big per-SAMPLE layers that run outside a fused chain: vanilla-NeRF training (flexnerf.cu,
 // models/model.py:58-76 layer by layer) and the `split` pose chain (codenerf.cu, eval.py:129-168).  Same contract as
 // cnrf_sgemm / cnrf_gemm_tc (internal.h) for ONE problem
-//     C[m, n] = epi( sum_k A[m, k] B(k, n) ),   M = hundreds of thousands of sample rows,  64 <= N <= 256,  K <= 320,
+//     C[m, n] = epi( sum_k A[m, k] B(k, n) ),   M = hundreds of thousands of sample rows,  64 <= N <= 256,  K <= 512,
 // A row-major (a_cs == 1), B a weight matrix of either majorness, split-bf16 like gemm_tc.cu (hi*hi + hi*lo + lo*hi in fp32
 // TMEM: ~16 mantissa bits).  gemm_tc_batch_kernel walks a CTA's K chunks serially -- load round trip, convert, MMA, wait --
 // and is latency-bound on these shapes (tensor pipe 10-17 %, ncu).  Here the roles are split and decoupled by rings:
@@ -21,7 +21,7 @@
 using namespace tc;
 
 namespace {
-constexpr int ST_ROWS = 128, ST_KC = 64, ST_MAXCH = 5;            // K <= 320
+constexpr int ST_ROWS = 128, ST_KC = 64, ST_MAXCH = 8;            // K <= 512 (the code-conditioned layers of the fp32-layout CodeNeRF chain)
 constexpr int A_IMG = ST_ROWS * 128, B_IMG = 256 * 128;           // one bf16 image of an A / B chunk: 16 KB / 32 KB
 constexpr int A_SLOT = 2 * A_IMG, B_SLOT = 2 * B_IMG;             // hi + lo
 constexpr int NA = 2, NB = 2;
@@ -30,7 +30,7 @@ constexpr int ST_THREADS = 32 * (ST_EPI + ST_CONV + 2);           // 0-7 epilogu
 constexpr int ST_STG_LD = 20;                                     // floats per staging row of 16 columns (80 B: 16-byte aligned)
 constexpr int ST_SMEM = NA * A_SLOT + NB * B_SLOT + 256 + ST_EPI * 32 * ST_STG_LD * 4 + 1024;
 
-__device__ uint8_t g_stream_b[ST_MAXCH * B_SLOT];                 // packed weights of the running call (320 KB)
+__device__ uint8_t g_stream_b[ST_MAXCH * B_SLOT];                 // packed weights of the running call (512 KB)
 __device__ int g_stream_error = 0;
 // Timer builds only (-DCNRF_STREAM_TIMERS): clock64 stamps of block 0's 6th tile: [0..] converter per chunk {loads issued, slot
 // free, arrived} at 0 + 3 ch; MMA per chunk {A seen, B seen, issued} at 16 + 3 ch, 31 accumulator free, 32 committed; TMA per

@@ -73,7 +73,7 @@ int cnrf_gemm_tc(const GemmArgs& a, cudaStream_t st);
 constexpr int CNRF_GEMM_BATCH_MAX = 24;     // (a 4.9 KB kernel parameter: CUDA >= 12.1 passes up to 32 KB)
 int cnrf_gemm_tc_batch(const GemmArgs* list, int count, cudaStream_t st);
 // gemm_stream.cu: persistent, pipelined split-bf16 GEMM for ONE big per-sample problem (M >= 296 x 128 rows, 64 <= N <= 256,
-// K <= 320, A row-major, B a weight matrix); CNRF_E_UNSUPPORTED otherwise.  cnrf_gemm_tc tries it first.
+// K <= 512, A row-major, B a weight matrix); CNRF_E_UNSUPPORTED otherwise.  cnrf_gemm_tc tries it first.
 int cnrf_gemm_stream(const GemmArgs& a, cudaStream_t st);
 int cnrf_gemm_stream_error();
 // one launch: dst[i][0..n[i]) = value[i]  (zero-filling gradient buffers, ones vectors)

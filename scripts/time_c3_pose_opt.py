@@ -110,6 +110,9 @@ def eager_reference():
     return {"s_per_iteration": s, "rays_per_s": n_rays / s}
 
 
+if os.environ.get("C3_ONLY"):          # launch lists: one mode only, e.g. C3_ONLY=split under ncu
+    print(json.dumps(drop_in(os.environ["C3_ONLY"]), indent=1))
+    sys.exit(0)
 out = {"config": "C3: 2048 rays/iteration of a 128x128 view, 64+64 samples, codes + pose (theta, phi, rho) under AdamW, frozen networks",
        "iterations_timed": iters,
        "drop_in_fp32_pose_chain (CODENERF_POSE_GRAD_PRECISION=fp32: CUDA-core FMA)": drop_in("fp32"),
